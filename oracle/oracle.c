@@ -1,0 +1,1249 @@
+/*
+ * oracle.c -- TEST INFRASTRUCTURE ONLY.
+ *
+ * A plain-C CPU restatement of the duckdb-spatial hot path (bbox / Hilbert /
+ * R-tree bulk load / probe / refinement).  It is the checker the CUDA product
+ * path is compared against; nothing in the product (duckdb-spatial_b200/,
+ * include/) may link, import or execute this file.  Only tests/,
+ * __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs use it.
+ *
+ * Every function cites the reference file:line it restates (paths relative to
+ * /root/reference).  Parity pinning: see tests/test_oracle_golden.py (golden
+ * vectors of the reference's own sqllogictests) and oracle/ref_harness.cpp
+ * (the reference's own headers / FlatRTree compiled here into oracle/_ref/).
+ *
+ * Build: gcc -O2 -fPIC -shared -fopenmp -ffp-contract=off oracle.c -o _build/liboracle.so -lm
+ * -ffp-contract=off: the reference is built for baseline x86-64 (no FMA), see
+ * SURVEY.md appendix A.1.
+ */
+#include <math.h>
+#include <float.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+#define ORC_API __attribute__((visibility("default")))
+
+/* ------------------------------------------------------------------------------------------------
+ * pcg32 (setseq_xsh_rr_64_32), duckdb/third_party/pcg/pcg_random.hpp:1667,1870 and
+ * RandomEngine, duckdb/src/common/random_engine.cpp:20-63
+ * ---------------------------------------------------------------------------------------------- */
+#define PCG_MULT 6364136223846793005ULL
+#define PCG_INC 1442695040888963407ULL /* (721347520444481703 << 1) | 1, default stream */
+
+typedef struct {
+	uint64_t state;
+} orc_pcg32;
+
+static void pcg_seed(orc_pcg32 *g, uint64_t seed) {
+	/* engine(state): state_ = bump(state + increment()) */
+	g->state = (seed + PCG_INC) * PCG_MULT + PCG_INC;
+}
+
+static uint32_t pcg_next(orc_pcg32 *g) {
+	uint64_t old = g->state;
+	g->state = old * PCG_MULT + PCG_INC;
+	/* xsh_rr: xorshift high, random rotate */
+	uint32_t xs = (uint32_t)(((old >> 18u) ^ old) >> 27u);
+	uint32_t rot = (uint32_t)(old >> 59u);
+	return (xs >> rot) | (xs << ((-rot) & 31));
+}
+
+/* LCG skip-ahead (Brown, "Random number generation with arbitrary strides") */
+static void pcg_advance(orc_pcg32 *g, uint64_t delta) {
+	uint64_t cur_mult = PCG_MULT, cur_plus = PCG_INC, acc_mult = 1, acc_plus = 0;
+	while (delta > 0) {
+		if (delta & 1) {
+			acc_mult *= cur_mult;
+			acc_plus = acc_plus * cur_mult + cur_plus;
+		}
+		cur_plus = (cur_mult + 1) * cur_plus;
+		cur_mult *= cur_mult;
+		delta >>= 1;
+	}
+	g->state = acc_mult * g->state + acc_plus;
+}
+
+ORC_API uint32_t orc_pcg32_nth(uint64_t seed, uint64_t n) {
+	orc_pcg32 g;
+	pcg_seed(&g, seed);
+	pcg_advance(&g, n);
+	return pcg_next(&g);
+}
+
+/* ST_GeneratePoints, src/spatial/modules/main/spatial_functions_table.cpp:82-99:
+ * x = NextRandom32(min_x,max_x) then y, one generator; NextRandom32(min,max) = min + ldexp(u32,-32)*(max-min)
+ * (random_engine.cpp:50-58).  `skip` = number of points to skip first (2 draws each). */
+ORC_API void orc_generate_points(uint64_t seed, uint64_t skip, uint64_t n, double min_x, double min_y, double max_x,
+                                 double max_y, double *x, double *y) {
+	orc_pcg32 g;
+	pcg_seed(&g, seed);
+	if (skip) {
+		pcg_advance(&g, 2 * skip);
+	}
+	for (uint64_t i = 0; i < n; i++) {
+		x[i] = min_x + ldexp((double)pcg_next(&g), -32) * (max_x - min_x);
+		y[i] = min_y + ldexp((double)pcg_next(&g), -32) * (max_y - min_y);
+	}
+}
+
+/* raw u32 stream, used by the synthetic box/polygon generators of the harness */
+ORC_API void orc_pcg32_fill(uint64_t seed, uint64_t skip, uint64_t n, uint32_t *out) {
+	orc_pcg32 g;
+	pcg_seed(&g, seed);
+	if (skip) {
+		pcg_advance(&g, skip);
+	}
+	for (uint64_t i = 0; i < n; i++) {
+		out[i] = pcg_next(&g);
+	}
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * MathUtil::DoubleToFloatDown/Up, src/spatial/util/math.hpp:19-47
+ * ---------------------------------------------------------------------------------------------- */
+ORC_API float orc_double_to_float_down(double d) {
+	if (d > (double)FLT_MAX) {
+		return FLT_MAX;
+	}
+	if (d <= (double)-FLT_MAX) {
+		return -FLT_MAX;
+	}
+	float f = (float)d;
+	if ((double)f <= d) {
+		return f;
+	}
+	return nextafterf(f, -FLT_MAX);
+}
+
+ORC_API float orc_double_to_float_up(double d) {
+	if (d >= (double)FLT_MAX) {
+		return FLT_MAX;
+	}
+	if (d < (double)-FLT_MAX) {
+		return -FLT_MAX;
+	}
+	float f = (float)d;
+	if ((double)f >= d) {
+		return f;
+	}
+	return nextafterf(f, FLT_MAX);
+}
+
+/* POINT_2D -> BOX_2DF as done for point blobs, src/spatial/geometry/geometry_type.hpp:137-144 */
+ORC_API void orc_bbox_from_points(const double *x, const double *y, uint64_t n, float *box4) {
+	for (uint64_t i = 0; i < n; i++) {
+		box4[4 * i + 0] = orc_double_to_float_down(x[i]);
+		box4[4 * i + 1] = orc_double_to_float_down(y[i]);
+		box4[4 * i + 2] = orc_double_to_float_up(x[i]);
+		box4[4 * i + 3] = orc_double_to_float_up(y[i]);
+	}
+}
+
+ORC_API void orc_bbox_from_box2d(const double *minx, const double *miny, const double *maxx, const double *maxy,
+                                 uint64_t n, float *box4) {
+	for (uint64_t i = 0; i < n; i++) {
+		box4[4 * i + 0] = orc_double_to_float_down(minx[i]);
+		box4[4 * i + 1] = orc_double_to_float_down(miny[i]);
+		box4[4 * i + 2] = orc_double_to_float_up(maxx[i]);
+		box4[4 * i + 3] = orc_double_to_float_up(maxy[i]);
+	}
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * Serialized GEOMETRY writers. Serde::Serialize, src/spatial/geometry/geometry_serialization.cpp:188-242
+ * [u8 type][u8 flags][u16 0][u32 0] [bbox 4 floats iff flags&4] [u32 type][u32 count][payload]
+ * ---------------------------------------------------------------------------------------------- */
+static void put_u32(uint8_t *p, uint32_t v) {
+	memcpy(p, &v, 4);
+}
+static void put_f32(uint8_t *p, float v) {
+	memcpy(p, &v, 4);
+}
+static void put_f64(uint8_t *p, double v) {
+	memcpy(p, &v, 8);
+}
+
+/* POINT_2D -> GEOMETRY (spatial_functions_cast.cpp:228-242): 32-byte blobs, no bbox */
+ORC_API void orc_write_point_blobs(const double *x, const double *y, uint64_t n, uint8_t *out) {
+	for (uint64_t i = 0; i < n; i++) {
+		uint8_t *p = out + 32 * i;
+		memset(p, 0, 16);
+		put_u32(p + 8, 0);  /* serialized type POINT */
+		put_u32(p + 12, 1); /* vertex count */
+		put_f64(p + 16, x[i]);
+		put_f64(p + 24, y[i]);
+	}
+}
+
+/* ST_MakeEnvelope (spatial_functions_scalar.cpp:5755-5786): 5-vertex polygon, 120-byte blobs with bbox.
+ * vertex order (minx,miny) (minx,maxy) (maxx,maxy) (maxx,miny) (minx,miny) */
+ORC_API void orc_write_envelope_blobs(const double *minx, const double *miny, const double *maxx, const double *maxy,
+                                      uint64_t n, uint8_t *out) {
+	for (uint64_t i = 0; i < n; i++) {
+		uint8_t *p = out + 120 * i;
+		memset(p, 0, 120);
+		p[0] = 2; /* POLYGON */
+		p[1] = 0x04;
+		const double vx[5] = {minx[i], minx[i], maxx[i], maxx[i], minx[i]};
+		const double vy[5] = {miny[i], maxy[i], maxy[i], miny[i], miny[i]};
+		double bx0 = DBL_MAX, by0 = DBL_MAX, bx1 = -DBL_MAX, by1 = -DBL_MAX;
+		for (int k = 0; k < 5; k++) {
+			bx0 = vx[k] < bx0 ? vx[k] : bx0;
+			by0 = vy[k] < by0 ? vy[k] : by0;
+			bx1 = bx1 < vx[k] ? vx[k] : bx1;
+			by1 = by1 < vy[k] ? vy[k] : by1;
+		}
+		put_f32(p + 8, orc_double_to_float_down(bx0));
+		put_f32(p + 12, orc_double_to_float_down(by0));
+		put_f32(p + 16, orc_double_to_float_up(bx1));
+		put_f32(p + 20, orc_double_to_float_up(by1));
+		put_u32(p + 24, 2); /* POLYGON */
+		put_u32(p + 28, 1); /* ring count */
+		put_u32(p + 32, 5); /* ring 0 vertex count, then 4 bytes pad (odd ring count) */
+		for (int k = 0; k < 5; k++) {
+			put_f64(p + 40 + 16 * k, vx[k]);
+			put_f64(p + 48 + 16 * k, vy[k]);
+		}
+	}
+}
+
+/* single-ring polygons from a flat vertex array: ring i = vertices [voff[i], voff[i+1]) (already closed).
+ * out_off[i] receives the byte offset of blob i; returns total bytes. out may be NULL to size. */
+ORC_API uint64_t orc_write_polygon_blobs(const double *vx, const double *vy, const uint64_t *voff, uint64_t n,
+                                         uint8_t *out, uint64_t *out_off) {
+	uint64_t pos = 0;
+	for (uint64_t i = 0; i < n; i++) {
+		const uint64_t nv = voff[i + 1] - voff[i];
+		const uint64_t sz = 8 + 16 + 8 + 8 + 16 * nv;
+		if (out_off) {
+			out_off[i] = pos;
+		}
+		if (out) {
+			uint8_t *p = out + pos;
+			memset(p, 0, 40);
+			p[0] = 2;
+			p[1] = 0x04;
+			double bx0 = DBL_MAX, by0 = DBL_MAX, bx1 = -DBL_MAX, by1 = -DBL_MAX;
+			for (uint64_t k = 0; k < nv; k++) {
+				const double X = vx[voff[i] + k], Y = vy[voff[i] + k];
+				bx0 = X < bx0 ? X : bx0;
+				by0 = Y < by0 ? Y : by0;
+				bx1 = bx1 < X ? X : bx1;
+				by1 = by1 < Y ? Y : by1;
+				put_f64(p + 40 + 16 * k, X);
+				put_f64(p + 48 + 16 * k, Y);
+			}
+			put_f32(p + 8, orc_double_to_float_down(bx0));
+			put_f32(p + 12, orc_double_to_float_down(by0));
+			put_f32(p + 16, orc_double_to_float_up(bx1));
+			put_f32(p + 20, orc_double_to_float_up(by1));
+			put_u32(p + 24, 2);
+			put_u32(p + 28, 1);
+			put_u32(p + 32, (uint32_t)nv);
+		}
+		pos += sz;
+	}
+	if (out_off) {
+		out_off[n] = pos;
+	}
+	return pos;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * geometry_t::TryGetCachedBounds, src/spatial/geometry/geometry_type.hpp:102-148
+ * returns 1 = box written, 0 = no box (NULL), -1 = unsupported version (reference throws,
+ * geometry_properties.hpp:28-36), -2 = truncated blob (Cursor bounds check throws).
+ * ---------------------------------------------------------------------------------------------- */
+ORC_API int orc_cached_bounds(const uint8_t *blob, uint64_t len, float *box4) {
+	if (len < 4) {
+		return -2;
+	}
+	const uint8_t type = blob[0];
+	const uint8_t flags = blob[1];
+	if ((flags & 0xC0) != 0) {
+		return -1;
+	}
+	if (flags & 0x04) {
+		if (len < 24) {
+			return -2;
+		}
+		memcpy(box4, blob + 8, 16);
+		return 1;
+	}
+	if (type == 0) {
+		if (len < 16) {
+			return -2;
+		}
+		uint32_t count;
+		memcpy(&count, blob + 12, 4);
+		if (count == 0) {
+			return 0;
+		}
+		if (len < 32) {
+			return -2;
+		}
+		double x, y;
+		memcpy(&x, blob + 16, 8);
+		memcpy(&y, blob + 24, 8);
+		box4[0] = orc_double_to_float_down(x);
+		box4[1] = orc_double_to_float_down(y);
+		box4[2] = orc_double_to_float_up(x);
+		box4[3] = orc_double_to_float_up(y);
+		return 1;
+	}
+	return 0;
+}
+
+/* ST_Extent_Approx over a column, spatial_functions_scalar.cpp:2684-2724 */
+ORC_API void orc_bbox_from_blobs(const uint8_t *data, const uint64_t *off, uint64_t n, float *box4, uint8_t *valid,
+                                 int32_t *status) {
+	for (uint64_t i = 0; i < n; i++) {
+		float b[4] = {0, 0, 0, 0};
+		int r = orc_cached_bounds(data + off[i], off[i + 1] - off[i], b);
+		memcpy(box4 + 4 * i, b, 16);
+		valid[i] = r == 1;
+		if (status) {
+			status[i] = r < 0 ? r : 0;
+		}
+	}
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * ST_Extent(GEOMETRY): Serde::Deserialize (geometry_serialization.cpp:244-329) +
+ * sgl::ops::try_get_extent_xy (src/sgl/sgl.hpp:1408-1486). Polygons: shell ring only.
+ * std::min(a,b) = (b<a)?b:a ; std::max(a,b) = (a<b)?b:a  (NaN vertices never win).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+	const uint8_t *p;
+	const uint8_t *end;
+	int err;
+	uint32_t vsize;
+	double b[4];
+	int any;
+} ext_cur;
+
+static uint32_t cur_u32(ext_cur *c) {
+	if (c->end - c->p < 4) {
+		c->err = 1;
+		return 0;
+	}
+	uint32_t v;
+	memcpy(&v, c->p, 4);
+	c->p += 4;
+	return v;
+}
+
+static void ext_verts(ext_cur *c, uint32_t count, int use) {
+	if ((uint64_t)(c->end - c->p) < (uint64_t)count * c->vsize) {
+		c->err = 1;
+		return;
+	}
+	if (use) {
+		if (count > 0) {
+			c->any = 1;
+		}
+		for (uint32_t i = 0; i < count; i++) {
+			double X, Y;
+			memcpy(&X, c->p + (uint64_t)i * c->vsize, 8);
+			memcpy(&Y, c->p + (uint64_t)i * c->vsize + 8, 8);
+			c->b[0] = X < c->b[0] ? X : c->b[0];
+			c->b[1] = Y < c->b[1] ? Y : c->b[1];
+			c->b[2] = c->b[2] < X ? X : c->b[2];
+			c->b[3] = c->b[3] < Y ? Y : c->b[3];
+		}
+	}
+	c->p += (uint64_t)count * c->vsize;
+}
+
+static void ext_rec(ext_cur *c, uint32_t type, int depth) {
+	if (c->err || depth > 64) {
+		c->err = 1;
+		return;
+	}
+	const uint32_t count = cur_u32(c);
+	if (c->err) {
+		return;
+	}
+	switch (type) {
+	case 0:
+	case 1:
+		ext_verts(c, count, 1);
+		break;
+	case 2: {
+		ext_cur rc = *c;
+		const uint64_t skip = (uint64_t)count * 4 + (count % 2 == 1 ? 4 : 0);
+		if ((uint64_t)(c->end - c->p) < skip) {
+			c->err = 1;
+			return;
+		}
+		c->p += skip;
+		for (uint32_t i = 0; i < count && !c->err; i++) {
+			const uint32_t rcnt = cur_u32(&rc);
+			ext_verts(c, rcnt, i == 0);
+		}
+	} break;
+	case 3:
+	case 4:
+	case 5:
+	case 6:
+		for (uint32_t i = 0; i < count && !c->err; i++) {
+			const uint32_t pt = cur_u32(c);
+			ext_rec(c, pt, depth + 1);
+		}
+		break;
+	default:
+		c->err = 1;
+	}
+}
+
+/* returns 1 = extent written, 0 = NULL (no vertices), -1 = version, -2 = malformed */
+ORC_API int orc_extent_exact(const uint8_t *blob, uint64_t len, double *box4) {
+	if (len < 8) {
+		return -2;
+	}
+	const uint8_t flags = blob[1];
+	if (flags & 0xC0) {
+		return -1;
+	}
+	ext_cur c;
+	c.p = blob + 8;
+	c.end = blob + len;
+	c.err = 0;
+	c.any = 0;
+	c.vsize = 8 * (2 + ((flags & 1) ? 1 : 0) + ((flags & 2) ? 1 : 0));
+	c.b[0] = c.b[1] = DBL_MAX;
+	c.b[2] = c.b[3] = -DBL_MAX;
+	if (flags & 0x04) {
+		const uint64_t bs = 4 * 2 * (2 + ((flags & 1) ? 1 : 0) + ((flags & 2) ? 1 : 0));
+		if ((uint64_t)(c.end - c.p) < bs) {
+			return -2;
+		}
+		c.p += bs;
+	}
+	(void)cur_u32(&c); /* serialized type (same as header type) */
+	ext_rec(&c, blob[0], 0);
+	if (c.err) {
+		return -2;
+	}
+	if (!c.any) {
+		return 0;
+	}
+	memcpy(box4, c.b, 32);
+	return 1;
+}
+
+ORC_API void orc_extent_from_blobs(const uint8_t *data, const uint64_t *off, uint64_t n, double *box4,
+                                   uint8_t *valid, int32_t *status) {
+	for (uint64_t i = 0; i < n; i++) {
+		double b[4] = {0, 0, 0, 0};
+		int r = orc_extent_exact(data + off[i], off[i + 1] - off[i], b);
+		memcpy(box4 + 4 * i, b, 32);
+		valid[i] = r == 1;
+		if (status) {
+			status[i] = r < 0 ? r : 0;
+		}
+	}
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * Hilbert. sgl::util::hilbert_encode / hilbert_f32_to_u32, src/sgl/sgl.hpp:1791-1862
+ * (restated from the public-domain rawrunprotected/hilbert_curves prefix-scan formulation)
+ * ---------------------------------------------------------------------------------------------- */
+static uint32_t interleave16(uint32_t x) {
+	x = (x | (x << 8)) & 0x00FF00FFu;
+	x = (x | (x << 4)) & 0x0F0F0F0Fu;
+	x = (x | (x << 2)) & 0x33333333u;
+	x = (x | (x << 1)) & 0x55555555u;
+	return x;
+}
+
+ORC_API uint32_t orc_hilbert_encode(uint32_t n, uint32_t x, uint32_t y) {
+	x <<= (16 - n);
+	y <<= (16 - n);
+	uint32_t A, B, C, D;
+	{ /* round 0, primed with x and y */
+		const uint32_t a = x ^ y;
+		const uint32_t b = 0xFFFFu ^ a;
+		const uint32_t c = 0xFFFFu ^ (x | y);
+		const uint32_t d = x & (y ^ 0xFFFFu);
+		A = a | (b >> 1);
+		B = (a >> 1) ^ a;
+		C = ((c >> 1) ^ (b & (d >> 1))) ^ c;
+		D = ((a & (c >> 1)) ^ (d >> 1)) ^ d;
+	}
+	for (int s = 2; s <= 4; s <<= 1) { /* rounds with shift 2 and 4 */
+		const uint32_t a = A, b = B, c = C, d = D;
+		A = (a & (a >> s)) ^ (b & (b >> s));
+		B = (a & (b >> s)) ^ (b & ((a ^ b) >> s));
+		C ^= (a & (c >> s)) ^ (b & (d >> s));
+		D ^= (b & (c >> s)) ^ ((a ^ b) & (d >> s));
+	}
+	{ /* final round, shift 8, only C and D needed */
+		const uint32_t a = A, b = B, c = C, d = D;
+		C ^= (a & (c >> 8)) ^ (b & (d >> 8));
+		D ^= (b & (c >> 8)) ^ ((a ^ b) & (d >> 8));
+	}
+	const uint32_t a = C ^ (C >> 1);
+	const uint32_t b = D ^ (D >> 1);
+	const uint32_t i0 = x ^ y;
+	const uint32_t i1 = b | (0xFFFFu ^ (i0 | a));
+	return ((interleave16(i1) << 1) | interleave16(i0)) >> (32 - 2 * n);
+}
+
+ORC_API uint32_t orc_hilbert_f32_to_u32(float f) {
+	if (isnan(f)) {
+		return 0xFFFFFFFFu;
+	}
+	uint32_t r;
+	memcpy(&r, &f, 4);
+	return (r & 0x80000000u) ? (r ^ 0xFFFFFFFFu) : (r | 0x80000000u);
+}
+
+/* C float/double -> uint32 casts are UB out of range; the reference (x86-64, SSE2 cvttss2si/cvttsd2si to a
+ * 64-bit register then truncation) yields the low 32 bits of the int64 conversion, 0 for the
+ * "integer indefinite" 0x8000000000000000. Restated explicitly so the oracle is deterministic. */
+static uint32_t cast_f64_u32(double v) {
+	if (!(v > -9223372036854775808.0 && v < 9223372036854775808.0)) {
+		return 0u; /* low 32 bits of 0x8000000000000000 */
+	}
+	return (uint32_t)(uint64_t)(int64_t)v;
+}
+static uint32_t cast_f32_u32(float v) {
+	return cast_f64_u32((double)v);
+}
+
+/* ST_Hilbert(x, y, bounds BOX_2D), spatial_functions_scalar.cpp:5250-5268 */
+ORC_API void orc_hilbert_xy(const double *x, const double *y, uint64_t n, const double *bounds, uint32_t *out) {
+	for (uint64_t i = 0; i < n; i++) {
+		const double hw = 65535 / (bounds[2] - bounds[0]);
+		const double hh = 65535 / (bounds[3] - bounds[1]);
+		const uint32_t hx = cast_f64_u32((x[i] - bounds[0]) * hw);
+		const uint32_t hy = cast_f64_u32((y[i] - bounds[1]) * hh);
+		out[i] = orc_hilbert_encode(16, hx, hy);
+	}
+}
+
+/* ST_Hilbert(box BOX_2D, bounds BOX_2D), ExecuteBox<double>, :5216-5245. box4 = n x (minx,miny,maxx,maxy) */
+ORC_API void orc_hilbert_box2d(const double *box4, uint64_t n, const double *bounds, uint32_t *out) {
+	for (uint64_t i = 0; i < n; i++) {
+		const double *b = box4 + 4 * i;
+		const double x = b[0] + (b[2] - b[0]) / 2.0;
+		const double y = b[1] + (b[3] - b[1]) / 2.0;
+		const double hw = 65535 / (bounds[2] - bounds[0]);
+		const double hh = 65535 / (bounds[3] - bounds[1]);
+		out[i] = orc_hilbert_encode(16, cast_f64_u32((x - bounds[0]) * hw), cast_f64_u32((y - bounds[1]) * hh));
+	}
+}
+
+/* ST_Hilbert(box BOX_2DF, bounds BOX_2DF), ExecuteBox<float>: pure fp32 */
+ORC_API void orc_hilbert_box2df(const float *box4, uint64_t n, const float *bounds, uint32_t *out) {
+	for (uint64_t i = 0; i < n; i++) {
+		const float *b = box4 + 4 * i;
+		const float x = b[0] + (b[2] - b[0]) / 2.0f;
+		const float y = b[1] + (b[3] - b[1]) / 2.0f;
+		const float hw = 65535 / (bounds[2] - bounds[0]);
+		const float hh = 65535 / (bounds[3] - bounds[1]);
+		out[i] = orc_hilbert_encode(16, cast_f32_u32((x - bounds[0]) * hw), cast_f32_u32((y - bounds[1]) * hh));
+	}
+}
+
+/* ST_Hilbert(geom), ExecuteGeometry :5273-5293: centre of the cached float box -> f32_to_u32 (32-bit values
+ * fed into the 16-bit routine, n=16 => no pre-shift; bits above 16 leak through exactly as in the reference). */
+ORC_API void orc_hilbert_geom(const uint8_t *data, const uint64_t *off, uint64_t n, uint32_t *out, uint8_t *valid) {
+	for (uint64_t i = 0; i < n; i++) {
+		float b[4];
+		const int r = orc_cached_bounds(data + off[i], off[i + 1] - off[i], b);
+		valid[i] = r == 1;
+		out[i] = 0;
+		if (r == 1) {
+			const float dx = b[0] + (b[2] - b[0]) / 2;
+			const float dy = b[1] + (b[3] - b[1]) / 2;
+			out[i] = orc_hilbert_encode(16, orc_hilbert_f32_to_u32(dx), orc_hilbert_f32_to_u32(dy));
+		}
+	}
+}
+
+/* ST_Hilbert(geom, bounds BOX_2D), ExecuteGeometryWithBounds :5295-5325: exact fp64 extent centre.
+ * status[i] = 1 where the reference throws (empty geometry). */
+ORC_API void orc_hilbert_geom_bounds(const uint8_t *data, const uint64_t *off, uint64_t n, const double *bounds,
+                                     uint32_t *out, int32_t *status) {
+	for (uint64_t i = 0; i < n; i++) {
+		double b[4];
+		const int r = orc_extent_exact(data + off[i], off[i + 1] - off[i], b);
+		out[i] = 0;
+		status[i] = r == 1 ? 0 : (r == 0 ? 1 : r);
+		if (r == 1) {
+			const double dx = b[0] + (b[2] - b[0]) / 2;
+			const double dy = b[1] + (b[3] - b[1]) / 2;
+			const double hw = 65535 / (bounds[2] - bounds[0]);
+			const double hh = 65535 / (bounds[3] - bounds[1]);
+			out[i] = orc_hilbert_encode(16, cast_f64_u32((dx - bounds[0]) * hw), cast_f64_u32((dy - bounds[1]) * hh));
+		}
+	}
+}
+
+/* Box2D<float>::Intersects, src/spatial/geometry/bbox.hpp:27-29 (closed intervals) */
+static int box_intersects(const float *a, const float *b) {
+	return !(a[0] > b[2] || a[2] < b[0] || a[1] > b[3] || a[3] < b[1]);
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * STR bulk load of the persistent RTREE.
+ *   sort key     : ST_Centroid(BOX_2DF).x = double(float(minx)+float(maxx)) * 0.5,
+ *                  spatial_functions_scalar.cpp:1490-1494, planned at rtree_index_create_logical.cpp:101-133
+ *   slice size   : rtree_index_create_physical.cpp:349-351
+ *   packing      : BuildRTreeBottomUp, rtree_index_create_physical.cpp:136-256
+ * Tie-break (reference: unspecified, DuckDB sort / std::sort are unstable): x ties keep input order,
+ * y ties keep x order. Documented in DESIGN.md ("tie-break rule"); result sets do not depend on it.
+ *
+ * Tree layout produced (shared with the CUDA builder): level l = array of 24-byte entries
+ * {u64 ptr, float box[4]} in packed order; node j of level l = entries [j*cap, min((j+1)*cap, count_l));
+ * level 0 ptr = row id (node type ROW_ID=0 in bits 56..63, rtree.cpp:37-42), level l>0 ptr =
+ * (type<<56) | child node index in level l-1, type = LEAF_PAGE(1) for l==1 else BRANCH_PAGE(2).
+ * The last level has exactly one entry = the root entry (tree.SetRoot, :238-252).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+	uint64_t ptr;
+	float box[4];
+} orc_entry;
+
+typedef struct {
+	int nlevels;
+	uint64_t counts[16];
+	orc_entry *levels[16];
+	uint32_t cap;
+	uint64_t slice;
+} orc_rtree;
+
+typedef struct {
+	double key;
+	uint64_t pos;
+} keypos;
+
+static int cmp_keypos(const void *a, const void *b) {
+	const keypos *x = (const keypos *)a, *y = (const keypos *)b;
+	if (x->key < y->key) {
+		return -1;
+	}
+	if (x->key > y->key) {
+		return 1;
+	}
+	return x->pos < y->pos ? -1 : (x->pos > y->pos ? 1 : 0);
+}
+
+static int cmp_rowid(const void *a, const void *b) {
+	const int64_t x = (int64_t)((const orc_entry *)a)->ptr, y = (int64_t)((const orc_entry *)b)->ptr;
+	return x < y ? -1 : (x > y ? 1 : 0);
+}
+
+ORC_API uint64_t orc_str_slice_size(uint64_t n, uint32_t cap) {
+	return (uint64_t)ceil(sqrt((double)((n + cap - 1) / cap))) * cap;
+}
+
+ORC_API double orc_str_sort_key(const float *box) {
+	return (double)(box[0] + box[2]) * 0.5;
+}
+
+ORC_API orc_rtree *orc_rtree_build_str(const float *box4, const int64_t *rowid, uint64_t n, uint32_t cap) {
+	orc_rtree *t = (orc_rtree *)calloc(1, sizeof(orc_rtree));
+	t->cap = cap;
+	if (n == 0) {
+		return t;
+	}
+	t->slice = orc_str_slice_size(n, cap);
+	/* ORDER BY x-centre */
+	keypos *kp = (keypos *)malloc(sizeof(keypos) * n);
+	for (uint64_t i = 0; i < n; i++) {
+		kp[i].key = orc_str_sort_key(box4 + 4 * i);
+		kp[i].pos = i;
+	}
+	qsort(kp, n, sizeof(keypos), cmp_keypos);
+	orc_entry *cur = (orc_entry *)malloc(sizeof(orc_entry) * n);
+	for (uint64_t i = 0; i < n; i++) {
+		cur[i].ptr = (uint64_t)rowid[kp[i].pos] & 0x00FFFFFFFFFFFFFFULL;
+		memcpy(cur[i].box, box4 + 4 * kp[i].pos, 16);
+	}
+	free(kp);
+	uint64_t cnt = n;
+	int level = 0;
+	while (cnt != 1) {
+		/* sort each slice by fp32 y centre: bounds.Center().y = (min.y + max.y) / 2 in float (bbox.hpp:78-80) */
+		keypos *sk = (keypos *)malloc(sizeof(keypos) * cnt);
+		orc_entry *sorted = (orc_entry *)malloc(sizeof(orc_entry) * cnt);
+		for (uint64_t s = 0; s < cnt; s += t->slice) {
+			const uint64_t e = s + t->slice < cnt ? s + t->slice : cnt;
+			for (uint64_t i = s; i < e; i++) {
+				sk[i].key = (double)((cur[i].box[1] + cur[i].box[3]) / 2.0f);
+				sk[i].pos = i;
+			}
+			qsort(sk + s, e - s, sizeof(keypos), cmp_keypos);
+			for (uint64_t i = s; i < e; i++) {
+				sorted[i] = cur[sk[i].pos];
+			}
+		}
+		free(sk);
+		free(cur);
+		/* pack nodes of cap, leaf nodes sorted by row id (:201-204), node box = union (rtree_node.hpp:92-99) */
+		const uint64_t nn = (cnt + cap - 1) / cap;
+		orc_entry *next = (orc_entry *)malloc(sizeof(orc_entry) * nn);
+		for (uint64_t j = 0; j < nn; j++) {
+			const uint64_t b = j * cap, e = b + cap < cnt ? b + cap : cnt;
+			if (level == 0) {
+				qsort(sorted + b, e - b, sizeof(orc_entry), cmp_rowid);
+			}
+			float u[4] = {FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX};
+			for (uint64_t i = b; i < e; i++) {
+				const float *x = sorted[i].box;
+				u[0] = x[0] < u[0] ? x[0] : u[0];
+				u[1] = x[1] < u[1] ? x[1] : u[1];
+				u[2] = x[2] > u[2] ? x[2] : u[2];
+				u[3] = x[3] > u[3] ? x[3] : u[3];
+			}
+			next[j].ptr = ((uint64_t)(level == 0 ? 1 : 2) << 56) | j;
+			memcpy(next[j].box, u, 16);
+		}
+		t->levels[level] = sorted;
+		t->counts[level] = cnt;
+		level++;
+		cur = next;
+		cnt = nn;
+	}
+	if (level == 0) {
+		/* single row id: wrapped into a leaf page (:241-246) */
+		t->levels[0] = cur;
+		t->counts[0] = 1;
+		orc_entry *root = (orc_entry *)malloc(sizeof(orc_entry));
+		root->ptr = ((uint64_t)1 << 56) | 0;
+		memcpy(root->box, cur[0].box, 16);
+		t->levels[1] = root;
+		t->counts[1] = 1;
+		t->nlevels = 2;
+		return t;
+	}
+	t->levels[level] = cur;
+	t->counts[level] = 1;
+	t->nlevels = level + 1;
+	return t;
+}
+
+ORC_API void orc_rtree_free(orc_rtree *t) {
+	if (!t) {
+		return;
+	}
+	for (int i = 0; i < t->nlevels; i++) {
+		free(t->levels[i]);
+	}
+	free(t);
+}
+
+ORC_API int orc_rtree_nlevels(const orc_rtree *t) {
+	return t->nlevels;
+}
+ORC_API uint64_t orc_rtree_level_count(const orc_rtree *t, int l) {
+	return t->counts[l];
+}
+ORC_API const void *orc_rtree_level_entries(const orc_rtree *t, int l) {
+	return t->levels[l];
+}
+ORC_API uint64_t orc_rtree_slice(const orc_rtree *t) {
+	return t->slice;
+}
+
+/* rtree_index_dump: DFS, root's entries are level 0 (rtree_index_pragmas.cpp:137-227, rtree_scanner.hpp:38-83).
+ * Emits (level, box, rowid or -1) rows; returns the number of rows (out arrays may be NULL to count). */
+static uint64_t dump_rec(const orc_rtree *t, int tl, uint64_t node, int32_t depth, int32_t *lvl, float *box,
+                         int64_t *rid, uint64_t pos) {
+	const uint64_t b = node * t->cap, e = b + t->cap < t->counts[tl] ? b + t->cap : t->counts[tl];
+	for (uint64_t i = b; i < e; i++) {
+		const orc_entry *en = &t->levels[tl][i];
+		if (lvl) {
+			lvl[pos] = depth;
+			memcpy(box + 4 * pos, en->box, 16);
+			rid[pos] = tl == 0 ? (int64_t)en->ptr : -1;
+		}
+		pos++;
+		if (tl > 0) {
+			pos = dump_rec(t, tl - 1, en->ptr & 0xFFFFFFFFFFFFULL, depth + 1, lvl, box, rid, pos);
+		}
+	}
+	return pos;
+}
+
+ORC_API uint64_t orc_rtree_dump(const orc_rtree *t, int32_t *lvl, float *box, int64_t *rid) {
+	if (t->nlevels == 0) {
+		return 0;
+	}
+	/* the root entry points at node 0 of level nlevels-2 */
+	return dump_rec(t, t->nlevels - 2, 0, 0, lvl, box, rid, 0);
+}
+
+/* RTreeIndex::InitializeScan/Scan, rtree_index.cpp:106-139: DFS, emits row ids in DFS order. */
+static uint64_t scan_rec(const orc_rtree *t, int tl, uint64_t node, const float *q, int64_t *out, uint64_t pos) {
+	const uint64_t b = node * t->cap, e = b + t->cap < t->counts[tl] ? b + t->cap : t->counts[tl];
+	for (uint64_t i = b; i < e; i++) {
+		const orc_entry *en = &t->levels[tl][i];
+		if (!box_intersects(q, en->box)) {
+			continue;
+		}
+		if (tl == 0) {
+			if (out) {
+				out[pos] = (int64_t)en->ptr;
+			}
+			pos++;
+		} else {
+			pos = scan_rec(t, tl - 1, en->ptr & 0xFFFFFFFFFFFFULL, q, out, pos);
+		}
+	}
+	return pos;
+}
+
+ORC_API uint64_t orc_rtree_scan(const orc_rtree *t, const float *qbox, int64_t *out) {
+	if (t->nlevels == 0) {
+		return 0;
+	}
+	const orc_entry *root = &t->levels[t->nlevels - 1][0];
+	if (!box_intersects(qbox, root->box)) {
+		return 0;
+	}
+	return scan_rec(t, t->nlevels - 2, 0, qbox, out, 0);
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * FlatRTree (join build side), src/spatial/operators/spatial_join_physical.cpp:72-320
+ * sort_mode 0 = the reference's own Hoare quicksort (:131-163) -> node-for-node identical to the reference
+ * sort_mode 1 = stable sort by (curve, insertion index)           -> what the CUDA radix sort produces
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+	uint32_t item_count, node_size, nodes, nlayers;
+	uint32_t layer_bounds[16];
+	float *box;    /* nodes x 4 */
+	uint32_t *idx; /* nodes */
+	float tree_box[4];
+} orc_flat;
+
+static void flat_swap(uint32_t *curve, float *box, uint32_t *idx, size_t a, size_t b) {
+	uint32_t c = curve[a];
+	curve[a] = curve[b];
+	curve[b] = c;
+	uint32_t i = idx[a];
+	idx[a] = idx[b];
+	idx[b] = i;
+	float t4[4];
+	memcpy(t4, box + 4 * a, 16);
+	memcpy(box + 4 * a, box + 4 * b, 16);
+	memcpy(box + 4 * b, t4, 16);
+}
+
+static void flat_qsort(uint32_t *curve, float *box, uint32_t *idx, size_t l, size_t r) {
+	/* FlatRTree::Sort, :135-163 (size_t wrap-around of l-1 / r+1 is intentional and benign) */
+	if (l < r) {
+		const uint32_t pivot = curve[(l + r) >> 1];
+		size_t pl = l - 1, pr = r + 1;
+		while (1) {
+			do {
+				++pl;
+			} while (curve[pl] < pivot);
+			do {
+				--pr;
+			} while (curve[pr] > pivot);
+			if (pl >= pr) {
+				break;
+			}
+			flat_swap(curve, box, idx, pl, pr);
+		}
+		flat_qsort(curve, box, idx, l, pr);
+		flat_qsort(curve, box, idx, pr + 1, r);
+	}
+}
+
+typedef struct {
+	uint32_t key, pos;
+} k32;
+static int cmp_k32(const void *a, const void *b) {
+	const k32 *x = (const k32 *)a, *y = (const k32 *)b;
+	if (x->key != y->key) {
+		return x->key < y->key ? -1 : 1;
+	}
+	return x->pos < y->pos ? -1 : (x->pos > y->pos ? 1 : 0);
+}
+
+/* Hilbert key of FlatRTree::Build, :173-187: all fp32 */
+ORC_API void orc_flat_curve(const float *box4, uint32_t n, const float *tree_box, uint32_t *curve) {
+	const float hw = 65535 / (tree_box[2] - tree_box[0]);
+	const float hh = 65535 / (tree_box[3] - tree_box[1]);
+	for (uint32_t i = 0; i < n; i++) {
+		const float *b = box4 + 4 * (size_t)i;
+		const uint32_t hx = cast_f32_u32(hw * ((b[0] + b[2]) / 2 - tree_box[0]));
+		const uint32_t hy = cast_f32_u32(hh * ((b[1] + b[3]) / 2 - tree_box[1]));
+		curve[i] = orc_hilbert_encode(16, hx, hy);
+	}
+}
+
+ORC_API orc_flat *orc_flat_build(const float *box4, uint32_t n, uint32_t node_size, int sort_mode) {
+	orc_flat *t = (orc_flat *)calloc(1, sizeof(orc_flat));
+	t->item_count = n;
+	t->node_size = node_size;
+	uint32_t count = n, nodes = n;
+	t->layer_bounds[t->nlayers++] = nodes;
+	if (n == 0) {
+		return t;
+	}
+	do {
+		count = (count + node_size - 1) / node_size;
+		nodes += count;
+		t->layer_bounds[t->nlayers++] = nodes;
+	} while (count > 1);
+	t->nodes = nodes;
+	t->box = (float *)malloc(sizeof(float) * 4 * (size_t)nodes);
+	t->idx = (uint32_t *)calloc(nodes, sizeof(uint32_t));
+	for (size_t i = 0; i < nodes; i++) { /* Box(): min=+max, max=lowest */
+		t->box[4 * i + 0] = t->box[4 * i + 1] = FLT_MAX;
+		t->box[4 * i + 2] = t->box[4 * i + 3] = -FLT_MAX;
+	}
+	float tb[4] = {FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX};
+	for (uint32_t i = 0; i < n; i++) { /* Push, :117-129 */
+		const float *b = box4 + 4 * (size_t)i;
+		memcpy(t->box + 4 * (size_t)i, b, 16);
+		t->idx[i] = i;
+		tb[0] = b[0] < tb[0] ? b[0] : tb[0];
+		tb[1] = b[1] < tb[1] ? b[1] : tb[1];
+		tb[2] = b[2] > tb[2] ? b[2] : tb[2];
+		tb[3] = b[3] > tb[3] ? b[3] : tb[3];
+	}
+	memcpy(t->tree_box, tb, 16);
+	uint32_t pos = n;
+	if (n <= node_size) { /* :168-171 */
+		memcpy(t->box + 4 * (size_t)pos, tb, 16);
+		return t;
+	}
+	uint32_t *curve = (uint32_t *)malloc(sizeof(uint32_t) * n);
+	orc_flat_curve(box4, n, tb, curve);
+	if (sort_mode == 0) {
+		flat_qsort(curve, t->box, t->idx, 0, (size_t)n - 1);
+	} else {
+		k32 *k = (k32 *)malloc(sizeof(k32) * n);
+		for (uint32_t i = 0; i < n; i++) {
+			k[i].key = curve[i];
+			k[i].pos = i;
+		}
+		qsort(k, n, sizeof(k32), cmp_k32);
+		for (uint32_t i = 0; i < n; i++) {
+			t->idx[i] = k[i].pos;
+			memcpy(t->box + 4 * (size_t)i, box4 + 4 * (size_t)k[i].pos, 16);
+		}
+		free(k);
+	}
+	free(curve);
+	/* level-by-level pack, :189-219 */
+	size_t entry = 0;
+	for (uint32_t layer = 0; layer + 1 < t->nlayers; layer++) {
+		const size_t end = t->layer_bounds[layer];
+		while (entry < end) {
+			const size_t node_idx = entry;
+			float nb[4];
+			memcpy(nb, t->box + 4 * entry, 16);
+			for (uint32_t c = 0; c < node_size && entry < end; c++, entry++) {
+				const float *b = t->box + 4 * entry;
+				nb[0] = b[0] < nb[0] ? b[0] : nb[0];
+				nb[1] = b[1] < nb[1] ? b[1] : nb[1];
+				nb[2] = b[2] > nb[2] ? b[2] : nb[2];
+				nb[3] = b[3] > nb[3] ? b[3] : nb[3];
+			}
+			t->idx[pos] = (uint32_t)node_idx;
+			memcpy(t->box + 4 * (size_t)pos, nb, 16);
+			pos++;
+		}
+	}
+	return t;
+}
+
+ORC_API void orc_flat_free(orc_flat *t) {
+	if (t) {
+		free(t->box);
+		free(t->idx);
+		free(t);
+	}
+}
+ORC_API uint32_t orc_flat_nodes(const orc_flat *t) {
+	return t->nodes;
+}
+ORC_API uint32_t orc_flat_nlayers(const orc_flat *t) {
+	return t->nlayers;
+}
+ORC_API const uint32_t *orc_flat_layer_bounds(const orc_flat *t) {
+	return t->layer_bounds;
+}
+ORC_API const float *orc_flat_boxes(const orc_flat *t) {
+	return t->box;
+}
+ORC_API const uint32_t *orc_flat_idx(const orc_flat *t) {
+	return t->idx;
+}
+ORC_API const float *orc_flat_tree_box(const orc_flat *t) {
+	return t->tree_box;
+}
+
+static size_t flat_upper_bound(const orc_flat *t, size_t node_idx) {
+	/* FlatRTree::UpperBound, :222-228 */
+	for (uint32_t i = 0; i < t->nlayers; i++) {
+		if (t->layer_bounds[i] > node_idx) {
+			return t->layer_bounds[i];
+		}
+	}
+	return t->layer_bounds[t->nlayers - 1];
+}
+
+/* FlatRTree::InitScan/Lookup, :230-302 (BFS with a FIFO queue). Emits insertion indices of matching items.
+ * queue must hold `nodes` entries. Returns number of matches; out may be NULL to count. */
+static uint64_t flat_lookup(const orc_flat *t, const float *q, size_t *queue, uint32_t *out, uint64_t cap) {
+	if (t->item_count == 0) {
+		return 0;
+	}
+	size_t qh = 0, qt = 0;
+	size_t beg = t->nodes - 1;
+	uint64_t cnt = 0;
+	while (1) {
+		size_t end = beg + t->node_size;
+		const size_t ub = flat_upper_bound(t, beg);
+		if (ub < end) {
+			end = ub;
+		}
+		for (size_t pos = beg; pos < end; pos++) {
+			if (!box_intersects(q, t->box + 4 * pos)) {
+				continue;
+			}
+			if (beg >= t->item_count) {
+				queue[qt++] = t->idx[pos];
+			} else {
+				if (out && cnt < cap) {
+					out[cnt] = t->idx[pos];
+				}
+				cnt++;
+			}
+		}
+		if (qh == qt) {
+			return cnt;
+		}
+		beg = queue[qh++];
+	}
+}
+
+ORC_API uint64_t orc_flat_lookup(const orc_flat *t, const float *qbox, uint32_t *out, uint64_t cap) {
+	size_t *queue = (size_t *)malloc(sizeof(size_t) * (t->nodes + 1));
+	const uint64_t c = flat_lookup(t, qbox, queue, out, cap);
+	free(queue);
+	return c;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * Refinement predicates
+ * ---------------------------------------------------------------------------------------------- */
+
+/* exact OGC answers for point x axis-aligned box (what GEOS returns for ST_Intersects / ST_Within of a POINT
+ * against an ST_MakeEnvelope polygon): intersects = closed, within/contains = strict. */
+ORC_API int orc_point_intersects_box(double x, double y, double minx, double miny, double maxx, double maxy) {
+	return minx <= x && x <= maxx && miny <= y && y <= maxy;
+}
+ORC_API int orc_point_within_box(double x, double y, double minx, double miny, double maxx, double maxy) {
+	return minx < x && x < maxx && miny < y && y < maxy;
+}
+
+/* ST_Contains::Operation (POLYGON_2D x POINT_2D winding number), spatial_functions_scalar.cpp:1938-2051,
+ * reached correctly through ST_Within(POINT_2D, POLYGON_2D) :7775-7781.
+ * polygon = rings [r0, r1) of ring_off[]; ring k = vertices [ring_off[k], ring_off[k+1]) of vx/vy. */
+ORC_API int orc_pip_native(double x, double y, const double *vx, const double *vy, const uint64_t *ring_off,
+                           uint64_t r0, uint64_t r1) {
+	int contains = 0, first = 1;
+	for (uint64_t r = r0; r < r1; r++) {
+		const uint64_t o = ring_off[r], len = ring_off[r + 1] - ring_off[r];
+		double x1 = vx[o], y1 = vy[o];
+		int wn = 0;
+		int on_edge = 0;
+		for (uint64_t c = o + 1; c < o + len; c++) {
+			const double x2 = vx[c], y2 = vy[c];
+			if (x1 == x2 && y1 == y2) {
+				x1 = x2;
+				y1 = y2;
+				continue;
+			}
+			const double y_min = y2 < y1 ? y2 : y1; /* std::min(y1,y2) */
+			const double y_max = y1 < y2 ? y2 : y1; /* std::max(y1,y2) */
+			if (y > y_max || y < y_min) {
+				x1 = x2;
+				y1 = y2;
+				continue;
+			}
+			const double side_v = ((x - x1) * (y2 - y1) - (x2 - x1) * (y - y1));
+			if (side_v == 0 &&
+			    (((x1 <= x && x < x2) || (x1 >= x && x > x2)) || ((y1 <= y && y < y2) || (y1 >= y && y > y2)))) {
+				on_edge = 1;
+				break;
+			} else if (side_v < 0 && (y1 < y && y <= y2)) {
+				wn++;
+			} else if (side_v > 0 && (y2 <= y && y < y1)) {
+				wn--;
+			}
+			x1 = x2;
+			y1 = y2;
+		}
+		if (on_edge) {
+			/* `contains = false; break;` leaves the coordinate loop only (:2011-2016); the ring is then
+			 * judged by the winding number accumulated so far (:2025-2044). */
+		}
+		const int in_ring = wn != 0;
+		if (first) {
+			if (!in_ring) {
+				contains = 0;
+				break;
+			}
+			contains = 1;
+		} else if (in_ring) {
+			contains = 0;
+			break;
+		}
+		first = 0;
+	}
+	return contains;
+}
+
+/* ST_Distance(POINT_2D, POINT_2D), spatial_functions_scalar.cpp:2189-2214 */
+ORC_API double orc_distance_pp(double x1, double y1, double x2, double y2) {
+	return sqrt(pow(x1 - x2, 2) + pow(y1 - y2, 2));
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * Whole joins (used as the pair-set oracle and as the timed CPU baseline; OpenMP over probe rows like the
+ * reference's per-chunk parallel probe, spatial_join_physical.hpp:39-41)
+ * pred: 0 = ST_Intersects(point, box) closed; 1 = ST_Within(point, box) strict
+ * Output pairs (probe index, build index) in probe-major order when threads==1.
+ * Returns the number of refined pairs; writes at most cap pairs. n_candidates (optional) = float-box hits.
+ * ---------------------------------------------------------------------------------------------- */
+ORC_API uint64_t orc_join_points_boxes(const double *px, const double *py, uint64_t np, const double *bminx,
+                                       const double *bminy, const double *bmaxx, const double *bmaxy, uint32_t nb,
+                                       int pred, int threads, uint32_t *out_probe, uint32_t *out_build, uint64_t cap,
+                                       uint64_t *n_candidates) {
+	float *bbox = (float *)malloc(sizeof(float) * 4 * (size_t)(nb ? nb : 1));
+	orc_bbox_from_box2d(bminx, bminy, bmaxx, bmaxy, nb, bbox);
+	orc_flat *t = orc_flat_build(bbox, nb, 32, 0);
+	free(bbox);
+	uint64_t total = 0, cand = 0;
+#ifdef _OPENMP
+	if (threads <= 0) {
+		threads = omp_get_max_threads();
+	}
+#else
+	threads = 1;
+#endif
+	if (nb == 0) {
+		orc_flat_free(t);
+		if (n_candidates) {
+			*n_candidates = 0;
+		}
+		return 0;
+	}
+	/* pass 1 (count) and pass 2 (fill) per fixed chunk so the output is deterministic for any thread count */
+	const uint64_t chunk = 2048; /* STANDARD_VECTOR_SIZE */
+	const uint64_t nchunks = (np + chunk - 1) / chunk;
+	uint64_t *ccount = (uint64_t *)calloc(nchunks + 1, sizeof(uint64_t));
+	for (int pass = 0; pass < 2; pass++) {
+#pragma omp parallel num_threads(threads) reduction(+ : cand)
+		{
+			size_t *queue = (size_t *)malloc(sizeof(size_t) * (t->nodes + 1));
+			uint32_t *hits = (uint32_t *)malloc(sizeof(uint32_t) * (size_t)nb);
+#pragma omp for schedule(dynamic, 16)
+			for (uint64_t c = 0; c < nchunks; c++) {
+				uint64_t w = pass ? ccount[c] : 0, local = 0;
+				const uint64_t e = (c + 1) * chunk < np ? (c + 1) * chunk : np;
+				for (uint64_t i = c * chunk; i < e; i++) {
+					float q[4] = {orc_double_to_float_down(px[i]), orc_double_to_float_down(py[i]),
+					              orc_double_to_float_up(px[i]), orc_double_to_float_up(py[i])};
+					const uint64_t h = flat_lookup(t, q, queue, hits, nb);
+					if (!pass) {
+						cand += h;
+					}
+					for (uint64_t k = 0; k < h; k++) {
+						const uint32_t b = hits[k];
+						const int ok = pred == 0
+						                   ? orc_point_intersects_box(px[i], py[i], bminx[b], bminy[b], bmaxx[b], bmaxy[b])
+						                   : orc_point_within_box(px[i], py[i], bminx[b], bminy[b], bmaxx[b], bmaxy[b]);
+						if (ok) {
+							if (pass && w < cap) {
+								out_probe[w] = (uint32_t)i;
+								out_build[w] = b;
+							}
+							w++;
+							local++;
+						}
+					}
+				}
+				if (!pass) {
+					ccount[c] = local;
+				}
+			}
+			free(queue);
+			free(hits);
+		}
+		if (!pass) {
+			uint64_t run = 0;
+			for (uint64_t c = 0; c < nchunks; c++) {
+				const uint64_t v = ccount[c];
+				ccount[c] = run;
+				run += v;
+			}
+			total = run;
+			if (!out_probe || cap == 0) {
+				break;
+			}
+		}
+	}
+	free(ccount);
+	orc_flat_free(t);
+	if (n_candidates) {
+		*n_candidates = cand;
+	}
+	return total;
+}
+
+/* brute-force radius join oracle (reference plan = BLOCKWISE_NL_JOIN over ST_DWithin / ST_Distance):
+ * pairs with orc_distance_pp <= r. O(n*m): small inputs only. */
+ORC_API uint64_t orc_dwithin_brute(const double *ax, const double *ay, uint64_t na, const double *bx, const double *by,
+                                   uint64_t nb, double r, uint32_t *out_a, uint32_t *out_b, double *out_d,
+                                   uint64_t cap) {
+	uint64_t w = 0;
+	for (uint64_t i = 0; i < na; i++) {
+		for (uint64_t j = 0; j < nb; j++) {
+			const double d = orc_distance_pp(ax[i], ay[i], bx[j], by[j]);
+			if (d <= r) {
+				if (w < cap && out_a) {
+					out_a[w] = (uint32_t)i;
+					out_b[w] = (uint32_t)j;
+					if (out_d) {
+						out_d[w] = d;
+					}
+				}
+				w++;
+			}
+		}
+	}
+	return w;
+}
+
+/* STR build timing helper for the CPU baseline: bbox from points + build, returns level count */
+ORC_API int orc_rtree_build_from_points(const double *x, const double *y, uint64_t n, uint32_t cap) {
+	float *b = (float *)malloc(sizeof(float) * 4 * (size_t)n);
+	int64_t *rid = (int64_t *)malloc(sizeof(int64_t) * (size_t)n);
+	orc_bbox_from_points(x, y, n, b);
+	for (uint64_t i = 0; i < n; i++) {
+		rid[i] = (int64_t)i;
+	}
+	orc_rtree *t = orc_rtree_build_str(b, rid, n, cap);
+	const int nl = t->nlevels;
+	orc_rtree_free(t);
+	free(b);
+	free(rid);
+	return nl;
+}
