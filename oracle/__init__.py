@@ -90,6 +90,8 @@ def lib():
         L.orc_flat_tree_box.restype = f32p
         L.orc_flat_tree_box.argtypes = [C.c_void_p]
         L.orc_flat_lookup.restype = C.c_uint64
+        L.orc_point_intersects_box.argtypes = [C.c_double] * 6
+        L.orc_point_within_box.argtypes = [C.c_double] * 6
         L.orc_pip_native.restype = C.c_int
         L.orc_pip_native.argtypes = [C.c_double, C.c_double, f64p, f64p, u64p, C.c_uint64, C.c_uint64]
         L.orc_distance_pp.restype = C.c_double
