@@ -1,0 +1,580 @@
+// capi.cu -- the extern "C" boundary (include/spatial_b200.h). Host-pointer calls stage through the context's
+// device arena on the context's stream and return after the results are back in host memory; device-pointer
+// calls only enqueue work (except where a count has to be returned).
+#include "internal.cuh"
+
+#define SB_BEGIN(ctx)                                                                                                \
+	SB_ARG((ctx) != nullptr, "ctx");                                                                                 \
+	SB_CUDA(cudaSetDevice((ctx)->device));                                                                           \
+	(ctx)->arena.reset()
+
+static int finish(sb_context *ctx, sb_mem mem) {
+	if (mem == SB_HOST) {
+		SB_CUDA(cudaStreamSynchronize(ctx->stream));
+	}
+	return SB_OK;
+}
+
+// ---- K1 ---------------------------------------------------------------------------------------------------------
+extern "C" int sb_bbox_from_points(sb_context *ctx, sb_mem mem, const double *x, const double *y, uint64_t n,
+                                   float *out_box4) {
+	SB_BEGIN(ctx);
+	const double *dx, *dy;
+	float *dout;
+	SB_TRY(sb_to_device(ctx, mem, x, n, &dx));
+	SB_TRY(sb_to_device(ctx, mem, y, n, &dy));
+	SB_TRY(sb_out_buffer(ctx, mem, out_box4, 4 * n, &dout));
+	SB_TRY(sbi_bbox_points(ctx, dx, dy, n, dout));
+	SB_TRY(sb_to_host(ctx, mem, out_box4, dout, 4 * n));
+	return finish(ctx, mem);
+}
+
+extern "C" int sb_bbox_from_box2d(sb_context *ctx, sb_mem mem, const double *min_x, const double *min_y,
+                                  const double *max_x, const double *max_y, uint64_t n, float *out_box4) {
+	SB_BEGIN(ctx);
+	const double *a, *b, *c, *d;
+	float *dout;
+	SB_TRY(sb_to_device(ctx, mem, min_x, n, &a));
+	SB_TRY(sb_to_device(ctx, mem, min_y, n, &b));
+	SB_TRY(sb_to_device(ctx, mem, max_x, n, &c));
+	SB_TRY(sb_to_device(ctx, mem, max_y, n, &d));
+	SB_TRY(sb_out_buffer(ctx, mem, out_box4, 4 * n, &dout));
+	SB_TRY(sbi_bbox_box2d(ctx, a, b, c, d, n, dout));
+	SB_TRY(sb_to_host(ctx, mem, out_box4, dout, 4 * n));
+	return finish(ctx, mem);
+}
+
+// shared by the four blob entry points. which: 0 approx box, 1 hilbert(geom), 2 exact extent, 3 hilbert(geom,bounds)
+static int blob_call(sb_context *ctx, sb_mem mem, int which, const uint8_t *data, const uint64_t *offsets, uint64_t n,
+                     float *out_f, double *out_d, uint32_t *out_key, uint8_t *out_valid, int32_t *row_status,
+                     const double *bounds) {
+	SB_BEGIN(ctx);
+	if (n == 0) {
+		return SB_OK;
+	}
+	SB_ARG(data != nullptr && offsets != nullptr, "data/offsets");
+	uint64_t total = 0;
+	if (mem == SB_HOST) {
+		total = offsets[n];
+	} else {
+		SB_CUDA(cudaMemcpyAsync(&total, offsets + n, sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+		SB_CUDA(cudaStreamSynchronize(ctx->stream));
+	}
+	const uint8_t *d_data;
+	const uint64_t *d_off;
+	SB_TRY(sb_to_device(ctx, mem, data, total, &d_data));
+	SB_TRY(sb_to_device(ctx, mem, offsets, n + 1, &d_off));
+	float *d_f = nullptr;
+	double *d_d = nullptr;
+	uint32_t *d_key = nullptr;
+	uint8_t *d_valid = nullptr;
+	int32_t *d_status = nullptr;
+	int *d_bad = nullptr;
+	SB_TRY(ctx->scratch_t(1, &d_bad));
+	SB_CUDA(cudaMemsetAsync(d_bad, 0, sizeof(int), ctx->stream));
+	SB_TRY(sb_out_buffer(ctx, mem, out_f, 4 * n, &d_f));
+	SB_TRY(sb_out_buffer(ctx, mem, out_d, 4 * n, &d_d));
+	SB_TRY(sb_out_buffer(ctx, mem, out_key, n, &d_key));
+	SB_TRY(sb_out_buffer(ctx, mem, out_valid, n, &d_valid));
+	if (row_status || which == 3) {
+		if (row_status) {
+			SB_TRY(sb_out_buffer(ctx, mem, row_status, n, &d_status));
+		} else {
+			SB_TRY(ctx->scratch_t(n, &d_status));
+		}
+	}
+	if (which == 0) {
+		SB_TRY(sbi_blob_bounds(ctx, 0, d_data, d_off, n, d_f, nullptr, d_valid, d_status, d_bad));
+	} else if (which == 1) {
+		SB_TRY(sbi_blob_bounds(ctx, 1, d_data, d_off, n, nullptr, d_key, d_valid, d_status, d_bad));
+	} else if (which == 2) {
+		SB_TRY(sbi_blob_extent(ctx, 0, d_data, d_off, n, d_d, d_valid, d_status, nullptr, nullptr, d_bad));
+	} else {
+		SB_TRY(sbi_blob_extent(ctx, 1, d_data, d_off, n, nullptr, nullptr, d_status, bounds, d_key, d_bad));
+	}
+	SB_TRY(sb_to_host(ctx, mem, out_f, d_f, 4 * n));
+	SB_TRY(sb_to_host(ctx, mem, out_d, d_d, 4 * n));
+	SB_TRY(sb_to_host(ctx, mem, out_key, d_key, n));
+	SB_TRY(sb_to_host(ctx, mem, out_valid, d_valid, n));
+	SB_TRY(sb_to_host(ctx, mem, row_status, d_status, n));
+	int bad = 0;
+	SB_CUDA(cudaMemcpyAsync(&bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+	SB_CUDA(cudaStreamSynchronize(ctx->stream));
+	if (bad == 1) {
+		sb_set_error("malformed or unsupported-version geometry blob(s); see row_status");
+		return SB_ERR_GEOMETRY;
+	}
+	if (bad == 2) {
+		sb_set_error("ST_Hilbert(geom, bounds) does not support empty geometries");
+		return SB_ERR_EMPTY;
+	}
+	return SB_OK;
+}
+
+extern "C" int sb_bbox_from_blobs(sb_context *ctx, sb_mem mem, const uint8_t *data, const uint64_t *offsets, uint64_t n,
+                                  float *out_box4, uint8_t *out_valid, int32_t *row_status) {
+	return blob_call(ctx, mem, 0, data, offsets, n, out_box4, nullptr, nullptr, out_valid, row_status, nullptr);
+}
+extern "C" int sb_extent_from_blobs(sb_context *ctx, sb_mem mem, const uint8_t *data, const uint64_t *offsets,
+                                    uint64_t n, double *out_box4, uint8_t *out_valid, int32_t *row_status) {
+	return blob_call(ctx, mem, 2, data, offsets, n, nullptr, out_box4, nullptr, out_valid, row_status, nullptr);
+}
+extern "C" int sb_hilbert_geom(sb_context *ctx, sb_mem mem, const uint8_t *data, const uint64_t *offsets, uint64_t n,
+                               uint32_t *out, uint8_t *out_valid) {
+	return blob_call(ctx, mem, 1, data, offsets, n, nullptr, nullptr, out, out_valid, nullptr, nullptr);
+}
+extern "C" int sb_hilbert_geom_bounds(sb_context *ctx, sb_mem mem, const uint8_t *data, const uint64_t *offsets,
+                                      uint64_t n, const double *bounds4, uint32_t *out, int32_t *row_status) {
+	SB_ARG(bounds4 != nullptr, "bounds4");
+	return blob_call(ctx, mem, 3, data, offsets, n, nullptr, nullptr, out, nullptr, row_status, bounds4);
+}
+
+// ---- K2 ---------------------------------------------------------------------------------------------------------
+extern "C" int sb_hilbert_xy(sb_context *ctx, sb_mem mem, const double *x, const double *y, uint64_t n,
+                             const double *bounds4, uint32_t *out) {
+	SB_BEGIN(ctx);
+	SB_ARG(bounds4 != nullptr, "bounds4");
+	const double *dx, *dy;
+	uint32_t *dout;
+	SB_TRY(sb_to_device(ctx, mem, x, n, &dx));
+	SB_TRY(sb_to_device(ctx, mem, y, n, &dy));
+	SB_TRY(sb_out_buffer(ctx, mem, out, n, &dout));
+	SB_TRY(sbi_hilbert_xy(ctx, dx, dy, n, bounds4, dout));
+	SB_TRY(sb_to_host(ctx, mem, out, dout, n));
+	return finish(ctx, mem);
+}
+
+extern "C" int sb_hilbert_box2d(sb_context *ctx, sb_mem mem, const double *box4, uint64_t n, const double *bounds4,
+                                uint32_t *out) {
+	SB_BEGIN(ctx);
+	SB_ARG(bounds4 != nullptr, "bounds4");
+	const double *db;
+	uint32_t *dout;
+	SB_TRY(sb_to_device(ctx, mem, box4, 4 * n, &db));
+	SB_TRY(sb_out_buffer(ctx, mem, out, n, &dout));
+	SB_TRY(sbi_hilbert_box2d(ctx, db, n, bounds4, dout));
+	SB_TRY(sb_to_host(ctx, mem, out, dout, n));
+	return finish(ctx, mem);
+}
+
+extern "C" int sb_hilbert_box2df(sb_context *ctx, sb_mem mem, const float *box4, uint64_t n, const float *bounds4,
+                                 uint32_t *out) {
+	SB_BEGIN(ctx);
+	SB_ARG(bounds4 != nullptr, "bounds4");
+	const float *db;
+	uint32_t *dout;
+	SB_TRY(sb_to_device(ctx, mem, box4, 4 * n, &db));
+	SB_TRY(sb_out_buffer(ctx, mem, out, n, &dout));
+	SB_TRY(sbi_hilbert_box2df(ctx, db, n, bounds4, dout));
+	SB_TRY(sb_to_host(ctx, mem, out, dout, n));
+	return finish(ctx, mem);
+}
+
+// ---- K3 ---------------------------------------------------------------------------------------------------------
+template <typename KeyT>
+static int sort_pairs(sb_context *ctx, sb_mem mem, KeyT *keys, uint32_t *values, uint64_t n) {
+	SB_BEGIN(ctx);
+	if (n == 0) {
+		return SB_OK;
+	}
+	KeyT *k = nullptr, *kb = nullptr;
+	uint32_t *v = nullptr, *vb = nullptr;
+	if (mem == SB_HOST) {
+		SB_TRY(ctx->scratch_t(n, &k));
+		SB_TRY(ctx->scratch_t(n, &v));
+		SB_CUDA(cudaMemcpyAsync(k, keys, n * sizeof(KeyT), cudaMemcpyHostToDevice, ctx->stream));
+		SB_CUDA(cudaMemcpyAsync(v, values, n * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+	} else {
+		k = keys;
+		v = values;
+	}
+	SB_TRY(ctx->scratch_t(n, &kb));
+	SB_TRY(ctx->scratch_t(n, &vb));
+	int alt = 0;
+	if (sizeof(KeyT) == 4) {
+		SB_TRY(sbi_radix_sort_u32(ctx, (uint32_t *)k, (uint32_t *)kb, v, vb, n, 0, 32, false, &alt));
+	} else {
+		SB_TRY(sbi_radix_sort_u64(ctx, (uint64_t *)k, (uint64_t *)kb, v, vb, n, 0, 64, false, &alt));
+	}
+	const KeyT *rk = alt ? kb : k;
+	const uint32_t *rv = alt ? vb : v;
+	const cudaMemcpyKind kind = mem == SB_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice;
+	if (mem == SB_HOST || alt) {
+		SB_CUDA(cudaMemcpyAsync(keys, rk, n * sizeof(KeyT), kind, ctx->stream));
+		SB_CUDA(cudaMemcpyAsync(values, rv, n * sizeof(uint32_t), kind, ctx->stream));
+	}
+	return finish(ctx, mem);
+}
+
+extern "C" int sb_sort_pairs_u32(sb_context *ctx, sb_mem mem, uint32_t *keys, uint32_t *values, uint64_t n) {
+	return sort_pairs<uint32_t>(ctx, mem, keys, values, n);
+}
+extern "C" int sb_sort_pairs_u64(sb_context *ctx, sb_mem mem, uint64_t *keys, uint32_t *values, uint64_t n) {
+	return sort_pairs<uint64_t>(ctx, mem, keys, values, n);
+}
+
+// ---- K4a --------------------------------------------------------------------------------------------------------
+extern "C" int sb_rtree_build_str(sb_context *ctx, sb_mem mem, const float *box4, const int64_t *row_ids, uint64_t n,
+                                  uint32_t max_node_capacity, sb_rtree **out) {
+	SB_BEGIN(ctx);
+	SB_ARG(out != nullptr, "out");
+	*out = nullptr;
+	const float *db;
+	const int64_t *dr;
+	SB_TRY(sb_to_device(ctx, mem, box4, 4 * n, &db));
+	SB_TRY(sb_to_device(ctx, mem, row_ids, n, &dr));
+	sb_rtree *t = nullptr;
+	int s = sbi_rtree_build_str(ctx, db, dr, n, max_node_capacity, &t);
+	if (s != SB_OK) {
+		if (t) {
+			sb_rtree_destroy(t);
+		}
+		return s;
+	}
+	*out = t;
+	return finish(ctx, mem);
+}
+
+extern "C" void sb_rtree_destroy(sb_rtree *tree) {
+	if (!tree) {
+		return;
+	}
+	cudaSetDevice(tree->device);
+	cudaFree(tree->entries);
+	delete tree;
+}
+extern "C" int sb_rtree_num_levels(const sb_rtree *tree) {
+	return tree ? tree->nlevels : 0;
+}
+extern "C" uint64_t sb_rtree_level_count(const sb_rtree *tree, int level) {
+	return (tree && level >= 0 && level < tree->nlevels) ? tree->counts[level] : 0;
+}
+extern "C" uint64_t sb_rtree_slice_size(const sb_rtree *tree) {
+	return tree ? tree->slice : 0;
+}
+
+extern "C" int sb_rtree_export_level(sb_context *ctx, const sb_rtree *tree, int level, sb_mem mem, void *out_entries) {
+	SB_ARG(ctx != nullptr && tree != nullptr && out_entries != nullptr, "ctx/tree/out");
+	SB_ARG(level >= 0 && level < tree->nlevels, "level");
+	SB_CUDA(cudaSetDevice(ctx->device));
+	SB_CUDA(cudaMemcpyAsync(out_entries, tree->entries + tree->offsets[level], tree->counts[level] * sizeof(sb_entry),
+	                        mem == SB_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, ctx->stream));
+	return finish(ctx, mem);
+}
+
+extern "C" int sb_rtree_scan(sb_context *ctx, const sb_rtree *tree, sb_mem mem, const float *query_box4, uint32_t nq,
+                             uint32_t *out_query, int64_t *out_row_id, uint64_t capacity, uint64_t *count) {
+	SB_BEGIN(ctx);
+	SB_ARG(tree != nullptr && count != nullptr, "tree/count");
+	const float *dq;
+	uint32_t *doq;
+	int64_t *dor;
+	SB_TRY(sb_to_device(ctx, mem, query_box4, 4 * (uint64_t)nq, &dq));
+	SB_TRY(sb_out_buffer(ctx, mem, out_query, capacity, &doq));
+	SB_TRY(sb_out_buffer(ctx, mem, out_row_id, capacity, &dor));
+	SB_TRY(sbi_rtree_scan(ctx, tree, dq, nq, doq, dor, capacity, count));
+	SB_TRY(sb_to_host(ctx, mem, out_query, doq, *count));
+	SB_TRY(sb_to_host(ctx, mem, out_row_id, dor, *count));
+	return finish(ctx, mem);
+}
+
+// ---- K4b / K5 -----------------------------------------------------------------------------------------------------
+extern "C" int sb_flat_build(sb_context *ctx, sb_mem mem, const float *box4, uint32_t n, uint32_t node_size,
+                             sb_flat **out) {
+	SB_BEGIN(ctx);
+	SB_ARG(out != nullptr, "out");
+	*out = nullptr;
+	const float *db;
+	SB_TRY(sb_to_device(ctx, mem, box4, 4 * (uint64_t)n, &db));
+	sb_flat *t = nullptr;
+	int s = sbi_flat_build(ctx, db, n, node_size, &t);
+	if (s != SB_OK) {
+		if (t) {
+			sb_flat_destroy(t);
+		}
+		return s;
+	}
+	*out = t;
+	return finish(ctx, mem);
+}
+
+extern "C" void sb_flat_destroy(sb_flat *tree) {
+	if (!tree) {
+		return;
+	}
+	if (tree->owns && tree->buffer) {
+		cudaSetDevice(tree->device);
+		cudaFree(tree->buffer);
+	}
+	delete tree;
+}
+extern "C" uint32_t sb_flat_item_count(const sb_flat *tree) {
+	return tree ? tree->h.item_count : 0;
+}
+extern "C" uint32_t sb_flat_node_count(const sb_flat *tree) {
+	return tree ? tree->h.nodes : 0;
+}
+extern "C" uint32_t sb_flat_num_layers(const sb_flat *tree) {
+	return tree ? tree->h.nlayers : 0;
+}
+extern "C" const uint32_t *sb_flat_layer_bounds(const sb_flat *tree) {
+	return tree ? tree->h.layer_bounds : nullptr;
+}
+extern "C" int sb_flat_device_buffer(const sb_flat *tree, void **dev_ptr, uint64_t *bytes) {
+	SB_ARG(tree != nullptr && dev_ptr != nullptr && bytes != nullptr, "tree/out");
+	*dev_ptr = tree->buffer;
+	*bytes = tree->bytes;
+	return SB_OK;
+}
+
+extern "C" int sb_flat_attach(sb_context *ctx, void *dev_ptr, uint64_t bytes, sb_flat **out) {
+	SB_ARG(ctx != nullptr && dev_ptr != nullptr && out != nullptr, "ctx/dev_ptr/out");
+	SB_ARG(bytes >= sizeof(sb_flat_header), "buffer too small");
+	SB_CUDA(cudaSetDevice(ctx->device));
+	sb_flat *t = new sb_flat();
+	SB_CUDA(cudaMemcpyAsync(&t->h, dev_ptr, sizeof(t->h), cudaMemcpyDeviceToHost, ctx->stream));
+	SB_CUDA(cudaStreamSynchronize(ctx->stream));
+	if (t->h.magic != SB_FLAT_MAGIC ||
+	    sizeof(sb_flat_header) + (uint64_t)t->h.nodes * (sizeof(float4) + sizeof(uint32_t)) > bytes) {
+		delete t;
+		sb_set_error("sb_flat_attach: not a FlatRTree buffer");
+		return SB_ERR_ARG;
+	}
+	t->device = ctx->device;
+	t->buffer = dev_ptr;
+	t->bytes = bytes;
+	t->owns = false;
+	*out = t;
+	return SB_OK;
+}
+
+extern "C" int sb_flat_export(sb_context *ctx, const sb_flat *tree, sb_mem mem, float *out_box4, uint32_t *out_idx) {
+	SB_ARG(ctx != nullptr && tree != nullptr, "ctx/tree");
+	SB_CUDA(cudaSetDevice(ctx->device));
+	const cudaMemcpyKind kind = mem == SB_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice;
+	if (tree->h.nodes) {
+		SB_CUDA(cudaMemcpyAsync(out_box4, tree->boxes(), sizeof(float4) * (size_t)tree->h.nodes, kind, ctx->stream));
+		SB_CUDA(cudaMemcpyAsync(out_idx, tree->idx(), sizeof(uint32_t) * (size_t)tree->h.nodes, kind, ctx->stream));
+	}
+	return finish(ctx, mem);
+}
+
+extern "C" int sb_flat_probe(sb_context *ctx, const sb_flat *tree, sb_mem mem, const float *probe_box4, uint64_t m,
+                             uint32_t *out_probe, uint32_t *out_build, uint64_t capacity, uint64_t *count) {
+	SB_BEGIN(ctx);
+	SB_ARG(tree != nullptr && count != nullptr, "tree/count");
+	const float *dq;
+	uint32_t *dop, *dob;
+	SB_TRY(sb_to_device(ctx, mem, probe_box4, 4 * m, &dq));
+	SB_TRY(sb_out_buffer(ctx, mem, out_probe, capacity, &dop));
+	SB_TRY(sb_out_buffer(ctx, mem, out_build, capacity, &dob));
+	sb_probe_args a;
+	a.probe_box = reinterpret_cast<const float4 *>(dq);
+	a.m = m;
+	SB_TRY(sbi_flat_probe(ctx, tree, a, dop, dob, capacity, count));
+	SB_TRY(sb_to_host(ctx, mem, out_probe, dop, *count));
+	SB_TRY(sb_to_host(ctx, mem, out_build, dob, *count));
+	return finish(ctx, mem);
+}
+
+extern "C" int sb_flat_probe_points(sb_context *ctx, const sb_flat *tree, sb_mem mem, sb_predicate pred,
+                                    const double *px, const double *py, uint64_t n_points, uint32_t probe_index_base,
+                                    const double *bbox2d4, uint32_t *out_probe, uint32_t *out_build, uint64_t capacity,
+                                    uint64_t *count) {
+	SB_BEGIN(ctx);
+	SB_ARG(tree != nullptr && count != nullptr, "tree/count");
+	const double *dx, *dy, *db = nullptr;
+	uint32_t *dop, *dob;
+	SB_TRY(sb_to_device(ctx, mem, px, n_points, &dx));
+	SB_TRY(sb_to_device(ctx, mem, py, n_points, &dy));
+	if (bbox2d4) {
+		SB_TRY(sb_to_device(ctx, mem, bbox2d4, 4 * (uint64_t)tree->h.item_count, &db));
+	}
+	SB_TRY(sb_out_buffer(ctx, mem, out_probe, capacity, &dop));
+	SB_TRY(sb_out_buffer(ctx, mem, out_build, capacity, &dob));
+	sb_probe_args a;
+	a.px = dx;
+	a.py = dy;
+	a.m = n_points;
+	a.index_base = probe_index_base;
+	a.build_box2d = reinterpret_cast<const double4 *>(db);
+	a.pred = db ? (int)pred : -1;
+	SB_TRY(sbi_flat_probe(ctx, tree, a, dop, dob, capacity, count));
+	SB_TRY(sb_to_host(ctx, mem, out_probe, dop, *count));
+	SB_TRY(sb_to_host(ctx, mem, out_build, dob, *count));
+	return finish(ctx, mem);
+}
+
+// ---- K6 ---------------------------------------------------------------------------------------------------------
+extern "C" int sb_refine_point_box(sb_context *ctx, sb_mem mem, sb_predicate pred, const double *px, const double *py,
+                                   const double *bmin_x, const double *bmin_y, const double *bmax_x,
+                                   const double *bmax_y, uint32_t *pair_probe, uint32_t *pair_build, uint64_t *count) {
+	SB_BEGIN(ctx);
+	SB_ARG(count != nullptr, "count");
+	SB_ARG(mem == SB_DEVICE, "refine kernels take device pointers (sizes of the coordinate columns are not known here)");
+	return sbi_refine_point_box(ctx, pred, px, py, bmin_x, bmin_y, bmax_x, bmax_y, pair_probe, pair_build, *count,
+	                            count);
+}
+
+extern "C" int sb_refine_point_polygon(sb_context *ctx, sb_mem mem, const double *px, const double *py,
+                                       const double *vx, const double *vy, const uint64_t *ring_vert_off,
+                                       const uint64_t *poly_ring_off, uint64_t n_polys, uint64_t n_rings,
+                                       uint64_t n_verts, uint64_t n_points, uint32_t *pair_probe, uint32_t *pair_build,
+                                       uint64_t *count) {
+	SB_BEGIN(ctx);
+	SB_ARG(count != nullptr, "count");
+	const uint64_t n = *count;
+	const double *dpx, *dpy, *dvx, *dvy;
+	const uint64_t *dro, *dpo;
+	SB_TRY(sb_to_device(ctx, mem, px, n_points, &dpx));
+	SB_TRY(sb_to_device(ctx, mem, py, n_points, &dpy));
+	SB_TRY(sb_to_device(ctx, mem, vx, n_verts, &dvx));
+	SB_TRY(sb_to_device(ctx, mem, vy, n_verts, &dvy));
+	SB_TRY(sb_to_device(ctx, mem, ring_vert_off, n_rings + 1, &dro));
+	SB_TRY(sb_to_device(ctx, mem, poly_ring_off, n_polys + 1, &dpo));
+	uint32_t *dpp = pair_probe, *dpb = pair_build;
+	if (mem == SB_HOST && n) {
+		SB_TRY(ctx->scratch_t(n, &dpp));
+		SB_TRY(ctx->scratch_t(n, &dpb));
+		SB_CUDA(cudaMemcpyAsync(dpp, pair_probe, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+		SB_CUDA(cudaMemcpyAsync(dpb, pair_build, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+	}
+	SB_TRY(sbi_refine_point_polygon(ctx, dpx, dpy, dvx, dvy, dro, dpo, dpp, dpb, n, count));
+	SB_TRY(sb_to_host(ctx, mem, pair_probe, dpp, *count));
+	SB_TRY(sb_to_host(ctx, mem, pair_build, dpb, *count));
+	return finish(ctx, mem);
+}
+
+extern "C" int sb_refine_dwithin(sb_context *ctx, sb_mem mem, const double *ax, const double *ay, const double *bx,
+                                 const double *by, double radius, uint32_t *pair_a, uint32_t *pair_b, double *out_dist,
+                                 uint64_t *count) {
+	SB_BEGIN(ctx);
+	SB_ARG(count != nullptr, "count");
+	SB_ARG(mem == SB_DEVICE, "refine kernels take device pointers (sizes of the coordinate columns are not known here)");
+	return sbi_refine_dwithin(ctx, ax, ay, bx, by, radius, pair_a, pair_b, out_dist, *count, count);
+}
+
+extern "C" int sb_distance_points(sb_context *ctx, sb_mem mem, const double *ax, const double *ay, const double *bx,
+                                  const double *by, uint64_t n, double *out) {
+	SB_BEGIN(ctx);
+	const double *a, *b, *c, *d;
+	double *dout;
+	SB_TRY(sb_to_device(ctx, mem, ax, n, &a));
+	SB_TRY(sb_to_device(ctx, mem, ay, n, &b));
+	SB_TRY(sb_to_device(ctx, mem, bx, n, &c));
+	SB_TRY(sb_to_device(ctx, mem, by, n, &d));
+	SB_TRY(sb_out_buffer(ctx, mem, out, n, &dout));
+	SB_TRY(sbi_distance_points(ctx, a, b, c, d, n, dout));
+	SB_TRY(sb_to_host(ctx, mem, out, dout, n));
+	return finish(ctx, mem);
+}
+
+// ---- whole joins -------------------------------------------------------------------------------------------------
+extern "C" int sb_join_points_boxes(sb_context *ctx, sb_mem mem, sb_predicate pred, const double *px, const double *py,
+                                    uint64_t n_points, const double *bmin_x, const double *bmin_y,
+                                    const double *bmax_x, const double *bmax_y, uint32_t n_boxes, uint32_t *out_probe,
+                                    uint32_t *out_build, uint64_t capacity, uint64_t *count) {
+	SB_BEGIN(ctx);
+	SB_ARG(count != nullptr, "count");
+	*count = 0;
+	const double *dx, *dy, *b0, *b1, *b2, *b3;
+	SB_TRY(sb_to_device(ctx, mem, px, n_points, &dx));
+	SB_TRY(sb_to_device(ctx, mem, py, n_points, &dy));
+	SB_TRY(sb_to_device(ctx, mem, bmin_x, (uint64_t)n_boxes, &b0));
+	SB_TRY(sb_to_device(ctx, mem, bmin_y, (uint64_t)n_boxes, &b1));
+	SB_TRY(sb_to_device(ctx, mem, bmax_x, (uint64_t)n_boxes, &b2));
+	SB_TRY(sb_to_device(ctx, mem, bmax_y, (uint64_t)n_boxes, &b3));
+	uint32_t *dop, *dob;
+	SB_TRY(sb_out_buffer(ctx, mem, out_probe, capacity, &dop));
+	SB_TRY(sb_out_buffer(ctx, mem, out_build, capacity, &dob));
+	if (n_boxes == 0 || n_points == 0) {
+		return finish(ctx, mem);
+	}
+	// build side: BOX_2D -> BOX_2DF (cached bbox of the envelope polygons) -> FlatRTree(node_size 32, :553)
+	float *fbox = nullptr;
+	double *box2d = nullptr;
+	SB_TRY(ctx->scratch_t(4 * (uint64_t)n_boxes, &fbox));
+	SB_TRY(ctx->scratch_t(4 * (uint64_t)n_boxes, &box2d));
+	SB_TRY(sbi_bbox_box2d(ctx, b0, b1, b2, b3, n_boxes, fbox));
+	SB_TRY(sbi_pack_box2d(ctx, b0, b1, b2, b3, n_boxes, box2d));
+	sb_flat *tree = nullptr;
+	int s = sbi_flat_build(ctx, fbox, n_boxes, 32, &tree);
+	if (s == SB_OK) {
+		sb_probe_args a;
+		a.px = dx;
+		a.py = dy;
+		a.m = n_points;
+		a.build_box2d = reinterpret_cast<const double4 *>(box2d);
+		a.pred = (int)pred;
+		s = sbi_flat_probe(ctx, tree, a, dop, dob, capacity, count);
+	}
+	if (s == SB_OK) {
+		s = sb_to_host(ctx, mem, out_probe, dop, *count);
+	}
+	if (s == SB_OK) {
+		s = sb_to_host(ctx, mem, out_build, dob, *count);
+	}
+	if (s == SB_OK) {
+		s = finish(ctx, mem);
+	} else {
+		cudaStreamSynchronize(ctx->stream);
+	}
+	if (tree) {
+		cudaStreamSynchronize(ctx->stream);
+		sb_flat_destroy(tree);
+	}
+	return s;
+}
+
+extern "C" int sb_join_dwithin(sb_context *ctx, sb_mem mem, const double *ax, const double *ay, uint64_t na,
+                               const double *bx, const double *by, uint32_t nb, double radius, uint32_t *out_a,
+                               uint32_t *out_b, double *out_dist, uint64_t capacity, uint64_t *count) {
+	SB_BEGIN(ctx);
+	SB_ARG(count != nullptr, "count");
+	SB_ARG(radius >= 0, "radius");
+	*count = 0;
+	const double *dax, *day, *dbx, *dby;
+	SB_TRY(sb_to_device(ctx, mem, ax, na, &dax));
+	SB_TRY(sb_to_device(ctx, mem, ay, na, &day));
+	SB_TRY(sb_to_device(ctx, mem, bx, (uint64_t)nb, &dbx));
+	SB_TRY(sb_to_device(ctx, mem, by, (uint64_t)nb, &dby));
+	uint32_t *doa, *dob;
+	double *dod;
+	SB_TRY(sb_out_buffer(ctx, mem, out_a, capacity, &doa));
+	SB_TRY(sb_out_buffer(ctx, mem, out_b, capacity, &dob));
+	SB_TRY(sb_out_buffer(ctx, mem, out_dist, capacity, &dod));
+	if (na == 0 || nb == 0) {
+		return finish(ctx, mem);
+	}
+	float *fbox = nullptr;
+	SB_TRY(ctx->scratch_t(4 * (uint64_t)nb, &fbox));
+	SB_TRY(sbi_expand_points(ctx, dbx, dby, nb, radius, fbox));
+	sb_flat *tree = nullptr;
+	int s = sbi_flat_build(ctx, fbox, nb, 32, &tree);
+	uint64_t cand = 0;
+	if (s == SB_OK) {
+		sb_probe_args a;
+		a.px = dax;
+		a.py = day;
+		a.m = na;
+		s = sbi_flat_probe(ctx, tree, a, doa, dob, capacity, &cand);
+		*count = cand;
+	}
+	if (s == SB_OK) {
+		s = sbi_refine_dwithin(ctx, dax, day, dbx, dby, radius, doa, dob, dod, cand, count);
+	}
+	if (s == SB_OK) {
+		s = sb_to_host(ctx, mem, out_a, doa, *count);
+	}
+	if (s == SB_OK) {
+		s = sb_to_host(ctx, mem, out_b, dob, *count);
+	}
+	if (s == SB_OK && out_dist) {
+		s = sb_to_host(ctx, mem, out_dist, dod, *count);
+	}
+	cudaStreamSynchronize(ctx->stream);
+	if (tree) {
+		sb_flat_destroy(tree);
+	}
+	return s;
+}

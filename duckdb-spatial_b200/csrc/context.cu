@@ -1,0 +1,224 @@
+// context.cu -- context, scratch arena, error string, kernel-class profiling.
+#include "common.cuh"
+
+#include <stdarg.h>
+
+static thread_local char g_err[512] = "";
+
+void sb_set_error(const char *fmt, ...) {
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(g_err, sizeof(g_err), fmt, ap);
+	va_end(ap);
+}
+
+extern "C" const char *sb_last_error(void) {
+	return g_err;
+}
+
+extern "C" const char *sb_version(void) {
+	return "spatial_b200 0.1 (sm_100a)";
+}
+
+// ---- arena --------------------------------------------------------------------------------------------------
+int sb_arena::alloc(size_t bytes, void **out) {
+	bytes = (bytes + 255) & ~(size_t)255;
+	if (bytes == 0) {
+		bytes = 256;
+	}
+	while (cur_block < blocks.size()) {
+		block &b = blocks[cur_block];
+		if (cur_off + bytes <= b.size) {
+			*out = b.ptr + cur_off;
+			cur_off += bytes;
+			used += bytes;
+			if (used > high_water) {
+				high_water = used;
+			}
+			return SB_OK;
+		}
+		cur_block++;
+		cur_off = 0;
+	}
+	size_t sz = bytes > ((size_t)64 << 20) ? bytes : ((size_t)64 << 20);
+	block nb;
+	cudaError_t e = cudaMalloc((void **)&nb.ptr, sz);
+	if (e != cudaSuccess) {
+		sb_set_error("cudaMalloc(%zu) failed: %s", sz, cudaGetErrorString(e));
+		return SB_ERR_CUDA;
+	}
+	nb.size = sz;
+	blocks.push_back(nb);
+	cur_block = blocks.size() - 1;
+	*out = nb.ptr;
+	cur_off = bytes;
+	used += bytes;
+	if (used > high_water) {
+		high_water = used;
+	}
+	return SB_OK;
+}
+
+void sb_arena::reset() {
+	// coalesce: if the last call spilled over several blocks, replace them by one block of the high-water size
+	if (blocks.size() > 1) {
+		size_t want = high_water + (high_water >> 3);
+		release(); // cudaFree synchronises, so nothing in flight still uses the old blocks
+		block nb;
+		if (cudaMalloc((void **)&nb.ptr, want) == cudaSuccess) {
+			nb.size = want;
+			blocks.push_back(nb);
+		} else {
+			cudaGetLastError();
+		}
+	}
+	cur_block = 0;
+	cur_off = 0;
+	used = 0;
+}
+
+void sb_arena::release() {
+	for (auto &b : blocks) {
+		cudaFree(b.ptr);
+	}
+	blocks.clear();
+	cur_block = 0;
+	cur_off = 0;
+	used = 0;
+}
+
+// ---- context ------------------------------------------------------------------------------------------------
+extern "C" int sb_context_create(int device, sb_context **out) {
+	SB_ARG(out != nullptr, "out");
+	int count = 0;
+	cudaError_t e = cudaGetDeviceCount(&count);
+	if (e != cudaSuccess || count == 0) {
+		sb_set_error("no CUDA device: %s (libspatial_b200 has no CPU fallback)", cudaGetErrorString(e));
+		cudaGetLastError();
+		return SB_ERR_CUDA;
+	}
+	SB_ARG(device >= 0 && device < count, "device index");
+	cudaDeviceProp prop;
+	SB_CUDA(cudaGetDeviceProperties(&prop, device));
+	if (prop.major != 10) {
+		sb_set_error("device %d is sm_%d%d; this library only contains sm_100a code", device, prop.major, prop.minor);
+		return SB_ERR_CUDA;
+	}
+	SB_CUDA(cudaSetDevice(device));
+	sb_context *ctx = new sb_context();
+	ctx->device = device;
+	SB_CUDA(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
+	ctx->stream = ctx->own_stream;
+	SB_CUDA(cudaMallocHost((void **)&ctx->pinned_u64, 64 * sizeof(uint64_t)));
+	*out = ctx;
+	return SB_OK;
+}
+
+extern "C" void sb_context_destroy(sb_context *ctx) {
+	if (!ctx) {
+		return;
+	}
+	cudaSetDevice(ctx->device);
+	cudaStreamSynchronize(ctx->stream);
+	for (auto &kv : ctx->prof) {
+		for (auto &p : kv.second.pending) {
+			cudaEventDestroy(p.first);
+			cudaEventDestroy(p.second);
+		}
+	}
+	for (auto ev : ctx->event_pool) {
+		cudaEventDestroy(ev);
+	}
+	ctx->arena.release();
+	cudaFreeHost(ctx->pinned_u64);
+	cudaStreamDestroy(ctx->own_stream);
+	delete ctx;
+}
+
+extern "C" int sb_context_set_stream(sb_context *ctx, void *cuda_stream) {
+	SB_ARG(ctx != nullptr, "ctx");
+	SB_CUDA(cudaStreamSynchronize(ctx->stream));
+	ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
+	return SB_OK;
+}
+
+extern "C" int sb_context_sync(sb_context *ctx) {
+	SB_ARG(ctx != nullptr, "ctx");
+	SB_CUDA(cudaStreamSynchronize(ctx->stream));
+	return SB_OK;
+}
+
+extern "C" uint64_t sb_context_launches(const sb_context *ctx) {
+	return ctx ? ctx->launches : 0;
+}
+
+extern "C" int sb_context_profile(sb_context *ctx, int enable) {
+	SB_ARG(ctx != nullptr, "ctx");
+	SB_CUDA(cudaStreamSynchronize(ctx->stream));
+	ctx->profiling = enable != 0;
+	for (auto &kv : ctx->prof) {
+		for (auto &p : kv.second.pending) {
+			ctx->event_pool.push_back(p.first);
+			ctx->event_pool.push_back(p.second);
+		}
+	}
+	ctx->prof.clear();
+	return SB_OK;
+}
+
+extern "C" int sb_context_profile_read(sb_context *ctx, const char *tag, double *ms, uint64_t *launches) {
+	SB_ARG(ctx != nullptr && tag != nullptr, "ctx/tag");
+	SB_CUDA(cudaStreamSynchronize(ctx->stream));
+	auto it = ctx->prof.find(tag);
+	double total = 0;
+	uint64_t n = 0;
+	if (it != ctx->prof.end()) {
+		sb_prof_entry &e = it->second;
+		for (auto &p : e.pending) {
+			float t = 0;
+			SB_CUDA(cudaEventElapsedTime(&t, p.first, p.second));
+			e.ms += t;
+			ctx->event_pool.push_back(p.first);
+			ctx->event_pool.push_back(p.second);
+		}
+		e.pending.clear();
+		total = e.ms;
+		n = e.launches;
+	}
+	if (ms) {
+		*ms = total;
+	}
+	if (launches) {
+		*launches = n;
+	}
+	return SB_OK;
+}
+
+static cudaEvent_t prof_event(sb_context *ctx) {
+	if (!ctx->event_pool.empty()) {
+		cudaEvent_t e = ctx->event_pool.back();
+		ctx->event_pool.pop_back();
+		return e;
+	}
+	cudaEvent_t e = nullptr;
+	cudaEventCreate(&e);
+	return e;
+}
+
+sb_prof_scope::sb_prof_scope(sb_context *c, const char *t) : ctx(c) {
+	if (ctx->profiling) {
+		tag = t;
+		a = prof_event(ctx);
+		b = prof_event(ctx);
+		cudaEventRecord(a, ctx->stream);
+	}
+}
+
+sb_prof_scope::~sb_prof_scope() {
+	if (a) {
+		cudaEventRecord(b, ctx->stream);
+		sb_prof_entry &e = ctx->prof[tag];
+		e.launches++;
+		e.pending.push_back({a, b});
+	}
+}

@@ -1,0 +1,107 @@
+// internal.cuh -- device-pointer entry points shared between the .cu files (everything here takes DEVICE
+// pointers and enqueues on ctx->stream; the extern "C" layer in capi.cu does the host staging).
+#pragma once
+#include "common.cuh"
+
+// bbox.cu
+int sbi_bbox_points(sb_context *ctx, const double *x, const double *y, uint64_t n, float *out);
+int sbi_bbox_box2d(sb_context *ctx, const double *x0, const double *y0, const double *x1, const double *y1, uint64_t n,
+                   float *out);
+int sbi_blob_bounds(sb_context *ctx, int mode, const uint8_t *data, const uint64_t *off, uint64_t n, float *out_box,
+                    uint32_t *out_key, uint8_t *valid, int32_t *status, int *any_bad);
+int sbi_blob_extent(sb_context *ctx, int mode, const uint8_t *data, const uint64_t *off, uint64_t n, double *out_box,
+                    uint8_t *valid, int32_t *status, const double *bounds, uint32_t *out_key, int *any_bad);
+int sbi_hilbert_xy(sb_context *ctx, const double *x, const double *y, uint64_t n, const double *b, uint32_t *out);
+int sbi_hilbert_box2d(sb_context *ctx, const double *box4, uint64_t n, const double *b, uint32_t *out);
+int sbi_hilbert_box2df(sb_context *ctx, const float *box4, uint64_t n, const float *b, uint32_t *out);
+
+// radix_sort.cu : sorts bits [begin_bit, end_bit) of the keys, stable. Ping-pongs between (keys, vals) and
+// (keys_alt, vals_alt); *result_in_alt tells where the sorted data ended up. vals_iota: values start as 0..n-1
+// (vals need not be initialised).
+int sbi_radix_sort_u32(sb_context *ctx, uint32_t *keys, uint32_t *keys_alt, uint32_t *vals, uint32_t *vals_alt,
+                       uint64_t n, int begin_bit, int end_bit, bool vals_iota, int *result_in_alt);
+int sbi_radix_sort_u64(sb_context *ctx, uint64_t *keys, uint64_t *keys_alt, uint32_t *vals, uint32_t *vals_alt,
+                       uint64_t n, int begin_bit, int end_bit, bool vals_iota, int *result_in_alt);
+int sbi_iota_u32(sb_context *ctx, uint32_t *out, uint64_t n);
+
+// 24-byte RTreeEntry (rtree_node.hpp:66-75)
+struct sb_entry {
+	uint64_t ptr;
+	float box[4];
+};
+static_assert(sizeof(sb_entry) == 24, "RTreeEntry must be 24 bytes");
+
+struct sb_rtree {
+	int device = 0;
+	uint32_t cap = 0;
+	uint64_t slice = 0;
+	int nlevels = 0;
+	uint64_t counts[16] = {0};
+	uint64_t offsets[16] = {0}; // entry offset of each level inside `entries`
+	sb_entry *entries = nullptr; // one device allocation holding all levels
+	uint64_t total = 0;
+};
+
+// FlatRTree in one device buffer: [sb_flat_header (256 B)][box_array: nodes x float4][idx_array: nodes x u32]
+struct sb_flat_header {
+	uint32_t magic;
+	uint32_t item_count, node_size, nodes, nlayers;
+	uint32_t layer_bounds[16];
+	float tree_box[4];
+	uint32_t pad[64 - 25];
+};
+static_assert(sizeof(sb_flat_header) == 256, "flat header is 256 bytes");
+#define SB_FLAT_MAGIC 0x53423246u
+
+struct sb_flat {
+	int device = 0;
+	sb_flat_header h;
+	void *buffer = nullptr; // device
+	uint64_t bytes = 0;
+	bool owns = true;
+	const float4 *boxes() const {
+		return reinterpret_cast<const float4 *>(static_cast<const char *>(buffer) + sizeof(sb_flat_header));
+	}
+	const uint32_t *idx() const {
+		return reinterpret_cast<const uint32_t *>(static_cast<const char *>(buffer) + sizeof(sb_flat_header) +
+		                                          sizeof(float4) * (size_t)h.nodes);
+	}
+};
+
+// rtree_str.cu
+int sbi_rtree_build_str(sb_context *ctx, const float *box4, const int64_t *row_ids, uint64_t n, uint32_t cap,
+                        sb_rtree **out);
+int sbi_rtree_scan(sb_context *ctx, const sb_rtree *tree, const float *qbox4, uint32_t nq, uint32_t *out_query,
+                   int64_t *out_row, uint64_t capacity, uint64_t *count);
+
+// flat_rtree.cu
+int sbi_flat_build(sb_context *ctx, const float *box4, uint32_t n, uint32_t node_size, sb_flat **out);
+// probe modes: boxes only (candidates), or points with a fused exact predicate against the build's BOX_2D
+struct sb_probe_args {
+	const float4 *probe_box = nullptr; // mode A: float probe boxes
+	const double *px = nullptr, *py = nullptr; // mode B: points (float box derived in-kernel)
+	const double4 *build_box2d = nullptr;      // mode B with pred >= 0: exact refinement
+	int pred = -1;                             // -1 = none
+	uint64_t m = 0;
+	uint32_t index_base = 0;
+};
+int sbi_flat_probe(sb_context *ctx, const sb_flat *tree, const sb_probe_args &args, uint32_t *out_probe,
+                   uint32_t *out_build, uint64_t capacity, uint64_t *count);
+
+// refine.cu
+int sbi_pack_box2d(sb_context *ctx, const double *x0, const double *y0, const double *x1, const double *y1, uint64_t n,
+                   double *out4);
+int sbi_refine_point_box(sb_context *ctx, int pred, const double *px, const double *py, const double *x0,
+                         const double *y0, const double *x1, const double *y1, uint32_t *pp, uint32_t *pb, uint64_t n,
+                         uint64_t *d_count);
+int sbi_refine_point_polygon(sb_context *ctx, const double *px, const double *py, const double *vx, const double *vy,
+                             const uint64_t *ring_off, const uint64_t *poly_off, uint32_t *pp, uint32_t *pb, uint64_t n,
+                             uint64_t *d_count);
+int sbi_refine_dwithin(sb_context *ctx, const double *ax, const double *ay, const double *bx, const double *by,
+                       double r, uint32_t *pa, uint32_t *pb, double *out_d, uint64_t n, uint64_t *d_count);
+int sbi_distance_points(sb_context *ctx, const double *ax, const double *ay, const double *bx, const double *by,
+                        uint64_t n, double *out);
+int sbi_expand_points(sb_context *ctx, const double *x, const double *y, uint64_t n, double r, float *out_box4);
+
+// read a device u64 counter back (synchronises the stream)
+int sbi_read_u64(sb_context *ctx, const uint64_t *dev, uint64_t *host);

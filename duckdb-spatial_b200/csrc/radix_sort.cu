@@ -1,0 +1,320 @@
+// radix_sort.cu -- K3: stable LSD radix sort of (key, u32 value) pairs, "onesweep" style:
+//   one histogram kernel reads the keys once and builds the digit histograms of ALL passes;
+//   each pass is then ONE kernel that ranks a tile with warp-cooperative match/ballot multi-split, resolves the
+//   tile's global digit offsets with a decoupled look-back over per-tile status words (no separate scan pass),
+//   and scatters through shared memory so the global writes are runs of same-digit items.
+// Traffic per pass: n*(key+value) read + n*(key+value) write, plus 1 KB of status words per 4096-item tile.
+// Replaces DuckDB's PhysicalOrder in the CREATE INDEX plan and FlatRTree::Sort (see include/spatial_b200.h).
+#include "internal.cuh"
+
+#define RS_THREADS 256
+#define RS_WARPS (RS_THREADS / 32)
+#define RS_BINS 256
+#define RS_FLAG_AGG 0x40000000u
+#define RS_FLAG_INC 0x80000000u
+#define RS_VALUE_MASK 0x3FFFFFFFu
+
+__device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t *p) {
+	uint32_t v;
+	asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+	return v;
+}
+__device__ __forceinline__ void st_volatile_u32(uint32_t *p, uint32_t v) {
+	asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// ---- histogram of every pass in one read of the keys --------------------------------------------------------
+template <typename KeyT, int MAX_PASSES>
+__global__ void __launch_bounds__(RS_THREADS) k_radix_hist(const KeyT *__restrict__ keys, uint64_t n, int begin_bit,
+                                                           int end_bit, int passes, uint32_t *__restrict__ hist) {
+	__shared__ uint32_t s_hist[MAX_PASSES * RS_BINS];
+	for (int i = threadIdx.x; i < passes * RS_BINS; i += RS_THREADS) {
+		s_hist[i] = 0;
+	}
+	__syncthreads();
+	const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
+	// loop bound rounded up to a whole warp so that __match_any_sync sees all 32 lanes
+	const uint64_t n_round = (n + 31) & ~(uint64_t)31;
+	for (uint64_t i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; i < n_round; i += stride) {
+		const bool valid = i < n;
+		const KeyT k = valid ? keys[i] : KeyT(0);
+#pragma unroll
+		for (int p = 0; p < MAX_PASSES; p++) {
+			if (p < passes) {
+				const int shift = begin_bit + 8 * p;
+				const int bits = min(8, end_bit - shift);
+				const uint32_t d = valid ? (uint32_t)((k >> shift) & (KeyT)((1u << bits) - 1)) : 256u;
+				// warp-aggregated: one shared atomic per distinct digit in the warp (skewed digits stay cheap)
+				const unsigned peers = __match_any_sync(0xFFFFFFFFu, d);
+				if (valid && (peers & sb_lanemask_lt()) == 0) {
+					atomicAdd(&s_hist[p * RS_BINS + d], (uint32_t)__popc(peers));
+				}
+			}
+		}
+	}
+	__syncthreads();
+	for (int i = threadIdx.x; i < passes * RS_BINS; i += RS_THREADS) {
+		const uint32_t c = s_hist[i];
+		if (c) {
+			atomicAdd(&hist[i], c);
+		}
+	}
+}
+
+// exclusive scan of each pass's 256 bins, in place. One block per pass.
+__global__ void __launch_bounds__(RS_BINS) k_radix_scan(uint32_t *__restrict__ hist) {
+	__shared__ uint32_t s_warp[RS_BINS / 32];
+	uint32_t *h = hist + blockIdx.x * RS_BINS;
+	const uint32_t v = h[threadIdx.x];
+	uint32_t inc = v;
+#pragma unroll
+	for (int s = 1; s < 32; s <<= 1) {
+		const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, s);
+		if (sb_lane() >= (unsigned)s) {
+			inc += o;
+		}
+	}
+	if (sb_lane() == 31) {
+		s_warp[threadIdx.x >> 5] = inc;
+	}
+	__syncthreads();
+	uint32_t base = 0;
+	for (int w = 0; w < (int)(threadIdx.x >> 5); w++) {
+		base += s_warp[w];
+	}
+	h[threadIdx.x] = base + inc - v;
+}
+
+// ---- one onesweep pass ---------------------------------------------------------------------------------------
+template <typename KeyT, int ITEMS>
+__global__ void __launch_bounds__(RS_THREADS)
+    k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const uint32_t *__restrict__ vals_in,
+               uint32_t *__restrict__ vals_out, uint64_t n, int shift, uint32_t digit_mask,
+               const uint32_t *__restrict__ bin_base, uint32_t *__restrict__ tile_state, uint32_t *__restrict__ ticket) {
+	constexpr int TILE = RS_THREADS * ITEMS;
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	KeyT *s_keys = reinterpret_cast<KeyT *>(smem_raw);
+	uint32_t *s_vals = reinterpret_cast<uint32_t *>(smem_raw + sizeof(KeyT) * TILE);
+	uint32_t *s_warp_hist = s_vals + TILE;          // [RS_WARPS][RS_BINS]
+	uint32_t *s_digit_off = s_warp_hist + RS_WARPS * RS_BINS; // [RS_BINS] tile-local exclusive scan over digits
+	uint32_t *s_global = s_digit_off + RS_BINS;     // [RS_BINS] global base - digit_off
+	uint32_t *s_scan = s_global + RS_BINS;          // [RS_WARPS]
+	__shared__ uint32_t s_tile;
+
+	if (threadIdx.x == 0) {
+		s_tile = atomicAdd(ticket, 1u); // tiles are claimed in order => a tile's predecessors are always running
+	}
+	for (int i = threadIdx.x; i < RS_WARPS * RS_BINS; i += RS_THREADS) {
+		s_warp_hist[i] = 0;
+	}
+	__syncthreads();
+	const uint32_t tile = s_tile;
+	const uint64_t tile_base = (uint64_t)tile * TILE;
+	const unsigned warp = threadIdx.x >> 5, lane = sb_lane();
+	const unsigned lt_mask = sb_lanemask_lt();
+	const uint32_t tile_count = (uint32_t)min((uint64_t)TILE, n - tile_base);
+
+	KeyT key[ITEMS];
+	uint32_t val[ITEMS];
+	uint32_t pos[ITEMS];
+	const uint64_t first = tile_base + (uint64_t)warp * (32 * ITEMS) + lane;
+#pragma unroll
+	for (int i = 0; i < ITEMS; i++) {
+		const uint64_t gi = first + (uint64_t)i * 32;
+		const bool valid = gi < n;
+		key[i] = valid ? keys_in[gi] : KeyT(0);
+		val[i] = valid ? (vals_in ? vals_in[gi] : (uint32_t)gi) : 0u;
+	}
+	// warp multi-split: stable rank of every key among the warp's keys with the same digit
+	uint32_t *my_hist = s_warp_hist + warp * RS_BINS;
+#pragma unroll
+	for (int i = 0; i < ITEMS; i++) {
+		const bool valid = first + (uint64_t)i * 32 < n;
+		const uint32_t d = valid ? ((uint32_t)(key[i] >> shift) & digit_mask) : 256u;
+		const unsigned peers = __match_any_sync(0xFFFFFFFFu, d);
+		const int leader = __ffs(peers) - 1;
+		uint32_t prev = 0;
+		if ((int)lane == leader && valid) {
+			prev = my_hist[d];
+			my_hist[d] = prev + __popc(peers);
+		}
+		prev = __shfl_sync(0xFFFFFFFFu, prev, leader);
+		pos[i] = prev + __popc(peers & lt_mask);
+		__syncwarp();
+	}
+	__syncthreads();
+
+	// thread d owns digit d: exclusive offsets of the warps, tile total, look-back
+	const unsigned d = threadIdx.x;
+	uint32_t total = 0;
+#pragma unroll
+	for (int w = 0; w < RS_WARPS; w++) {
+		const uint32_t c = s_warp_hist[w * RS_BINS + d];
+		s_warp_hist[w * RS_BINS + d] = total;
+		total += c;
+	}
+	uint32_t *my_state = tile_state + (uint64_t)tile * RS_BINS + d;
+	st_volatile_u32(my_state, (tile == 0 ? RS_FLAG_INC : RS_FLAG_AGG) | total);
+
+	// block exclusive scan of `total` over the 256 digits
+	uint32_t inc = total;
+#pragma unroll
+	for (int s = 1; s < 32; s <<= 1) {
+		const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, s);
+		if (lane >= (unsigned)s) {
+			inc += o;
+		}
+	}
+	if (lane == 31) {
+		s_scan[warp] = inc;
+	}
+	__syncthreads();
+	uint32_t dbase = 0;
+	for (unsigned w = 0; w < warp; w++) {
+		dbase += s_scan[w];
+	}
+	const uint32_t digit_off = dbase + inc - total;
+	s_digit_off[d] = digit_off;
+
+	uint32_t excl = 0;
+	if (tile > 0) {
+		int64_t look = (int64_t)tile - 1;
+		while (true) {
+			const uint32_t s = ld_volatile_u32(tile_state + (uint64_t)look * RS_BINS + d);
+			if ((s & (RS_FLAG_AGG | RS_FLAG_INC)) == 0) {
+				continue; // predecessor has not published yet
+			}
+			excl += s & RS_VALUE_MASK;
+			if (s & RS_FLAG_INC) {
+				break;
+			}
+			look--;
+		}
+		st_volatile_u32(my_state, RS_FLAG_INC | (excl + total));
+	}
+	s_global[d] = bin_base[d] + excl - digit_off;
+	__syncthreads();
+
+	// scatter into shared memory in tile-sorted order
+#pragma unroll
+	for (int i = 0; i < ITEMS; i++) {
+		if (first + (uint64_t)i * 32 < n) {
+			const uint32_t dg = (uint32_t)(key[i] >> shift) & digit_mask;
+			const uint32_t p = s_digit_off[dg] + s_warp_hist[warp * RS_BINS + dg] + pos[i];
+			s_keys[p] = key[i];
+			s_vals[p] = val[i];
+		}
+	}
+	__syncthreads();
+	// coalesced runs out to global memory
+#pragma unroll
+	for (int i = 0; i < ITEMS; i++) {
+		const uint32_t p = threadIdx.x + i * RS_THREADS;
+		if (p < tile_count) {
+			const KeyT k = s_keys[p];
+			const uint32_t dg = (uint32_t)(k >> shift) & digit_mask;
+			const uint32_t g = s_global[dg] + p;
+			keys_out[g] = k;
+			vals_out[g] = s_vals[p];
+		}
+	}
+}
+
+template <typename KeyT>
+struct rs_cfg {
+	static constexpr int ITEMS = sizeof(KeyT) == 4 ? 16 : 12;
+	static constexpr int TILE = RS_THREADS * ITEMS;
+	static constexpr size_t SMEM =
+	    (sizeof(KeyT) + 4) * TILE + sizeof(uint32_t) * (RS_WARPS * RS_BINS + 2 * RS_BINS + RS_WARPS);
+	static constexpr int MAX_PASSES = sizeof(KeyT);
+};
+
+template <typename KeyT>
+int sbi_radix_sort_impl(sb_context *ctx, KeyT *keys, KeyT *keys_alt, uint32_t *vals, uint32_t *vals_alt, uint64_t n,
+                        int begin_bit, int end_bit, bool vals_iota, int *result_in_alt) {
+	using cfg = rs_cfg<KeyT>;
+	*result_in_alt = 0;
+	if (n == 0) {
+		return SB_OK;
+	}
+	SB_ARG(n < ((uint64_t)1 << 30), "radix sort: n must be < 2^30");
+	SB_ARG(begin_bit >= 0 && end_bit <= (int)sizeof(KeyT) * 8 && begin_bit <= end_bit, "radix sort bit range");
+	const int passes = (end_bit - begin_bit + 7) / 8;
+	if (passes == 0) {
+		if (vals_iota) { // still materialise the identity permutation
+			SB_TRY(sbi_iota_u32(ctx, vals, n));
+		}
+		return SB_OK;
+	}
+	const uint64_t tiles = (n + cfg::TILE - 1) / cfg::TILE;
+	// temp: [passes*256 hist][passes tickets (padded to 64)][passes * tiles * 256 status words]
+	const size_t words = (size_t)passes * RS_BINS + 64 + (size_t)passes * tiles * RS_BINS;
+	uint32_t *temp = nullptr;
+	SB_TRY(ctx->scratch_t<uint32_t>(words, &temp));
+	SB_CUDA(cudaMemsetAsync(temp, 0, words * sizeof(uint32_t), ctx->stream));
+	uint32_t *hist = temp;
+	uint32_t *tickets = temp + (size_t)passes * RS_BINS;
+	uint32_t *state = tickets + 64;
+
+	static bool attr_set = false;
+	if (!attr_set) {
+		SB_CUDA(cudaFuncSetAttribute(k_onesweep<KeyT, cfg::ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+		                             (int)cfg::SMEM));
+		attr_set = true;
+	}
+	{
+		sb_prof_scope ps(ctx, "radix_hist");
+		k_radix_hist<KeyT, cfg::MAX_PASSES><<<sb_grid(n, RS_THREADS * 8, 8), RS_THREADS, 0, ctx->stream>>>(
+		    keys, n, begin_bit, end_bit, passes, hist);
+		SB_LAUNCH_CHECK(ctx);
+		k_radix_scan<<<passes, RS_BINS, 0, ctx->stream>>>(hist);
+		SB_LAUNCH_CHECK(ctx);
+	}
+	KeyT *kin = keys, *kout = keys_alt;
+	uint32_t *vin = vals, *vout = vals_alt;
+	for (int p = 0; p < passes; p++) {
+		const int shift = begin_bit + 8 * p;
+		const int bits = end_bit - shift < 8 ? end_bit - shift : 8;
+		sb_prof_scope ps(ctx, "radix_onesweep");
+		k_onesweep<KeyT, cfg::ITEMS><<<(unsigned)tiles, RS_THREADS, cfg::SMEM, ctx->stream>>>(
+		    kin, kout, (p == 0 && vals_iota) ? nullptr : vin, vout, n, shift, (1u << bits) - 1, hist + p * RS_BINS,
+		    state + (size_t)p * tiles * RS_BINS, tickets + p);
+		SB_LAUNCH_CHECK(ctx);
+		KeyT *tk = kin;
+		kin = kout;
+		kout = tk;
+		uint32_t *tv = vin;
+		vin = vout;
+		vout = tv;
+	}
+	*result_in_alt = (passes & 1);
+	return SB_OK;
+}
+
+int sbi_radix_sort_u32(sb_context *ctx, uint32_t *keys, uint32_t *keys_alt, uint32_t *vals, uint32_t *vals_alt,
+                       uint64_t n, int begin_bit, int end_bit, bool vals_iota, int *result_in_alt) {
+	return sbi_radix_sort_impl<uint32_t>(ctx, keys, keys_alt, vals, vals_alt, n, begin_bit, end_bit, vals_iota,
+	                                     result_in_alt);
+}
+
+int sbi_radix_sort_u64(sb_context *ctx, uint64_t *keys, uint64_t *keys_alt, uint32_t *vals, uint32_t *vals_alt,
+                       uint64_t n, int begin_bit, int end_bit, bool vals_iota, int *result_in_alt) {
+	return sbi_radix_sort_impl<uint64_t>(ctx, keys, keys_alt, vals, vals_alt, n, begin_bit, end_bit, vals_iota,
+	                                     result_in_alt);
+}
+
+__global__ void __launch_bounds__(256) k_iota_u32(uint32_t *out, uint64_t n) {
+	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+		out[i] = (uint32_t)i;
+	}
+}
+
+int sbi_iota_u32(sb_context *ctx, uint32_t *out, uint64_t n) {
+	if (n == 0) {
+		return SB_OK;
+	}
+	k_iota_u32<<<sb_grid(n, 256, 16), 256, 0, ctx->stream>>>(out, n);
+	SB_LAUNCH_CHECK(ctx);
+	return SB_OK;
+}

@@ -1,0 +1,240 @@
+// refine.cu -- K6: exact fp64 refinement of candidate pairs, compacting survivors in place.
+// Compiled with -fmad=false: every product/difference is individually rounded like the reference's x86-64 build.
+#include "internal.cuh"
+
+int sbi_read_u64(sb_context *ctx, const uint64_t *dev, uint64_t *host) {
+	SB_CUDA(cudaMemcpyAsync(ctx->pinned_u64, dev, sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+	SB_CUDA(cudaStreamSynchronize(ctx->stream));
+	*host = ctx->pinned_u64[0];
+	return SB_OK;
+}
+
+__global__ void __launch_bounds__(256) k_pack_box2d(const double *__restrict__ x0, const double *__restrict__ y0,
+                                                    const double *__restrict__ x1, const double *__restrict__ y1,
+                                                    uint64_t n, double4 *__restrict__ out) {
+	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+		out[i] = make_double4(x0[i], y0[i], x1[i], y1[i]);
+	}
+}
+
+int sbi_pack_box2d(sb_context *ctx, const double *x0, const double *y0, const double *x1, const double *y1, uint64_t n,
+                   double *out4) {
+	if (n == 0) {
+		return SB_OK;
+	}
+	k_pack_box2d<<<sb_grid(n, 256, 16), 256, 0, ctx->stream>>>(x0, y0, x1, y1, n, reinterpret_cast<double4 *>(out4));
+	SB_LAUNCH_CHECK(ctx);
+	return SB_OK;
+}
+
+// Order-preserving in-place compaction of a pair list is done in two kernels: flags + per-block counts, then a
+// decoupled look-back is overkill here -- survivors are appended through a warp-aggregated atomic cursor into a
+// scratch copy and copied back (pair order is not part of the contract; pair SETS are).
+template <class PRED>
+__global__ void __launch_bounds__(256) k_refine(PRED pred, const uint32_t *__restrict__ pa,
+                                                const uint32_t *__restrict__ pb, uint64_t n, uint32_t *__restrict__ oa,
+                                                uint32_t *__restrict__ ob, double *__restrict__ od,
+                                                unsigned long long *__restrict__ counter) {
+	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+	const uint64_t n_round = (n + 31) & ~(uint64_t)31;
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+		bool keep = false;
+		uint32_t a = 0, b = 0;
+		double dist = 0.0;
+		if (i < n) {
+			a = pa[i];
+			b = pb[i];
+			keep = pred(a, b, dist);
+		}
+		const unsigned m = __ballot_sync(0xFFFFFFFFu, keep);
+		if (m) {
+			unsigned long long base = 0;
+			const int leader = __ffs(m) - 1;
+			if ((int)sb_lane() == leader) {
+				base = atomicAdd(counter, (unsigned long long)__popc(m));
+			}
+			base = __shfl_sync(0xFFFFFFFFu, base, leader);
+			if (keep) {
+				const unsigned long long o = base + __popc(m & sb_lanemask_lt());
+				oa[o] = a;
+				ob[o] = b;
+				if (od) {
+					od[o] = dist;
+				}
+			}
+		}
+	}
+}
+
+struct pred_point_box {
+	const double *px, *py, *x0, *y0, *x1, *y1;
+	int strict;
+	__device__ bool operator()(uint32_t a, uint32_t b, double &) const {
+		const double x = px[a], y = py[a];
+		const double bx0 = x0[b], by0 = y0[b], bx1 = x1[b], by1 = y1[b];
+		return strict ? (bx0 < x && x < bx1 && by0 < y && y < by1) : (bx0 <= x && x <= bx1 && by0 <= y && y <= by1);
+	}
+};
+
+// ST_Contains::Operation, spatial_functions_scalar.cpp:1938-2051 -- literal control flow, plain fp64 (no FMA):
+// an on-edge hit only leaves the coordinate loop; the ring is then judged by the winding number so far.
+struct pred_point_polygon {
+	const double *px, *py, *vx, *vy;
+	const uint64_t *ring_off, *poly_off;
+	__device__ bool operator()(uint32_t a, uint32_t p, double &) const {
+		const double x = px[a], y = py[a];
+		bool contains = false, first = true;
+		for (uint64_t r = poly_off[p]; r < poly_off[p + 1]; r++) {
+			const uint64_t o = ring_off[r], e = ring_off[r + 1];
+			double x1 = vx[o], y1 = vy[o];
+			int wn = 0;
+			for (uint64_t c = o + 1; c < e; c++) {
+				const double x2 = vx[c], y2 = vy[c];
+				if (!(x1 == x2 && y1 == y2)) {
+					const double y_min = y2 < y1 ? y2 : y1;
+					const double y_max = y1 < y2 ? y2 : y1;
+					if (!(y > y_max || y < y_min)) {
+						const double side_v = __dsub_rn(__dmul_rn(__dsub_rn(x, x1), __dsub_rn(y2, y1)),
+						                                __dmul_rn(__dsub_rn(x2, x1), __dsub_rn(y, y1)));
+						if (side_v == 0.0 && (((x1 <= x && x < x2) || (x1 >= x && x > x2)) ||
+						                      ((y1 <= y && y < y2) || (y1 >= y && y > y2)))) {
+							break;
+						} else if (side_v < 0.0 && (y1 < y && y <= y2)) {
+							wn++;
+						} else if (side_v > 0.0 && (y2 <= y && y < y1)) {
+							wn--;
+						}
+					}
+				}
+				x1 = x2;
+				y1 = y2;
+			}
+			const bool in_ring = wn != 0;
+			if (first) {
+				if (!in_ring) {
+					contains = false;
+					break;
+				}
+				contains = true;
+			} else if (in_ring) {
+				contains = false;
+				break;
+			}
+			first = false;
+		}
+		return contains;
+	}
+};
+
+// ST_Distance(POINT_2D, POINT_2D) :2189-2214: sqrt(pow(dx,2) + pow(dy,2)); pow(v,2) == v*v exactly (glibc),
+// sqrt is IEEE correctly rounded on both sides.
+__device__ __forceinline__ double dist_pp(double ax, double ay, double bx, double by) {
+	const double dx = __dsub_rn(ax, bx), dy = __dsub_rn(ay, by);
+	return __dsqrt_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
+}
+
+struct pred_dwithin {
+	const double *ax, *ay, *bx, *by;
+	double r;
+	__device__ bool operator()(uint32_t a, uint32_t b, double &d) const {
+		d = dist_pp(ax[a], ay[a], bx[b], by[b]);
+		return d <= r;
+	}
+};
+
+template <class PRED>
+static int run_refine(sb_context *ctx, const char *tag, PRED pred, uint32_t *pa, uint32_t *pb, double *od, uint64_t n,
+                      uint64_t *count) {
+	*count = 0;
+	if (n == 0) {
+		return SB_OK;
+	}
+	uint32_t *oa = nullptr, *ob = nullptr;
+	double *tmp_d = nullptr;
+	unsigned long long *d_counter = nullptr;
+	SB_TRY(ctx->scratch_t(n, &oa));
+	SB_TRY(ctx->scratch_t(n, &ob));
+	if (od) {
+		SB_TRY(ctx->scratch_t(n, &tmp_d));
+	}
+	SB_TRY(ctx->scratch_t(1, &d_counter));
+	SB_CUDA(cudaMemsetAsync(d_counter, 0, sizeof(*d_counter), ctx->stream));
+	{
+		sb_prof_scope ps(ctx, tag);
+		k_refine<<<sb_grid(n, 256, 16), 256, 0, ctx->stream>>>(pred, pa, pb, n, oa, ob, tmp_d, d_counter);
+		SB_LAUNCH_CHECK(ctx);
+	}
+	SB_TRY(sbi_read_u64(ctx, reinterpret_cast<const uint64_t *>(d_counter), count));
+	if (*count) {
+		SB_CUDA(cudaMemcpyAsync(pa, oa, *count * sizeof(uint32_t), cudaMemcpyDeviceToDevice, ctx->stream));
+		SB_CUDA(cudaMemcpyAsync(pb, ob, *count * sizeof(uint32_t), cudaMemcpyDeviceToDevice, ctx->stream));
+		if (od) {
+			SB_CUDA(cudaMemcpyAsync(od, tmp_d, *count * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
+		}
+	}
+	return SB_OK;
+}
+
+int sbi_refine_point_box(sb_context *ctx, int pred, const double *px, const double *py, const double *x0,
+                         const double *y0, const double *x1, const double *y1, uint32_t *pp, uint32_t *pb, uint64_t n,
+                         uint64_t *count) {
+	pred_point_box p = {px, py, x0, y0, x1, y1, pred == SB_PRED_WITHIN};
+	return run_refine(ctx, "refine_box", p, pp, pb, nullptr, n, count);
+}
+
+int sbi_refine_point_polygon(sb_context *ctx, const double *px, const double *py, const double *vx, const double *vy,
+                             const uint64_t *ring_off, const uint64_t *poly_off, uint32_t *pp, uint32_t *pb, uint64_t n,
+                             uint64_t *count) {
+	pred_point_polygon p = {px, py, vx, vy, ring_off, poly_off};
+	return run_refine(ctx, "refine_pip", p, pp, pb, nullptr, n, count);
+}
+
+int sbi_refine_dwithin(sb_context *ctx, const double *ax, const double *ay, const double *bx, const double *by,
+                       double r, uint32_t *pa, uint32_t *pb, double *out_d, uint64_t n, uint64_t *count) {
+	pred_dwithin p = {ax, ay, bx, by, r};
+	return run_refine(ctx, "refine_dist", p, pa, pb, out_d, n, count);
+}
+
+__global__ void __launch_bounds__(256) k_distance(const double *__restrict__ ax, const double *__restrict__ ay,
+                                                  const double *__restrict__ bx, const double *__restrict__ by,
+                                                  uint64_t n, double *__restrict__ out) {
+	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+		out[i] = dist_pp(ax[i], ay[i], bx[i], by[i]);
+	}
+}
+
+int sbi_distance_points(sb_context *ctx, const double *ax, const double *ay, const double *bx, const double *by,
+                        uint64_t n, double *out) {
+	if (n == 0) {
+		return SB_OK;
+	}
+	sb_prof_scope ps(ctx, "refine_dist");
+	k_distance<<<sb_grid(n, 256, 16), 256, 0, ctx->stream>>>(ax, ay, bx, by, n, out);
+	SB_LAUNCH_CHECK(ctx);
+	return SB_OK;
+}
+
+// conservative float boxes of points grown by r (radius-join build side): any b with dist(a,b) <= r as computed
+// by dist_pp has |ax-bx| <= r(1+2^-52) and likewise in y, so a's float box intersects this one.
+__global__ void __launch_bounds__(256) k_expand_points(const double *__restrict__ x, const double *__restrict__ y,
+                                                       uint64_t n, double r, float4 *__restrict__ out) {
+	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+		const double X = x[i], Y = y[i];
+		const double ex = (fabs(X) + r) * 0x1p-48, ey = (fabs(Y) + r) * 0x1p-48;
+		out[i] = make_float4(sb_f64_to_f32_down(X - r - ex), sb_f64_to_f32_down(Y - r - ey),
+		                     sb_f64_to_f32_up(X + r + ex), sb_f64_to_f32_up(Y + r + ey));
+	}
+}
+
+int sbi_expand_points(sb_context *ctx, const double *x, const double *y, uint64_t n, double r, float *out_box4) {
+	if (n == 0) {
+		return SB_OK;
+	}
+	sb_prof_scope ps(ctx, "bbox");
+	k_expand_points<<<sb_grid(n, 256, 16), 256, 0, ctx->stream>>>(x, y, n, r, reinterpret_cast<float4 *>(out_box4));
+	SB_LAUNCH_CHECK(ctx);
+	return SB_OK;
+}

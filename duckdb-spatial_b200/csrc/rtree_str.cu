@@ -1,0 +1,402 @@
+// rtree_str.cu -- K4a: STR bulk load of the persistent RTREE + batched index scan.
+//
+// Reference algorithm (see include/spatial_b200.h for file:line): ORDER BY x-centre, then per layer: runs of
+// `slice` entries re-sorted by fp32 y-centre, packed `cap` per node, leaf nodes sorted by row id, node box = union.
+// B200 formulation: every sort is one stable radix sort over the whole layer --
+//   x-order : 32-bit key  = order-preserving bits of float(min_x + max_x)   (x0.5 in fp64 is monotone and exact)
+//   y-order : 64-bit key  = (position_in_layer / slice) << 32 | order-preserving bits of float((min_y+max_y)/2)
+// followed by a pack kernel (one CTA per node: gather, rank-sort by row id in shared memory, union, coalesced
+// 24-byte entry stores). Level sizes are known on the host from n and cap, so the whole build is enqueued
+// without a single device->host synchronisation.
+#include "internal.cuh"
+
+#include <math.h>
+
+__global__ void __launch_bounds__(256) k_str_xkeys(const float4 *__restrict__ box, uint64_t n,
+                                                   uint32_t *__restrict__ keys) {
+	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+		const float4 b = box[i];
+		// ST_Centroid::ExecuteBox<float>: (float)min_x + (float)max_x in fp32, spatial_functions_scalar.cpp:1490-1494
+		keys[i] = sb_f32_sort_key(__fadd_rn(b.x, b.z));
+	}
+}
+
+// level 0: entries are addressed through the x-order permutation
+__global__ void __launch_bounds__(256) k_str_ykeys_leaf(const float4 *__restrict__ box,
+                                                        const uint32_t *__restrict__ perm, uint64_t n, uint64_t slice,
+                                                        uint64_t *__restrict__ keys, uint32_t *__restrict__ vals) {
+	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+	for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += stride) {
+		const uint32_t src = perm[j];
+		const float4 b = box[src];
+		// bounds.Center().y = (min.y + max.y) / 2 in fp32, bbox.hpp:78-80, rtree_index_create_physical.cpp:172-174
+		const float yc = __fdiv_rn(__fadd_rn(b.y, b.w), 2.0f);
+		keys[j] = ((j / slice) << 32) | (uint64_t)sb_f32_sort_key(yc);
+		vals[j] = src;
+	}
+}
+
+__global__ void __launch_bounds__(256) k_str_ykeys_upper(const sb_entry *__restrict__ cur, uint64_t n, uint64_t slice,
+                                                         uint64_t *__restrict__ keys) {
+	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+	for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += stride) {
+		const float yc = __fdiv_rn(__fadd_rn(cur[j].box[1], cur[j].box[3]), 2.0f);
+		keys[j] = ((j / slice) << 32) | (uint64_t)sb_f32_sort_key(yc);
+	}
+}
+
+// One CTA per node. LEAF: gather (row id, box) through the permutation and order the node's entries by row id
+// (RTreeNode::SortEntriesByRowId, rtree_node.hpp:151-155). UPPER: gather already-built entries in sorted order.
+// Writes the node's entries (24 B each, staged in shared memory, stored as coalesced 8-byte words) and one
+// parent entry {(type<<56)|node index, union box}.
+template <bool LEAF>
+__global__ void __launch_bounds__(256)
+    k_str_pack(const float4 *__restrict__ box, const int64_t *__restrict__ row_ids, const sb_entry *__restrict__ cur,
+               const uint32_t *__restrict__ perm, uint64_t count, uint32_t cap, sb_entry *__restrict__ level_out,
+               sb_entry *__restrict__ parent_out, uint64_t parent_type) {
+	__shared__ int64_t s_row[256];
+	__shared__ uint64_t s_words[256 * 3];
+	__shared__ float s_red[8][4];
+	const uint64_t node = blockIdx.x;
+	const uint64_t beg = node * cap;
+	const uint32_t cnt = (uint32_t)min((uint64_t)cap, count - beg);
+	const unsigned t = threadIdx.x;
+	sb_entry e;
+	e.ptr = 0;
+	e.box[0] = e.box[1] = FLT_MAX;
+	e.box[2] = e.box[3] = -FLT_MAX;
+	if (t < cnt) {
+		const uint32_t src = perm[beg + t];
+		if (LEAF) {
+			const float4 b = box[src];
+			e.ptr = (uint64_t)row_ids[src] & 0x00FFFFFFFFFFFFFFull; // RTree::MakeRowId: type ROW_ID = 0
+			e.box[0] = b.x, e.box[1] = b.y, e.box[2] = b.z, e.box[3] = b.w;
+		} else {
+			e = cur[src];
+		}
+	}
+	uint32_t rank = t;
+	if (LEAF) {
+		if (t < cnt) {
+			s_row[t] = (int64_t)(e.ptr << 8) >> 8; // sign-extended 56-bit row id
+		}
+		__syncthreads();
+		if (t < cnt) {
+			const int64_t mine = s_row[t];
+			rank = 0;
+			for (uint32_t k = 0; k < cnt; k++) {
+				const int64_t o = s_row[k];
+				rank += (o < mine) || (o == mine && k < t);
+			}
+		}
+	}
+	if (t < cnt) {
+		s_words[3 * rank + 0] = e.ptr;
+		s_words[3 * rank + 1] = ((uint64_t)__float_as_uint(e.box[1]) << 32) | __float_as_uint(e.box[0]);
+		s_words[3 * rank + 2] = ((uint64_t)__float_as_uint(e.box[3]) << 32) | __float_as_uint(e.box[2]);
+	}
+	// union of the node's boxes (RTreeNode::GetBounds, rtree_node.hpp:92-99): fp32 min/max
+	float u0 = e.box[0], u1 = e.box[1], u2 = e.box[2], u3 = e.box[3];
+#pragma unroll
+	for (int s = 16; s > 0; s >>= 1) {
+		u0 = fminf(u0, __shfl_xor_sync(0xFFFFFFFFu, u0, s));
+		u1 = fminf(u1, __shfl_xor_sync(0xFFFFFFFFu, u1, s));
+		u2 = fmaxf(u2, __shfl_xor_sync(0xFFFFFFFFu, u2, s));
+		u3 = fmaxf(u3, __shfl_xor_sync(0xFFFFFFFFu, u3, s));
+	}
+	if (sb_lane() == 0) {
+		s_red[t >> 5][0] = u0, s_red[t >> 5][1] = u1, s_red[t >> 5][2] = u2, s_red[t >> 5][3] = u3;
+	}
+	__syncthreads();
+	uint64_t *out_words = reinterpret_cast<uint64_t *>(level_out + beg);
+	for (uint32_t w = t; w < cnt * 3; w += blockDim.x) {
+		out_words[w] = s_words[w];
+	}
+	if (t == 0) {
+		const unsigned nw = (blockDim.x + 31) >> 5;
+		for (unsigned w = 1; w < nw; w++) {
+			u0 = fminf(u0, s_red[w][0]);
+			u1 = fminf(u1, s_red[w][1]);
+			u2 = fmaxf(u2, s_red[w][2]);
+			u3 = fmaxf(u3, s_red[w][3]);
+		}
+		sb_entry p;
+		p.ptr = (parent_type << 56) | node;
+		p.box[0] = u0, p.box[1] = u1, p.box[2] = u2, p.box[3] = u3;
+		parent_out[node] = p;
+	}
+}
+
+static int bit_width_u64(uint64_t v) {
+	int b = 0;
+	while (v) {
+		b++;
+		v >>= 1;
+	}
+	return b;
+}
+
+int sbi_rtree_build_str(sb_context *ctx, const float *box4, const int64_t *row_ids, uint64_t n, uint32_t cap,
+                        sb_rtree **out) {
+	SB_ARG(cap >= 4 && cap <= 255, "max_node_capacity must be in [4, 255]");
+	SB_ARG(n < ((uint64_t)1 << 30), "n must be < 2^30");
+	sb_rtree *t = new sb_rtree();
+	t->device = ctx->device;
+	t->cap = cap;
+	*out = t;
+	if (n == 0) {
+		return SB_OK;
+	}
+	// Finalize: slice = ceil(sqrt(ceil(n / cap))) * cap, rtree_index_create_physical.cpp:349-351
+	t->slice = (uint64_t)ceil(sqrt((double)((n + cap - 1) / cap))) * cap;
+	// level sizes are a pure function of (n, cap)
+	uint64_t cnt = n;
+	int nl = 0;
+	uint64_t total = 0;
+	while (true) {
+		t->counts[nl] = cnt;
+		t->offsets[nl] = total;
+		total += cnt;
+		nl++;
+		if (cnt == 1 && nl > 1) {
+			break;
+		}
+		cnt = (cnt + cap - 1) / cap; // n == 1: a lone row id is wrapped into a leaf page (:241-246)
+	}
+	t->nlevels = nl;
+	t->total = total;
+	SB_CUDA(cudaMalloc((void **)&t->entries, total * sizeof(sb_entry)));
+
+	const float4 *box = reinterpret_cast<const float4 *>(box4);
+	const unsigned block = ((cap + 31) / 32) * 32;
+
+	// --- ORDER BY x centre ---------------------------------------------------------------------------------
+	uint32_t *k32 = nullptr, *k32b = nullptr, *v32 = nullptr, *v32b = nullptr;
+	SB_TRY(ctx->scratch_t(n, &k32));
+	SB_TRY(ctx->scratch_t(n, &k32b));
+	SB_TRY(ctx->scratch_t(n, &v32));
+	SB_TRY(ctx->scratch_t(n, &v32b));
+	{
+		sb_prof_scope ps(ctx, "str_keys");
+		k_str_xkeys<<<sb_grid(n, 256, 16), 256, 0, ctx->stream>>>(box, n, k32);
+		SB_LAUNCH_CHECK(ctx);
+	}
+	int alt = 0;
+	SB_TRY(sbi_radix_sort_u32(ctx, k32, k32b, v32, v32b, n, 0, 32, true, &alt));
+	const uint32_t *xperm = alt ? v32b : v32;
+	uint32_t *free_v = alt ? v32 : v32b; // the other value buffer is reusable
+
+	// --- level 0: y-sort inside slices, pack leaves ---------------------------------------------------------
+	uint64_t *k64 = nullptr, *k64b = nullptr;
+	SB_TRY(ctx->scratch_t(n, &k64));
+	SB_TRY(ctx->scratch_t(n, &k64b));
+	uint32_t *yv = free_v, *yvb = k32; // k32/k32b are dead after the x sort
+	{
+		sb_prof_scope ps(ctx, "str_keys");
+		k_str_ykeys_leaf<<<sb_grid(n, 256, 16), 256, 0, ctx->stream>>>(box, xperm, n, t->slice, k64, yv);
+		SB_LAUNCH_CHECK(ctx);
+	}
+	const uint64_t nslices0 = (n + t->slice - 1) / t->slice;
+	SB_TRY(sbi_radix_sort_u64(ctx, k64, k64b, yv, yvb, n, 0, 32 + bit_width_u64(nslices0 - 1), false, &alt));
+	const uint32_t *perm = alt ? yvb : yv;
+
+	uint64_t nodes = (n + cap - 1) / cap;
+	sb_entry *parents = nullptr, *parents_b = nullptr;
+	SB_TRY(ctx->scratch_t(nodes, &parents));
+	SB_TRY(ctx->scratch_t((nodes + cap - 1) / cap + 1, &parents_b));
+	{
+		sb_prof_scope ps(ctx, "str_pack");
+		k_str_pack<true><<<(unsigned)nodes, block, 0, ctx->stream>>>(box, row_ids, nullptr, perm, n, cap,
+		                                                            t->entries + t->offsets[0], parents, 1ull);
+		SB_LAUNCH_CHECK(ctx);
+	}
+	// --- upper levels ------------------------------------------------------------------------------------------
+	for (int level = 1; level < nl; level++) {
+		const uint64_t c = t->counts[level];
+		if (c == 1) {
+			SB_CUDA(cudaMemcpyAsync(t->entries + t->offsets[level], parents, sizeof(sb_entry), cudaMemcpyDeviceToDevice,
+			                        ctx->stream));
+			break;
+		}
+		{
+			sb_prof_scope ps(ctx, "str_keys");
+			k_str_ykeys_upper<<<sb_grid(c, 256, 16), 256, 0, ctx->stream>>>(parents, c, t->slice, k64);
+			SB_LAUNCH_CHECK(ctx);
+		}
+		const uint64_t ns = (c + t->slice - 1) / t->slice;
+		SB_TRY(sbi_radix_sort_u64(ctx, k64, k64b, yv, yvb, c, 0, 32 + bit_width_u64(ns - 1), true, &alt));
+		const uint32_t *p = alt ? yvb : yv;
+		const uint64_t nn = (c + cap - 1) / cap;
+		{
+			sb_prof_scope ps(ctx, "str_pack");
+			k_str_pack<false><<<(unsigned)nn, block, 0, ctx->stream>>>(nullptr, nullptr, parents, p, c, cap,
+			                                                          t->entries + t->offsets[level], parents_b, 2ull);
+			SB_LAUNCH_CHECK(ctx);
+		}
+		sb_entry *tmp = parents;
+		parents = parents_b;
+		parents_b = tmp;
+	}
+	return SB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Batched index scan. One warp per query, depth-first with an explicit stack in shared memory, so the row ids of
+// a query come out in exactly the reference's DFS order (rtree_scanner.hpp:38-83). Two launches: count, fill.
+// ---------------------------------------------------------------------------------------------------------------
+#define SCAN_WARPS 4
+#define SCAN_STACK 1536 // >= (levels-1) * cap + 1 for cap <= 255 and up to 7 levels
+
+struct scan_levels {
+	const sb_entry *lvl[16];
+	uint64_t cnt[16];
+	int nlevels;
+	uint32_t cap;
+};
+
+__device__ __forceinline__ void load_entry(const sb_entry *e, uint64_t &ptr, float4 &b) {
+	const uint64_t *w = reinterpret_cast<const uint64_t *>(e);
+	ptr = w[0];
+	const uint64_t a = w[1], c = w[2];
+	b = make_float4(__uint_as_float((uint32_t)a), __uint_as_float((uint32_t)(a >> 32)), __uint_as_float((uint32_t)c),
+	                __uint_as_float((uint32_t)(c >> 32)));
+}
+
+__global__ void __launch_bounds__(SCAN_WARPS * 32)
+    k_rtree_scan(scan_levels L, const float4 *__restrict__ queries, uint32_t nq, uint64_t *__restrict__ counts,
+                 const uint64_t *__restrict__ offsets, uint32_t *__restrict__ out_query,
+                 int64_t *__restrict__ out_row) {
+	__shared__ uint32_t s_stack[SCAN_WARPS][SCAN_STACK];
+	const unsigned warp = threadIdx.x >> 5, lane = sb_lane();
+	const unsigned lt = sb_lanemask_lt();
+	uint32_t *stack = s_stack[warp];
+	const uint32_t nwarps = gridDim.x * SCAN_WARPS;
+	for (uint32_t q = blockIdx.x * SCAN_WARPS + warp; q < nq; q += nwarps) {
+		const float4 qb = queries[q];
+		uint64_t emitted = 0;
+		const uint64_t base = offsets ? offsets[q] : 0;
+		int sp = 0;
+		{
+			// RTreeIndex::InitializeScan root pre-check, rtree_index.cpp:110
+			uint64_t rp;
+			float4 rb;
+			load_entry(L.lvl[L.nlevels - 1], rp, rb);
+			if (sb_box_intersects(qb, rb)) {
+				if (lane == 0) {
+					stack[0] = ((uint32_t)(L.nlevels - 2) << 28) | 0u;
+				}
+				sp = 1;
+			}
+		}
+		__syncwarp();
+		while (sp > 0) {
+			const uint32_t top = stack[sp - 1];
+			sp--;
+			__syncwarp();
+			const int level = (int)(top >> 28);
+			const uint64_t node = top & 0x0FFFFFFFu;
+			const uint64_t beg = node * L.cap;
+			const uint32_t cnt = (uint32_t)min((uint64_t)L.cap, L.cnt[level] - beg);
+			if (level == 0) {
+				for (uint32_t c0 = 0; c0 < cnt; c0 += 32) {
+					const uint32_t i = c0 + lane;
+					bool hit = false;
+					uint64_t ptr = 0;
+					if (i < cnt) {
+						float4 b;
+						load_entry(L.lvl[0] + beg + i, ptr, b);
+						hit = sb_box_intersects(qb, b);
+					}
+					const unsigned m = __ballot_sync(0xFFFFFFFFu, hit);
+					if (hit && out_row) {
+						const uint64_t o = base + emitted + __popc(m & lt);
+						out_row[o] = (int64_t)(ptr << 8) >> 8;
+						out_query[o] = q;
+					}
+					emitted += __popc(m);
+				}
+			} else {
+				// push hit children in reverse entry order so that the first hit is popped first (pre-order DFS)
+				const uint32_t chunks = (cnt + 31) / 32;
+				for (int c = (int)chunks - 1; c >= 0; c--) {
+					const uint32_t i = (uint32_t)c * 32 + lane;
+					bool hit = false;
+					uint64_t ptr = 0;
+					if (i < cnt) {
+						float4 b;
+						load_entry(L.lvl[level] + beg + i, ptr, b);
+						hit = sb_box_intersects(qb, b);
+					}
+					const unsigned m = __ballot_sync(0xFFFFFFFFu, hit);
+					const int nh = __popc(m);
+					if (hit) {
+						// lanes above me are pushed first (deeper in the stack)
+						const int above = __popc(m & ~lt & ~(1u << lane));
+						const int slot = sp + above;
+						if (slot < SCAN_STACK) {
+							stack[slot] = ((uint32_t)(level - 1) << 28) | (uint32_t)(ptr & 0x0FFFFFFFull);
+						}
+					}
+					sp += nh;
+				}
+				__syncwarp();
+			}
+		}
+		if (lane == 0 && counts) {
+			counts[q] = emitted;
+		}
+	}
+}
+
+int sbi_rtree_scan(sb_context *ctx, const sb_rtree *tree, const float *qbox4, uint32_t nq, uint32_t *out_query,
+                   int64_t *out_row, uint64_t capacity, uint64_t *count) {
+	*count = 0;
+	if (nq == 0 || tree->nlevels == 0) {
+		return SB_OK;
+	}
+	SB_ARG((uint64_t)(tree->nlevels - 1) * tree->cap + 1 <= SCAN_STACK, "tree too deep for the scan stack");
+	scan_levels L;
+	L.nlevels = tree->nlevels;
+	L.cap = tree->cap;
+	for (int i = 0; i < tree->nlevels; i++) {
+		L.lvl[i] = tree->entries + tree->offsets[i];
+		L.cnt[i] = tree->counts[i];
+	}
+	uint64_t *d_counts = nullptr, *d_offsets = nullptr;
+	SB_TRY(ctx->scratch_t(nq, &d_counts));
+	SB_TRY(ctx->scratch_t(nq, &d_offsets));
+	const unsigned grid = sb_grid(nq, SCAN_WARPS, 8);
+	const float4 *q = reinterpret_cast<const float4 *>(qbox4);
+	{
+		sb_prof_scope ps(ctx, "rtree_scan");
+		k_rtree_scan<<<grid, SCAN_WARPS * 32, 0, ctx->stream>>>(L, q, nq, d_counts, nullptr, nullptr, nullptr);
+		SB_LAUNCH_CHECK(ctx);
+	}
+	std::vector<uint64_t> h(nq);
+	SB_CUDA(cudaMemcpyAsync(h.data(), d_counts, nq * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+	SB_CUDA(cudaStreamSynchronize(ctx->stream));
+	uint64_t run = 0;
+	for (uint32_t i = 0; i < nq; i++) {
+		const uint64_t c = h[i];
+		h[i] = run;
+		run += c;
+	}
+	*count = run;
+	if (run > capacity) {
+		sb_set_error("rtree scan: %llu results, capacity %llu", (unsigned long long)run, (unsigned long long)capacity);
+		return SB_ERR_CAPACITY;
+	}
+	if (run == 0) {
+		return SB_OK;
+	}
+	SB_CUDA(cudaMemcpyAsync(d_offsets, h.data(), nq * sizeof(uint64_t), cudaMemcpyHostToDevice, ctx->stream));
+	{
+		sb_prof_scope ps(ctx, "rtree_scan");
+		k_rtree_scan<<<grid, SCAN_WARPS * 32, 0, ctx->stream>>>(L, q, nq, nullptr, d_offsets, out_query, out_row);
+		SB_LAUNCH_CHECK(ctx);
+	}
+	// h (pageable) is read by the async H2D copy: finish it before h goes out of scope
+	SB_CUDA(cudaStreamSynchronize(ctx->stream));
+	return SB_OK;
+}

@@ -1,0 +1,211 @@
+/*
+ * spatial_b200.h -- C-ABI of libspatial_b200.so: the B200 (sm_100a) implementation of duckdb-spatial's
+ * data-parallel hot path. This is the drop-in boundary: the DuckDB extension keeps its own ScalarFunction /
+ * index / operator registrations and their bodies call these entry points on whole columns.
+ * Reference paths are relative to the yuiseki/duckdb-spatial tree.
+ *
+ * Conventions
+ *  - every function returns 0 on success, a negative sb_status otherwise; sb_last_error() gives the message of
+ *    the calling thread's last failure. No C++ types, no exceptions cross this boundary.
+ *  - `mem` says where ALL data pointers of that call live: SB_HOST (pageable or pinned host memory; the library
+ *    stages through device memory and copies results back before returning) or SB_DEVICE (device pointers on
+ *    the context's device; the call is asynchronous on the context's stream unless it returns a count).
+ *  - boxes are 4 floats/doubles in the order min_x, min_y, max_x, max_y (BOX_2DF / BOX_2D child order,
+ *    src/spatial/spatial_types.cpp:40-71).
+ *  - blobs: a GEOMETRY column is passed as one byte buffer + n+1 byte offsets (DuckDB string_t payloads packed
+ *    back to back by the host glue).
+ *  - There is no CPU fallback: every entry point fails with SB_ERR_CUDA when no sm_100 device is usable.
+ */
+#ifndef SPATIAL_B200_H
+#define SPATIAL_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SB_API __attribute__((visibility("default")))
+
+typedef enum { SB_HOST = 0, SB_DEVICE = 1 } sb_mem;
+
+typedef enum {
+	SB_OK = 0,
+	SB_ERR_CUDA = -1,     /* CUDA runtime error (message has the CUDA string) */
+	SB_ERR_ARG = -2,      /* invalid argument */
+	SB_ERR_CAPACITY = -3, /* caller-provided output too small; *count holds the needed size */
+	SB_ERR_GEOMETRY = -4, /* a blob failed validation (per-row status array has details) */
+	SB_ERR_EMPTY = -5     /* operation not defined on an empty geometry (ST_Hilbert(geom, bounds)) */
+} sb_status;
+
+/* per-row blob status written by the blob kernels (never a trap in-kernel) */
+#define SB_ROW_OK 0
+#define SB_ROW_BAD_VERSION (-1) /* geometry_properties.hpp:28-36 CheckVersion throws NotImplementedException */
+#define SB_ROW_TRUNCATED (-2)   /* Cursor bounds check, util/cursor.hpp throws SerializationException */
+#define SB_ROW_EMPTY 1          /* ST_Hilbert(geom,bounds) on empty input: InvalidInputException */
+
+typedef struct sb_context sb_context;
+typedef struct sb_rtree sb_rtree; /* persistent RTREE index, STR bulk-loaded (CREATE INDEX ... USING RTREE) */
+typedef struct sb_flat sb_flat;   /* FlatRTree of the spatial join build side */
+
+SB_API const char *sb_last_error(void);
+SB_API const char *sb_version(void);
+
+/* One context per calling thread / GPU: owns a stream and a scratch arena. */
+SB_API int sb_context_create(int device, sb_context **out);
+SB_API void sb_context_destroy(sb_context *ctx);
+/* adopt an external stream (e.g. torch.cuda.current_stream().cuda_stream); NULL restores the private stream */
+SB_API int sb_context_set_stream(sb_context *ctx, void *cuda_stream);
+SB_API int sb_context_sync(sb_context *ctx);
+/* number of kernels this context has launched so far (bench.py's gpu_launches) */
+SB_API uint64_t sb_context_launches(const sb_context *ctx);
+/* milliseconds the dominant kernel class spent on the GPU since the last reset, measured with CUDA events on
+ * the context's stream (profiling must be enabled; adds two event records per tagged launch) */
+SB_API int sb_context_profile(sb_context *ctx, int enable);
+SB_API int sb_context_profile_read(sb_context *ctx, const char *tag, double *ms, uint64_t *launches);
+
+/* ---- K1: bounding boxes --------------------------------------------------------------------------------
+ * POINT_2D columns (x[], y[]) -> BOX_2DF rounded outward.
+ * replaces: geometry_t::TryGetCachedBounds point branch, src/spatial/geometry/geometry_type.hpp:126-145 +
+ * MathUtil::DoubleToFloatDown/Up, src/spatial/util/math.hpp:19-47 */
+SB_API int sb_bbox_from_points(sb_context *ctx, sb_mem mem, const double *x, const double *y, uint64_t n,
+                               float *out_box4);
+/* BOX_2D columns -> BOX_2DF rounded outward (same rounding, Serde bbox write geometry_serialization.cpp:226-230) */
+SB_API int sb_bbox_from_box2d(sb_context *ctx, sb_mem mem, const double *min_x, const double *min_y,
+                              const double *max_x, const double *max_y, uint64_t n, float *out_box4);
+/* ST_Extent_Approx(GEOMETRY): replaces ST_Extent_Approx::Execute, spatial_functions_scalar.cpp:2684-2724
+ * (TryGetCachedBounds per row). valid[i]=0 -> SQL NULL. row_status may be NULL. */
+SB_API int sb_bbox_from_blobs(sb_context *ctx, sb_mem mem, const uint8_t *data, const uint64_t *offsets, uint64_t n,
+                              float *out_box4, uint8_t *out_valid, int32_t *row_status);
+/* ST_Extent(GEOMETRY): replaces ST_Extent::Execute, spatial_functions_scalar.cpp:2527-2571 =
+ * Serde::Deserialize (geometry_serialization.cpp:290-329) + sgl::ops::try_get_extent_xy (sgl.hpp:1408-1486) */
+SB_API int sb_extent_from_blobs(sb_context *ctx, sb_mem mem, const uint8_t *data, const uint64_t *offsets, uint64_t n,
+                                double *out_box4, uint8_t *out_valid, int32_t *row_status);
+
+/* ---- K2: Hilbert keys (ST_Hilbert, spatial_functions_scalar.cpp:5210-5396) -------------------------------- */
+/* ST_Hilbert(x DOUBLE, y DOUBLE, bounds BOX_2D): ExecuteLonlat :5250-5268. bounds = 4 doubles (host memory). */
+SB_API int sb_hilbert_xy(sb_context *ctx, sb_mem mem, const double *x, const double *y, uint64_t n,
+                         const double *bounds4, uint32_t *out);
+/* ST_Hilbert(box BOX_2D, bounds BOX_2D): ExecuteBox<double> :5216-5245. box4 = n x 4 doubles (AoS) */
+SB_API int sb_hilbert_box2d(sb_context *ctx, sb_mem mem, const double *box4, uint64_t n, const double *bounds4,
+                            uint32_t *out);
+/* ST_Hilbert(box BOX_2DF, bounds BOX_2DF): ExecuteBox<float> */
+SB_API int sb_hilbert_box2df(sb_context *ctx, sb_mem mem, const float *box4, uint64_t n, const float *bounds4,
+                             uint32_t *out);
+/* ST_Hilbert(geom GEOMETRY): ExecuteGeometry :5273-5293 (cached float box centre, f32->u32 order map) */
+SB_API int sb_hilbert_geom(sb_context *ctx, sb_mem mem, const uint8_t *data, const uint64_t *offsets, uint64_t n,
+                           uint32_t *out, uint8_t *out_valid);
+/* ST_Hilbert(geom GEOMETRY, bounds BOX_2D): ExecuteGeometryWithBounds :5295-5325. Returns SB_ERR_EMPTY when a
+ * row is empty (the reference throws); row_status marks the rows. */
+SB_API int sb_hilbert_geom_bounds(sb_context *ctx, sb_mem mem, const uint8_t *data, const uint64_t *offsets,
+                                  uint64_t n, const double *bounds4, uint32_t *out, int32_t *row_status);
+
+/* ---- K3: radix sort (stable, LSD onesweep) -------------------------------------------------------------
+ * replaces: DuckDB PhysicalOrder planned at rtree_index_create_logical.cpp:101-133 and FlatRTree::Sort,
+ * spatial_join_physical.cpp:131-163. Sorts (key, value) pairs in place; ties keep input order. */
+SB_API int sb_sort_pairs_u32(sb_context *ctx, sb_mem mem, uint32_t *keys, uint32_t *values, uint64_t n);
+SB_API int sb_sort_pairs_u64(sb_context *ctx, sb_mem mem, uint64_t *keys, uint32_t *values, uint64_t n);
+
+/* ---- K4a: persistent RTREE, STR bulk load ---------------------------------------------------------------
+ * replaces: ORDER BY x-centre (rtree_index_create_logical.cpp:101-133, key = ST_Centroid::ExecuteBox<float>
+ * spatial_functions_scalar.cpp:1490-1494), PhysicalCreateRTreeIndex::Sink/Finalize and BuildRTreeBottomUp,
+ * src/spatial/index/rtree/rtree_index_create_physical.cpp:95-131, 136-256, 334-363.
+ * Input rows must already be filtered to non-NULL, non-empty geometries (valid bbox), as the reference's plan
+ * does (rtree_index_create_logical.cpp:42-72). max_node_capacity in [4, 255] (rtree_index.cpp:30-63). */
+SB_API int sb_rtree_build_str(sb_context *ctx, sb_mem mem, const float *box4, const int64_t *row_ids, uint64_t n,
+                              uint32_t max_node_capacity, sb_rtree **out);
+SB_API void sb_rtree_destroy(sb_rtree *tree);
+/* level 0 = leaf entries (row ids); the last level has one entry = the root entry. */
+SB_API int sb_rtree_num_levels(const sb_rtree *tree);
+SB_API uint64_t sb_rtree_level_count(const sb_rtree *tree, int level);
+SB_API uint64_t sb_rtree_slice_size(const sb_rtree *tree);
+/* Copies one level out as 24-byte RTreeEntry records {u64 pointer, float min_x, min_y, max_x, max_y}
+ * (rtree_node.hpp:66-75). Node j of the level = entries [j*cap, min((j+1)*cap, count)); the host glue copies each
+ * run into a FixedSizeAllocator page (rtree.cpp:28-35) and rewrites `pointer` of upper levels
+ * ((type<<56) | child node index, type LEAF_PAGE=1 / BRANCH_PAGE=2) into IndexPointers. Leaf-level pointers are
+ * row ids with type ROW_ID=0 (rtree.cpp:37-42). */
+SB_API int sb_rtree_export_level(sb_context *ctx, const sb_rtree *tree, int level, sb_mem mem, void *out_entries);
+/* Batched index scan: replaces RTreeIndex::InitializeScan/Scan (rtree_index.cpp:106-139, rtree_scanner.hpp:38-83)
+ * for nq query boxes at once. Emits (query index, row id) for every leaf entry whose float box intersects the
+ * query box (closed intervals, bbox.hpp:27-29). Order: grouped by nothing in particular (sort to compare).
+ * capacity = number of result slots; *count = results found; SB_ERR_CAPACITY when count > capacity. */
+SB_API int sb_rtree_scan(sb_context *ctx, const sb_rtree *tree, sb_mem mem, const float *query_box4, uint32_t nq,
+                         uint32_t *out_query, int64_t *out_row_id, uint64_t capacity, uint64_t *count);
+
+/* ---- K4b: FlatRTree (join build side) -------------------------------------------------------------------
+ * replaces FlatRTree ctor/Push/Sort/Build, src/spatial/operators/spatial_join_physical.cpp:76-220 (Hilbert key
+ * in fp32 :173-187, sort, bottom-up pack of node_size). Tie order of equal Hilbert keys = insertion order.
+ * The packed tree lives in ONE device buffer (header | boxes | idx) so it can be broadcast to other GPUs. */
+SB_API int sb_flat_build(sb_context *ctx, sb_mem mem, const float *box4, uint32_t n, uint32_t node_size,
+                         sb_flat **out);
+SB_API void sb_flat_destroy(sb_flat *tree);
+SB_API uint32_t sb_flat_item_count(const sb_flat *tree);
+SB_API uint32_t sb_flat_node_count(const sb_flat *tree);
+SB_API uint32_t sb_flat_num_layers(const sb_flat *tree);
+/* layer_bounds (host copy, num_layers entries), spatial_join_physical.cpp:86-96 */
+SB_API const uint32_t *sb_flat_layer_bounds(const sb_flat *tree);
+/* device buffer holding the whole tree + its size, for NCCL broadcast */
+SB_API int sb_flat_device_buffer(const sb_flat *tree, void **dev_ptr, uint64_t *bytes);
+/* build a tree view over a (received) device buffer produced by sb_flat_device_buffer on another GPU. The
+ * buffer stays owned by the caller and must outlive the tree. */
+SB_API int sb_flat_attach(sb_context *ctx, void *dev_ptr, uint64_t bytes, sb_flat **out);
+/* copy box_array / idx_array out (node_count entries each) */
+SB_API int sb_flat_export(sb_context *ctx, const sb_flat *tree, sb_mem mem, float *out_box4, uint32_t *out_idx);
+
+/* ---- K5: batched probe ----------------------------------------------------------------------------------
+ * replaces FlatRTree::InitScan/Scan/Lookup (:230-302) driven per probe row by
+ * PhysicalSpatialJoin::ExecuteInternal (:748-849). Emits candidate pairs (probe index, build insertion index)
+ * for every leaf box intersecting the probe box. */
+SB_API int sb_flat_probe(sb_context *ctx, const sb_flat *tree, sb_mem mem, const float *probe_box4, uint64_t m,
+                         uint32_t *out_probe, uint32_t *out_build, uint64_t capacity, uint64_t *count);
+
+/* ---- K6: refinement -------------------------------------------------------------------------------------
+ * Predicates over candidate pairs; survivors are compacted in place (pairs arrays) and *count updated. */
+typedef enum {
+	SB_PRED_INTERSECTS = 0, /* ST_Intersects(point, envelope polygon): closed, GEOS semantics geos_module.cpp:1128-1153 */
+	SB_PRED_WITHIN = 1      /* ST_Within(point, envelope polygon) / ST_Contains(envelope, point): strict, :386-415,1885-1908 */
+} sb_predicate;
+
+SB_API int sb_refine_point_box(sb_context *ctx, sb_mem mem, sb_predicate pred, const double *px, const double *py,
+                               const double *bmin_x, const double *bmin_y, const double *bmax_x, const double *bmax_y,
+                               uint32_t *pair_probe, uint32_t *pair_build, uint64_t *count);
+/* ST_Within(POINT_2D, POLYGON_2D): winding number with the reference's operation order,
+ * ST_Contains::Operation spatial_functions_scalar.cpp:1938-2051 (reached via ST_Within :7775-7781).
+ * Polygons in DuckDB list layout: polygon p = rings [poly_ring_off[p], poly_ring_off[p+1]),
+ * ring r = vertices [ring_vert_off[r], ring_vert_off[r+1]) of vx[], vy[]. */
+SB_API int sb_refine_point_polygon(sb_context *ctx, sb_mem mem, const double *px, const double *py, const double *vx,
+                                   const double *vy, const uint64_t *ring_vert_off, const uint64_t *poly_ring_off,
+                                   uint64_t n_polys, uint64_t n_rings, uint64_t n_verts, uint64_t n_points,
+                                   uint32_t *pair_probe, uint32_t *pair_build, uint64_t *count);
+/* ST_Distance(POINT_2D, POINT_2D) (:2189-2214) for each pair, and ST_DWithin filtering (dist <= r). out_dist may
+ * be NULL. Survivors compacted in place. */
+SB_API int sb_refine_dwithin(sb_context *ctx, sb_mem mem, const double *ax, const double *ay, const double *bx,
+                             const double *by, double radius, uint32_t *pair_a, uint32_t *pair_b, double *out_dist,
+                             uint64_t *count);
+/* elementwise ST_Distance(POINT_2D, POINT_2D) */
+SB_API int sb_distance_points(sb_context *ctx, sb_mem mem, const double *ax, const double *ay, const double *bx,
+                              const double *by, uint64_t n, double *out);
+
+/* ---- whole join (the call PhysicalSpatialJoin::Finalize + ExecuteInternal would make) ----------------------
+ * Points (probe side, LHS) x boxes (build side, RHS, given as BOX_2D columns of the envelope polygons):
+ * bbox -> FlatRTree build -> probe -> exact refinement, pairs out. */
+SB_API int sb_join_points_boxes(sb_context *ctx, sb_mem mem, sb_predicate pred, const double *px, const double *py,
+                                uint64_t n_points, const double *bmin_x, const double *bmin_y, const double *bmax_x,
+                                const double *bmax_y, uint32_t n_boxes, uint32_t *out_probe, uint32_t *out_build,
+                                uint64_t capacity, uint64_t *count);
+/* probe an existing tree with points and refine in the same kernel (multi-GPU path: tree was broadcast).
+ * point indices emitted = probe_index_base + local index. */
+SB_API int sb_flat_probe_points(sb_context *ctx, const sb_flat *tree, sb_mem mem, sb_predicate pred, const double *px,
+                                const double *py, uint64_t n_points, uint32_t probe_index_base, const double *bbox2d4,
+                                uint32_t *out_probe, uint32_t *out_build, uint64_t capacity, uint64_t *count);
+/* radius join (new capability behind the same operator): all (a, b) with distance <= radius.
+ * Builds a FlatRTree over b's points expanded by radius, probes with a, refines with ST_Distance. */
+SB_API int sb_join_dwithin(sb_context *ctx, sb_mem mem, const double *ax, const double *ay, uint64_t na,
+                           const double *bx, const double *by, uint32_t nb, double radius, uint32_t *out_a,
+                           uint32_t *out_b, double *out_dist, uint64_t capacity, uint64_t *count);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
