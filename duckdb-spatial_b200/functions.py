@@ -1,0 +1,397 @@
+"""Host-side mirror of the reference's function / index / operator surface for the hot path, over the C-ABI.
+
+Names follow the reference (ST_Extent_Approx, ST_Extent, ST_Hilbert, RTreeIndex, FlatRTree, SpatialJoin).
+Inputs may be numpy arrays (host memory: the C-ABI stages them through HBM, SB_HOST) or torch CUDA tensors
+(device memory, SB_DEVICE, zero-copy). Outputs come back in the same kind of container.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import capi
+
+ENTRY_DTYPE = np.dtype([("ptr", np.uint64), ("box", np.float32, 4)])  # RTreeEntry, rtree_node.hpp:66-75
+
+
+def _is_torch(a):
+    return a is not None and type(a).__module__.split(".")[0] == "torch"
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if _is_torch(a):
+        assert a.is_contiguous()
+        return a.data_ptr()
+    assert a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data
+
+
+class Context:
+    """One per GPU / calling thread (sb_context): owns a stream and a scratch arena."""
+
+    def __init__(self, device=0):
+        self.L = capi.lib()
+        h = C.c_void_p()
+        capi.check(self.L.sb_context_create(device, C.byref(h)))
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.sb_context_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- plumbing ------------------------------------------------------------------------------------------
+    def use_torch_stream(self):
+        import torch
+
+        capi.check(self.L.sb_context_set_stream(self.h, torch.cuda.current_stream().cuda_stream))
+
+    def use_private_stream(self):
+        capi.check(self.L.sb_context_set_stream(self.h, None))
+
+    def sync(self):
+        capi.check(self.L.sb_context_sync(self.h))
+
+    @property
+    def launches(self):
+        return self.L.sb_context_launches(self.h)
+
+    def profile(self, enable=True):
+        capi.check(self.L.sb_context_profile(self.h, 1 if enable else 0))
+
+    def profile_read(self, tag):
+        ms, n = C.c_double(0), C.c_uint64(0)
+        capi.check(self.L.sb_context_profile_read(self.h, tag.encode(), C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    def _mem(self, *arrays):
+        kinds = {_is_torch(a) for a in arrays if a is not None}
+        assert len(kinds) == 1, "all arrays of one call must be numpy (host) or torch CUDA (device)"
+        return capi.DEVICE if kinds.pop() else capi.HOST
+
+    def _empty(self, like, shape, dtype):
+        if _is_torch(like):
+            import torch
+
+            tdt = {np.float32: torch.float32, np.float64: torch.float64, np.uint32: torch.int32, np.uint8: torch.uint8,
+                   np.int32: torch.int32, np.int64: torch.int64, np.uint64: torch.int64}[dtype]
+            return torch.empty(shape, dtype=tdt, device=like.device)
+        return np.empty(shape, dtype)
+
+    @staticmethod
+    def _f64(a):
+        return a if _is_torch(a) else np.ascontiguousarray(a, np.float64)
+
+    # -- K1 ------------------------------------------------------------------------------------------------
+    def bbox_from_points(self, x, y):
+        """POINT_2D -> BOX_2DF (TryGetCachedBounds point branch)."""
+        x, y = self._f64(x), self._f64(y)
+        out = self._empty(x, (len(x), 4), np.float32)
+        capi.check(self.L.sb_bbox_from_points(self.h, self._mem(x, y), _ptr(x), _ptr(y), len(x), _ptr(out)))
+        return out
+
+    def bbox_from_box2d(self, minx, miny, maxx, maxy):
+        a = [self._f64(v) for v in (minx, miny, maxx, maxy)]
+        out = self._empty(a[0], (len(a[0]), 4), np.float32)
+        capi.check(self.L.sb_bbox_from_box2d(self.h, self._mem(*a), *[_ptr(v) for v in a], len(a[0]), _ptr(out)))
+        return out
+
+    def st_extent_approx(self, data, offsets, want_status=False):
+        """ST_Extent_Approx(GEOMETRY) -> (BOX_2DF [n,4], valid [n])"""
+        n = len(offsets) - 1
+        box = self._empty(data, (n, 4), np.float32)
+        valid = self._empty(data, (n,), np.uint8)
+        status = self._empty(data, (n,), np.int32)
+        rc = self.L.sb_bbox_from_blobs(self.h, self._mem(data, offsets), _ptr(data), _ptr(offsets), n, _ptr(box),
+                                       _ptr(valid), _ptr(status))
+        if want_status:
+            return box, valid, status, rc
+        capi.check(rc)
+        return box, valid
+
+    def st_extent(self, data, offsets, want_status=False):
+        """ST_Extent(GEOMETRY) -> (BOX_2D [n,4], valid [n])"""
+        n = len(offsets) - 1
+        box = self._empty(data, (n, 4), np.float64)
+        valid = self._empty(data, (n,), np.uint8)
+        status = self._empty(data, (n,), np.int32)
+        rc = self.L.sb_extent_from_blobs(self.h, self._mem(data, offsets), _ptr(data), _ptr(offsets), n, _ptr(box),
+                                         _ptr(valid), _ptr(status))
+        if want_status:
+            return box, valid, status, rc
+        capi.check(rc)
+        return box, valid
+
+    # -- K2 ------------------------------------------------------------------------------------------------
+    def st_hilbert_xy(self, x, y, bounds):
+        x, y = self._f64(x), self._f64(y)
+        b = np.ascontiguousarray(bounds, np.float64)
+        out = self._empty(x, (len(x),), np.uint32)
+        capi.check(self.L.sb_hilbert_xy(self.h, self._mem(x, y), _ptr(x), _ptr(y), len(x), _ptr(b), _ptr(out)))
+        return out
+
+    def st_hilbert_box2d(self, box4, bounds):
+        box4 = box4 if _is_torch(box4) else np.ascontiguousarray(box4, np.float64)
+        b = np.ascontiguousarray(bounds, np.float64)
+        out = self._empty(box4, (len(box4),), np.uint32)
+        capi.check(self.L.sb_hilbert_box2d(self.h, self._mem(box4), _ptr(box4), len(box4), _ptr(b), _ptr(out)))
+        return out
+
+    def st_hilbert_box2df(self, box4, bounds):
+        box4 = box4 if _is_torch(box4) else np.ascontiguousarray(box4, np.float32)
+        b = np.ascontiguousarray(bounds, np.float32)
+        out = self._empty(box4, (len(box4),), np.uint32)
+        capi.check(self.L.sb_hilbert_box2df(self.h, self._mem(box4), _ptr(box4), len(box4), _ptr(b), _ptr(out)))
+        return out
+
+    def st_hilbert_geom(self, data, offsets):
+        n = len(offsets) - 1
+        out = self._empty(data, (n,), np.uint32)
+        valid = self._empty(data, (n,), np.uint8)
+        capi.check(self.L.sb_hilbert_geom(self.h, self._mem(data, offsets), _ptr(data), _ptr(offsets), n, _ptr(out),
+                                          _ptr(valid)))
+        return out, valid
+
+    def st_hilbert_geom_bounds(self, data, offsets, bounds, want_status=False):
+        n = len(offsets) - 1
+        b = np.ascontiguousarray(bounds, np.float64)
+        out = self._empty(data, (n,), np.uint32)
+        status = self._empty(data, (n,), np.int32)
+        rc = self.L.sb_hilbert_geom_bounds(self.h, self._mem(data, offsets), _ptr(data), _ptr(offsets), n, _ptr(b),
+                                           _ptr(out), _ptr(status))
+        if want_status:
+            return out, status, rc
+        capi.check(rc)
+        return out
+
+    # -- K3 ------------------------------------------------------------------------------------------------
+    def sort_pairs(self, keys, values):
+        """in-place stable sort of (keys, values); keys uint32 or uint64 (torch: int32 / int64 bit patterns)."""
+        itemsize = keys.element_size() if _is_torch(keys) else keys.dtype.itemsize
+        fn = self.L.sb_sort_pairs_u32 if itemsize == 4 else self.L.sb_sort_pairs_u64
+        capi.check(fn(self.h, self._mem(keys, values), _ptr(keys), _ptr(values), len(keys)))
+        return keys, values
+
+    # -- K6 ------------------------------------------------------------------------------------------------
+    def st_distance_points(self, ax, ay, bx, by):
+        a = [self._f64(v) for v in (ax, ay, bx, by)]
+        out = self._empty(a[0], (len(a[0]),), np.float64)
+        capi.check(self.L.sb_distance_points(self.h, self._mem(*a), *[_ptr(v) for v in a], len(a[0]), _ptr(out)))
+        return out
+
+    def st_within_point_polygon(self, px, py, vx, vy, ring_off, poly_off, pair_point, pair_poly):
+        """ST_Within(POINT_2D, POLYGON_2D) over candidate pairs -> surviving (point, polygon) pairs."""
+        px, py, vx, vy = [self._f64(v) for v in (px, py, vx, vy)]
+        cnt = C.c_uint64(len(pair_point))
+        pp = pair_point.clone() if _is_torch(pair_point) else np.ascontiguousarray(pair_point, np.uint32).copy()
+        pb = pair_poly.clone() if _is_torch(pair_poly) else np.ascontiguousarray(pair_poly, np.uint32).copy()
+        capi.check(self.L.sb_refine_point_polygon(
+            self.h, self._mem(px, py, vx, vy, ring_off, poly_off, pp, pb), _ptr(px), _ptr(py), _ptr(vx), _ptr(vy),
+            _ptr(ring_off), _ptr(poly_off), len(poly_off) - 1, len(ring_off) - 1, len(vx), len(px), _ptr(pp), _ptr(pb),
+            C.byref(cnt)))
+        return pp[: cnt.value], pb[: cnt.value]
+
+    # -- whole joins ---------------------------------------------------------------------------------------
+    def spatial_join_points_boxes(self, px, py, bminx, bminy, bmaxx, bmaxy, predicate="intersects", capacity=None):
+        """PhysicalSpatialJoin for POINT probe side x envelope-polygon build side. Returns pairs [k,2] uint32
+        (probe row, build row), unordered."""
+        px, py = self._f64(px), self._f64(py)
+        b = [self._f64(v) for v in (bminx, bminy, bmaxx, bmaxy)]
+        pred = capi.PRED_INTERSECTS if predicate == "intersects" else capi.PRED_WITHIN
+        cap = int(capacity if capacity is not None else max(1024, 2 * len(px)))
+        while True:
+            op = self._empty(px, (cap,), np.uint32)
+            ob = self._empty(px, (cap,), np.uint32)
+            cnt = C.c_uint64(0)
+            rc = self.L.sb_join_points_boxes(self.h, self._mem(px, py, *b), pred, _ptr(px), _ptr(py), len(px),
+                                             *[_ptr(v) for v in b], len(b[0]), _ptr(op), _ptr(ob), cap, C.byref(cnt))
+            if rc == capi.ERR_CAPACITY:
+                cap = int(cnt.value)
+                continue
+            capi.check(rc)
+            return op[: cnt.value], ob[: cnt.value]
+
+    def join_dwithin(self, ax, ay, bx, by, radius, capacity=None):
+        ax, ay, bx, by = [self._f64(v) for v in (ax, ay, bx, by)]
+        cap = int(capacity if capacity is not None else max(1024, 4 * len(ax)))
+        while True:
+            oa = self._empty(ax, (cap,), np.uint32)
+            ob = self._empty(ax, (cap,), np.uint32)
+            od = self._empty(ax, (cap,), np.float64)
+            cnt = C.c_uint64(0)
+            rc = self.L.sb_join_dwithin(self.h, self._mem(ax, ay, bx, by), _ptr(ax), _ptr(ay), len(ax), _ptr(bx),
+                                        _ptr(by), len(bx), float(radius), _ptr(oa), _ptr(ob), _ptr(od), cap,
+                                        C.byref(cnt))
+            if rc == capi.ERR_CAPACITY:
+                cap = int(cnt.value)
+                continue
+            capi.check(rc)
+            return oa[: cnt.value], ob[: cnt.value], od[: cnt.value]
+
+
+class RTreeIndex:
+    """CREATE INDEX ... USING RTREE: STR bulk load on the GPU + batched index scans (sb_rtree)."""
+
+    def __init__(self, ctx, box4, row_ids, max_node_capacity=128):
+        self.ctx = ctx
+        if not _is_torch(box4):
+            box4 = np.ascontiguousarray(box4, np.float32)
+            row_ids = np.ascontiguousarray(row_ids, np.int64)
+        h = C.c_void_p()
+        capi.check(ctx.L.sb_rtree_build_str(ctx.h, ctx._mem(box4, row_ids), _ptr(box4), _ptr(row_ids), len(row_ids),
+                                            max_node_capacity, C.byref(h)))
+        self.h = h
+        self.cap = max_node_capacity
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.ctx.L.sb_rtree_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def nlevels(self):
+        return self.ctx.L.sb_rtree_num_levels(self.h)
+
+    @property
+    def slice(self):
+        return self.ctx.L.sb_rtree_slice_size(self.h)
+
+    def level_counts(self):
+        return [self.ctx.L.sb_rtree_level_count(self.h, l) for l in range(self.nlevels)]
+
+    def level(self, l):
+        """level l as a numpy structured array of 24-byte RTreeEntry records (host copy)."""
+        n = self.ctx.L.sb_rtree_level_count(self.h, l)
+        out = np.empty(n, ENTRY_DTYPE)
+        capi.check(self.ctx.L.sb_rtree_export_level(self.ctx.h, self.h, l, capi.HOST, _ptr(out)))
+        return out
+
+    def scan(self, query_box4, capacity=None):
+        """batched RTreeIndex scan -> (query index [k], row id [k]); per query in the reference's DFS order."""
+        q = query_box4 if _is_torch(query_box4) else np.ascontiguousarray(query_box4, np.float32).reshape(-1, 4)
+        cap = int(capacity if capacity is not None else 1 << 16)
+        while True:
+            oq = self.ctx._empty(q, (cap,), np.uint32)
+            orow = self.ctx._empty(q, (cap,), np.int64)
+            cnt = C.c_uint64(0)
+            rc = self.ctx.L.sb_rtree_scan(self.ctx.h, self.h, self.ctx._mem(q), _ptr(q), len(q), _ptr(oq), _ptr(orow),
+                                          cap, C.byref(cnt))
+            if rc == capi.ERR_CAPACITY:
+                cap = int(cnt.value)
+                continue
+            capi.check(rc)
+            return oq[: cnt.value], orow[: cnt.value]
+
+
+class FlatRTree:
+    """The join build side (FlatRTree, node size 32): Hilbert sort + bottom-up pack on the GPU."""
+
+    def __init__(self, ctx, box4=None, node_size=32, _handle=None, _keepalive=None):
+        self.ctx = ctx
+        self._keepalive = _keepalive
+        if _handle is not None:
+            self.h = _handle
+            return
+        if not _is_torch(box4):
+            box4 = np.ascontiguousarray(box4, np.float32)
+        h = C.c_void_p()
+        capi.check(ctx.L.sb_flat_build(ctx.h, ctx._mem(box4), _ptr(box4), len(box4), node_size, C.byref(h)))
+        self.h = h
+
+    @classmethod
+    def attach(cls, ctx, device_tensor):
+        """view over a tree buffer received from another GPU (torch uint8 CUDA tensor)."""
+        h = C.c_void_p()
+        capi.check(ctx.L.sb_flat_attach(ctx.h, device_tensor.data_ptr(), device_tensor.numel(), C.byref(h)))
+        return cls(ctx, _handle=h, _keepalive=device_tensor)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.ctx.L.sb_flat_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def item_count(self):
+        return self.ctx.L.sb_flat_item_count(self.h)
+
+    @property
+    def nodes(self):
+        return self.ctx.L.sb_flat_node_count(self.h)
+
+    @property
+    def layer_bounds(self):
+        n = self.ctx.L.sb_flat_num_layers(self.h)
+        p = self.ctx.L.sb_flat_layer_bounds(self.h)
+        return np.array([p[i] for i in range(n)], np.uint32)
+
+    def device_buffer(self):
+        """(device pointer, bytes) of the packed tree, for NCCL broadcast."""
+        p, b = C.c_void_p(), C.c_uint64()
+        capi.check(self.ctx.L.sb_flat_device_buffer(self.h, C.byref(p), C.byref(b)))
+        return p.value, b.value
+
+    def export(self):
+        n = self.nodes
+        box = np.empty((n, 4), np.float32)
+        idx = np.empty(n, np.uint32)
+        capi.check(self.ctx.L.sb_flat_export(self.ctx.h, self.h, capi.HOST, _ptr(box), _ptr(idx)))
+        return box, idx
+
+    def probe(self, probe_box4, capacity=None):
+        """candidate pairs (probe index, build index) for float probe boxes."""
+        q = probe_box4 if _is_torch(probe_box4) else np.ascontiguousarray(probe_box4, np.float32).reshape(-1, 4)
+        cap = int(capacity if capacity is not None else max(1024, 2 * len(q)))
+        while True:
+            op = self.ctx._empty(q, (cap,), np.uint32)
+            ob = self.ctx._empty(q, (cap,), np.uint32)
+            cnt = C.c_uint64(0)
+            rc = self.ctx.L.sb_flat_probe(self.ctx.h, self.h, self.ctx._mem(q), _ptr(q), len(q), _ptr(op), _ptr(ob),
+                                          cap, C.byref(cnt))
+            if rc == capi.ERR_CAPACITY:
+                cap = int(cnt.value)
+                continue
+            capi.check(rc)
+            return op[: cnt.value], ob[: cnt.value]
+
+    def probe_points(self, px, py, build_box2d4=None, predicate="intersects", index_base=0, capacity=None, out=None):
+        """probe with points; with build_box2d4 ([n,4] float64 AoS) the exact predicate is fused into the kernel."""
+        px, py = self.ctx._f64(px), self.ctx._f64(py)
+        pred = capi.PRED_INTERSECTS if predicate == "intersects" else capi.PRED_WITHIN
+        cap = int(capacity if capacity is not None else max(1024, 2 * len(px)))
+        while True:
+            if out is not None:
+                op, ob = out
+                cap = len(op)
+            else:
+                op = self.ctx._empty(px, (cap,), np.uint32)
+                ob = self.ctx._empty(px, (cap,), np.uint32)
+            cnt = C.c_uint64(0)
+            arrays = (px, py) if build_box2d4 is None else (px, py, build_box2d4)
+            rc = self.ctx.L.sb_flat_probe_points(self.ctx.h, self.h, self.ctx._mem(*arrays), pred, _ptr(px), _ptr(py),
+                                                 len(px), index_base, _ptr(build_box2d4), _ptr(op), _ptr(ob), cap,
+                                                 C.byref(cnt))
+            if rc == capi.ERR_CAPACITY and out is None:
+                cap = int(cnt.value)
+                continue
+            capi.check(rc)
+            return op[: cnt.value], ob[: cnt.value]
