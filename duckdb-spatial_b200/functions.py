@@ -90,6 +90,20 @@ class Context:
     def _f64(a):
         return a if _is_torch(a) else np.ascontiguousarray(a, np.float64)
 
+    # -- harness: ST_GeneratePoints ------------------------------------------------------------------------
+    def st_generate_points(self, seed, n, bounds=(0.0, 0.0, 10000.0, 10000.0), skip=0, device=False):
+        """points [skip, skip+n) of ST_GeneratePoints(bounds, *, seed): numpy arrays, or torch CUDA tensors."""
+        b = np.ascontiguousarray(bounds, np.float64)
+        if device:
+            import torch
+
+            x = torch.empty(n, dtype=torch.float64, device="cuda:%d" % self.device)
+            y = torch.empty_like(x)
+        else:
+            x, y = np.empty(n, np.float64), np.empty(n, np.float64)
+        capi.check(self.L.sb_generate_points(self.h, self._mem(x, y), seed, skip, n, _ptr(b), _ptr(x), _ptr(y)))
+        return x, y
+
     # -- K1 ------------------------------------------------------------------------------------------------
     def bbox_from_points(self, x, y):
         """POINT_2D -> BOX_2DF (TryGetCachedBounds point branch)."""

@@ -205,6 +205,12 @@ SB_API int sb_join_dwithin(sb_context *ctx, sb_mem mem, const double *ax, const 
                            const double *bx, const double *by, uint32_t nb, double radius, uint32_t *out_a,
                            uint32_t *out_b, double *out_dist, uint64_t capacity, uint64_t *count);
 
+/* ---- harness utility: ST_GeneratePoints on the device ---------------------------------------------------------
+ * restates ST_GeneratePoints (spatial_functions_table.cpp:82-99) on DuckDB's pcg32 RandomEngine with skip-ahead:
+ * produces points [skip, skip+n) of the sequential stream of `seed`, bit-identical to the CPU generator. */
+SB_API int sb_generate_points(sb_context *ctx, sb_mem mem, uint64_t seed, uint64_t skip, uint64_t n,
+                              const double *bounds4, double *x, double *y);
+
 #ifdef __cplusplus
 }
 #endif

@@ -403,3 +403,14 @@ def test_dwithin_join_and_distance(ctx, O):
     d = ctx.st_distance_points(ax[:2000], ay[:2000], bx[:2000], by[:2000])
     od = np.array([O.lib().orc_distance_pp(*map(float, t)) for t in zip(ax[:2000], ay[:2000], bx[:2000], by[:2000])])
     assert (np.abs(d - od) <= 1e-12 * np.maximum(od, 1e-300)).all()
+
+
+def test_generate_points_bit_exact(ctx, O):
+    # golden: row 50000 of the seed-1337 stream (rtree_block_reclaim.test_slow:24-27) + the whole stream vs oracle
+    x, y = ctx.st_generate_points(1337, 100003)
+    assert x[49999] == 4732.4060765095055 and y[49999] == 128.3674407750368
+    ox, oy = O.generate_points(1337, 100003)
+    assert (x == ox).all() and (y == oy).all()
+    xs, ys = ctx.st_generate_points(42, 1000, (-10.0, 5.0, 300.0, 77.0), skip=123457)
+    ox, oy = O.generate_points(42, 1000, (-10.0, 5.0, 300.0, 77.0), skip=123457)
+    assert (xs == ox).all() and (ys == oy).all()
