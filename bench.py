@@ -309,9 +309,9 @@ def run_ours(a):
         for _ in range(max(a.warmup, 3)):
             pairs = step()
         clocks = Clocks(local)
-        if rank == 0:
+        if rank == 0 and not os.environ.get("SB_BENCH_NOCLOCKS"):
             clocks.start()
-        ctx.profile(True)
+        ctx.profile(not os.environ.get("SB_BENCH_NOPROF"))
         launches0 = ctx.launches
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

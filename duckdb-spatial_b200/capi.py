@@ -21,6 +21,7 @@ SIGNATURES = {
     "sb_context_destroy": (None, [vp]),
     "sb_context_set_stream": (i32, [vp, vp]),
     "sb_context_sync": (i32, [vp]),
+    "sb_context_set_option": (i32, [vp, C.c_char_p, C.c_int64]),
     "sb_context_launches": (u64, [vp]),
     "sb_context_profile": (i32, [vp, i32]),
     "sb_context_profile_read": (i32, [vp, C.c_char_p, C.POINTER(f64), C.POINTER(u64)]),

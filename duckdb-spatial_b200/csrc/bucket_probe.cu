@@ -1,0 +1,683 @@
+// bucket_probe.cu -- K5 v2: the bulk point-probe of the spatial join (points x FlatRTree), bucketed.
+//
+// Replaces the per-row loop of PhysicalSpatialJoin::ExecuteInternal (spatial_join_physical.cpp:748-849:
+// TryGetCachedBounds -> FlatRTree::InitScan/Scan per probe row -> exact predicate) for a whole probe column.
+// The candidate set of a probe row is fixed by the reference: every leaf entry whose float box intersects the
+// probe's float box (a leaf hit implies all its ancestors hit, because parent boxes are exact fmin/fmax unions).
+// v1 (flat_rtree.cu) walks the tree per probe and is instruction- and L2-bound (0.8 % of the HBM roofline:
+// profiles/README.md r1a). v2 makes the probes coherent first and then shares all per-node work between them:
+//
+//   1. a monotone 20-bit quantiser Q(v) = floor((v - tree_min) * 2^20 / tree_extent) per axis slices the tree box
+//      into 32x32 buckets (Q >> 15) of 32x32 sub-cells ((Q >> 10) & 31) with a 15-bit in-bucket coordinate
+//      (Q & 32767). Because Q is monotone, a <= x <= c implies Q(a) <= Q(x) <= Q(c): quantised comparisons are
+//      conservative, equality is the only ambiguous case, and it is resolved with the exact predicate.
+//   2. k_bp_hist / k_bp_scatter partition the probe points into the 1024 buckets (one pass over the points,
+//      16 B read + 20 B written per point). Points whose float box misses the tree box are dropped here
+//      (the root test of FlatRTree::Scan).
+//   3. k_bp_cand_* bin the leaf level of the packed tree (Hilbert order, 16 B boxes) into the same buckets.
+//   4. k_bp_probe: one CTA per (bucket, slice of its points): stages the bucket's leaf entries in shared memory
+//      as 8-byte quantised boxes, builds a 32x32 sub-cell directory (CSR) over them in shared memory, then every
+//      thread streams points: look up the sub-cell list (~18 entries for config C3 instead of ~200 box tests of a
+//      root-to-leaf walk), test with 4 integer instructions per entry, resolve quantisation ties with the exact
+//      fp64 (or float-box) predicate, and emit pairs through a shared-memory staging buffer so that the global
+//      writes are coalesced and the global pair counter sees one atomic per ~4000 pairs.
+//
+// Algorithmic DRAM bytes per probe: 16 (coordinates) + 8 per emitted pair; the partition adds 36 B of real
+// traffic per probe.
+#include "internal.cuh"
+
+#define BP_G 32                  // buckets per axis
+#define BP_NB (BP_G * BP_G)      // 1024 buckets (+1 for points with NaN coordinates)
+#define BP_QBITS 20              // quantiser bits per axis
+#define BP_QMAX ((1 << BP_QBITS) - 1)
+#define BP_SLICE 32768u          // points per work unit
+
+struct bp_grid {
+	double minx, miny, sx, sy; // Q(v) = clamp(floor((v - min) * s), 0, BP_QMAX)
+	float tb[4];               // tree box
+};
+
+__device__ __forceinline__ int bp_q(double v, double mn, double s) {
+	const int c = __double2int_rd((v - mn) * s); // saturating; NaN -> 0
+	return min(max(c, 0), BP_QMAX);
+}
+
+__global__ void k_bp_grid_init(const sb_flat_header *__restrict__ hdr, bp_grid *__restrict__ g) {
+	if (threadIdx.x == 0) {
+		const double x0 = hdr->tree_box[0], y0 = hdr->tree_box[1], x1 = hdr->tree_box[2], y1 = hdr->tree_box[3];
+		const double w = x1 - x0, h = y1 - y0;
+		g->minx = x0;
+		g->miny = y0;
+		g->sx = (w > 0 && w < 1.7e308) ? (double)(1 << BP_QBITS) / w : 0.0;
+		g->sy = (h > 0 && h < 1.7e308) ? (double)(1 << BP_QBITS) / h : 0.0;
+		g->tb[0] = hdr->tree_box[0], g->tb[1] = hdr->tree_box[1], g->tb[2] = hdr->tree_box[2], g->tb[3] = hdr->tree_box[3];
+	}
+}
+
+// bucket of a probe point: -1 = its float box misses the tree box (no candidates), BP_NB = NaN coordinate
+__device__ __forceinline__ int bp_bucket(double x, double y, const bp_grid &g) {
+	if (x != x || y != y) {
+		return BP_NB;
+	}
+	const float4 q = make_float4(sb_f64_to_f32_down(x), sb_f64_to_f32_down(y), sb_f64_to_f32_up(x), sb_f64_to_f32_up(y));
+	if (!sb_box_intersects(q, make_float4(g.tb[0], g.tb[1], g.tb[2], g.tb[3]))) {
+		return -1;
+	}
+	const int qx = bp_q(x, g.minx, g.sx), qy = bp_q(y, g.miny, g.sy);
+	return (qy >> 15) * BP_G + (qx >> 15);
+}
+
+// ---- 2. partition of the probe points ------------------------------------------------------------------------
+#define BPH_THREADS 512
+__global__ void __launch_bounds__(BPH_THREADS) k_bp_hist(const double *__restrict__ px, const double *__restrict__ py,
+                                                         uint64_t n, const bp_grid *__restrict__ gp,
+                                                         uint32_t *__restrict__ hist) {
+	__shared__ uint32_t s_hist[BP_NB + 1];
+	for (int i = threadIdx.x; i <= BP_NB; i += BPH_THREADS) {
+		s_hist[i] = 0;
+	}
+	const bp_grid g = *gp;
+	__syncthreads();
+	const uint64_t stride = (uint64_t)gridDim.x * BPH_THREADS;
+	for (uint64_t i = (uint64_t)blockIdx.x * BPH_THREADS + threadIdx.x; i < n; i += stride) {
+		const int b = bp_bucket(px[i], py[i], g);
+		if (b >= 0) {
+			atomicAdd(&s_hist[b], 1u);
+		}
+	}
+	__syncthreads();
+	for (int i = threadIdx.x; i <= BP_NB; i += BPH_THREADS) {
+		const uint32_t c = s_hist[i];
+		if (c) {
+			atomicAdd(&hist[i], c);
+		}
+	}
+}
+
+#define BPS_THREADS 1024
+#define BPS_ITEMS 8
+#define BPS_TILE (BPS_THREADS * BPS_ITEMS)
+__global__ void __launch_bounds__(BPS_THREADS)
+    k_bp_scatter(const double *__restrict__ px, const double *__restrict__ py, uint64_t n, uint32_t index_base,
+                 const bp_grid *__restrict__ gp, uint32_t *__restrict__ cursor, double2 *__restrict__ oxy,
+                 uint32_t *__restrict__ oidx) {
+	__shared__ uint32_t s_cnt[BP_NB + 1];
+	__shared__ uint32_t s_base[BP_NB + 1];
+	const bp_grid g = *gp;
+	const uint64_t tiles = (n + BPS_TILE - 1) / BPS_TILE;
+	for (uint64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+		for (int i = threadIdx.x; i <= BP_NB; i += BPS_THREADS) {
+			s_cnt[i] = 0;
+		}
+		__syncthreads();
+		double x[BPS_ITEMS], y[BPS_ITEMS];
+		int b[BPS_ITEMS];
+		uint32_t r[BPS_ITEMS];
+		const uint64_t base = tile * BPS_TILE + threadIdx.x;
+#pragma unroll
+		for (int k = 0; k < BPS_ITEMS; k++) {
+			const uint64_t i = base + (uint64_t)k * BPS_THREADS;
+			b[k] = -1;
+			if (i < n) {
+				x[k] = px[i];
+				y[k] = py[i];
+				b[k] = bp_bucket(x[k], y[k], g);
+			}
+		}
+#pragma unroll
+		for (int k = 0; k < BPS_ITEMS; k++) {
+			r[k] = b[k] >= 0 ? atomicAdd(&s_cnt[b[k]], 1u) : 0u;
+		}
+		__syncthreads();
+		for (int i = threadIdx.x; i <= BP_NB; i += BPS_THREADS) {
+			const uint32_t c = s_cnt[i];
+			if (c) {
+				s_base[i] = atomicAdd(&cursor[i], c);
+			}
+		}
+		__syncthreads();
+#pragma unroll
+		for (int k = 0; k < BPS_ITEMS; k++) {
+			if (b[k] >= 0) {
+				const uint32_t dst = s_base[b[k]] + r[k];
+				oxy[dst] = make_double2(x[k], y[k]);
+				oidx[dst] = (uint32_t)(base + (uint64_t)k * BPS_THREADS) + index_base;
+			}
+		}
+		__syncthreads();
+	}
+}
+
+// ---- 3. the tree's leaf level binned into the same buckets ----------------------------------------------------
+// Quantised extent of a leaf float box under the CANDIDATE semantics of the reference: a point x can produce a
+// float box [down(x), up(x)] that intersects [b.x, b.z] only if pred(b.x) < x < succ(b.z) (pred / succ = the
+// neighbouring floats), so [Q(pred(b.x)), Q(succ(b.z))] covers every such point. NaN bounds never exclude
+// (Box::Intersects, bbox.hpp:27-29, is written with negated comparisons) => open-ended.
+__device__ __forceinline__ void bp_leaf_range(const float4 b, const bp_grid &g, int &x0, int &y0, int &x1, int &y1) {
+	const float ax = nextafterf(b.x, -INFINITY), ay = nextafterf(b.y, -INFINITY);
+	const float cx = nextafterf(b.z, INFINITY), cy = nextafterf(b.w, INFINITY);
+	x0 = ax != ax ? 0 : bp_q((double)ax, g.minx, g.sx);
+	y0 = ay != ay ? 0 : bp_q((double)ay, g.miny, g.sy);
+	x1 = cx != cx ? BP_QMAX : bp_q((double)cx, g.minx, g.sx);
+	y1 = cy != cy ? BP_QMAX : bp_q((double)cy, g.miny, g.sy);
+}
+
+template <bool FILL>
+__global__ void __launch_bounds__(256) k_bp_cand(const float4 *__restrict__ boxes, uint32_t items,
+                                                 const bp_grid *__restrict__ gp, uint32_t *__restrict__ counter,
+                                                 uint32_t *__restrict__ cand_pos) {
+	const bp_grid g = *gp;
+	const uint32_t stride = gridDim.x * blockDim.x;
+	for (uint32_t pos = blockIdx.x * blockDim.x + threadIdx.x; pos < items; pos += stride) {
+		int x0, y0, x1, y1;
+		bp_leaf_range(boxes[pos], g, x0, y0, x1, y1);
+		for (int by = y0 >> 15; by <= (y1 >> 15); by++) {
+			for (int bx = x0 >> 15; bx <= (x1 >> 15); bx++) {
+				const uint32_t slot = atomicAdd(&counter[by * BP_G + bx], 1u);
+				if (FILL) {
+					cand_pos[slot] = pos;
+				}
+			}
+		}
+	}
+}
+
+// ---- offsets, cursors and the work-unit table -----------------------------------------------------------------
+struct bp_unit {
+	uint32_t bucket, pbeg, pend;
+};
+// tables: [0] pt_hist (1025) [1] pt_off (1026) [2] pt_cursor (1025) [3] cand_cnt (1024) [4] cand_off (1025)
+//         [5] cand_cursor (1024); totals: {points kept (no NaN), candidates, units, NaN points}
+struct bp_tables {
+	uint32_t pt_hist[BP_NB + 1];
+	uint32_t pt_off[BP_NB + 2];
+	uint32_t pt_cursor[BP_NB + 1];
+	uint32_t cand_cnt[BP_NB];
+	uint32_t cand_off[BP_NB + 1];
+	uint32_t cand_cursor[BP_NB];
+	uint32_t ticket;
+	uint32_t pad;
+	uint64_t totals[4];
+};
+
+__device__ __forceinline__ uint32_t bp_block_excl_scan_1024(uint32_t v, uint32_t *s_warp, uint32_t *total) {
+	// blockDim.x == 1024
+	const unsigned lane = sb_lane(), warp = threadIdx.x >> 5;
+	uint32_t inc = v;
+#pragma unroll
+	for (int s = 1; s < 32; s <<= 1) {
+		const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, s);
+		if (lane >= (unsigned)s) {
+			inc += o;
+		}
+	}
+	__syncthreads();
+	if (lane == 31) {
+		s_warp[warp] = inc;
+	}
+	__syncthreads();
+	if (warp == 0) {
+		uint32_t w = s_warp[lane];
+#pragma unroll
+		for (int s = 1; s < 32; s <<= 1) {
+			const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, w, s);
+			if (lane >= (unsigned)s) {
+				w += o;
+			}
+		}
+		s_warp[lane] = w; // inclusive over warps
+	}
+	__syncthreads();
+	const uint32_t base = warp ? s_warp[warp - 1] : 0u;
+	*total = s_warp[31];
+	return base + inc - v;
+}
+
+__global__ void __launch_bounds__(1024) k_bp_scan(bp_tables *__restrict__ T, bp_unit *__restrict__ units) {
+	__shared__ uint32_t s_warp[32];
+	const unsigned b = threadIdx.x;
+	uint32_t total;
+	// points (the NaN bucket goes last)
+	const uint32_t np = T->pt_hist[b];
+	const uint32_t po = bp_block_excl_scan_1024(np, s_warp, &total);
+	T->pt_off[b] = po;
+	T->pt_cursor[b] = po;
+	if (b == 0) {
+		const uint32_t nan = T->pt_hist[BP_NB];
+		T->pt_off[BP_NB] = total;
+		T->pt_cursor[BP_NB] = total;
+		T->pt_off[BP_NB + 1] = total + nan;
+		T->totals[0] = total;
+		T->totals[3] = nan;
+	}
+	// candidates
+	const uint32_t nc = T->cand_cnt[b];
+	const uint32_t co = bp_block_excl_scan_1024(nc, s_warp, &total);
+	T->cand_off[b] = co;
+	T->cand_cursor[b] = co;
+	if (b == 0) {
+		T->cand_off[BP_NB] = total;
+		T->totals[1] = total;
+	}
+	// work units: slices of at most BP_SLICE points of a bucket that has both points and candidates
+	const uint32_t nu = (np && nc) ? (np + BP_SLICE - 1) / BP_SLICE : 0u;
+	const uint32_t uo = bp_block_excl_scan_1024(nu, s_warp, &total);
+	for (uint32_t k = 0; k < nu; k++) {
+		bp_unit u;
+		u.bucket = b;
+		u.pbeg = po + k * BP_SLICE;
+		u.pend = min(po + np, u.pbeg + BP_SLICE);
+		units[uo + k] = u;
+	}
+	if (b == 0) {
+		T->totals[2] = total;
+		T->ticket = 0;
+	}
+}
+
+// ---- 4. the probe kernel ---------------------------------------------------------------------------------------
+#define BPP_THREADS 512
+#define BPP_CMAX 4096   // staged leaf entries per chunk
+#define BPP_EMAX 40960  // sub-cell directory entries per chunk (u16 offsets => < 65536)
+#define BPP_WMAX 512    // entries covering more than BPP_WIDE_T sub-cells: tested by every point instead
+#define BPP_WIDE_T 64
+#define BPP_STAGE 6144  // pairs staged per round before the coalesced flush
+#define BPP_C 0x80008000u
+
+struct bpp_smem {
+	uint2 qbox[BPP_CMAX];     // x = (ly0 << 16) | lx0, y = ((ly1 << 16) | lx1) | BPP_C
+	uint32_t cidx[BPP_CMAX];  // build-side index (FlatRTree idx_array value)
+	uint32_t cpos[BPP_CMAX];  // position in the tree's leaf level
+	uint32_t cnt[BP_NB];      // sub-cell counts, then fill cursors
+	uint16_t off[BP_NB + 8];  // CSR offsets
+	uint16_t ent[BPP_EMAX];   // CSR entries: staged-entry numbers
+	uint16_t wide[BPP_WMAX];
+	uint2 stage[BPP_STAGE];
+	uint32_t scan[32];
+	uint32_t unit, n_ent, n_wide, n_stage, stage_limit;
+	unsigned long long gbase;
+};
+
+// MODE 1: candidate semantics (float boxes, Box::Intersects). MODE 2: fused exact predicate on the build's BOX_2D.
+template <int MODE>
+__device__ __forceinline__ bool bp_exact(double x, double y, uint32_t pos, uint32_t bi, const float4 *__restrict__ boxes,
+                                         const double4 *__restrict__ build_box2d, int pred) {
+	if (MODE == 1) {
+		const float4 q = make_float4(sb_f64_to_f32_down(x), sb_f64_to_f32_down(y), sb_f64_to_f32_up(x), sb_f64_to_f32_up(y));
+		return sb_box_intersects(q, __ldg(boxes + pos));
+	} else {
+		const double4 b = build_box2d[bi];
+		return pred == SB_PRED_INTERSECTS ? (b.x <= x && x <= b.z && b.y <= y && y <= b.w)
+		                                  : (b.x < x && x < b.z && b.y < y && y < b.w);
+	}
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(BPP_THREADS, 1)
+    k_bp_probe(const float4 *__restrict__ boxes, const uint32_t *__restrict__ idx,
+               const double4 *__restrict__ build_box2d, int pred, const bp_grid *__restrict__ gp,
+               bp_tables *__restrict__ T, const bp_unit *__restrict__ units, const uint32_t *__restrict__ cand_pos,
+               const double2 *__restrict__ pxy, const uint32_t *__restrict__ pidx, uint32_t *__restrict__ out_probe,
+               uint32_t *__restrict__ out_build, uint64_t capacity, unsigned long long *__restrict__ counter) {
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	bpp_smem &S = *reinterpret_cast<bpp_smem *>(smem_raw);
+	const bp_grid g = *gp;
+	const unsigned tid = threadIdx.x, lane = sb_lane();
+	const unsigned lt = sb_lanemask_lt();
+	const uint32_t n_units = (uint32_t)T->totals[2];
+
+	while (true) {
+		__syncthreads();
+		if (tid == 0) {
+			S.unit = atomicAdd(&T->ticket, 1u);
+		}
+		__syncthreads();
+		const uint32_t u = S.unit;
+		if (u >= n_units) {
+			break;
+		}
+		const bp_unit unit = units[u];
+		const int ox = (int)(unit.bucket % BP_G) << 15, oy = (int)(unit.bucket / BP_G) << 15;
+		const uint32_t cbeg = T->cand_off[unit.bucket], cend = T->cand_off[unit.bucket + 1];
+		uint32_t c0 = cbeg;
+		while (c0 < cend) {
+			// ---- (a) stage a chunk of leaf entries as quantised in-bucket boxes ----
+			uint32_t ntry = min((uint32_t)BPP_CMAX, cend - c0);
+			while (true) {
+				__syncthreads();
+				if (tid == 0) {
+					S.n_ent = 0;
+					S.n_wide = 0;
+					S.n_stage = 0;
+					S.stage_limit = 0xFFFFFFFFu;
+				}
+				for (unsigned i = tid; i < BP_NB; i += BPP_THREADS) {
+					S.cnt[i] = 0;
+				}
+				__syncthreads();
+				for (uint32_t j = tid; j < ntry; j += BPP_THREADS) {
+					const uint32_t pos = cand_pos[c0 + j];
+					const uint32_t bi = __ldg(idx + pos);
+					int x0, y0, x1, y1;
+					bool empty = false;
+					if (MODE == 1) {
+						bp_leaf_range(__ldg(boxes + pos), g, x0, y0, x1, y1);
+					} else {
+						const double4 e = build_box2d[bi];
+						empty = (e.x != e.x) || (e.y != e.y) || (e.z != e.z) || (e.w != e.w);
+						x0 = bp_q(e.x, g.minx, g.sx), y0 = bp_q(e.y, g.miny, g.sy);
+						x1 = bp_q(e.z, g.minx, g.sx), y1 = bp_q(e.w, g.miny, g.sy);
+					}
+					empty = empty || x1 < ox || x0 > ox + 32767 || y1 < oy || y0 > oy + 32767 || x0 > x1 || y0 > y1;
+					const uint32_t lx0 = (uint32_t)(max(x0, ox) - ox), ly0 = (uint32_t)(max(y0, oy) - oy);
+					const uint32_t lx1 = (uint32_t)(min(x1, ox + 32767) - ox), ly1 = (uint32_t)(min(y1, oy + 32767) - oy);
+					uint2 qb;
+					qb.x = empty ? 0x7FFF7FFFu : ((ly0 << 16) | lx0);
+					qb.y = (empty ? 0u : ((ly1 << 16) | lx1)) | BPP_C;
+					S.qbox[j] = qb;
+					S.cidx[j] = bi;
+					S.cpos[j] = pos;
+					if (!empty) {
+						const uint32_t cells = ((lx1 >> 10) - (lx0 >> 10) + 1) * ((ly1 >> 10) - (ly0 >> 10) + 1);
+						if (cells > BPP_WIDE_T) {
+							atomicAdd(&S.n_wide, 1u);
+						} else {
+							atomicAdd(&S.n_ent, cells);
+							for (uint32_t cy = ly0 >> 10; cy <= (ly1 >> 10); cy++) {
+								for (uint32_t cx = lx0 >> 10; cx <= (lx1 >> 10); cx++) {
+									atomicAdd(&S.cnt[cy * 32 + cx], 1u);
+								}
+							}
+						}
+					}
+				}
+				__syncthreads();
+				if (S.n_ent <= BPP_EMAX && S.n_wide <= BPP_WMAX) {
+					break;
+				}
+				ntry = (ntry + 1) / 2; // rare: directory would overflow shared memory -> smaller chunk
+			}
+			// ---- (b) CSR offsets over the 1024 sub-cells (2 per thread) ----
+			{
+				const uint32_t a = S.cnt[2 * tid], b = S.cnt[2 * tid + 1];
+				uint32_t inc = a + b;
+#pragma unroll
+				for (int s = 1; s < 32; s <<= 1) {
+					const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, s);
+					if (lane >= (unsigned)s) {
+						inc += o;
+					}
+				}
+				if (lane == 31) {
+					S.scan[tid >> 5] = inc;
+				}
+				__syncthreads();
+				uint32_t base = 0;
+				for (unsigned w = 0; w < (tid >> 5); w++) {
+					base += S.scan[w];
+				}
+				const uint32_t ex = base + inc - (a + b);
+				S.off[2 * tid] = (uint16_t)ex;
+				S.off[2 * tid + 1] = (uint16_t)(ex + a);
+				S.cnt[2 * tid] = ex;
+				S.cnt[2 * tid + 1] = ex + a;
+				if (tid == BPP_THREADS - 1) {
+					S.off[BP_NB] = (uint16_t)(ex + a + b);
+				}
+				if (tid == 0) {
+					S.n_wide = 0;
+				}
+			}
+			__syncthreads();
+			// ---- (c) fill the directory ----
+			for (uint32_t j = tid; j < ntry; j += BPP_THREADS) {
+				const uint2 qb = S.qbox[j];
+				const uint32_t hi = qb.y & ~BPP_C;
+				const uint32_t lx0 = qb.x & 0xFFFFu, ly0 = qb.x >> 16, lx1 = hi & 0xFFFFu, ly1 = hi >> 16;
+				if (lx0 > lx1 || ly0 > ly1) {
+					continue; // empty
+				}
+				const uint32_t cells = ((lx1 >> 10) - (lx0 >> 10) + 1) * ((ly1 >> 10) - (ly0 >> 10) + 1);
+				if (cells > BPP_WIDE_T) {
+					S.wide[atomicAdd(&S.n_wide, 1u)] = (uint16_t)j;
+				} else {
+					for (uint32_t cy = ly0 >> 10; cy <= (ly1 >> 10); cy++) {
+						for (uint32_t cx = lx0 >> 10; cx <= (lx1 >> 10); cx++) {
+							S.ent[atomicAdd(&S.cnt[cy * 32 + cx], 1u)] = (uint16_t)j;
+						}
+					}
+				}
+			}
+			__syncthreads();
+			const uint32_t n_wide = S.n_wide;
+
+			// ---- (d) stream the unit's points ----
+			for (uint32_t p0 = unit.pbeg; p0 < unit.pend; p0 += BPP_THREADS) {
+				const uint32_t i = p0 + tid;
+				double x = 0, y = 0;
+				uint32_t id = 0, PqC = 0, beg = 0, lenc = 0, len = 0;
+				if (i < unit.pend) {
+					const double2 xy = pxy[i];
+					x = xy.x, y = xy.y;
+					id = pidx[i];
+					const uint32_t lx = (uint32_t)(bp_q(x, g.minx, g.sx) - ox), ly = (uint32_t)(bp_q(y, g.miny, g.sy) - oy);
+					PqC = ((ly << 16) | lx) | BPP_C;
+					const uint32_t sc = (ly >> 10) * 32 + (lx >> 10);
+					beg = S.off[sc];
+					lenc = S.off[sc + 1] - beg;
+					len = lenc + n_wide;
+				}
+				for (uint32_t e0 = 0; __syncthreads_or(len > e0); e0 += 64) {
+					// test up to 64 entries of this point's list; hits go to a bit mask
+					unsigned long long mask = 0;
+					const uint32_t kend = len > e0 ? min(len - e0, 64u) : 0u;
+					for (uint32_t k = 0; k < kend; k++) {
+						const uint32_t e = e0 + k;
+						const uint32_t j = e < lenc ? S.ent[beg + e] : S.wide[e - lenc];
+						const uint2 qb = S.qbox[j];
+						const uint32_t t1 = PqC - qb.x, t2 = qb.y - (PqC & ~BPP_C);
+						if ((t1 & t2 & BPP_C) == BPP_C) { // inside the closed quantised box
+							const uint32_t s1 = t1 - 0x00010001u, s2 = t2 - 0x00010001u;
+							// strictly inside on all four sides => exact hit; a tie needs the exact predicate
+							if ((s1 & s2 & BPP_C) == BPP_C ||
+							    bp_exact<MODE>(x, y, S.cpos[j], S.cidx[j], boxes, build_box2d, pred)) {
+								mask |= 1ull << k;
+							}
+						}
+					}
+					// reserve staging space: warp scan of the hit counts, one shared atomic per warp
+					const uint32_t cntk = (uint32_t)__popcll(mask);
+					uint32_t inc = cntk;
+#pragma unroll
+					for (int s = 1; s < 32; s <<= 1) {
+						const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, s);
+						if (lane >= (unsigned)s) {
+							inc += o;
+						}
+					}
+					const uint32_t wtotal = __shfl_sync(0xFFFFFFFFu, inc, 31);
+					uint32_t wbase = 0;
+					if (lane == 31 && wtotal) {
+						wbase = atomicAdd(&S.n_stage, wtotal);
+					}
+					wbase = __shfl_sync(0xFFFFFFFFu, wbase, 31);
+					uint32_t my = wbase + inc - cntk;
+					if (wbase + wtotal <= BPP_STAGE) {
+						while (mask) {
+							const int k = __ffsll((long long)mask) - 1;
+							mask &= mask - 1;
+							const uint32_t e = e0 + k;
+							const uint32_t j = e < lenc ? S.ent[beg + e] : S.wide[e - lenc];
+							S.stage[my++] = make_uint2(id, S.cidx[j]);
+						}
+					} else if (wtotal) {
+						// rare: this round produced more pairs than the staging buffer holds -> straight to global
+						if (lane == 31) {
+							atomicMin(&S.stage_limit, wbase);
+						}
+						unsigned long long gb = 0;
+						if (lane == 31) {
+							gb = atomicAdd(counter, (unsigned long long)wtotal);
+						}
+						gb = __shfl_sync(0xFFFFFFFFu, gb, 31) + (inc - cntk);
+						while (mask) {
+							const int k = __ffsll((long long)mask) - 1;
+							mask &= mask - 1;
+							const uint32_t e = e0 + k;
+							const uint32_t j = e < lenc ? S.ent[beg + e] : S.wide[e - lenc];
+							if (gb < capacity) {
+								out_probe[gb] = id;
+								out_build[gb] = S.cidx[j];
+							}
+							gb++;
+						}
+					}
+					__syncthreads();
+					const uint32_t nst = min(S.n_stage, S.stage_limit);
+					if (tid == 0) {
+						S.gbase = nst ? atomicAdd(counter, (unsigned long long)nst) : 0ull;
+					}
+					__syncthreads();
+					const unsigned long long gbase = S.gbase;
+					for (uint32_t t = tid; t < nst; t += BPP_THREADS) {
+						const uint2 p = S.stage[t];
+						if (gbase + t < capacity) {
+							out_probe[gbase + t] = p.x;
+							out_build[gbase + t] = p.y;
+						}
+					}
+					__syncthreads();
+					if (tid == 0) {
+						S.n_stage = 0;
+						S.stage_limit = 0xFFFFFFFFu;
+					}
+				}
+			}
+			c0 += ntry;
+		}
+	}
+}
+
+__global__ void __launch_bounds__(256) k_bp_unpack(const double2 *__restrict__ pxy, uint32_t n, double *__restrict__ x,
+                                                   double *__restrict__ y) {
+	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+		x[i] = pxy[i].x;
+		y[i] = pxy[i].y;
+	}
+}
+
+// ---- host side ---------------------------------------------------------------------------------------------------
+int sbi_flat_probe_bucketed(sb_context *ctx, const sb_flat *tree, const sb_probe_args &a, uint32_t *out_probe,
+                            uint32_t *out_build, uint64_t capacity, uint64_t *count) {
+	*count = 0;
+	const uint64_t n = a.m;
+	const uint32_t items = tree->h.item_count;
+	if (n == 0 || items == 0) {
+		return SB_OK;
+	}
+	SB_ARG(a.px != nullptr && a.py != nullptr, "bucketed probe takes points");
+	SB_ARG(n + a.index_base <= 0xFFFFFFFFull, "probe indices must fit 32 bits");
+	const int mode = a.pred >= 0 ? 2 : 1;
+	SB_ARG(mode == 1 || a.build_box2d != nullptr, "build_box2d");
+
+	bp_grid *d_grid = nullptr;
+	bp_tables *d_tab = nullptr;
+	bp_unit *d_units = nullptr;
+	double2 *d_pxy = nullptr;
+	uint32_t *d_pidx = nullptr, *d_cand = nullptr;
+	unsigned long long *d_counter = nullptr;
+	const uint64_t max_units = n / BP_SLICE + BP_NB + 1;
+	SB_TRY(ctx->scratch_t(1, &d_grid));
+	SB_TRY(ctx->scratch_t(1, &d_tab));
+	SB_TRY(ctx->scratch_t(max_units, &d_units));
+	SB_TRY(ctx->scratch_t(1, &d_counter));
+	SB_TRY(ctx->scratch_t(n, &d_pxy));
+	SB_TRY(ctx->scratch_t(n, &d_pidx));
+	SB_CUDA(cudaMemsetAsync(d_tab, 0, sizeof(bp_tables), ctx->stream));
+	SB_CUDA(cudaMemsetAsync(d_counter, 0, sizeof(*d_counter), ctx->stream));
+	const sb_flat_header *d_hdr = static_cast<const sb_flat_header *>(tree->buffer);
+	{
+		sb_prof_scope ps(ctx, "bp_partition");
+		k_bp_grid_init<<<1, 32, 0, ctx->stream>>>(d_hdr, d_grid);
+		SB_LAUNCH_CHECK(ctx);
+		k_bp_hist<<<sb_grid(n, BPH_THREADS * 8, 4), BPH_THREADS, 0, ctx->stream>>>(a.px, a.py, n, d_grid, d_tab->pt_hist);
+		SB_LAUNCH_CHECK(ctx);
+	}
+	{
+		sb_prof_scope ps(ctx, "bp_cand");
+		k_bp_cand<false><<<sb_grid(items, 256, 8), 256, 0, ctx->stream>>>(tree->boxes(), items, d_grid, d_tab->cand_cnt,
+		                                                                 nullptr);
+		SB_LAUNCH_CHECK(ctx);
+		k_bp_scan<<<1, 1024, 0, ctx->stream>>>(d_tab, d_units);
+		SB_LAUNCH_CHECK(ctx);
+	}
+	uint64_t totals[4];
+	SB_CUDA(cudaMemcpyAsync(ctx->pinned_u64, d_tab->totals, sizeof(totals), cudaMemcpyDeviceToHost, ctx->stream));
+	SB_CUDA(cudaStreamSynchronize(ctx->stream));
+	memcpy(totals, ctx->pinned_u64, sizeof(totals));
+	const uint64_t n_cand = totals[1], n_units = totals[2], n_nan = totals[3];
+	SB_ARG(n_cand < 0xFFFFFFFFull, "bucketed probe: candidate directory too large");
+	SB_TRY(ctx->scratch_t(n_cand ? n_cand : 1, &d_cand));
+	{
+		sb_prof_scope ps(ctx, "bp_partition");
+		k_bp_scatter<<<sb_grid(n, BPS_TILE, 2), BPS_THREADS, 0, ctx->stream>>>(a.px, a.py, n, a.index_base, d_grid,
+		                                                                     d_tab->pt_cursor, d_pxy, d_pidx);
+		SB_LAUNCH_CHECK(ctx);
+	}
+	{
+		sb_prof_scope ps(ctx, "bp_cand");
+		k_bp_cand<true><<<sb_grid(items, 256, 8), 256, 0, ctx->stream>>>(tree->boxes(), items, d_grid, d_tab->cand_cursor,
+		                                                                d_cand);
+		SB_LAUNCH_CHECK(ctx);
+	}
+	if (n_units) {
+		static bool attr_set = false;
+		if (!attr_set) {
+			SB_CUDA(cudaFuncSetAttribute(k_bp_probe<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(bpp_smem)));
+			SB_CUDA(cudaFuncSetAttribute(k_bp_probe<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(bpp_smem)));
+			attr_set = true;
+		}
+		const unsigned grid = (unsigned)(n_units < SB_NUM_SMS ? n_units : SB_NUM_SMS);
+		sb_prof_scope ps(ctx, "flat_probe");
+		if (mode == 1) {
+			k_bp_probe<1><<<grid, BPP_THREADS, sizeof(bpp_smem), ctx->stream>>>(
+			    tree->boxes(), tree->idx(), nullptr, -1, d_grid, d_tab, d_units, d_cand, d_pxy, d_pidx, out_probe, out_build,
+			    capacity, d_counter);
+		} else {
+			k_bp_probe<2><<<grid, BPP_THREADS, sizeof(bpp_smem), ctx->stream>>>(
+			    tree->boxes(), tree->idx(), a.build_box2d, a.pred, d_grid, d_tab, d_units, d_cand, d_pxy, d_pidx, out_probe,
+			    out_build, capacity, d_counter);
+		}
+		SB_LAUNCH_CHECK(ctx);
+	}
+	uint64_t c1 = 0;
+	SB_TRY(sbi_read_u64(ctx, reinterpret_cast<const uint64_t *>(d_counter), &c1));
+	*count = c1;
+	if (n_nan && mode == 1) {
+		// NaN coordinates: Box::Intersects never rejects on a NaN axis. Such rows take the per-probe tree walk.
+		double *nx = nullptr, *ny = nullptr;
+		SB_TRY(ctx->scratch_t(n_nan, &nx));
+		SB_TRY(ctx->scratch_t(n_nan, &ny));
+		const uint64_t off = totals[0];
+		k_bp_unpack<<<sb_grid(n_nan, 256, 8), 256, 0, ctx->stream>>>(d_pxy + off, (uint32_t)n_nan, nx, ny);
+		SB_LAUNCH_CHECK(ctx);
+		sb_probe_args b;
+		b.px = nx;
+		b.py = ny;
+		b.m = n_nan;
+		b.ids = d_pidx + off;
+		b.force_walk = true;
+		uint64_t c2 = 0;
+		const uint64_t done = c1 < capacity ? c1 : capacity;
+		int s = sbi_flat_probe(ctx, tree, b, out_probe + done, out_build + done, capacity - done, &c2);
+		*count = c1 + c2;
+		if (s != SB_OK && s != SB_ERR_CAPACITY) {
+			return s;
+		}
+	}
+	if (*count > capacity) {
+		sb_set_error("probe: %llu pairs, capacity %llu", (unsigned long long)*count, (unsigned long long)capacity);
+		return SB_ERR_CAPACITY;
+	}
+	return SB_OK;
+}

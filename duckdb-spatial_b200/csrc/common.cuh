@@ -73,6 +73,9 @@ struct sb_context {
 	bool profiling = false;
 	std::map<std::string, sb_prof_entry> prof;
 	std::vector<cudaEvent_t> event_pool;
+	// sb_context_set_option("probe_path"): 0 = auto (bulk point probes take the bucketed kernel), 1 = always the
+	// per-probe tree walk, 2 = always bucketed
+	int probe_path = 0;
 	// pinned staging for small host<->device transfers (counters)
 	uint64_t *pinned_u64 = nullptr;
 

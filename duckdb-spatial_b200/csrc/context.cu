@@ -142,6 +142,17 @@ extern "C" int sb_context_set_stream(sb_context *ctx, void *cuda_stream) {
 	return SB_OK;
 }
 
+extern "C" int sb_context_set_option(sb_context *ctx, const char *key, int64_t value) {
+	SB_ARG(ctx != nullptr && key != nullptr, "ctx/key");
+	if (strcmp(key, "probe_path") == 0) {
+		SB_ARG(value >= 0 && value <= 2, "probe_path must be 0 (auto), 1 (tree walk) or 2 (bucketed)");
+		ctx->probe_path = (int)value;
+		return SB_OK;
+	}
+	sb_set_error("unknown option '%s'", key);
+	return SB_ERR_ARG;
+}
+
 extern "C" int sb_context_sync(sb_context *ctx) {
 	SB_ARG(ctx != nullptr, "ctx");
 	SB_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -163,6 +174,13 @@ extern "C" int sb_context_profile(sb_context *ctx, int enable) {
 		}
 	}
 	ctx->prof.clear();
+	// event creation is slow on a busy device (measured: >100 ms per step of host stalls when the pool was filled
+	// lazily inside the timed region), so the pool is filled here, outside any timed region
+	while (enable && ctx->event_pool.size() < 2048) {
+		cudaEvent_t e = nullptr;
+		SB_CUDA(cudaEventCreate(&e));
+		ctx->event_pool.push_back(e);
+	}
 	return SB_OK;
 }
 

@@ -219,7 +219,7 @@ __global__ void __launch_bounds__(PR_WARPS * 32)
     k_flat_probe(const float4 *__restrict__ boxes, const uint32_t *__restrict__ idx, const flat_meta M,
                  const float4 *__restrict__ probe_box, const double *__restrict__ px, const double *__restrict__ py,
                  const double4 *__restrict__ build_box2d, int pred, uint64_t m, uint32_t index_base,
-                 uint32_t *__restrict__ out_probe, uint32_t *__restrict__ out_build, uint64_t capacity,
+                 const uint32_t *__restrict__ ids, uint32_t *__restrict__ out_probe, uint32_t *__restrict__ out_build, uint64_t capacity,
                  unsigned long long *__restrict__ counter) {
 	__shared__ uint32_t s_stack[PR_WARPS][PR_STACK];
 	__shared__ uint2 s_out[PR_WARPS][PR_OUT];
@@ -295,7 +295,8 @@ __global__ void __launch_bounds__(PR_WARPS * 32)
 				}
 				const unsigned hm = __ballot_sync(0xFFFFFFFFu, hit);
 				if (hit) {
-					obuf[ocnt + __popc(hm & lt)] = make_uint2((uint32_t)(chunk * 32 + pl) + index_base, payload);
+					obuf[ocnt + __popc(hm & lt)] =
+					    make_uint2(ids ? ids[chunk * 32 + pl] : (uint32_t)(chunk * 32 + pl) + index_base, payload);
 				}
 				ocnt += __popc(hm);
 				__syncwarp();
@@ -341,6 +342,10 @@ int sbi_flat_probe(sb_context *ctx, const sb_flat *tree, const sb_probe_args &a,
 		return SB_OK;
 	}
 	SB_ARG(a.m + a.index_base <= 0xFFFFFFFFull, "probe indices must fit 32 bits");
+	// bulk point probes: bucketed kernel (same pair set); small batches and box probes: per-probe tree walk
+	if (!a.force_walk && !a.probe_box && ctx->probe_path != 1 && (ctx->probe_path == 2 || a.m >= (1u << 17))) {
+		return sbi_flat_probe_bucketed(ctx, tree, a, out_probe, out_build, capacity, count);
+	}
 	flat_meta M;
 	M.item_count = tree->h.item_count;
 	M.node_size = tree->h.node_size;
@@ -355,15 +360,15 @@ int sbi_flat_probe(sb_context *ctx, const sb_flat *tree, const sb_probe_args &a,
 		sb_prof_scope ps(ctx, "flat_probe");
 		if (a.probe_box) {
 			k_flat_probe<0><<<grid, PR_WARPS * 32, 0, ctx->stream>>>(tree->boxes(), tree->idx(), M, a.probe_box, nullptr,
-			                                                        nullptr, nullptr, -1, a.m, a.index_base, out_probe,
+			                                                        nullptr, nullptr, -1, a.m, a.index_base, a.ids, out_probe,
 			                                                        out_build, capacity, d_counter);
 		} else if (a.pred < 0) {
 			k_flat_probe<1><<<grid, PR_WARPS * 32, 0, ctx->stream>>>(tree->boxes(), tree->idx(), M, nullptr, a.px, a.py,
-			                                                        nullptr, -1, a.m, a.index_base, out_probe, out_build,
+			                                                        nullptr, -1, a.m, a.index_base, a.ids, out_probe, out_build,
 			                                                        capacity, d_counter);
 		} else {
 			k_flat_probe<2><<<grid, PR_WARPS * 32, 0, ctx->stream>>>(tree->boxes(), tree->idx(), M, nullptr, a.px, a.py,
-			                                                        a.build_box2d, a.pred, a.m, a.index_base, out_probe,
+			                                                        a.build_box2d, a.pred, a.m, a.index_base, a.ids, out_probe,
 			                                                        out_build, capacity, d_counter);
 		}
 		SB_LAUNCH_CHECK(ctx);

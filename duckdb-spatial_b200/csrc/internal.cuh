@@ -84,9 +84,15 @@ struct sb_probe_args {
 	int pred = -1;                             // -1 = none
 	uint64_t m = 0;
 	uint32_t index_base = 0;
+	const uint32_t *ids = nullptr; // optional: emitted probe id = ids[i] instead of index_base + i
+	bool force_walk = false;       // always take the per-probe tree walk (v1)
 };
 int sbi_flat_probe(sb_context *ctx, const sb_flat *tree, const sb_probe_args &args, uint32_t *out_probe,
                    uint32_t *out_build, uint64_t capacity, uint64_t *count);
+
+// bucket_probe.cu : bulk point probe (v2), same result set as sbi_flat_probe's tree walk
+int sbi_flat_probe_bucketed(sb_context *ctx, const sb_flat *tree, const sb_probe_args &args, uint32_t *out_probe,
+                            uint32_t *out_build, uint64_t capacity, uint64_t *count);
 
 // refine.cu
 int sbi_pack_box2d(sb_context *ctx, const double *x0, const double *y0, const double *x1, const double *y1, uint64_t n,

@@ -57,6 +57,9 @@ class Context:
     def use_private_stream(self):
         capi.check(self.L.sb_context_set_stream(self.h, None))
 
+    def set_option(self, key, value):
+        capi.check(self.L.sb_context_set_option(self.h, key.encode(), int(value)))
+
     def sync(self):
         capi.check(self.L.sb_context_sync(self.h))
 

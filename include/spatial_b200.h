@@ -58,6 +58,9 @@ SB_API void sb_context_destroy(sb_context *ctx);
 /* adopt an external stream (e.g. torch.cuda.current_stream().cuda_stream); NULL restores the private stream */
 SB_API int sb_context_set_stream(sb_context *ctx, void *cuda_stream);
 SB_API int sb_context_sync(sb_context *ctx);
+/* tuning / test knobs. "probe_path": 0 = auto, 1 = per-probe tree walk only, 2 = bucketed bulk probe only
+ * (both produce the same pair set; the parity tests run every join through both). */
+SB_API int sb_context_set_option(sb_context *ctx, const char *key, int64_t value);
 /* number of kernels this context has launched so far (bench.py's gpu_launches) */
 SB_API uint64_t sb_context_launches(const sb_context *ctx);
 /* milliseconds the dominant kernel class spent on the GPU since the last reset, measured with CUDA events on
