@@ -94,26 +94,39 @@ __global__ void __launch_bounds__(BPH_THREADS) k_bp_hist(const double *__restric
 	}
 }
 
-#define BPS_THREADS 1024
+// One tile = 4096 points: rank inside the tile's bucket with shared atomics, reserve the tile's share of every
+// bucket with one global atomic per non-empty bucket, reorder the tile by bucket in shared memory, and write it out
+// so that consecutive threads write consecutive addresses (runs of one bucket): whole sectors, no partial-sector
+// read-modify-write in L2 (the v1 of this kernel scattered 8/16-byte stores: 396 M partial sectors, 9.7 ms).
+#define BPS_THREADS 512
 #define BPS_ITEMS 8
 #define BPS_TILE (BPS_THREADS * BPS_ITEMS)
-__global__ void __launch_bounds__(BPS_THREADS)
+struct bps_smem {
+	double2 xy[BPS_TILE];
+	uint32_t idx[BPS_TILE];
+	uint16_t bkt[BPS_TILE];
+	uint32_t cnt[BP_NB + 8];   // counts, then (global base - tile offset) per bucket
+	uint32_t off[BP_NB + 8];   // tile-local exclusive offsets
+	uint32_t scan[16];
+};
+__global__ void __launch_bounds__(BPS_THREADS, 2)
     k_bp_scatter(const double *__restrict__ px, const double *__restrict__ py, uint64_t n, uint32_t index_base,
                  const bp_grid *__restrict__ gp, uint32_t *__restrict__ cursor, double2 *__restrict__ oxy,
                  uint32_t *__restrict__ oidx) {
-	__shared__ uint32_t s_cnt[BP_NB + 1];
-	__shared__ uint32_t s_base[BP_NB + 1];
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	bps_smem &S = *reinterpret_cast<bps_smem *>(smem_raw);
 	const bp_grid g = *gp;
+	const unsigned tid = threadIdx.x, lane = sb_lane(), warp = tid >> 5;
 	const uint64_t tiles = (n + BPS_TILE - 1) / BPS_TILE;
 	for (uint64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-		for (int i = threadIdx.x; i <= BP_NB; i += BPS_THREADS) {
-			s_cnt[i] = 0;
+		for (int i = tid; i <= BP_NB; i += BPS_THREADS) {
+			S.cnt[i] = 0;
 		}
 		__syncthreads();
 		double x[BPS_ITEMS], y[BPS_ITEMS];
 		int b[BPS_ITEMS];
 		uint32_t r[BPS_ITEMS];
-		const uint64_t base = tile * BPS_TILE + threadIdx.x;
+		const uint64_t base = tile * BPS_TILE + tid;
 #pragma unroll
 		for (int k = 0; k < BPS_ITEMS; k++) {
 			const uint64_t i = base + (uint64_t)k * BPS_THREADS;
@@ -121,28 +134,69 @@ __global__ void __launch_bounds__(BPS_THREADS)
 			if (i < n) {
 				x[k] = px[i];
 				y[k] = py[i];
-				b[k] = bp_bucket(x[k], y[k], g);
 			}
 		}
 #pragma unroll
 		for (int k = 0; k < BPS_ITEMS; k++) {
-			r[k] = b[k] >= 0 ? atomicAdd(&s_cnt[b[k]], 1u) : 0u;
+			if (base + (uint64_t)k * BPS_THREADS < n) {
+				b[k] = bp_bucket(x[k], y[k], g);
+			}
+			r[k] = b[k] >= 0 ? atomicAdd(&S.cnt[b[k]], 1u) : 0u;
 		}
 		__syncthreads();
-		for (int i = threadIdx.x; i <= BP_NB; i += BPS_THREADS) {
-			const uint32_t c = s_cnt[i];
-			if (c) {
-				s_base[i] = atomicAdd(&cursor[i], c);
+		// exclusive scan over the 1025 bins (2 per thread + the NaN bin) and the global reservations
+		{
+			const uint32_t c0 = S.cnt[2 * tid], c1 = S.cnt[2 * tid + 1];
+			uint32_t inc = c0 + c1;
+#pragma unroll
+			for (int s = 1; s < 32; s <<= 1) {
+				const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, s);
+				if (lane >= (unsigned)s) {
+					inc += o;
+				}
+			}
+			if (lane == 31) {
+				S.scan[warp] = inc;
+			}
+			__syncthreads();
+			uint32_t wb = 0;
+			for (unsigned w = 0; w < warp; w++) {
+				wb += S.scan[w];
+			}
+			const uint32_t e0 = wb + inc - (c0 + c1), e1 = e0 + c0;
+			S.off[2 * tid] = e0;
+			S.off[2 * tid + 1] = e1;
+			if (c0) {
+				S.cnt[2 * tid] = atomicAdd(&cursor[2 * tid], c0) - e0;
+			}
+			if (c1) {
+				S.cnt[2 * tid + 1] = atomicAdd(&cursor[2 * tid + 1], c1) - e1;
+			}
+			if (tid == BPS_THREADS - 1) {
+				const uint32_t cn = S.cnt[BP_NB], en = e1 + c1;
+				S.off[BP_NB] = en;
+				S.off[BP_NB + 1] = en + cn;
+				if (cn) {
+					S.cnt[BP_NB] = atomicAdd(&cursor[BP_NB], cn) - en;
+				}
 			}
 		}
 		__syncthreads();
 #pragma unroll
 		for (int k = 0; k < BPS_ITEMS; k++) {
 			if (b[k] >= 0) {
-				const uint32_t dst = s_base[b[k]] + r[k];
-				oxy[dst] = make_double2(x[k], y[k]);
-				oidx[dst] = (uint32_t)(base + (uint64_t)k * BPS_THREADS) + index_base;
+				const uint32_t slot = S.off[b[k]] + r[k];
+				S.xy[slot] = make_double2(x[k], y[k]);
+				S.idx[slot] = (uint32_t)(base + (uint64_t)k * BPS_THREADS) + index_base;
+				S.bkt[slot] = (uint16_t)b[k];
 			}
+		}
+		__syncthreads();
+		const uint32_t kept = S.off[BP_NB + 1];
+		for (uint32_t t = tid; t < kept; t += BPS_THREADS) {
+			const uint32_t dst = S.cnt[S.bkt[t]] + t;
+			oxy[dst] = S.xy[t];
+			oidx[dst] = S.idx[t];
 		}
 		__syncthreads();
 	}
@@ -276,29 +330,31 @@ __global__ void __launch_bounds__(1024) k_bp_scan(bp_tables *__restrict__ T, bp_
 }
 
 // ---- 4. the probe kernel ---------------------------------------------------------------------------------------
-#define BPP_THREADS 512
+#define BPP_THREADS 1024
 #define BPP_CMAX 4096   // staged leaf entries per chunk
 #define BPP_EMAX 40960  // sub-cell directory entries per chunk (u16 offsets => < 65536)
 #define BPP_WMAX 512    // entries covering more than BPP_WIDE_T sub-cells: tested by every point instead
 #define BPP_WIDE_T 64
-#define BPP_STAGE 6144  // pairs staged per round before the coalesced flush
 #define BPP_C 0x80008000u
+#define BPP_K 0x00010001u
 
+// MODE 1: candidate semantics (float boxes, Box::Intersects). MODE 2: fused exact predicate on the build's BOX_2D.
+template <int MODE>
 struct bpp_smem {
+	static constexpr int STAGE = MODE == 1 ? 9216 : 11264; // pairs staged per round before the coalesced flush
 	uint2 qbox[BPP_CMAX];     // x = (ly0 << 16) | lx0, y = ((ly1 << 16) | lx1) | BPP_C
 	uint32_t cidx[BPP_CMAX];  // build-side index (FlatRTree idx_array value)
-	uint32_t cpos[BPP_CMAX];  // position in the tree's leaf level
+	uint32_t cpos[MODE == 1 ? BPP_CMAX : 1]; // position in the tree's leaf level (float box for the tie test)
 	uint32_t cnt[BP_NB];      // sub-cell counts, then fill cursors
 	uint16_t off[BP_NB + 8];  // CSR offsets
 	uint16_t ent[BPP_EMAX];   // CSR entries: staged-entry numbers
 	uint16_t wide[BPP_WMAX];
-	uint2 stage[BPP_STAGE];
+	uint2 stage[STAGE];
 	uint32_t scan[32];
 	uint32_t unit, n_ent, n_wide, n_stage, stage_limit;
 	unsigned long long gbase;
 };
 
-// MODE 1: candidate semantics (float boxes, Box::Intersects). MODE 2: fused exact predicate on the build's BOX_2D.
 template <int MODE>
 __device__ __forceinline__ bool bp_exact(double x, double y, uint32_t pos, uint32_t bi, const float4 *__restrict__ boxes,
                                          const double4 *__restrict__ build_box2d, int pred) {
@@ -312,6 +368,142 @@ __device__ __forceinline__ bool bp_exact(double x, double y, uint32_t pos, uint3
 	}
 }
 
+// Three-state test of a point (PqC = packed 15-bit in-bucket coordinates | BPP_C) against a quantised box.
+// Each 16-bit half of t1 / t2 is 0x8000 + (p - lo) resp. 0x8000 + (hi - p), always in [1, 0xFFFF] (no borrow
+// between halves): bit 15 set <=> that side holds in the closed sense; >= 0x8001 <=> it holds strictly.
+// Strictly inside on all four sides => the exact predicate is true; outside on any side => false;
+// otherwise (a tie in quantised space) the exact predicate decides.
+#define BPP_TEST(j, bit, mask, tmask)                                                                                \
+	do {                                                                                                             \
+		const uint2 qb_ = S.qbox[j];                                                                                 \
+		const uint32_t t1_ = PqC - qb_.x, t2_ = qb_.y - Pq;                                                          \
+		if (((t1_ - BPP_K) & (t2_ - BPP_K) & BPP_C) == BPP_C) {                                                      \
+			mask |= (bit);                                                                                           \
+		} else if ((t1_ & t2_ & BPP_C) == BPP_C) {                                                                   \
+			tmask |= (bit);                                                                                          \
+		}                                                                                                            \
+	} while (0)
+
+// Flush protocol of one pass: every thread holds a 64-bit hit mask over its entry list `ep`. Warp scan of the hit
+// counts -> one shared atomic per warp reserves staging space -> pairs are written to the staging buffer ->
+// one global atomic per CTA reserves output space -> coalesced copy-out. A warp whose pairs do not fit the
+// staging buffer (dense inputs) writes them straight to global memory.
+template <int MODE>
+__device__ __forceinline__ void bpp_emit(bpp_smem<MODE> &S, uint32_t mlo, uint32_t mhi, const uint16_t *ep, uint32_t id,
+                                         uint32_t *__restrict__ out_probe, uint32_t *__restrict__ out_build,
+                                         uint64_t capacity, unsigned long long *__restrict__ counter) {
+	constexpr uint32_t STAGE = bpp_smem<MODE>::STAGE;
+	const unsigned tid = threadIdx.x, lane = sb_lane();
+	const uint32_t cntk = (uint32_t)(__popc(mlo) + __popc(mhi));
+	uint32_t inc = cntk;
+#pragma unroll
+	for (int s = 1; s < 32; s <<= 1) {
+		const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, s);
+		if (lane >= (unsigned)s) {
+			inc += o;
+		}
+	}
+	const uint32_t wtotal = __shfl_sync(0xFFFFFFFFu, inc, 31);
+	uint32_t wbase = 0;
+	if (lane == 31 && wtotal) {
+		wbase = atomicAdd(&S.n_stage, wtotal);
+	}
+	wbase = __shfl_sync(0xFFFFFFFFu, wbase, 31);
+	if (wbase + wtotal <= STAGE) {
+		uint2 *dst = S.stage + wbase + (inc - cntk);
+		while (mlo) {
+			const int k = 31 - __clz(mlo);
+			mlo ^= 1u << k;
+			*dst++ = make_uint2(id, S.cidx[ep[k]]);
+		}
+		while (mhi) {
+			const int k = 31 - __clz(mhi);
+			mhi ^= 1u << k;
+			*dst++ = make_uint2(id, S.cidx[ep[32 + k]]);
+		}
+	} else if (wtotal) {
+		if (lane == 31) {
+			atomicMin(&S.stage_limit, wbase);
+		}
+		unsigned long long gb = 0;
+		if (lane == 31) {
+			gb = atomicAdd(counter, (unsigned long long)wtotal);
+		}
+		gb = __shfl_sync(0xFFFFFFFFu, gb, 31) + (inc - cntk);
+		while (mlo | mhi) {
+			int k;
+			if (mlo) {
+				k = 31 - __clz(mlo);
+				mlo ^= 1u << k;
+			} else {
+				k = 31 - __clz(mhi);
+				mhi ^= 1u << k;
+				k += 32;
+			}
+			if (gb < capacity) {
+				out_probe[gb] = id;
+				out_build[gb] = S.cidx[ep[k]];
+			}
+			gb++;
+		}
+	}
+	__syncthreads();
+	const uint32_t nst = min(S.n_stage, S.stage_limit);
+	if (tid == 0) {
+		S.gbase = nst ? atomicAdd(counter, (unsigned long long)nst) : 0ull;
+	}
+	__syncthreads();
+	const unsigned long long gbase = S.gbase;
+	for (uint32_t t = tid; t < nst; t += BPP_THREADS) {
+		const uint2 p = S.stage[t];
+		if (gbase + t < capacity) {
+			out_probe[gbase + t] = p.x;
+			out_build[gbase + t] = p.y;
+		}
+	}
+	__syncthreads();
+	if (tid == 0) {
+		S.n_stage = 0;
+		S.stage_limit = 0xFFFFFFFFu;
+	}
+}
+
+// tests up to 64 entries ep[0..n) for one point; ties are resolved with the exact predicate
+#define BPP_PASS(ep, n)                                                                                              \
+	do {                                                                                                             \
+		uint32_t tlo_ = 0, thi_ = 0;                                                                                 \
+		const uint32_t n0_ = min((uint32_t)(n), 32u);                                                                \
+		uint32_t bit_ = 1;                                                                                           \
+		for (uint32_t k_ = 0; k_ < n0_; k_++, bit_ <<= 1) {                                                          \
+			BPP_TEST((ep)[k_], bit_, mlo, tlo_);                                                                     \
+		}                                                                                                            \
+		if ((n) > 32u) {                                                                                             \
+			bit_ = 1;                                                                                                \
+			for (uint32_t k_ = 32; k_ < (uint32_t)(n); k_++, bit_ <<= 1) {                                           \
+				BPP_TEST((ep)[k_], bit_, mhi, thi_);                                                                 \
+			}                                                                                                        \
+		}                                                                                                            \
+		while (tlo_ | thi_) {                                                                                        \
+			int k_;                                                                                                  \
+			if (tlo_) {                                                                                              \
+				k_ = 31 - __clz(tlo_);                                                                               \
+				tlo_ ^= 1u << k_;                                                                                    \
+			} else {                                                                                                 \
+				k_ = 31 - __clz(thi_);                                                                               \
+				thi_ ^= 1u << k_;                                                                                    \
+				k_ += 32;                                                                                            \
+			}                                                                                                        \
+			const uint32_t j_ = (ep)[k_];                                                                            \
+			if (bp_exact<MODE>(x, y, MODE == 1 ? S.cpos[j_] : 0u, S.cidx[j_], boxes, build_box2d, pred)) {           \
+				if (k_ < 32) {                                                                                       \
+					mlo |= 1u << k_;                                                                                 \
+				} else {                                                                                             \
+					mhi |= 1u << (k_ - 32);                                                                          \
+				}                                                                                                    \
+			}                                                                                                        \
+		}                                                                                                            \
+	} while (0)
+
 template <int MODE>
 __global__ void __launch_bounds__(BPP_THREADS, 1)
     k_bp_probe(const float4 *__restrict__ boxes, const uint32_t *__restrict__ idx,
@@ -320,10 +512,9 @@ __global__ void __launch_bounds__(BPP_THREADS, 1)
                const double2 *__restrict__ pxy, const uint32_t *__restrict__ pidx, uint32_t *__restrict__ out_probe,
                uint32_t *__restrict__ out_build, uint64_t capacity, unsigned long long *__restrict__ counter) {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
-	bpp_smem &S = *reinterpret_cast<bpp_smem *>(smem_raw);
+	bpp_smem<MODE> &S = *reinterpret_cast<bpp_smem<MODE> *>(smem_raw);
 	const bp_grid g = *gp;
-	const unsigned tid = threadIdx.x, lane = sb_lane();
-	const unsigned lt = sb_lanemask_lt();
+	const unsigned tid = threadIdx.x;
 	const uint32_t n_units = (uint32_t)T->totals[2];
 
 	while (true) {
@@ -341,7 +532,7 @@ __global__ void __launch_bounds__(BPP_THREADS, 1)
 		const uint32_t cbeg = T->cand_off[unit.bucket], cend = T->cand_off[unit.bucket + 1];
 		uint32_t c0 = cbeg;
 		while (c0 < cend) {
-			// ---- (a) stage a chunk of leaf entries as quantised in-bucket boxes ----
+			// ---- (a) stage a chunk of leaf entries as quantised in-bucket boxes, count directory entries ----
 			uint32_t ntry = min((uint32_t)BPP_CMAX, cend - c0);
 			while (true) {
 				__syncthreads();
@@ -351,9 +542,7 @@ __global__ void __launch_bounds__(BPP_THREADS, 1)
 					S.n_stage = 0;
 					S.stage_limit = 0xFFFFFFFFu;
 				}
-				for (unsigned i = tid; i < BP_NB; i += BPP_THREADS) {
-					S.cnt[i] = 0;
-				}
+				S.cnt[tid] = 0; // BPP_THREADS == BP_NB
 				__syncthreads();
 				for (uint32_t j = tid; j < ntry; j += BPP_THREADS) {
 					const uint32_t pos = cand_pos[c0 + j];
@@ -362,6 +551,7 @@ __global__ void __launch_bounds__(BPP_THREADS, 1)
 					bool empty = false;
 					if (MODE == 1) {
 						bp_leaf_range(__ldg(boxes + pos), g, x0, y0, x1, y1);
+						S.cpos[j] = pos;
 					} else {
 						const double4 e = build_box2d[bi];
 						empty = (e.x != e.x) || (e.y != e.y) || (e.z != e.z) || (e.w != e.w);
@@ -376,7 +566,6 @@ __global__ void __launch_bounds__(BPP_THREADS, 1)
 					qb.y = (empty ? 0u : ((ly1 << 16) | lx1)) | BPP_C;
 					S.qbox[j] = qb;
 					S.cidx[j] = bi;
-					S.cpos[j] = pos;
 					if (!empty) {
 						const uint32_t cells = ((lx1 >> 10) - (lx0 >> 10) + 1) * ((ly1 >> 10) - (ly0 >> 10) + 1);
 						if (cells > BPP_WIDE_T) {
@@ -395,34 +584,17 @@ __global__ void __launch_bounds__(BPP_THREADS, 1)
 				if (S.n_ent <= BPP_EMAX && S.n_wide <= BPP_WMAX) {
 					break;
 				}
-				ntry = (ntry + 1) / 2; // rare: directory would overflow shared memory -> smaller chunk
+				ntry = (ntry + 1) / 2; // rare: the directory would overflow shared memory -> smaller chunk
 			}
-			// ---- (b) CSR offsets over the 1024 sub-cells (2 per thread) ----
+			// ---- (b) CSR offsets over the 1024 sub-cells (one per thread) ----
 			{
-				const uint32_t a = S.cnt[2 * tid], b = S.cnt[2 * tid + 1];
-				uint32_t inc = a + b;
-#pragma unroll
-				for (int s = 1; s < 32; s <<= 1) {
-					const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, s);
-					if (lane >= (unsigned)s) {
-						inc += o;
-					}
-				}
-				if (lane == 31) {
-					S.scan[tid >> 5] = inc;
-				}
-				__syncthreads();
-				uint32_t base = 0;
-				for (unsigned w = 0; w < (tid >> 5); w++) {
-					base += S.scan[w];
-				}
-				const uint32_t ex = base + inc - (a + b);
-				S.off[2 * tid] = (uint16_t)ex;
-				S.off[2 * tid + 1] = (uint16_t)(ex + a);
-				S.cnt[2 * tid] = ex;
-				S.cnt[2 * tid + 1] = ex + a;
+				uint32_t total;
+				const uint32_t c = S.cnt[tid];
+				const uint32_t ex = bp_block_excl_scan_1024(c, S.scan, &total);
+				S.off[tid] = (uint16_t)ex;
+				S.cnt[tid] = ex;
 				if (tid == BPP_THREADS - 1) {
-					S.off[BP_NB] = (uint16_t)(ex + a + b);
+					S.off[BP_NB] = (uint16_t)(ex + c);
 				}
 				if (tid == 0) {
 					S.n_wide = 0;
@@ -451,106 +623,41 @@ __global__ void __launch_bounds__(BPP_THREADS, 1)
 			__syncthreads();
 			const uint32_t n_wide = S.n_wide;
 
-			// ---- (d) stream the unit's points ----
+			// ---- (d) stream the unit's points, one per thread and round ----
 			for (uint32_t p0 = unit.pbeg; p0 < unit.pend; p0 += BPP_THREADS) {
 				const uint32_t i = p0 + tid;
+				const bool valid = i < unit.pend;
 				double x = 0, y = 0;
-				uint32_t id = 0, PqC = 0, beg = 0, lenc = 0, len = 0;
-				if (i < unit.pend) {
+				uint32_t id = 0, PqC = BPP_C, Pq = 0, beg = 0, lenc = 0;
+				if (valid) {
 					const double2 xy = pxy[i];
 					x = xy.x, y = xy.y;
 					id = pidx[i];
 					const uint32_t lx = (uint32_t)(bp_q(x, g.minx, g.sx) - ox), ly = (uint32_t)(bp_q(y, g.miny, g.sy) - oy);
-					PqC = ((ly << 16) | lx) | BPP_C;
+					Pq = (ly << 16) | lx;
+					PqC = Pq | BPP_C;
 					const uint32_t sc = (ly >> 10) * 32 + (lx >> 10);
 					beg = S.off[sc];
 					lenc = S.off[sc + 1] - beg;
-					len = lenc + n_wide;
 				}
-				for (uint32_t e0 = 0; __syncthreads_or(len > e0); e0 += 64) {
-					// test up to 64 entries of this point's list; hits go to a bit mask
-					unsigned long long mask = 0;
-					const uint32_t kend = len > e0 ? min(len - e0, 64u) : 0u;
-					for (uint32_t k = 0; k < kend; k++) {
-						const uint32_t e = e0 + k;
-						const uint32_t j = e < lenc ? S.ent[beg + e] : S.wide[e - lenc];
-						const uint2 qb = S.qbox[j];
-						const uint32_t t1 = PqC - qb.x, t2 = qb.y - (PqC & ~BPP_C);
-						if ((t1 & t2 & BPP_C) == BPP_C) { // inside the closed quantised box
-							const uint32_t s1 = t1 - 0x00010001u, s2 = t2 - 0x00010001u;
-							// strictly inside on all four sides => exact hit; a tie needs the exact predicate
-							if ((s1 & s2 & BPP_C) == BPP_C ||
-							    bp_exact<MODE>(x, y, S.cpos[j], S.cidx[j], boxes, build_box2d, pred)) {
-								mask |= 1ull << k;
-							}
-						}
+				for (uint32_t e0 = 0; __syncthreads_or(lenc > e0); e0 += 64) {
+					uint32_t mlo = 0, mhi = 0;
+					const uint16_t *ep = S.ent + beg + e0;
+					if (lenc > e0) {
+						const uint32_t n = min(lenc - e0, 64u);
+						BPP_PASS(ep, n);
 					}
-					// reserve staging space: warp scan of the hit counts, one shared atomic per warp
-					const uint32_t cntk = (uint32_t)__popcll(mask);
-					uint32_t inc = cntk;
-#pragma unroll
-					for (int s = 1; s < 32; s <<= 1) {
-						const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, s);
-						if (lane >= (unsigned)s) {
-							inc += o;
-						}
-					}
-					const uint32_t wtotal = __shfl_sync(0xFFFFFFFFu, inc, 31);
-					uint32_t wbase = 0;
-					if (lane == 31 && wtotal) {
-						wbase = atomicAdd(&S.n_stage, wtotal);
-					}
-					wbase = __shfl_sync(0xFFFFFFFFu, wbase, 31);
-					uint32_t my = wbase + inc - cntk;
-					if (wbase + wtotal <= BPP_STAGE) {
-						while (mask) {
-							const int k = __ffsll((long long)mask) - 1;
-							mask &= mask - 1;
-							const uint32_t e = e0 + k;
-							const uint32_t j = e < lenc ? S.ent[beg + e] : S.wide[e - lenc];
-							S.stage[my++] = make_uint2(id, S.cidx[j]);
-						}
-					} else if (wtotal) {
-						// rare: this round produced more pairs than the staging buffer holds -> straight to global
-						if (lane == 31) {
-							atomicMin(&S.stage_limit, wbase);
-						}
-						unsigned long long gb = 0;
-						if (lane == 31) {
-							gb = atomicAdd(counter, (unsigned long long)wtotal);
-						}
-						gb = __shfl_sync(0xFFFFFFFFu, gb, 31) + (inc - cntk);
-						while (mask) {
-							const int k = __ffsll((long long)mask) - 1;
-							mask &= mask - 1;
-							const uint32_t e = e0 + k;
-							const uint32_t j = e < lenc ? S.ent[beg + e] : S.wide[e - lenc];
-							if (gb < capacity) {
-								out_probe[gb] = id;
-								out_build[gb] = S.cidx[j];
-							}
-							gb++;
-						}
+					bpp_emit<MODE>(S, mlo, mhi, ep, id, out_probe, out_build, capacity, counter);
+				}
+				for (uint32_t w0 = 0; w0 < n_wide; w0 += 64) {
+					uint32_t mlo = 0, mhi = 0;
+					const uint16_t *ep = S.wide + w0;
+					if (valid) {
+						const uint32_t n = min(n_wide - w0, 64u);
+						BPP_PASS(ep, n);
 					}
 					__syncthreads();
-					const uint32_t nst = min(S.n_stage, S.stage_limit);
-					if (tid == 0) {
-						S.gbase = nst ? atomicAdd(counter, (unsigned long long)nst) : 0ull;
-					}
-					__syncthreads();
-					const unsigned long long gbase = S.gbase;
-					for (uint32_t t = tid; t < nst; t += BPP_THREADS) {
-						const uint2 p = S.stage[t];
-						if (gbase + t < capacity) {
-							out_probe[gbase + t] = p.x;
-							out_build[gbase + t] = p.y;
-						}
-					}
-					__syncthreads();
-					if (tid == 0) {
-						S.n_stage = 0;
-						S.stage_limit = 0xFFFFFFFFu;
-					}
+					bpp_emit<MODE>(S, mlo, mhi, ep, id, out_probe, out_build, capacity, counter);
 				}
 			}
 			c0 += ntry;
@@ -620,8 +727,13 @@ int sbi_flat_probe_bucketed(sb_context *ctx, const sb_flat *tree, const sb_probe
 	SB_TRY(ctx->scratch_t(n_cand ? n_cand : 1, &d_cand));
 	{
 		sb_prof_scope ps(ctx, "bp_partition");
-		k_bp_scatter<<<sb_grid(n, BPS_TILE, 2), BPS_THREADS, 0, ctx->stream>>>(a.px, a.py, n, a.index_base, d_grid,
-		                                                                     d_tab->pt_cursor, d_pxy, d_pidx);
+		static bool sattr = false;
+		if (!sattr) {
+			SB_CUDA(cudaFuncSetAttribute(k_bp_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(bps_smem)));
+			sattr = true;
+		}
+		k_bp_scatter<<<sb_grid(n, BPS_TILE, 2), BPS_THREADS, sizeof(bps_smem), ctx->stream>>>(
+		    a.px, a.py, n, a.index_base, d_grid, d_tab->pt_cursor, d_pxy, d_pidx);
 		SB_LAUNCH_CHECK(ctx);
 	}
 	{
@@ -633,18 +745,19 @@ int sbi_flat_probe_bucketed(sb_context *ctx, const sb_flat *tree, const sb_probe
 	if (n_units) {
 		static bool attr_set = false;
 		if (!attr_set) {
-			SB_CUDA(cudaFuncSetAttribute(k_bp_probe<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(bpp_smem)));
-			SB_CUDA(cudaFuncSetAttribute(k_bp_probe<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(bpp_smem)));
+			SB_CUDA(cudaFuncSetAttribute(k_bp_probe<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(bpp_smem<1>)));
+			SB_CUDA(cudaFuncSetAttribute(k_bp_probe<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+			                             (int)sizeof(bpp_smem<2>)));
 			attr_set = true;
 		}
 		const unsigned grid = (unsigned)(n_units < SB_NUM_SMS ? n_units : SB_NUM_SMS);
 		sb_prof_scope ps(ctx, "flat_probe");
 		if (mode == 1) {
-			k_bp_probe<1><<<grid, BPP_THREADS, sizeof(bpp_smem), ctx->stream>>>(
+			k_bp_probe<1><<<grid, BPP_THREADS, sizeof(bpp_smem<1>), ctx->stream>>>(
 			    tree->boxes(), tree->idx(), nullptr, -1, d_grid, d_tab, d_units, d_cand, d_pxy, d_pidx, out_probe, out_build,
 			    capacity, d_counter);
 		} else {
-			k_bp_probe<2><<<grid, BPP_THREADS, sizeof(bpp_smem), ctx->stream>>>(
+			k_bp_probe<2><<<grid, BPP_THREADS, sizeof(bpp_smem<2>), ctx->stream>>>(
 			    tree->boxes(), tree->idx(), a.build_box2d, a.pred, d_grid, d_tab, d_units, d_cand, d_pxy, d_pidx, out_probe,
 			    out_build, capacity, d_counter);
 		}
