@@ -703,6 +703,7 @@ int sbi_flat_probe_bucketed(sb_context *ctx, const sb_flat *tree, const sb_probe
 	SB_CUDA(cudaMemsetAsync(d_tab, 0, sizeof(bp_tables), ctx->stream));
 	SB_CUDA(cudaMemsetAsync(d_counter, 0, sizeof(*d_counter), ctx->stream));
 	const sb_flat_header *d_hdr = static_cast<const sb_flat_header *>(tree->buffer);
+	SB_TRACE(ctx, "bp: scratch + memsets");
 	{
 		sb_prof_scope ps(ctx, "bp_partition");
 		k_bp_grid_init<<<1, 32, 0, ctx->stream>>>(d_hdr, d_grid);
@@ -718,6 +719,7 @@ int sbi_flat_probe_bucketed(sb_context *ctx, const sb_flat *tree, const sb_probe
 		k_bp_scan<<<1, 1024, 0, ctx->stream>>>(d_tab, d_units);
 		SB_LAUNCH_CHECK(ctx);
 	}
+	SB_TRACE(ctx, "bp: hist + cand count + scan");
 	uint64_t totals[4];
 	SB_CUDA(cudaMemcpyAsync(ctx->pinned_u64, d_tab->totals, sizeof(totals), cudaMemcpyDeviceToHost, ctx->stream));
 	SB_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -742,6 +744,7 @@ int sbi_flat_probe_bucketed(sb_context *ctx, const sb_flat *tree, const sb_probe
 		                                                                d_cand);
 		SB_LAUNCH_CHECK(ctx);
 	}
+	SB_TRACE(ctx, "bp: scatter + cand fill");
 	if (n_units) {
 		static bool attr_set = false;
 		if (!attr_set) {
@@ -765,6 +768,7 @@ int sbi_flat_probe_bucketed(sb_context *ctx, const sb_flat *tree, const sb_probe
 	}
 	uint64_t c1 = 0;
 	SB_TRY(sbi_read_u64(ctx, reinterpret_cast<const uint64_t *>(d_counter), &c1));
+	SB_TRACE(ctx, "bp: probe kernel");
 	*count = c1;
 	if (n_nan && mode == 1) {
 		// NaN coordinates: Box::Intersects never rejects on a NaN axis. Such rows take the per-probe tree walk.

@@ -240,7 +240,7 @@ extern "C" void sb_rtree_destroy(sb_rtree *tree) {
 		return;
 	}
 	cudaSetDevice(tree->device);
-	cudaFree(tree->entries);
+	cudaFreeAsync(tree->entries, nullptr); // callers destroy a tree only after its work has completed
 	delete tree;
 }
 extern "C" int sb_rtree_num_levels(const sb_rtree *tree) {
@@ -304,7 +304,7 @@ extern "C" void sb_flat_destroy(sb_flat *tree) {
 	}
 	if (tree->owns && tree->buffer) {
 		cudaSetDevice(tree->device);
-		cudaFree(tree->buffer);
+		cudaFreeAsync(tree->buffer, nullptr); // callers destroy a tree only after its work has completed
 	}
 	delete tree;
 }
@@ -490,6 +490,7 @@ extern "C" int sb_join_points_boxes(sb_context *ctx, sb_mem mem, sb_predicate pr
 	if (n_boxes == 0 || n_points == 0) {
 		return finish(ctx, mem);
 	}
+	SB_TRACE(ctx, "join: begin (inputs staged)");
 	// build side: BOX_2D -> BOX_2DF (cached bbox of the envelope polygons) -> FlatRTree(node_size 32, :553)
 	float *fbox = nullptr;
 	double *box2d = nullptr;
@@ -498,7 +499,9 @@ extern "C" int sb_join_points_boxes(sb_context *ctx, sb_mem mem, sb_predicate pr
 	SB_TRY(sbi_bbox_box2d(ctx, b0, b1, b2, b3, n_boxes, fbox));
 	SB_TRY(sbi_pack_box2d(ctx, b0, b1, b2, b3, n_boxes, box2d));
 	sb_flat *tree = nullptr;
+	SB_TRACE(ctx, "join: bbox");
 	int s = sbi_flat_build(ctx, fbox, n_boxes, 32, &tree);
+	SB_TRACE(ctx, "join: tree build");
 	if (s == SB_OK) {
 		sb_probe_args a;
 		a.px = dx;
@@ -519,10 +522,12 @@ extern "C" int sb_join_points_boxes(sb_context *ctx, sb_mem mem, sb_predicate pr
 	} else {
 		cudaStreamSynchronize(ctx->stream);
 	}
+	SB_TRACE(ctx, "join: probe + copy out");
 	if (tree) {
 		cudaStreamSynchronize(ctx->stream);
 		sb_flat_destroy(tree);
 	}
+	SB_TRACE(ctx, "join: tree free");
 	return s;
 }
 

@@ -53,6 +53,7 @@ struct sb_arena {
 	};
 	std::vector<block> blocks;
 	size_t cur_block = 0, cur_off = 0, high_water = 0, used = 0;
+	cudaStream_t *stream = nullptr; // blocks come from the device's stream-ordered pool, ordered on *stream
 	int alloc(size_t bytes, void **out);
 	void reset();
 	void release();
@@ -76,6 +77,9 @@ struct sb_context {
 	// sb_context_set_option("probe_path"): 0 = auto (bulk point probes take the bucketed kernel), 1 = always the
 	// per-probe tree walk, 2 = always bucketed
 	int probe_path = 0;
+	// sb_context_set_option("trace", 1): synchronise at SB_TRACE points and print the wall time of each phase
+	int trace = 0;
+	double trace_t0 = 0;
 	// pinned staging for small host<->device transfers (counters)
 	uint64_t *pinned_u64 = nullptr;
 
@@ -96,6 +100,14 @@ struct sb_prof_scope {
 	sb_prof_scope(sb_context *c, const char *t);
 	~sb_prof_scope();
 };
+
+void sb_trace_point(sb_context *ctx, const char *what);
+#define SB_TRACE(ctx, what)                                                                                          \
+	do {                                                                                                             \
+		if ((ctx)->trace) {                                                                                          \
+			sb_trace_point(ctx, what);                                                                               \
+		}                                                                                                            \
+	} while (0)
 
 // stage helpers for SB_HOST calls
 template <class T>

@@ -20,6 +20,14 @@ extern "C" const char *sb_version(void) {
 	return "spatial_b200 0.1 (sm_100a)";
 }
 
+#include <chrono>
+void sb_trace_point(sb_context *ctx, const char *what) {
+	cudaStreamSynchronize(ctx->stream);
+	const double t = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+	fprintf(stderr, "[sb trace] %-28s +%9.3f ms\n", what, ctx->trace_t0 ? t - ctx->trace_t0 : 0.0);
+	ctx->trace_t0 = t;
+}
+
 // ---- arena --------------------------------------------------------------------------------------------------
 int sb_arena::alloc(size_t bytes, void **out) {
 	bytes = (bytes + 255) & ~(size_t)255;
@@ -42,7 +50,7 @@ int sb_arena::alloc(size_t bytes, void **out) {
 	}
 	size_t sz = bytes > ((size_t)64 << 20) ? bytes : ((size_t)64 << 20);
 	block nb;
-	cudaError_t e = cudaMalloc((void **)&nb.ptr, sz);
+	cudaError_t e = cudaMallocAsync((void **)&nb.ptr, sz, *stream);
 	if (e != cudaSuccess) {
 		sb_set_error("cudaMalloc(%zu) failed: %s", sz, cudaGetErrorString(e));
 		return SB_ERR_CUDA;
@@ -63,9 +71,9 @@ void sb_arena::reset() {
 	// coalesce: if the last call spilled over several blocks, replace them by one block of the high-water size
 	if (blocks.size() > 1) {
 		size_t want = high_water + (high_water >> 3);
-		release(); // cudaFree synchronises, so nothing in flight still uses the old blocks
+		release(); // stream-ordered free: work already enqueued on the stream still sees the old blocks
 		block nb;
-		if (cudaMalloc((void **)&nb.ptr, want) == cudaSuccess) {
+		if (cudaMallocAsync((void **)&nb.ptr, want, *stream) == cudaSuccess) {
 			nb.size = want;
 			blocks.push_back(nb);
 		} else {
@@ -79,7 +87,7 @@ void sb_arena::reset() {
 
 void sb_arena::release() {
 	for (auto &b : blocks) {
-		cudaFree(b.ptr);
+		cudaFreeAsync(b.ptr, *stream);
 	}
 	blocks.clear();
 	cur_block = 0;
@@ -109,6 +117,16 @@ extern "C" int sb_context_create(int device, sb_context **out) {
 	ctx->device = device;
 	SB_CUDA(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
 	ctx->stream = ctx->own_stream;
+	ctx->arena.stream = &ctx->stream;
+	// Device buffers (scratch arena, trees) come from the stream-ordered pool and the pool keeps what is freed:
+	// cudaMalloc/cudaFree of a few hundred MB per call cost milliseconds (measured: 3.5 -> 17 ms per index build
+	// depending on the allocator state), pool allocations microseconds.
+	{
+		cudaMemPool_t pool;
+		SB_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+		uint64_t keep = UINT64_MAX;
+		SB_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+	}
 	SB_CUDA(cudaMallocHost((void **)&ctx->pinned_u64, 64 * sizeof(uint64_t)));
 	*out = ctx;
 	return SB_OK;
@@ -147,6 +165,10 @@ extern "C" int sb_context_set_option(sb_context *ctx, const char *key, int64_t v
 	if (strcmp(key, "probe_path") == 0) {
 		SB_ARG(value >= 0 && value <= 2, "probe_path must be 0 (auto), 1 (tree walk) or 2 (bucketed)");
 		ctx->probe_path = (int)value;
+		return SB_OK;
+	}
+	if (strcmp(key, "trace") == 0) {
+		ctx->trace = (int)value;
 		return SB_OK;
 	}
 	sb_set_error("unknown option '%s'", key);

@@ -125,7 +125,7 @@ int sbi_flat_build(sb_context *ctx, const float *box4, uint32_t n, uint32_t node
 	t->h.nodes = n > 0 ? (uint32_t)nodes : 0;
 	t->bytes = sizeof(sb_flat_header) + (size_t)t->h.nodes * (sizeof(float4) + sizeof(uint32_t));
 	t->bytes = (t->bytes + 255) & ~(uint64_t)255;
-	SB_CUDA(cudaMalloc(&t->buffer, t->bytes));
+	SB_CUDA(cudaMallocAsync(&t->buffer, t->bytes, ctx->stream));
 	t->owns = true;
 	SB_CUDA(cudaMemcpyAsync(t->buffer, &t->h, sizeof(t->h), cudaMemcpyHostToDevice, ctx->stream));
 	if (n == 0) {
