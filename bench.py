@@ -205,6 +205,9 @@ def run_ours(a):
     import sb200
 
     sb = sb200.load()
+    import importlib
+
+    D = importlib.import_module("duckdb_spatial_b200.distributed")
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -258,7 +261,6 @@ def run_ours(a):
             box2d = torch.empty((B, 4), dtype=torch.float64, device=dev)
             del t0
             counts = torch.zeros(world, dtype=torch.int64, device=dev)
-            gather_p = gather_b = None
 
         def step_multi():
             # rank 0: build; everyone: receive the packed tree + the build side's exact boxes; probe own slice
@@ -280,23 +282,8 @@ def run_ours(a):
             dist.all_gather_into_tensor(counts, mine)
             total = int(counts.sum().item())
             if not a.no_gather:
-                nonlocal gather_p, gather_b
-                cl = counts.tolist()
-                if rank == 0:
-                    if gather_p is None or gather_p.numel() < total:
-                        gather_p = torch.empty(int(total * 1.05), dtype=torch.int32, device=dev)
-                        gather_b = torch.empty(int(total * 1.05), dtype=torch.int32, device=dev)
-                    ops, o = [], cl[0]
-                    gather_p[: cl[0]].copy_(out_p[: cl[0]])
-                    gather_b[: cl[0]].copy_(out_b[: cl[0]])
-                    for r in range(1, world):
-                        ops.append(dist.P2POp(dist.irecv, gather_p[o : o + cl[r]], r))
-                        ops.append(dist.P2POp(dist.irecv, gather_b[o : o + cl[r]], r))
-                        o += cl[r]
-                else:
-                    ops = [dist.P2POp(dist.isend, out_p[: cl[rank]], 0), dist.P2POp(dist.isend, out_b[: cl[rank]], 0)]
-                for w in dist.batch_isend_irecv(ops):
-                    w.wait()
+                # variable-length pair lists -> rank 0 (grouped send/recv), duckdb-spatial_b200/distributed.py
+                D.gather_pairs(out_p[: cnt.value], out_b[: cnt.value], dst=0)
             return total
 
         step = step_multi if world > 1 else step_single
