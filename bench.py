@@ -39,7 +39,9 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-index", action="store_true", help="skip the CREATE INDEX (STR) side measurement")
-    ap.add_argument("--no-gather", action="store_true", help="N>1: leave the pair lists sharded")
+    ap.add_argument("--gather", action="store_true",
+                    help="N>1: also move every rank's pair list to rank 0 (bounded by rank 0's NVLink ingest, "
+                         "8 B/pair: see DESIGN.md section 7). Default: pair lists stay sharded, counts are all-gathered")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     return ap.parse_args()
 
@@ -281,7 +283,7 @@ def run_ours(a):
             mine = torch.tensor([cnt.value], dtype=torch.int64, device=dev)
             dist.all_gather_into_tensor(counts, mine)
             total = int(counts.sum().item())
-            if not a.no_gather:
+            if a.gather:
                 # variable-length pair lists -> rank 0 (grouped send/recv), duckdb-spatial_b200/distributed.py
                 D.gather_pairs(out_p[: cnt.value], out_b[: cnt.value], dst=0)
             return total
@@ -349,7 +351,7 @@ def run_ours(a):
             "config": {"workload": workload_name(a), "points_per_gpu": P, "boxes": B,
                        "l2": "inputs (%.1f GB of coordinates per step) exceed the 126 MB L2: no flush needed" % (16e-9 * P),
                        "parallelism": "tree broadcast + probe sharding x%d" % world if world > 1 else "single GPU",
-                       "gather_pairs": (world > 1 and not a.no_gather)},
+                       "gather_pairs": (world > 1 and a.gather)},
             "pairs_per_step": total_pairs // a.steps, "probes_per_s": P * world * a.steps / (ms / 1e3),
             "gpu_launches": int(launches), "roofline": roofline, "clocks": clk,
         }

@@ -339,9 +339,12 @@ __global__ void __launch_bounds__(1024) k_bp_scan(bp_tables *__restrict__ T, bp_
 #define BPP_K 0x00010001u
 
 // MODE 1: candidate semantics (float boxes, Box::Intersects). MODE 2: fused exact predicate on the build's BOX_2D.
+#define BPP_GROUPS 4                      // independent 256-thread groups per CTA (named barriers 1..4)
+#define BPP_GTHREADS (BPP_THREADS / BPP_GROUPS)
 template <int MODE>
 struct bpp_smem {
-	static constexpr int STAGE = MODE == 1 ? 9216 : 11264; // pairs staged per round before the coalesced flush
+	// pairs staged per group and round before the coalesced flush (a round = 256 points, ~2200 pairs at C3)
+	static constexpr int STAGE = MODE == 1 ? 2304 : 2816;
 	uint2 qbox[BPP_CMAX];     // x = (ly0 << 16) | lx0, y = ((ly1 << 16) | lx1) | BPP_C
 	uint32_t cidx[BPP_CMAX];  // build-side index (FlatRTree idx_array value)
 	uint32_t cpos[MODE == 1 ? BPP_CMAX : 1]; // position in the tree's leaf level (float box for the tie test)
@@ -349,11 +352,27 @@ struct bpp_smem {
 	uint16_t off[BP_NB + 8];  // CSR offsets
 	uint16_t ent[BPP_EMAX];   // CSR entries: staged-entry numbers
 	uint16_t wide[BPP_WMAX];
-	uint2 stage[STAGE];
+	uint32_t stage_p[BPP_GROUPS][STAGE]; // staged pairs, structure of arrays: probe ids / build ids
+	uint32_t stage_b[BPP_GROUPS][STAGE];
 	uint32_t scan[32];
-	uint32_t unit, n_ent, n_wide, n_stage, stage_limit;
-	unsigned long long gbase;
+	uint32_t unit, n_ent, n_wide;
+	uint32_t n_stage[BPP_GROUPS], stage_limit[BPP_GROUPS];
+	unsigned long long gbase[BPP_GROUPS];
 };
+
+// barriers of one 256-thread group: the four groups of a CTA stream their points independently, so that one group's
+// flush (global atomic round trip + stores) overlaps the other groups' tests
+__device__ __forceinline__ void bpp_gsync(unsigned gid) {
+	asm volatile("bar.sync %0, %1;" ::"r"(gid + 1), "n"(BPP_GTHREADS) : "memory");
+}
+__device__ __forceinline__ bool bpp_gor(unsigned gid, bool p) {
+	unsigned r;
+	asm volatile("{\n\t.reg .pred q, r;\n\tsetp.ne.u32 q, %2, 0;\n\tbar.red.or.pred r, %1, %3, q;\n\tselp.u32 %0, 1, 0, r;\n\t}"
+	             : "=r"(r)
+	             : "r"(gid + 1), "r"((unsigned)p), "n"(BPP_GTHREADS)
+	             : "memory");
+	return r != 0;
+}
 
 template <int MODE>
 __device__ __forceinline__ bool bp_exact(double x, double y, uint32_t pos, uint32_t bi, const float4 *__restrict__ boxes,
@@ -384,16 +403,17 @@ __device__ __forceinline__ bool bp_exact(double x, double y, uint32_t pos, uint3
 		}                                                                                                            \
 	} while (0)
 
-// Flush protocol of one pass: every thread holds a 64-bit hit mask over its entry list `ep`. Warp scan of the hit
-// counts -> one shared atomic per warp reserves staging space -> pairs are written to the staging buffer ->
-// one global atomic per CTA reserves output space -> coalesced copy-out. A warp whose pairs do not fit the
-// staging buffer (dense inputs) writes them straight to global memory.
+// Flush protocol of one pass (per 256-thread group): every thread holds a 64-bit hit mask over its entry list `ep`.
+// Warp scan of the hit counts -> one shared atomic per warp reserves staging space -> pairs go to the group's staging
+// arrays -> one global atomic per group reserves output space -> copy-out with 16-byte stores. A warp whose pairs do
+// not fit the staging buffer (dense inputs) writes them straight to global memory.
 template <int MODE>
-__device__ __forceinline__ void bpp_emit(bpp_smem<MODE> &S, uint32_t mlo, uint32_t mhi, const uint16_t *ep, uint32_t id,
-                                         uint32_t *__restrict__ out_probe, uint32_t *__restrict__ out_build,
+__device__ __forceinline__ void bpp_emit(bpp_smem<MODE> &S, unsigned gid, uint32_t mlo, uint32_t mhi, const uint16_t *ep,
+                                         uint32_t id, uint32_t *__restrict__ out_probe, uint32_t *__restrict__ out_build,
                                          uint64_t capacity, unsigned long long *__restrict__ counter) {
 	constexpr uint32_t STAGE = bpp_smem<MODE>::STAGE;
-	const unsigned tid = threadIdx.x, lane = sb_lane();
+	const unsigned gtid = threadIdx.x & (BPP_GTHREADS - 1), lane = sb_lane();
+	uint32_t *sp = S.stage_p[gid], *sb = S.stage_b[gid];
 	const uint32_t cntk = (uint32_t)(__popc(mlo) + __popc(mhi));
 	uint32_t inc = cntk;
 #pragma unroll
@@ -406,24 +426,28 @@ __device__ __forceinline__ void bpp_emit(bpp_smem<MODE> &S, uint32_t mlo, uint32
 	const uint32_t wtotal = __shfl_sync(0xFFFFFFFFu, inc, 31);
 	uint32_t wbase = 0;
 	if (lane == 31 && wtotal) {
-		wbase = atomicAdd(&S.n_stage, wtotal);
+		wbase = atomicAdd(&S.n_stage[gid], wtotal);
 	}
 	wbase = __shfl_sync(0xFFFFFFFFu, wbase, 31);
 	if (wbase + wtotal <= STAGE) {
-		uint2 *dst = S.stage + wbase + (inc - cntk);
+		uint32_t d = wbase + (inc - cntk);
 		while (mlo) {
 			const int k = 31 - __clz(mlo);
 			mlo ^= 1u << k;
-			*dst++ = make_uint2(id, S.cidx[ep[k]]);
+			sp[d] = id;
+			sb[d] = S.cidx[ep[k]];
+			d++;
 		}
 		while (mhi) {
 			const int k = 31 - __clz(mhi);
 			mhi ^= 1u << k;
-			*dst++ = make_uint2(id, S.cidx[ep[32 + k]]);
+			sp[d] = id;
+			sb[d] = S.cidx[ep[32 + k]];
+			d++;
 		}
 	} else if (wtotal) {
 		if (lane == 31) {
-			atomicMin(&S.stage_limit, wbase);
+			atomicMin(&S.stage_limit[gid], wbase);
 		}
 		unsigned long long gb = 0;
 		if (lane == 31) {
@@ -447,24 +471,45 @@ __device__ __forceinline__ void bpp_emit(bpp_smem<MODE> &S, uint32_t mlo, uint32
 			gb++;
 		}
 	}
-	__syncthreads();
-	const uint32_t nst = min(S.n_stage, S.stage_limit);
-	if (tid == 0) {
-		S.gbase = nst ? atomicAdd(counter, (unsigned long long)nst) : 0ull;
+	bpp_gsync(gid);
+	const uint32_t nst = min(S.n_stage[gid], S.stage_limit[gid]);
+	if (gtid == 0) {
+		S.gbase[gid] = nst ? atomicAdd(counter, (unsigned long long)nst) : 0ull;
 	}
-	__syncthreads();
-	const unsigned long long gbase = S.gbase;
-	for (uint32_t t = tid; t < nst; t += BPP_THREADS) {
-		const uint2 p = S.stage[t];
-		if (gbase + t < capacity) {
-			out_probe[gbase + t] = p.x;
-			out_build[gbase + t] = p.y;
+	bpp_gsync(gid);
+	const unsigned long long gbase = S.gbase[gid];
+	uint32_t *op = out_probe + gbase, *ob = out_build + gbase;
+	// head: up to the first 16-byte boundary of the destination (both columns must agree), then 16-byte stores
+	const uint32_t ha = (uint32_t)((16u - ((uintptr_t)op & 15u)) & 15u) >> 2, hb = (uint32_t)((16u - ((uintptr_t)ob & 15u)) & 15u) >> 2;
+	if (ha == hb && gbase + nst <= capacity) {
+		const uint32_t head = min(ha, nst);
+		if (gtid < head) {
+			op[gtid] = sp[gtid];
+			ob[gtid] = sb[gtid];
+		}
+		const uint32_t quads = (nst - head) >> 2;
+		for (uint32_t t = gtid; t < quads; t += BPP_GTHREADS) {
+			const uint32_t o = head + 4 * t;
+			*reinterpret_cast<uint4 *>(op + o) = make_uint4(sp[o], sp[o + 1], sp[o + 2], sp[o + 3]);
+			*reinterpret_cast<uint4 *>(ob + o) = make_uint4(sb[o], sb[o + 1], sb[o + 2], sb[o + 3]);
+		}
+		const uint32_t done = head + 4 * quads;
+		if (gtid < nst - done) {
+			op[done + gtid] = sp[done + gtid];
+			ob[done + gtid] = sb[done + gtid];
+		}
+	} else {
+		for (uint32_t t = gtid; t < nst; t += BPP_GTHREADS) {
+			if (gbase + t < capacity) {
+				op[t] = sp[t];
+				ob[t] = sb[t];
+			}
 		}
 	}
-	__syncthreads();
-	if (tid == 0) {
-		S.n_stage = 0;
-		S.stage_limit = 0xFFFFFFFFu;
+	bpp_gsync(gid);
+	if (gtid == 0) {
+		S.n_stage[gid] = 0;
+		S.stage_limit[gid] = 0xFFFFFFFFu;
 	}
 }
 
@@ -539,8 +584,10 @@ __global__ void __launch_bounds__(BPP_THREADS, 1)
 				if (tid == 0) {
 					S.n_ent = 0;
 					S.n_wide = 0;
-					S.n_stage = 0;
-					S.stage_limit = 0xFFFFFFFFu;
+				}
+				if (tid < BPP_GROUPS) {
+					S.n_stage[tid] = 0;
+					S.stage_limit[tid] = 0xFFFFFFFFu;
 				}
 				S.cnt[tid] = 0; // BPP_THREADS == BP_NB
 				__syncthreads();
@@ -623,9 +670,10 @@ __global__ void __launch_bounds__(BPP_THREADS, 1)
 			__syncthreads();
 			const uint32_t n_wide = S.n_wide;
 
-			// ---- (d) stream the unit's points, one per thread and round ----
-			for (uint32_t p0 = unit.pbeg; p0 < unit.pend; p0 += BPP_THREADS) {
-				const uint32_t i = p0 + tid;
+			// ---- (d) stream the unit's points: each 256-thread group takes every fourth round of 256 points ----
+			const unsigned gid = tid / BPP_GTHREADS, gtid = tid & (BPP_GTHREADS - 1);
+			for (uint32_t p0 = unit.pbeg + gid * BPP_GTHREADS; p0 < unit.pend; p0 += BPP_THREADS) {
+				const uint32_t i = p0 + gtid;
 				const bool valid = i < unit.pend;
 				double x = 0, y = 0;
 				uint32_t id = 0, PqC = BPP_C, Pq = 0, beg = 0, lenc = 0;
@@ -640,14 +688,14 @@ __global__ void __launch_bounds__(BPP_THREADS, 1)
 					beg = S.off[sc];
 					lenc = S.off[sc + 1] - beg;
 				}
-				for (uint32_t e0 = 0; __syncthreads_or(lenc > e0); e0 += 64) {
+				for (uint32_t e0 = 0; bpp_gor(gid, lenc > e0); e0 += 64) {
 					uint32_t mlo = 0, mhi = 0;
 					const uint16_t *ep = S.ent + beg + e0;
 					if (lenc > e0) {
 						const uint32_t n = min(lenc - e0, 64u);
 						BPP_PASS(ep, n);
 					}
-					bpp_emit<MODE>(S, mlo, mhi, ep, id, out_probe, out_build, capacity, counter);
+					bpp_emit<MODE>(S, gid, mlo, mhi, ep, id, out_probe, out_build, capacity, counter);
 				}
 				for (uint32_t w0 = 0; w0 < n_wide; w0 += 64) {
 					uint32_t mlo = 0, mhi = 0;
@@ -656,8 +704,8 @@ __global__ void __launch_bounds__(BPP_THREADS, 1)
 						const uint32_t n = min(n_wide - w0, 64u);
 						BPP_PASS(ep, n);
 					}
-					__syncthreads();
-					bpp_emit<MODE>(S, mlo, mhi, ep, id, out_probe, out_build, capacity, counter);
+					bpp_gsync(gid);
+					bpp_emit<MODE>(S, gid, mlo, mhi, ep, id, out_probe, out_build, capacity, counter);
 				}
 			}
 			c0 += ntry;
