@@ -71,7 +71,7 @@ __device__ __forceinline__ int bp_bucket(double x, double y, const bp_grid &g) {
 #define BPH_THREADS 512
 __global__ void __launch_bounds__(BPH_THREADS) k_bp_hist(const double *__restrict__ px, const double *__restrict__ py,
                                                          uint64_t n, const bp_grid *__restrict__ gp,
-                                                         uint32_t *__restrict__ hist) {
+                                                         uint32_t *__restrict__ hist, uint32_t *__restrict__ fine) {
 	__shared__ uint32_t s_hist[BP_NB + 1];
 	for (int i = threadIdx.x; i <= BP_NB; i += BPH_THREADS) {
 		s_hist[i] = 0;
@@ -80,9 +80,14 @@ __global__ void __launch_bounds__(BPH_THREADS) k_bp_hist(const double *__restric
 	__syncthreads();
 	const uint64_t stride = (uint64_t)gridDim.x * BPH_THREADS;
 	for (uint64_t i = (uint64_t)blockIdx.x * BPH_THREADS + threadIdx.x; i < n; i += stride) {
-		const int b = bp_bucket(px[i], py[i], g);
+		const double x = px[i], y = py[i];
+		const int b = bp_bucket(x, y, g);
 		if (b >= 0) {
 			atomicAdd(&s_hist[b], 1u);
+			if (fine && b < BP_NB) {
+				const int qx = bp_q(x, g.minx, g.sx), qy = bp_q(y, g.miny, g.sy);
+				atomicAdd(&fine[(b << 10) | (((qy >> 10) & 31) << 5) | ((qx >> 10) & 31)], 1u);
+			}
 		}
 	}
 	__syncthreads();
@@ -741,6 +746,7 @@ int sbi_flat_probe_bucketed(sb_context *ctx, const sb_flat *tree, const sb_probe
 	double2 *d_pxy = nullptr;
 	uint32_t *d_pidx = nullptr, *d_cand = nullptr;
 	unsigned long long *d_counter = nullptr;
+	uint32_t *d_fine = nullptr; // (bucket, sub-cell) histogram for a second partition level: measured +0.7 ms, unused
 	const uint64_t max_units = n / BP_SLICE + BP_NB + 1;
 	SB_TRY(ctx->scratch_t(1, &d_grid));
 	SB_TRY(ctx->scratch_t(1, &d_tab));
@@ -756,7 +762,7 @@ int sbi_flat_probe_bucketed(sb_context *ctx, const sb_flat *tree, const sb_probe
 		sb_prof_scope ps(ctx, "bp_partition");
 		k_bp_grid_init<<<1, 32, 0, ctx->stream>>>(d_hdr, d_grid);
 		SB_LAUNCH_CHECK(ctx);
-		k_bp_hist<<<sb_grid(n, BPH_THREADS * 8, 4), BPH_THREADS, 0, ctx->stream>>>(a.px, a.py, n, d_grid, d_tab->pt_hist);
+		k_bp_hist<<<sb_grid(n, BPH_THREADS * 8, 4), BPH_THREADS, 0, ctx->stream>>>(a.px, a.py, n, d_grid, d_tab->pt_hist, d_fine);
 		SB_LAUNCH_CHECK(ctx);
 	}
 	{

@@ -469,6 +469,120 @@ extern "C" int sb_distance_points(sb_context *ctx, sb_mem mem, const double *ax,
 	return finish(ctx, mem);
 }
 
+// Host-pointer join of a large probe column: the probe column is streamed through the device in chunks so that the
+// H2D copy of chunk k+1, the probe of chunk k and the D2H copy of chunk k-1's pairs overlap (three streams, PCIe is
+// full duplex). The call is bound by the larger of the two copy directions instead of their sum plus the kernels.
+static int join_points_boxes_pipelined(sb_context *ctx, sb_predicate pred, const double *px, const double *py,
+                                       uint64_t n_points, const sb_flat *tree, const double4 *box2d, uint32_t n_boxes,
+                                       uint32_t *out_probe, uint32_t *out_build, uint64_t capacity, uint64_t *count) {
+	const uint64_t chunk = ctx->pipe_chunk;
+	// a chunk's pairs must fit one output slot; a probe row pairs with at most n_boxes build rows. When a chunk
+	// overflows its slot it is split (below), so any positive slot size >= n_boxes terminates.
+	uint64_t slot_cap = 12 * chunk;
+	if (slot_cap < n_boxes) {
+		slot_cap = n_boxes;
+	}
+	double *dx[2], *dy[2];
+	uint32_t *dp[2], *db[2];
+	cudaEvent_t h2d_done[2], d2h_done[2], probe_done[2];
+	for (int k = 0; k < 2; k++) {
+		SB_TRY(ctx->scratch_t(chunk, &dx[k]));
+		SB_TRY(ctx->scratch_t(chunk, &dy[k]));
+		SB_TRY(ctx->scratch_t(slot_cap, &dp[k]));
+		SB_TRY(ctx->scratch_t(slot_cap, &db[k]));
+		SB_CUDA(cudaEventCreateWithFlags(&h2d_done[k], cudaEventDisableTiming));
+		SB_CUDA(cudaEventCreateWithFlags(&d2h_done[k], cudaEventDisableTiming));
+		SB_CUDA(cudaEventCreateWithFlags(&probe_done[k], cudaEventDisableTiming));
+	}
+	// the slots were just carved from the arena on ctx->stream: the side streams may touch them after this point
+	SB_CUDA(cudaEventRecord(probe_done[0], ctx->stream));
+	SB_CUDA(cudaStreamWaitEvent(ctx->h2d_stream, probe_done[0], 0));
+	SB_CUDA(cudaStreamWaitEvent(ctx->d2h_stream, probe_done[0], 0));
+	const sb_arena::mark_t mark = ctx->arena.mark();
+	int status = SB_OK;
+	uint64_t total = 0;
+	const uint64_t nchunks = (n_points + chunk - 1) / chunk;
+	auto issue_h2d = [&](uint64_t c) -> int {
+		const int slot = (int)(c & 1);
+		const uint64_t beg = c * chunk, len = (n_points - beg < chunk) ? n_points - beg : chunk;
+		// the slot's previous occupant (chunk c-2) must have been probed
+		SB_CUDA(cudaStreamWaitEvent(ctx->h2d_stream, probe_done[slot], 0));
+		SB_CUDA(cudaMemcpyAsync(dx[slot], px + beg, len * sizeof(double), cudaMemcpyHostToDevice, ctx->h2d_stream));
+		SB_CUDA(cudaMemcpyAsync(dy[slot], py + beg, len * sizeof(double), cudaMemcpyHostToDevice, ctx->h2d_stream));
+		SB_CUDA(cudaEventRecord(h2d_done[slot], ctx->h2d_stream));
+		return SB_OK;
+	};
+	if (nchunks) {
+		status = issue_h2d(0);
+	}
+	for (uint64_t c = 0; c < nchunks && status == SB_OK; c++) {
+		const int slot = (int)(c & 1);
+		const uint64_t beg = c * chunk, len = (n_points - beg < chunk) ? n_points - beg : chunk;
+		if (c + 1 < nchunks) {
+			status = issue_h2d(c + 1);
+			if (status != SB_OK) {
+				break;
+			}
+		}
+		SB_CUDA(cudaStreamWaitEvent(ctx->stream, h2d_done[slot], 0));
+		SB_CUDA(cudaStreamWaitEvent(ctx->stream, d2h_done[slot], 0)); // pairs of chunk c-2 have left the slot
+		// probe the chunk; split it when its pairs do not fit the slot
+		uint64_t done = 0;
+		uint64_t piece = len;
+		while (done < len && status == SB_OK) {
+			if (piece > len - done) {
+				piece = len - done;
+			}
+			sb_probe_args a;
+			a.px = dx[slot] + done;
+			a.py = dy[slot] + done;
+			a.m = piece;
+			a.index_base = (uint32_t)(beg + done);
+			a.build_box2d = box2d;
+			a.pred = (int)pred;
+			uint64_t got = 0;
+			ctx->arena.rewind(mark);
+			int s = sbi_flat_probe(ctx, tree, a, dp[slot], db[slot], slot_cap, &got);
+			if (s == SB_ERR_CAPACITY && piece > 1) {
+				piece = (piece + 1) / 2;
+				continue;
+			}
+			if (s != SB_OK) {
+				status = s;
+				break;
+			}
+			// sbi_flat_probe returned => the pairs are complete in the slot (it synchronises to read the count)
+			if (total + got <= capacity) {
+				SB_CUDA(cudaMemcpyAsync(out_probe + total, dp[slot], got * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->d2h_stream));
+				SB_CUDA(cudaMemcpyAsync(out_build + total, db[slot], got * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->d2h_stream));
+			}
+			total += got;
+			done += piece;
+			if (done < len) {
+				// the same slot is written again: wait for this piece's copy-out
+				SB_CUDA(cudaEventRecord(d2h_done[slot], ctx->d2h_stream));
+				SB_CUDA(cudaStreamWaitEvent(ctx->stream, d2h_done[slot], 0));
+			}
+		}
+		SB_CUDA(cudaEventRecord(d2h_done[slot], ctx->d2h_stream));
+		SB_CUDA(cudaEventRecord(probe_done[slot], ctx->stream));
+	}
+	cudaStreamSynchronize(ctx->h2d_stream);
+	cudaStreamSynchronize(ctx->d2h_stream);
+	cudaStreamSynchronize(ctx->stream);
+	for (int k = 0; k < 2; k++) {
+		cudaEventDestroy(h2d_done[k]);
+		cudaEventDestroy(d2h_done[k]);
+		cudaEventDestroy(probe_done[k]);
+	}
+	*count = total;
+	if (status == SB_OK && total > capacity) {
+		sb_set_error("join: %llu pairs, capacity %llu", (unsigned long long)total, (unsigned long long)capacity);
+		return SB_ERR_CAPACITY;
+	}
+	return status;
+}
+
 // ---- whole joins -------------------------------------------------------------------------------------------------
 extern "C" int sb_join_points_boxes(sb_context *ctx, sb_mem mem, sb_predicate pred, const double *px, const double *py,
                                     uint64_t n_points, const double *bmin_x, const double *bmin_y,
@@ -477,18 +591,21 @@ extern "C" int sb_join_points_boxes(sb_context *ctx, sb_mem mem, sb_predicate pr
 	SB_BEGIN(ctx);
 	SB_ARG(count != nullptr, "count");
 	*count = 0;
-	const double *dx, *dy, *b0, *b1, *b2, *b3;
-	SB_TRY(sb_to_device(ctx, mem, px, n_points, &dx));
-	SB_TRY(sb_to_device(ctx, mem, py, n_points, &dy));
+	if (n_boxes == 0 || n_points == 0) {
+		return SB_OK;
+	}
+	const bool pipelined = mem == SB_HOST && n_points >= 2ull * ctx->pipe_chunk;
+	const double *dx = nullptr, *dy = nullptr, *b0, *b1, *b2, *b3;
 	SB_TRY(sb_to_device(ctx, mem, bmin_x, (uint64_t)n_boxes, &b0));
 	SB_TRY(sb_to_device(ctx, mem, bmin_y, (uint64_t)n_boxes, &b1));
 	SB_TRY(sb_to_device(ctx, mem, bmax_x, (uint64_t)n_boxes, &b2));
 	SB_TRY(sb_to_device(ctx, mem, bmax_y, (uint64_t)n_boxes, &b3));
-	uint32_t *dop, *dob;
-	SB_TRY(sb_out_buffer(ctx, mem, out_probe, capacity, &dop));
-	SB_TRY(sb_out_buffer(ctx, mem, out_build, capacity, &dob));
-	if (n_boxes == 0 || n_points == 0) {
-		return finish(ctx, mem);
+	uint32_t *dop = nullptr, *dob = nullptr;
+	if (!pipelined) {
+		SB_TRY(sb_to_device(ctx, mem, px, n_points, &dx));
+		SB_TRY(sb_to_device(ctx, mem, py, n_points, &dy));
+		SB_TRY(sb_out_buffer(ctx, mem, out_probe, capacity, &dop));
+		SB_TRY(sb_out_buffer(ctx, mem, out_build, capacity, &dob));
 	}
 	SB_TRACE(ctx, "join: begin (inputs staged)");
 	// build side: BOX_2D -> BOX_2DF (cached bbox of the envelope polygons) -> FlatRTree(node_size 32, :553)
@@ -502,7 +619,10 @@ extern "C" int sb_join_points_boxes(sb_context *ctx, sb_mem mem, sb_predicate pr
 	SB_TRACE(ctx, "join: bbox");
 	int s = sbi_flat_build(ctx, fbox, n_boxes, 32, &tree);
 	SB_TRACE(ctx, "join: tree build");
-	if (s == SB_OK) {
+	if (s == SB_OK && pipelined) {
+		s = join_points_boxes_pipelined(ctx, pred, px, py, n_points, tree, reinterpret_cast<const double4 *>(box2d),
+		                                n_boxes, out_probe, out_build, capacity, count);
+	} else if (s == SB_OK) {
 		sb_probe_args a;
 		a.px = dx;
 		a.py = dy;
@@ -510,17 +630,17 @@ extern "C" int sb_join_points_boxes(sb_context *ctx, sb_mem mem, sb_predicate pr
 		a.build_box2d = reinterpret_cast<const double4 *>(box2d);
 		a.pred = (int)pred;
 		s = sbi_flat_probe(ctx, tree, a, dop, dob, capacity, count);
-	}
-	if (s == SB_OK) {
-		s = sb_to_host(ctx, mem, out_probe, dop, *count);
-	}
-	if (s == SB_OK) {
-		s = sb_to_host(ctx, mem, out_build, dob, *count);
-	}
-	if (s == SB_OK) {
-		s = finish(ctx, mem);
-	} else {
-		cudaStreamSynchronize(ctx->stream);
+		if (s == SB_OK) {
+			s = sb_to_host(ctx, mem, out_probe, dop, *count);
+		}
+		if (s == SB_OK) {
+			s = sb_to_host(ctx, mem, out_build, dob, *count);
+		}
+		if (s == SB_OK) {
+			s = finish(ctx, mem);
+		} else {
+			cudaStreamSynchronize(ctx->stream);
+		}
 	}
 	SB_TRACE(ctx, "join: probe + copy out");
 	if (tree) {

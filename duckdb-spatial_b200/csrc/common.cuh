@@ -55,6 +55,16 @@ struct sb_arena {
 	size_t cur_block = 0, cur_off = 0, high_water = 0, used = 0;
 	cudaStream_t *stream = nullptr; // blocks come from the device's stream-ordered pool, ordered on *stream
 	int alloc(size_t bytes, void **out);
+	// mark / rewind: give back everything allocated after the mark (same stream => safe to reuse in stream order)
+	struct mark_t {
+		size_t cur_block, cur_off, used;
+	};
+	mark_t mark() const {
+		return {cur_block, cur_off, used};
+	}
+	void rewind(const mark_t &m) {
+		cur_block = m.cur_block, cur_off = m.cur_off, used = m.used;
+	}
 	void reset();
 	void release();
 };
@@ -80,6 +90,9 @@ struct sb_context {
 	// sb_context_set_option("trace", 1): synchronise at SB_TRACE points and print the wall time of each phase
 	int trace = 0;
 	double trace_t0 = 0;
+	// second and third stream of the host-pointer join pipeline (H2D of the next chunk / D2H of the previous one)
+	cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
+	uint64_t pipe_chunk = 16u << 20; // probe rows per chunk of that pipeline (option "pipe_chunk")
 	// pinned staging for small host<->device transfers (counters)
 	uint64_t *pinned_u64 = nullptr;
 

@@ -117,6 +117,8 @@ extern "C" int sb_context_create(int device, sb_context **out) {
 	ctx->device = device;
 	SB_CUDA(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
 	ctx->stream = ctx->own_stream;
+	SB_CUDA(cudaStreamCreateWithFlags(&ctx->h2d_stream, cudaStreamNonBlocking));
+	SB_CUDA(cudaStreamCreateWithFlags(&ctx->d2h_stream, cudaStreamNonBlocking));
 	ctx->arena.stream = &ctx->stream;
 	// Device buffers (scratch arena, trees) come from the stream-ordered pool and the pool keeps what is freed:
 	// cudaMalloc/cudaFree of a few hundred MB per call cost milliseconds (measured: 3.5 -> 17 ms per index build
@@ -149,6 +151,8 @@ extern "C" void sb_context_destroy(sb_context *ctx) {
 	}
 	ctx->arena.release();
 	cudaFreeHost(ctx->pinned_u64);
+	cudaStreamDestroy(ctx->h2d_stream);
+	cudaStreamDestroy(ctx->d2h_stream);
 	cudaStreamDestroy(ctx->own_stream);
 	delete ctx;
 }
@@ -165,6 +169,11 @@ extern "C" int sb_context_set_option(sb_context *ctx, const char *key, int64_t v
 	if (strcmp(key, "probe_path") == 0) {
 		SB_ARG(value >= 0 && value <= 2, "probe_path must be 0 (auto), 1 (tree walk) or 2 (bucketed)");
 		ctx->probe_path = (int)value;
+		return SB_OK;
+	}
+	if (strcmp(key, "pipe_chunk") == 0) {
+		SB_ARG(value >= 1024, "pipe_chunk must be >= 1024 rows");
+		ctx->pipe_chunk = (uint64_t)value;
 		return SB_OK;
 	}
 	if (strcmp(key, "trace") == 0) {

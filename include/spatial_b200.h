@@ -59,7 +59,9 @@ SB_API void sb_context_destroy(sb_context *ctx);
 SB_API int sb_context_set_stream(sb_context *ctx, void *cuda_stream);
 SB_API int sb_context_sync(sb_context *ctx);
 /* tuning / test knobs. "probe_path": 0 = auto, 1 = per-probe tree walk only, 2 = bucketed bulk probe only
- * (both produce the same pair set; the parity tests run every join through both). */
+ * (both produce the same pair set; the parity tests run every join through both). "pipe_chunk": probe rows per
+ * chunk of the host-pointer join pipeline (default 16 Mi; calls with >= 2 chunks overlap H2D / probe / D2H).
+ * "trace": 1 = print per-phase wall times to stderr (synchronises at every phase). */
 SB_API int sb_context_set_option(sb_context *ctx, const char *key, int64_t value);
 /* number of kernels this context has launched so far (bench.py's gpu_launches) */
 SB_API uint64_t sb_context_launches(const sb_context *ctx);

@@ -183,3 +183,39 @@ def test_index_base_and_capacity(ctx, sb, O):
     assert (sort_pairs(p - 1000000, bb) == sort_pairs(exp[:, 0], exp[:, 1])).all()
     assert rc == sb.capi.ERR_CAPACITY and cnt.value == len(exp)
     assert (op[1000:] == 0xFFFFFFFF).all() and (ob[1000:] == 0xFFFFFFFF).all()
+
+
+def test_host_pipeline_chunks(ctx, O):
+    # host-pointer join streamed in chunks (H2D / probe / D2H overlapped); small chunks force many iterations, the
+    # dense cluster overflows an output slot (12 pairs per chunk row) and splits the chunk
+    rng = np.random.default_rng(31)
+    m = 3000
+    cx, cy = rng.uniform(0, 1000, m), rng.uniform(0, 1000, m)
+    w = rng.uniform(1, 12, m)
+    cx[:200], cy[:200], w[:200] = 300.0, 300.0, 40.0
+    n = 150001
+    px, py = rng.uniform(0, 1000, n), rng.uniform(0, 1000, n)
+    px[20000:24000] = rng.uniform(280, 320, 4000)
+    py[20000:24000] = rng.uniform(280, 320, 4000)
+    b = [cx - w, cy - w, cx + w, cy + w]
+    exp, _ = O.join_points_boxes(px, py, *b, pred=0)
+    e = sort_pairs(exp[:, 0], exp[:, 1])
+    ctx.set_option("pipe_chunk", 4096)
+    try:
+        for path in (1, 2):
+            ctx.set_option("probe_path", path)
+            p, bb = ctx.spatial_join_points_boxes(px, py, *b, capacity=len(e) + 5)
+            g = sort_pairs(p, bb)
+            assert g.shape == e.shape and (g == e).all()
+        # capacity too small: needed count comes back
+        import ctypes as C
+        op = np.zeros(1000, np.uint32)
+        cnt = C.c_uint64(0)
+        args = [v.ctypes.data for v in (px, py)] + [n] + [np.ascontiguousarray(v).ctypes.data for v in b]
+        bb4 = [np.ascontiguousarray(v) for v in b]
+        rc = ctx.L.sb_join_points_boxes(ctx.h, 0, 0, px.ctypes.data, py.ctypes.data, n, *[v.ctypes.data for v in bb4], m,
+                                        op.ctypes.data, op.ctypes.data, 1000, C.byref(cnt))
+        assert rc == -3 and cnt.value == len(e)
+    finally:
+        ctx.set_option("probe_path", 0)
+        ctx.set_option("pipe_chunk", 16 << 20)
