@@ -357,8 +357,10 @@ struct bpp_smem {
 	uint16_t off[BP_NB + 8];  // CSR offsets
 	uint16_t ent[BPP_EMAX];   // CSR entries: staged-entry numbers
 	uint16_t wide[BPP_WMAX];
-	uint32_t stage_p[BPP_GROUPS][STAGE]; // staged pairs, structure of arrays: probe ids / build ids
-	uint32_t stage_b[BPP_GROUPS][STAGE];
+	// staged pairs, 4 bytes each: (thread of the group << 16) | staged-entry number; the copy-out expands them
+	// through rid[] (probe row id of each thread in this round) and cidx[]
+	uint32_t stage[BPP_GROUPS][STAGE];
+	uint32_t rid[BPP_GROUPS][BPP_GTHREADS];
 	uint32_t scan[32];
 	uint32_t unit, n_ent, n_wide;
 	uint32_t n_stage[BPP_GROUPS], stage_limit[BPP_GROUPS];
@@ -418,7 +420,8 @@ __device__ __forceinline__ void bpp_emit(bpp_smem<MODE> &S, unsigned gid, uint32
                                          uint64_t capacity, unsigned long long *__restrict__ counter) {
 	constexpr uint32_t STAGE = bpp_smem<MODE>::STAGE;
 	const unsigned gtid = threadIdx.x & (BPP_GTHREADS - 1), lane = sb_lane();
-	uint32_t *sp = S.stage_p[gid], *sb = S.stage_b[gid];
+	uint32_t *st = S.stage[gid];
+	const uint32_t tag = gtid << 16;
 	const uint32_t cntk = (uint32_t)(__popc(mlo) + __popc(mhi));
 	uint32_t inc = cntk;
 #pragma unroll
@@ -439,16 +442,12 @@ __device__ __forceinline__ void bpp_emit(bpp_smem<MODE> &S, unsigned gid, uint32
 		while (mlo) {
 			const int k = 31 - __clz(mlo);
 			mlo ^= 1u << k;
-			sp[d] = id;
-			sb[d] = S.cidx[ep[k]];
-			d++;
+			st[d++] = tag | ep[k];
 		}
 		while (mhi) {
 			const int k = 31 - __clz(mhi);
 			mhi ^= 1u << k;
-			sp[d] = id;
-			sb[d] = S.cidx[ep[32 + k]];
-			d++;
+			st[d++] = tag | ep[32 + k];
 		}
 	} else if (wtotal) {
 		if (lane == 31) {
@@ -484,30 +483,21 @@ __device__ __forceinline__ void bpp_emit(bpp_smem<MODE> &S, unsigned gid, uint32
 	bpp_gsync(gid);
 	const unsigned long long gbase = S.gbase[gid];
 	uint32_t *op = out_probe + gbase, *ob = out_build + gbase;
-	// head: up to the first 16-byte boundary of the destination (both columns must agree), then 16-byte stores
-	const uint32_t ha = (uint32_t)((16u - ((uintptr_t)op & 15u)) & 15u) >> 2, hb = (uint32_t)((16u - ((uintptr_t)ob & 15u)) & 15u) >> 2;
-	if (ha == hb && gbase + nst <= capacity) {
-		const uint32_t head = min(ha, nst);
-		if (gtid < head) {
-			op[gtid] = sp[gtid];
-			ob[gtid] = sb[gtid];
-		}
-		const uint32_t quads = (nst - head) >> 2;
-		for (uint32_t t = gtid; t < quads; t += BPP_GTHREADS) {
-			const uint32_t o = head + 4 * t;
-			*reinterpret_cast<uint4 *>(op + o) = make_uint4(sp[o], sp[o + 1], sp[o + 2], sp[o + 3]);
-			*reinterpret_cast<uint4 *>(ob + o) = make_uint4(sb[o], sb[o + 1], sb[o + 2], sb[o + 3]);
-		}
-		const uint32_t done = head + 4 * quads;
-		if (gtid < nst - done) {
-			op[done + gtid] = sp[done + gtid];
-			ob[done + gtid] = sb[done + gtid];
+	// copy-out: one conflict-free shared load per pair, expansion through rid[] / cidx[], two coalesced 4-byte stores
+	// (the shared-memory pipe, not the instruction count, limits this kernel: profiles/README.md r1e)
+	const uint32_t *rid = S.rid[gid];
+	if (gbase + nst <= capacity) {
+		for (uint32_t t = gtid; t < nst; t += BPP_GTHREADS) {
+			const uint32_t v = st[t];
+			op[t] = rid[v >> 16];
+			ob[t] = S.cidx[v & 0xFFFFu];
 		}
 	} else {
 		for (uint32_t t = gtid; t < nst; t += BPP_GTHREADS) {
 			if (gbase + t < capacity) {
-				op[t] = sp[t];
-				ob[t] = sb[t];
+				const uint32_t v = st[t];
+				op[t] = rid[v >> 16];
+				ob[t] = S.cidx[v & 0xFFFFu];
 			}
 		}
 	}
@@ -683,9 +673,19 @@ __global__ void __launch_bounds__(BPP_THREADS, 1)
 				double x = 0, y = 0;
 				uint32_t id = 0, PqC = BPP_C, Pq = 0, beg = 0, lenc = 0;
 				if (valid) {
+					id = pidx[i];
+				}
+				S.rid[gid][gtid] = id; // read by this round's copy-outs (after the group barrier)
+				if (i + BPP_THREADS < unit.pend) {
+					// this group's next round: pull the lines into L2 now, the loads then cost an L2 hit
+					asm volatile("prefetch.global.L2 [%0];" ::"l"(pxy + i + BPP_THREADS));
+					if ((gtid & 7) == 0) {
+						asm volatile("prefetch.global.L2 [%0];" ::"l"(pidx + i + BPP_THREADS));
+					}
+				}
+				if (valid) {
 					const double2 xy = pxy[i];
 					x = xy.x, y = xy.y;
-					id = pidx[i];
 					const uint32_t lx = (uint32_t)(bp_q(x, g.minx, g.sx) - ox), ly = (uint32_t)(bp_q(y, g.miny, g.sy) - oy);
 					Pq = (ly << 16) | lx;
 					PqC = Pq | BPP_C;
