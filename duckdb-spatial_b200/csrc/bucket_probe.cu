@@ -357,6 +357,9 @@ struct bpp_smem {
 	uint16_t off[BP_NB + 8];  // CSR offsets
 	uint16_t ent[BPP_EMAX];   // CSR entries: staged-entry numbers
 	uint16_t wide[BPP_WMAX];
+	// per sub-cell and 2x2 micro-cell: x = entries (of the first 32 of the list) that contain the whole micro-cell
+	// strictly (every point of it is an exact hit), y = entries that only overlap it (tested per point)
+	uint2 mask[BP_NB * 4];
 	// staged pairs, 4 bytes each: (thread of the group << 16) | staged-entry number; the copy-out expands them
 	// through rid[] (probe row id of each thread in this round) and cidx[]
 	uint32_t stage[BPP_GROUPS][STAGE];
@@ -508,6 +511,49 @@ __device__ __forceinline__ void bpp_emit(bpp_smem<MODE> &S, unsigned gid, uint32
 	}
 }
 
+#define BPP_RESOLVE_TIES(ep, tlo_, thi_)                                                                             \
+	while (tlo_ | thi_) {                                                                                            \
+		int k_;                                                                                                      \
+		if (tlo_) {                                                                                                  \
+			k_ = 31 - __clz(tlo_);                                                                                   \
+			tlo_ ^= 1u << k_;                                                                                        \
+		} else {                                                                                                     \
+			k_ = 31 - __clz(thi_);                                                                                   \
+			thi_ ^= 1u << k_;                                                                                        \
+			k_ += 32;                                                                                                \
+		}                                                                                                            \
+		const uint32_t j_ = (ep)[k_];                                                                                \
+		if (bp_exact<MODE>(x, y, MODE == 1 ? S.cpos[j_] : 0u, S.cidx[j_], boxes, build_box2d, pred)) {               \
+			if (k_ < 32) {                                                                                           \
+				mlo |= 1u << k_;                                                                                     \
+			} else {                                                                                                 \
+				mhi |= 1u << (k_ - 32);                                                                              \
+			}                                                                                                        \
+		}                                                                                                            \
+	}
+
+// first pass over a sub-cell list with the micro-cell masks: `mk.x` are hits without any test, only the entries in
+// `mk.y` are tested; entries 32..63 of long lists are tested one by one
+#define BPP_PASS_MASKED(ep, n, mk)                                                                                   \
+	do {                                                                                                             \
+		uint32_t tlo_ = 0, thi_ = 0;                                                                                 \
+		uint32_t amb_ = (mk).y;                                                                                      \
+		mlo = (mk).x;                                                                                                \
+		while (amb_) {                                                                                               \
+			const int k_ = 31 - __clz(amb_);                                                                         \
+			const uint32_t bit_ = 1u << k_;                                                                          \
+			amb_ ^= bit_;                                                                                            \
+			BPP_TEST((ep)[k_], bit_, mlo, tlo_);                                                                     \
+		}                                                                                                            \
+		if ((n) > 32u) {                                                                                             \
+			uint32_t bit_ = 1;                                                                                       \
+			for (uint32_t k_ = 32; k_ < (uint32_t)(n); k_++, bit_ <<= 1) {                                           \
+				BPP_TEST((ep)[k_], bit_, mhi, thi_);                                                                 \
+			}                                                                                                        \
+		}                                                                                                            \
+		BPP_RESOLVE_TIES(ep, tlo_, thi_);                                                                            \
+	} while (0)
+
 // tests up to 64 entries ep[0..n) for one point; ties are resolved with the exact predicate
 #define BPP_PASS(ep, n)                                                                                              \
 	do {                                                                                                             \
@@ -523,25 +569,7 @@ __device__ __forceinline__ void bpp_emit(bpp_smem<MODE> &S, unsigned gid, uint32
 				BPP_TEST((ep)[k_], bit_, mhi, thi_);                                                                 \
 			}                                                                                                        \
 		}                                                                                                            \
-		while (tlo_ | thi_) {                                                                                        \
-			int k_;                                                                                                  \
-			if (tlo_) {                                                                                              \
-				k_ = 31 - __clz(tlo_);                                                                               \
-				tlo_ ^= 1u << k_;                                                                                    \
-			} else {                                                                                                 \
-				k_ = 31 - __clz(thi_);                                                                               \
-				thi_ ^= 1u << k_;                                                                                    \
-				k_ += 32;                                                                                            \
-			}                                                                                                        \
-			const uint32_t j_ = (ep)[k_];                                                                            \
-			if (bp_exact<MODE>(x, y, MODE == 1 ? S.cpos[j_] : 0u, S.cidx[j_], boxes, build_box2d, pred)) {           \
-				if (k_ < 32) {                                                                                       \
-					mlo |= 1u << k_;                                                                                 \
-				} else {                                                                                             \
-					mhi |= 1u << (k_ - 32);                                                                          \
-				}                                                                                                    \
-			}                                                                                                        \
-		}                                                                                                            \
+		BPP_RESOLVE_TIES(ep, tlo_, thi_);                                                                            \
 	} while (0)
 
 template <int MODE>
@@ -664,6 +692,34 @@ __global__ void __launch_bounds__(BPP_THREADS, 1)
 			}
 			__syncthreads();
 			const uint32_t n_wide = S.n_wide;
+			// ---- (c') micro-cell masks: one thread per sub-cell classifies the first 32 entries of its list against
+			// the four 512x512-quantum quarters of the sub-cell
+			{
+				const uint32_t lb = S.off[tid], ln = min((uint32_t)S.off[tid + 1] - lb, 32u);
+				const uint32_t sx = (tid & 31u) << 10, sy = (tid >> 5) << 10;
+				uint32_t df[4] = {0, 0, 0, 0}, am[4] = {0, 0, 0, 0};
+				for (uint32_t e = 0; e < ln; e++) {
+					const uint2 qb = S.qbox[S.ent[lb + e]];
+					const uint32_t hi = qb.y & ~BPP_C;
+					const uint32_t lx0 = qb.x & 0xFFFFu, ly0 = qb.x >> 16, lx1 = hi & 0xFFFFu, ly1 = hi >> 16;
+#pragma unroll
+					for (int m = 0; m < 4; m++) {
+						const uint32_t mx0 = sx + (m & 1) * 512u, mx1 = mx0 + 511u, my0 = sy + (m >> 1) * 512u, my1 = my0 + 511u;
+						if (!(lx1 < mx0 || lx0 > mx1 || ly1 < my0 || ly0 > my1)) {
+							if (lx0 < mx0 && mx1 < lx1 && ly0 < my0 && my1 < ly1) {
+								df[m] |= 1u << e;
+							} else {
+								am[m] |= 1u << e;
+							}
+						}
+					}
+				}
+#pragma unroll
+				for (int m = 0; m < 4; m++) {
+					S.mask[tid * 4 + m] = make_uint2(df[m], am[m]);
+				}
+			}
+			__syncthreads();
 
 			// ---- (d) stream the unit's points: each 256-thread group takes every fourth round of 256 points ----
 			const unsigned gid = tid / BPP_GTHREADS, gtid = tid & (BPP_GTHREADS - 1);
@@ -671,7 +727,7 @@ __global__ void __launch_bounds__(BPP_THREADS, 1)
 				const uint32_t i = p0 + gtid;
 				const bool valid = i < unit.pend;
 				double x = 0, y = 0;
-				uint32_t id = 0, PqC = BPP_C, Pq = 0, beg = 0, lenc = 0;
+				uint32_t id = 0, PqC = BPP_C, Pq = 0, beg = 0, lenc = 0, msel = 0;
 				if (valid) {
 					id = pidx[i];
 				}
@@ -692,13 +748,19 @@ __global__ void __launch_bounds__(BPP_THREADS, 1)
 					const uint32_t sc = (ly >> 10) * 32 + (lx >> 10);
 					beg = S.off[sc];
 					lenc = S.off[sc + 1] - beg;
+					msel = sc * 4 + ((ly >> 9) & 1u) * 2 + ((lx >> 9) & 1u);
 				}
 				for (uint32_t e0 = 0; bpp_gor(gid, lenc > e0); e0 += 64) {
 					uint32_t mlo = 0, mhi = 0;
 					const uint16_t *ep = S.ent + beg + e0;
 					if (lenc > e0) {
 						const uint32_t n = min(lenc - e0, 64u);
-						BPP_PASS(ep, n);
+						if (e0 == 0) {
+							const uint2 mk = S.mask[msel];
+							BPP_PASS_MASKED(ep, n, mk);
+						} else {
+							BPP_PASS(ep, n);
+						}
 					}
 					bpp_emit<MODE>(S, gid, mlo, mhi, ep, id, out_probe, out_build, capacity, counter);
 				}
