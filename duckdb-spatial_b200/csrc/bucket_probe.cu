@@ -914,3 +914,695 @@ int sbi_flat_probe_bucketed(sb_context *ctx, const sb_flat *tree, const sb_probe
 	}
 	return SB_OK;
 }
+
+// ==================================================================================================================
+// K5 v3: cell-sorted probe. The v2 kernel above is issue-bound (33 warp instructions per probe, profiles r1e): every
+// lane walks its own sub-cell list, so the test and emit loops run max-over-lanes iterations and every pair passes
+// through a shared-memory staging buffer. v3 sorts the probes one level further -- by sub-cell inside the bucket --
+// so that the 32 lanes of a warp always share ONE sub-cell and therefore one entry list:
+//
+//   pass 1  k_cp_scatter1   points -> 8-byte records {15+15-bit in-bucket quantised coordinate, probe id}, grouped
+//                           by bucket (16 B read, 8 B written per point instead of 20 B), + the (bucket, sub-cell)
+//                           histogram
+//   scan    k_cp_scan2      per-bucket exclusive scan of the 1024 sub-cell counts -> cell_off[1024 x 1024 + 1]
+//   pass 2  k_cp_scatter2   records of one bucket -> grouped by sub-cell (8 B read + 8 B written per point)
+//   probe   k_cp_probe      a warp takes one sub-cell: the entry list is warp-uniform (broadcast shared loads, no
+//                           divergence); entries whose quantised box strictly covers the sub-cell hit every point
+//                           without a test (32 pairs per store instruction, straight to global memory); the others
+//                           are tested by all lanes at once, the hit ballots are kept in registers (lane e keeps
+//                           entry e's masks for up to 8 rounds of 32 points), one global atomic per warp and batch
+//                           (<= 256 points x 32 entries) reserves the output range, and the pairs are written
+//                           entry-major, ballot-compacted, with no staging buffer and no CTA barrier.
+//
+// The exact coordinates are only needed for quantisation ties (Q(p) equal to a box bound): they are fetched from the
+// caller's columns through the probe id. Result set: identical to v2 and to the tree walk (same three-state test).
+// ==================================================================================================================
+#define CP_TILE1 8192u
+#define CP_TILE2 16384u
+#define CP_NCELL (BP_NB * 1024u)
+
+__device__ __forceinline__ uint32_t cp_subcell(uint32_t pq) {
+	return ((pq >> 26) << 5) | ((pq >> 10) & 31u); // (ly >> 10) * 32 + (lx >> 10)
+}
+
+struct cps1_smem {
+	uint2 rec[CP_TILE1];
+	uint16_t bkt[CP_TILE1];
+	uint32_t cnt[BP_NB + 8];
+	uint32_t off[BP_NB + 8];
+	uint32_t scan[32];
+};
+
+__global__ void __launch_bounds__(1024, 1)
+    k_cp_scatter1(const double *__restrict__ px, const double *__restrict__ py, uint64_t n, uint32_t index_base,
+                  const bp_grid *__restrict__ gp, uint32_t *__restrict__ cursor, uint32_t *__restrict__ fine,
+                  uint2 *__restrict__ orec) {
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	cps1_smem &S = *reinterpret_cast<cps1_smem *>(smem_raw);
+	const bp_grid g = *gp;
+	const unsigned tid = threadIdx.x;
+	const uint64_t tiles = (n + CP_TILE1 - 1) / CP_TILE1;
+	constexpr int ITEMS = CP_TILE1 / 1024;
+	for (uint64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+		S.cnt[tid] = 0;
+		if (tid == 0) {
+			S.cnt[BP_NB] = 0;
+		}
+		__syncthreads();
+		const uint64_t base = tile * CP_TILE1 + tid;
+		double x[ITEMS], y[ITEMS];
+#pragma unroll
+		for (int k = 0; k < ITEMS; k++) {
+			const uint64_t i = base + (uint64_t)k * 1024;
+			if (i < n) {
+				x[k] = px[i];
+				y[k] = py[i];
+			}
+		}
+		uint32_t pq[ITEMS], br[ITEMS];
+#pragma unroll
+		for (int k = 0; k < ITEMS; k++) {
+			const uint64_t i = base + (uint64_t)k * 1024;
+			br[k] = 0xFFFFFFFFu;
+			pq[k] = 0;
+			if (i < n) {
+				const int b = bp_bucket(x[k], y[k], g);
+				if (b >= 0) {
+					const int qx = bp_q(x[k], g.minx, g.sx), qy = bp_q(y[k], g.miny, g.sy);
+					pq[k] = ((uint32_t)(qy & 32767) << 16) | (uint32_t)(qx & 32767);
+					br[k] = ((uint32_t)b << 16) | atomicAdd(&S.cnt[b], 1u);
+				}
+			}
+		}
+		__syncthreads();
+		{
+			uint32_t total;
+			const uint32_t c = S.cnt[tid];
+			const uint32_t ex = bp_block_excl_scan_1024(c, S.scan, &total);
+			S.off[tid] = ex;
+			if (c) {
+				S.cnt[tid] = atomicAdd(&cursor[tid], c) - ex;
+			}
+			if (tid == 1023) {
+				const uint32_t cn = S.cnt[BP_NB];
+				S.off[BP_NB] = total;
+				S.off[BP_NB + 1] = total + cn;
+				if (cn) {
+					S.cnt[BP_NB] = atomicAdd(&cursor[BP_NB], cn) - total;
+				}
+			}
+		}
+		__syncthreads();
+#pragma unroll
+		for (int k = 0; k < ITEMS; k++) {
+			if (br[k] != 0xFFFFFFFFu) {
+				const uint32_t b = br[k] >> 16;
+				const uint32_t slot = S.off[b] + (br[k] & 0xFFFFu);
+				S.rec[slot] = make_uint2(pq[k], (uint32_t)(base + (uint64_t)k * 1024) + index_base);
+				S.bkt[slot] = (uint16_t)b;
+			}
+		}
+		__syncthreads();
+		const uint32_t kept = S.off[BP_NB + 1];
+		for (uint32_t t = tid; t < kept; t += 1024) {
+			const uint32_t b = S.bkt[t];
+			const uint2 r = S.rec[t];
+			orec[S.cnt[b] + t] = r;
+			if (b < BP_NB) {
+				atomicAdd(&fine[(b << 10) | cp_subcell(r.x)], 1u);
+			}
+		}
+		__syncthreads();
+	}
+}
+
+// one CTA per bucket: cell_off[b * 1024 + s] = pt_off[b] + exclusive scan of the bucket's sub-cell counts;
+// `fine` becomes the pass-2 cursor array
+__global__ void __launch_bounds__(1024) k_cp_scan2(const bp_tables *__restrict__ T, uint32_t *__restrict__ fine,
+                                                   uint32_t *__restrict__ cell_off) {
+	__shared__ uint32_t s_warp[32];
+	const uint32_t b = blockIdx.x, i = b * 1024u + threadIdx.x;
+	uint32_t total;
+	const uint32_t ex = bp_block_excl_scan_1024(fine[i], s_warp, &total) + T->pt_off[b];
+	cell_off[i] = ex;
+	fine[i] = ex;
+	if (b == BP_NB - 1 && threadIdx.x == 0) {
+		cell_off[CP_NCELL] = T->pt_off[BP_NB];
+	}
+}
+
+struct cps2_smem {
+	uint2 rec[CP_TILE2];
+	uint32_t cnt[BP_NB];
+	uint32_t off[BP_NB];
+	uint32_t scan[32];
+};
+
+__global__ void __launch_bounds__(1024, 1)
+    k_cp_scatter2(const bp_tables *__restrict__ T, const bp_unit *__restrict__ units, const uint2 *__restrict__ irec,
+                  uint32_t *__restrict__ cursor2, uint2 *__restrict__ orec) {
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	cps2_smem &S = *reinterpret_cast<cps2_smem *>(smem_raw);
+	const unsigned tid = threadIdx.x;
+	const uint32_t n_units = (uint32_t)T->totals[2];
+	constexpr int ITEMS = CP_TILE2 / 1024;
+	// work items: halves of the probe units (a unit has at most BP_SLICE = 2 x CP_TILE2 records of one bucket)
+	for (uint32_t w = blockIdx.x; w < 2 * n_units; w += gridDim.x) {
+		const bp_unit u = units[w >> 1];
+		const uint32_t tbeg = u.pbeg + (w & 1u) * CP_TILE2;
+		const uint32_t tend = min(u.pend, tbeg + CP_TILE2);
+		if (tbeg >= tend) {
+			continue; // uniform
+		}
+		S.cnt[tid] = 0;
+		__syncthreads();
+		uint2 r[ITEMS];
+		uint32_t rk[ITEMS];
+#pragma unroll
+		for (int k = 0; k < ITEMS; k++) {
+			const uint32_t i = tbeg + k * 1024 + tid;
+			if (i < tend) {
+				r[k] = irec[i];
+			}
+		}
+#pragma unroll
+		for (int k = 0; k < ITEMS; k++) {
+			const uint32_t i = tbeg + k * 1024 + tid;
+			rk[k] = i < tend ? atomicAdd(&S.cnt[cp_subcell(r[k].x)], 1u) : 0u;
+		}
+		__syncthreads();
+		{
+			uint32_t total;
+			const uint32_t c = S.cnt[tid];
+			const uint32_t ex = bp_block_excl_scan_1024(c, S.scan, &total);
+			S.off[tid] = ex;
+			if (c) {
+				S.cnt[tid] = atomicAdd(&cursor2[(u.bucket << 10) | tid], c) - ex;
+			}
+		}
+		__syncthreads();
+#pragma unroll
+		for (int k = 0; k < ITEMS; k++) {
+			const uint32_t i = tbeg + k * 1024 + tid;
+			if (i < tend) {
+				S.rec[S.off[cp_subcell(r[k].x)] + rk[k]] = r[k];
+			}
+		}
+		__syncthreads();
+		const uint32_t nt = tend - tbeg;
+		for (uint32_t t = tid; t < nt; t += 1024) {
+			const uint2 v = S.rec[t];
+			orec[S.cnt[cp_subcell(v.x)] + t] = v;
+		}
+		__syncthreads();
+	}
+}
+
+#define CPP_RB 8 // rounds of 32 points per batch
+template <int MODE>
+struct cpp_smem {
+	uint2 qbox[BPP_CMAX];
+	uint32_t cidx[BPP_CMAX];
+	uint32_t cpos[MODE == 1 ? BPP_CMAX : 1];
+	uint32_t cnt[BP_NB];
+	uint16_t off[BP_NB + 8];
+	uint16_t ent[BPP_EMAX];
+	uint16_t wide[BPP_WMAX];
+	uint32_t scan[32];
+	uint32_t unit, n_ent, n_wide, next_sc, sc_first, sc_last;
+};
+
+// two predicated 4-byte stores sharing one predicate (no branch around the store pair)
+__device__ __forceinline__ void cpp_st2_if(uint32_t *p0, uint32_t v0, uint32_t *p1, uint32_t v1, uint32_t pred) {
+	asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %4, 0;\n\t@q st.global.u32 [%0], %1;\n\t@q st.global.u32 [%2], %3;\n\t}"
+	             :
+	             : "l"(p0), "r"(v0), "l"(p1), "r"(v1), "r"(pred)
+	             : "memory");
+}
+
+// writes the pairs of one batch: entry-major; definite entries emit every point of the batch, tested entries their
+// ballot-compacted hits. `base` is warp-uniform; offsets inside the batch are 32-bit.
+template <bool GUARD>
+__device__ __forceinline__ void cpp_write(const uint32_t (&id)[CPP_RB], const uint32_t (&mk)[CPP_RB], uint32_t defm,
+                                          const uint16_t *ep, uint32_t ne, uint32_t npts, const uint32_t *cidx,
+                                          unsigned long long base, uint64_t capacity, uint32_t *__restrict__ out_probe,
+                                          uint32_t *__restrict__ out_build) {
+	unsigned lane = sb_lane(), lt = sb_lanemask_lt(), eq = 1u << lane;
+	uint32_t *pp = out_probe + base, *pb = out_build + base;
+	// keep the lane id and the two batch pointers in registers: offsets inside the batch stay 32-bit (one IMAD.WIDE
+	// per store instead of a re-derived 64-bit base + offset sum)
+	asm volatile("" : "+r"(lane), "+r"(lt), "+r"(eq), "+l"(pp), "+l"(pb));
+	const uint32_t room = GUARD ? (uint32_t)(capacity > base ? min((unsigned long long)0xFFFFFFFFu, capacity - base) : 0ull)
+	                            : 0xFFFFFFFFu;
+	uint32_t off = 0;
+	for (uint32_t e = 0; e < ne; e++) {
+		const uint32_t bi = cidx[ep[e]];
+		if ((defm >> e) & 1u) {
+#pragma unroll
+			for (int r = 0; r < CPP_RB; r++) {
+				if ((uint32_t)(r & ~1) * 32u < npts) { // rounds are enabled in pairs (one uniform branch per two rounds)
+					const uint32_t o = off + (unsigned)r * 32u + lane;
+					cpp_st2_if(pp + o, id[r], pb + o, bi, ((unsigned)r * 32u + lane < npts) && (!GUARD || o < room));
+				}
+			}
+			off += npts;
+		} else {
+#pragma unroll
+			for (int r = 0; r < CPP_RB; r++) {
+				if ((uint32_t)(r & ~1) * 32u < npts) {
+					const uint32_t m = __shfl_sync(0xFFFFFFFFu, mk[r], e);
+					const uint32_t o = off + __popc(m & lt);
+					cpp_st2_if(pp + o, id[r], pb + o, bi, GUARD ? ((m & eq) && o < room) : (m & eq));
+					off += __popc(m);
+				}
+			}
+		}
+	}
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(BPP_THREADS, 1)
+    k_cp_probe(const float4 *__restrict__ boxes, const uint32_t *__restrict__ idx,
+               const double4 *__restrict__ build_box2d, int pred, const bp_grid *__restrict__ gp,
+               bp_tables *__restrict__ T, const bp_unit *__restrict__ units, const uint32_t *__restrict__ cand_pos,
+               const uint2 *__restrict__ rec, const uint32_t *__restrict__ cell_off, const double *__restrict__ px,
+               const double *__restrict__ py, uint32_t index_base, uint32_t *__restrict__ out_probe,
+               uint32_t *__restrict__ out_build, uint64_t capacity, unsigned long long *__restrict__ counter) {
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	cpp_smem<MODE> &S = *reinterpret_cast<cpp_smem<MODE> *>(smem_raw);
+	const bp_grid g = *gp;
+	const unsigned tid = threadIdx.x, lane = sb_lane();
+	const uint32_t n_units = (uint32_t)T->totals[2];
+
+	while (true) {
+		__syncthreads();
+		if (tid == 0) {
+			S.unit = atomicAdd(&T->ticket, 1u);
+		}
+		__syncthreads();
+		const uint32_t u = S.unit;
+		if (u >= n_units) {
+			break;
+		}
+		const bp_unit unit = units[u];
+		const uint32_t *coff = cell_off + ((size_t)unit.bucket << 10);
+		if (tid == 0) {
+			// sub-cells of this bucket that own points of [pbeg, pend): first = last s with coff[s] <= pbeg,
+			// last = last s with coff[s] < pend
+			uint32_t lo = 0, hi = 1023;
+			while (lo < hi) {
+				const uint32_t mid = (lo + hi + 1) >> 1;
+				if (coff[mid] <= unit.pbeg) {
+					lo = mid;
+				} else {
+					hi = mid - 1;
+				}
+			}
+			S.sc_first = lo;
+			lo = 0, hi = 1023;
+			while (lo < hi) {
+				const uint32_t mid = (lo + hi + 1) >> 1;
+				if (coff[mid] < unit.pend) {
+					lo = mid;
+				} else {
+					hi = mid - 1;
+				}
+			}
+			S.sc_last = lo;
+		}
+		__syncthreads();
+		const uint32_t sc_first = S.sc_first, sc_last = S.sc_last;
+		const int ox = (int)(unit.bucket % BP_G) << 15, oy = (int)(unit.bucket / BP_G) << 15;
+		const uint32_t cbeg = T->cand_off[unit.bucket], cend = T->cand_off[unit.bucket + 1];
+		uint32_t c0 = cbeg;
+		while (c0 < cend) {
+			// ---- (a) stage a chunk of leaf entries as quantised in-bucket boxes, count directory entries ----
+			uint32_t ntry = min((uint32_t)BPP_CMAX, cend - c0);
+			while (true) {
+				__syncthreads();
+				if (tid == 0) {
+					S.n_ent = 0;
+					S.n_wide = 0;
+				}
+				S.cnt[tid] = 0; // BPP_THREADS == BP_NB
+				__syncthreads();
+				for (uint32_t j = tid; j < ntry; j += BPP_THREADS) {
+					const uint32_t pos = cand_pos[c0 + j];
+					const uint32_t bi = __ldg(idx + pos);
+					int x0, y0, x1, y1;
+					bool empty = false;
+					if (MODE == 1) {
+						bp_leaf_range(__ldg(boxes + pos), g, x0, y0, x1, y1);
+						S.cpos[j] = pos;
+					} else {
+						const double4 e = build_box2d[bi];
+						empty = (e.x != e.x) || (e.y != e.y) || (e.z != e.z) || (e.w != e.w);
+						x0 = bp_q(e.x, g.minx, g.sx), y0 = bp_q(e.y, g.miny, g.sy);
+						x1 = bp_q(e.z, g.minx, g.sx), y1 = bp_q(e.w, g.miny, g.sy);
+					}
+					empty = empty || x1 < ox || x0 > ox + 32767 || y1 < oy || y0 > oy + 32767 || x0 > x1 || y0 > y1;
+					const uint32_t lx0 = (uint32_t)(max(x0, ox) - ox), ly0 = (uint32_t)(max(y0, oy) - oy);
+					const uint32_t lx1 = (uint32_t)(min(x1, ox + 32767) - ox), ly1 = (uint32_t)(min(y1, oy + 32767) - oy);
+					// rows of sub-cells outside [sc_first, sc_last] hold no point of this unit
+					if (!empty && ((ly1 >> 10) < (sc_first >> 5) || (ly0 >> 10) > (sc_last >> 5))) {
+						empty = true;
+					}
+					uint2 qb;
+					qb.x = empty ? 0x7FFF7FFFu : ((ly0 << 16) | lx0);
+					qb.y = (empty ? 0u : ((ly1 << 16) | lx1)) | BPP_C;
+					S.qbox[j] = qb;
+					S.cidx[j] = bi;
+					if (!empty) {
+						const uint32_t cells = ((lx1 >> 10) - (lx0 >> 10) + 1) * ((ly1 >> 10) - (ly0 >> 10) + 1);
+						if (cells > BPP_WIDE_T) {
+							atomicAdd(&S.n_wide, 1u);
+						} else {
+							uint32_t added = 0;
+							for (uint32_t cy = ly0 >> 10; cy <= (ly1 >> 10); cy++) {
+								for (uint32_t cx = lx0 >> 10; cx <= (lx1 >> 10); cx++) {
+									const uint32_t s = cy * 32 + cx;
+									if (s >= sc_first && s <= sc_last) {
+										atomicAdd(&S.cnt[s], 1u);
+										added++;
+									}
+								}
+							}
+							atomicAdd(&S.n_ent, added);
+						}
+					}
+				}
+				__syncthreads();
+				if (S.n_ent <= BPP_EMAX && S.n_wide <= BPP_WMAX) {
+					break;
+				}
+				ntry = (ntry + 1) / 2; // rare: the directory would overflow shared memory -> smaller chunk
+			}
+			// ---- (b) CSR offsets over the 1024 sub-cells (one per thread) ----
+			{
+				uint32_t total;
+				const uint32_t c = S.cnt[tid];
+				const uint32_t ex = bp_block_excl_scan_1024(c, S.scan, &total);
+				S.off[tid] = (uint16_t)ex;
+				S.cnt[tid] = ex;
+				if (tid == BPP_THREADS - 1) {
+					S.off[BP_NB] = (uint16_t)(ex + c);
+				}
+				if (tid == 0) {
+					S.n_wide = 0;
+					S.next_sc = sc_first;
+				}
+			}
+			__syncthreads();
+			// ---- (c) fill the directory ----
+			for (uint32_t j = tid; j < ntry; j += BPP_THREADS) {
+				const uint2 qb = S.qbox[j];
+				const uint32_t hi = qb.y & ~BPP_C;
+				const uint32_t lx0 = qb.x & 0xFFFFu, ly0 = qb.x >> 16, lx1 = hi & 0xFFFFu, ly1 = hi >> 16;
+				if (lx0 > lx1 || ly0 > ly1) {
+					continue; // empty
+				}
+				const uint32_t cells = ((lx1 >> 10) - (lx0 >> 10) + 1) * ((ly1 >> 10) - (ly0 >> 10) + 1);
+				if (cells > BPP_WIDE_T) {
+					S.wide[atomicAdd(&S.n_wide, 1u)] = (uint16_t)j;
+				} else {
+					for (uint32_t cy = ly0 >> 10; cy <= (ly1 >> 10); cy++) {
+						for (uint32_t cx = lx0 >> 10; cx <= (lx1 >> 10); cx++) {
+							const uint32_t s = cy * 32 + cx;
+							if (s >= sc_first && s <= sc_last) {
+								S.ent[atomicAdd(&S.cnt[s], 1u)] = (uint16_t)j;
+							}
+						}
+					}
+				}
+			}
+			__syncthreads();
+			const uint32_t n_wide = S.n_wide;
+
+			// ---- (d) warps take sub-cells; all 32 lanes share the sub-cell's entry list ----
+			unsigned wlane = lane;
+			asm volatile("" : "+r"(wlane)); // a register copy of the lane id (otherwise re-read from SR_TID per use)
+			while (true) {
+				uint32_t sc = 0;
+				if (lane == 0) {
+					sc = atomicAdd(&S.next_sc, 1u);
+				}
+				sc = __shfl_sync(0xFFFFFFFFu, sc, 0);
+				if (sc > sc_last) {
+					break;
+				}
+				const uint32_t p0 = max(__ldg(coff + sc), unit.pbeg);
+				const uint32_t p1 = min(__ldg(coff + sc + 1), unit.pend); // cell_off is contiguous across buckets
+				const uint32_t lb = S.off[sc], n0 = (uint32_t)S.off[sc + 1] - lb;
+				if (p0 >= p1 || n0 + n_wide == 0) {
+					continue;
+				}
+				const uint32_t sx0 = (sc & 31u) << 10, sy0 = (sc >> 5) << 10;
+				for (uint32_t pb = p0; pb < p1; pb += 32 * CPP_RB) {
+					const uint32_t npts = min(p1 - pb, (uint32_t)(32 * CPP_RB));
+					uint32_t PqC[CPP_RB], id[CPP_RB];
+#pragma unroll
+					for (int r = 0; r < CPP_RB; r++) {
+						const uint32_t i = pb + r * 32 + lane;
+						PqC[r] = BPP_C;
+						id[r] = 0;
+						if (i < p1) {
+							const uint2 v = rec[i];
+							PqC[r] = v.x | BPP_C;
+							id[r] = v.y;
+						}
+					}
+					for (int pass = 0; pass < 2; pass++) {
+						const uint16_t *list = pass == 0 ? S.ent + lb : S.wide;
+						const uint32_t nl = pass == 0 ? n0 : n_wide;
+						for (uint32_t e0 = 0; e0 < nl; e0 += 32) {
+							const uint16_t *ep = list + e0;
+							const uint32_t ne = min(nl - e0, 32u);
+							uint32_t mk[CPP_RB];
+#pragma unroll
+							for (int r = 0; r < CPP_RB; r++) {
+								mk[r] = 0;
+							}
+							uint32_t defm = 0;
+							for (uint32_t e = 0; e < ne; e++) {
+								const uint32_t j = ep[e];
+								const uint2 qb = S.qbox[j];
+								const uint32_t hi = qb.y & ~BPP_C;
+								const uint32_t lx0 = qb.x & 0xFFFFu, ly0 = qb.x >> 16, lx1 = hi & 0xFFFFu, ly1 = hi >> 16;
+								if (lx0 < sx0 && sx0 + 1023u < lx1 && ly0 < sy0 && sy0 + 1023u < ly1) {
+									defm |= 1u << e; // strictly covers the sub-cell: every point is an exact hit
+									continue;
+								}
+								// per 16-bit half: t1 = 0x8000 + (p - lo), t2 = 0x8000 + (hi - p); s1 / s2 = the same minus 1.
+								// bit 15 of t <=> that side holds (closed), of s <=> it holds strictly. hiC2 - PqC == qb.y - Pq.
+								const uint32_t lo = qb.x, hiC2 = qb.y + BPP_C, loK = lo + BPP_K, hiK = hiC2 - BPP_K;
+								const bool mine = wlane == e;
+								uint32_t tie = 0;
+#pragma unroll
+								for (int r = 0; r < CPP_RB; r++) {
+									if ((uint32_t)(r & ~1) * 32u < npts) { // rounds are enabled in pairs
+										const uint32_t s1 = PqC[r] - loK, s2 = hiK - PqC[r];
+										const uint32_t ms = __ballot_sync(0xFFFFFFFFu, (s1 & s2 & BPP_C) == BPP_C);
+										const uint32_t t1 = PqC[r] - lo, t2 = hiC2 - PqC[r];
+										const uint32_t mc = __ballot_sync(0xFFFFFFFFu, (t1 & t2 & BPP_C) == BPP_C);
+										tie |= mc ^ ms;
+										if (mine) {
+											mk[r] = ms;
+										}
+									}
+								}
+								if (tie) {
+									// some lane sits exactly on a quantised bound of this entry: the exact predicate decides
+#pragma unroll
+									for (int r = 0; r < CPP_RB; r++) {
+										if ((uint32_t)r * 32u < npts) {
+											const uint32_t s1 = PqC[r] - loK, s2 = hiK - PqC[r];
+											const uint32_t t1 = PqC[r] - lo, t2 = hiC2 - PqC[r];
+											bool h = false;
+											if ((t1 & t2 & BPP_C) == BPP_C && (s1 & s2 & BPP_C) != BPP_C && (uint32_t)r * 32u + lane < npts) {
+												const uint32_t o = id[r] - index_base;
+												h = bp_exact<MODE>(px[o], py[o], MODE == 1 ? S.cpos[j] : 0u, S.cidx[j], boxes, build_box2d,
+												                   pred);
+											}
+											const uint32_t m = __ballot_sync(0xFFFFFFFFu, h);
+											if (mine) {
+												mk[r] |= m;
+											}
+										}
+									}
+								}
+							}
+							uint32_t cnt = 0;
+#pragma unroll
+							for (int r = 0; r < CPP_RB; r++) {
+								// lanes past the end of the batch carry PqC = 0|C: drop whatever they matched
+								const uint32_t left = npts > (uint32_t)r * 32u ? npts - (uint32_t)r * 32u : 0u;
+								mk[r] &= left >= 32u ? 0xFFFFFFFFu : ((1u << left) - 1u);
+								cnt += __popc(mk[r]);
+							}
+							cnt = __reduce_add_sync(0xFFFFFFFFu, cnt) + __popc(defm) * npts;
+							if (cnt == 0) {
+								continue;
+							}
+							unsigned long long base = 0;
+							if (lane == 0) {
+								base = atomicAdd(counter, (unsigned long long)cnt);
+							}
+							base = __shfl_sync(0xFFFFFFFFu, base, 0);
+							if (base + cnt <= capacity) {
+								cpp_write<false>(id, mk, defm, ep, ne, npts, S.cidx, base, capacity, out_probe, out_build);
+							} else {
+								cpp_write<true>(id, mk, defm, ep, ne, npts, S.cidx, base, capacity, out_probe, out_build);
+							}
+						}
+					}
+				}
+			}
+			c0 += ntry;
+		}
+	}
+}
+
+// NaN probes (bucket BP_NB) back to coordinate columns + ids for the tree walk
+__global__ void __launch_bounds__(256) k_cp_unpack(const uint2 *__restrict__ rec, uint32_t n, const double *__restrict__ px,
+                                                   const double *__restrict__ py, uint32_t index_base,
+                                                   double *__restrict__ x, double *__restrict__ y,
+                                                   uint32_t *__restrict__ ids) {
+	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+		const uint32_t id = rec[i].y;
+		x[i] = px[id - index_base];
+		y[i] = py[id - index_base];
+		ids[i] = id;
+	}
+}
+
+int sbi_flat_probe_cells(sb_context *ctx, const sb_flat *tree, const sb_probe_args &a, uint32_t *out_probe,
+                         uint32_t *out_build, uint64_t capacity, uint64_t *count) {
+	*count = 0;
+	const uint64_t n = a.m;
+	const uint32_t items = tree->h.item_count;
+	if (n == 0 || items == 0) {
+		return SB_OK;
+	}
+	SB_ARG(a.px != nullptr && a.py != nullptr, "cell probe takes points");
+	SB_ARG(n + a.index_base <= 0xFFFFFFFFull, "probe indices must fit 32 bits");
+	const int mode = a.pred >= 0 ? 2 : 1;
+	SB_ARG(mode == 1 || a.build_box2d != nullptr, "build_box2d");
+
+	bp_grid *d_grid = nullptr;
+	bp_tables *d_tab = nullptr;
+	bp_unit *d_units = nullptr;
+	uint2 *d_rec_a = nullptr, *d_rec_b = nullptr;
+	uint32_t *d_cand = nullptr, *d_fine = nullptr, *d_cell_off = nullptr;
+	unsigned long long *d_counter = nullptr;
+	const uint64_t max_units = n / BP_SLICE + BP_NB + 1;
+	SB_TRY(ctx->scratch_t(1, &d_grid));
+	SB_TRY(ctx->scratch_t(1, &d_tab));
+	SB_TRY(ctx->scratch_t(max_units, &d_units));
+	SB_TRY(ctx->scratch_t(1, &d_counter));
+	SB_TRY(ctx->scratch_t(n, &d_rec_a));
+	SB_TRY(ctx->scratch_t(n, &d_rec_b));
+	SB_TRY(ctx->scratch_t(CP_NCELL, &d_fine));
+	SB_TRY(ctx->scratch_t(CP_NCELL + 1, &d_cell_off));
+	SB_CUDA(cudaMemsetAsync(d_tab, 0, sizeof(bp_tables), ctx->stream));
+	SB_CUDA(cudaMemsetAsync(d_counter, 0, sizeof(*d_counter), ctx->stream));
+	SB_CUDA(cudaMemsetAsync(d_fine, 0, sizeof(uint32_t) * CP_NCELL, ctx->stream));
+	const sb_flat_header *d_hdr = static_cast<const sb_flat_header *>(tree->buffer);
+	{
+		sb_prof_scope ps(ctx, "bp_partition");
+		k_bp_grid_init<<<1, 32, 0, ctx->stream>>>(d_hdr, d_grid);
+		SB_LAUNCH_CHECK(ctx);
+		k_bp_hist<<<sb_grid(n, BPH_THREADS * 8, 4), BPH_THREADS, 0, ctx->stream>>>(a.px, a.py, n, d_grid, d_tab->pt_hist, nullptr);
+		SB_LAUNCH_CHECK(ctx);
+	}
+	{
+		sb_prof_scope ps(ctx, "bp_cand");
+		k_bp_cand<false><<<sb_grid(items, 256, 8), 256, 0, ctx->stream>>>(tree->boxes(), items, d_grid, d_tab->cand_cnt,
+		                                                                 nullptr);
+		SB_LAUNCH_CHECK(ctx);
+		k_bp_scan<<<1, 1024, 0, ctx->stream>>>(d_tab, d_units);
+		SB_LAUNCH_CHECK(ctx);
+	}
+	SB_TRACE(ctx, "cp: hist + cand count + scan");
+	uint64_t totals[4];
+	SB_CUDA(cudaMemcpyAsync(ctx->pinned_u64, d_tab->totals, sizeof(totals), cudaMemcpyDeviceToHost, ctx->stream));
+	SB_CUDA(cudaStreamSynchronize(ctx->stream));
+	memcpy(totals, ctx->pinned_u64, sizeof(totals));
+	const uint64_t n_cand = totals[1], n_units = totals[2], n_nan = totals[3];
+	SB_ARG(n_cand < 0xFFFFFFFFull, "cell probe: candidate directory too large");
+	SB_TRY(ctx->scratch_t(n_cand ? n_cand : 1, &d_cand));
+	static bool attr_set = false;
+	if (!attr_set) {
+		SB_CUDA(cudaFuncSetAttribute(k_cp_scatter1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(cps1_smem)));
+		SB_CUDA(cudaFuncSetAttribute(k_cp_scatter2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(cps2_smem)));
+		SB_CUDA(cudaFuncSetAttribute(k_cp_probe<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(cpp_smem<1>)));
+		SB_CUDA(cudaFuncSetAttribute(k_cp_probe<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(cpp_smem<2>)));
+		attr_set = true;
+	}
+	{
+		sb_prof_scope ps(ctx, "bp_partition");
+		k_cp_scatter1<<<sb_grid(n, CP_TILE1, 1), 1024, sizeof(cps1_smem), ctx->stream>>>(
+		    a.px, a.py, n, a.index_base, d_grid, d_tab->pt_cursor, d_fine, d_rec_a);
+		SB_LAUNCH_CHECK(ctx);
+		if (n_units) {
+			k_cp_scan2<<<BP_NB, 1024, 0, ctx->stream>>>(d_tab, d_fine, d_cell_off);
+			SB_LAUNCH_CHECK(ctx);
+			k_cp_scatter2<<<sb_grid(2 * n_units, 1, 1), 1024, sizeof(cps2_smem), ctx->stream>>>(d_tab, d_units, d_rec_a, d_fine,
+			                                                                                   d_rec_b);
+			SB_LAUNCH_CHECK(ctx);
+		}
+	}
+	{
+		sb_prof_scope ps(ctx, "bp_cand");
+		k_bp_cand<true><<<sb_grid(items, 256, 8), 256, 0, ctx->stream>>>(tree->boxes(), items, d_grid, d_tab->cand_cursor,
+		                                                                d_cand);
+		SB_LAUNCH_CHECK(ctx);
+	}
+	SB_TRACE(ctx, "cp: scatter passes + cand fill");
+	if (n_units) {
+		const unsigned grid = (unsigned)(n_units < SB_NUM_SMS ? n_units : SB_NUM_SMS);
+		sb_prof_scope ps(ctx, "flat_probe");
+		if (mode == 1) {
+			k_cp_probe<1><<<grid, BPP_THREADS, sizeof(cpp_smem<1>), ctx->stream>>>(
+			    tree->boxes(), tree->idx(), nullptr, -1, d_grid, d_tab, d_units, d_cand, d_rec_b, d_cell_off, a.px, a.py,
+			    a.index_base, out_probe, out_build, capacity, d_counter);
+		} else {
+			k_cp_probe<2><<<grid, BPP_THREADS, sizeof(cpp_smem<2>), ctx->stream>>>(
+			    tree->boxes(), tree->idx(), a.build_box2d, a.pred, d_grid, d_tab, d_units, d_cand, d_rec_b, d_cell_off, a.px,
+			    a.py, a.index_base, out_probe, out_build, capacity, d_counter);
+		}
+		SB_LAUNCH_CHECK(ctx);
+	}
+	uint64_t c1 = 0;
+	SB_TRY(sbi_read_u64(ctx, reinterpret_cast<const uint64_t *>(d_counter), &c1));
+	SB_TRACE(ctx, "cp: probe kernel");
+	*count = c1;
+	if (n_nan && mode == 1) {
+		// NaN coordinates: Box::Intersects never rejects on a NaN axis. Such rows take the per-probe tree walk.
+		double *nx = nullptr, *ny = nullptr;
+		uint32_t *nid = nullptr;
+		SB_TRY(ctx->scratch_t(n_nan, &nx));
+		SB_TRY(ctx->scratch_t(n_nan, &ny));
+		SB_TRY(ctx->scratch_t(n_nan, &nid));
+		k_cp_unpack<<<sb_grid(n_nan, 256, 8), 256, 0, ctx->stream>>>(d_rec_a + totals[0], (uint32_t)n_nan, a.px, a.py,
+		                                                            a.index_base, nx, ny, nid);
+		SB_LAUNCH_CHECK(ctx);
+		sb_probe_args b;
+		b.px = nx;
+		b.py = ny;
+		b.m = n_nan;
+		b.ids = nid;
+		b.force_walk = true;
+		uint64_t c2 = 0;
+		const uint64_t done = c1 < capacity ? c1 : capacity;
+		int s = sbi_flat_probe(ctx, tree, b, out_probe + done, out_build + done, capacity - done, &c2);
+		*count = c1 + c2;
+		if (s != SB_OK && s != SB_ERR_CAPACITY) {
+			return s;
+		}
+	}
+	if (*count > capacity) {
+		sb_set_error("probe: %llu pairs, capacity %llu", (unsigned long long)*count, (unsigned long long)capacity);
+		return SB_ERR_CAPACITY;
+	}
+	return SB_OK;
+}

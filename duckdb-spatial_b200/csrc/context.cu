@@ -167,7 +167,7 @@ extern "C" int sb_context_set_stream(sb_context *ctx, void *cuda_stream) {
 extern "C" int sb_context_set_option(sb_context *ctx, const char *key, int64_t value) {
 	SB_ARG(ctx != nullptr && key != nullptr, "ctx/key");
 	if (strcmp(key, "probe_path") == 0) {
-		SB_ARG(value >= 0 && value <= 2, "probe_path must be 0 (auto), 1 (tree walk) or 2 (bucketed)");
+		SB_ARG(value >= 0 && value <= 3, "probe_path must be 0 (auto), 1 (tree walk), 2 (bucketed v2) or 3 (cell-sorted v3)");
 		ctx->probe_path = (int)value;
 		return SB_OK;
 	}

@@ -343,8 +343,11 @@ int sbi_flat_probe(sb_context *ctx, const sb_flat *tree, const sb_probe_args &a,
 	}
 	SB_ARG(a.m + a.index_base <= 0xFFFFFFFFull, "probe indices must fit 32 bits");
 	// bulk point probes: bucketed kernel (same pair set); small batches and box probes: per-probe tree walk
-	if (!a.force_walk && !a.probe_box && ctx->probe_path != 1 && (ctx->probe_path == 2 || a.m >= (1u << 17))) {
-		return sbi_flat_probe_bucketed(ctx, tree, a, out_probe, out_build, capacity, count);
+	if (!a.force_walk && !a.probe_box && ctx->probe_path != 1 && (ctx->probe_path >= 2 || a.m >= (1u << 17))) {
+		if (ctx->probe_path == 2) {
+			return sbi_flat_probe_bucketed(ctx, tree, a, out_probe, out_build, capacity, count);
+		}
+		return sbi_flat_probe_cells(ctx, tree, a, out_probe, out_build, capacity, count);
 	}
 	flat_meta M;
 	M.item_count = tree->h.item_count;

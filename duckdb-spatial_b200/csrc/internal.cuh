@@ -94,6 +94,10 @@ int sbi_flat_probe(sb_context *ctx, const sb_flat *tree, const sb_probe_args &ar
 int sbi_flat_probe_bucketed(sb_context *ctx, const sb_flat *tree, const sb_probe_args &args, uint32_t *out_probe,
                             uint32_t *out_build, uint64_t capacity, uint64_t *count);
 
+// bucket_probe.cu : cell-sorted bulk point probe (v3): probes sorted by (bucket, sub-cell), warp-uniform entry lists
+int sbi_flat_probe_cells(sb_context *ctx, const sb_flat *tree, const sb_probe_args &args, uint32_t *out_probe,
+                         uint32_t *out_build, uint64_t capacity, uint64_t *count);
+
 // refine.cu
 int sbi_pack_box2d(sb_context *ctx, const double *x0, const double *y0, const double *x1, const double *y1, uint64_t n,
                    double *out4);

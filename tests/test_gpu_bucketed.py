@@ -1,5 +1,6 @@
-"""-m gpu: the bucketed bulk probe (bucket_probe.cu, probe_path=2) against the oracle and against the per-probe tree
-walk (probe_path=1): identical pair sets on uniform, skewed, degenerate and boundary-heavy inputs."""
+"""-m gpu: the bulk point probes (bucket_probe.cu: probe_path=2 bucketed v2, probe_path=3 cell-sorted v3, the default)
+against the oracle and against the per-probe tree walk (probe_path=1): identical pair sets on uniform, skewed,
+degenerate and boundary-heavy inputs."""
 import numpy as np
 import pytest
 
@@ -18,9 +19,13 @@ def sort_pairs(p, b):
     return a[np.lexsort((a[:, 1], a[:, 0]))]
 
 
-def both_paths(ctx, fn):
+PATHS = (1, 2, 3)
+NAMES = {1: "tree walk", 2: "bucketed probe (v2)", 3: "cell-sorted probe (v3)"}
+
+
+def all_paths(ctx, fn):
     out = []
-    for path in (1, 2):
+    for path in PATHS:
         ctx.set_option("probe_path", path)
         try:
             out.append(fn())
@@ -31,12 +36,12 @@ def both_paths(ctx, fn):
 
 def check_join(ctx, O, px, py, b, pred):
     name = "intersects" if pred == 0 else "within"
-    (p1, b1), (p2, b2) = both_paths(ctx, lambda: ctx.spatial_join_points_boxes(px, py, *b, predicate=name, capacity=4096))
+    res = all_paths(ctx, lambda: ctx.spatial_join_points_boxes(px, py, *b, predicate=name, capacity=4096))
     exp, _ = O.join_points_boxes(px, py, *b, pred=pred)
     e = sort_pairs(exp[:, 0], exp[:, 1]) if len(exp) else np.zeros((0, 2), np.int64)
-    g1, g2 = sort_pairs(p1, b1), sort_pairs(p2, b2)
-    assert g1.shape == e.shape and (g1 == e).all(), "tree walk differs from the oracle"
-    assert g2.shape == e.shape and (g2 == e).all(), "bucketed probe differs from the oracle"
+    for path, (p, bb) in zip(PATHS, res):
+        g = sort_pairs(p, bb)
+        assert g.shape == e.shape and (g == e).all(), NAMES[path] + " differs from the oracle"
     return len(e)
 
 
@@ -146,9 +151,10 @@ def test_candidate_mode_matches_tree_lookup(ctx, sb, O):
     px[1000:1500] = np.nextafter(px[:500], -np.inf)
     py[1000:1500] = py[:500]
     px[1500], py[1501] = np.nan, np.nan
-    (p1, b1), (p2, b2) = both_paths(ctx, lambda: tree.probe_points(px, py))
-    g1, g2 = sort_pairs(p1, b1), sort_pairs(p2, b2)
+    (p1, b1), (p2, b2), (p3, b3) = all_paths(ctx, lambda: tree.probe_points(px, py))
+    g1, g2, g3 = sort_pairs(p1, b1), sort_pairs(p2, b2), sort_pairs(p3, b3)
     assert g1.shape == g2.shape and (g1 == g2).all()
+    assert g1.shape == g3.shape and (g1 == g3).all()
     ot = O.FlatTree(box, 32, sort_mode=0)
     k = 3000
     qb = O.bbox_from_points(px[:k], py[:k])
@@ -157,7 +163,8 @@ def test_candidate_mode_matches_tree_lookup(ctx, sb, O):
     assert (g2[sel] == sort_pairs([e[0] for e in exp], [e[1] for e in exp])).all()
 
 
-def test_index_base_and_capacity(ctx, sb, O):
+@pytest.mark.parametrize("path", [2, 3])
+def test_index_base_and_capacity(ctx, sb, O, path):
     import ctypes as C
 
     rng = np.random.default_rng(23)
@@ -168,7 +175,7 @@ def test_index_base_and_capacity(ctx, sb, O):
     tree = sb.FlatRTree(ctx, box, 32)
     px, py = rng.uniform(0, 1000, n), rng.uniform(0, 1000, n)
     b2d = np.ascontiguousarray(np.stack(b, 1))
-    ctx.set_option("probe_path", 2)
+    ctx.set_option("probe_path", path)
     try:
         p, bb = tree.probe_points(px, py, b2d, "intersects", index_base=1000000)
         # too-small capacity: SB_ERR_CAPACITY with the needed count, nothing written past the end
@@ -202,7 +209,7 @@ def test_host_pipeline_chunks(ctx, O):
     e = sort_pairs(exp[:, 0], exp[:, 1])
     ctx.set_option("pipe_chunk", 4096)
     try:
-        for path in (1, 2):
+        for path in PATHS:
             ctx.set_option("probe_path", path)
             p, bb = ctx.spatial_join_points_boxes(px, py, *b, capacity=len(e) + 5)
             g = sort_pairs(p, bb)
@@ -219,3 +226,20 @@ def test_host_pipeline_chunks(ctx, O):
     finally:
         ctx.set_option("probe_path", 0)
         ctx.set_option("pipe_chunk", 16 << 20)
+
+
+def test_heavy_sub_cell(ctx, O):
+    # 400k probes inside ONE sub-cell of the quantiser grid (70k of them identical): a v3 warp owns a sub-cell, so this
+    # is its worst-balanced input; boxes around the cluster are partly definite covers, partly edge cases
+    rng = np.random.default_rng(41)
+    n = 400000
+    px = np.concatenate([rng.uniform(500.0, 500.5, n - 70000), np.full(70000, 500.25)])
+    py = np.concatenate([rng.uniform(500.0, 500.5, n - 70000), np.full(70000, 500.25)])
+    m = 3000
+    cx, cy = rng.uniform(0, 1000, m), rng.uniform(0, 1000, m)
+    w = rng.uniform(1, 30, m)
+    cx[:40], cy[:40] = rng.uniform(499.5, 501, 40), rng.uniform(499.5, 501, 40)
+    w[:40] = rng.uniform(0.05, 3, 40)
+    cx[40], cy[40], w[40] = 500.25, 500.25, 0.0  # degenerate box exactly on the identical points
+    check_join(ctx, O, px, py, [cx - w, cy - w, cx + w, cy + w], 0)
+    check_join(ctx, O, px, py, [cx - w, cy - w, cx + w, cy + w], 1)
