@@ -1142,8 +1142,8 @@ __device__ __forceinline__ void cpp_st2_if(uint32_t *p0, uint32_t v0, uint32_t *
 
 // writes the pairs of one batch: entry-major; definite entries emit every point of the batch, tested entries their
 // ballot-compacted hits. `base` is warp-uniform; offsets inside the batch are 32-bit.
-template <bool GUARD>
-__device__ __forceinline__ void cpp_write(const uint32_t (&id)[CPP_RB], const uint32_t (&mk)[CPP_RB], uint32_t defm,
+template <bool GUARD, int NR>
+__device__ __forceinline__ void cpp_write(const uint32_t (&id)[NR], const uint32_t (&mk)[NR], uint32_t defm,
                                           const uint16_t *ep, uint32_t ne, uint32_t npts, const uint32_t *cidx,
                                           unsigned long long base, uint64_t capacity, uint32_t *__restrict__ out_probe,
                                           uint32_t *__restrict__ out_build) {
@@ -1159,22 +1159,120 @@ __device__ __forceinline__ void cpp_write(const uint32_t (&id)[CPP_RB], const ui
 		const uint32_t bi = cidx[ep[e]];
 		if ((defm >> e) & 1u) {
 #pragma unroll
-			for (int r = 0; r < CPP_RB; r++) {
-				if ((uint32_t)(r & ~1) * 32u < npts) { // rounds are enabled in pairs (one uniform branch per two rounds)
-					const uint32_t o = off + (unsigned)r * 32u + lane;
-					cpp_st2_if(pp + o, id[r], pb + o, bi, ((unsigned)r * 32u + lane < npts) && (!GUARD || o < room));
-				}
+			for (int r = 0; r < NR; r++) {
+				const uint32_t o = off + (unsigned)r * 32u + lane;
+				cpp_st2_if(pp + o, id[r], pb + o, bi,
+				           (r < NR - 1 || (unsigned)r * 32u + lane < npts) && (!GUARD || o < room));
 			}
 			off += npts;
 		} else {
 #pragma unroll
-			for (int r = 0; r < CPP_RB; r++) {
-				if ((uint32_t)(r & ~1) * 32u < npts) {
-					const uint32_t m = __shfl_sync(0xFFFFFFFFu, mk[r], e);
-					const uint32_t o = off + __popc(m & lt);
-					cpp_st2_if(pp + o, id[r], pb + o, bi, GUARD ? ((m & eq) && o < room) : (m & eq));
-					off += __popc(m);
+			for (int r = 0; r < NR; r++) {
+				const uint32_t m = __shfl_sync(0xFFFFFFFFu, mk[r], e);
+				const uint32_t o = off + __popc(m & lt);
+				cpp_st2_if(pp + o, id[r], pb + o, bi, GUARD ? ((m & eq) && o < room) : (m & eq));
+				off += __popc(m);
+			}
+		}
+	}
+}
+
+struct cpp_args {
+	const float4 *boxes;
+	const double4 *build_box2d;
+	int pred;
+	const uint2 *rec;
+	const double *px, *py;
+	uint32_t index_base;
+	uint32_t *out_probe, *out_build;
+	uint64_t capacity;
+	unsigned long long *counter;
+};
+
+// One batch = the points [pb, pb + npts) of one sub-cell (NR = ceil(npts / 32) rounds of 32 lanes, only the last round
+// may be partial) against the sub-cell's entry list and the bucket's wide list, 32 entries at a time.
+template <int MODE, int NR>
+__device__ __forceinline__ void cpp_batch(cpp_smem<MODE> &S, const cpp_args &A, unsigned wlane, uint32_t pb, uint32_t npts,
+                                          uint32_t lb, uint32_t n0, uint32_t n_wide, uint32_t sx0, uint32_t sy0) {
+	uint32_t PqC[NR], id[NR];
+#pragma unroll
+	for (int r = 0; r < NR; r++) {
+		PqC[r] = BPP_C;
+		id[r] = 0;
+		if (r < NR - 1 || (unsigned)r * 32u + wlane < npts) {
+			const uint2 v = A.rec[pb + r * 32 + wlane];
+			PqC[r] = v.x | BPP_C;
+			id[r] = v.y;
+		}
+	}
+	const uint32_t last_mask = npts - (NR - 1) * 32u >= 32u ? 0xFFFFFFFFu : ((1u << (npts - (NR - 1) * 32u)) - 1u);
+	for (int pass = 0; pass < 2; pass++) {
+		const uint16_t *list = pass == 0 ? S.ent + lb : S.wide;
+		const uint32_t nl = pass == 0 ? n0 : n_wide;
+		for (uint32_t e0 = 0; e0 < nl; e0 += 32) {
+			const uint16_t *ep = list + e0;
+			const uint32_t ne = min(nl - e0, 32u);
+			uint32_t mk[NR];
+#pragma unroll
+			for (int r = 0; r < NR; r++) {
+				mk[r] = 0;
+			}
+			uint32_t defm = 0;
+			for (uint32_t e = 0; e < ne; e++) {
+				const uint32_t j = ep[e];
+				const uint2 qb = S.qbox[j];
+				const uint32_t hi = qb.y & ~BPP_C;
+				const uint32_t lx0 = qb.x & 0xFFFFu, ly0 = qb.x >> 16, lx1 = hi & 0xFFFFu, ly1 = hi >> 16;
+				if (lx0 < sx0 && sx0 + 1023u < lx1 && ly0 < sy0 && sy0 + 1023u < ly1) {
+					defm |= 1u << e; // strictly covers the sub-cell: every point is an exact hit
+					continue;
 				}
+				// per 16-bit half: t1 = 0x8000 + (p - lo), t2 = 0x8000 + (hi - p); s1 / s2 = the same minus 1.
+				// bit 15 of t <=> that side holds (closed), of s <=> it holds strictly. hiC2 - PqC == qb.y - Pq.
+				const uint32_t lo = qb.x, hiC2 = qb.y + BPP_C, loK = lo + BPP_K, hiK = hiC2 - BPP_K;
+				const bool mine = wlane == e;
+#pragma unroll
+				for (int r = 0; r < NR; r++) {
+					const uint32_t s1 = PqC[r] - loK, s2 = hiK - PqC[r];
+					uint32_t ms = __ballot_sync(0xFFFFFFFFu, (s1 & s2 & BPP_C) == BPP_C);
+					const uint32_t t1 = PqC[r] - lo, t2 = hiC2 - PqC[r];
+					const bool closed = (t1 & t2 & BPP_C) == BPP_C;
+					const uint32_t mc = __ballot_sync(0xFFFFFFFFu, closed);
+					if (mc != ms) {
+						// some lane sits exactly on a quantised bound of this entry: the exact predicate decides
+						bool h = false;
+						if (closed && !((ms >> wlane) & 1u) && (r < NR - 1 || (unsigned)r * 32u + wlane < npts)) {
+							const uint32_t o = id[r] - A.index_base;
+							h = bp_exact<MODE>(A.px[o], A.py[o], MODE == 1 ? S.cpos[j] : 0u, S.cidx[j], A.boxes, A.build_box2d,
+							                   A.pred);
+						}
+						ms |= __ballot_sync(0xFFFFFFFFu, h);
+					}
+					if (mine) {
+						mk[r] = ms;
+					}
+				}
+			}
+			// lanes past the end of the batch carry PqC = 0|C: drop whatever they matched
+			mk[NR - 1] &= last_mask;
+			uint32_t cnt = 0;
+#pragma unroll
+			for (int r = 0; r < NR; r++) {
+				cnt += __popc(mk[r]);
+			}
+			cnt = __reduce_add_sync(0xFFFFFFFFu, cnt) + __popc(defm) * npts;
+			if (cnt == 0) {
+				continue;
+			}
+			unsigned long long base = 0;
+			if (wlane == 0) {
+				base = atomicAdd(A.counter, (unsigned long long)cnt);
+			}
+			base = __shfl_sync(0xFFFFFFFFu, base, 0);
+			if (base + cnt <= A.capacity) {
+				cpp_write<false, NR>(id, mk, defm, ep, ne, npts, S.cidx, base, A.capacity, A.out_probe, A.out_build);
+			} else {
+				cpp_write<true, NR>(id, mk, defm, ep, ne, npts, S.cidx, base, A.capacity, A.out_probe, A.out_build);
 			}
 		}
 	}
@@ -1341,6 +1439,7 @@ __global__ void __launch_bounds__(BPP_THREADS, 1)
 			// ---- (d) warps take sub-cells; all 32 lanes share the sub-cell's entry list ----
 			unsigned wlane = lane;
 			asm volatile("" : "+r"(wlane)); // a register copy of the lane id (otherwise re-read from SR_TID per use)
+			const cpp_args A = {boxes, build_box2d, pred, rec, px, py, index_base, out_probe, out_build, capacity, counter};
 			while (true) {
 				uint32_t sc = 0;
 				if (lane == 0) {
@@ -1359,101 +1458,15 @@ __global__ void __launch_bounds__(BPP_THREADS, 1)
 				const uint32_t sx0 = (sc & 31u) << 10, sy0 = (sc >> 5) << 10;
 				for (uint32_t pb = p0; pb < p1; pb += 32 * CPP_RB) {
 					const uint32_t npts = min(p1 - pb, (uint32_t)(32 * CPP_RB));
-					uint32_t PqC[CPP_RB], id[CPP_RB];
-#pragma unroll
-					for (int r = 0; r < CPP_RB; r++) {
-						const uint32_t i = pb + r * 32 + lane;
-						PqC[r] = BPP_C;
-						id[r] = 0;
-						if (i < p1) {
-							const uint2 v = rec[i];
-							PqC[r] = v.x | BPP_C;
-							id[r] = v.y;
-						}
-					}
-					for (int pass = 0; pass < 2; pass++) {
-						const uint16_t *list = pass == 0 ? S.ent + lb : S.wide;
-						const uint32_t nl = pass == 0 ? n0 : n_wide;
-						for (uint32_t e0 = 0; e0 < nl; e0 += 32) {
-							const uint16_t *ep = list + e0;
-							const uint32_t ne = min(nl - e0, 32u);
-							uint32_t mk[CPP_RB];
-#pragma unroll
-							for (int r = 0; r < CPP_RB; r++) {
-								mk[r] = 0;
-							}
-							uint32_t defm = 0;
-							for (uint32_t e = 0; e < ne; e++) {
-								const uint32_t j = ep[e];
-								const uint2 qb = S.qbox[j];
-								const uint32_t hi = qb.y & ~BPP_C;
-								const uint32_t lx0 = qb.x & 0xFFFFu, ly0 = qb.x >> 16, lx1 = hi & 0xFFFFu, ly1 = hi >> 16;
-								if (lx0 < sx0 && sx0 + 1023u < lx1 && ly0 < sy0 && sy0 + 1023u < ly1) {
-									defm |= 1u << e; // strictly covers the sub-cell: every point is an exact hit
-									continue;
-								}
-								// per 16-bit half: t1 = 0x8000 + (p - lo), t2 = 0x8000 + (hi - p); s1 / s2 = the same minus 1.
-								// bit 15 of t <=> that side holds (closed), of s <=> it holds strictly. hiC2 - PqC == qb.y - Pq.
-								const uint32_t lo = qb.x, hiC2 = qb.y + BPP_C, loK = lo + BPP_K, hiK = hiC2 - BPP_K;
-								const bool mine = wlane == e;
-								uint32_t tie = 0;
-#pragma unroll
-								for (int r = 0; r < CPP_RB; r++) {
-									if ((uint32_t)(r & ~1) * 32u < npts) { // rounds are enabled in pairs
-										const uint32_t s1 = PqC[r] - loK, s2 = hiK - PqC[r];
-										const uint32_t ms = __ballot_sync(0xFFFFFFFFu, (s1 & s2 & BPP_C) == BPP_C);
-										const uint32_t t1 = PqC[r] - lo, t2 = hiC2 - PqC[r];
-										const uint32_t mc = __ballot_sync(0xFFFFFFFFu, (t1 & t2 & BPP_C) == BPP_C);
-										tie |= mc ^ ms;
-										if (mine) {
-											mk[r] = ms;
-										}
-									}
-								}
-								if (tie) {
-									// some lane sits exactly on a quantised bound of this entry: the exact predicate decides
-#pragma unroll
-									for (int r = 0; r < CPP_RB; r++) {
-										if ((uint32_t)r * 32u < npts) {
-											const uint32_t s1 = PqC[r] - loK, s2 = hiK - PqC[r];
-											const uint32_t t1 = PqC[r] - lo, t2 = hiC2 - PqC[r];
-											bool h = false;
-											if ((t1 & t2 & BPP_C) == BPP_C && (s1 & s2 & BPP_C) != BPP_C && (uint32_t)r * 32u + lane < npts) {
-												const uint32_t o = id[r] - index_base;
-												h = bp_exact<MODE>(px[o], py[o], MODE == 1 ? S.cpos[j] : 0u, S.cidx[j], boxes, build_box2d,
-												                   pred);
-											}
-											const uint32_t m = __ballot_sync(0xFFFFFFFFu, h);
-											if (mine) {
-												mk[r] |= m;
-											}
-										}
-									}
-								}
-							}
-							uint32_t cnt = 0;
-#pragma unroll
-							for (int r = 0; r < CPP_RB; r++) {
-								// lanes past the end of the batch carry PqC = 0|C: drop whatever they matched
-								const uint32_t left = npts > (uint32_t)r * 32u ? npts - (uint32_t)r * 32u : 0u;
-								mk[r] &= left >= 32u ? 0xFFFFFFFFu : ((1u << left) - 1u);
-								cnt += __popc(mk[r]);
-							}
-							cnt = __reduce_add_sync(0xFFFFFFFFu, cnt) + __popc(defm) * npts;
-							if (cnt == 0) {
-								continue;
-							}
-							unsigned long long base = 0;
-							if (lane == 0) {
-								base = atomicAdd(counter, (unsigned long long)cnt);
-							}
-							base = __shfl_sync(0xFFFFFFFFu, base, 0);
-							if (base + cnt <= capacity) {
-								cpp_write<false>(id, mk, defm, ep, ne, npts, S.cidx, base, capacity, out_probe, out_build);
-							} else {
-								cpp_write<true>(id, mk, defm, ep, ne, npts, S.cidx, base, capacity, out_probe, out_build);
-							}
-						}
+					switch ((npts + 31u) >> 5) { // one fully unrolled instance per round count: no per-round branches
+					case 1: cpp_batch<MODE, 1>(S, A, wlane, pb, npts, lb, n0, n_wide, sx0, sy0); break;
+					case 2: cpp_batch<MODE, 2>(S, A, wlane, pb, npts, lb, n0, n_wide, sx0, sy0); break;
+					case 3: cpp_batch<MODE, 3>(S, A, wlane, pb, npts, lb, n0, n_wide, sx0, sy0); break;
+					case 4: cpp_batch<MODE, 4>(S, A, wlane, pb, npts, lb, n0, n_wide, sx0, sy0); break;
+					case 5: cpp_batch<MODE, 5>(S, A, wlane, pb, npts, lb, n0, n_wide, sx0, sy0); break;
+					case 6: cpp_batch<MODE, 6>(S, A, wlane, pb, npts, lb, n0, n_wide, sx0, sy0); break;
+					case 7: cpp_batch<MODE, 7>(S, A, wlane, pb, npts, lb, n0, n_wide, sx0, sy0); break;
+					default: cpp_batch<MODE, 8>(S, A, wlane, pb, npts, lb, n0, n_wide, sx0, sy0); break;
 					}
 				}
 			}
