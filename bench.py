@@ -332,7 +332,7 @@ def run_ours(a):
         probe_avg_s = probe_ms / max(probe_n, 1) / 1e3
         algo_bytes = 16.0 * P + 8.0 * my_pairs
         achieved = algo_bytes / probe_avg_s / 1e9 if probe_avg_s > 0 else 0.0
-        roofline = {"bound": "hbm", "kernel": "k_bp_probe<2>", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+        roofline = {"bound": "hbm", "kernel": "k_cp_probe<2>", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                     "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
                     "kernel_ms": probe_ms / max(probe_n, 1), "kernel_share_of_step": probe_ms / max(ms, 1e-9),
                     "phase_ms_per_step": phases,
@@ -340,7 +340,7 @@ def run_ours(a):
         tr = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tr):
             try:
-                roofline["traffic"] = json.load(open(tr)).get("k_bp_probe_bytes_per_launch")
+                roofline["traffic"] = json.load(open(tr)).get("k_cp_probe_bytes_per_launch")
             except Exception:
                 pass
 
