@@ -703,3 +703,41 @@ extern "C" int sb_join_dwithin(sb_context *ctx, sb_mem mem, const double *ax, co
 	}
 	return s;
 }
+
+// ---- A11: LEFT / RIGHT / FULL bookkeeping --------------------------------------------------------------------------
+extern "C" int sb_join_mark_matched(sb_context *ctx, sb_mem mem, const uint32_t *pair_probe, const uint32_t *pair_build,
+                                    uint64_t count, uint32_t probe_index_base, uint8_t *probe_matched, uint64_t n_probe,
+                                    uint8_t *build_matched, uint64_t n_build) {
+	SB_BEGIN(ctx);
+	SB_ARG(count == 0 || (pair_probe != nullptr && pair_build != nullptr), "pairs");
+	const uint32_t *dp, *db;
+	SB_TRY(sb_to_device(ctx, mem, pair_probe, count, &dp));
+	SB_TRY(sb_to_device(ctx, mem, pair_build, count, &db));
+	// flags accumulate: host flag arrays go to the device, are OR-ed there and come back
+	const uint8_t *pm_in = nullptr, *bm_in = nullptr;
+	SB_TRY(sb_to_device(ctx, mem, (const uint8_t *)probe_matched, n_probe, &pm_in));
+	SB_TRY(sb_to_device(ctx, mem, (const uint8_t *)build_matched, n_build, &bm_in));
+	uint8_t *pm = const_cast<uint8_t *>(pm_in), *bm = const_cast<uint8_t *>(bm_in);
+	SB_TRY(sbi_mark_matched(ctx, dp, db, count, probe_index_base, pm, n_probe, bm, n_build));
+	SB_TRY(sb_to_host(ctx, mem, probe_matched, pm, n_probe));
+	SB_TRY(sb_to_host(ctx, mem, build_matched, bm, n_build));
+	return finish(ctx, mem);
+}
+
+extern "C" int sb_join_unmatched_rows(sb_context *ctx, sb_mem mem, const uint8_t *matched, uint64_t n, uint32_t row_base,
+                                      uint32_t *out_rows, uint64_t capacity, uint64_t *count) {
+	SB_BEGIN(ctx);
+	SB_ARG(count != nullptr, "count");
+	SB_ARG(n == 0 || matched != nullptr, "matched");
+	SB_ARG((uint64_t)row_base + n <= 0x100000000ull, "row ids must fit 32 bits");
+	const uint8_t *dm;
+	uint32_t *dout;
+	SB_TRY(sb_to_device(ctx, mem, matched, n, &dm));
+	SB_TRY(sb_out_buffer(ctx, mem, out_rows, capacity, &dout));
+	const int s = sbi_unmatched_rows(ctx, dm, n, row_base, dout, capacity, count);
+	if (s != SB_OK) {
+		return s;
+	}
+	SB_TRY(sb_to_host(ctx, mem, out_rows, dout, *count));
+	return finish(ctx, mem);
+}

@@ -113,5 +113,11 @@ int sbi_distance_points(sb_context *ctx, const double *ax, const double *ay, con
                         uint64_t n, double *out);
 int sbi_expand_points(sb_context *ctx, const double *x, const double *y, uint64_t n, double r, float *out_box4);
 
+// LEFT / RIGHT / FULL join bookkeeping (refine.cu)
+int sbi_mark_matched(sb_context *ctx, const uint32_t *pp, const uint32_t *pb, uint64_t n, uint32_t probe_base,
+                     uint8_t *pm, uint64_t n_probe, uint8_t *bm, uint64_t n_build);
+int sbi_unmatched_rows(sb_context *ctx, const uint8_t *flags, uint64_t n, uint32_t row_base, uint32_t *out,
+                       uint64_t capacity, uint64_t *count);
+
 // read a device u64 counter back (synchronises the stream)
 int sbi_read_u64(sb_context *ctx, const uint64_t *dev, uint64_t *host);

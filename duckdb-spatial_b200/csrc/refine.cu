@@ -238,3 +238,169 @@ int sbi_expand_points(sb_context *ctx, const double *x, const double *y, uint64_
 	SB_LAUNCH_CHECK(ctx);
 	return SB_OK;
 }
+
+// ---- A11: LEFT / RIGHT / FULL join bookkeeping --------------------------------------------------------------------
+// The reference marks matched probe rows in left_outer_marker[] (spatial_join_physical.cpp:867-876) and matched build
+// rows in a bool column of the build tuple (:878-891); unmatched probe rows are emitted NULL-padded per input chunk
+// (:917-938), unmatched build rows by the source scan after all probes (:1022-1068). Here: flag arrays over whole
+// columns + an order-preserving selection of the rows whose flag is 0.
+__global__ void __launch_bounds__(256) k_mark_matched(const uint32_t *__restrict__ pp, const uint32_t *__restrict__ pb,
+                                                      uint64_t n, uint32_t probe_base, uint8_t *__restrict__ pm,
+                                                      uint64_t n_probe, uint8_t *__restrict__ bm, uint64_t n_build) {
+	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+		if (pm) {
+			const uint64_t p = (uint64_t)pp[i] - probe_base;
+			if (p < n_probe) {
+				pm[p] = 1;
+			}
+		}
+		if (bm) {
+			const uint64_t b = pb[i];
+			if (b < n_build) {
+				bm[b] = 1;
+			}
+		}
+	}
+}
+
+int sbi_mark_matched(sb_context *ctx, const uint32_t *pp, const uint32_t *pb, uint64_t n, uint32_t probe_base,
+                     uint8_t *pm, uint64_t n_probe, uint8_t *bm, uint64_t n_build) {
+	if (n == 0 || (!pm && !bm)) {
+		return SB_OK;
+	}
+	k_mark_matched<<<sb_grid(n, 256, 16), 256, 0, ctx->stream>>>(pp, pb, n, probe_base, pm, n_probe, bm, n_build);
+	SB_LAUNCH_CHECK(ctx);
+	return SB_OK;
+}
+
+#define UM_TILE 4096
+__global__ void __launch_bounds__(256) k_unmatched_count(const uint8_t *__restrict__ flags, uint64_t n,
+                                                         uint32_t *__restrict__ tile_cnt) {
+	__shared__ uint32_t s_cnt;
+	for (uint64_t tile = blockIdx.x; tile * UM_TILE < n; tile += gridDim.x) {
+		if (threadIdx.x == 0) {
+			s_cnt = 0;
+		}
+		__syncthreads();
+		uint32_t c = 0;
+		for (uint32_t k = threadIdx.x; k < UM_TILE; k += 256) {
+			const uint64_t i = tile * UM_TILE + k;
+			c += (i < n && flags[i] == 0) ? 1u : 0u;
+		}
+		c = __reduce_add_sync(0xFFFFFFFFu, c);
+		if (sb_lane() == 0 && c) {
+			atomicAdd(&s_cnt, c);
+		}
+		__syncthreads();
+		if (threadIdx.x == 0) {
+			tile_cnt[tile] = s_cnt;
+		}
+		__syncthreads();
+	}
+}
+
+// exclusive scan of the tile counts by one CTA (tiles <= n / 4096: a few 10^4 at the BASELINE sizes)
+__global__ void __launch_bounds__(1024) k_unmatched_scan(uint32_t *__restrict__ tile_cnt, uint64_t tiles,
+                                                         unsigned long long *__restrict__ total) {
+	__shared__ uint32_t s_warp[32];
+	__shared__ unsigned long long s_run;
+	if (threadIdx.x == 0) {
+		s_run = 0;
+	}
+	__syncthreads();
+	for (uint64_t t0 = 0; t0 < tiles; t0 += 1024) {
+		const uint64_t t = t0 + threadIdx.x;
+		const uint32_t c = t < tiles ? tile_cnt[t] : 0u;
+		const unsigned lane = sb_lane(), warp = threadIdx.x >> 5;
+		uint32_t inc = c;
+#pragma unroll
+		for (int s = 1; s < 32; s <<= 1) {
+			const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, s);
+			if (lane >= (unsigned)s) {
+				inc += o;
+			}
+		}
+		if (lane == 31) {
+			s_warp[warp] = inc;
+		}
+		__syncthreads();
+		uint32_t wb = 0;
+		for (unsigned w = 0; w < warp; w++) {
+			wb += s_warp[w];
+		}
+		const unsigned long long run = s_run;
+		if (t < tiles) {
+			// offsets fit 32 bits: at most 2^32 rows per column (row ids are uint32)
+			tile_cnt[t] = (uint32_t)(run + wb + inc - c);
+		}
+		__syncthreads();
+		if (threadIdx.x == 1023) {
+			s_run = run + wb + inc;
+		}
+		__syncthreads();
+	}
+	if (threadIdx.x == 0) {
+		*total = s_run;
+	}
+}
+
+__global__ void __launch_bounds__(256) k_unmatched_write(const uint8_t *__restrict__ flags, uint64_t n,
+                                                         const uint32_t *__restrict__ tile_off, uint32_t row_base,
+                                                         uint32_t *__restrict__ out, uint64_t capacity) {
+	__shared__ uint32_t s_warp[8];
+	for (uint64_t tile = blockIdx.x; tile * UM_TILE < n; tile += gridDim.x) {
+		uint32_t run = tile_off[tile];
+		// 16 rounds of 256 consecutive rows keep the output ascending
+		for (uint32_t k0 = 0; k0 < UM_TILE; k0 += 256) {
+			const uint64_t i = tile * UM_TILE + k0 + threadIdx.x;
+			const bool un = i < n && flags[i] == 0;
+			const uint32_t m = __ballot_sync(0xFFFFFFFFu, un);
+			const unsigned lane = sb_lane(), warp = threadIdx.x >> 5;
+			if (lane == 0) {
+				s_warp[warp] = __popc(m);
+			}
+			__syncthreads();
+			uint32_t wb = 0, tot = 0;
+#pragma unroll
+			for (unsigned w = 0; w < 8; w++) {
+				const uint32_t c = s_warp[w];
+				wb += w < warp ? c : 0u;
+				tot += c;
+			}
+			if (un) {
+				const uint64_t o = (uint64_t)run + wb + __popc(m & sb_lanemask_lt());
+				if (o < capacity) {
+					out[o] = (uint32_t)i + row_base;
+				}
+			}
+			run += tot;
+			__syncthreads();
+		}
+	}
+}
+
+int sbi_unmatched_rows(sb_context *ctx, const uint8_t *flags, uint64_t n, uint32_t row_base, uint32_t *out,
+                       uint64_t capacity, uint64_t *count) {
+	*count = 0;
+	if (n == 0) {
+		return SB_OK;
+	}
+	const uint64_t tiles = (n + UM_TILE - 1) / UM_TILE;
+	uint32_t *d_tiles = nullptr;
+	unsigned long long *d_total = nullptr;
+	SB_TRY(ctx->scratch_t(tiles, &d_tiles));
+	SB_TRY(ctx->scratch_t(1, &d_total));
+	k_unmatched_count<<<sb_grid(tiles, 1, 16), 256, 0, ctx->stream>>>(flags, n, d_tiles);
+	SB_LAUNCH_CHECK(ctx);
+	k_unmatched_scan<<<1, 1024, 0, ctx->stream>>>(d_tiles, tiles, d_total);
+	SB_LAUNCH_CHECK(ctx);
+	k_unmatched_write<<<sb_grid(tiles, 1, 16), 256, 0, ctx->stream>>>(flags, n, d_tiles, row_base, out, capacity);
+	SB_LAUNCH_CHECK(ctx);
+	SB_TRY(sbi_read_u64(ctx, reinterpret_cast<const uint64_t *>(d_total), count));
+	if (*count > capacity) {
+		sb_set_error("unmatched rows: %llu, capacity %llu", (unsigned long long)*count, (unsigned long long)capacity);
+		return SB_ERR_CAPACITY;
+	}
+	return SB_OK;
+}

@@ -236,6 +236,52 @@ class Context:
             capi.check(rc)
             return op[: cnt.value], ob[: cnt.value]
 
+    def join_mark_matched(self, pair_probe, pair_build, n_probe, n_build, probe_index_base=0, probe_matched=None,
+                          build_matched=None):
+        """LEFT / RIGHT / FULL bookkeeping: flag arrays (uint8) with 1 for every row that appears in the pair list.
+        Existing flag arrays are OR-ed into (the build side accumulates over probe batches)."""
+        like = pair_probe
+        if probe_matched is None:
+            probe_matched = self._zeros_u8(like, n_probe)
+        if build_matched is None:
+            build_matched = self._zeros_u8(like, n_build)
+        capi.check(self.L.sb_join_mark_matched(self.h, self._mem(pair_probe, pair_build, probe_matched, build_matched),
+                                               _ptr(pair_probe), _ptr(pair_build), len(pair_probe), probe_index_base,
+                                               _ptr(probe_matched), n_probe, _ptr(build_matched), n_build))
+        return probe_matched, build_matched
+
+    def join_unmatched_rows(self, matched, row_base=0):
+        """ascending row ids (row_base + position) whose flag is 0."""
+        n = len(matched)
+        out = self._empty(matched, (max(n, 1),), np.uint32)
+        cnt = C.c_uint64(0)
+        capi.check(self.L.sb_join_unmatched_rows(self.h, self._mem(matched), _ptr(matched), n, row_base, _ptr(out), n,
+                                                 C.byref(cnt)))
+        return out[: cnt.value]
+
+    def _zeros_u8(self, like, n):
+        if _is_torch(like):
+            import torch
+
+            return torch.zeros(n, dtype=torch.uint8, device=like.device)
+        return np.zeros(n, np.uint8)
+
+    def spatial_join(self, px, py, bminx, bminy, bmaxx, bmaxy, predicate="intersects", join_type="inner", capacity=None):
+        """PhysicalSpatialJoin with join type INNER / LEFT / RIGHT / FULL (spatial_join_physical.cpp:748-938,
+        1022-1068). Returns (pairs_probe, pairs_build, unmatched_probe_rows, unmatched_build_rows): the unmatched
+        lists are what the reference emits NULL-padded; they are empty for join types that do not propagate
+        that side."""
+        jt = join_type.lower()
+        assert jt in ("inner", "left", "right", "full", "outer")
+        p, b = self.spatial_join_points_boxes(px, py, bminx, bminy, bmaxx, bmaxy, predicate, capacity)
+        empty = p[:0]
+        if jt == "inner":
+            return p, b, empty, empty
+        pm, bm = self.join_mark_matched(p, b, len(px), len(bminx))
+        up = self.join_unmatched_rows(pm) if jt in ("left", "full", "outer") else empty
+        ub = self.join_unmatched_rows(bm) if jt in ("right", "full", "outer") else empty
+        return p, b, up, ub
+
     def join_dwithin(self, ax, ay, bx, by, radius, capacity=None):
         ax, ay, bx, by = [self._f64(v) for v in (ax, ay, bx, by)]
         cap = int(capacity if capacity is not None else max(1024, 4 * len(ax)))

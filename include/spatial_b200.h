@@ -210,6 +210,20 @@ SB_API int sb_join_dwithin(sb_context *ctx, sb_mem mem, const double *ax, const 
                            const double *bx, const double *by, uint32_t nb, double radius, uint32_t *out_a,
                            uint32_t *out_b, double *out_dist, uint64_t capacity, uint64_t *count);
 
+/* ---- LEFT / RIGHT / FULL join bookkeeping ----------------------------------------------------------------------
+ * replaces the left_outer_marker[] stores (spatial_join_physical.cpp:867-876) and the matched-flag store into the
+ * build tuple (:878-891) for a whole pair list: probe_matched[pair_probe[i] - probe_index_base] = 1 and
+ * build_matched[pair_build[i]] = 1. Flags are only ever set, never cleared, so the build-side array accumulates over
+ * probe batches exactly like the tuple's match column. Either flag array may be NULL. */
+SB_API int sb_join_mark_matched(sb_context *ctx, sb_mem mem, const uint32_t *pair_probe, const uint32_t *pair_build,
+                                uint64_t count, uint32_t probe_index_base, uint8_t *probe_matched, uint64_t n_probe,
+                                uint8_t *build_matched, uint64_t n_build);
+/* rows whose flag is 0, ascending, as row_base + position: the EMIT_LHS selection of unmatched probe rows
+ * (:917-938, emitted NULL-padded on the build side) and the RIGHT / FULL source scan of unmatched build rows
+ * (PhysicalSpatialJoin::GetData :1022-1068, NULL-padded on the probe side). SB_ERR_CAPACITY when *count > capacity. */
+SB_API int sb_join_unmatched_rows(sb_context *ctx, sb_mem mem, const uint8_t *matched, uint64_t n, uint32_t row_base,
+                                  uint32_t *out_rows, uint64_t capacity, uint64_t *count);
+
 /* ---- harness utility: ST_GeneratePoints on the device ---------------------------------------------------------
  * restates ST_GeneratePoints (spatial_functions_table.cpp:82-99) on DuckDB's pcg32 RandomEngine with skip-ahead:
  * produces points [skip, skip+n) of the sequential stream of `seed`, bit-identical to the CPU generator. */

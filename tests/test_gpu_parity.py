@@ -414,3 +414,41 @@ def test_generate_points_bit_exact(ctx, O):
     xs, ys = ctx.st_generate_points(42, 1000, (-10.0, 5.0, 300.0, 77.0), skip=123457)
     ox, oy = O.generate_points(42, 1000, (-10.0, 5.0, 300.0, 77.0), skip=123457)
     assert (xs == ox).all() and (ys == oy).all()
+
+
+@pytest.mark.parametrize("jt", ["inner", "left", "right", "full"])
+def test_outer_join_bookkeeping(ctx, O, jt):
+    # LEFT / RIGHT / FULL semantics of PhysicalSpatialJoin (spatial_join_physical.cpp:867-938, 1022-1068): unmatched
+    # probe rows / unmatched build rows are emitted once, in row order
+    n, m = 150000, 40000
+    px, py = O.generate_points(1337, n, (0, 0, 1000, 1000))
+    u = O.uniform01(42, 2 * m)
+    cx, cy = u[0::2] * 1400 - 200, u[1::2] * 1400 - 200  # some boxes lie outside every point
+    b = [cx - 0.8, cy - 0.8, cx + 0.8, cy + 0.8]
+    p, bb, up, ub = ctx.spatial_join(px, py, *b, predicate="intersects", join_type=jt)
+    exp, _ = O.join_points_boxes(px, py, *b, pred=0)
+    assert (sort_pairs(p, bb) == sort_pairs(exp[:, 0], exp[:, 1])).all()
+    eup = np.setdiff1d(np.arange(n), exp[:, 0]) if jt in ("left", "full") else np.zeros(0, np.int64)
+    eub = np.setdiff1d(np.arange(m), exp[:, 1]) if jt in ("right", "full") else np.zeros(0, np.int64)
+    assert len(up) == len(eup) and (np.asarray(up, np.int64) == eup).all()
+    assert len(ub) == len(eub) and (np.asarray(ub, np.int64) == eub).all()
+    if jt == "full":
+        assert len(eup) > 1000 and len(eub) > 1000
+
+
+def test_build_flags_accumulate_over_probe_batches(ctx, O):
+    # the build-side match column accumulates over probe chunks (the tuple's bool column, :878-891)
+    n, m = 60000, 5000
+    px, py = O.generate_points(7, n, (0, 0, 100, 100))
+    u = O.uniform01(9, 2 * m)
+    cx, cy = u[0::2] * 100, u[1::2] * 100
+    b = [cx - 0.05, cy - 0.05, cx + 0.05, cy + 0.05]
+    bm = None
+    for lo in range(0, n, 20000):
+        p, bb = ctx.spatial_join_points_boxes(px[lo:lo + 20000], py[lo:lo + 20000], *b)
+        pm, bm = ctx.join_mark_matched(p, bb, 20000, m, build_matched=bm)
+        exp, _ = O.join_points_boxes(px[lo:lo + 20000], py[lo:lo + 20000], *b, pred=0)
+        assert (ctx.join_unmatched_rows(pm, row_base=lo) == np.setdiff1d(np.arange(20000), exp[:, 0]) + lo).all()
+    exp, _ = O.join_points_boxes(px, py, *b, pred=0)
+    assert (ctx.join_unmatched_rows(bm) == np.setdiff1d(np.arange(m), exp[:, 1])).all()
+    assert len(ctx.join_unmatched_rows(np.zeros(0, np.uint8))) == 0
