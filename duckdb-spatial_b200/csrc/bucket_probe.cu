@@ -26,21 +26,7 @@
 // traffic per probe.
 #include "internal.cuh"
 
-#define BP_G 32                  // buckets per axis
-#define BP_NB (BP_G * BP_G)      // 1024 buckets (+1 for points with NaN coordinates)
-#define BP_QBITS 20              // quantiser bits per axis
-#define BP_QMAX ((1 << BP_QBITS) - 1)
-#define BP_SLICE 32768u          // points per work unit
-
-struct bp_grid {
-	double minx, miny, sx, sy; // Q(v) = clamp(floor((v - min) * s), 0, BP_QMAX)
-	float tb[4];               // tree box
-};
-
-__device__ __forceinline__ int bp_q(double v, double mn, double s) {
-	const int c = __double2int_rd((v - mn) * s); // saturating; NaN -> 0
-	return min(max(c, 0), BP_QMAX);
-}
+#include "cells.cuh"
 
 __global__ void k_bp_grid_init(const sb_flat_header *__restrict__ hdr, bp_grid *__restrict__ g) {
 	if (threadIdx.x == 0) {
@@ -208,19 +194,6 @@ __global__ void __launch_bounds__(BPS_THREADS, 2)
 }
 
 // ---- 3. the tree's leaf level binned into the same buckets ----------------------------------------------------
-// Quantised extent of a leaf float box under the CANDIDATE semantics of the reference: a point x can produce a
-// float box [down(x), up(x)] that intersects [b.x, b.z] only if pred(b.x) < x < succ(b.z) (pred / succ = the
-// neighbouring floats), so [Q(pred(b.x)), Q(succ(b.z))] covers every such point. NaN bounds never exclude
-// (Box::Intersects, bbox.hpp:27-29, is written with negated comparisons) => open-ended.
-__device__ __forceinline__ void bp_leaf_range(const float4 b, const bp_grid &g, int &x0, int &y0, int &x1, int &y1) {
-	const float ax = nextafterf(b.x, -INFINITY), ay = nextafterf(b.y, -INFINITY);
-	const float cx = nextafterf(b.z, INFINITY), cy = nextafterf(b.w, INFINITY);
-	x0 = ax != ax ? 0 : bp_q((double)ax, g.minx, g.sx);
-	y0 = ay != ay ? 0 : bp_q((double)ay, g.miny, g.sy);
-	x1 = cx != cx ? BP_QMAX : bp_q((double)cx, g.minx, g.sx);
-	y1 = cy != cy ? BP_QMAX : bp_q((double)cy, g.miny, g.sy);
-}
-
 template <bool FILL>
 __global__ void __launch_bounds__(256) k_bp_cand(const float4 *__restrict__ boxes, uint32_t items,
                                                  const bp_grid *__restrict__ gp, uint32_t *__restrict__ counter,
@@ -242,23 +215,6 @@ __global__ void __launch_bounds__(256) k_bp_cand(const float4 *__restrict__ boxe
 }
 
 // ---- offsets, cursors and the work-unit table -----------------------------------------------------------------
-struct bp_unit {
-	uint32_t bucket, pbeg, pend;
-};
-// tables: [0] pt_hist (1025) [1] pt_off (1026) [2] pt_cursor (1025) [3] cand_cnt (1024) [4] cand_off (1025)
-//         [5] cand_cursor (1024); totals: {points kept (no NaN), candidates, units, NaN points}
-struct bp_tables {
-	uint32_t pt_hist[BP_NB + 1];
-	uint32_t pt_off[BP_NB + 2];
-	uint32_t pt_cursor[BP_NB + 1];
-	uint32_t cand_cnt[BP_NB];
-	uint32_t cand_off[BP_NB + 1];
-	uint32_t cand_cursor[BP_NB];
-	uint32_t ticket;
-	uint32_t pad;
-	uint64_t totals[4];
-};
-
 __device__ __forceinline__ uint32_t bp_block_excl_scan_1024(uint32_t v, uint32_t *s_warp, uint32_t *total) {
 	// blockDim.x == 1024
 	const unsigned lane = sb_lane(), warp = threadIdx.x >> 5;
@@ -1488,43 +1444,32 @@ __global__ void __launch_bounds__(256) k_cp_unpack(const uint2 *__restrict__ rec
 	}
 }
 
-int sbi_flat_probe_cells(sb_context *ctx, const sb_flat *tree, const sb_probe_args &a, uint32_t *out_probe,
-                         uint32_t *out_build, uint64_t capacity, uint64_t *count) {
-	*count = 0;
-	const uint64_t n = a.m;
+// Front end shared by the cell-sorted probe and the point-in-polygon join (pip_join.cu): partitions the probe points
+// into (bucket, sub-cell) cells of the tree box's quantiser grid and bins the tree's leaf level into the buckets.
+int sbi_cell_partition(sb_context *ctx, const sb_flat *tree, const double *px, const double *py, uint64_t n,
+                       uint32_t index_base, sb_cell_partition *P) {
 	const uint32_t items = tree->h.item_count;
-	if (n == 0 || items == 0) {
-		return SB_OK;
-	}
-	SB_ARG(a.px != nullptr && a.py != nullptr, "cell probe takes points");
-	SB_ARG(n + a.index_base <= 0xFFFFFFFFull, "probe indices must fit 32 bits");
-	const int mode = a.pred >= 0 ? 2 : 1;
-	SB_ARG(mode == 1 || a.build_box2d != nullptr, "build_box2d");
-
 	bp_grid *d_grid = nullptr;
 	bp_tables *d_tab = nullptr;
 	bp_unit *d_units = nullptr;
 	uint2 *d_rec_a = nullptr, *d_rec_b = nullptr;
 	uint32_t *d_cand = nullptr, *d_fine = nullptr, *d_cell_off = nullptr;
-	unsigned long long *d_counter = nullptr;
 	const uint64_t max_units = n / BP_SLICE + BP_NB + 1;
 	SB_TRY(ctx->scratch_t(1, &d_grid));
 	SB_TRY(ctx->scratch_t(1, &d_tab));
 	SB_TRY(ctx->scratch_t(max_units, &d_units));
-	SB_TRY(ctx->scratch_t(1, &d_counter));
 	SB_TRY(ctx->scratch_t(n, &d_rec_a));
 	SB_TRY(ctx->scratch_t(n, &d_rec_b));
 	SB_TRY(ctx->scratch_t(CP_NCELL, &d_fine));
 	SB_TRY(ctx->scratch_t(CP_NCELL + 1, &d_cell_off));
 	SB_CUDA(cudaMemsetAsync(d_tab, 0, sizeof(bp_tables), ctx->stream));
-	SB_CUDA(cudaMemsetAsync(d_counter, 0, sizeof(*d_counter), ctx->stream));
 	SB_CUDA(cudaMemsetAsync(d_fine, 0, sizeof(uint32_t) * CP_NCELL, ctx->stream));
 	const sb_flat_header *d_hdr = static_cast<const sb_flat_header *>(tree->buffer);
 	{
 		sb_prof_scope ps(ctx, "bp_partition");
 		k_bp_grid_init<<<1, 32, 0, ctx->stream>>>(d_hdr, d_grid);
 		SB_LAUNCH_CHECK(ctx);
-		k_bp_hist<<<sb_grid(n, BPH_THREADS * 8, 4), BPH_THREADS, 0, ctx->stream>>>(a.px, a.py, n, d_grid, d_tab->pt_hist, nullptr);
+		k_bp_hist<<<sb_grid(n, BPH_THREADS * 8, 4), BPH_THREADS, 0, ctx->stream>>>(px, py, n, d_grid, d_tab->pt_hist, nullptr);
 		SB_LAUNCH_CHECK(ctx);
 	}
 	{
@@ -1540,25 +1485,24 @@ int sbi_flat_probe_cells(sb_context *ctx, const sb_flat *tree, const sb_probe_ar
 	SB_CUDA(cudaMemcpyAsync(ctx->pinned_u64, d_tab->totals, sizeof(totals), cudaMemcpyDeviceToHost, ctx->stream));
 	SB_CUDA(cudaStreamSynchronize(ctx->stream));
 	memcpy(totals, ctx->pinned_u64, sizeof(totals));
-	const uint64_t n_cand = totals[1], n_units = totals[2], n_nan = totals[3];
+	const uint64_t n_cand = totals[1], n_units = totals[2];
 	SB_ARG(n_cand < 0xFFFFFFFFull, "cell probe: candidate directory too large");
 	SB_TRY(ctx->scratch_t(n_cand ? n_cand : 1, &d_cand));
 	static bool attr_set = false;
 	if (!attr_set) {
 		SB_CUDA(cudaFuncSetAttribute(k_cp_scatter1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(cps1_smem)));
 		SB_CUDA(cudaFuncSetAttribute(k_cp_scatter2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(cps2_smem)));
-		SB_CUDA(cudaFuncSetAttribute(k_cp_probe<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(cpp_smem<1>)));
-		SB_CUDA(cudaFuncSetAttribute(k_cp_probe<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(cpp_smem<2>)));
 		attr_set = true;
 	}
 	{
 		sb_prof_scope ps(ctx, "bp_partition");
-		k_cp_scatter1<<<sb_grid(n, CP_TILE1, 1), 1024, sizeof(cps1_smem), ctx->stream>>>(
-		    a.px, a.py, n, a.index_base, d_grid, d_tab->pt_cursor, d_fine, d_rec_a);
+		k_cp_scatter1<<<sb_grid(n, CP_TILE1, 1), 1024, sizeof(cps1_smem), ctx->stream>>>(px, py, n, index_base, d_grid,
+		                                                                                d_tab->pt_cursor, d_fine, d_rec_a);
+		SB_LAUNCH_CHECK(ctx);
+		// (cell_off is needed even without units: consumers index it for every cell)
+		k_cp_scan2<<<BP_NB, 1024, 0, ctx->stream>>>(d_tab, d_fine, d_cell_off);
 		SB_LAUNCH_CHECK(ctx);
 		if (n_units) {
-			k_cp_scan2<<<BP_NB, 1024, 0, ctx->stream>>>(d_tab, d_fine, d_cell_off);
-			SB_LAUNCH_CHECK(ctx);
 			k_cp_scatter2<<<sb_grid(2 * n_units, 1, 1), 1024, sizeof(cps2_smem), ctx->stream>>>(d_tab, d_units, d_rec_a, d_fine,
 			                                                                                   d_rec_b);
 			SB_LAUNCH_CHECK(ctx);
@@ -1571,6 +1515,53 @@ int sbi_flat_probe_cells(sb_context *ctx, const sb_flat *tree, const sb_probe_ar
 		SB_LAUNCH_CHECK(ctx);
 	}
 	SB_TRACE(ctx, "cp: scatter passes + cand fill");
+	P->grid = d_grid;
+	P->tables = d_tab;
+	P->units = d_units;
+	P->cand_pos = d_cand;
+	P->rec_bucketed = d_rec_a;
+	P->rec = d_rec_b;
+	P->cell_off = d_cell_off;
+	P->n_kept = totals[0];
+	P->n_cand = n_cand;
+	P->n_units = n_units;
+	P->n_nan = totals[3];
+	return SB_OK;
+}
+
+int sbi_flat_probe_cells(sb_context *ctx, const sb_flat *tree, const sb_probe_args &a, uint32_t *out_probe,
+                         uint32_t *out_build, uint64_t capacity, uint64_t *count) {
+	*count = 0;
+	const uint64_t n = a.m;
+	const uint32_t items = tree->h.item_count;
+	if (n == 0 || items == 0) {
+		return SB_OK;
+	}
+	SB_ARG(a.px != nullptr && a.py != nullptr, "cell probe takes points");
+	SB_ARG(n + a.index_base <= 0xFFFFFFFFull, "probe indices must fit 32 bits");
+	const int mode = a.pred >= 0 ? 2 : 1;
+	SB_ARG(mode == 1 || a.build_box2d != nullptr, "build_box2d");
+
+	unsigned long long *d_counter = nullptr;
+	SB_TRY(ctx->scratch_t(1, &d_counter));
+	SB_CUDA(cudaMemsetAsync(d_counter, 0, sizeof(*d_counter), ctx->stream));
+	sb_cell_partition P;
+	SB_TRY(sbi_cell_partition(ctx, tree, a.px, a.py, n, a.index_base, &P));
+	const bp_grid *d_grid = static_cast<const bp_grid *>(P.grid);
+	bp_tables *d_tab = static_cast<bp_tables *>(P.tables);
+	const bp_unit *d_units = static_cast<const bp_unit *>(P.units);
+	const uint32_t *d_cand = P.cand_pos, *d_cell_off = P.cell_off;
+	const uint2 *d_rec_a = static_cast<const uint2 *>(P.rec_bucketed), *d_rec_b = static_cast<const uint2 *>(P.rec);
+	const uint64_t n_units = P.n_units, n_nan = P.n_nan;
+	uint64_t totals[1] = {P.n_kept};
+	{
+		static bool attr_set = false;
+		if (!attr_set) {
+			SB_CUDA(cudaFuncSetAttribute(k_cp_probe<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(cpp_smem<1>)));
+			SB_CUDA(cudaFuncSetAttribute(k_cp_probe<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(cpp_smem<2>)));
+			attr_set = true;
+		}
+	}
 	if (n_units) {
 		const unsigned grid = (unsigned)(n_units < SB_NUM_SMS ? n_units : SB_NUM_SMS);
 		sb_prof_scope ps(ctx, "flat_probe");

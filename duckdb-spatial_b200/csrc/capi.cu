@@ -741,3 +741,63 @@ extern "C" int sb_join_unmatched_rows(sb_context *ctx, sb_mem mem, const uint8_t
 	SB_TRY(sb_to_host(ctx, mem, out_rows, dout, *count));
 	return finish(ctx, mem);
 }
+
+// ---- ST_Within(point, polygon) join ---------------------------------------------------------------------------------
+int sbi_pip_boxes(sb_context *ctx, const double *vx, const double *vy, const uint64_t *ring_off, const uint64_t *poly_off,
+                  uint64_t n_polys, float *out_box4);
+
+extern "C" int sb_join_points_polygons(sb_context *ctx, sb_mem mem, const double *px, const double *py, uint64_t n_points,
+                                       const double *vx, const double *vy, const uint64_t *ring_vert_off,
+                                       const uint64_t *poly_ring_off, uint64_t n_polys, uint64_t n_rings, uint64_t n_verts,
+                                       uint32_t *out_point, uint32_t *out_poly, uint64_t capacity, uint64_t *count) {
+	SB_BEGIN(ctx);
+	SB_ARG(count != nullptr, "count");
+	*count = 0;
+	const double *dpx, *dpy, *dvx, *dvy;
+	const uint64_t *dro, *dpo;
+	SB_TRY(sb_to_device(ctx, mem, px, n_points, &dpx));
+	SB_TRY(sb_to_device(ctx, mem, py, n_points, &dpy));
+	SB_TRY(sb_to_device(ctx, mem, vx, n_verts, &dvx));
+	SB_TRY(sb_to_device(ctx, mem, vy, n_verts, &dvy));
+	SB_TRY(sb_to_device(ctx, mem, ring_vert_off, n_rings + 1, &dro));
+	SB_TRY(sb_to_device(ctx, mem, poly_ring_off, n_polys + 1, &dpo));
+	uint32_t *dop, *dob;
+	SB_TRY(sb_out_buffer(ctx, mem, out_point, capacity, &dop));
+	SB_TRY(sb_out_buffer(ctx, mem, out_poly, capacity, &dob));
+	if (n_points == 0 || n_polys == 0) {
+		return finish(ctx, mem);
+	}
+	int s;
+	// polygon-centric kernel when every polygon sees many probes (option "pip_path": 1 = candidate list, 2 = polygon-centric)
+	const bool centric = ctx->pip_path == 2 || (ctx->pip_path == 0 && n_points >= (1u << 17) && n_points / n_polys >= 32);
+	if (centric) {
+		s = sbi_join_points_polygons(ctx, dpx, dpy, n_points, dvx, dvy, dro, dpo, n_polys, dop, dob, capacity, count);
+	} else {
+		float *fbox = nullptr;
+		SB_TRY(ctx->scratch_t(4 * n_polys, &fbox));
+		SB_TRY(sbi_pip_boxes(ctx, dvx, dvy, dro, dpo, n_polys, fbox));
+		sb_flat *tree = nullptr;
+		s = sbi_flat_build(ctx, fbox, (uint32_t)n_polys, 32, &tree);
+		uint64_t cand = 0;
+		if (s == SB_OK) {
+			sb_probe_args a;
+			a.px = dpx;
+			a.py = dpy;
+			a.m = n_points;
+			s = sbi_flat_probe(ctx, tree, a, dop, dob, capacity, &cand);
+			*count = cand;
+		}
+		if (s == SB_OK) {
+			s = sbi_refine_point_polygon(ctx, dpx, dpy, dvx, dvy, dro, dpo, dop, dob, cand, count);
+		}
+		if (tree) {
+			sb_flat_destroy(tree);
+		}
+	}
+	if (s != SB_OK) {
+		return s;
+	}
+	SB_TRY(sb_to_host(ctx, mem, out_point, dop, *count));
+	SB_TRY(sb_to_host(ctx, mem, out_poly, dob, *count));
+	return finish(ctx, mem);
+}

@@ -87,6 +87,8 @@ struct sb_context {
 	// sb_context_set_option("probe_path"): 0 = auto (bulk point probes take the bucketed kernel), 1 = always the
 	// per-probe tree walk, 2 = always bucketed
 	int probe_path = 0;
+	// sb_context_set_option("pip_path"): 0 = auto, 1 = FlatRTree candidates + per-pair refinement, 2 = polygon-centric
+	int pip_path = 0;
 	// sb_context_set_option("trace", 1): synchronise at SB_TRACE points and print the wall time of each phase
 	int trace = 0;
 	double trace_t0 = 0;

@@ -171,6 +171,11 @@ extern "C" int sb_context_set_option(sb_context *ctx, const char *key, int64_t v
 		ctx->probe_path = (int)value;
 		return SB_OK;
 	}
+	if (strcmp(key, "pip_path") == 0) {
+		SB_ARG(value >= 0 && value <= 2, "pip_path must be 0 (auto), 1 (candidate list + refine) or 2 (polygon-centric)");
+		ctx->pip_path = (int)value;
+		return SB_OK;
+	}
 	if (strcmp(key, "pipe_chunk") == 0) {
 		SB_ARG(value >= 1024, "pipe_chunk must be >= 1024 rows");
 		ctx->pipe_chunk = (uint64_t)value;

@@ -98,6 +98,27 @@ int sbi_flat_probe_bucketed(sb_context *ctx, const sb_flat *tree, const sb_probe
 int sbi_flat_probe_cells(sb_context *ctx, const sb_flat *tree, const sb_probe_args &args, uint32_t *out_probe,
                          uint32_t *out_build, uint64_t capacity, uint64_t *count);
 
+// Result of the v3 front end: probe points as 8-byte records {(ly << 16) | lx in-bucket quantised coordinate, probe
+// id} grouped by cell = bucket * 1024 + sub-cell (32 x 32 buckets of 32 x 32 sub-cells over the tree box);
+// cell_off[cell] .. cell_off[cell + 1] is the record range of a cell. Everything lives in the context's arena.
+struct sb_cell_partition {
+	const void *grid = nullptr;   // bp_grid (quantiser of the tree box)
+	void *tables = nullptr;       // bp_tables
+	const void *units = nullptr;  // bp_unit[n_units]: (bucket, record range <= 32768) work units
+	const uint32_t *cand_pos = nullptr; // leaf positions of the tree binned by bucket (tables->cand_off)
+	const void *rec_bucketed = nullptr; // records grouped by bucket only (NaN probes at the end)
+	const void *rec = nullptr;          // records grouped by cell
+	const uint32_t *cell_off = nullptr; // 1024 * 1024 + 1 offsets
+	uint64_t n_kept = 0, n_cand = 0, n_units = 0, n_nan = 0;
+};
+int sbi_cell_partition(sb_context *ctx, const sb_flat *tree, const double *px, const double *py, uint64_t n,
+                       uint32_t index_base, sb_cell_partition *P);
+
+// pip_join.cu : ST_Within(point, polygon) join, polygon-centric over the cell-sorted points
+int sbi_join_points_polygons(sb_context *ctx, const double *px, const double *py, uint64_t n_points, const double *vx,
+                             const double *vy, const uint64_t *ring_off, const uint64_t *poly_off, uint64_t n_polys,
+                             uint32_t *out_point, uint32_t *out_poly, uint64_t capacity, uint64_t *count);
+
 // refine.cu
 int sbi_pack_box2d(sb_context *ctx, const double *x0, const double *y0, const double *x1, const double *y1, uint64_t n,
                    double *out4);

@@ -1,6 +1,7 @@
 // refine.cu -- K6: exact fp64 refinement of candidate pairs, compacting survivors in place.
 // Compiled with -fmad=false: every product/difference is individually rounded like the reference's x86-64 build.
 #include "internal.cuh"
+#include "pip.cuh"
 
 int sbi_read_u64(sb_context *ctx, const uint64_t *dev, uint64_t *host) {
 	SB_CUDA(cudaMemcpyAsync(ctx->pinned_u64, dev, sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
@@ -83,47 +84,7 @@ struct pred_point_polygon {
 	const double *px, *py, *vx, *vy;
 	const uint64_t *ring_off, *poly_off;
 	__device__ bool operator()(uint32_t a, uint32_t p, double &) const {
-		const double x = px[a], y = py[a];
-		bool contains = false, first = true;
-		for (uint64_t r = poly_off[p]; r < poly_off[p + 1]; r++) {
-			const uint64_t o = ring_off[r], e = ring_off[r + 1];
-			double x1 = vx[o], y1 = vy[o];
-			int wn = 0;
-			for (uint64_t c = o + 1; c < e; c++) {
-				const double x2 = vx[c], y2 = vy[c];
-				if (!(x1 == x2 && y1 == y2)) {
-					const double y_min = y2 < y1 ? y2 : y1;
-					const double y_max = y1 < y2 ? y2 : y1;
-					if (!(y > y_max || y < y_min)) {
-						const double side_v = __dsub_rn(__dmul_rn(__dsub_rn(x, x1), __dsub_rn(y2, y1)),
-						                                __dmul_rn(__dsub_rn(x2, x1), __dsub_rn(y, y1)));
-						if (side_v == 0.0 && (((x1 <= x && x < x2) || (x1 >= x && x > x2)) ||
-						                      ((y1 <= y && y < y2) || (y1 >= y && y > y2)))) {
-							break;
-						} else if (side_v < 0.0 && (y1 < y && y <= y2)) {
-							wn++;
-						} else if (side_v > 0.0 && (y2 <= y && y < y1)) {
-							wn--;
-						}
-					}
-				}
-				x1 = x2;
-				y1 = y2;
-			}
-			const bool in_ring = wn != 0;
-			if (first) {
-				if (!in_ring) {
-					contains = false;
-					break;
-				}
-				contains = true;
-			} else if (in_ring) {
-				contains = false;
-				break;
-			}
-			first = false;
-		}
-		return contains;
+		return sb_pip_native(px[a], py[a], vx, vy, ring_off, poly_off[p], poly_off[p + 1]);
 	}
 };
 

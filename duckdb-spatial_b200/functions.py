@@ -282,6 +282,28 @@ class Context:
         ub = self.join_unmatched_rows(bm) if jt in ("right", "full", "outer") else empty
         return p, b, up, ub
 
+    def join_points_polygons(self, px, py, vx, vy, ring_off, poly_off, capacity=None, out=None):
+        """ST_Within(point, polygon) join over POLYGON_2D list columns -> (point rows, polygon rows), unordered."""
+        px, py, vx, vy = [self._f64(v) for v in (px, py, vx, vy)]
+        cap = int(capacity if capacity is not None else max(1024, 2 * len(px)))
+        while True:
+            if out is not None:
+                op, ob = out
+                cap = len(op)
+            else:
+                op = self._empty(px, (cap,), np.uint32)
+                ob = self._empty(px, (cap,), np.uint32)
+            cnt = C.c_uint64(0)
+            rc = self.L.sb_join_points_polygons(self.h, self._mem(px, py, vx, vy, ring_off, poly_off), _ptr(px), _ptr(py),
+                                                len(px), _ptr(vx), _ptr(vy), _ptr(ring_off), _ptr(poly_off),
+                                                len(poly_off) - 1, len(ring_off) - 1, len(vx), _ptr(op), _ptr(ob), cap,
+                                                C.byref(cnt))
+            if rc == capi.ERR_CAPACITY and out is None:
+                cap = int(cnt.value)
+                continue
+            capi.check(rc)
+            return op[: cnt.value], ob[: cnt.value]
+
     def join_dwithin(self, ax, ay, bx, by, radius, capacity=None):
         ax, ay, bx, by = [self._f64(v) for v in (ax, ay, bx, by)]
         cap = int(capacity if capacity is not None else max(1024, 4 * len(ax)))

@@ -61,7 +61,9 @@ SB_API int sb_context_sync(sb_context *ctx);
 /* tuning / test knobs. "probe_path": 0 = auto, 1 = per-probe tree walk only, 2 = bucketed bulk probe only
  * (both produce the same pair set; the parity tests run every join through both). "pipe_chunk": probe rows per
  * chunk of the host-pointer join pipeline (default 16 Mi; calls with >= 2 chunks overlap H2D / probe / D2H).
- * "trace": 1 = print per-phase wall times to stderr (synchronises at every phase). */
+ * "trace": 1 = print per-phase wall times to stderr (synchronises at every phase). "probe_path" 3 = the cell-sorted
+ * bulk probe (v3, what auto picks), 2 = the bucketed v2 kernel. "pip_path": route of sb_join_points_polygons, 0 = auto,
+ * 1 = FlatRTree candidates + sb_refine_point_polygon, 2 = polygon-centric kernel. */
 SB_API int sb_context_set_option(sb_context *ctx, const char *key, int64_t value);
 /* number of kernels this context has launched so far (bench.py's gpu_launches) */
 SB_API uint64_t sb_context_launches(const sb_context *ctx);
@@ -204,6 +206,15 @@ SB_API int sb_join_points_boxes(sb_context *ctx, sb_mem mem, sb_predicate pred, 
 SB_API int sb_flat_probe_points(sb_context *ctx, const sb_flat *tree, sb_mem mem, sb_predicate pred, const double *px,
                                 const double *py, uint64_t n_points, uint32_t probe_index_base, const double *bbox2d4,
                                 uint32_t *out_probe, uint32_t *out_build, uint64_t capacity, uint64_t *count);
+/* ST_Within(point, polygon) / ST_Contains(polygon, point) join: every (point row, polygon row) whose cached float
+ * boxes intersect (the FlatRTree candidate rule, spatial_join_physical.cpp:764-849) and for which the winding-number
+ * routine ST_Contains::Operation (spatial_functions_scalar.cpp:1938-2051) holds. Polygons in DuckDB list layout (see
+ * sb_refine_point_polygon). Large probe sides run polygon-centric over cell-sorted points with a per-polygon edge
+ * index in shared memory (pip_join.cu); small ones take FlatRTree probe + sb_refine_point_polygon. Same pair set. */
+SB_API int sb_join_points_polygons(sb_context *ctx, sb_mem mem, const double *px, const double *py, uint64_t n_points,
+                                   const double *vx, const double *vy, const uint64_t *ring_vert_off,
+                                   const uint64_t *poly_ring_off, uint64_t n_polys, uint64_t n_rings, uint64_t n_verts,
+                                   uint32_t *out_point, uint32_t *out_poly, uint64_t capacity, uint64_t *count);
 /* radius join (new capability behind the same operator): all (a, b) with distance <= radius.
  * Builds a FlatRTree over b's points expanded by radius, probes with a, refines with ST_Distance. */
 SB_API int sb_join_dwithin(sb_context *ctx, sb_mem mem, const double *ax, const double *ay, uint64_t na,

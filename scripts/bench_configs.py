@@ -162,7 +162,7 @@ def main():
             px, py = ctx.st_generate_points(1337, P, DOMAIN, device=True)
             fvx, fvy = vx.reshape(-1), vy.reshape(-1)
             if hasattr(ctx, "join_points_polygons"):
-                cap = int(P * 0.75) + (1 << 20)
+                cap = int(P * 1.3) + (1 << 20)
                 out = (torch.empty(cap, dtype=torch.int32, device=dev), torch.empty(cap, dtype=torch.int32, device=dev))
                 ms, (gp, gb) = timed(stream, lambda: ctx.join_points_polygons(px, py, fvx, fvy, voff, poly_off, out=out), a.reps, warm=1)
                 res = {"path": "sb_join_points_polygons", "ms": ms, "pairs": int(len(gp))}

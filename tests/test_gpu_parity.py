@@ -452,3 +452,92 @@ def test_build_flags_accumulate_over_probe_batches(ctx, O):
     exp, _ = O.join_points_boxes(px, py, *b, pred=0)
     assert (ctx.join_unmatched_rows(bm) == np.setdiff1d(np.arange(m), exp[:, 1])).all()
     assert len(ctx.join_unmatched_rows(np.zeros(0, np.uint8))) == 0
+
+
+def _pip_expected(O, px, py, vx, vy, voff, poly_off, fbox):
+    """oracle: candidates = float-box hits (FlatRTree lookup semantics), predicate = the native winding routine"""
+    qb = O.bbox_from_points(px, py)
+    out = []
+    for b in range(len(poly_off) - 1):
+        fb = fbox[b]
+        if not (fb[0] <= fb[2]):
+            continue
+        m = ~((qb[:, 0] > fb[2]) | (qb[:, 2] < fb[0]) | (qb[:, 1] > fb[3]) | (qb[:, 3] < fb[1]))
+        for a in np.nonzero(m)[0]:
+            if O.pip_native(px[a], py[a], vx, vy, voff, int(poly_off[b]), int(poly_off[b + 1])):
+                out.append((int(a), b))
+    return out
+
+
+def test_join_points_polygons_both_routes(ctx, sb, O):
+    # C4-shaped join through both routes of sb_join_points_polygons (polygon-centric kernel with the shared-memory
+    # edge index / FlatRTree candidates + refine) against the oracle: jagged stars, an axis-aligned square with probes
+    # on its vertices and edges, a polygon with a hole (literal-loop path), a degenerate and an empty polygon
+    npoly, k, n = 40, 60, 140000
+    vx, vy, voff = _star_polygons(O, 99, npoly, k, 20, 60, 1000)
+    rings = [(vx[int(voff[i]):int(voff[i + 1])], vy[int(voff[i]):int(voff[i + 1])]) for i in range(npoly)]
+    poly_rings = [[r] for r in rings]
+    sq = (np.array([100.0, 100, 200, 200, 100]), np.array([100.0, 200, 200, 100, 100]))
+    poly_rings.append([sq])
+    outer = (np.array([600.0, 600, 800, 800, 600]), np.array([600.0, 800, 800, 600, 600]))
+    hole = (np.array([650.0, 750, 750, 650, 650]), np.array([650.0, 650, 750, 750, 650]))
+    poly_rings.append([outer, hole])
+    poly_rings.append([(np.array([300.0, 300, 300]), np.array([300.0, 300, 300]))])  # zero-area
+    poly_rings.append([])  # no rings at all
+    big = 900  # a ring with more vertices than the index path would ever need
+    t = np.linspace(0, 2 * np.pi, big, endpoint=False)
+    poly_rings.append([(np.append(500 + 90 * np.cos(t), 590.0), np.append(400 + 70 * np.sin(t), 400.0))])
+    fx, fy, roff, poff = [], [], [0], [0]
+    for pr in poly_rings:
+        for rx, ry in pr:
+            fx.append(rx)
+            fy.append(ry)
+            roff.append(roff[-1] + len(rx))
+        poff.append(poff[-1] + len(pr))
+    vx, vy = np.concatenate(fx), np.concatenate(fy)
+    roff, poff = np.array(roff, np.uint64), np.array(poff, np.uint64)
+    px, py = O.generate_points(1337, n, (0, 0, 1000, 1000))
+    px[:8] = [100, 150, 200, 150, 100, 200, 150, 99.999]
+    py[:8] = [150, 100, 150, 200, 100, 200, 150, 150]
+    px[8:12], py[8:12] = [650, 700, 600, 300], [700, 650, 700, 300]  # on the hole / the shell / the degenerate polygon
+    px[12], py[13] = np.nan, np.nan
+    # probes exactly on star vertices and edge midpoints
+    px[20:60], py[20:60] = rings[3][0][:40], rings[3][1][:40]
+    px[60:100] = (rings[5][0][:40] + rings[5][0][1:41]) / 2
+    py[60:100] = (rings[5][1][:40] + rings[5][1][1:41]) / 2
+    fbox = np.zeros((len(poly_rings), 4), np.float32)
+    for i, pr in enumerate(poly_rings):
+        if not pr:
+            fbox[i] = [1, 1, 0, 0]
+            continue
+        ax, ay = np.concatenate([r[0] for r in pr]), np.concatenate([r[1] for r in pr])
+        fbox[i] = O.bbox_from_box2d([ax.min()], [ay.min()], [ax.max()], [ay.max()])[0]
+    exp = _pip_expected(O, px, py, vx, vy, roff, poff, fbox)
+    e = sort_pairs([t[0] for t in exp], [t[1] for t in exp])
+    assert len(e) > 20000
+    for route in (2, 1):
+        ctx.set_option("pip_path", route)
+        try:
+            gp, gb = ctx.join_points_polygons(px, py, vx, vy, roff, poff, capacity=1024)
+        finally:
+            ctx.set_option("pip_path", 0)
+        g = sort_pairs(gp, gb)
+        assert g.shape == e.shape and (g == e).all(), "route %d differs from the oracle" % route
+
+
+def test_join_points_polygons_routes_agree_large(ctx, O):
+    # larger randomised case: the polygon-centric kernel (edge index, W0 prefix counts) must produce exactly the pair
+    # set of FlatRTree candidates + the literal winding loop (route 1 is itself checked against the oracle above)
+    npoly, k, n = 300, 200, 3000000
+    vx, vy, voff = _star_polygons(O, 7, npoly, k, 5, 90, 2000)
+    poff = np.arange(npoly + 1, dtype=np.uint64)
+    px, py = O.generate_points(11, n, (0, 0, 2000, 2000))
+    res = []
+    for route in (1, 2):
+        ctx.set_option("pip_path", route)
+        try:
+            res.append(sort_pairs(*ctx.join_points_polygons(px, py, vx, vy, voff, poff, capacity=4 * n)))
+        finally:
+            ctx.set_option("pip_path", 0)
+    assert len(res[0]) > 1000000
+    assert res[0].shape == res[1].shape and (res[0] == res[1]).all()
