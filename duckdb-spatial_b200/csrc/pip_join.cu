@@ -37,13 +37,13 @@
 #include "cells.cuh"
 #include "pip.cuh"
 
-#define PIP_G 32
+#define PIP_G 32 // (the row scans below assume one warp = one row set: PIP_G == 32)
 #define PIP_NCELL (PIP_G * PIP_G)
 #define PIP_MAXE 1024
-#define PIP_LMAX 20480
+#define PIP_LMAX 12288
 #define PIP_THREADS 256
 #define PIP_WARPS (PIP_THREADS / 32)
-#define PIP_STAGE 512
+#define PIP_STAGE 256
 
 struct pip_poly {
 	double minx, miny, maxx, maxy; // exact extent over all vertices
@@ -145,8 +145,12 @@ struct pip_smem {
 	double vx[PIP_MAXE + 1], vy[PIP_MAXE + 1];
 	uchar4 rng[PIP_MAXE]; // per edge: x = first row, y = last row, z = first column (of lo), w = last column (of hi)
 	int w0[PIP_NCELL];    // difference array per row, then W0 per cell
-	uint32_t cnt[PIP_NCELL];
+	uint32_t cnt[PIP_NCELL];  // cell lists: counts, then fill cursors
+	uint32_t rcnt[PIP_NCELL]; // row lists: entries per (row, first column), then fill cursors
 	uint16_t off[PIP_NCELL + 8];
+	uint16_t npre[PIP_NCELL]; // per cell: how many entries of its row's list (sorted by first column, descending) lie right of it
+	uint16_t rowoff[PIP_G + 8];
+	uint16_t rowlist[2 * PIP_MAXE];
 	uint16_t list[PIP_LMAX];
 	uint32_t stage[PIP_WARPS][PIP_STAGE];
 	uint32_t scan[PIP_WARPS];
@@ -177,7 +181,7 @@ __device__ __forceinline__ void pip_flush(uint32_t *stage, uint32_t cnt, uint32_
 	__syncwarp();
 }
 
-__global__ void __launch_bounds__(PIP_THREADS, 2)
+__global__ void __launch_bounds__(PIP_THREADS, 3)
     k_pip_join(const pip_poly *__restrict__ polys, uint32_t n_polys, const double *__restrict__ gvx,
                const double *__restrict__ gvy, const uint64_t *__restrict__ ring_off, const uint64_t *__restrict__ poly_off,
                const bp_grid *__restrict__ gp, const uint2 *__restrict__ rec, const double2 *__restrict__ xy,
@@ -224,6 +228,7 @@ __global__ void __launch_bounds__(PIP_THREADS, 2)
 			for (uint32_t c = tid; c < PIP_NCELL; c += PIP_THREADS) {
 				S.w0[c] = 0;
 				S.cnt[c] = 0;
+				S.rcnt[c] = 0;
 			}
 			__syncthreads();
 			for (uint32_t e = tid; e < ne; e += PIP_THREADS) {
@@ -237,18 +242,19 @@ __global__ void __launch_bounds__(PIP_THREADS, 2)
 					const int ry0 = pip_cell(eymin, P.miny, fsy), ry1 = pip_cell(eymax, P.miny, fsy);
 					rg = make_uchar4((unsigned char)ry0, (unsigned char)ry1, (unsigned char)c0, (unsigned char)c1);
 					const int dir = y2 > y1 ? 1 : -1;
-					uint32_t added = 0;
 					for (int r = ry0; r <= ry1; r++) {
-						const bool spans = r > ry0 && r < ry1;
-						if (spans && c0 > 0) {
-							atomicAdd(&S.w0[r * PIP_G + c0], dir); // columns < c0 of this row get `dir` (suffix sum below)
+						if (c0 > 0) {
+							if (r > ry0 && r < ry1) {
+								atomicAdd(&S.w0[r * PIP_G + c0], dir); // columns < c0 of a spanned row get `dir` (suffix sum below)
+							} else {
+								atomicAdd(&S.rcnt[r * PIP_G + c0], 1u); // end row: cells left of c0 apply the y rule only
+							}
 						}
-						for (int c = spans ? c0 : 0; c <= c1; c++) {
+						for (int c = c0; c <= c1; c++) {
 							atomicAdd(&S.cnt[r * PIP_G + c], 1u);
-							added++;
 						}
 					}
-					atomicAdd(&S.n_list, added);
+					atomicAdd(&S.n_list, (uint32_t)((ry1 - ry0 + 1) * (c1 - c0 + 1)));
 				}
 				S.rng[e] = rg;
 			}
@@ -258,14 +264,30 @@ __global__ void __launch_bounds__(PIP_THREADS, 2)
 			}
 		}
 		if (indexed) {
-			// W0[r][c] = sum of the difference entries of the columns right of c; CSR offsets of the lists
+			// per row: W0[r][c] = sum of the difference entries of the columns right of c; npre[r][c] = number of row-list
+			// entries whose first column is right of c; the row list is ordered by first column, descending
 			if (tid < PIP_G) {
 				int run = 0;
+				uint32_t nrun = 0;
 				for (int c = PIP_G - 1; c >= 0; c--) {
 					const int d = S.w0[tid * PIP_G + c];
+					const uint32_t n = S.rcnt[tid * PIP_G + c];
 					S.w0[tid * PIP_G + c] = run;
+					S.npre[tid * PIP_G + c] = (uint16_t)nrun;
+					S.rcnt[tid * PIP_G + c] = nrun; // position of the group (row, first column c) inside the row list
 					run += d;
+					nrun += n;
 				}
+				// exclusive scan of the row totals over the 32 rows of this warp
+				uint32_t inc = nrun;
+#pragma unroll
+				for (int sft = 1; sft < 32; sft <<= 1) {
+					const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, sft);
+					if (lane >= (unsigned)sft) {
+						inc += o;
+					}
+				}
+				S.rowoff[tid] = (uint16_t)(inc - nrun);
 			}
 			{
 				// exclusive scan of cnt over 1024 cells with 256 threads (4 consecutive cells per thread)
@@ -277,9 +299,9 @@ __global__ void __launch_bounds__(PIP_THREADS, 2)
 				}
 				uint32_t inc = sum;
 #pragma unroll
-				for (int s = 1; s < 32; s <<= 1) {
-					const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, s);
-					if (lane >= (unsigned)s) {
+				for (int sft = 1; sft < 32; sft <<= 1) {
+					const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, sft);
+					if (lane >= (unsigned)sft) {
 						inc += o;
 					}
 				}
@@ -306,8 +328,10 @@ __global__ void __launch_bounds__(PIP_THREADS, 2)
 			for (uint32_t e = tid; e < ne; e += PIP_THREADS) {
 				const uchar4 rg = S.rng[e];
 				for (int r = rg.x; r <= (int)rg.y; r++) {
-					const bool spans = r > (int)rg.x && r < (int)rg.y;
-					for (int c = spans ? rg.z : 0; c <= (int)rg.w; c++) {
+					if (rg.z > 0 && !(r > (int)rg.x && r < (int)rg.y)) {
+						S.rowlist[S.rowoff[r] + atomicAdd(&S.rcnt[r * PIP_G + rg.z], 1u)] = (uint16_t)e;
+					}
+					for (int c = rg.z; c <= (int)rg.w; c++) {
 						S.list[atomicAdd(&S.cnt[r * PIP_G + c], 1u)] = (uint16_t)e;
 					}
 				}
@@ -320,13 +344,14 @@ __global__ void __launch_bounds__(PIP_THREADS, 2)
 		const int n_items = (gy1 - gy0 + 1) * nseg;
 		uint32_t *stage = S.stage[warp];
 		uint32_t nst = 0;
-		for (int it = warp; it < n_items; it += PIP_WARPS) {
+		for (int it = 0; it < n_items; it++) {
 			const int gy = gy0 + it / nseg, bx = (gx0 >> 5) + it % nseg;
 			const int xa = max(gx0, bx << 5), xb = min(gx1, (bx << 5) + 31);
 			const uint32_t cell_a = ((uint32_t)((gy >> 5) * BP_G + bx) << 10) | ((uint32_t)(gy & 31) << 5) | (uint32_t)(xa & 31);
 			const uint32_t cell_b = cell_a + (uint32_t)(xb - xa);
 			const uint32_t p0 = __ldg(cell_off + cell_a), p1 = __ldg(cell_off + cell_b + 1);
-			for (uint32_t i0 = p0; i0 < p1; i0 += 32) {
+			// the warps of the CTA interleave 32-point chunks of every segment (balanced to the chunk)
+			for (uint32_t i0 = p0 + warp * 32; i0 < p1; i0 += 32 * PIP_WARPS) {
 				const uint32_t i = i0 + lane;
 				bool hit = false;
 				uint32_t id = 0;
@@ -337,8 +362,19 @@ __global__ void __launch_bounds__(PIP_THREADS, 2)
 					const float4 pb = make_float4(sb_f64_to_f32_down(x), sb_f64_to_f32_down(y), sb_f64_to_f32_up(x), sb_f64_to_f32_up(y));
 					if (sb_box_intersects(pb, P.fbox)) {
 						if (indexed) {
-							const int c = pip_cell(y, P.miny, fsy) * PIP_G + pip_cell(x, P.minx, fsx);
+							const int row = pip_cell(y, P.miny, fsy);
+							const int c = row * PIP_G + pip_cell(x, P.minx, fsx);
 							int wn = S.w0[c];
+							// end-row edges wholly right of the cell: the sign of side_v is known (< 0 upward, > 0 downward,
+							// never 0), only the half-open y rule of the crossing test is left
+							const uint16_t *rl = S.rowlist + S.rowoff[row];
+							const uint32_t np = S.npre[c];
+							for (uint32_t k = 0; k < np; k++) {
+								const uint32_t e = rl[k];
+								const double y1 = S.vy[e], y2 = S.vy[e + 1];
+								wn += (y1 < y && y <= y2) ? 1 : 0;
+								wn -= (y2 <= y && y < y1) ? 1 : 0;
+							}
 							bool on_edge = false;
 							const uint32_t le = S.off[c + 1];
 							for (uint32_t k = S.off[c]; k < le; k++) {
@@ -447,7 +483,7 @@ int sbi_join_points_polygons(sb_context *ctx, const double *px, const double *py
 	}
 	{
 		sb_prof_scope ps(ctx, "pip_join");
-		const unsigned grid = (unsigned)(n_polys < 2 * SB_NUM_SMS ? n_polys : 2 * SB_NUM_SMS);
+		const unsigned grid = (unsigned)(n_polys < 3 * SB_NUM_SMS ? n_polys : 3 * SB_NUM_SMS);
 		k_pip_join<<<grid, PIP_THREADS, sizeof(pip_smem), ctx->stream>>>(
 		    d_polys, (uint32_t)n_polys, vx, vy, ring_off, poly_off, static_cast<const bp_grid *>(part.grid),
 		    static_cast<const uint2 *>(part.rec), d_xy, part.cell_off, d_ticket, out_point, out_poly, capacity, d_counter);
