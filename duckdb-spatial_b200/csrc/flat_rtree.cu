@@ -344,7 +344,9 @@ int sbi_flat_probe(sb_context *ctx, const sb_flat *tree, const sb_probe_args &a,
 	SB_ARG(a.m + a.index_base <= 0xFFFFFFFFull, "probe indices must fit 32 bits");
 	// bulk point probes: bucketed kernel (same pair set); small batches and box probes: per-probe tree walk
 	if (!a.force_walk && !a.probe_box && ctx->probe_path != 1 && (ctx->probe_path >= 2 || a.m >= (1u << 17))) {
-		if (ctx->probe_path == 2) {
+		// v3 (cell-sorted) needs dense sub-cells to fill its warps: ~1 M sub-cells over the tree box, so below a few
+		// 10^7 probes per call (e.g. the 16 Mi-row chunks of the host-pointer pipeline) the bucketed v2 kernel is used
+		if (ctx->probe_path == 2 || (ctx->probe_path == 0 && a.m < (40ull << 20))) {
 			return sbi_flat_probe_bucketed(ctx, tree, a, out_probe, out_build, capacity, count);
 		}
 		return sbi_flat_probe_cells(ctx, tree, a, out_probe, out_build, capacity, count);
