@@ -194,27 +194,50 @@ __global__ void __launch_bounds__(BPS_THREADS, 2)
 }
 
 // ---- 3. the tree's leaf level binned into the same buckets ----------------------------------------------------
+// The leaf level is in Hilbert order, so the 32 leaves of a warp almost always fall into the same bucket: one atomic
+// per group of equal buckets (match.any) instead of one per leaf -- the per-leaf version spent 0.3 ms per launch at C3
+// on same-address atomics. Leaves that straddle buckets take the plain loop.
 template <bool FILL>
 __global__ void __launch_bounds__(256) k_bp_cand(const float4 *__restrict__ boxes, uint32_t items,
                                                  const bp_grid *__restrict__ gp, uint32_t *__restrict__ counter,
                                                  uint32_t *__restrict__ cand_pos) {
 	const bp_grid g = *gp;
 	const uint32_t stride = gridDim.x * blockDim.x;
-	for (uint32_t pos = blockIdx.x * blockDim.x + threadIdx.x; pos < items; pos += stride) {
-		int x0, y0, x1, y1;
-		bp_leaf_range(boxes[pos], g, x0, y0, x1, y1);
-		for (int by = y0 >> 15; by <= (y1 >> 15); by++) {
-			for (int bx = x0 >> 15; bx <= (x1 >> 15); bx++) {
-				const uint32_t slot = atomicAdd(&counter[by * BP_G + bx], 1u);
-				if (FILL) {
-					cand_pos[slot] = pos;
+	const unsigned lane = sb_lane(), lt = sb_lanemask_lt();
+	const uint32_t items_round = (items + 31u) & ~31u;
+	for (uint32_t pos = blockIdx.x * blockDim.x + threadIdx.x; pos < items_round; pos += stride) {
+		int x0 = 1, y0 = 1, x1 = 0, y1 = 0;
+		if (pos < items) {
+			bp_leaf_range(boxes[pos], g, x0, y0, x1, y1);
+		}
+		const int bx0 = x0 >> 15, bx1 = x1 >> 15, by0 = y0 >> 15, by1 = y1 >> 15;
+		const bool live = pos < items && x0 <= x1 && y0 <= y1;
+		const bool single = live && bx0 == bx1 && by0 == by1;
+		const uint32_t key = single ? (uint32_t)(by0 * BP_G + bx0) : 0xFFFFFFFFu - lane; // non-single lanes: unique keys
+		const uint32_t peers = __match_any_sync(0xFFFFFFFFu, key);
+		if (single) {
+			const int leader = __ffs(peers) - 1;
+			uint32_t base = 0;
+			if ((int)lane == leader) {
+				base = atomicAdd(&counter[key], (uint32_t)__popc(peers));
+			}
+			base = __shfl_sync(peers, base, leader);
+			if (FILL) {
+				cand_pos[base + __popc(peers & lt)] = pos;
+			}
+		} else if (live) {
+			for (int by = by0; by <= by1; by++) {
+				for (int bx = bx0; bx <= bx1; bx++) {
+					const uint32_t slot = atomicAdd(&counter[by * BP_G + bx], 1u);
+					if (FILL) {
+						cand_pos[slot] = pos;
+					}
 				}
 			}
 		}
 	}
 }
 
-// ---- offsets, cursors and the work-unit table -----------------------------------------------------------------
 __device__ __forceinline__ uint32_t bp_block_excl_scan_1024(uint32_t v, uint32_t *s_warp, uint32_t *total) {
 	// blockDim.x == 1024
 	const unsigned lane = sb_lane(), warp = threadIdx.x >> 5;
@@ -901,20 +924,23 @@ __device__ __forceinline__ uint32_t cp_subcell(uint32_t pq) {
 	return ((pq >> 26) << 5) | ((pq >> 10) & 31u); // (ly >> 10) * 32 + (lx >> 10)
 }
 
+template <bool XY>
 struct cps1_smem {
 	uint2 rec[CP_TILE1];
 	uint16_t bkt[CP_TILE1];
 	uint32_t cnt[BP_NB + 8];
 	uint32_t off[BP_NB + 8];
 	uint32_t scan[32];
+	double2 xy[XY ? CP_TILE1 : 1]; // XY: the exact coordinates travel with the records (polygon join)
 };
 
+template <bool XY>
 __global__ void __launch_bounds__(1024, 1)
     k_cp_scatter1(const double *__restrict__ px, const double *__restrict__ py, uint64_t n, uint32_t index_base,
                   const bp_grid *__restrict__ gp, uint32_t *__restrict__ cursor, uint32_t *__restrict__ fine,
-                  uint2 *__restrict__ orec) {
+                  uint2 *__restrict__ orec, double2 *__restrict__ oxy) {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
-	cps1_smem &S = *reinterpret_cast<cps1_smem *>(smem_raw);
+	cps1_smem<XY> &S = *reinterpret_cast<cps1_smem<XY> *>(smem_raw);
 	const bp_grid g = *gp;
 	const unsigned tid = threadIdx.x;
 	const uint64_t tiles = (n + CP_TILE1 - 1) / CP_TILE1;
@@ -976,6 +1002,9 @@ __global__ void __launch_bounds__(1024, 1)
 				const uint32_t slot = S.off[b] + (br[k] & 0xFFFFu);
 				S.rec[slot] = make_uint2(pq[k], (uint32_t)(base + (uint64_t)k * 1024) + index_base);
 				S.bkt[slot] = (uint16_t)b;
+				if (XY) {
+					S.xy[slot] = make_double2(x[k], y[k]);
+				}
 			}
 		}
 		__syncthreads();
@@ -984,6 +1013,9 @@ __global__ void __launch_bounds__(1024, 1)
 			const uint32_t b = S.bkt[t];
 			const uint2 r = S.rec[t];
 			orec[S.cnt[b] + t] = r;
+			if (XY) {
+				oxy[S.cnt[b] + t] = S.xy[t];
+			}
 			if (b < BP_NB) {
 				atomicAdd(&fine[(b << 10) | cp_subcell(r.x)], 1u);
 			}
@@ -1007,18 +1039,21 @@ __global__ void __launch_bounds__(1024) k_cp_scan2(const bp_tables *__restrict__
 	}
 }
 
+template <bool XY>
 struct cps2_smem {
 	uint2 rec[CP_TILE2];
+	uint32_t src[XY ? CP_TILE2 : 1]; // XY: position of the record in bucket order (where its coordinates are)
 	uint32_t cnt[BP_NB];
 	uint32_t off[BP_NB];
 	uint32_t scan[32];
 };
 
+template <bool XY>
 __global__ void __launch_bounds__(1024, 1)
     k_cp_scatter2(const bp_tables *__restrict__ T, const bp_unit *__restrict__ units, const uint2 *__restrict__ irec,
-                  uint32_t *__restrict__ cursor2, uint2 *__restrict__ orec) {
+                  uint32_t *__restrict__ cursor2, uint2 *__restrict__ orec, uint32_t *__restrict__ osrc) {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
-	cps2_smem &S = *reinterpret_cast<cps2_smem *>(smem_raw);
+	cps2_smem<XY> &S = *reinterpret_cast<cps2_smem<XY> *>(smem_raw);
 	const unsigned tid = threadIdx.x;
 	const uint32_t n_units = (uint32_t)T->totals[2];
 	constexpr int ITEMS = CP_TILE2 / 1024;
@@ -1061,14 +1096,22 @@ __global__ void __launch_bounds__(1024, 1)
 		for (int k = 0; k < ITEMS; k++) {
 			const uint32_t i = tbeg + k * 1024 + tid;
 			if (i < tend) {
-				S.rec[S.off[cp_subcell(r[k].x)] + rk[k]] = r[k];
+				const uint32_t slot = S.off[cp_subcell(r[k].x)] + rk[k];
+				S.rec[slot] = r[k];
+				if (XY) {
+					S.src[slot] = i;
+				}
 			}
 		}
 		__syncthreads();
 		const uint32_t nt = tend - tbeg;
 		for (uint32_t t = tid; t < nt; t += 1024) {
 			const uint2 v = S.rec[t];
-			orec[S.cnt[cp_subcell(v.x)] + t] = v;
+			const uint32_t dst = S.cnt[cp_subcell(v.x)] + t;
+			orec[dst] = v;
+			if (XY) {
+				osrc[dst] = S.src[t];
+			}
 		}
 		__syncthreads();
 	}
@@ -1447,7 +1490,7 @@ __global__ void __launch_bounds__(256) k_cp_unpack(const uint2 *__restrict__ rec
 // Front end shared by the cell-sorted probe and the point-in-polygon join (pip_join.cu): partitions the probe points
 // into (bucket, sub-cell) cells of the tree box's quantiser grid and bins the tree's leaf level into the buckets.
 int sbi_cell_partition(sb_context *ctx, const sb_flat *tree, const double *px, const double *py, uint64_t n,
-                       uint32_t index_base, sb_cell_partition *P) {
+                       uint32_t index_base, sb_cell_partition *P, bool want_xy) {
 	const uint32_t items = tree->h.item_count;
 	bp_grid *d_grid = nullptr;
 	bp_tables *d_tab = nullptr;
@@ -1460,6 +1503,12 @@ int sbi_cell_partition(sb_context *ctx, const sb_flat *tree, const double *px, c
 	SB_TRY(ctx->scratch_t(max_units, &d_units));
 	SB_TRY(ctx->scratch_t(n, &d_rec_a));
 	SB_TRY(ctx->scratch_t(n, &d_rec_b));
+	double2 *d_xy_a = nullptr;
+	uint32_t *d_src = nullptr;
+	if (want_xy) {
+		SB_TRY(ctx->scratch_t(n, &d_xy_a));
+		SB_TRY(ctx->scratch_t(n, &d_src));
+	}
 	SB_TRY(ctx->scratch_t(CP_NCELL, &d_fine));
 	SB_TRY(ctx->scratch_t(CP_NCELL + 1, &d_cell_off));
 	SB_CUDA(cudaMemsetAsync(d_tab, 0, sizeof(bp_tables), ctx->stream));
@@ -1490,21 +1539,33 @@ int sbi_cell_partition(sb_context *ctx, const sb_flat *tree, const double *px, c
 	SB_TRY(ctx->scratch_t(n_cand ? n_cand : 1, &d_cand));
 	static bool attr_set = false;
 	if (!attr_set) {
-		SB_CUDA(cudaFuncSetAttribute(k_cp_scatter1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(cps1_smem)));
-		SB_CUDA(cudaFuncSetAttribute(k_cp_scatter2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(cps2_smem)));
+		SB_CUDA(cudaFuncSetAttribute(k_cp_scatter1<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(cps1_smem<false>)));
+		SB_CUDA(cudaFuncSetAttribute(k_cp_scatter2<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(cps2_smem<false>)));
+		SB_CUDA(cudaFuncSetAttribute(k_cp_scatter1<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(cps1_smem<true>)));
+		SB_CUDA(cudaFuncSetAttribute(k_cp_scatter2<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(cps2_smem<true>)));
 		attr_set = true;
 	}
 	{
 		sb_prof_scope ps(ctx, "bp_partition");
-		k_cp_scatter1<<<sb_grid(n, CP_TILE1, 1), 1024, sizeof(cps1_smem), ctx->stream>>>(px, py, n, index_base, d_grid,
-		                                                                                d_tab->pt_cursor, d_fine, d_rec_a);
+		if (want_xy) {
+			k_cp_scatter1<true><<<sb_grid(n, CP_TILE1, 1), 1024, sizeof(cps1_smem<true>), ctx->stream>>>(
+			    px, py, n, index_base, d_grid, d_tab->pt_cursor, d_fine, d_rec_a, d_xy_a);
+		} else {
+			k_cp_scatter1<false><<<sb_grid(n, CP_TILE1, 1), 1024, sizeof(cps1_smem<false>), ctx->stream>>>(
+			    px, py, n, index_base, d_grid, d_tab->pt_cursor, d_fine, d_rec_a, nullptr);
+		}
 		SB_LAUNCH_CHECK(ctx);
 		// (cell_off is needed even without units: consumers index it for every cell)
 		k_cp_scan2<<<BP_NB, 1024, 0, ctx->stream>>>(d_tab, d_fine, d_cell_off);
 		SB_LAUNCH_CHECK(ctx);
 		if (n_units) {
-			k_cp_scatter2<<<sb_grid(2 * n_units, 1, 1), 1024, sizeof(cps2_smem), ctx->stream>>>(d_tab, d_units, d_rec_a, d_fine,
-			                                                                                   d_rec_b);
+			if (want_xy) {
+				k_cp_scatter2<true><<<sb_grid(2 * n_units, 1, 1), 1024, sizeof(cps2_smem<true>), ctx->stream>>>(
+				    d_tab, d_units, d_rec_a, d_fine, d_rec_b, d_src);
+			} else {
+				k_cp_scatter2<false><<<sb_grid(2 * n_units, 1, 1), 1024, sizeof(cps2_smem<false>), ctx->stream>>>(
+				    d_tab, d_units, d_rec_a, d_fine, d_rec_b, nullptr);
+			}
 			SB_LAUNCH_CHECK(ctx);
 		}
 	}
@@ -1521,6 +1582,8 @@ int sbi_cell_partition(sb_context *ctx, const sb_flat *tree, const double *px, c
 	P->cand_pos = d_cand;
 	P->rec_bucketed = d_rec_a;
 	P->rec = d_rec_b;
+	P->xy_bucketed = d_xy_a;
+	P->src = d_src;
 	P->cell_off = d_cell_off;
 	P->n_kept = totals[0];
 	P->n_cand = n_cand;

@@ -109,10 +109,14 @@ struct sb_cell_partition {
 	const void *rec_bucketed = nullptr; // records grouped by bucket only (NaN probes at the end)
 	const void *rec = nullptr;          // records grouped by cell
 	const uint32_t *cell_off = nullptr; // 1024 * 1024 + 1 offsets
+	// want_xy: exact coordinates in bucket order (aligned with rec_bucketed) and, per cell-ordered record, its position
+	// in bucket order -- the coordinates then move with two coalesced / window-local passes instead of random reads
+	const void *xy_bucketed = nullptr; // double2[n]
+	const uint32_t *src = nullptr;
 	uint64_t n_kept = 0, n_cand = 0, n_units = 0, n_nan = 0;
 };
 int sbi_cell_partition(sb_context *ctx, const sb_flat *tree, const double *px, const double *py, uint64_t n,
-                       uint32_t index_base, sb_cell_partition *P);
+                       uint32_t index_base, sb_cell_partition *P, bool want_xy = false);
 
 // pip_join.cu : ST_Within(point, polygon) join, polygon-centric over the cell-sorted points
 int sbi_join_points_polygons(sb_context *ctx, const double *px, const double *py, uint64_t n_points, const double *vx,

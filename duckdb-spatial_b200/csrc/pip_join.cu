@@ -126,17 +126,19 @@ __global__ void k_pip_header(const uint32_t *__restrict__ tb_ord, uint32_t n_pol
 	}
 }
 
-// coordinates of the cell-sorted records, in record order (only the buckets that have work units are sorted)
-__global__ void __launch_bounds__(256) k_pip_gather(const bp_tables *__restrict__ T, const bp_unit *__restrict__ units,
-                                                    const uint2 *__restrict__ rec, const double *__restrict__ px,
-                                                    const double *__restrict__ py, uint32_t index_base,
+// coordinates of the cell-sorted records, in record order (only the buckets that have work units are sorted). The
+// source positions of a 16384-record tile of pass 2 lie inside that tile (a 256 KB window of the bucket-ordered
+// coordinates): every fetched sector is used completely. (Gathering from the caller's columns through the probe id
+// instead cost 254 B of DRAM reads per point: profiles r1f_full_keys_pip_join.txt.)
+__global__ void __launch_bounds__(512) k_pip_gather(const bp_tables *__restrict__ T, const bp_unit *__restrict__ units,
+                                                    const uint32_t *__restrict__ src, const double2 *__restrict__ xy_in,
                                                     double2 *__restrict__ xy) {
 	const uint32_t n_units = (uint32_t)T->totals[2];
-	for (uint32_t u = blockIdx.x; u < n_units; u += gridDim.x) {
-		const bp_unit unit = units[u];
-		for (uint32_t i = unit.pbeg + threadIdx.x; i < unit.pend; i += blockDim.x) {
-			const uint32_t o = rec[i].y - index_base;
-			xy[i] = make_double2(px[o], py[o]);
+	for (uint32_t w = blockIdx.x; w < 2 * n_units; w += gridDim.x) {
+		const bp_unit unit = units[w >> 1];
+		const uint32_t beg = unit.pbeg + (w & 1u) * 16384u, end = min(unit.pend, beg + 16384u);
+		for (uint32_t i = beg + threadIdx.x; i < end; i += blockDim.x) {
+			xy[i] = xy_in[src[i]];
 		}
 	}
 }
@@ -465,7 +467,7 @@ int sbi_join_points_polygons(sb_context *ctx, const double *px, const double *py
 		SB_LAUNCH_CHECK(ctx);
 	}
 	sb_cell_partition part;
-	SB_TRY(sbi_cell_partition(ctx, &tree, px, py, n_points, 0, &part));
+	SB_TRY(sbi_cell_partition(ctx, &tree, px, py, n_points, 0, &part, /*want_xy=*/true));
 	if (part.n_units == 0) {
 		return SB_OK;
 	}
@@ -476,9 +478,9 @@ int sbi_join_points_polygons(sb_context *ctx, const double *px, const double *py
 	}
 	{
 		sb_prof_scope ps(ctx, "pip_gather");
-		k_pip_gather<<<sb_grid(part.n_units, 1, 8), 256, 0, ctx->stream>>>(
-		    static_cast<const bp_tables *>(part.tables), static_cast<const bp_unit *>(part.units),
-		    static_cast<const uint2 *>(part.rec), px, py, 0, d_xy);
+		k_pip_gather<<<sb_grid(2 * part.n_units, 1, 4), 512, 0, ctx->stream>>>(
+		    static_cast<const bp_tables *>(part.tables), static_cast<const bp_unit *>(part.units), part.src,
+		    static_cast<const double2 *>(part.xy_bucketed), d_xy);
 		SB_LAUNCH_CHECK(ctx);
 	}
 	{
