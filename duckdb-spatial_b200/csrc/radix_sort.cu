@@ -13,6 +13,7 @@
 #define RS_FLAG_AGG 0x40000000u
 #define RS_FLAG_INC 0x80000000u
 #define RS_VALUE_MASK 0x3FFFFFFFu
+#define RS_LOOK 8 // predecessor status words fetched per look-back round
 
 __device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t *p) {
 	uint32_t v;
@@ -23,38 +24,50 @@ __device__ __forceinline__ void st_volatile_u32(uint32_t *p, uint32_t v) {
 	asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+// Lanes of the warp whose digit equals this lane's, from 8 ballots (one per digit bit). `match.any` gives the same
+// mask in one instruction but issues at ~200 cycles per warp on sm_100 (measured: 4 of them per key made the histogram
+// kernel 225 us for 10 M keys, 16 per thread a third of a onesweep pass); the ballots cost ~25 issue slots.
+__device__ __forceinline__ unsigned rs_peers8(uint32_t d, bool valid) {
+	unsigned peers = __ballot_sync(0xFFFFFFFFu, valid);
+#pragma unroll
+	for (int b = 0; b < 8; b++) {
+		const bool bit = (d >> b) & 1u;
+		const unsigned m = __ballot_sync(0xFFFFFFFFu, bit);
+		peers &= bit ? m : ~m;
+	}
+	return peers;
+}
+
 // ---- histogram of every pass in one read of the keys --------------------------------------------------------
 template <typename KeyT, int MAX_PASSES>
 __global__ void __launch_bounds__(RS_THREADS) k_radix_hist(const KeyT *__restrict__ keys, uint64_t n, int begin_bit,
                                                            int end_bit, int passes, uint32_t *__restrict__ hist) {
-	__shared__ uint32_t s_hist[MAX_PASSES * RS_BINS];
-	for (int i = threadIdx.x; i < passes * RS_BINS; i += RS_THREADS) {
+	// 4 replicas per pass (replica = lane & 3): a digit that is constant over the warp (the top bytes of float keys)
+	// costs an 8-way instead of a 32-way same-address conflict, uniform digits pay nothing extra
+	__shared__ uint32_t s_hist[MAX_PASSES * 4 * RS_BINS];
+	for (int i = threadIdx.x; i < passes * 4 * RS_BINS; i += RS_THREADS) {
 		s_hist[i] = 0;
 	}
 	__syncthreads();
 	const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
-	// loop bound rounded up to a whole warp so that __match_any_sync sees all 32 lanes
-	const uint64_t n_round = (n + 31) & ~(uint64_t)31;
-	for (uint64_t i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; i < n_round; i += stride) {
-		const bool valid = i < n;
-		const KeyT k = valid ? keys[i] : KeyT(0);
+	uint32_t *mine = s_hist + (threadIdx.x & 3u) * RS_BINS;
+	for (uint64_t i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; i < n; i += stride) {
+		const KeyT k = keys[i];
 #pragma unroll
 		for (int p = 0; p < MAX_PASSES; p++) {
 			if (p < passes) {
 				const int shift = begin_bit + 8 * p;
 				const int bits = min(8, end_bit - shift);
-				const uint32_t d = valid ? (uint32_t)((k >> shift) & (KeyT)((1u << bits) - 1)) : 256u;
-				// warp-aggregated: one shared atomic per distinct digit in the warp (skewed digits stay cheap)
-				const unsigned peers = __match_any_sync(0xFFFFFFFFu, d);
-				if (valid && (peers & sb_lanemask_lt()) == 0) {
-					atomicAdd(&s_hist[p * RS_BINS + d], (uint32_t)__popc(peers));
-				}
+				const uint32_t d = (uint32_t)((k >> shift) & (KeyT)((1u << bits) - 1));
+				atomicAdd(&mine[p * 4 * RS_BINS + d], 1u);
 			}
 		}
 	}
 	__syncthreads();
 	for (int i = threadIdx.x; i < passes * RS_BINS; i += RS_THREADS) {
-		const uint32_t c = s_hist[i];
+		const int p = i / RS_BINS, d = i % RS_BINS;
+		const uint32_t *h = s_hist + p * 4 * RS_BINS + d;
+		const uint32_t c = h[0] + h[RS_BINS] + h[2 * RS_BINS] + h[3 * RS_BINS];
 		if (c) {
 			atomicAdd(&hist[i], c);
 		}
@@ -87,7 +100,7 @@ __global__ void __launch_bounds__(RS_BINS) k_radix_scan(uint32_t *__restrict__ h
 
 // ---- one onesweep pass ---------------------------------------------------------------------------------------
 template <typename KeyT, int ITEMS>
-__global__ void __launch_bounds__(RS_THREADS)
+__global__ void __launch_bounds__(RS_THREADS, 3)
     k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const uint32_t *__restrict__ vals_in,
                uint32_t *__restrict__ vals_out, uint64_t n, int shift, uint32_t digit_mask,
                const uint32_t *__restrict__ bin_base, uint32_t *__restrict__ tile_state, uint32_t *__restrict__ ticket) {
@@ -130,8 +143,8 @@ __global__ void __launch_bounds__(RS_THREADS)
 #pragma unroll
 	for (int i = 0; i < ITEMS; i++) {
 		const bool valid = first + (uint64_t)i * 32 < n;
-		const uint32_t d = valid ? ((uint32_t)(key[i] >> shift) & digit_mask) : 256u;
-		const unsigned peers = __match_any_sync(0xFFFFFFFFu, d);
+		const uint32_t d = valid ? ((uint32_t)(key[i] >> shift) & digit_mask) : 0u;
+		const unsigned peers = rs_peers8(d, valid);
 		const int leader = __ffs(peers) - 1;
 		uint32_t prev = 0;
 		if ((int)lane == leader && valid) {
@@ -178,17 +191,27 @@ __global__ void __launch_bounds__(RS_THREADS)
 
 	uint32_t excl = 0;
 	if (tile > 0) {
+		// look back over the predecessors' status words, RS_LOOK loads in flight at a time (a one-at-a-time walk made the
+		// first wave of tiles pay one L2 round trip per predecessor: the whole pass was latency bound at 10 M keys)
 		int64_t look = (int64_t)tile - 1;
-		while (true) {
-			const uint32_t s = ld_volatile_u32(tile_state + (uint64_t)look * RS_BINS + d);
-			if ((s & (RS_FLAG_AGG | RS_FLAG_INC)) == 0) {
-				continue; // predecessor has not published yet
+		bool done = false;
+		while (!done) {
+			uint32_t st[RS_LOOK];
+#pragma unroll
+			for (int j = 0; j < RS_LOOK; j++) {
+				st[j] = look - j >= 0 ? ld_volatile_u32(tile_state + (uint64_t)(look - j) * RS_BINS + d) : RS_FLAG_INC;
 			}
-			excl += s & RS_VALUE_MASK;
-			if (s & RS_FLAG_INC) {
-				break;
+#pragma unroll
+			for (int j = 0; j < RS_LOOK; j++) {
+				if (!done) {
+					if ((st[j] & (RS_FLAG_AGG | RS_FLAG_INC)) == 0) {
+						break; // this predecessor has not published yet: poll again from here
+					}
+					excl += st[j] & RS_VALUE_MASK;
+					look--;
+					done = (st[j] & RS_FLAG_INC) != 0;
+				}
 			}
-			look--;
 		}
 		st_volatile_u32(my_state, RS_FLAG_INC | (excl + total));
 	}
