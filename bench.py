@@ -43,6 +43,8 @@ def parse():
                     help="N>1: also move every rank's pair list to rank 0 (bounded by rank 0's NVLink ingest, "
                          "8 B/pair: see DESIGN.md section 7). Default: pair lists stay sharded, counts are all-gathered")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--ctx-opt", action="append", default=[], metavar="KEY=VALUE",
+                    help="sb_context_set_option before the run (A/B measurements, e.g. probe_path=2, fine_hist=1)")
     return ap.parse_args()
 
 
@@ -228,6 +230,9 @@ def run_ours(a):
     peak_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
 
     ctx = sb.Context(local)
+    for kv in a.ctx_opt:
+        k, v = kv.split("=")
+        ctx.set_option(k, int(v))
     stream = torch.cuda.Stream(device=dev)
     P, B = a.points, a.boxes
     h = SIDE / 2

@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(BPH_THREADS) k_bp_hist(const double *__restric
 		const int b = bp_bucket(x, y, g);
 		if (b >= 0) {
 			atomicAdd(&s_hist[b], 1u);
-			if (fine && b < BP_NB) {
+			if (b < BP_NB) {
 				const int qx = bp_q(x, g.minx, g.sx), qy = bp_q(y, g.miny, g.sy);
 				atomicAdd(&fine[(b << 10) | (((qy >> 10) & 31) << 5) | ((qx >> 10) & 31)], 1u);
 			}
@@ -824,11 +824,7 @@ int sbi_flat_probe_bucketed(sb_context *ctx, const sb_flat *tree, const sb_probe
 	SB_TRY(ctx->scratch_t(n_cand ? n_cand : 1, &d_cand));
 	{
 		sb_prof_scope ps(ctx, "bp_partition");
-		static bool sattr = false;
-		if (!sattr) {
-			SB_CUDA(cudaFuncSetAttribute(k_bp_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(bps_smem)));
-			sattr = true;
-		}
+		SB_SMEM_OPTIN(ctx, k_bp_scatter, sizeof(bps_smem));
 		k_bp_scatter<<<sb_grid(n, BPS_TILE, 2), BPS_THREADS, sizeof(bps_smem), ctx->stream>>>(
 		    a.px, a.py, n, a.index_base, d_grid, d_tab->pt_cursor, d_pxy, d_pidx);
 		SB_LAUNCH_CHECK(ctx);
@@ -841,13 +837,8 @@ int sbi_flat_probe_bucketed(sb_context *ctx, const sb_flat *tree, const sb_probe
 	}
 	SB_TRACE(ctx, "bp: scatter + cand fill");
 	if (n_units) {
-		static bool attr_set = false;
-		if (!attr_set) {
-			SB_CUDA(cudaFuncSetAttribute(k_bp_probe<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(bpp_smem<1>)));
-			SB_CUDA(cudaFuncSetAttribute(k_bp_probe<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-			                             (int)sizeof(bpp_smem<2>)));
-			attr_set = true;
-		}
+		SB_SMEM_OPTIN(ctx, k_bp_probe<1>, sizeof(bpp_smem<1>));
+		SB_SMEM_OPTIN(ctx, k_bp_probe<2>, sizeof(bpp_smem<2>));
 		const unsigned grid = (unsigned)(n_units < SB_NUM_SMS ? n_units : SB_NUM_SMS);
 		sb_prof_scope ps(ctx, "flat_probe");
 		if (mode == 1) {
@@ -1537,14 +1528,10 @@ int sbi_cell_partition(sb_context *ctx, const sb_flat *tree, const double *px, c
 	const uint64_t n_cand = totals[1], n_units = totals[2];
 	SB_ARG(n_cand < 0xFFFFFFFFull, "cell probe: candidate directory too large");
 	SB_TRY(ctx->scratch_t(n_cand ? n_cand : 1, &d_cand));
-	static bool attr_set = false;
-	if (!attr_set) {
-		SB_CUDA(cudaFuncSetAttribute(k_cp_scatter1<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(cps1_smem<false>)));
-		SB_CUDA(cudaFuncSetAttribute(k_cp_scatter2<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(cps2_smem<false>)));
-		SB_CUDA(cudaFuncSetAttribute(k_cp_scatter1<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(cps1_smem<true>)));
-		SB_CUDA(cudaFuncSetAttribute(k_cp_scatter2<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(cps2_smem<true>)));
-		attr_set = true;
-	}
+	SB_SMEM_OPTIN(ctx, k_cp_scatter1<false>, sizeof(cps1_smem<false>));
+	SB_SMEM_OPTIN(ctx, k_cp_scatter2<false>, sizeof(cps2_smem<false>));
+	SB_SMEM_OPTIN(ctx, k_cp_scatter1<true>, sizeof(cps1_smem<true>));
+	SB_SMEM_OPTIN(ctx, k_cp_scatter2<true>, sizeof(cps2_smem<true>));
 	{
 		sb_prof_scope ps(ctx, "bp_partition");
 		if (want_xy) {
@@ -1617,14 +1604,8 @@ int sbi_flat_probe_cells(sb_context *ctx, const sb_flat *tree, const sb_probe_ar
 	const uint2 *d_rec_a = static_cast<const uint2 *>(P.rec_bucketed), *d_rec_b = static_cast<const uint2 *>(P.rec);
 	const uint64_t n_units = P.n_units, n_nan = P.n_nan;
 	uint64_t totals[1] = {P.n_kept};
-	{
-		static bool attr_set = false;
-		if (!attr_set) {
-			SB_CUDA(cudaFuncSetAttribute(k_cp_probe<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(cpp_smem<1>)));
-			SB_CUDA(cudaFuncSetAttribute(k_cp_probe<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(cpp_smem<2>)));
-			attr_set = true;
-		}
-	}
+	SB_SMEM_OPTIN(ctx, k_cp_probe<1>, sizeof(cpp_smem<1>));
+	SB_SMEM_OPTIN(ctx, k_cp_probe<2>, sizeof(cpp_smem<2>));
 	if (n_units) {
 		const unsigned grid = (unsigned)(n_units < SB_NUM_SMS ? n_units : SB_NUM_SMS);
 		sb_prof_scope ps(ctx, "flat_probe");

@@ -7,6 +7,7 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <atomic>
 #include <map>
 #include <string>
 #include <vector>
@@ -170,6 +171,18 @@ static inline unsigned sb_grid(uint64_t work_items, unsigned per_block, unsigned
 	do {                                                                                                             \
 		(ctx)->launches++;                                                                                           \
 		SB_CUDA(cudaGetLastError());                                                                                 \
+	} while (0)
+
+// Opt a kernel into more than 48 KB of dynamic shared memory. The attribute is per device and the C-ABI allows contexts
+// on several devices (and threads) of one process, so it is set once per (call site, device), race-free.
+#define SB_SMEM_OPTIN(ctx, func, bytes)                                                                              \
+	do {                                                                                                             \
+		static std::atomic<uint64_t> _done{0};                                                                       \
+		const uint64_t _bit = 1ull << ((ctx)->device & 63);                                                          \
+		if (!(_done.load(std::memory_order_acquire) & _bit)) {                                                       \
+			SB_CUDA(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes)));          \
+			_done.fetch_or(_bit, std::memory_order_release);                                                         \
+		}                                                                                                            \
 	} while (0)
 
 // ---- device helpers ---------------------------------------------------------------------------------------

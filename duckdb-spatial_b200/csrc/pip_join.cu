@@ -471,11 +471,7 @@ int sbi_join_points_polygons(sb_context *ctx, const double *px, const double *py
 	if (part.n_units == 0) {
 		return SB_OK;
 	}
-	static bool attr_set = false;
-	if (!attr_set) {
-		SB_CUDA(cudaFuncSetAttribute(k_pip_join, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(pip_smem)));
-		attr_set = true;
-	}
+	SB_SMEM_OPTIN(ctx, k_pip_join, sizeof(pip_smem));
 	{
 		sb_prof_scope ps(ctx, "pip_gather");
 		k_pip_gather<<<sb_grid(2 * part.n_units, 1, 4), 512, 0, ctx->stream>>>(

@@ -279,12 +279,7 @@ int sbi_radix_sort_impl(sb_context *ctx, KeyT *keys, KeyT *keys_alt, uint32_t *v
 	uint32_t *tickets = temp + (size_t)passes * RS_BINS;
 	uint32_t *state = tickets + 64;
 
-	static bool attr_set = false;
-	if (!attr_set) {
-		SB_CUDA(cudaFuncSetAttribute(k_onesweep<KeyT, cfg::ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-		                             (int)cfg::SMEM));
-		attr_set = true;
-	}
+	SB_SMEM_OPTIN(ctx, (k_onesweep<KeyT, cfg::ITEMS>), cfg::SMEM);
 	{
 		sb_prof_scope ps(ctx, "radix_hist");
 		k_radix_hist<KeyT, cfg::MAX_PASSES><<<sb_grid(n, RS_THREADS * 8, 8), RS_THREADS, 0, ctx->stream>>>(
