@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(BPH_THREADS) k_bp_hist(const double *__restric
 		const int b = bp_bucket(x, y, g);
 		if (b >= 0) {
 			atomicAdd(&s_hist[b], 1u);
-			if (b < BP_NB) {
+			if (fine && b < BP_NB) {
 				const int qx = bp_q(x, g.minx, g.sx), qy = bp_q(y, g.miny, g.sy);
 				atomicAdd(&fine[(b << 10) | (((qy >> 10) & 31) << 5) | ((qx >> 10) & 31)], 1u);
 			}

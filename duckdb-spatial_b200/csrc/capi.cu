@@ -482,15 +482,29 @@ static int join_points_boxes_pipelined(sb_context *ctx, sb_predicate pred, const
 	if (slot_cap < n_boxes) {
 		slot_cap = n_boxes;
 	}
-	double *dx[2], *dy[2];
+	// Input slots: as many chunks as fit a staging budget (all of them at the BASELINE sizes), so that the H2D copies run
+	// ahead at full rate and are over early: the D2H of the pair lists (4 x the input bytes at C3) then has the link to
+	// itself. (With two input slots the H2D traffic was spread over the whole call and the duplex interference cost
+	// ~15 % of the D2H rate: scripts/diag_pcie.py.) Output slots: two, the pairs leave as fast as the link allows.
+	const uint64_t nchunks = (n_points + chunk - 1) / chunk;
+	size_t free_b = 0, total_b = 0;
+	SB_CUDA(cudaMemGetInfo(&free_b, &total_b));
+	uint64_t in_slots = (uint64_t)(free_b / 4) / (chunk * 2 * sizeof(double));
+	in_slots = in_slots < 2 ? 2 : in_slots;
+	in_slots = in_slots > nchunks ? (nchunks ? nchunks : 1) : in_slots;
+	std::vector<double *> dx(in_slots), dy(in_slots);
+	std::vector<cudaEvent_t> h2d_done(in_slots), in_free(in_slots);
 	uint32_t *dp[2], *db[2];
-	cudaEvent_t h2d_done[2], d2h_done[2], probe_done[2];
-	for (int k = 0; k < 2; k++) {
+	cudaEvent_t d2h_done[2], probe_done[2];
+	for (uint64_t k = 0; k < in_slots; k++) {
 		SB_TRY(ctx->scratch_t(chunk, &dx[k]));
 		SB_TRY(ctx->scratch_t(chunk, &dy[k]));
+		SB_CUDA(cudaEventCreateWithFlags(&h2d_done[k], cudaEventDisableTiming));
+		SB_CUDA(cudaEventCreateWithFlags(&in_free[k], cudaEventDisableTiming));
+	}
+	for (int k = 0; k < 2; k++) {
 		SB_TRY(ctx->scratch_t(slot_cap, &dp[k]));
 		SB_TRY(ctx->scratch_t(slot_cap, &db[k]));
-		SB_CUDA(cudaEventCreateWithFlags(&h2d_done[k], cudaEventDisableTiming));
 		SB_CUDA(cudaEventCreateWithFlags(&d2h_done[k], cudaEventDisableTiming));
 		SB_CUDA(cudaEventCreateWithFlags(&probe_done[k], cudaEventDisableTiming));
 	}
@@ -498,33 +512,34 @@ static int join_points_boxes_pipelined(sb_context *ctx, sb_predicate pred, const
 	SB_CUDA(cudaEventRecord(probe_done[0], ctx->stream));
 	SB_CUDA(cudaStreamWaitEvent(ctx->h2d_stream, probe_done[0], 0));
 	SB_CUDA(cudaStreamWaitEvent(ctx->d2h_stream, probe_done[0], 0));
+	for (uint64_t k = 0; k < in_slots; k++) {
+		SB_CUDA(cudaEventRecord(in_free[k], ctx->stream));
+	}
 	const sb_arena::mark_t mark = ctx->arena.mark();
 	int status = SB_OK;
 	uint64_t total = 0;
-	const uint64_t nchunks = (n_points + chunk - 1) / chunk;
 	auto issue_h2d = [&](uint64_t c) -> int {
-		const int slot = (int)(c & 1);
+		const uint64_t islot = c % in_slots;
 		const uint64_t beg = c * chunk, len = (n_points - beg < chunk) ? n_points - beg : chunk;
-		// the slot's previous occupant (chunk c-2) must have been probed
-		SB_CUDA(cudaStreamWaitEvent(ctx->h2d_stream, probe_done[slot], 0));
-		SB_CUDA(cudaMemcpyAsync(dx[slot], px + beg, len * sizeof(double), cudaMemcpyHostToDevice, ctx->h2d_stream));
-		SB_CUDA(cudaMemcpyAsync(dy[slot], py + beg, len * sizeof(double), cudaMemcpyHostToDevice, ctx->h2d_stream));
-		SB_CUDA(cudaEventRecord(h2d_done[slot], ctx->h2d_stream));
+		// the slot's previous occupant (chunk c - in_slots) must have been probed
+		SB_CUDA(cudaStreamWaitEvent(ctx->h2d_stream, in_free[islot], 0));
+		SB_CUDA(cudaMemcpyAsync(dx[islot], px + beg, len * sizeof(double), cudaMemcpyHostToDevice, ctx->h2d_stream));
+		SB_CUDA(cudaMemcpyAsync(dy[islot], py + beg, len * sizeof(double), cudaMemcpyHostToDevice, ctx->h2d_stream));
+		SB_CUDA(cudaEventRecord(h2d_done[islot], ctx->h2d_stream));
 		return SB_OK;
 	};
-	if (nchunks) {
-		status = issue_h2d(0);
-	}
+	uint64_t next_h2d = 0;
 	for (uint64_t c = 0; c < nchunks && status == SB_OK; c++) {
 		const int slot = (int)(c & 1);
+		const uint64_t islot = c % in_slots;
 		const uint64_t beg = c * chunk, len = (n_points - beg < chunk) ? n_points - beg : chunk;
-		if (c + 1 < nchunks) {
-			status = issue_h2d(c + 1);
-			if (status != SB_OK) {
-				break;
-			}
+		while (next_h2d < nchunks && next_h2d < c + in_slots && status == SB_OK) {
+			status = issue_h2d(next_h2d++);
 		}
-		SB_CUDA(cudaStreamWaitEvent(ctx->stream, h2d_done[slot], 0));
+		if (status != SB_OK) {
+			break;
+		}
+		SB_CUDA(cudaStreamWaitEvent(ctx->stream, h2d_done[islot], 0));
 		SB_CUDA(cudaStreamWaitEvent(ctx->stream, d2h_done[slot], 0)); // pairs of chunk c-2 have left the slot
 		// probe the chunk; split it when its pairs do not fit the slot
 		uint64_t done = 0;
@@ -534,8 +549,8 @@ static int join_points_boxes_pipelined(sb_context *ctx, sb_predicate pred, const
 				piece = len - done;
 			}
 			sb_probe_args a;
-			a.px = dx[slot] + done;
-			a.py = dy[slot] + done;
+			a.px = dx[islot] + done;
+			a.py = dy[islot] + done;
 			a.m = piece;
 			a.index_base = (uint32_t)(beg + done);
 			a.build_box2d = box2d;
@@ -566,12 +581,16 @@ static int join_points_boxes_pipelined(sb_context *ctx, sb_predicate pred, const
 		}
 		SB_CUDA(cudaEventRecord(d2h_done[slot], ctx->d2h_stream));
 		SB_CUDA(cudaEventRecord(probe_done[slot], ctx->stream));
+		SB_CUDA(cudaEventRecord(in_free[islot], ctx->stream));
 	}
 	cudaStreamSynchronize(ctx->h2d_stream);
 	cudaStreamSynchronize(ctx->d2h_stream);
 	cudaStreamSynchronize(ctx->stream);
-	for (int k = 0; k < 2; k++) {
+	for (uint64_t k = 0; k < in_slots; k++) {
 		cudaEventDestroy(h2d_done[k]);
+		cudaEventDestroy(in_free[k]);
+	}
+	for (int k = 0; k < 2; k++) {
 		cudaEventDestroy(d2h_done[k]);
 		cudaEventDestroy(probe_done[k]);
 	}
