@@ -795,8 +795,8 @@ int sbi_flat_probe_bucketed(sb_context *ctx, const sb_flat *tree, const sb_probe
 	SB_TRY(ctx->scratch_t(1, &d_counter));
 	SB_TRY(ctx->scratch_t(n, &d_pxy));
 	SB_TRY(ctx->scratch_t(n, &d_pidx));
-	SB_CUDA(cudaMemsetAsync(d_tab, 0, sizeof(bp_tables), ctx->stream));
-	SB_CUDA(cudaMemsetAsync(d_counter, 0, sizeof(*d_counter), ctx->stream));
+	SB_TRY(sbi_zero(ctx, d_tab, sizeof(bp_tables)));
+	SB_TRY(sbi_zero(ctx, d_counter, sizeof(*d_counter)));
 	const sb_flat_header *d_hdr = static_cast<const sb_flat_header *>(tree->buffer);
 	SB_TRACE(ctx, "bp: scratch + memsets");
 	{
@@ -816,9 +816,7 @@ int sbi_flat_probe_bucketed(sb_context *ctx, const sb_flat *tree, const sb_probe
 	}
 	SB_TRACE(ctx, "bp: hist + cand count + scan");
 	uint64_t totals[4];
-	SB_CUDA(cudaMemcpyAsync(ctx->pinned_u64, d_tab->totals, sizeof(totals), cudaMemcpyDeviceToHost, ctx->stream));
-	SB_CUDA(cudaStreamSynchronize(ctx->stream));
-	memcpy(totals, ctx->pinned_u64, sizeof(totals));
+	SB_TRY(sbi_read_words(ctx, d_tab->totals, 4, totals));
 	const uint64_t n_cand = totals[1], n_units = totals[2], n_nan = totals[3];
 	SB_ARG(n_cand < 0xFFFFFFFFull, "bucketed probe: candidate directory too large");
 	SB_TRY(ctx->scratch_t(n_cand ? n_cand : 1, &d_cand));
@@ -1502,8 +1500,8 @@ int sbi_cell_partition(sb_context *ctx, const sb_flat *tree, const double *px, c
 	}
 	SB_TRY(ctx->scratch_t(CP_NCELL, &d_fine));
 	SB_TRY(ctx->scratch_t(CP_NCELL + 1, &d_cell_off));
-	SB_CUDA(cudaMemsetAsync(d_tab, 0, sizeof(bp_tables), ctx->stream));
-	SB_CUDA(cudaMemsetAsync(d_fine, 0, sizeof(uint32_t) * CP_NCELL, ctx->stream));
+	SB_TRY(sbi_zero(ctx, d_tab, sizeof(bp_tables)));
+	SB_TRY(sbi_zero(ctx, d_fine, sizeof(uint32_t) * CP_NCELL));
 	const sb_flat_header *d_hdr = static_cast<const sb_flat_header *>(tree->buffer);
 	{
 		sb_prof_scope ps(ctx, "bp_partition");
@@ -1522,9 +1520,7 @@ int sbi_cell_partition(sb_context *ctx, const sb_flat *tree, const double *px, c
 	}
 	SB_TRACE(ctx, "cp: hist + cand count + scan");
 	uint64_t totals[4];
-	SB_CUDA(cudaMemcpyAsync(ctx->pinned_u64, d_tab->totals, sizeof(totals), cudaMemcpyDeviceToHost, ctx->stream));
-	SB_CUDA(cudaStreamSynchronize(ctx->stream));
-	memcpy(totals, ctx->pinned_u64, sizeof(totals));
+	SB_TRY(sbi_read_words(ctx, d_tab->totals, 4, totals));
 	const uint64_t n_cand = totals[1], n_units = totals[2];
 	SB_ARG(n_cand < 0xFFFFFFFFull, "cell probe: candidate directory too large");
 	SB_TRY(ctx->scratch_t(n_cand ? n_cand : 1, &d_cand));
@@ -1594,7 +1590,7 @@ int sbi_flat_probe_cells(sb_context *ctx, const sb_flat *tree, const sb_probe_ar
 
 	unsigned long long *d_counter = nullptr;
 	SB_TRY(ctx->scratch_t(1, &d_counter));
-	SB_CUDA(cudaMemsetAsync(d_counter, 0, sizeof(*d_counter), ctx->stream));
+	SB_TRY(sbi_zero(ctx, d_counter, sizeof(*d_counter)));
 	sb_cell_partition P;
 	SB_TRY(sbi_cell_partition(ctx, tree, a.px, a.py, n, a.index_base, &P));
 	const bp_grid *d_grid = static_cast<const bp_grid *>(P.grid);

@@ -95,9 +95,9 @@ struct sb_context {
 	double trace_t0 = 0;
 	// second and third stream of the host-pointer join pipeline (H2D of the next chunk / D2H of the previous one)
 	cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
-	uint64_t pipe_chunk = 16u << 20; // probe rows per chunk of that pipeline (option "pipe_chunk")
+	uint64_t pipe_chunk = 8u << 20;  // probe rows per chunk of that pipeline (option "pipe_chunk")
 	// pinned staging for small host<->device transfers (counters)
-	uint64_t *pinned_u64 = nullptr;
+	uint64_t *pinned_u64 = nullptr, *pinned_u64_dev = nullptr;
 
 	int scratch(size_t bytes, void **out) {
 		return arena.alloc(bytes, out);
@@ -120,7 +120,7 @@ struct sb_prof_scope {
 void sb_trace_point(sb_context *ctx, const char *what);
 #define SB_TRACE(ctx, what)                                                                                          \
 	do {                                                                                                             \
-		if ((ctx)->trace) {                                                                                          \
+		if ((ctx)->trace & 1) {                                                                                      \
 			sb_trace_point(ctx, what);                                                                               \
 		}                                                                                                            \
 	} while (0)

@@ -28,6 +28,46 @@ void sb_trace_point(sb_context *ctx, const char *what) {
 	ctx->trace_t0 = t;
 }
 
+// ---- small transfers that stay off the copy engines ----------------------------------------------------------
+// A counter read-back or a small memset issued as cudaMemcpyAsync / cudaMemsetAsync runs on a copy engine; inside the
+// host-pointer join pipeline that engine is busy with ~20 ms bulk copies of the previous chunk's pairs and the small
+// transfer queues behind them, which serialised probe and copy-out (measured: 282 -> see DESIGN.md section 5). So
+// counters are stored to mapped pinned memory by a one-block kernel and small clears are kernels too.
+__global__ void k_read_words(const uint64_t *__restrict__ src, uint64_t *__restrict__ dst, int n) {
+	if ((int)threadIdx.x < n) {
+		dst[threadIdx.x] = src[threadIdx.x];
+	}
+	__threadfence_system();
+}
+
+int sbi_read_words(sb_context *ctx, const void *dev, int nwords, uint64_t *host) {
+	SB_ARG(nwords >= 1 && nwords <= 64, "sbi_read_words: 1..64 words");
+	k_read_words<<<1, 64, 0, ctx->stream>>>(static_cast<const uint64_t *>(dev), ctx->pinned_u64_dev, nwords);
+	SB_CUDA(cudaGetLastError());
+	SB_CUDA(cudaStreamSynchronize(ctx->stream));
+	memcpy(host, ctx->pinned_u64, (size_t)nwords * sizeof(uint64_t));
+	return SB_OK;
+}
+
+__global__ void __launch_bounds__(256) k_zero_words(uint32_t *__restrict__ p, uint64_t nwords) {
+	for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < nwords; i += (uint64_t)gridDim.x * blockDim.x) {
+		p[i] = 0;
+	}
+}
+
+int sbi_zero(sb_context *ctx, void *dev, size_t bytes) {
+	SB_ARG((bytes & 3) == 0 && (reinterpret_cast<uintptr_t>(dev) & 3) == 0, "sbi_zero: 4-byte granules");
+	if (bytes == 0) {
+		return SB_OK;
+	}
+	const uint64_t nwords = bytes / 4;
+	uint64_t blocks = (nwords + 255) / 256;
+	blocks = blocks > 1184 ? 1184 : blocks;
+	k_zero_words<<<(unsigned)blocks, 256, 0, ctx->stream>>>(static_cast<uint32_t *>(dev), nwords);
+	SB_CUDA(cudaGetLastError());
+	return SB_OK;
+}
+
 // ---- arena --------------------------------------------------------------------------------------------------
 int sb_arena::alloc(size_t bytes, void **out) {
 	bytes = (bytes + 255) & ~(size_t)255;
@@ -129,7 +169,9 @@ extern "C" int sb_context_create(int device, sb_context **out) {
 		uint64_t keep = UINT64_MAX;
 		SB_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
 	}
-	SB_CUDA(cudaMallocHost((void **)&ctx->pinned_u64, 64 * sizeof(uint64_t)));
+	// mapped: the counters are written by a kernel (sbi_read_words), not by a copy engine
+	SB_CUDA(cudaHostAlloc((void **)&ctx->pinned_u64, 64 * sizeof(uint64_t), cudaHostAllocMapped));
+	SB_CUDA(cudaHostGetDevicePointer((void **)&ctx->pinned_u64_dev, ctx->pinned_u64, 0));
 	*out = ctx;
 	return SB_OK;
 }

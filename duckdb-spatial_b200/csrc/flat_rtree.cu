@@ -359,7 +359,7 @@ int sbi_flat_probe(sb_context *ctx, const sb_flat *tree, const sb_probe_args &a,
 	memcpy(M.layer_bounds, tree->h.layer_bounds, sizeof(M.layer_bounds));
 	unsigned long long *d_counter = nullptr;
 	SB_TRY(ctx->scratch_t(1, &d_counter));
-	SB_CUDA(cudaMemsetAsync(d_counter, 0, sizeof(*d_counter), ctx->stream));
+	SB_TRY(sbi_zero(ctx, d_counter, sizeof(*d_counter)));
 	const unsigned grid = sb_grid((a.m + 31) / 32, PR_WARPS, 8);
 	{
 		sb_prof_scope ps(ctx, "flat_probe");

@@ -146,3 +146,6 @@ int sbi_unmatched_rows(sb_context *ctx, const uint8_t *flags, uint64_t n, uint32
 
 // read a device u64 counter back (synchronises the stream)
 int sbi_read_u64(sb_context *ctx, const uint64_t *dev, uint64_t *host);
+// context.cu: counter read-back / small clears as kernels (kept off the copy engines, see there)
+int sbi_read_words(sb_context *ctx, const void *dev, int nwords, uint64_t *host);
+int sbi_zero(sb_context *ctx, void *dev, size_t bytes);

@@ -4,10 +4,7 @@
 #include "pip.cuh"
 
 int sbi_read_u64(sb_context *ctx, const uint64_t *dev, uint64_t *host) {
-	SB_CUDA(cudaMemcpyAsync(ctx->pinned_u64, dev, sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
-	SB_CUDA(cudaStreamSynchronize(ctx->stream));
-	*host = ctx->pinned_u64[0];
-	return SB_OK;
+	return sbi_read_words(ctx, dev, 1, host);
 }
 
 __global__ void __launch_bounds__(256) k_pack_box2d(const double *__restrict__ x0, const double *__restrict__ y0,
@@ -120,7 +117,7 @@ static int run_refine(sb_context *ctx, const char *tag, PRED pred, uint32_t *pa,
 		SB_TRY(ctx->scratch_t(n, &tmp_d));
 	}
 	SB_TRY(ctx->scratch_t(1, &d_counter));
-	SB_CUDA(cudaMemsetAsync(d_counter, 0, sizeof(*d_counter), ctx->stream));
+	SB_TRY(sbi_zero(ctx, d_counter, sizeof(*d_counter)));
 	{
 		sb_prof_scope ps(ctx, tag);
 		k_refine<<<sb_grid(n, 256, 16), 256, 0, ctx->stream>>>(pred, pa, pb, n, oa, ob, tmp_d, d_counter);

@@ -60,8 +60,9 @@ SB_API int sb_context_set_stream(sb_context *ctx, void *cuda_stream);
 SB_API int sb_context_sync(sb_context *ctx);
 /* tuning / test knobs. "probe_path": 0 = auto, 1 = per-probe tree walk only, 2 = bucketed bulk probe only
  * (both produce the same pair set; the parity tests run every join through both). "pipe_chunk": probe rows per
- * chunk of the host-pointer join pipeline (default 16 Mi; calls with >= 2 chunks overlap H2D / probe / D2H).
- * "trace": 1 = print per-phase wall times to stderr (synchronises at every phase). "probe_path" 3 = the cell-sorted
+ * chunk of the host-pointer join pipeline (default 8 Mi; calls with >= 2 chunks overlap H2D / probe / D2H).
+ * "trace": bit 0 = print per-phase wall times to stderr (synchronises at every phase), bit 1 = print the per-chunk
+ * timeline of that pipeline's three streams when the call ends (no extra synchronisation). "probe_path" 3 = the cell-sorted
  * bulk probe (v3, what auto picks), 2 = the bucketed v2 kernel. "pip_path": route of sb_join_points_polygons, 0 = auto,
  * 1 = FlatRTree candidates + sb_refine_point_polygon, 2 = polygon-centric kernel. */
 SB_API int sb_context_set_option(sb_context *ctx, const char *key, int64_t value);

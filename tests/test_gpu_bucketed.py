@@ -225,7 +225,7 @@ def test_host_pipeline_chunks(ctx, O):
         assert rc == -3 and cnt.value == len(e)
     finally:
         ctx.set_option("probe_path", 0)
-        ctx.set_option("pipe_chunk", 16 << 20)
+        ctx.set_option("pipe_chunk", 8 << 20)
 
 
 def test_heavy_sub_cell(ctx, O):
