@@ -1,6 +1,7 @@
 // bbox.cu -- K1 (bounding boxes from POINT_2D / BOX_2D / serialized GEOMETRY) and K2 (Hilbert keys).
 // All kernels are HBM-streaming: one coalesced read of the coordinates, one coalesced write of the boxes / keys.
 #include "internal.cuh"
+#include "blob.cuh"
 
 // ---------------------------------------------------------------------------------------------------------------
 // POINT_2D -> BOX_2DF. 16 B in, 16 B out per point. Two points per thread: double2 loads, two float4 stores.
@@ -68,23 +69,6 @@ int sbi_bbox_box2d(sb_context *ctx, const double *x0, const double *y0, const do
 // ---------------------------------------------------------------------------------------------------------------
 // Serialized GEOMETRY blobs. Byte-exact loads (blobs packed by the host may be only 1-byte aligned).
 // ---------------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t ld_u32(const uint8_t *p) {
-	if (((uintptr_t)p & 3) == 0) {
-		return *reinterpret_cast<const uint32_t *>(p);
-	}
-	return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
-}
-__device__ __forceinline__ float ld_f32(const uint8_t *p) {
-	return __uint_as_float(ld_u32(p));
-}
-__device__ __forceinline__ double ld_f64(const uint8_t *p) {
-	if (((uintptr_t)p & 7) == 0) {
-		return *reinterpret_cast<const double *>(p);
-	}
-	const unsigned long long lo = ld_u32(p), hi = ld_u32(p + 4);
-	return __longlong_as_double((long long)(lo | (hi << 32)));
-}
-
 // geometry_t::TryGetCachedBounds, geometry_type.hpp:102-148. returns 1 / 0 / SB_ROW_* (<0)
 __device__ __forceinline__ int cached_bounds(const uint8_t *b, uint64_t len, float4 &box) {
 	if (len < 4) {

@@ -129,6 +129,126 @@ extern "C" int sb_hilbert_geom_bounds(sb_context *ctx, sb_mem mem, const uint8_t
 	return blob_call(ctx, mem, 3, data, offsets, n, nullptr, nullptr, out, nullptr, row_status, bounds4);
 }
 
+// ---- GEOMETRY -> POINT_2D / POLYGON_2D columns -------------------------------------------------------------------
+static int blob_inputs(sb_context *ctx, sb_mem mem, const uint8_t *data, const uint64_t *offsets, uint64_t n,
+                       const uint8_t **d_data, const uint64_t **d_off) {
+	SB_ARG(data != nullptr && offsets != nullptr, "data/offsets");
+	uint64_t total = 0;
+	if (mem == SB_HOST) {
+		total = offsets[n];
+	} else {
+		SB_TRY(sbi_read_words(ctx, offsets + n, 1, &total));
+	}
+	SB_TRY(sb_to_device(ctx, mem, data, total, d_data));
+	SB_TRY(sb_to_device(ctx, mem, offsets, n + 1, d_off));
+	return SB_OK;
+}
+
+static int blob_verdict(sb_context *ctx, const int *d_bad) {
+	uint64_t bad = 0;
+	SB_TRY(sbi_read_words(ctx, d_bad, 1, &bad)); // d_bad is an 8-byte scratch cell, low word = flag
+	if ((uint32_t)bad == 2) {
+		sb_set_error("GEOMETRY cast: row(s) of another geometry type, or malformed blob(s); see row_status");
+		return SB_ERR_GEOMETRY;
+	}
+	if ((uint32_t)bad == 1) {
+		sb_set_error("Cannot cast empty point GEOMETRY to POINT_2D; see row_status");
+		return SB_ERR_EMPTY;
+	}
+	return SB_OK;
+}
+
+extern "C" int sb_points_from_blobs(sb_context *ctx, sb_mem mem, const uint8_t *data, const uint64_t *offsets, uint64_t n,
+                                    double *out_x, double *out_y, int32_t *row_status) {
+	SB_BEGIN(ctx);
+	if (n == 0) {
+		return SB_OK;
+	}
+	SB_ARG(out_x != nullptr && out_y != nullptr, "out_x/out_y");
+	const uint8_t *d_data;
+	const uint64_t *d_off;
+	SB_TRY(blob_inputs(ctx, mem, data, offsets, n, &d_data, &d_off));
+	double *dx = nullptr, *dy = nullptr;
+	int32_t *d_status = nullptr;
+	uint64_t *d_bad = nullptr;
+	SB_TRY(ctx->scratch_t(1, &d_bad));
+	SB_TRY(sbi_zero(ctx, d_bad, sizeof(uint64_t)));
+	SB_TRY(sb_out_buffer(ctx, mem, out_x, n, &dx));
+	SB_TRY(sb_out_buffer(ctx, mem, out_y, n, &dy));
+	SB_TRY(sb_out_buffer(ctx, mem, row_status, n, &d_status));
+	SB_TRY(sbi_points_from_blobs(ctx, d_data, d_off, n, dx, dy, d_status, reinterpret_cast<int *>(d_bad)));
+	SB_TRY(sb_to_host(ctx, mem, out_x, dx, n));
+	SB_TRY(sb_to_host(ctx, mem, out_y, dy, n));
+	SB_TRY(sb_to_host(ctx, mem, row_status, d_status, n));
+	const int verdict = blob_verdict(ctx, reinterpret_cast<const int *>(d_bad));
+	const int s = finish(ctx, mem);
+	return s != SB_OK ? s : verdict;
+}
+
+extern "C" int sb_polygons_from_blobs(sb_context *ctx, sb_mem mem, const uint8_t *data, const uint64_t *offsets,
+                                      uint64_t n, uint64_t *poly_ring_off, uint64_t *ring_vert_off, double *vx, double *vy,
+                                      uint64_t ring_capacity, uint64_t vertex_capacity, uint64_t *n_rings,
+                                      uint64_t *n_verts, int32_t *row_status) {
+	SB_BEGIN(ctx);
+	SB_ARG(n_rings != nullptr && n_verts != nullptr, "n_rings/n_verts");
+	SB_ARG(poly_ring_off != nullptr, "poly_ring_off");
+	*n_rings = 0;
+	*n_verts = 0;
+	if (n == 0) {
+		if (mem == SB_HOST) {
+			poly_ring_off[0] = 0;
+			if (ring_vert_off) {
+				ring_vert_off[0] = 0;
+			}
+		} else {
+			SB_TRY(sbi_zero(ctx, poly_ring_off, sizeof(uint64_t)));
+			if (ring_vert_off) {
+				SB_TRY(sbi_zero(ctx, ring_vert_off, sizeof(uint64_t)));
+			}
+			SB_CUDA(cudaStreamSynchronize(ctx->stream));
+		}
+		return SB_OK;
+	}
+	const uint8_t *d_data;
+	const uint64_t *d_off;
+	SB_TRY(blob_inputs(ctx, mem, data, offsets, n, &d_data, &d_off));
+	uint64_t *d_pro = nullptr, *d_rvo = nullptr;
+	double *dvx = nullptr, *dvy = nullptr;
+	int32_t *d_status = nullptr;
+	uint64_t *d_bad = nullptr;
+	SB_TRY(ctx->scratch_t(1, &d_bad));
+	SB_TRY(sbi_zero(ctx, d_bad, sizeof(uint64_t)));
+	SB_TRY(sb_out_buffer(ctx, mem, poly_ring_off, n + 1, &d_pro));
+	SB_TRY(sb_out_buffer(ctx, mem, row_status, n, &d_status));
+	sb_poly_transcode T;
+	SB_TRY(sbi_polygons_count(ctx, d_data, d_off, n, &T, d_status, reinterpret_cast<int *>(d_bad), d_pro, n_rings, n_verts));
+	SB_TRY(sb_to_host(ctx, mem, poly_ring_off, d_pro, n + 1));
+	SB_TRY(sb_to_host(ctx, mem, row_status, d_status, n));
+	const bool fits = *n_rings <= ring_capacity && *n_verts <= vertex_capacity && ring_vert_off != nullptr &&
+	                  (*n_verts == 0 || (vx != nullptr && vy != nullptr));
+	if (fits) {
+		SB_TRY(sb_out_buffer(ctx, mem, ring_vert_off, *n_rings + 1, &d_rvo));
+		SB_TRY(sb_out_buffer(ctx, mem, vx, *n_verts, &dvx));
+		SB_TRY(sb_out_buffer(ctx, mem, vy, *n_verts, &dvy));
+		SB_TRY(sbi_polygons_fill(ctx, d_data, d_off, n, &T, d_pro, d_rvo, dvx, dvy));
+		SB_TRY(sb_to_host(ctx, mem, ring_vert_off, d_rvo, *n_rings + 1));
+		SB_TRY(sb_to_host(ctx, mem, vx, dvx, *n_verts));
+		SB_TRY(sb_to_host(ctx, mem, vy, dvy, *n_verts));
+	}
+	const int verdict = blob_verdict(ctx, reinterpret_cast<const int *>(d_bad));
+	const int s = finish(ctx, mem);
+	if (s != SB_OK) {
+		return s;
+	}
+	if (!fits) {
+		sb_set_error("polygons_from_blobs: %llu rings / %llu vertices, capacity %llu / %llu",
+		             (unsigned long long)*n_rings, (unsigned long long)*n_verts, (unsigned long long)ring_capacity,
+		             (unsigned long long)vertex_capacity);
+		return SB_ERR_CAPACITY;
+	}
+	return verdict;
+}
+
 // ---- K2 ---------------------------------------------------------------------------------------------------------
 extern "C" int sb_hilbert_xy(sb_context *ctx, sb_mem mem, const double *x, const double *y, uint64_t n,
                              const double *bounds4, uint32_t *out) {

@@ -145,6 +145,18 @@ int sbi_unmatched_rows(sb_context *ctx, const uint8_t *flags, uint64_t n, uint32
                        uint64_t capacity, uint64_t *count);
 
 // read a device u64 counter back (synchronises the stream)
+// transcode.cu: GEOMETRY blobs -> POINT_2D / POLYGON_2D columns
+struct sb_poly_transcode {
+	uint32_t *row_rings = nullptr;            // rings per row (0 for bad rows)
+	unsigned long long *row_verts = nullptr;  // vertices per row, then the row's first vertex
+	unsigned long long *tile_sums = nullptr, *totals = nullptr;
+};
+int sbi_points_from_blobs(sb_context *ctx, const uint8_t *data, const uint64_t *off, uint64_t n, double *ox, double *oy,
+                          int32_t *status, int *any_bad);
+int sbi_polygons_count(sb_context *ctx, const uint8_t *data, const uint64_t *off, uint64_t n, sb_poly_transcode *T,
+                       int32_t *status, int *any_bad, uint64_t *poly_ring_off, uint64_t *n_rings, uint64_t *n_verts);
+int sbi_polygons_fill(sb_context *ctx, const uint8_t *data, const uint64_t *off, uint64_t n, const sb_poly_transcode *T,
+                      const uint64_t *poly_ring_off, uint64_t *ring_vert_off, double *vx, double *vy);
 int sbi_read_u64(sb_context *ctx, const uint64_t *dev, uint64_t *host);
 // context.cu: counter read-back / small clears as kernels (kept off the copy engines, see there)
 int sbi_read_words(sb_context *ctx, const void *dev, int nwords, uint64_t *host);

@@ -147,6 +147,42 @@ class Context:
         capi.check(rc)
         return box, valid
 
+    # -- GEOMETRY -> coordinate columns --------------------------------------------------------------------
+    def points_from_blobs(self, data, offsets, want_status=False):
+        """GEOMETRY -> POINT_2D cast (PointCasts::FromGeometryCast): (x, y); raises where the reference throws."""
+        n = len(offsets) - 1
+        x = self._empty(data, (n,), np.float64)
+        y = self._empty(data, (n,), np.float64)
+        status = self._empty(data, (n,), np.int32)
+        rc = self.L.sb_points_from_blobs(self.h, self._mem(data, offsets), _ptr(data), _ptr(offsets), n, _ptr(x), _ptr(y),
+                                         _ptr(status))
+        if want_status:
+            return x, y, status, rc
+        capi.check(rc)
+        return x, y
+
+    def polygons_from_blobs(self, data, offsets, want_status=False):
+        """GEOMETRY -> POLYGON_2D cast in list layout: (poly_ring_off [n+1], ring_vert_off [rings+1], vx, vy).
+        Two calls through the C-ABI: the first sizes the outputs (SB_ERR_CAPACITY with the counts)."""
+        n = len(offsets) - 1
+        mem = self._mem(data, offsets)
+        poly_off = self._empty(data, (n + 1,), np.uint64)
+        status = self._empty(data, (n,), np.int32)
+        nr, nv = C.c_uint64(0), C.c_uint64(0)
+        rc = self.L.sb_polygons_from_blobs(self.h, mem, _ptr(data), _ptr(offsets), n, _ptr(poly_off), None, None, None,
+                                           0, 0, C.byref(nr), C.byref(nv), _ptr(status))
+        if rc not in (capi.OK, capi.ERR_CAPACITY, capi.ERR_GEOMETRY):
+            capi.check(rc)
+        ring_off = self._empty(data, (nr.value + 1,), np.uint64)
+        vx = self._empty(data, (nv.value,), np.float64)
+        vy = self._empty(data, (nv.value,), np.float64)
+        rc = self.L.sb_polygons_from_blobs(self.h, mem, _ptr(data), _ptr(offsets), n, _ptr(poly_off), _ptr(ring_off),
+                                           _ptr(vx), _ptr(vy), nr.value, nv.value, C.byref(nr), C.byref(nv), _ptr(status))
+        if want_status:
+            return poly_off, ring_off, vx, vy, status, rc
+        capi.check(rc)
+        return poly_off, ring_off, vx, vy
+
     # -- K2 ------------------------------------------------------------------------------------------------
     def st_hilbert_xy(self, x, y, bounds):
         x, y = self._f64(x), self._f64(y)

@@ -44,6 +44,7 @@ typedef enum {
 #define SB_ROW_BAD_VERSION (-1) /* geometry_properties.hpp:28-36 CheckVersion throws NotImplementedException */
 #define SB_ROW_TRUNCATED (-2)   /* Cursor bounds check, util/cursor.hpp throws SerializationException */
 #define SB_ROW_EMPTY 1          /* ST_Hilbert(geom,bounds) on empty input: InvalidInputException */
+#define SB_ROW_WRONG_TYPE (-3)  /* GEOMETRY -> POINT_2D / POLYGON_2D cast of another geometry type: ConversionException */
 
 typedef struct sb_context sb_context;
 typedef struct sb_rtree sb_rtree; /* persistent RTREE index, STR bulk-loaded (CREATE INDEX ... USING RTREE) */
@@ -90,6 +91,24 @@ SB_API int sb_bbox_from_blobs(sb_context *ctx, sb_mem mem, const uint8_t *data, 
  * Serde::Deserialize (geometry_serialization.cpp:290-329) + sgl::ops::try_get_extent_xy (sgl.hpp:1408-1486) */
 SB_API int sb_extent_from_blobs(sb_context *ctx, sb_mem mem, const uint8_t *data, const uint64_t *offsets, uint64_t n,
                                 double *out_box4, uint8_t *out_valid, int32_t *row_status);
+
+/* ---- GEOMETRY column -> coordinate columns (what the join entry points take) ------------------------------
+ * GEOMETRY -> POINT_2D: replaces PointCasts::FromGeometryCast, spatial_functions_cast.cpp:247-270 (Serde::Deserialize
+ * + get_vertex_xy(0)). The reference throws on the first non-POINT / empty POINT row; here every row gets a status
+ * (row_status may be NULL), bad rows yield NaN, NaN and the call returns SB_ERR_GEOMETRY (wrong type, malformed) or
+ * SB_ERR_EMPTY (only empty points) after the whole column is converted. Z / M ordinates are dropped. */
+SB_API int sb_points_from_blobs(sb_context *ctx, sb_mem mem, const uint8_t *data, const uint64_t *offsets, uint64_t n,
+                                double *out_x, double *out_y, int32_t *row_status);
+/* GEOMETRY -> POLYGON_2D in DuckDB list layout (the layout of sb_refine_point_polygon / sb_join_points_polygons):
+ * replaces PolygonCasts::FromGeometryCast, spatial_functions_cast.cpp:473-537. poly_ring_off has n + 1 entries,
+ * ring_vert_off ring_capacity + 1, vx / vy vertex_capacity. *n_rings / *n_verts always return the sizes needed;
+ * SB_ERR_CAPACITY when a capacity is too small (poly_ring_off is complete even then: call once with capacities 0 to
+ * size the outputs). Non-POLYGON rows: status SB_ROW_WRONG_TYPE, zero rings, SB_ERR_GEOMETRY at the end (the
+ * reference throws ConversionException). POLYGON EMPTY is a valid row with zero rings. */
+SB_API int sb_polygons_from_blobs(sb_context *ctx, sb_mem mem, const uint8_t *data, const uint64_t *offsets, uint64_t n,
+                                  uint64_t *poly_ring_off, uint64_t *ring_vert_off, double *vx, double *vy,
+                                  uint64_t ring_capacity, uint64_t vertex_capacity, uint64_t *n_rings,
+                                  uint64_t *n_verts, int32_t *row_status);
 
 /* ---- K2: Hilbert keys (ST_Hilbert, spatial_functions_scalar.cpp:5210-5396) -------------------------------- */
 /* ST_Hilbert(x DOUBLE, y DOUBLE, bounds BOX_2D): ExecuteLonlat :5250-5268. bounds = 4 doubles (host memory). */

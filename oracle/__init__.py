@@ -242,6 +242,32 @@ def extent_from_blobs(data, off):
     return box, valid, status
 
 
+def points_from_blobs(data, off):
+    """GEOMETRY -> POINT_2D cast: (x, y, status)."""
+    n = len(off) - 1
+    x = np.zeros(n, np.float64)
+    y = np.zeros(n, np.float64)
+    status = np.zeros(n, np.int32)
+    lib().orc_points_from_blobs(_p(data, u8p), _p(off, u64p), C.c_uint64(n), _p(x, f64p), _p(y, f64p), _p(status, i32p))
+    return x, y, status
+
+
+def polygons_from_blobs(data, off):
+    """GEOMETRY -> POLYGON_2D cast in list layout: (poly_ring_off, ring_vert_off, vx, vy, status)."""
+    n = len(off) - 1
+    poly_off = np.zeros(n + 1, np.uint64)
+    status = np.zeros(n, np.int32)
+    nr, nv = C.c_uint64(0), C.c_uint64(0)
+    lib().orc_polygons_from_blobs(_p(data, u8p), _p(off, u64p), C.c_uint64(n), _p(poly_off, u64p), None, None, None,
+                                  C.byref(nr), C.byref(nv), _p(status, i32p))
+    ring_off = np.zeros(nr.value + 1, np.uint64)
+    vx = np.zeros(nv.value, np.float64)
+    vy = np.zeros(nv.value, np.float64)
+    lib().orc_polygons_from_blobs(_p(data, u8p), _p(off, u64p), C.c_uint64(n), _p(poly_off, u64p), _p(ring_off, u64p),
+                                  _p(vx, f64p), _p(vy, f64p), C.byref(nr), C.byref(nv), _p(status, i32p))
+    return poly_off, ring_off, vx, vy, status
+
+
 def hilbert_xy(x, y, bounds):
     n = len(x)
     out = np.empty(n, np.uint32)

@@ -313,6 +313,122 @@ ORC_API void orc_bbox_from_blobs(const uint8_t *data, const uint64_t *off, uint6
 }
 
 /* ------------------------------------------------------------------------------------------------
+ * GEOMETRY -> POINT_2D, PointCasts::FromGeometryCast (src/spatial/modules/main/spatial_functions_cast.cpp:247-270):
+ * Serde::Deserialize (geometry_serialization.cpp:290-329), type must be POINT ("Cannot cast non-point GEOMETRY"),
+ * must not be empty ("Cannot cast empty point GEOMETRY"), result = get_vertex_xy(0) (Z / M dropped).
+ * status: 0 ok, 1 empty point, -1 version, -2 malformed, -3 another geometry type; bad rows get NaN.
+ * ---------------------------------------------------------------------------------------------- */
+static int cast_header(const uint8_t *b, uint64_t len, uint32_t want, uint64_t *pos, uint32_t *vsize, uint32_t *count) {
+	if (len < 8) {
+		return -2;
+	}
+	const uint8_t flags = b[1];
+	if (flags & 0xC0) {
+		return -1;
+	}
+	if (b[0] != want) {
+		return b[0] <= 6 ? -3 : -2;
+	}
+	const uint32_t dims = 2 + ((flags & 1) ? 1 : 0) + ((flags & 2) ? 1 : 0);
+	*vsize = 8 * dims;
+	*pos = 8 + ((flags & 4) ? 8 * dims : 0); /* bbox: 2 floats per dimension */
+	if (*pos + 8 > len) {
+		return -2;
+	}
+	memcpy(count, b + *pos + 4, 4); /* [u32 type (ignored at the root)][u32 count] */
+	*pos += 8;
+	return 0;
+}
+
+ORC_API void orc_points_from_blobs(const uint8_t *data, const uint64_t *off, uint64_t n, double *x, double *y,
+                                   int32_t *status) {
+	for (uint64_t i = 0; i < n; i++) {
+		const uint8_t *b = data + off[i];
+		const uint64_t len = off[i + 1] - off[i];
+		uint64_t pos = 0;
+		uint32_t vsize = 0, count = 0;
+		int r = cast_header(b, len, 0, &pos, &vsize, &count);
+		x[i] = y[i] = NAN;
+		if (r == 0) {
+			if (count == 0) {
+				r = 1;
+			} else if (pos + vsize > len) {
+				r = -2;
+			} else {
+				memcpy(&x[i], b + pos, 8);
+				memcpy(&y[i], b + pos + 8, 8);
+			}
+		}
+		if (status) {
+			status[i] = r;
+		}
+	}
+}
+
+/* GEOMETRY -> POLYGON_2D, PolygonCasts::FromGeometryCast (spatial_functions_cast.cpp:473-537): one list entry
+ * (total_rings, ring count) per row, one (total_coords, ring size) per ring, x / y of every vertex in ring order.
+ * Call with ring_off = NULL to size: returns rings in *n_rings, vertices in *n_verts. poly_off has n + 1 entries. */
+ORC_API void orc_polygons_from_blobs(const uint8_t *data, const uint64_t *off, uint64_t n, uint64_t *poly_off,
+                                     uint64_t *ring_off, double *vx, double *vy, uint64_t *n_rings, uint64_t *n_verts,
+                                     int32_t *status) {
+	uint64_t total_rings = 0, total_coords = 0;
+	for (uint64_t i = 0; i < n; i++) {
+		const uint8_t *b = data + off[i];
+		const uint64_t len = off[i + 1] - off[i];
+		uint64_t pos = 0;
+		uint32_t vsize = 0, count = 0;
+		int r = cast_header(b, len, 2, &pos, &vsize, &count);
+		poly_off[i] = total_rings;
+		uint64_t vpos = 0, verts = 0;
+		if (r == 0) {
+			vpos = pos + 4ull * count + ((count & 1) ? 4 : 0);
+			if (vpos > len) {
+				r = -2;
+			}
+		}
+		if (r == 0) {
+			for (uint32_t k = 0; k < count; k++) {
+				uint32_t c;
+				memcpy(&c, b + pos + 4ull * k, 4);
+				verts += c;
+			}
+			if (vpos + verts * vsize > len) {
+				r = -2;
+			}
+		}
+		if (status) {
+			status[i] = r;
+		}
+		if (r != 0) {
+			continue;
+		}
+		if (ring_off) {
+			const uint8_t *v = b + vpos;
+			for (uint32_t k = 0; k < count; k++) {
+				uint32_t c;
+				memcpy(&c, b + pos + 4ull * k, 4);
+				ring_off[total_rings + k] = total_coords;
+				for (uint32_t j = 0; j < c; j++) {
+					memcpy(&vx[total_coords + j], v, 8);
+					memcpy(&vy[total_coords + j], v + 8, 8);
+					v += vsize;
+				}
+				total_coords += c;
+			}
+		} else {
+			total_coords += verts;
+		}
+		total_rings += count;
+	}
+	poly_off[n] = total_rings;
+	if (ring_off) {
+		ring_off[total_rings] = total_coords;
+	}
+	*n_rings = total_rings;
+	*n_verts = total_coords;
+}
+
+/* ------------------------------------------------------------------------------------------------
  * ST_Extent(GEOMETRY): Serde::Deserialize (geometry_serialization.cpp:244-329) +
  * sgl::ops::try_get_extent_xy (src/sgl/sgl.hpp:1408-1486). Polygons: shell ring only.
  * std::min(a,b) = (b<a)?b:a ; std::max(a,b) = (a<b)?b:a  (NaN vertices never win).
