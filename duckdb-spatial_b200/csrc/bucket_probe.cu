@@ -1046,10 +1046,11 @@ __global__ void __launch_bounds__(1024, 1)
 	const unsigned tid = threadIdx.x;
 	const uint32_t n_units = (uint32_t)T->totals[2];
 	constexpr int ITEMS = CP_TILE2 / 1024;
-	// work items: halves of the probe units (a unit has at most BP_SLICE = 2 x CP_TILE2 records of one bucket)
-	for (uint32_t w = blockIdx.x; w < 2 * n_units; w += gridDim.x) {
-		const bp_unit u = units[w >> 1];
-		const uint32_t tbeg = u.pbeg + (w & 1u) * CP_TILE2;
+	// work items: tiles of the probe units (a unit has at most BP_SLICE = BP_UNIT_TILES x CP_TILE2 records of one bucket)
+	static_assert(BP_SLICE == BP_UNIT_TILES * CP_TILE2, "unit = whole tiles");
+	for (uint32_t w = blockIdx.x; w < BP_UNIT_TILES * n_units; w += gridDim.x) {
+		const bp_unit u = units[w / BP_UNIT_TILES];
+		const uint32_t tbeg = u.pbeg + (w % BP_UNIT_TILES) * CP_TILE2;
 		const uint32_t tend = min(u.pend, tbeg + CP_TILE2);
 		if (tbeg >= tend) {
 			continue; // uniform
@@ -1543,10 +1544,10 @@ int sbi_cell_partition(sb_context *ctx, const sb_flat *tree, const double *px, c
 		SB_LAUNCH_CHECK(ctx);
 		if (n_units) {
 			if (want_xy) {
-				k_cp_scatter2<true><<<sb_grid(2 * n_units, 1, 1), 1024, sizeof(cps2_smem<true>), ctx->stream>>>(
+				k_cp_scatter2<true><<<sb_grid(BP_UNIT_TILES * n_units, 1, 1), 1024, sizeof(cps2_smem<true>), ctx->stream>>>(
 				    d_tab, d_units, d_rec_a, d_fine, d_rec_b, d_src);
 			} else {
-				k_cp_scatter2<false><<<sb_grid(2 * n_units, 1, 1), 1024, sizeof(cps2_smem<false>), ctx->stream>>>(
+				k_cp_scatter2<false><<<sb_grid(BP_UNIT_TILES * n_units, 1, 1), 1024, sizeof(cps2_smem<false>), ctx->stream>>>(
 				    d_tab, d_units, d_rec_a, d_fine, d_rec_b, nullptr);
 			}
 			SB_LAUNCH_CHECK(ctx);

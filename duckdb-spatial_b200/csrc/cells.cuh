@@ -7,7 +7,10 @@
 #define BP_NB (BP_G * BP_G)      // 1024 buckets (+1 for points with NaN coordinates)
 #define BP_QBITS 20              // quantiser bits per axis
 #define BP_QMAX ((1 << BP_QBITS) - 1)
-#define BP_SLICE 32768u          // points per work unit
+#ifndef BP_SLICE
+#define BP_SLICE 65536u          // points per work unit
+#endif
+#define BP_UNIT_TILES (BP_SLICE / 16384u) // 16384-record tiles per unit (pass 2 of the cell partition, k_pip_gather)
 
 struct bp_grid {
 	double minx, miny, sx, sy; // Q(v) = clamp(floor((v - min) * s), 0, BP_QMAX)

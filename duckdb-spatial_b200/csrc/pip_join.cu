@@ -134,9 +134,9 @@ __global__ void __launch_bounds__(512) k_pip_gather(const bp_tables *__restrict_
                                                     const uint32_t *__restrict__ src, const double2 *__restrict__ xy_in,
                                                     double2 *__restrict__ xy) {
 	const uint32_t n_units = (uint32_t)T->totals[2];
-	for (uint32_t w = blockIdx.x; w < 2 * n_units; w += gridDim.x) {
-		const bp_unit unit = units[w >> 1];
-		const uint32_t beg = unit.pbeg + (w & 1u) * 16384u, end = min(unit.pend, beg + 16384u);
+	for (uint32_t w = blockIdx.x; w < BP_UNIT_TILES * n_units; w += gridDim.x) {
+		const bp_unit unit = units[w / BP_UNIT_TILES];
+		const uint32_t beg = unit.pbeg + (w % BP_UNIT_TILES) * 16384u, end = min(unit.pend, beg + 16384u);
 		for (uint32_t i = beg + threadIdx.x; i < end; i += blockDim.x) {
 			xy[i] = xy_in[src[i]];
 		}
@@ -474,7 +474,7 @@ int sbi_join_points_polygons(sb_context *ctx, const double *px, const double *py
 	SB_SMEM_OPTIN(ctx, k_pip_join, sizeof(pip_smem));
 	{
 		sb_prof_scope ps(ctx, "pip_gather");
-		k_pip_gather<<<sb_grid(2 * part.n_units, 1, 4), 512, 0, ctx->stream>>>(
+		k_pip_gather<<<sb_grid(BP_UNIT_TILES * part.n_units, 1, 4), 512, 0, ctx->stream>>>(
 		    static_cast<const bp_tables *>(part.tables), static_cast<const bp_unit *>(part.units), part.src,
 		    static_cast<const double2 *>(part.xy_bucketed), d_xy);
 		SB_LAUNCH_CHECK(ctx);
