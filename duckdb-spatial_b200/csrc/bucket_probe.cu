@@ -1258,10 +1258,10 @@ __device__ __forceinline__ void cpp_batch(cpp_smem<MODE> &S, const cpp_args &A, 
 				base = atomicAdd(A.counter, (unsigned long long)cnt);
 			}
 			base = __shfl_sync(0xFFFFFFFFu, base, 0);
+			// a batch that does not fit is counted but not written: on SB_ERR_CAPACITY the caller gets the needed size and
+			// unspecified array contents (a guarded write variant per round count was a third of the kernel's code)
 			if (base + cnt <= A.capacity) {
 				cpp_write<false, NR>(id, mk, defm, ep, ne, npts, S.cidx, base, A.capacity, A.out_probe, A.out_build);
-			} else {
-				cpp_write<true, NR>(id, mk, defm, ep, ne, npts, S.cidx, base, A.capacity, A.out_probe, A.out_build);
 			}
 		}
 	}

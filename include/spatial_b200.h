@@ -34,7 +34,8 @@ typedef enum {
 	SB_OK = 0,
 	SB_ERR_CUDA = -1,     /* CUDA runtime error (message has the CUDA string) */
 	SB_ERR_ARG = -2,      /* invalid argument */
-	SB_ERR_CAPACITY = -3, /* caller-provided output too small; *count holds the needed size */
+	SB_ERR_CAPACITY = -3, /* caller-provided output too small; *count holds the needed size, the output arrays'
+	                         contents are unspecified */
 	SB_ERR_GEOMETRY = -4, /* a blob failed validation (per-row status array has details) */
 	SB_ERR_EMPTY = -5     /* operation not defined on an empty geometry (ST_Hilbert(geom, bounds)) */
 } sb_status;
