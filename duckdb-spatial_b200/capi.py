@@ -29,6 +29,7 @@ SIGNATURES = {
     "sb_bbox_from_box2d": (i32, [vp, i32, vp, vp, vp, vp, u64, vp]),
     "sb_bbox_from_blobs": (i32, [vp, i32, vp, vp, u64, vp, vp, vp]),
     "sb_extent_from_blobs": (i32, [vp, i32, vp, vp, u64, vp, vp, vp]),
+    "sb_extent_from_wkb": (i32, [vp, i32, vp, vp, u64, vp, vp, vp]),
     "sb_points_from_blobs": (i32, [vp, i32, vp, vp, u64, vp, vp, vp]),
     "sb_polygons_from_blobs": (i32, [vp, i32, vp, vp, u64, vp, vp, vp, vp, u64, u64, vp, vp, vp]),
     "sb_hilbert_xy": (i32, [vp, i32, vp, vp, u64, vp, vp]),

@@ -185,6 +185,38 @@ extern "C" int sb_points_from_blobs(sb_context *ctx, sb_mem mem, const uint8_t *
 	return s != SB_OK ? s : verdict;
 }
 
+extern "C" int sb_extent_from_wkb(sb_context *ctx, sb_mem mem, const uint8_t *data, const uint64_t *offsets, uint64_t n,
+                                  double *out_box4, uint8_t *out_valid, int32_t *row_status) {
+	SB_BEGIN(ctx);
+	if (n == 0) {
+		return SB_OK;
+	}
+	SB_ARG(out_box4 != nullptr && out_valid != nullptr, "out_box4/out_valid");
+	const uint8_t *d_data;
+	const uint64_t *d_off;
+	SB_TRY(blob_inputs(ctx, mem, data, offsets, n, &d_data, &d_off));
+	double *d_box = nullptr;
+	uint8_t *d_valid = nullptr;
+	int32_t *d_status = nullptr;
+	uint64_t *d_bad = nullptr;
+	SB_TRY(ctx->scratch_t(1, &d_bad));
+	SB_TRY(sbi_zero(ctx, d_bad, sizeof(uint64_t)));
+	SB_TRY(sb_out_buffer(ctx, mem, out_box4, 4 * n, &d_box));
+	SB_TRY(sb_out_buffer(ctx, mem, out_valid, n, &d_valid));
+	SB_TRY(sb_out_buffer(ctx, mem, row_status, n, &d_status));
+	SB_TRY(sbi_wkb_extent(ctx, d_data, d_off, n, d_box, d_valid, d_status, reinterpret_cast<int *>(d_bad)));
+	SB_TRY(sb_to_host(ctx, mem, out_box4, d_box, 4 * n));
+	SB_TRY(sb_to_host(ctx, mem, out_valid, d_valid, n));
+	SB_TRY(sb_to_host(ctx, mem, row_status, d_status, n));
+	uint64_t bad = 0;
+	SB_TRY(sbi_read_words(ctx, d_bad, 1, &bad));
+	if ((uint32_t)bad) {
+		sb_set_error("Failed to parse WKB: see row_status");
+		return SB_ERR_GEOMETRY;
+	}
+	return finish(ctx, mem);
+}
+
 extern "C" int sb_polygons_from_blobs(sb_context *ctx, sb_mem mem, const uint8_t *data, const uint64_t *offsets,
                                       uint64_t n, uint64_t *poly_ring_off, uint64_t *ring_vert_off, double *vx, double *vy,
                                       uint64_t ring_capacity, uint64_t vertex_capacity, uint64_t *n_rings,

@@ -153,6 +153,8 @@ struct sb_poly_transcode {
 };
 int sbi_points_from_blobs(sb_context *ctx, const uint8_t *data, const uint64_t *off, uint64_t n, double *ox, double *oy,
                           int32_t *status, int *any_bad);
+int sbi_wkb_extent(sb_context *ctx, const uint8_t *data, const uint64_t *off, uint64_t n, double *out_box, uint8_t *valid,
+                   int32_t *status, int *any_bad);
 int sbi_polygons_count(sb_context *ctx, const uint8_t *data, const uint64_t *off, uint64_t n, sb_poly_transcode *T,
                        int32_t *status, int *any_bad, uint64_t *poly_ring_off, uint64_t *n_rings, uint64_t *n_verts);
 int sbi_polygons_fill(sb_context *ctx, const uint8_t *data, const uint64_t *off, uint64_t n, const sb_poly_transcode *T,

@@ -337,3 +337,194 @@ int sbi_polygons_fill(sb_context *ctx, const uint8_t *data, const uint64_t *off,
 	SB_LAUNCH_CHECK(ctx);
 	return SB_OK;
 }
+
+// ---- ST_Extent(WKB_BLOB) ------------------------------------------------------------------------------------------
+// ST_Extent::ExecuteWKB (spatial_functions_scalar.cpp:2576-2629) = sgl::ops::wkb_reader_try_parse_stats
+// (src/sgl/sgl.cpp:903-1058, nan_as_empty, stack of 128): one warp per blob, the part headers are walked by all lanes
+// in lockstep (uniform loads), vertex runs are strided over the lanes, then a warp min / max reduction. Both byte
+// orders, ISO (type + 1000 / 2000 / 3000) and EWKB (0x80000000 / 0x40000000 / 0x20000000 + SRID) flags, every ring
+// of a polygon counts. min / max keep the accumulator when the vertex is NaN (std::min / std::max argument order).
+#define WKB_STACK 128
+#define WKB_WARPS 8
+
+__device__ __forceinline__ uint32_t wkb_u32(const uint8_t *p, bool le) {
+	const uint32_t v = ld_u32(p);
+	return le ? v : __byte_perm(v, 0, 0x0123);
+}
+__device__ __forceinline__ double wkb_f64(const uint8_t *p, bool le) {
+	if (le) {
+		return ld_f64(p);
+	}
+	const unsigned long long hi = __byte_perm(ld_u32(p), 0, 0x0123), lo = __byte_perm(ld_u32(p + 4), 0, 0x0123);
+	return __longlong_as_double((long long)(lo | (hi << 32)));
+}
+
+struct wkb_acc {
+	double x0, y0, x1, y1;
+};
+__device__ __forceinline__ void wkb_add(wkb_acc &a, double X, double Y) {
+	a.x0 = X < a.x0 ? X : a.x0;
+	a.y0 = Y < a.y0 ? Y : a.y0;
+	a.x1 = a.x1 < X ? X : a.x1;
+	a.y1 = a.y1 < Y ? Y : a.y1;
+}
+
+// returns 1 / 0 / SB_ROW_* (all lanes agree); box valid in all lanes
+__device__ int wkb_extent_warp(const uint8_t *b, uint64_t len, uint32_t *stack, double4 &box) {
+	const unsigned lane = sb_lane();
+	wkb_acc a = {DBL_MAX, DBL_MAX, -DBL_MAX, -DBL_MAX};
+	uint64_t pos = 0;
+	uint32_t depth = 0, vc = 0; // the reference counts vertices in uint32_t
+	while (true) {
+		if (pos + 5 > len) {
+			return SB_ROW_TRUNCATED;
+		}
+		const bool le = b[pos] != 0;
+		const uint32_t id = wkb_u32(b + pos + 1, le);
+		pos += 5;
+		// static_cast<geometry_type>(uint8_t): the low byte of the remainder
+		const uint32_t type = ((id & 0xffffu) % 1000u) & 0xffu, fl = (id & 0xffffu) / 1000u;
+		const bool has_z = fl == 1 || fl == 3 || (id & 0x80000000u), has_m = fl == 2 || fl == 3 || (id & 0x40000000u);
+		if (id & 0x20000000u) {
+			if (pos + 4 > len) {
+				return SB_ROW_TRUNCATED;
+			}
+			pos += 4;
+		}
+		const uint32_t vsize = 16 + (has_z ? 8 : 0) + (has_m ? 8 : 0);
+		bool descend = false;
+		if (type == 1) {
+			if (pos + vsize > len) {
+				return SB_ROW_TRUNCATED;
+			}
+			const double x = wkb_f64(b + pos, le), y = wkb_f64(b + pos + 8, le);
+			bool all_nan = x != x && y != y;
+			for (uint32_t k = 16; k < vsize; k += 8) {
+				const double w = wkb_f64(b + pos + k, le);
+				all_nan = all_nan && w != w;
+			}
+			pos += vsize;
+			if (!all_nan) {
+				if (lane == 0) {
+					wkb_add(a, x, y);
+				}
+				vc++;
+			}
+		} else if (type == 2 || type == 3) {
+			uint32_t rings = 1;
+			if (type == 3) {
+				if (pos + 4 > len) {
+					return SB_ROW_TRUNCATED;
+				}
+				rings = wkb_u32(b + pos, le);
+				pos += 4;
+			}
+			for (uint32_t r = 0; r < rings; r++) {
+				if (pos + 4 > len) {
+					return SB_ROW_TRUNCATED;
+				}
+				const uint32_t np = wkb_u32(b + pos, le);
+				pos += 4;
+				if (pos + (uint64_t)np * vsize > len) {
+					return SB_ROW_TRUNCATED;
+				}
+				for (uint32_t i = lane; i < np; i += 32) {
+					const uint8_t *v = b + pos + (uint64_t)i * vsize;
+					wkb_add(a, wkb_f64(v, le), wkb_f64(v + 8, le));
+				}
+				pos += (uint64_t)np * vsize;
+				vc += np;
+			}
+		} else if (type >= 4 && type <= 7) {
+			if (depth >= WKB_STACK) {
+				return SB_ROW_RECURSION;
+			}
+			if (pos + 4 > len) {
+				return SB_ROW_TRUNCATED;
+			}
+			const uint32_t count = wkb_u32(b + pos, le);
+			pos += 4;
+			if (count != 0) {
+				__syncwarp();
+				if (lane == 0) {
+					stack[depth] = count;
+				}
+				__syncwarp();
+				depth++;
+				descend = true;
+			}
+		} else {
+			return SB_ROW_WRONG_TYPE;
+		}
+		if (descend) {
+			continue;
+		}
+		bool done = false;
+		while (true) {
+			if (depth == 0) {
+				done = true;
+				break;
+			}
+			__syncwarp();
+			const uint32_t left = stack[depth - 1] - 1;
+			__syncwarp();
+			if (lane == 0) {
+				stack[depth - 1] = left;
+			}
+			__syncwarp();
+			if (left > 0) {
+				break;
+			}
+			depth--;
+		}
+		if (done) {
+			break;
+		}
+	}
+#pragma unroll
+	for (int s = 16; s > 0; s >>= 1) {
+		const double ox0 = __shfl_xor_sync(0xFFFFFFFFu, a.x0, s), oy0 = __shfl_xor_sync(0xFFFFFFFFu, a.y0, s);
+		const double ox1 = __shfl_xor_sync(0xFFFFFFFFu, a.x1, s), oy1 = __shfl_xor_sync(0xFFFFFFFFu, a.y1, s);
+		a.x0 = ox0 < a.x0 ? ox0 : a.x0;
+		a.y0 = oy0 < a.y0 ? oy0 : a.y0;
+		a.x1 = a.x1 < ox1 ? ox1 : a.x1;
+		a.y1 = a.y1 < oy1 ? oy1 : a.y1;
+	}
+	box = make_double4(a.x0, a.y0, a.x1, a.y1);
+	return vc ? 1 : 0;
+}
+
+__global__ void __launch_bounds__(32 * WKB_WARPS) k_wkb_extent(const uint8_t *__restrict__ data,
+                                                               const uint64_t *__restrict__ off, uint64_t n,
+                                                               double4 *__restrict__ out_box, uint8_t *__restrict__ valid,
+                                                               int32_t *__restrict__ status, int *__restrict__ any_bad) {
+	__shared__ uint32_t s_stack[WKB_WARPS][WKB_STACK];
+	const uint64_t warps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+	for (uint64_t i = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < n; i += warps) {
+		const uint64_t o = off[i];
+		double4 box = make_double4(0, 0, 0, 0);
+		const int r = wkb_extent_warp(data + o, off[i + 1] - o, s_stack[threadIdx.x >> 5], box);
+		if (sb_lane() == 0) {
+			out_box[i] = r == 1 ? box : make_double4(0, 0, 0, 0);
+			valid[i] = r == 1;
+			if (status) {
+				status[i] = r < 0 ? r : 0;
+			}
+			if (r < 0) {
+				atomicMax(any_bad, 2);
+			}
+		}
+	}
+}
+
+int sbi_wkb_extent(sb_context *ctx, const uint8_t *data, const uint64_t *off, uint64_t n, double *out_box, uint8_t *valid,
+                   int32_t *status, int *any_bad) {
+	if (n == 0) {
+		return SB_OK;
+	}
+	sb_prof_scope ps(ctx, "extent");
+	k_wkb_extent<<<sb_grid(n * 32, 32 * WKB_WARPS, 16), 32 * WKB_WARPS, 0, ctx->stream>>>(
+	    data, off, n, reinterpret_cast<double4 *>(out_box), valid, status, any_bad);
+	SB_LAUNCH_CHECK(ctx);
+	return SB_OK;
+}

@@ -147,6 +147,19 @@ class Context:
         capi.check(rc)
         return box, valid
 
+    def st_extent_wkb(self, data, offsets, want_status=False):
+        """ST_Extent(WKB_BLOB) -> (BOX_2D [n,4], valid [n])"""
+        n = len(offsets) - 1
+        box = self._empty(data, (n, 4), np.float64)
+        valid = self._empty(data, (n,), np.uint8)
+        status = self._empty(data, (n,), np.int32)
+        rc = self.L.sb_extent_from_wkb(self.h, self._mem(data, offsets), _ptr(data), _ptr(offsets), n, _ptr(box),
+                                       _ptr(valid), _ptr(status))
+        if want_status:
+            return box, valid, status, rc
+        capi.check(rc)
+        return box, valid
+
     # -- GEOMETRY -> coordinate columns --------------------------------------------------------------------
     def points_from_blobs(self, data, offsets, want_status=False):
         """GEOMETRY -> POINT_2D cast (PointCasts::FromGeometryCast): (x, y); raises where the reference throws."""

@@ -45,7 +45,9 @@ typedef enum {
 #define SB_ROW_BAD_VERSION (-1) /* geometry_properties.hpp:28-36 CheckVersion throws NotImplementedException */
 #define SB_ROW_TRUNCATED (-2)   /* Cursor bounds check, util/cursor.hpp throws SerializationException */
 #define SB_ROW_EMPTY 1          /* ST_Hilbert(geom,bounds) on empty input: InvalidInputException */
-#define SB_ROW_WRONG_TYPE (-3)  /* GEOMETRY -> POINT_2D / POLYGON_2D cast of another geometry type: ConversionException */
+#define SB_ROW_WRONG_TYPE (-3)  /* GEOMETRY -> POINT_2D / POLYGON_2D cast of another geometry type: ConversionException;
+                                   WKB: unsupported geometry type id (SGL_WKB_READER_UNSUPPORTED_TYPE) */
+#define SB_ROW_RECURSION (-4)   /* WKB nested deeper than 128 collections (SGL_WKB_READER_RECURSION_LIMIT) */
 
 typedef struct sb_context sb_context;
 typedef struct sb_rtree sb_rtree; /* persistent RTREE index, STR bulk-loaded (CREATE INDEX ... USING RTREE) */
@@ -92,6 +94,14 @@ SB_API int sb_bbox_from_blobs(sb_context *ctx, sb_mem mem, const uint8_t *data, 
  * Serde::Deserialize (geometry_serialization.cpp:290-329) + sgl::ops::try_get_extent_xy (sgl.hpp:1408-1486) */
 SB_API int sb_extent_from_blobs(sb_context *ctx, sb_mem mem, const uint8_t *data, const uint64_t *offsets, uint64_t n,
                                 double *out_box4, uint8_t *out_valid, int32_t *row_status);
+
+/* ST_Extent(WKB_BLOB): replaces ST_Extent::ExecuteWKB, spatial_functions_scalar.cpp:2576-2629 =
+ * sgl::ops::wkb_reader_try_parse_stats (src/sgl/sgl.cpp:903-1058; nan_as_empty, 128 nesting levels). Both byte orders,
+ * ISO and EWKB Z / M / SRID flags; all rings of a polygon count. valid[i] = 0 -> SQL NULL (no vertices). Rows the
+ * reference fails to parse (InvalidInputException "Failed to parse WKB") get a negative row_status and the call
+ * returns SB_ERR_GEOMETRY. */
+SB_API int sb_extent_from_wkb(sb_context *ctx, sb_mem mem, const uint8_t *data, const uint64_t *offsets, uint64_t n,
+                              double *out_box4, uint8_t *out_valid, int32_t *row_status);
 
 /* ---- GEOMETRY column -> coordinate columns (what the join entry points take) ------------------------------
  * GEOMETRY -> POINT_2D: replaces PointCasts::FromGeometryCast, spatial_functions_cast.cpp:247-270 (Serde::Deserialize

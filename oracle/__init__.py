@@ -242,6 +242,28 @@ def extent_from_blobs(data, off):
     return box, valid, status
 
 
+def extent_from_wkb(data, off):
+    """ST_Extent(WKB_BLOB): (box [n,4] f64, valid, status)."""
+    n = len(off) - 1
+    box = np.zeros((n, 4), np.float64)
+    valid = np.zeros(n, np.uint8)
+    status = np.zeros(n, np.int32)
+    lib().orc_extent_from_wkb(_p(data, u8p), _p(off, u64p), C.c_uint64(n), _p(box, f64p), _p(valid, u8p), _p(status, i32p))
+    return box, valid, status
+
+
+def ref_wkb_extent(blob):
+    """The reference's own wkb_reader_try_parse_stats on one blob (libref.so): (rc, box4, vertex_count)."""
+    R = ref()
+    n = len(blob)
+    b = np.frombuffer(bytes(blob) + b"\0", np.uint8)  # never a NULL buffer (the reader asserts on it)
+    box = np.zeros(4, np.float64)
+    vc = C.c_uint64(0)
+    R.ref_wkb_extent.restype = C.c_int
+    rc = R.ref_wkb_extent(_p(b, u8p), C.c_uint64(n), _p(box, f64p), C.byref(vc))
+    return rc, box, vc.value
+
+
 def points_from_blobs(data, off):
     """GEOMETRY -> POINT_2D cast: (x, y, status)."""
     n = len(off) - 1

@@ -313,6 +313,161 @@ ORC_API void orc_bbox_from_blobs(const uint8_t *data, const uint64_t *off, uint6
 }
 
 /* ------------------------------------------------------------------------------------------------
+ * ST_Extent(WKB_BLOB): ST_Extent::ExecuteWKB (spatial_functions_scalar.cpp:2576-2629) =
+ * sgl::ops::wkb_reader_try_parse_stats (src/sgl/sgl.cpp:903-1058) with nan_as_empty, stack of 128.
+ * Per part: [u8 byte order][u32 type], type = (id & 0xffff) % 1000, ISO Z/M = (id & 0xffff) / 1000 in {1,2,3},
+ * EWKB Z = 0x80000000, M = 0x40000000, SRID = 0x20000000 (+ u32 skipped). Every ring of a polygon counts
+ * (unlike ST_Extent(GEOMETRY), which looks at the shell only). std::min / std::max: NaN never wins.
+ * returns 1 = box, 0 = NULL (no vertices), -1 unsupported type, -2 out of bounds, -3 recursion limit
+ * (the reference throws InvalidInputException "Failed to parse WKB" for the negative ones).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+	const uint8_t *p, *end;
+	int le, err;
+} wkb_cur;
+
+static uint32_t wkb_u32(wkb_cur *c) {
+	if (c->end - c->p < 4) {
+		c->err = -2;
+		return 0;
+	}
+	uint32_t v = c->le ? ((uint32_t)c->p[0] | ((uint32_t)c->p[1] << 8) | ((uint32_t)c->p[2] << 16) | ((uint32_t)c->p[3] << 24))
+	                   : ((uint32_t)c->p[3] | ((uint32_t)c->p[2] << 8) | ((uint32_t)c->p[1] << 16) | ((uint32_t)c->p[0] << 24));
+	c->p += 4;
+	return v;
+}
+
+static double wkb_f64(wkb_cur *c) {
+	if (c->end - c->p < 8) {
+		c->err = -2;
+		return 0;
+	}
+	uint64_t v = 0;
+	for (int i = 0; i < 8; i++) {
+		v |= (uint64_t)c->p[c->le ? i : 7 - i] << (8 * i);
+	}
+	c->p += 8;
+	double d;
+	memcpy(&d, &v, 8);
+	return d;
+}
+
+static void wkb_acc(double *b, double x, double y) {
+	b[0] = x < b[0] ? x : b[0];
+	b[1] = y < b[1] ? y : b[1];
+	b[2] = b[2] < x ? x : b[2];
+	b[3] = b[3] < y ? y : b[3];
+}
+
+ORC_API int orc_wkb_extent(const uint8_t *blob, uint64_t len, double *box4, uint64_t *vertex_count) {
+	wkb_cur c = {blob, blob + len, 0, 0};
+	uint32_t stack[128];
+	uint32_t depth = 0, vc = 0; /* the reference counts in uint32_t */
+	double b[4] = {DBL_MAX, DBL_MAX, -DBL_MAX, -DBL_MAX};
+	for (;;) {
+		if (c.end - c.p < 1) {
+			return -2;
+		}
+		c.le = *c.p++ != 0;
+		const uint32_t id = wkb_u32(&c);
+		if (c.err) {
+			return c.err;
+		}
+		/* static_cast<geometry_type>(uint8_t): the reference keeps the low byte of the remainder */
+		const uint32_t type = ((id & 0xffff) % 1000) & 0xff, fl = (id & 0xffff) / 1000;
+		const int has_z = fl == 1 || fl == 3 || (id & 0x80000000u), has_m = fl == 2 || fl == 3 || (id & 0x40000000u);
+		if (id & 0x20000000u) {
+			wkb_u32(&c);
+			if (c.err) {
+				return c.err;
+			}
+		}
+		const uint32_t extra = (has_z ? 1 : 0) + (has_m ? 1 : 0);
+		int descend = 0;
+		if (type == 1) {
+			const double x = wkb_f64(&c), y = c.err ? 0 : wkb_f64(&c);
+			int all_nan = isnan(x) && isnan(y);
+			for (uint32_t k = 0; k < extra && !c.err; k++) {
+				const double z = wkb_f64(&c);
+				all_nan = all_nan && isnan(z);
+			}
+			if (c.err) {
+				return c.err;
+			}
+			if (!all_nan) {
+				wkb_acc(b, x, y);
+				vc++;
+			}
+		} else if (type == 2 || type == 3) {
+			const uint32_t rings = type == 3 ? wkb_u32(&c) : 1;
+			if (c.err) {
+				return c.err;
+			}
+			for (uint32_t r = 0; r < rings; r++) {
+				const uint32_t np = wkb_u32(&c);
+				if (c.err) {
+					return c.err;
+				}
+				for (uint32_t i = 0; i < np; i++) {
+					const double x = wkb_f64(&c), y = c.err ? 0 : wkb_f64(&c);
+					if (c.err || (uint64_t)(c.end - c.p) < 8ull * extra) {
+						return -2;
+					}
+					c.p += 8 * extra;
+					wkb_acc(b, x, y);
+				}
+				vc += np;
+			}
+		} else if (type >= 4 && type <= 7) {
+			if (depth >= 128) {
+				return -3;
+			}
+			const uint32_t count = wkb_u32(&c);
+			if (c.err) {
+				return c.err;
+			}
+			if (count != 0) {
+				stack[depth++] = count;
+				descend = 1;
+			}
+		} else {
+			return -1;
+		}
+		if (descend) {
+			continue;
+		}
+		for (;;) {
+			if (depth == 0) {
+				*vertex_count = vc;
+				if (vc == 0) {
+					return 0;
+				}
+				memcpy(box4, b, 32);
+				return 1;
+			}
+			if (--stack[depth - 1] > 0) {
+				break;
+			}
+			depth--;
+		}
+	}
+}
+
+ORC_API void orc_extent_from_wkb(const uint8_t *data, const uint64_t *off, uint64_t n, double *box4, uint8_t *valid,
+                                 int32_t *status) {
+	for (uint64_t i = 0; i < n; i++) {
+		double b[4] = {0, 0, 0, 0};
+		uint64_t vc = 0;
+		const int r = orc_wkb_extent(data + off[i], off[i + 1] - off[i], b, &vc);
+		memcpy(box4 + 4 * i, b, 32);
+		valid[i] = r == 1;
+		if (status) {
+			status[i] = r < 0 ? r : 0;
+		}
+	}
+}
+
+/* ------------------------------------------------------------------------------------------------
  * GEOMETRY -> POINT_2D, PointCasts::FromGeometryCast (src/spatial/modules/main/spatial_functions_cast.cpp:247-270):
  * Serde::Deserialize (geometry_serialization.cpp:290-329), type must be POINT ("Cannot cast non-point GEOMETRY"),
  * must not be empty ("Cannot cast empty point GEOMETRY"), result = get_vertex_xy(0) (Z / M dropped).

@@ -20,6 +20,8 @@
 #include "spatial/geometry/geometry_type.hpp"
 #include "sgl/sgl.hpp"
 #include "pcg_random.hpp"
+// the reference's WKB reader (wkb_reader_try_parse_stats, the body of ST_Extent(WKB_BLOB)), compiled where it lies
+#include "/root/reference/src/sgl/sgl.cpp"
 
 #include <cmath>
 #include <cstdlib>
@@ -232,6 +234,33 @@ __attribute__((visibility("default"))) uint64_t ref_flat_join_count(void *h, con
 		*cand_out = cand;
 	}
 	return total;
+}
+
+// ST_Extent(WKB_BLOB): ST_Extent::ExecuteWKB, spatial_functions_scalar.cpp:2576-2629 (reader flags as set there).
+// returns 1 = box written, 0 = NULL (no vertices), negative = -(sgl error code) where the reference throws.
+__attribute__((visibility("default"))) int ref_wkb_extent(const uint8_t *buf, uint64_t len, double *box4, uint64_t *vertex_count) {
+	uint32_t stack[128] = {};
+	sgl::ops::wkb_reader reader = {};
+	reader.allow_mixed_zm = true;
+	reader.nan_as_empty = true;
+	reader.stack_buf = stack;
+	reader.stack_cap = 128;
+	reader.buf = reinterpret_cast<const char *>(buf);
+	reader.end = reader.buf + len;
+	sgl::box_xy bbox = {};
+	size_t vc = 0;
+	if (!sgl::ops::wkb_reader_try_parse_stats(&reader, &bbox, &vc)) {
+		return -(int)reader.error;
+	}
+	*vertex_count = vc;
+	if (vc == 0) {
+		return 0;
+	}
+	box4[0] = bbox.min.x;
+	box4[1] = bbox.min.y;
+	box4[2] = bbox.max.x;
+	box4[3] = bbox.max.y;
+	return 1;
 }
 
 } // extern "C"

@@ -87,3 +87,37 @@ EXTENT_CASES = [
     (("GEOMETRYCOLLECTION", [("POINT", [(0, 0)]), ("LINESTRING", [(0, 0), (1, 1)])]), (0, 0, 1, 1)),
     (("GEOMETRYCOLLECTION", [("GEOMETRYCOLLECTION", [("POINT", [(0, 0)]), ("LINESTRING", [(0, 0), (1, 1)])])]), (0, 0, 1, 1)),
 ]
+
+
+# ---- WKB (ISO and EWKB flavours, both byte orders) for ST_Extent(WKB_BLOB) ---------------------------------------
+def wkb(g, le=True, z=False, m=False, ewkb=False, srid=None, extra=7.5):
+    """WKB bytes of a nested-tuple geometry. ISO: type + 1000 (Z) / 2000 (M) / 3000 (ZM); EWKB: 0x80000000 / 0x40000000
+    flags, optional SRID (0x20000000) on this part. Z / M ordinates are filled with `extra`."""
+    t, body = g
+    e = "<" if le else ">"
+    code = TYPES.index(t) + 1
+    if ewkb:
+        code |= (0x80000000 if z else 0) | (0x40000000 if m else 0) | (0x20000000 if srid is not None else 0)
+    else:
+        code += 1000 * ((1 if z else 0) + (2 if m else 0))
+    out = struct.pack("B", 1 if le else 0) + struct.pack(e + "I", code)
+    if ewkb and srid is not None:
+        out += struct.pack(e + "I", srid)
+    nd = (1 if z else 0) + (1 if m else 0)
+
+    def vert(v):
+        return struct.pack(e + "dd", float(v[0]), float(v[1])) + struct.pack(e + "d", extra) * nd
+
+    if t == "POINT":
+        out += vert(body[0]) if body else struct.pack(e + "d", float("nan")) * (2 + nd)
+    elif t == "LINESTRING":
+        out += struct.pack(e + "I", len(body)) + b"".join(vert(v) for v in body)
+    elif t == "POLYGON":
+        out += struct.pack(e + "I", len(body))
+        for ring in body:
+            out += struct.pack(e + "I", len(ring)) + b"".join(vert(v) for v in ring)
+    else:
+        out += struct.pack(e + "I", len(body))
+        for part in body:
+            out += wkb(part, le=le, z=z, m=m, ewkb=ewkb, extra=extra)
+    return out

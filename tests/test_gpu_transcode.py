@@ -170,3 +170,36 @@ def test_blob_columns_feed_the_polygon_join(ctx, O):
     sb_ = np.lexsort((np.asarray(b[1]), np.asarray(b[0])))
     assert len(a[0]) == len(b[0]) > 0
     assert (np.asarray(a[0])[sa] == np.asarray(b[0])[sb_]).all() and (np.asarray(a[1])[sa] == np.asarray(b[1])[sb_]).all()
+
+
+def test_extent_from_wkb(ctx, O, sb):
+    # ST_Extent(WKB_BLOB): every flavour and every rejected input of tests/test_wkb_oracle.py, host and device memory
+    from test_wkb_oracle import wkb_cases
+    rng = np.random.default_rng(8)
+    blobs = wkb_cases(rng, 1500)
+    data, off = O.concat_blobs(blobs)
+    ebox, evalid, estatus = O.extent_from_wkb(data, off)
+    box, valid, status, rc = ctx.st_extent_wkb(data, off, want_status=True)
+    assert rc == sb.capi.ERR_GEOMETRY
+    # oracle / reference codes are -(SGL_WKB_READER_ERROR): 1 unsupported type, 2 out of bounds, 3 recursion limit;
+    # the library reports them as SB_ROW_WRONG_TYPE (-3), SB_ROW_TRUNCATED (-2), SB_ROW_RECURSION (-4)
+    to_row = {0: 0, -1: -3, -2: -2, -3: -4}
+    assert (valid == evalid).all() and (status == np.array([to_row[int(s)] for s in estatus])).all()
+    assert {-2, -3, -4} <= set(status.tolist())
+    assert (bits(box)[evalid == 1] == bits(ebox)[evalid == 1]).all()
+    good = estatus == 0
+    gd, go = O.concat_blobs([b for b, g in zip(blobs, good) if g])
+    import torch
+    dbox, dvalid = ctx.st_extent_wkb(torch.from_numpy(gd).cuda(), torch.from_numpy(go.view(np.int64)).cuda())
+    assert (dvalid.cpu().numpy() == evalid[good]).all()
+    v = evalid[good] == 1
+    assert (bits(dbox.cpu().numpy())[v] == bits(ebox[good])[v]).all()
+    # a long ring: the lanes stride over the vertices
+    t = np.linspace(0, 2 * np.pi, 100001)
+    ring = list(zip(1e3 * np.cos(t), 1e3 * np.sin(t)))
+    for kw in ({}, {"le": False, "z": True}):
+        d1, o1 = O.concat_blobs([geomblob.wkb(("POLYGON", [ring]), **kw)])
+        b1, v1 = ctx.st_extent_wkb(d1, o1)
+        e1, ev1, _ = O.extent_from_wkb(d1, o1)
+        assert v1[0] == 1 and (bits(b1) == bits(e1)).all()
+    assert len(ctx.st_extent_wkb(np.zeros(0, np.uint8), np.zeros(1, np.uint64))[0]) == 0
