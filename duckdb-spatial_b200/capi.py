@@ -29,6 +29,12 @@ SIGNATURES = {
     "sb_bbox_from_box2d": (i32, [vp, i32, vp, vp, vp, vp, u64, vp]),
     "sb_bbox_from_blobs": (i32, [vp, i32, vp, vp, u64, vp, vp, vp]),
     "sb_extent_from_blobs": (i32, [vp, i32, vp, vp, u64, vp, vp, vp]),
+    "sb_join_op_create": (i32, [vp, i32, i32, vp, vp, vp, vp, u32, u64, vp]),
+    "sb_join_op_push": (i32, [vp, vp, vp, u64, vp]),
+    "sb_join_op_flush": (i32, [vp, vp, vp, u64, vp, vp, u64, vp]),
+    "sb_join_op_finish": (i32, [vp, vp, u64, vp]),
+    "sb_join_op_rows_pushed": (u64, [vp]),
+    "sb_join_op_destroy": (None, [vp]),
     "sb_extent_from_wkb": (i32, [vp, i32, vp, vp, u64, vp, vp, vp]),
     "sb_points_from_blobs": (i32, [vp, i32, vp, vp, u64, vp, vp, vp]),
     "sb_polygons_from_blobs": (i32, [vp, i32, vp, vp, u64, vp, vp, vp, vp, u64, u64, vp, vp, vp]),

@@ -371,6 +371,70 @@ class Context:
             return oa[: cnt.value], ob[: cnt.value], od[: cnt.value]
 
 
+class SpatialJoinOp:
+    """PhysicalSpatialJoin for a streaming probe side (sb_join_op): the build side is finalized at construction,
+    probe chunks (DuckDB: <= 2048 rows) are pushed and probed in device batches. Host (numpy) columns."""
+
+    TYPES = {"inner": 0, "left": 1, "right": 2, "full": 3, "outer": 3}
+
+    def __init__(self, ctx, bminx, bminy, bmaxx, bmaxy, predicate="intersects", join_type="inner", batch_rows=1 << 20):
+        self.ctx = ctx
+        self.jt = self.TYPES[join_type.lower()]
+        b = [np.ascontiguousarray(v, np.float64) for v in (bminx, bminy, bmaxx, bmaxy)]
+        self.n_build = len(b[0])
+        self.batch_rows = int(batch_rows)
+        pred = capi.PRED_INTERSECTS if predicate == "intersects" else capi.PRED_WITHIN
+        h = C.c_void_p()
+        capi.check(ctx.L.sb_join_op_create(ctx.h, pred, self.jt, *[_ptr(v) for v in b], self.n_build, self.batch_rows,
+                                           C.byref(h)))
+        self.h = h
+        self.pending = 0
+
+    def push(self, px, py):
+        """append one probe chunk; flushes first when the chunk would not fit. Returns the flush result or None."""
+        px, py = np.ascontiguousarray(px, np.float64), np.ascontiguousarray(py, np.float64)
+        out = None
+        if self.pending + len(px) > self.batch_rows:
+            out = self.flush()
+        pend = C.c_uint64(0)
+        capi.check(self.ctx.L.sb_join_op_push(self.h, _ptr(px), _ptr(py), len(px), C.byref(pend)))
+        self.pending = pend.value
+        return out
+
+    def flush(self, capacity=None):
+        """probe the pending rows: (pair_probe, pair_build, unmatched_probe_rows)"""
+        cap = int(capacity if capacity is not None else max(1024, 2 * self.pending))
+        lhs = np.empty(max(self.pending, 1), np.uint32)
+        while True:
+            op, ob = np.empty(cap, np.uint32), np.empty(cap, np.uint32)
+            n, nl = C.c_uint64(0), C.c_uint64(0)
+            rc = self.ctx.L.sb_join_op_flush(self.h, _ptr(op), _ptr(ob), cap, C.byref(n), _ptr(lhs), len(lhs), C.byref(nl))
+            if rc == capi.ERR_CAPACITY and n.value > cap:
+                cap = int(n.value)
+                continue
+            capi.check(rc)
+            self.pending = 0
+            return op[: n.value], ob[: n.value], lhs[: nl.value]
+
+    def finish(self):
+        """after the last flush: unmatched build rows (RIGHT / FULL), ascending"""
+        out = np.empty(max(self.n_build, 1), np.uint32)
+        n = C.c_uint64(0)
+        capi.check(self.ctx.L.sb_join_op_finish(self.h, _ptr(out), len(out), C.byref(n)))
+        return out[: n.value]
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.ctx.L.sb_join_op_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class RTreeIndex:
     """CREATE INDEX ... USING RTREE: STR bulk load on the GPU + batched index scans (sb_rtree)."""
 

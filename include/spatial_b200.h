@@ -266,6 +266,29 @@ SB_API int sb_join_mark_matched(sb_context *ctx, sb_mem mem, const uint32_t *pai
 SB_API int sb_join_unmatched_rows(sb_context *ctx, sb_mem mem, const uint8_t *matched, uint64_t n, uint32_t row_base,
                                   uint32_t *out_rows, uint64_t capacity, uint64_t *count);
 
+/* ---- probe-side operator glue: PhysicalSpatialJoin's life cycle for a STREAMING probe side ------------------
+ * DuckDB hands the operator one <= 2048-row probe chunk per ExecuteInternal call (spatial_join_physical.cpp:695-945);
+ * a GPU probe wants batches of >= 10^5 rows. The op buffers pushed chunks in pinned memory (CachingOperatorState-style)
+ * and probes them as one device batch. Host pointers throughout (DuckDB vectors). Probe row ids count pushed rows from
+ * 0 across batches; build row ids index the build columns (the row_array order of :117-129).
+ *   create : Sink / Finalize :431-601 -- BOX_2D build keys -> BOX_2DF -> FlatRTree(32), kept in HBM
+ *   push   : append a chunk (SB_ERR_CAPACITY when it does not fit the batch: flush first)
+ *   flush  : probe + exact predicate of the pending rows -> INNER pairs; LEFT / FULL also return the pending rows
+ *            without a match, ascending (EMIT_LHS :917-938: the caller emits them NULL-padded). SB_ERR_CAPACITY leaves
+ *            the batch pending with *n_pairs = the capacity to come back with.
+ *   finish : GetData :1022-1068 -- RIGHT / FULL: build rows no probe row matched, ascending. */
+typedef struct sb_join_op sb_join_op;
+typedef enum { SB_JOIN_INNER = 0, SB_JOIN_LEFT = 1, SB_JOIN_RIGHT = 2, SB_JOIN_FULL = 3 } sb_join_type;
+SB_API int sb_join_op_create(sb_context *ctx, sb_predicate pred, sb_join_type join_type, const double *bmin_x,
+                             const double *bmin_y, const double *bmax_x, const double *bmax_y, uint32_t n_build,
+                             uint64_t batch_rows, sb_join_op **out);
+SB_API int sb_join_op_push(sb_join_op *op, const double *px, const double *py, uint64_t n_rows, uint64_t *pending);
+SB_API int sb_join_op_flush(sb_join_op *op, uint32_t *out_probe, uint32_t *out_build, uint64_t pair_capacity,
+                            uint64_t *n_pairs, uint32_t *out_lhs_unmatched, uint64_t lhs_capacity, uint64_t *n_lhs);
+SB_API int sb_join_op_finish(sb_join_op *op, uint32_t *out_rhs_unmatched, uint64_t capacity, uint64_t *n_rhs);
+SB_API uint64_t sb_join_op_rows_pushed(const sb_join_op *op);
+SB_API void sb_join_op_destroy(sb_join_op *op);
+
 /* ---- harness utility: ST_GeneratePoints on the device ---------------------------------------------------------
  * restates ST_GeneratePoints (spatial_functions_table.cpp:82-99) on DuckDB's pcg32 RandomEngine with skip-ahead:
  * produces points [skip, skip+n) of the sequential stream of `seed`, bit-identical to the CPU generator. */
