@@ -238,6 +238,40 @@ __global__ void __launch_bounds__(256) k_bp_cand(const float4 *__restrict__ boxe
 	}
 }
 
+// exclusive scan over the CTA (WARPS x 32 threads, WARPS <= 32)
+template <int WARPS>
+__device__ __forceinline__ uint32_t bp_block_excl_scan(uint32_t v, uint32_t *s_warp, uint32_t *total) {
+	const unsigned lane = sb_lane(), warp = threadIdx.x >> 5;
+	uint32_t inc = v;
+#pragma unroll
+	for (int s = 1; s < 32; s <<= 1) {
+		const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, s);
+		if (lane >= (unsigned)s) {
+			inc += o;
+		}
+	}
+	__syncthreads();
+	if (lane == 31) {
+		s_warp[warp] = inc;
+	}
+	__syncthreads();
+	if (warp == 0) {
+		uint32_t w = lane < WARPS ? s_warp[lane] : 0u;
+#pragma unroll
+		for (int s = 1; s < 32; s <<= 1) {
+			const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, w, s);
+			if (lane >= (unsigned)s) {
+				w += o;
+			}
+		}
+		s_warp[lane] = w; // inclusive over warps
+	}
+	__syncthreads();
+	const uint32_t base = warp ? s_warp[warp - 1] : 0u;
+	*total = s_warp[31];
+	return base + inc - v;
+}
+
 __device__ __forceinline__ uint32_t bp_block_excl_scan_1024(uint32_t v, uint32_t *s_warp, uint32_t *total) {
 	// blockDim.x == 1024
 	const unsigned lane = sb_lane(), warp = threadIdx.x >> 5;
@@ -1108,6 +1142,10 @@ __global__ void __launch_bounds__(1024, 1)
 }
 
 #define CPP_RB 8 // rounds of 32 points per batch
+#ifndef CPP_THREADS
+#define CPP_THREADS 1024 // threads per probe CTA: 1024 (one CTA per SM) or 512 (two CTAs per SM, smaller directory)
+#endif
+#define CPP_EMAX (CPP_THREADS == 1024 ? BPP_EMAX : 24576)
 template <int MODE>
 struct cpp_smem {
 	uint2 qbox[BPP_CMAX];
@@ -1115,7 +1153,7 @@ struct cpp_smem {
 	uint32_t cpos[MODE == 1 ? BPP_CMAX : 1];
 	uint32_t cnt[BP_NB];
 	uint16_t off[BP_NB + 8];
-	uint16_t ent[BPP_EMAX];
+	uint16_t ent[CPP_EMAX];
 	uint16_t wide[BPP_WMAX];
 	uint32_t scan[32];
 	uint32_t unit, n_ent, n_wide, next_sc, sc_first, sc_last;
@@ -1268,7 +1306,7 @@ __device__ __forceinline__ void cpp_batch(cpp_smem<MODE> &S, const cpp_args &A, 
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(BPP_THREADS, 1)
+__global__ void __launch_bounds__(CPP_THREADS, 1024 / CPP_THREADS)
     k_cp_probe(const float4 *__restrict__ boxes, const uint32_t *__restrict__ idx,
                const double4 *__restrict__ build_box2d, int pred, const bp_grid *__restrict__ gp,
                bp_tables *__restrict__ T, const bp_unit *__restrict__ units, const uint32_t *__restrict__ cand_pos,
@@ -1331,9 +1369,11 @@ __global__ void __launch_bounds__(BPP_THREADS, 1)
 					S.n_ent = 0;
 					S.n_wide = 0;
 				}
-				S.cnt[tid] = 0; // BPP_THREADS == BP_NB
+				for (uint32_t sc = tid; sc < BP_NB; sc += CPP_THREADS) {
+					S.cnt[sc] = 0;
+				}
 				__syncthreads();
-				for (uint32_t j = tid; j < ntry; j += BPP_THREADS) {
+				for (uint32_t j = tid; j < ntry; j += CPP_THREADS) {
 					const uint32_t pos = cand_pos[c0 + j];
 					const uint32_t bi = __ldg(idx + pos);
 					int x0, y0, x1, y1;
@@ -1379,20 +1419,30 @@ __global__ void __launch_bounds__(BPP_THREADS, 1)
 					}
 				}
 				__syncthreads();
-				if (S.n_ent <= BPP_EMAX && S.n_wide <= BPP_WMAX) {
+				if (S.n_ent <= CPP_EMAX && S.n_wide <= BPP_WMAX) {
 					break;
 				}
 				ntry = (ntry + 1) / 2; // rare: the directory would overflow shared memory -> smaller chunk
 			}
 			// ---- (b) CSR offsets over the 1024 sub-cells (one per thread) ----
 			{
-				uint32_t total;
-				const uint32_t c = S.cnt[tid];
-				const uint32_t ex = bp_block_excl_scan_1024(c, S.scan, &total);
-				S.off[tid] = (uint16_t)ex;
-				S.cnt[tid] = ex;
-				if (tid == BPP_THREADS - 1) {
-					S.off[BP_NB] = (uint16_t)(ex + c);
+				// each thread owns PER consecutive sub-cells
+				constexpr int PER = BP_NB / CPP_THREADS;
+				uint32_t total, c[PER], sum = 0;
+#pragma unroll
+				for (int q = 0; q < PER; q++) {
+					c[q] = S.cnt[tid * PER + q];
+					sum += c[q];
+				}
+				uint32_t ex = bp_block_excl_scan<CPP_THREADS / 32>(sum, S.scan, &total);
+#pragma unroll
+				for (int q = 0; q < PER; q++) {
+					S.off[tid * PER + q] = (uint16_t)ex;
+					S.cnt[tid * PER + q] = ex;
+					ex += c[q];
+				}
+				if (tid == CPP_THREADS - 1) {
+					S.off[BP_NB] = (uint16_t)ex;
 				}
 				if (tid == 0) {
 					S.n_wide = 0;
@@ -1401,7 +1451,7 @@ __global__ void __launch_bounds__(BPP_THREADS, 1)
 			}
 			__syncthreads();
 			// ---- (c) fill the directory ----
-			for (uint32_t j = tid; j < ntry; j += BPP_THREADS) {
+			for (uint32_t j = tid; j < ntry; j += CPP_THREADS) {
 				const uint2 qb = S.qbox[j];
 				const uint32_t hi = qb.y & ~BPP_C;
 				const uint32_t lx0 = qb.x & 0xFFFFu, ly0 = qb.x >> 16, lx1 = hi & 0xFFFFu, ly1 = hi >> 16;
@@ -1604,14 +1654,15 @@ int sbi_flat_probe_cells(sb_context *ctx, const sb_flat *tree, const sb_probe_ar
 	SB_SMEM_OPTIN(ctx, k_cp_probe<1>, sizeof(cpp_smem<1>));
 	SB_SMEM_OPTIN(ctx, k_cp_probe<2>, sizeof(cpp_smem<2>));
 	if (n_units) {
-		const unsigned grid = (unsigned)(n_units < SB_NUM_SMS ? n_units : SB_NUM_SMS);
+		const uint64_t ctas = (uint64_t)SB_NUM_SMS * (1024 / CPP_THREADS);
+		const unsigned grid = (unsigned)(n_units < ctas ? n_units : ctas);
 		sb_prof_scope ps(ctx, "flat_probe");
 		if (mode == 1) {
-			k_cp_probe<1><<<grid, BPP_THREADS, sizeof(cpp_smem<1>), ctx->stream>>>(
+			k_cp_probe<1><<<grid, CPP_THREADS, sizeof(cpp_smem<1>), ctx->stream>>>(
 			    tree->boxes(), tree->idx(), nullptr, -1, d_grid, d_tab, d_units, d_cand, d_rec_b, d_cell_off, a.px, a.py,
 			    a.index_base, out_probe, out_build, capacity, d_counter);
 		} else {
-			k_cp_probe<2><<<grid, BPP_THREADS, sizeof(cpp_smem<2>), ctx->stream>>>(
+			k_cp_probe<2><<<grid, CPP_THREADS, sizeof(cpp_smem<2>), ctx->stream>>>(
 			    tree->boxes(), tree->idx(), a.build_box2d, a.pred, d_grid, d_tab, d_units, d_cand, d_rec_b, d_cell_off, a.px,
 			    a.py, a.index_base, out_probe, out_build, capacity, d_counter);
 		}
