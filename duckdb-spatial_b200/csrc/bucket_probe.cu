@@ -1141,16 +1141,26 @@ __global__ void __launch_bounds__(1024, 1)
 	}
 }
 
-#define CPP_RB 8 // rounds of 32 points per batch
+#ifndef CPP_RB
+#define CPP_RB 8 // rounds of 32 points per batch (8 or 4)
+#endif
 #ifndef CPP_THREADS
 #define CPP_THREADS 1024 // threads per probe CTA: 1024 (one CTA per SM) or 512 (two CTAs per SM, smaller directory)
 #endif
+#ifndef CPP_CTAS
+#define CPP_CTAS (1024 / CPP_THREADS) // resident probe CTAs per SM
+#endif
+#ifndef CPP_EMAX
 #define CPP_EMAX (CPP_THREADS == 1024 ? BPP_EMAX : 24576)
+#endif
+#ifndef CPP_CMAX
+#define CPP_CMAX BPP_CMAX
+#endif
 template <int MODE>
 struct cpp_smem {
-	uint2 qbox[BPP_CMAX];
-	uint32_t cidx[BPP_CMAX];
-	uint32_t cpos[MODE == 1 ? BPP_CMAX : 1];
+	uint2 qbox[CPP_CMAX];
+	uint32_t cidx[CPP_CMAX];
+	uint32_t cpos[MODE == 1 ? CPP_CMAX : 1];
 	uint32_t cnt[BP_NB];
 	uint16_t off[BP_NB + 8];
 	uint16_t ent[CPP_EMAX];
@@ -1306,7 +1316,7 @@ __device__ __forceinline__ void cpp_batch(cpp_smem<MODE> &S, const cpp_args &A, 
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(CPP_THREADS, 1024 / CPP_THREADS)
+__global__ void __launch_bounds__(CPP_THREADS, CPP_CTAS)
     k_cp_probe(const float4 *__restrict__ boxes, const uint32_t *__restrict__ idx,
                const double4 *__restrict__ build_box2d, int pred, const bp_grid *__restrict__ gp,
                bp_tables *__restrict__ T, const bp_unit *__restrict__ units, const uint32_t *__restrict__ cand_pos,
@@ -1362,7 +1372,7 @@ __global__ void __launch_bounds__(CPP_THREADS, 1024 / CPP_THREADS)
 		uint32_t c0 = cbeg;
 		while (c0 < cend) {
 			// ---- (a) stage a chunk of leaf entries as quantised in-bucket boxes, count directory entries ----
-			uint32_t ntry = min((uint32_t)BPP_CMAX, cend - c0);
+			uint32_t ntry = min((uint32_t)CPP_CMAX, cend - c0);
 			while (true) {
 				__syncthreads();
 				if (tid == 0) {
@@ -1501,11 +1511,15 @@ __global__ void __launch_bounds__(CPP_THREADS, 1024 / CPP_THREADS)
 					case 1: cpp_batch<MODE, 1>(S, A, wlane, pb, npts, lb, n0, n_wide, sx0, sy0); break;
 					case 2: cpp_batch<MODE, 2>(S, A, wlane, pb, npts, lb, n0, n_wide, sx0, sy0); break;
 					case 3: cpp_batch<MODE, 3>(S, A, wlane, pb, npts, lb, n0, n_wide, sx0, sy0); break;
+#if CPP_RB == 4
+					default: cpp_batch<MODE, 4>(S, A, wlane, pb, npts, lb, n0, n_wide, sx0, sy0); break;
+#else
 					case 4: cpp_batch<MODE, 4>(S, A, wlane, pb, npts, lb, n0, n_wide, sx0, sy0); break;
 					case 5: cpp_batch<MODE, 5>(S, A, wlane, pb, npts, lb, n0, n_wide, sx0, sy0); break;
 					case 6: cpp_batch<MODE, 6>(S, A, wlane, pb, npts, lb, n0, n_wide, sx0, sy0); break;
 					case 7: cpp_batch<MODE, 7>(S, A, wlane, pb, npts, lb, n0, n_wide, sx0, sy0); break;
 					default: cpp_batch<MODE, 8>(S, A, wlane, pb, npts, lb, n0, n_wide, sx0, sy0); break;
+#endif
 					}
 				}
 			}
@@ -1654,7 +1668,7 @@ int sbi_flat_probe_cells(sb_context *ctx, const sb_flat *tree, const sb_probe_ar
 	SB_SMEM_OPTIN(ctx, k_cp_probe<1>, sizeof(cpp_smem<1>));
 	SB_SMEM_OPTIN(ctx, k_cp_probe<2>, sizeof(cpp_smem<2>));
 	if (n_units) {
-		const uint64_t ctas = (uint64_t)SB_NUM_SMS * (1024 / CPP_THREADS);
+		const uint64_t ctas = (uint64_t)SB_NUM_SMS * CPP_CTAS;
 		const unsigned grid = (unsigned)(n_units < ctas ? n_units : ctas);
 		sb_prof_scope ps(ctx, "flat_probe");
 		if (mode == 1) {
