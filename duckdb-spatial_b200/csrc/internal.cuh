@@ -20,6 +20,9 @@ int sbi_hilbert_box2df(sb_context *ctx, const float *box4, uint64_t n, const flo
 // (vals need not be initialised).
 int sbi_radix_sort_u32(sb_context *ctx, uint32_t *keys, uint32_t *keys_alt, uint32_t *vals, uint32_t *vals_alt,
                        uint64_t n, int begin_bit, int end_bit, bool vals_iota, int *result_in_alt);
+int sbi_radix_sort_u32_segmented(sb_context *ctx, uint32_t *keys, uint32_t *keys_alt, uint32_t *vals, uint32_t *vals_alt,
+                                 uint64_t n, uint64_t seg_size, int begin_bit, int end_bit, bool vals_iota,
+                                 int *result_in_alt);
 int sbi_radix_sort_u64(sb_context *ctx, uint64_t *keys, uint64_t *keys_alt, uint32_t *vals, uint32_t *vals_alt,
                        uint64_t n, int begin_bit, int end_bit, bool vals_iota, int *result_in_alt);
 int sbi_iota_u32(sb_context *ctx, uint32_t *out, uint64_t n);

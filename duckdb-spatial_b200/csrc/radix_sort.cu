@@ -98,12 +98,79 @@ __global__ void __launch_bounds__(RS_BINS) k_radix_scan(uint32_t *__restrict__ h
 	h[threadIdx.x] = base + inc - v;
 }
 
+// segmented variant: one CTA per onesweep tile (tiles do not straddle segments), hist[(pass * nseg + seg) * 256 + digit]
+template <typename KeyT, int MAX_PASSES, int TILE>
+__global__ void __launch_bounds__(RS_THREADS) k_radix_hist_seg(const KeyT *__restrict__ keys, uint64_t n, int begin_bit,
+                                                               int end_bit, int passes, uint64_t seg_size,
+                                                               uint32_t tiles_per_seg, uint32_t nseg,
+                                                               uint32_t *__restrict__ hist) {
+	__shared__ uint32_t s_hist[MAX_PASSES * 4 * RS_BINS];
+	for (int i = threadIdx.x; i < passes * 4 * RS_BINS; i += RS_THREADS) {
+		s_hist[i] = 0;
+	}
+	__syncthreads();
+	const uint32_t seg = blockIdx.x / tiles_per_seg;
+	const uint64_t beg = (uint64_t)seg * seg_size + (uint64_t)(blockIdx.x % tiles_per_seg) * TILE;
+	const uint64_t end = min(min(n, (uint64_t)(seg + 1) * seg_size), beg + TILE);
+	uint32_t *mine = s_hist + (threadIdx.x & 3u) * RS_BINS;
+	for (uint64_t i = beg + threadIdx.x; i < end; i += RS_THREADS) {
+		const KeyT k = keys[i];
+#pragma unroll
+		for (int p = 0; p < MAX_PASSES; p++) {
+			if (p < passes) {
+				const int shift = begin_bit + 8 * p;
+				const int bits = min(8, end_bit - shift);
+				const uint32_t d = (uint32_t)((k >> shift) & (KeyT)((1u << bits) - 1));
+				atomicAdd(&mine[p * 4 * RS_BINS + d], 1u);
+			}
+		}
+	}
+	__syncthreads();
+	for (int i = threadIdx.x; i < passes * RS_BINS; i += RS_THREADS) {
+		const int p = i / RS_BINS, d = i % RS_BINS;
+		const uint32_t *h = s_hist + p * 4 * RS_BINS + d;
+		const uint32_t c = h[0] + h[RS_BINS] + h[2 * RS_BINS] + h[3 * RS_BINS];
+		if (c) {
+			atomicAdd(&hist[((size_t)p * nseg + seg) * RS_BINS + d], c);
+		}
+	}
+}
+
+// exclusive scan of the 256 bins of every (pass, segment) + the segment's first position. One block per row.
+__global__ void __launch_bounds__(RS_BINS) k_radix_scan_seg(uint32_t *__restrict__ hist, uint32_t nseg, uint64_t seg_size) {
+	__shared__ uint32_t s_warp[RS_BINS / 32];
+	uint32_t *h = hist + (size_t)blockIdx.x * RS_BINS;
+	const uint32_t seg = blockIdx.x % nseg;
+	const uint32_t v = h[threadIdx.x];
+	uint32_t inc = v;
+#pragma unroll
+	for (int s = 1; s < 32; s <<= 1) {
+		const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, s);
+		if (sb_lane() >= (unsigned)s) {
+			inc += o;
+		}
+	}
+	if (sb_lane() == 31) {
+		s_warp[threadIdx.x >> 5] = inc;
+	}
+	__syncthreads();
+	uint32_t base = (uint32_t)((uint64_t)seg * seg_size);
+	for (int w = 0; w < (int)(threadIdx.x >> 5); w++) {
+		base += s_warp[w];
+	}
+	h[threadIdx.x] = base + inc - v;
+}
+
 // ---- one onesweep pass ---------------------------------------------------------------------------------------
-template <typename KeyT, int ITEMS>
+// SEG: segmented sort -- the input is a sequence of `seg_size`-item segments (the last one may be shorter) and items
+// never leave their segment: tiles do not straddle segments (`tiles_per_seg` tiles each), the first tile of a segment
+// starts a new look-back chain, and bin_base holds one row of 256 bases per segment (segment start + digit prefix).
+template <typename KeyT, int ITEMS, bool SEG>
 __global__ void __launch_bounds__(RS_THREADS, 3)
     k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const uint32_t *__restrict__ vals_in,
                uint32_t *__restrict__ vals_out, uint64_t n, int shift, uint32_t digit_mask,
-               const uint32_t *__restrict__ bin_base, uint32_t *__restrict__ tile_state, uint32_t *__restrict__ ticket) {
+               const uint32_t *__restrict__ bin_base, uint32_t *__restrict__ tile_state, uint32_t *__restrict__ ticket,
+               uint64_t seg_size, uint32_t tiles_per_seg) {
 	constexpr int TILE = RS_THREADS * ITEMS;
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	KeyT *s_keys = reinterpret_cast<KeyT *>(smem_raw);
@@ -122,10 +189,16 @@ __global__ void __launch_bounds__(RS_THREADS, 3)
 	}
 	__syncthreads();
 	const uint32_t tile = s_tile;
-	const uint64_t tile_base = (uint64_t)tile * TILE;
+	const uint32_t seg = SEG ? tile / tiles_per_seg : 0u;
+	const uint32_t chain_first = SEG ? seg * tiles_per_seg : 0u; // first tile of this tile's look-back chain
+	const uint64_t tile_base = SEG ? (uint64_t)seg * seg_size + (uint64_t)(tile - chain_first) * TILE : (uint64_t)tile * TILE;
+	if (SEG) {
+		n = min(n, (uint64_t)(seg + 1) * seg_size); // end of the segment: everything below is bounded by it
+		bin_base += (size_t)seg * RS_BINS;
+	}
 	const unsigned warp = threadIdx.x >> 5, lane = sb_lane();
 	const unsigned lt_mask = sb_lanemask_lt();
-	const uint32_t tile_count = (uint32_t)min((uint64_t)TILE, n - tile_base);
+	const uint32_t tile_count = tile_base < n ? (uint32_t)min((uint64_t)TILE, n - tile_base) : 0u;
 
 	KeyT key[ITEMS];
 	uint32_t val[ITEMS];
@@ -167,7 +240,7 @@ __global__ void __launch_bounds__(RS_THREADS, 3)
 		total += c;
 	}
 	uint32_t *my_state = tile_state + (uint64_t)tile * RS_BINS + d;
-	st_volatile_u32(my_state, (tile == 0 ? RS_FLAG_INC : RS_FLAG_AGG) | total);
+	st_volatile_u32(my_state, (tile == chain_first ? RS_FLAG_INC : RS_FLAG_AGG) | total);
 
 	// block exclusive scan of `total` over the 256 digits
 	uint32_t inc = total;
@@ -190,7 +263,7 @@ __global__ void __launch_bounds__(RS_THREADS, 3)
 	s_digit_off[d] = digit_off;
 
 	uint32_t excl = 0;
-	if (tile > 0) {
+	if (tile > chain_first) {
 		// look back over the predecessors' status words, RS_LOOK loads in flight at a time (a one-at-a-time walk made the
 		// first wave of tiles pay one L2 round trip per predecessor: the whole pass was latency bound at 10 M keys)
 		int64_t look = (int64_t)tile - 1;
@@ -199,7 +272,8 @@ __global__ void __launch_bounds__(RS_THREADS, 3)
 			uint32_t st[RS_LOOK];
 #pragma unroll
 			for (int j = 0; j < RS_LOOK; j++) {
-				st[j] = look - j >= 0 ? ld_volatile_u32(tile_state + (uint64_t)(look - j) * RS_BINS + d) : RS_FLAG_INC;
+				st[j] = look - j >= (int64_t)chain_first ? ld_volatile_u32(tile_state + (uint64_t)(look - j) * RS_BINS + d)
+				                                         : RS_FLAG_INC;
 			}
 #pragma unroll
 			for (int j = 0; j < RS_LOOK; j++) {
@@ -279,7 +353,7 @@ int sbi_radix_sort_impl(sb_context *ctx, KeyT *keys, KeyT *keys_alt, uint32_t *v
 	uint32_t *tickets = temp + (size_t)passes * RS_BINS;
 	uint32_t *state = tickets + 64;
 
-	SB_SMEM_OPTIN(ctx, (k_onesweep<KeyT, cfg::ITEMS>), cfg::SMEM);
+	SB_SMEM_OPTIN(ctx, (k_onesweep<KeyT, cfg::ITEMS, false>), cfg::SMEM);
 	{
 		sb_prof_scope ps(ctx, "radix_hist");
 		k_radix_hist<KeyT, cfg::MAX_PASSES><<<sb_grid(n, RS_THREADS * 8, 8), RS_THREADS, 0, ctx->stream>>>(
@@ -294,11 +368,74 @@ int sbi_radix_sort_impl(sb_context *ctx, KeyT *keys, KeyT *keys_alt, uint32_t *v
 		const int shift = begin_bit + 8 * p;
 		const int bits = end_bit - shift < 8 ? end_bit - shift : 8;
 		sb_prof_scope ps(ctx, "radix_onesweep");
-		k_onesweep<KeyT, cfg::ITEMS><<<(unsigned)tiles, RS_THREADS, cfg::SMEM, ctx->stream>>>(
+		k_onesweep<KeyT, cfg::ITEMS, false><<<(unsigned)tiles, RS_THREADS, cfg::SMEM, ctx->stream>>>(
 		    kin, kout, (p == 0 && vals_iota) ? nullptr : vin, vout, n, shift, (1u << bits) - 1, hist + p * RS_BINS,
-		    state + (size_t)p * tiles * RS_BINS, tickets + p);
+		    state + (size_t)p * tiles * RS_BINS, tickets + p, 0, 0);
 		SB_LAUNCH_CHECK(ctx);
 		KeyT *tk = kin;
+		kin = kout;
+		kout = tk;
+		uint32_t *tv = vin;
+		vin = vout;
+		vout = tv;
+	}
+	*result_in_alt = (passes & 1);
+	return SB_OK;
+}
+
+// Segmented sort of 32-bit keys: every `seg_size`-item segment of the input (the last one may be shorter) is sorted on
+// its own, stably, in (end_bit - begin_bit) / 8 passes -- the segment index costs no pass (the STR y-sort inside
+// vertical slices was a 64-bit (slice, y) sort of 6 passes before; it is 4 passes over 32-bit keys now).
+int sbi_radix_sort_u32_segmented(sb_context *ctx, uint32_t *keys, uint32_t *keys_alt, uint32_t *vals, uint32_t *vals_alt,
+                                 uint64_t n, uint64_t seg_size, int begin_bit, int end_bit, bool vals_iota,
+                                 int *result_in_alt) {
+	using cfg = rs_cfg<uint32_t>;
+	*result_in_alt = 0;
+	if (n == 0) {
+		return SB_OK;
+	}
+	SB_ARG(n < ((uint64_t)1 << 30), "radix sort: n must be < 2^30");
+	SB_ARG(seg_size >= 1, "segment size");
+	SB_ARG(begin_bit >= 0 && end_bit <= 32 && begin_bit <= end_bit, "radix sort bit range");
+	const int passes = (end_bit - begin_bit + 7) / 8;
+	if (passes == 0) {
+		if (vals_iota) {
+			SB_TRY(sbi_iota_u32(ctx, vals, n));
+		}
+		return SB_OK;
+	}
+	const uint64_t nseg = (n + seg_size - 1) / seg_size;
+	const uint64_t tps = (seg_size + cfg::TILE - 1) / cfg::TILE;
+	const uint64_t tiles = nseg * tps;
+	SB_ARG(tiles < 0x7FFFFFFFull && nseg < 0x7FFFFFFFull, "segmented sort: too many segments");
+	const size_t hist_words = (size_t)passes * nseg * RS_BINS;
+	const size_t words = hist_words + 64 + (size_t)passes * tiles * RS_BINS;
+	uint32_t *temp = nullptr;
+	SB_TRY(ctx->scratch_t<uint32_t>(words, &temp));
+	SB_CUDA(cudaMemsetAsync(temp, 0, words * sizeof(uint32_t), ctx->stream));
+	uint32_t *hist = temp;
+	uint32_t *tickets = temp + hist_words;
+	uint32_t *state = tickets + 64;
+	SB_SMEM_OPTIN(ctx, (k_onesweep<uint32_t, cfg::ITEMS, true>), cfg::SMEM);
+	{
+		sb_prof_scope ps(ctx, "radix_hist");
+		k_radix_hist_seg<uint32_t, cfg::MAX_PASSES, cfg::TILE><<<(unsigned)tiles, RS_THREADS, 0, ctx->stream>>>(
+		    keys, n, begin_bit, end_bit, passes, seg_size, (uint32_t)tps, (uint32_t)nseg, hist);
+		SB_LAUNCH_CHECK(ctx);
+		k_radix_scan_seg<<<(unsigned)(passes * nseg), RS_BINS, 0, ctx->stream>>>(hist, (uint32_t)nseg, seg_size);
+		SB_LAUNCH_CHECK(ctx);
+	}
+	uint32_t *kin = keys, *kout = keys_alt;
+	uint32_t *vin = vals, *vout = vals_alt;
+	for (int p = 0; p < passes; p++) {
+		const int shift = begin_bit + 8 * p;
+		const int bits = end_bit - shift < 8 ? end_bit - shift : 8;
+		sb_prof_scope ps(ctx, "radix_onesweep");
+		k_onesweep<uint32_t, cfg::ITEMS, true><<<(unsigned)tiles, RS_THREADS, cfg::SMEM, ctx->stream>>>(
+		    kin, kout, (p == 0 && vals_iota) ? nullptr : vin, vout, n, shift, (1u << bits) - 1,
+		    hist + (size_t)p * nseg * RS_BINS, state + (size_t)p * tiles * RS_BINS, tickets + p, seg_size, (uint32_t)tps);
+		SB_LAUNCH_CHECK(ctx);
+		uint32_t *tk = kin;
 		kin = kout;
 		kout = tk;
 		uint32_t *tv = vin;

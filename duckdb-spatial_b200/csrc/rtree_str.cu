@@ -4,7 +4,8 @@
 // `slice` entries re-sorted by fp32 y-centre, packed `cap` per node, leaf nodes sorted by row id, node box = union.
 // B200 formulation: every sort is one stable radix sort over the whole layer --
 //   x-order : 32-bit key  = order-preserving bits of float(min_x + max_x)   (x0.5 in fp64 is monotone and exact)
-//   y-order : 64-bit key  = (position_in_layer / slice) << 32 | order-preserving bits of float((min_y+max_y)/2)
+//   y-order : 32-bit key  = order-preserving bits of float((min_y+max_y)/2), sorted per slice of the x order by the
+//             segmented radix sort (segment = `slice` consecutive positions of the layer)
 // followed by a pack kernel (one CTA per node: gather, rank-sort by row id in shared memory, union, coalesced
 // 24-byte entry stores). Level sizes are known on the host from n and cap, so the whole build is enqueued
 // without a single device->host synchronisation.
@@ -24,25 +25,25 @@ __global__ void __launch_bounds__(256) k_str_xkeys(const float4 *__restrict__ bo
 
 // level 0: entries are addressed through the x-order permutation
 __global__ void __launch_bounds__(256) k_str_ykeys_leaf(const float4 *__restrict__ box,
-                                                        const uint32_t *__restrict__ perm, uint64_t n, uint64_t slice,
-                                                        uint64_t *__restrict__ keys, uint32_t *__restrict__ vals) {
+                                                        const uint32_t *__restrict__ perm, uint64_t n,
+                                                        uint32_t *__restrict__ keys, uint32_t *__restrict__ vals) {
 	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
 	for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += stride) {
 		const uint32_t src = perm[j];
 		const float4 b = box[src];
 		// bounds.Center().y = (min.y + max.y) / 2 in fp32, bbox.hpp:78-80, rtree_index_create_physical.cpp:172-174
 		const float yc = __fdiv_rn(__fadd_rn(b.y, b.w), 2.0f);
-		keys[j] = ((j / slice) << 32) | (uint64_t)sb_f32_sort_key(yc);
+		keys[j] = sb_f32_sort_key(yc); // the slice is the segment of the segmented sort, not part of the key
 		vals[j] = src;
 	}
 }
 
-__global__ void __launch_bounds__(256) k_str_ykeys_upper(const sb_entry *__restrict__ cur, uint64_t n, uint64_t slice,
-                                                         uint64_t *__restrict__ keys) {
+__global__ void __launch_bounds__(256) k_str_ykeys_upper(const sb_entry *__restrict__ cur, uint64_t n,
+                                                         uint32_t *__restrict__ keys) {
 	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
 	for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += stride) {
 		const float yc = __fdiv_rn(__fadd_rn(cur[j].box[1], cur[j].box[3]), 2.0f);
-		keys[j] = ((j / slice) << 32) | (uint64_t)sb_f32_sort_key(yc);
+		keys[j] = sb_f32_sort_key(yc);
 	}
 }
 
@@ -128,15 +129,6 @@ __global__ void __launch_bounds__(256)
 	}
 }
 
-static int bit_width_u64(uint64_t v) {
-	int b = 0;
-	while (v) {
-		b++;
-		v >>= 1;
-	}
-	return b;
-}
-
 int sbi_rtree_build_str(sb_context *ctx, const float *box4, const int64_t *row_ids, uint64_t n, uint32_t cap,
                         sb_rtree **out) {
 	SB_ARG(cap >= 4 && cap <= 255, "max_node_capacity must be in [4, 255]");
@@ -188,17 +180,17 @@ int sbi_rtree_build_str(sb_context *ctx, const float *box4, const int64_t *row_i
 	uint32_t *free_v = alt ? v32 : v32b; // the other value buffer is reusable
 
 	// --- level 0: y-sort inside slices, pack leaves ---------------------------------------------------------
-	uint64_t *k64 = nullptr, *k64b = nullptr;
-	SB_TRY(ctx->scratch_t(n, &k64));
-	SB_TRY(ctx->scratch_t(n, &k64b));
-	uint32_t *yv = free_v, *yvb = k32; // k32/k32b are dead after the x sort
+	// segmented sort: every slice of the x order is sorted by y on its own (4 passes over 32-bit keys; a 64-bit
+	// (slice, y) key sort needed 6)
+	uint32_t *yk = k32, *ykb = k32b; // dead after the x sort
+	uint32_t *yv = free_v, *yvb = nullptr;
+	SB_TRY(ctx->scratch_t(n, &yvb));
 	{
 		sb_prof_scope ps(ctx, "str_keys");
-		k_str_ykeys_leaf<<<sb_grid(n, 256, 16), 256, 0, ctx->stream>>>(box, xperm, n, t->slice, k64, yv);
+		k_str_ykeys_leaf<<<sb_grid(n, 256, 16), 256, 0, ctx->stream>>>(box, xperm, n, yk, yv);
 		SB_LAUNCH_CHECK(ctx);
 	}
-	const uint64_t nslices0 = (n + t->slice - 1) / t->slice;
-	SB_TRY(sbi_radix_sort_u64(ctx, k64, k64b, yv, yvb, n, 0, 32 + bit_width_u64(nslices0 - 1), false, &alt));
+	SB_TRY(sbi_radix_sort_u32_segmented(ctx, yk, ykb, yv, yvb, n, t->slice, 0, 32, false, &alt));
 	const uint32_t *perm = alt ? yvb : yv;
 
 	uint64_t nodes = (n + cap - 1) / cap;
@@ -221,11 +213,10 @@ int sbi_rtree_build_str(sb_context *ctx, const float *box4, const int64_t *row_i
 		}
 		{
 			sb_prof_scope ps(ctx, "str_keys");
-			k_str_ykeys_upper<<<sb_grid(c, 256, 16), 256, 0, ctx->stream>>>(parents, c, t->slice, k64);
+			k_str_ykeys_upper<<<sb_grid(c, 256, 16), 256, 0, ctx->stream>>>(parents, c, yk);
 			SB_LAUNCH_CHECK(ctx);
 		}
-		const uint64_t ns = (c + t->slice - 1) / t->slice;
-		SB_TRY(sbi_radix_sort_u64(ctx, k64, k64b, yv, yvb, c, 0, 32 + bit_width_u64(ns - 1), true, &alt));
+		SB_TRY(sbi_radix_sort_u32_segmented(ctx, yk, ykb, yv, yvb, c, t->slice, 0, 32, true, &alt));
 		const uint32_t *p = alt ? yvb : yv;
 		const uint64_t nn = (c + cap - 1) / cap;
 		{
