@@ -51,6 +51,8 @@ SIGNATURES = {
     "sb_rtree_level_count": (u64, [vp, i32]),
     "sb_rtree_slice_size": (u64, [vp]),
     "sb_rtree_export_level": (i32, [vp, vp, i32, i32, vp]),
+    "sb_rtree_pages_layout": (i32, [vp, u64, vp]),
+    "sb_rtree_export_pages": (i32, [vp, vp, u64, i32, vp, vp, vp]),
     "sb_rtree_scan": (i32, [vp, vp, i32, vp, u32, vp, vp, u64, C.POINTER(u64)]),
     "sb_flat_build": (i32, [vp, i32, vp, u32, u32, C.POINTER(vp)]),
     "sb_flat_destroy": (None, [vp]),

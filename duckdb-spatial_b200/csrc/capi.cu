@@ -414,6 +414,28 @@ extern "C" int sb_rtree_export_level(sb_context *ctx, const sb_rtree *tree, int 
 	return finish(ctx, mem);
 }
 
+extern "C" int sb_rtree_pages_layout(const sb_rtree *tree, uint64_t block_size, sb_rtree_pages_info *info) {
+	SB_ARG(tree != nullptr && info != nullptr, "tree/info");
+	return sbi_rtree_pages_info(tree, block_size, info);
+}
+
+extern "C" int sb_rtree_export_pages(sb_context *ctx, const sb_rtree *tree, uint64_t block_size, sb_mem mem,
+                                     void *leaf_images, void *branch_images, void *root_entry) {
+	SB_BEGIN(ctx);
+	SB_ARG(tree != nullptr && root_entry != nullptr, "tree/root_entry");
+	sb_rtree_pages_info info;
+	SB_TRY(sbi_rtree_pages_info(tree, block_size, &info));
+	uint8_t *dl, *db;
+	const uint64_t lbytes = info.leaf_buffers * block_size, bbytes = info.branch_buffers * block_size;
+	SB_ARG((lbytes == 0 || leaf_images != nullptr) && (bbytes == 0 || branch_images != nullptr), "image buffers");
+	SB_TRY(sb_out_buffer(ctx, mem, static_cast<uint8_t *>(leaf_images), lbytes, &dl));
+	SB_TRY(sb_out_buffer(ctx, mem, static_cast<uint8_t *>(branch_images), bbytes, &db));
+	SB_TRY(sbi_rtree_export_pages(ctx, tree, block_size, dl, db, root_entry));
+	SB_TRY(sb_to_host(ctx, mem, static_cast<uint8_t *>(leaf_images), dl, lbytes));
+	SB_TRY(sb_to_host(ctx, mem, static_cast<uint8_t *>(branch_images), db, bbytes));
+	return finish(ctx, mem);
+}
+
 extern "C" int sb_rtree_scan(sb_context *ctx, const sb_rtree *tree, sb_mem mem, const float *query_box4, uint32_t nq,
                              uint32_t *out_query, int64_t *out_row_id, uint64_t capacity, uint64_t *count) {
 	SB_BEGIN(ctx);

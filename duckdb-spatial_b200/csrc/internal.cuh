@@ -77,6 +77,11 @@ int sbi_rtree_build_str(sb_context *ctx, const float *box4, const int64_t *row_i
 int sbi_rtree_scan(sb_context *ctx, const sb_rtree *tree, const float *qbox4, uint32_t nq, uint32_t *out_query,
                    int64_t *out_row, uint64_t capacity, uint64_t *count);
 
+int sbi_fsa_layout(uint64_t segment_size, uint64_t block_size, uint64_t *segments_per_buffer, uint64_t *bitmask_count);
+int sbi_rtree_pages_info(const sb_rtree *tree, uint64_t block_size, sb_rtree_pages_info *info);
+int sbi_rtree_export_pages(sb_context *ctx, const sb_rtree *tree, uint64_t block_size, void *leaf_img,
+                           void *branch_img, void *root_entry);
+
 // flat_rtree.cu
 int sbi_flat_build(sb_context *ctx, const float *box4, uint32_t n, uint32_t node_size, sb_flat **out);
 // probe modes: boxes only (candidates), or points with a fused exact predicate against the build's BOX_2D

@@ -391,3 +391,181 @@ int sbi_rtree_scan(sb_context *ctx, const sb_rtree *tree, const float *qbox4, ui
 	SB_CUDA(cudaStreamSynchronize(ctx->stream));
 	return SB_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Persistent-index export: the tree as the block images DuckDB's FixedSizeAllocator holds.
+//
+// The reference allocates one page per node while packing (tree.MakePage, rtree_index_create_physical.cpp:181-184):
+// leaf pages from `leaf_allocator`, branch pages from `node_allocator` (rtree.cpp:28-35), in node order, level by
+// level. A fresh allocator hands out segments sequentially (FixedSizeAllocator::New + FixedSizeBuffer::GetOffset,
+// duckdb/src/execution/index/fixed_size_allocator.cpp:43-80, fixed_size_buffer.cpp:154-165): page k lives in buffer
+// k / segments_per_buffer at offset k % segments_per_buffer, so every IndexPointer is a pure function of the node
+// index and the images can be written by the device in one pass:
+//   buffer image = [bitmask_count validity words: bit = 1 for a FREE segment][segments_per_buffer segments][slack]
+//   segment      = RTreeNode {u32 count, 20 unused bytes} + max_node_capacity RTreeEntry (rtree_node.hpp:66-75, 183-189)
+//   pointer      = metadata (node type) << 56 | offset << 32 | buffer id (index_pointer.hpp:19-24)
+// One CTA per page; 8-byte words, consecutive threads write consecutive words.
+// ---------------------------------------------------------------------------------------------------------------
+int sbi_fsa_layout(uint64_t segment_size, uint64_t block_size, uint64_t *segments_per_buffer, uint64_t *bitmask_count) {
+	SB_ARG(segment_size >= 8 && (segment_size & 7) == 0, "segment size must be a multiple of 8");
+	SB_ARG((block_size & 7) == 0 && segment_size + 8 <= block_size, "block size: multiple of 8, >= segment + bitmask word");
+	// one validity word per 64 segments; a word is added whenever the words so far cannot cover one more segment
+	uint64_t used = 0, words = 0, segs = 0;
+	while (used < block_size) {
+		if (words == 0 || (words * 64) % segs == 0) {
+			words++;
+			used += 8;
+		}
+		if (used >= block_size) {
+			break;
+		}
+		const uint64_t fit = (block_size - used) / segment_size;
+		const uint64_t take = fit < 64 ? fit : 64;
+		if (take == 0) {
+			break;
+		}
+		segs += take;
+		used += take * segment_size;
+	}
+	*segments_per_buffer = segs;
+	*bitmask_count = words;
+	return SB_OK;
+}
+
+struct page_levels {
+	const sb_entry *ent[16]; // entries the pages of this node level are cut from
+	uint64_t cnt[16];        // number of such entries
+	uint64_t page_base[16];  // first page of the node level inside this allocator
+	uint64_t child_base[16]; // first page of the children inside THEIR allocator
+	int n;
+	uint32_t cap;
+	uint32_t rewrite; // 0: leaf pages (row ids stay as they are), 1: branch pages
+	uint64_t pages, spb, bitmask_words, seg_words, block_words;
+};
+
+__device__ __forceinline__ uint64_t page_pointer(uint64_t type_and_child, uint64_t child_base, uint64_t spb) {
+	const uint64_t c = (type_and_child & 0x00FFFFFFFFFFFFFFull) + child_base;
+	return (type_and_child & 0xFF00000000000000ull) | ((c % spb) << 32) | (c / spb);
+}
+
+__global__ void __launch_bounds__(128) k_rtree_pages(const page_levels P, uint64_t *__restrict__ img) {
+	const uint64_t page = blockIdx.x;
+	int l = 0;
+	while (l + 1 < P.n && page >= P.page_base[l + 1]) {
+		l++;
+	}
+	const uint64_t node = page - P.page_base[l];
+	const uint64_t first = node * P.cap;
+	const uint64_t left = P.cnt[l] - first;
+	const uint32_t count = left < P.cap ? (uint32_t)left : P.cap;
+	const uint64_t *src = reinterpret_cast<const uint64_t *>(P.ent[l] + first);
+	const uint64_t buf = page / P.spb, slot = page % P.spb;
+	uint64_t *bufp = img + buf * P.block_words;
+	uint64_t *dst = bufp + P.bitmask_words + slot * P.seg_words;
+	for (uint32_t w = threadIdx.x; w < P.seg_words; w += blockDim.x) {
+		uint64_t v = 0;
+		if (w == 0) {
+			v = count; // RTreeNode::count, then 20 unused bytes
+		} else if (w >= 3 && w - 3 < 3 * count) {
+			v = src[w - 3];
+			if (P.rewrite && (w % 3) == 0) {
+				v = page_pointer(v, P.child_base[l], P.spb);
+			}
+		}
+		dst[w] = v;
+	}
+	if (slot == 0) {
+		// validity words (1 = free) and the slack behind the last segment
+		const uint64_t rest = P.pages - buf * P.spb;
+		const uint64_t used = rest < P.spb ? rest : P.spb;
+		for (uint32_t w = threadIdx.x; w < P.bitmask_words; w += blockDim.x) {
+			uint64_t m = 0;
+			for (uint32_t b = 0; b < 64; b++) {
+				const uint64_t s = (uint64_t)w * 64 + b;
+				m |= (uint64_t)(s >= used && s < P.spb) << b;
+			}
+			bufp[w] = m;
+		}
+		for (uint64_t w = P.bitmask_words + P.spb * P.seg_words + threadIdx.x; w < P.block_words; w += blockDim.x) {
+			bufp[w] = 0;
+		}
+	}
+}
+
+int sbi_rtree_pages_info(const sb_rtree *tree, uint64_t block_size, sb_rtree_pages_info *info) {
+	memset(info, 0, sizeof(*info));
+	info->segment_size = 24 + 24 * (uint64_t)tree->cap; // RTreeConfig::GetNodeByteSize == GetLeafByteSize, rtree.hpp:21-26
+	SB_TRY(sbi_fsa_layout(info->segment_size, block_size, &info->segments_per_buffer, &info->bitmask_count));
+	info->bitmask_offset = info->bitmask_count * 8;
+	if (tree->nlevels >= 2) {
+		info->leaf_pages = tree->counts[1];
+		for (int l = 2; l < tree->nlevels; l++) {
+			info->branch_pages += tree->counts[l];
+		}
+	}
+	const uint64_t spb = info->segments_per_buffer;
+	info->leaf_buffers = (info->leaf_pages + spb - 1) / spb;
+	info->branch_buffers = (info->branch_pages + spb - 1) / spb;
+	return SB_OK;
+}
+
+// leaf_img / branch_img: device, leaf_buffers / branch_buffers blocks of block_size bytes. root_entry: host, 24 bytes.
+int sbi_rtree_export_pages(sb_context *ctx, const sb_rtree *tree, uint64_t block_size, void *leaf_img,
+                           void *branch_img, void *root_entry) {
+	sb_rtree_pages_info info;
+	SB_TRY(sbi_rtree_pages_info(tree, block_size, &info));
+	uint64_t root[3] = {0, 0, 0};
+	if (tree->nlevels >= 2) {
+		SB_ARG(info.leaf_pages < (1ull << 31) && info.segments_per_buffer < (1ull << 24), "too many pages");
+		page_levels P;
+		memset(&P, 0, sizeof(P));
+		P.cap = tree->cap;
+		P.spb = info.segments_per_buffer;
+		P.bitmask_words = info.bitmask_count;
+		P.seg_words = info.segment_size / 8;
+		P.block_words = block_size / 8;
+		for (int pass = 0; pass < 2; pass++) {
+			uint8_t *img = static_cast<uint8_t *>(pass == 0 ? leaf_img : branch_img);
+			const uint64_t pages = pass == 0 ? info.leaf_pages : info.branch_pages;
+			if (pages == 0) {
+				continue;
+			}
+			SB_ARG(img != nullptr, "page image buffer");
+			P.pages = pages;
+			P.rewrite = (uint32_t)pass;
+			if (pass == 0) {
+				P.n = 1;
+				P.ent[0] = tree->entries + tree->offsets[0];
+				P.cnt[0] = tree->counts[0];
+				P.page_base[0] = 0;
+				P.child_base[0] = 0;
+			} else {
+				// node level L >= 1 is cut from the level-L entries; its children are the pages of node level L-1
+				P.n = tree->nlevels - 2;
+				uint64_t base = 0;
+				for (int L = 1; L <= P.n; L++) {
+					P.ent[L - 1] = tree->entries + tree->offsets[L];
+					P.cnt[L - 1] = tree->counts[L];
+					P.page_base[L - 1] = base;
+					P.child_base[L - 1] = L == 1 ? 0 : P.page_base[L - 2];
+					base += tree->counts[L + 1];
+				}
+			}
+			// segments of the last buffer that stay free
+			const uint64_t nbuf = (pages + P.spb - 1) / P.spb;
+			const uint64_t used_last = pages - (nbuf - 1) * P.spb;
+			SB_TRY(sbi_zero(ctx, img + (nbuf - 1) * block_size + info.bitmask_offset + used_last * info.segment_size,
+			                (P.spb - used_last) * info.segment_size));
+			sb_prof_scope ps(ctx, "rtree_pages");
+			k_rtree_pages<<<(unsigned)pages, 128, 0, ctx->stream>>>(P, reinterpret_cast<uint64_t *>(img));
+			SB_LAUNCH_CHECK(ctx);
+		}
+		// the root entry: pointer of the single top-level entry, rewritten like any other page pointer
+		SB_TRY(sbi_read_words(ctx, tree->entries + tree->offsets[tree->nlevels - 1], 3, root));
+		const uint64_t top_base = tree->nlevels == 2 ? 0 : info.branch_pages - 1; // the top node is the last branch page
+		const uint64_t c = (root[0] & 0x00FFFFFFFFFFFFFFull) + top_base;
+		root[0] = (root[0] & 0xFF00000000000000ull) | ((c % info.segments_per_buffer) << 32) | (c / info.segments_per_buffer);
+	}
+	memcpy(root_entry, root, 24);
+	return SB_OK;
+}

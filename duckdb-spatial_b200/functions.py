@@ -478,6 +478,35 @@ class RTreeIndex:
         capi.check(self.ctx.L.sb_rtree_export_level(self.ctx.h, self.h, l, capi.HOST, _ptr(out)))
         return out
 
+    def pages_layout(self, block_size=262136):
+        """FixedSizeAllocator geometry + page / buffer counts of the exported tree (sb_rtree_pages_layout)."""
+        info = (C.c_uint64 * 8)()
+        capi.check(self.ctx.L.sb_rtree_pages_layout(self.h, block_size, info))
+        names = ("segment_size", "segments_per_buffer", "bitmask_count", "bitmask_offset", "leaf_pages",
+                 "leaf_buffers", "branch_pages", "branch_buffers")
+        return dict(zip(names, (int(v) for v in info)))
+
+    def pages(self, block_size=262136, device=False):
+        """The tree as the block images of the reference's leaf / branch FixedSizeAllocators, IndexPointers
+        included (GetStorageInfo path, rtree_index.cpp:234-259) -> (layout, leaf images, branch images, root entry).
+        Images are uint8 arrays (numpy, or CUDA torch tensors with device=True)."""
+        info = self.pages_layout(block_size)
+        root = np.zeros(1, ENTRY_DTYPE)
+        if device:
+            import torch
+
+            dev = torch.device("cuda", self.ctx.device)
+            leaf = torch.empty(info["leaf_buffers"] * block_size, dtype=torch.uint8, device=dev)
+            branch = torch.empty(info["branch_buffers"] * block_size, dtype=torch.uint8, device=dev)
+            mem = capi.DEVICE
+        else:
+            leaf = np.empty(info["leaf_buffers"] * block_size, np.uint8)
+            branch = np.empty(info["branch_buffers"] * block_size, np.uint8)
+            mem = capi.HOST
+        capi.check(self.ctx.L.sb_rtree_export_pages(self.ctx.h, self.h, block_size, mem, _ptr(leaf), _ptr(branch),
+                                                    _ptr(root)))
+        return info, leaf, branch, root[0]
+
     def scan(self, query_box4, capacity=None):
         """batched RTreeIndex scan -> (query index [k], row id [k]); per query in the reference's DFS order."""
         q = query_box4 if _is_torch(query_box4) else np.ascontiguousarray(query_box4, np.float32).reshape(-1, 4)

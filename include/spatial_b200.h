@@ -164,6 +164,26 @@ SB_API uint64_t sb_rtree_slice_size(const sb_rtree *tree);
  * ((type<<56) | child node index, type LEAF_PAGE=1 / BRANCH_PAGE=2) into IndexPointers. Leaf-level pointers are
  * row ids with type ROW_ID=0 (rtree.cpp:37-42). */
 SB_API int sb_rtree_export_level(sb_context *ctx, const sb_rtree *tree, int level, sb_mem mem, void *out_entries);
+/* Persistent-index export (GetStorageInfo / checkpoint path, rtree_index.cpp:234-259): the whole tree as the block
+ * images of the reference's two FixedSizeAllocators (rtree.hpp:31-36; leaf pages and branch pages), with real
+ * IndexPointers (index_pointer.hpp:19-24: metadata << 56 | offset << 32 | buffer id), exactly as
+ * BuildRTreeBottomUp's tree.MakePage sequence (rtree_index_create_physical.cpp:181-184, 241-246) leaves them in
+ * fresh allocators: page k of an allocator = buffer k / segments_per_buffer, offset k % segments_per_buffer
+ * (fixed_size_allocator.cpp:43-80, fixed_size_buffer.cpp:154-165). block_size = BlockManager::GetBlockSize()
+ * (262136 for the default 256 KiB blocks). Each image is block_size bytes: bitmask_count validity words (bit set =
+ * segment free), then segments of segment_size bytes = RTreeNode {u32 count, 20 B unused} + max_node_capacity
+ * RTreeEntry (rtree_node.hpp:66-75, 183-189); unused entries, free segments and the slack are zero.
+ * The host glue copies image b into buffers[b] of the allocator, sets its segment_count
+ * (min(segments_per_buffer, pages - b * segments_per_buffer)) and calls tree.SetRoot(root_entry). */
+typedef struct sb_rtree_pages_info {
+	uint64_t segment_size, segments_per_buffer, bitmask_count, bitmask_offset;
+	uint64_t leaf_pages, leaf_buffers, branch_pages, branch_buffers;
+} sb_rtree_pages_info;
+SB_API int sb_rtree_pages_layout(const sb_rtree *tree, uint64_t block_size, sb_rtree_pages_info *info);
+/* leaf_images: leaf_buffers * block_size bytes, branch_images: branch_buffers * block_size bytes (`mem` says where);
+ * root_entry: 24 bytes of HOST memory (one RTreeEntry; all zero for an empty tree). */
+SB_API int sb_rtree_export_pages(sb_context *ctx, const sb_rtree *tree, uint64_t block_size, sb_mem mem,
+                                 void *leaf_images, void *branch_images, void *root_entry);
 /* Batched index scan: replaces RTreeIndex::InitializeScan/Scan (rtree_index.cpp:106-139, rtree_scanner.hpp:38-83)
  * for nq query boxes at once. Emits (query index, row id) for every leaf entry whose float box intersects the
  * query box (closed intervals, bbox.hpp:27-29). Order: grouped by nothing in particular (sort to compare).

@@ -374,6 +374,26 @@ class StrTree:
         lib().orc_rtree_dump(C.c_void_p(self.h), _p(lvl, i32p), _p(box, f32p), _p(rid, i64p))
         return lvl, box, rid
 
+    def pages(self, block_size=262136):
+        """FixedSizeAllocator block images of the tree -> (counts dict, leaf images, branch images, root entry)."""
+        L = lib()
+        L.orc_rtree_export_pages.restype = C.c_int
+        L.orc_fsa_layout.restype = C.c_int
+        lay = (C.c_uint64 * 3)()
+        if L.orc_fsa_layout(C.c_uint64(24 + 24 * self.cap), C.c_uint64(block_size), lay):
+            raise ValueError("segment does not fit the block")
+        cnt = (C.c_uint64 * 4)()
+        root = np.zeros(1, ENTRY_DTYPE)
+        L.orc_rtree_export_pages(C.c_void_p(self.h), C.c_uint64(block_size), None, None, _p(root, C.c_void_p), cnt)
+        leaf = np.empty(cnt[1] * block_size, np.uint8)
+        branch = np.empty(cnt[3] * block_size, np.uint8)
+        L.orc_rtree_export_pages(C.c_void_p(self.h), C.c_uint64(block_size), _p(leaf, C.c_void_p),
+                                 _p(branch, C.c_void_p), _p(root, C.c_void_p), cnt)
+        info = dict(segment_size=24 + 24 * self.cap, segments_per_buffer=lay[0], bitmask_count=lay[1],
+                    bitmask_offset=lay[2], leaf_pages=cnt[0], leaf_buffers=cnt[1], branch_pages=cnt[2],
+                    branch_buffers=cnt[3])
+        return info, leaf, branch, root[0]
+
     def scan(self, qbox):
         q = np.asarray(qbox, np.float32)
         n = lib().orc_rtree_scan(C.c_void_p(self.h), _p(q, f32p), None)

@@ -1052,6 +1052,136 @@ ORC_API uint64_t orc_rtree_dump(const orc_rtree *t, int32_t *lvl, float *box, in
 	return dump_rec(t, t->nlevels - 2, 0, 0, lvl, box, rid, 0);
 }
 
+/* ------------------------------------------------------------------------------------------------
+ * Persistent-index page images. Restates, as a sequential emulation:
+ *  - FixedSizeAllocator's constructor (segments per buffer / bitmask words),
+ *    duckdb/src/execution/index/fixed_size_allocator.cpp:7-41
+ *  - FixedSizeAllocator::New on a fresh allocator: new buffer when none has space, mask.SetAllValid, then
+ *    FixedSizeBuffer::GetOffset takes bit `segment_count` (fills a buffer sequentially) and clears it,
+ *    fixed_size_allocator.cpp:43-80, fixed_size_buffer.cpp:154-165
+ *  - segment address = buffer + offset * segment_size + bitmask_offset, fixed_size_allocator.hpp:53-61
+ *  - IndexPointer(buffer_id, offset) + SetMetadata(type), index_pointer.hpp:19-58; RTree::MakePage rtree.cpp:28-35
+ *  - the MakePage / PushEntry order of BuildRTreeBottomUp, rtree_index_create_physical.cpp:143-252
+ * PARITY UNPINNED for the allocator part: FixedSizeAllocator needs a live DuckDB BlockManager and is not in
+ * libref.so; the tree content is pinned (orc_rtree_build_str is node-for-node the reference's). Memory the
+ * reference leaves uninitialised (unused entries, free segments, slack, bitmask bits past the last segment)
+ * is zero here.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+	uint64_t segment_size, spb, bitmask_count, bitmask_offset, block_size;
+	uint8_t *img;      /* may be NULL: count only */
+	uint64_t nbuffers; /* buffers created so far */
+	uint64_t seg_in_last;
+	uint64_t total;
+} orc_fsa;
+
+ORC_API int orc_fsa_layout(uint64_t segment_size, uint64_t block_size, uint64_t *out3) {
+	const uint64_t bits_per_value = 64;
+	uint64_t byte_count = 0, bitmask_count = 0, available = 0;
+	if (segment_size > block_size - 8) {
+		return -1;
+	}
+	while (byte_count < block_size) {
+		if (!bitmask_count || (bitmask_count * bits_per_value) % available == 0) {
+			bitmask_count++;
+			byte_count += 8;
+		}
+		uint64_t remaining_bytes = block_size - byte_count;
+		uint64_t remaining_segments = remaining_bytes / segment_size;
+		if (remaining_segments > bits_per_value) {
+			remaining_segments = bits_per_value;
+		}
+		if (remaining_segments == 0) {
+			break;
+		}
+		available += remaining_segments;
+		byte_count += remaining_segments * segment_size;
+	}
+	out3[0] = available;
+	out3[1] = bitmask_count;
+	out3[2] = bitmask_count * 8;
+	return 0;
+}
+
+/* FixedSizeAllocator::New -> IndexPointer bits (without metadata); *seg = address of the segment or NULL */
+static uint64_t fsa_new(orc_fsa *a, uint8_t **seg) {
+	if (a->nbuffers == 0 || a->seg_in_last == a->spb) {
+		/* new buffer: all segments valid (= free) */
+		if (a->img) {
+			uint8_t *buf = a->img + a->nbuffers * a->block_size;
+			memset(buf, 0, a->block_size);
+			uint64_t *mask = (uint64_t *)buf;
+			for (uint64_t i = 0; i < a->spb; i++) {
+				mask[i / 64] |= 1ULL << (i % 64);
+			}
+		}
+		a->nbuffers++;
+		a->seg_in_last = 0;
+	}
+	const uint64_t buffer_id = a->nbuffers - 1, offset = a->seg_in_last;
+	if (a->img) {
+		uint8_t *buf = a->img + buffer_id * a->block_size;
+		((uint64_t *)buf)[offset / 64] &= ~(1ULL << (offset % 64)); /* SetInvalid = taken */
+		*seg = buf + offset * a->segment_size + a->bitmask_offset;
+	} else {
+		*seg = NULL;
+	}
+	a->seg_in_last++;
+	a->total++;
+	return (offset << 32) | buffer_id;
+}
+
+/* out_counts: leaf_pages, leaf_buffers, branch_pages, branch_buffers. Images may be NULL (sizes only).
+ * root24 = the RTreeEntry given to tree.SetRoot. */
+ORC_API int orc_rtree_export_pages(const orc_rtree *t, uint64_t block_size, uint8_t *leaf_img, uint8_t *branch_img,
+                                   void *root24, uint64_t *out_counts) {
+	uint64_t lay[3];
+	const uint64_t segment_size = 24 + 24 * (uint64_t)t->cap; /* sizeof(RTreeNode) + sizeof(RTreeEntry) * cap */
+	if (orc_fsa_layout(segment_size, block_size, lay)) {
+		return -1;
+	}
+	orc_fsa leaf = {segment_size, lay[0], lay[1], lay[2], block_size, leaf_img, 0, 0, 0};
+	orc_fsa node = {segment_size, lay[0], lay[1], lay[2], block_size, branch_img, 0, 0, 0};
+	orc_entry root = {0, {0, 0, 0, 0}};
+	if (t->nlevels >= 2) {
+		/* pointers of the pages made for the previous layer, in node order */
+		uint64_t *prev = NULL;
+		for (int l = 0; l + 1 < t->nlevels; l++) {
+			const uint64_t nodes = t->counts[l + 1];
+			uint64_t *cur = (uint64_t *)malloc(nodes * sizeof(uint64_t));
+			for (uint64_t j = 0; j < nodes; j++) {
+				uint8_t *seg;
+				const uint64_t type = l == 0 ? 1 : 2; /* LEAF_PAGE / BRANCH_PAGE */
+				cur[j] = fsa_new(l == 0 ? &leaf : &node, &seg) | (type << 56);
+				const uint64_t b = j * t->cap, e = b + t->cap < t->counts[l] ? b + t->cap : t->counts[l];
+				if (seg) {
+					uint32_t count = 0;
+					orc_entry *dst = (orc_entry *)(seg + 24);
+					for (uint64_t i = b; i < e; i++) {
+						orc_entry en = t->levels[l][i];
+						if (l > 0) {
+							en.ptr = prev[en.ptr & 0xFFFFFFFFFFFFULL];
+						}
+						dst[count++] = en; /* PushEntry */
+					}
+					memcpy(seg, &count, 4);
+				}
+			}
+			free(prev);
+			prev = cur;
+		}
+		root = t->levels[t->nlevels - 1][0];
+		root.ptr = prev[0];
+		free(prev);
+	}
+	memcpy(root24, &root, 24);
+	out_counts[0] = leaf.total;
+	out_counts[1] = leaf.nbuffers;
+	out_counts[2] = node.total;
+	out_counts[3] = node.nbuffers;
+	return 0;
+}
+
 /* RTreeIndex::InitializeScan/Scan, rtree_index.cpp:106-139: DFS, emits row ids in DFS order. */
 static uint64_t scan_rec(const orc_rtree *t, int tl, uint64_t node, const float *q, int64_t *out, uint64_t pos) {
 	const uint64_t b = node * t->cap, e = b + t->cap < t->counts[tl] ? b + t->cap : t->counts[tl];

@@ -100,13 +100,18 @@ def main():
             qb = ctx.bbox_from_box2d(qx, qy, qx + sx, qy + sy)
             cap = 1 << 26
             sms, (oq, orow) = timed(stream, lambda: idx.scan(qb, capacity=cap), a.reps)
+            pms, (pinfo, pleaf, pbranch, _) = timed(stream, lambda: idx.pages(device=True), a.reps)
+            pbytes = 24.0 * sum(idx.level_counts()) + pleaf.numel() + pbranch.numel()
             print(json.dumps({"config": "C1 rtree_points_index", "keys": n, "build_ms": ms, "build_mkeys_per_s": n / ms / 1e3,
                               "build_algorithmic_gbs": 48.2 * n / ms / 1e6, "build_hbm_frac": 48.2 * n / ms / 1e6 / hbm,
                               "levels": idx.level_counts(), "known_answer_(450,450,650,650)": int(len(r1)),
                               "batched_scan_queries": 10000, "batched_scan_ms": sms, "batched_scan_rows": int(len(orow)),
-                              "scan_rows_per_s": len(orow) / sms * 1e3}), flush=True)
+                              "scan_rows_per_s": len(orow) / sms * 1e3,
+                              "export_pages_ms": pms, "export_pages": [pinfo["leaf_pages"], pinfo["branch_pages"]],
+                              "export_pages_gbs": pbytes / pms / 1e6, "export_pages_hbm_frac": pbytes / pms / 1e6 / hbm}),
+                  flush=True)
             idx.close()
-            del x, y, rows, oq, orow
+            del x, y, rows, oq, orow, pleaf, pbranch
         # ---- C2: RTREE over polygon / box GEOMETRY blobs + range scans ---------------------------------------------
         if want("c2") and a.c2:
             n = a.c2
