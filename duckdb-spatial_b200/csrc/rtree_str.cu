@@ -79,12 +79,35 @@ __global__ void __launch_bounds__(256)
 	}
 	uint32_t rank = t;
 	if (LEAF) {
+		// rank of the entry among the node's row ids. Fast path: when every row id of the node is within 2^31 of
+		// the first one, ranks are counted over 32-bit offsets read four at a time; equal row ids (not expected:
+		// row ids are unique) or a wider spread fall back to the 64-bit count with the position tie-break.
+		__shared__ __align__(16) uint32_t s_k32[256];
+		__shared__ uint32_t s_slot[256];
+		const int64_t mine = (int64_t)(e.ptr << 8) >> 8; // sign-extended 56-bit row id
 		if (t < cnt) {
-			s_row[t] = (int64_t)(e.ptr << 8) >> 8; // sign-extended 56-bit row id
+			s_row[t] = mine;
 		}
 		__syncthreads();
-		if (t < cnt) {
-			const int64_t mine = s_row[t];
+		const int64_t d = mine - s_row[0];
+		const bool narrow = t >= cnt || d == (int64_t)(int32_t)d;
+		const uint32_t k32 = t < cnt ? (uint32_t)(int32_t)d ^ 0x80000000u : 0xFFFFFFFFu;
+		s_k32[t] = k32;
+		bool slow = !__syncthreads_and(narrow);
+		if (!slow) {
+			rank = 0;
+			const uint4 *k4 = reinterpret_cast<const uint4 *>(s_k32);
+			for (uint32_t k = 0; k < (cnt + 3) / 4; k++) {
+				const uint4 v = k4[k];
+				rank += (v.x < k32) + (v.y < k32) + (v.z < k32) + (v.w < k32);
+			}
+			if (t < cnt) {
+				s_slot[rank] = t;
+			}
+			__syncthreads();
+			slow = __syncthreads_or(t < cnt && s_slot[rank] != t);
+		}
+		if (slow && t < cnt) {
 			rank = 0;
 			for (uint32_t k = 0; k < cnt; k++) {
 				const int64_t o = s_row[k];

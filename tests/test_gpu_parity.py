@@ -211,6 +211,16 @@ def test_str_build_node_for_node(ctx, sb, O, n, cap):
     assert pos == len(orow)
 
 
+@pytest.mark.parametrize("n,cap,spread", [(20000, 128, 1 << 33), (20000, 100, 1 << 31), (3000, 255, 1 << 40)])
+def test_str_build_wide_row_ids(ctx, sb, O, n, cap, spread):
+    # row ids further apart than 2^31 inside a node: the leaf pack's 64-bit ranking path
+    rng = np.random.default_rng(n + cap)
+    x, y = O.generate_points(99, n, (0, 0, 1000, 1000))
+    box = O.bbox_from_box2d(x - 1, y - 1, x + 1, y + 1)
+    rows = rng.permutation(n).astype(np.int64) * spread + 7
+    _tree_equal(sb.RTreeIndex(ctx, box, rows, cap), O.StrTree(box, rows, cap))
+
+
 def test_str_empty(ctx, sb):
     idx = sb.RTreeIndex(ctx, np.zeros((0, 4), np.float32), np.zeros(0, np.int64))
     assert idx.nlevels == 0
