@@ -57,6 +57,7 @@ def main():
     ap.add_argument("--c5", type=int, nargs=2, default=[100_000_000, 10_000_000])
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--only", default="")
+    ap.add_argument("--ctx-opt", action="append", default=[], metavar="KEY=VALUE", help="sb_context_set_option, for A/B runs")
     a = ap.parse_args()
     import numpy as np
     import torch
@@ -67,6 +68,9 @@ def main():
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(0)
     ctx = sb.Context(0)
+    for kv in a.ctx_opt:
+        k, v = kv.split("=")
+        ctx.set_option(k, int(v))
     stream = torch.cuda.Stream(device=dev)
     peaks = {}
     try:
