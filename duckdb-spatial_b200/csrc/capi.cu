@@ -643,6 +643,72 @@ extern "C" int sb_distance_points(sb_context *ctx, sb_mem mem, const double *ax,
 	return finish(ctx, mem);
 }
 
+extern "C" int sb_intersects_box2d(sb_context *ctx, sb_mem mem, const double *a_min_x, const double *a_min_y,
+                                   const double *a_max_x, const double *a_max_y, const double *b_min_x,
+                                   const double *b_min_y, const double *b_max_x, const double *b_max_y,
+                                   uint32_t stride, const uint8_t *valid_a, const uint8_t *valid_b, uint64_t n,
+                                   uint8_t *out) {
+	SB_BEGIN(ctx);
+	SB_ARG(stride == 1 || stride == 4, "stride must be 1 (SoA columns) or 4 (AoS rows)");
+	SB_ARG(out != nullptr || n == 0, "out");
+	const double *src[8] = {a_min_x, a_min_y, a_max_x, a_max_y, b_min_x, b_min_y, b_max_x, b_max_y};
+	const double *dev[8];
+	if (stride == 4 && mem == SB_HOST) {
+		// AoS rows: stage each box array once (columns are the four interleaved offsets of one buffer)
+		for (int s = 0; s < 2; s++) {
+			const double *base = src[4 * s];
+			for (int c = 1; c < 4; c++) {
+				SB_ARG(src[4 * s + c] == base + c, "stride 4 expects box4 + 0..3");
+			}
+			const double *d;
+			SB_TRY(sb_to_device(ctx, mem, base, 4 * n, &d));
+			for (int c = 0; c < 4; c++) {
+				dev[4 * s + c] = d + c;
+			}
+		}
+	} else {
+		for (int c = 0; c < 8; c++) {
+			SB_TRY(sb_to_device(ctx, mem, src[c], stride == 1 ? n : 4 * n - (c & 3), &dev[c]));
+		}
+	}
+	const uint8_t *va = nullptr, *vb = nullptr;
+	if (valid_a) {
+		SB_TRY(sb_to_device(ctx, mem, valid_a, n, &va));
+	}
+	if (valid_b) {
+		SB_TRY(sb_to_device(ctx, mem, valid_b, n, &vb));
+	}
+	uint8_t *dout;
+	SB_TRY(sb_out_buffer(ctx, mem, out, n, &dout));
+	SB_TRY(sbi_box2d_intersects(ctx, dev, dev + 4, stride, va, vb, n, dout));
+	SB_TRY(sb_to_host(ctx, mem, out, dout, n));
+	return finish(ctx, mem);
+}
+
+extern "C" int sb_distance_point_linestring(sb_context *ctx, sb_mem mem, const double *px, const double *py,
+                                            const uint64_t *list_entries, uint64_t n, const double *vx,
+                                            const double *vy, uint64_t n_vertices, double *out) {
+	SB_BEGIN(ctx);
+	const double *dx, *dy, *dvx, *dvy;
+	const uint64_t *dl;
+	double *dout;
+	if (mem == SB_HOST) {
+		for (uint64_t i = 0; i < n; i++) {
+			const uint64_t off = list_entries[2 * i], len = list_entries[2 * i + 1];
+			SB_ARG(off <= n_vertices && len <= n_vertices - off, "list entry outside the vertex columns");
+		}
+	}
+	SB_TRY(sb_to_device(ctx, mem, px, n, &dx));
+	SB_TRY(sb_to_device(ctx, mem, py, n, &dy));
+	SB_TRY(sb_to_device(ctx, mem, list_entries, 2 * n, &dl));
+	SB_TRY(sb_to_device(ctx, mem, vx, n_vertices, &dvx));
+	SB_TRY(sb_to_device(ctx, mem, vy, n_vertices, &dvy));
+	SB_TRY(sb_out_buffer(ctx, mem, out, n, &dout));
+	SB_TRY(sbi_distance_point_linestring(ctx, dx, dy, dl, dvx, dvy, n, dout));
+	SB_TRY(sb_to_host(ctx, mem, out, dout, n));
+	return finish(ctx, mem);
+}
+
 // Host-pointer join of a large probe column: the probe column is streamed through the device in chunks so that the
 // H2D copy of chunk k+1, the probe of chunk k and the D2H copy of chunk k-1's pairs overlap (three streams, PCIe is
 // full duplex). The call is bound by the larger of the two copy directions instead of their sum plus the kernels.

@@ -82,6 +82,12 @@ int sbi_rtree_pages_info(const sb_rtree *tree, uint64_t block_size, sb_rtree_pag
 int sbi_rtree_export_pages(sb_context *ctx, const sb_rtree *tree, uint64_t block_size, void *leaf_img,
                            void *branch_img, void *root_entry);
 
+// refine.cu (native-type scalar functions)
+int sbi_box2d_intersects(sb_context *ctx, const double *const a[4], const double *const b[4], uint32_t stride,
+                         const uint8_t *va, const uint8_t *vb, uint64_t n, uint8_t *out);
+int sbi_distance_point_linestring(sb_context *ctx, const double *px, const double *py, const uint64_t *lists,
+                                  const double *vx, const double *vy, uint64_t n, double *out);
+
 // flat_rtree.cu
 int sbi_flat_build(sb_context *ctx, const float *box4, uint32_t n, uint32_t node_size, sb_flat **out);
 // probe modes: boxes only (candidates), or points with a fused exact predicate against the build's BOX_2D

@@ -362,3 +362,107 @@ int sbi_unmatched_rows(sb_context *ctx, const uint8_t *flags, uint64_t n, uint32
 	}
 	return SB_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Native-type scalar predicates next to the join path
+// ---------------------------------------------------------------------------------------------------------------
+// ST_Intersects(BOX_2D, BOX_2D), spatial_functions_scalar.cpp:5407-5416 (same test as sgl::box_xy::intersects,
+// sgl.hpp:93-95): NOT (a.min_x > b.max_x OR a.max_x < b.min_x OR a.min_y > b.max_y OR a.max_y < b.min_y); NaNs make
+// every comparison false, i.e. "intersects", exactly as on the CPU. Rows whose validity byte is 0 give false
+// (ST_Intersects_Extent's "no extent" rows, :5456-5481).
+__global__ void __launch_bounds__(256)
+    k_box2d_intersects(const double *__restrict__ a0, const double *__restrict__ a1, const double *__restrict__ a2,
+                       const double *__restrict__ a3, const double *__restrict__ b0, const double *__restrict__ b1,
+                       const double *__restrict__ b2, const double *__restrict__ b3, uint32_t stride,
+                       const uint8_t *__restrict__ va, const uint8_t *__restrict__ vb, uint64_t n,
+                       uint8_t *__restrict__ out) {
+	const uint64_t step = (uint64_t)gridDim.x * blockDim.x;
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += step) {
+		const uint64_t k = i * stride;
+		bool r = !(a0[k] > b2[k] || a2[k] < b0[k] || a1[k] > b3[k] || a3[k] < b1[k]);
+		if ((va && !va[i]) || (vb && !vb[i])) {
+			r = false;
+		}
+		out[i] = r ? 1 : 0;
+	}
+}
+
+int sbi_box2d_intersects(sb_context *ctx, const double *const a[4], const double *const b[4], uint32_t stride,
+                         const uint8_t *va, const uint8_t *vb, uint64_t n, uint8_t *out) {
+	if (n == 0) {
+		return SB_OK;
+	}
+	sb_prof_scope ps(ctx, "box_intersects");
+	k_box2d_intersects<<<sb_grid(n, 256, 16), 256, 0, ctx->stream>>>(a[0], a[1], a[2], a[3], b[0], b[1], b[2], b[3],
+	                                                                 stride, va, vb, n, out);
+	SB_LAUNCH_CHECK(ctx);
+	return SB_OK;
+}
+
+// ST_Distance(POINT_2D, LINESTRING_2D), spatial_functions_scalar.cpp:2219-2258, with ClosestPointOnSegment :2158-2176
+// (ApproxEqualTo: |dx| < 1e-6 AND |dy| < 1e-6, vertex.hpp:50-52) and DistanceToSegmentSquared :2178-2184. Same operation
+// order, no FMA contraction (the library is built with -fmad=false). The reference keeps the minimum of the squared
+// segment distances with `<` (NaN never replaces it) and stops at 0: a minimum over non-negative values, so the
+// lanes of a warp can take every 32nd segment and combine with the same `<` -- the result is the same double.
+// One warp per row.
+__device__ __forceinline__ double seg_dist2(double px, double py, double x1, double y1, double x2, double y2) {
+	double cx, cy;
+	if (fabs(x1 - x2) < 1e-6 && fabs(y1 - y2) < 1e-6) {
+		cx = x1, cy = y1;
+	} else {
+		const double n1 = (px - x1) * (x2 - x1) + (py - y1) * (y2 - y1);
+		const double n2 = (x2 - x1) * (x2 - x1) + (y2 - y1) * (y2 - y1);
+		const double r = n1 / n2;
+		if (r <= 0) {
+			cx = x1, cy = y1;
+		} else if (r >= 1) {
+			cx = x2, cy = y2;
+		} else {
+			cx = x1 + r * (x2 - x1), cy = y1 + r * (y2 - y1);
+		}
+	}
+	const double dx = px - cx, dy = py - cy;
+	return dx * dx + dy * dy;
+}
+
+__global__ void __launch_bounds__(256)
+    k_dist_point_line(const double *__restrict__ px, const double *__restrict__ py, const uint64_t *__restrict__ lists,
+                      const double *__restrict__ vx, const double *__restrict__ vy, uint64_t n,
+                      double *__restrict__ out) {
+	const unsigned lane = sb_lane();
+	const uint64_t warps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+	for (uint64_t i = (((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5); i < n; i += warps) {
+		const uint64_t off = lists[2 * i], len = lists[2 * i + 1];
+		const double x = px[i], y = py[i];
+		double best = DBL_MAX;
+		// the reference's `length - 1` wraps for an empty list (it then reads past the list); here an empty or
+		// one-vertex line has no segment and yields sqrt(DBL_MAX), the value the loop starts from
+		for (uint64_t j = lane; j + 1 < len; j += 32) {
+			const double d = seg_dist2(x, y, vx[off + j], vy[off + j], vx[off + j + 1], vy[off + j + 1]);
+			if (d < best) {
+				best = d;
+			}
+		}
+#pragma unroll
+		for (int s = 16; s > 0; s >>= 1) {
+			const double o = __shfl_xor_sync(0xFFFFFFFFu, best, s);
+			if (o < best) {
+				best = o;
+			}
+		}
+		if (lane == 0) {
+			out[i] = sqrt(best);
+		}
+	}
+}
+
+int sbi_distance_point_linestring(sb_context *ctx, const double *px, const double *py, const uint64_t *lists,
+                                  const double *vx, const double *vy, uint64_t n, double *out) {
+	if (n == 0) {
+		return SB_OK;
+	}
+	sb_prof_scope ps(ctx, "refine_dist");
+	k_dist_point_line<<<sb_grid(n * 32, 256, 16), 256, 0, ctx->stream>>>(px, py, lists, vx, vy, n, out);
+	SB_LAUNCH_CHECK(ctx);
+	return SB_OK;
+}

@@ -52,7 +52,10 @@ class Context:
     def use_torch_stream(self):
         import torch
 
-        capi.check(self.L.sb_context_set_stream(self.h, torch.cuda.current_stream().cuda_stream))
+        # torch's default stream has handle 0, which sb_context_set_stream reads as "back to the private stream":
+        # name the legacy default stream explicitly (cudaStreamLegacy = 0x1) so the work is ordered with torch's
+        h = torch.cuda.current_stream().cuda_stream
+        capi.check(self.L.sb_context_set_stream(self.h, h if h else 1))
 
     def use_private_stream(self):
         capi.check(self.L.sb_context_set_stream(self.h, None))
@@ -252,6 +255,41 @@ class Context:
         out = self._empty(a[0], (len(a[0]),), np.float64)
         capi.check(self.L.sb_distance_points(self.h, self._mem(*a), *[_ptr(v) for v in a], len(a[0]), _ptr(out)))
         return out
+
+    def st_distance_point_linestring(self, px, py, list_entries, vx, vy):
+        """ST_Distance(POINT_2D, LINESTRING_2D); list_entries = [n,2] uint64 (offset, length) rows into vx / vy."""
+        px, py, vx, vy = [self._f64(v) for v in (px, py, vx, vy)]
+        le = list_entries if _is_torch(list_entries) else np.ascontiguousarray(list_entries, np.uint64).reshape(-1, 2)
+        out = self._empty(px, (len(px),), np.float64)
+        capi.check(self.L.sb_distance_point_linestring(self.h, self._mem(px, py, le, vx, vy), _ptr(px), _ptr(py),
+                                                       _ptr(le), len(px), _ptr(vx), _ptr(vy), len(vx), _ptr(out)))
+        return out
+
+    def st_intersects_box2d(self, a_box4, b_box4, valid_a=None, valid_b=None):
+        """ST_Intersects(BOX_2D, BOX_2D) over AoS [n,4] float64 boxes -> uint8[n]; rows whose validity byte is 0 are 0."""
+        a = a_box4 if _is_torch(a_box4) else np.ascontiguousarray(a_box4, np.float64).reshape(-1, 4)
+        b = b_box4 if _is_torch(b_box4) else np.ascontiguousarray(b_box4, np.float64).reshape(-1, 4)
+        out = self._empty(a, (len(a),), np.uint8)
+        pa, pb = _ptr(a), _ptr(b)
+        cols = [pa + 8 * c for c in range(4)] + [pb + 8 * c for c in range(4)]
+        capi.check(self.L.sb_intersects_box2d(self.h, self._mem(a, b), *cols, 4, _ptr(valid_a), _ptr(valid_b),
+                                              len(a), _ptr(out)))
+        return out
+
+    def st_intersects_box2d_columns(self, a_cols, b_cols):
+        """same over DuckDB's struct child vectors: two lists of four float64 columns (min_x, min_y, max_x, max_y)."""
+        cols = [self._f64(v) for v in list(a_cols) + list(b_cols)]
+        out = self._empty(cols[0], (len(cols[0]),), np.uint8)
+        capi.check(self.L.sb_intersects_box2d(self.h, self._mem(*cols), *[_ptr(v) for v in cols], 1, None, None,
+                                              len(cols[0]), _ptr(out)))
+        return out
+
+    def st_intersects_extent(self, data_a, off_a, data_b, off_b):
+        """ST_Intersects_Extent(GEOMETRY, GEOMETRY), spatial_functions_scalar.cpp:5456-5481: the exact extents of both
+        sides (sb_extent_from_blobs) and the box test; rows where either side has no extent are false."""
+        ea, va = self.st_extent(data_a, off_a)
+        eb, vb = self.st_extent(data_b, off_b)
+        return self.st_intersects_box2d(ea, eb, va, vb)
 
     def st_within_point_polygon(self, px, py, vx, vy, ring_off, poly_off, pair_point, pair_poly):
         """ST_Within(POINT_2D, POLYGON_2D) over candidate pairs -> surviving (point, polygon) pairs."""

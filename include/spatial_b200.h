@@ -59,7 +59,8 @@ SB_API const char *sb_version(void);
 /* One context per calling thread / GPU: owns a stream and a scratch arena. */
 SB_API int sb_context_create(int device, sb_context **out);
 SB_API void sb_context_destroy(sb_context *ctx);
-/* adopt an external stream (e.g. torch.cuda.current_stream().cuda_stream); NULL restores the private stream */
+/* adopt an external stream (e.g. torch.cuda.current_stream().cuda_stream); NULL restores the private stream, so the
+ * legacy default stream has to be named as cudaStreamLegacy ((cudaStream_t)0x1) */
 SB_API int sb_context_set_stream(sb_context *ctx, void *cuda_stream);
 SB_API int sb_context_sync(sb_context *ctx);
 /* tuning / test knobs. "probe_path": 0 = auto, 1 = per-probe tree walk only, 2 = bucketed bulk probe only
@@ -244,6 +245,23 @@ SB_API int sb_refine_dwithin(sb_context *ctx, sb_mem mem, const double *ax, cons
 /* elementwise ST_Distance(POINT_2D, POINT_2D) */
 SB_API int sb_distance_points(sb_context *ctx, sb_mem mem, const double *ax, const double *ay, const double *bx,
                               const double *by, uint64_t n, double *out);
+/* ST_Intersects(BOX_2D, BOX_2D): replaces ST_Intersects::ExecuteBox, spatial_functions_scalar.cpp:5407-5416 (closed
+ * intervals; the test of sgl::box_xy::intersects, sgl.hpp:93-95). Each box is four double columns read at index
+ * i * stride: stride 1 = DuckDB's struct child vectors, stride 4 = AoS rows such as sb_extent_from_blobs writes (pass
+ * box4 + 0..3). valid_a / valid_b (may be NULL): rows with a 0 byte give 0. With the extents and validity bytes of two
+ * sb_extent_from_blobs calls this is ST_Intersects_Extent(GEOMETRY, GEOMETRY), :5456-5481. out: one byte per row. */
+SB_API int sb_intersects_box2d(sb_context *ctx, sb_mem mem, const double *a_min_x, const double *a_min_y,
+                               const double *a_max_x, const double *a_max_y, const double *b_min_x,
+                               const double *b_min_y, const double *b_max_x, const double *b_max_y, uint32_t stride,
+                               const uint8_t *valid_a, const uint8_t *valid_b, uint64_t n, uint8_t *out);
+/* ST_Distance(POINT_2D, LINESTRING_2D): replaces ST_Distance::PointLineStringOperation, spatial_functions_scalar.cpp:
+ * 2219-2258 (ClosestPointOnSegment :2158-2176 incl. its 1e-6 ApproxEqualTo vertex test, vertex.hpp:50-52; squared
+ * distances, `<` minimum, one sqrt). list_entries = DuckDB list_entry_t rows {u64 offset, u64 length} into the
+ * vertex columns vx / vy (n_vertices long). Lines with fewer than two vertices give sqrt(DBL_MAX) (the reference's
+ * loop bound underflows for an empty list). Bit-identical doubles. */
+SB_API int sb_distance_point_linestring(sb_context *ctx, sb_mem mem, const double *px, const double *py,
+                                        const uint64_t *list_entries, uint64_t n, const double *vx, const double *vy,
+                                        uint64_t n_vertices, double *out);
 
 /* ---- whole join (the call PhysicalSpatialJoin::Finalize + ExecuteInternal would make) ----------------------
  * Points (probe side, LHS) x boxes (build side, RHS, given as BOX_2D columns of the envelope polygons):

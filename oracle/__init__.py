@@ -485,3 +485,24 @@ def dwithin_brute(ax, ay, bx, by, r):
     od = np.empty(n, np.float64)
     lib().orc_dwithin_brute(*args, _p(oa, u32p), _p(ob, u32p), _p(od, f64p), C.c_uint64(n))
     return np.stack([oa, ob], 1), od
+
+
+def box2d_intersects(a_box4, b_box4, valid_a=None, valid_b=None):
+    a = np.ascontiguousarray(a_box4, np.float64).reshape(-1, 4)
+    b = np.ascontiguousarray(b_box4, np.float64).reshape(-1, 4)
+    va = None if valid_a is None else np.ascontiguousarray(valid_a, np.uint8)
+    vb = None if valid_b is None else np.ascontiguousarray(valid_b, np.uint8)
+    out = np.empty(len(a), np.uint8)
+    u8p = C.POINTER(C.c_uint8)
+    lib().orc_box2d_intersects(_p(a, f64p), _p(b, f64p), None if va is None else _p(va, u8p),
+                               None if vb is None else _p(vb, u8p), C.c_uint64(len(a)), _p(out, u8p))
+    return out
+
+
+def distance_point_linestring(px, py, lists, vx, vy):
+    px, py, vx, vy = [np.ascontiguousarray(v, np.float64) for v in (px, py, vx, vy)]
+    lists = np.ascontiguousarray(lists, np.uint64).reshape(-1, 2)
+    out = np.empty(len(px), np.float64)
+    lib().orc_distance_point_linestring(_p(px, f64p), _p(py, f64p), _p(lists, C.POINTER(C.c_uint64)), C.c_uint64(len(px)),
+                                        _p(vx, f64p), _p(vy, f64p), _p(out, f64p))
+    return out

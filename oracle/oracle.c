@@ -1648,3 +1648,60 @@ ORC_API int orc_rtree_build_from_points(const double *x, const double *y, uint64
 	free(rid);
 	return nl;
 }
+
+/* ------------------------------------------------------------------------------------------------
+ * Native-type scalar functions
+ * ---------------------------------------------------------------------------------------------- */
+/* ST_Intersects(BOX_2D, BOX_2D), spatial_functions_scalar.cpp:5407-5416; with validity bytes: ST_Intersects_Extent,
+ * :5456-5481 (rows without an extent are false; box_xy::intersects sgl.hpp:93-95). a, b: AoS rows of 4 doubles. */
+ORC_API void orc_box2d_intersects(const double *a, const double *b, const uint8_t *va, const uint8_t *vb, uint64_t n,
+                                  uint8_t *out) {
+	for (uint64_t i = 0; i < n; i++) {
+		const double *l = a + 4 * i, *r = b + 4 * i;
+		int v = !(l[0] > r[2] || l[2] < r[0] || l[1] > r[3] || l[3] < r[1]);
+		if ((va && !va[i]) || (vb && !vb[i])) {
+			v = 0;
+		}
+		out[i] = (uint8_t)v;
+	}
+}
+
+/* ST_Distance(POINT_2D, LINESTRING_2D): PointLineStringOperation spatial_functions_scalar.cpp:2219-2258,
+ * ClosestPointOnSegment :2158-2176, ApproxEqualTo vertex.hpp:50-52, DistanceToSegmentSquared :2178-2184.
+ * PARITY UNPINNED by execution (the function needs DuckDB vectors; no reference test holds a value for it);
+ * the arithmetic follows the source line by line. Built without FMA contraction (-ffp-contract=off).
+ * Lines with fewer than two vertices: sqrt(DBL_MAX) (the reference's `length - 1` underflows for an empty list). */
+ORC_API void orc_distance_point_linestring(const double *px, const double *py, const uint64_t *lists, uint64_t n,
+                                           const double *vx, const double *vy, double *out) {
+	for (uint64_t i = 0; i < n; i++) {
+		const uint64_t offset = lists[2 * i], length = lists[2 * i + 1];
+		double min_distance = DBL_MAX;
+		for (uint64_t j = 0; j + 1 < length; j++) {
+			const double x1 = vx[offset + j], y1 = vy[offset + j], x2 = vx[offset + j + 1], y2 = vy[offset + j + 1];
+			double cx, cy;
+			if (fabs(x1 - x2) < 1e-6 && fabs(y1 - y2) < 1e-6) {
+				cx = x1, cy = y1;
+			} else {
+				const double n1 = ((px[i] - x1) * (x2 - x1) + (py[i] - y1) * (y2 - y1));
+				const double n2 = ((x2 - x1) * (x2 - x1) + (y2 - y1) * (y2 - y1));
+				const double r = n1 / n2;
+				if (r <= 0) {
+					cx = x1, cy = y1;
+				} else if (r >= 1) {
+					cx = x2, cy = y2;
+				} else {
+					cx = x1 + r * (x2 - x1), cy = y1 + r * (y2 - y1);
+				}
+			}
+			const double dx = px[i] - cx, dy = py[i] - cy;
+			const double distance = dx * dx + dy * dy;
+			if (distance < min_distance) {
+				min_distance = distance;
+				if (min_distance == 0) {
+					break;
+				}
+			}
+		}
+		out[i] = sqrt(min_distance);
+	}
+}
