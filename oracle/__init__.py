@@ -38,6 +38,12 @@ def build(force=False):
         force or not os.path.exists(ref) or os.path.getmtime(ref) < os.path.getmtime(rsrc)
     ):
         subprocess.check_call(["make", "-s", "-C", _HERE, "_ref/libref.so"])
+    ref2 = os.path.join(_HERE, "_ref", "libref_scalar.so")
+    rsrc2 = os.path.join(_HERE, "ref_scalar.cpp")
+    if os.path.isdir("/root/reference/src/spatial") and (
+        force or not os.path.exists(ref2) or os.path.getmtime(ref2) < os.path.getmtime(rsrc2)
+    ):
+        subprocess.check_call(["make", "-s", "-C", _HERE, "_ref/libref_scalar.so"])
 
 
 def _p(a, t):
@@ -141,6 +147,28 @@ def ref():
         R.ref_cached_bounds.restype = C.c_int
         _REF = R
     return _REF
+
+
+_REF_SCALAR = None
+
+
+def ref_scalar():
+    """The reference's scalar-function TU (oracle/_ref/libref_scalar.so, see ref_scalar.cpp) or None."""
+    global _REF_SCALAR
+    if _REF_SCALAR is None:
+        path = os.path.join(_HERE, "_ref", "libref_scalar.so")
+        if not os.path.exists(path):
+            try:
+                build()
+            except Exception:
+                pass
+        if not os.path.exists(path):
+            return None
+        R = C.CDLL(path, mode=os.RTLD_LAZY)
+        R.ref_dist_to_segment_squared.restype = C.c_double
+        R.ref_dist_to_segment_squared.argtypes = [C.c_double] * 6
+        _REF_SCALAR = R
+    return _REF_SCALAR
 
 
 # ---------------------------------------------------------------------------------------------------

@@ -1668,8 +1668,9 @@ ORC_API void orc_box2d_intersects(const double *a, const double *b, const uint8_
 
 /* ST_Distance(POINT_2D, LINESTRING_2D): PointLineStringOperation spatial_functions_scalar.cpp:2219-2258,
  * ClosestPointOnSegment :2158-2176, ApproxEqualTo vertex.hpp:50-52, DistanceToSegmentSquared :2178-2184.
- * PARITY UNPINNED by execution (the function needs DuckDB vectors; no reference test holds a value for it);
- * the arithmetic follows the source line by line. Built without FMA contraction (-ffp-contract=off).
+ * Pinned on the reference's own DistanceToSegmentSquared compiled from its source (oracle/ref_scalar.cpp ->
+ * _ref/libref_scalar.so; tests/test_oracle_vs_ref.py folds it with the row loop). No reference test holds a value
+ * for this function. Built without FMA contraction (-ffp-contract=off).
  * Lines with fewer than two vertices: sqrt(DBL_MAX) (the reference's `length - 1` underflows for an empty list). */
 ORC_API void orc_distance_point_linestring(const double *px, const double *py, const uint64_t *lists, uint64_t n,
                                            const double *vx, const double *vy, double *out) {

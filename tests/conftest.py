@@ -36,3 +36,11 @@ def sb():
     import sb200
 
     return sb200.load()
+
+
+@pytest.fixture(scope="session")
+def RS(O):
+    r = O.ref_scalar()
+    if r is None:
+        pytest.skip("oracle/_ref/libref_scalar.so not built (no /root/reference)")
+    return r

@@ -161,3 +161,28 @@ def test_ref_join_count_matches_oracle(O, R):
         on, oc = O.join_points_boxes(px, py, *b, pred=pred, want_pairs=False)
         assert tot == on and cand.value == oc
     R.ref_flat_free(h)
+
+
+def test_point_linestring_distance_vs_reference_segment_helper(O, RS):
+    """orc_distance_point_linestring against the reference's own DistanceToSegmentSquared / ClosestPointOnSegment
+    (spatial_functions_scalar.cpp:2158-2184, compiled in oracle/_ref/libref_scalar.so) folded with the loop of
+    PointLineStringOperation (:2236-2256: `<` minimum, stop at 0, one sqrt)."""
+    from test_native_scalar import make_lines
+
+    rng = np.random.default_rng(17)
+    px, py, lists, vx, vy = make_lines(rng, 400, max_len=30)
+    got = O.distance_point_linestring(px, py, lists, vx, vy)
+    dmax = np.finfo(np.float64).max
+    nseg = 0
+    for i in range(len(px)):
+        o, l = int(lists[i, 0]), int(lists[i, 1])
+        best = dmax
+        for j in range(max(l - 1, 0)):
+            d = RS.ref_dist_to_segment_squared(px[i], py[i], vx[o + j], vy[o + j], vx[o + j + 1], vy[o + j + 1])
+            nseg += 1
+            if d < best:
+                best = d
+                if best == 0:
+                    break
+        assert np.float64(got[i]).view(np.uint64) == np.sqrt(np.float64(best)).view(np.uint64), i
+    assert nseg > 5000
