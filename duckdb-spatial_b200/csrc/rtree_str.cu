@@ -154,6 +154,57 @@ __global__ void __launch_bounds__(256)
 	}
 }
 
+// Small upper levels (<= STR_SMALL entries) in ONE launch instead of eight: y keys, the sort inside the slices and the
+// pack of a whole level by a single CTA. The order is the one the segmented radix sort produces -- by (slice, y key),
+// ties in input order -- because the index is the last part of a unique 64-bit key: slice (11 bits) | y key (32) |
+// index (11), sorted with a bitonic network in shared memory. One thread per node then streams its entries out and
+// takes the union box in entry order (fp32 min / max are order-free).
+#define STR_SMALL 2048
+__global__ void __launch_bounds__(1024)
+    k_str_small_level(const sb_entry *__restrict__ cur, uint32_t count, uint32_t cap, uint64_t slice,
+                      sb_entry *__restrict__ level_out, sb_entry *__restrict__ parent_out, uint64_t parent_type) {
+	__shared__ uint64_t s_key[STR_SMALL];
+	const unsigned t = threadIdx.x;
+	for (uint32_t i = t; i < STR_SMALL; i += blockDim.x) {
+		uint64_t k = ~0ull; // padding sorts last
+		if (i < count) {
+			const float yc = __fdiv_rn(__fadd_rn(cur[i].box[1], cur[i].box[3]), 2.0f);
+			k = ((uint64_t)(i / slice) << 43) | ((uint64_t)sb_f32_sort_key(yc) << 11) | i;
+		}
+		s_key[i] = k;
+	}
+	__syncthreads();
+	for (uint32_t size = 2; size <= STR_SMALL; size <<= 1) {
+		for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+			for (uint32_t i = t; i < STR_SMALL / 2; i += blockDim.x) {
+				const uint32_t lo = 2 * i - (i & (stride - 1));
+				const uint32_t hi = lo + stride;
+				const bool up = (lo & size) == 0;
+				const uint64_t a = s_key[lo], b = s_key[hi];
+				if ((a > b) == up) {
+					s_key[lo] = b;
+					s_key[hi] = a;
+				}
+			}
+			__syncthreads();
+		}
+	}
+	const uint32_t nodes = (count + cap - 1) / cap;
+	for (uint32_t node = t; node < nodes; node += blockDim.x) {
+		const uint32_t beg = node * cap, end = min(beg + cap, count);
+		float u0 = FLT_MAX, u1 = FLT_MAX, u2 = -FLT_MAX, u3 = -FLT_MAX;
+		for (uint32_t j = beg; j < end; j++) {
+			const sb_entry e = cur[s_key[j] & 2047u];
+			level_out[j] = e;
+			u0 = fminf(u0, e.box[0]), u1 = fminf(u1, e.box[1]), u2 = fmaxf(u2, e.box[2]), u3 = fmaxf(u3, e.box[3]);
+		}
+		sb_entry p;
+		p.ptr = (parent_type << 56) | node;
+		p.box[0] = u0, p.box[1] = u1, p.box[2] = u2, p.box[3] = u3;
+		parent_out[node] = p;
+	}
+}
+
 int sbi_rtree_build_str(sb_context *ctx, const float *box4, const int64_t *row_ids, uint64_t n, uint32_t cap,
                         sb_rtree **out) {
 	SB_ARG(cap >= 4 && cap <= 255, "max_node_capacity must be in [4, 255]");
@@ -237,6 +288,16 @@ int sbi_rtree_build_str(sb_context *ctx, const float *box4, const int64_t *row_i
 			SB_CUDA(cudaMemcpyAsync(t->entries + t->offsets[level], parents, sizeof(sb_entry), cudaMemcpyDeviceToDevice,
 			                        ctx->stream));
 			break;
+		}
+		if (c <= STR_SMALL) {
+			sb_prof_scope ps(ctx, "str_pack");
+			k_str_small_level<<<1, 1024, 0, ctx->stream>>>(parents, (uint32_t)c, cap, t->slice,
+			                                               t->entries + t->offsets[level], parents_b, 2ull);
+			SB_LAUNCH_CHECK(ctx);
+			sb_entry *tmp = parents;
+			parents = parents_b;
+			parents_b = tmp;
+			continue;
 		}
 		{
 			sb_prof_scope ps(ctx, "str_keys");
