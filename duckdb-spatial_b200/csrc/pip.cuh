@@ -1,6 +1,8 @@
 // pip.cuh -- ST_Contains::Operation (POLYGON_2D x POINT_2D winding number), spatial_functions_scalar.cpp:1938-2051,
 // reached through ST_Within(POINT_2D, POLYGON_2D) :7775-7781. Literal control flow, plain fp64 (no FMA): an on-edge
-// hit only leaves the coordinate loop; the ring is then judged by the winding number accumulated so far.
+// hit sets contains = false and only leaves the coordinate loop (:2011-2016); the ring is then judged by the winding
+// number accumulated so far -- the shell overwrites `contains`, a hole that is not "in_ring" leaves it false (so a
+// point on a hole's boundary is outside; pinned on the reference's own ST_Within, tests/test_oracle_vs_refdb.py).
 #pragma once
 #include "common.cuh"
 
@@ -32,11 +34,15 @@ __device__ __forceinline__ bool sb_pip_native(double x, double y, const double *
 	bool contains = false, first = true;
 	for (uint64_t r = r0; r < r1; r++) {
 		const uint64_t o = ring_off[r], e = ring_off[r + 1];
-		double x1 = vx[o], y1 = vy[o];
+		double x1 = 0.0, y1 = 0.0;
+		if (o < e) { // an empty last ring must not read past the vertex columns
+			x1 = vx[o], y1 = vy[o];
+		}
 		int wn = 0;
 		for (uint64_t c = o + 1; c < e; c++) {
 			const double x2 = vx[c], y2 = vy[c];
 			if (sb_pip_edge(x, y, x1, y1, x2, y2, wn)) {
+				contains = false;
 				break;
 			}
 			x1 = x2;

@@ -44,6 +44,10 @@ def build(force=False):
         force or not os.path.exists(ref2) or os.path.getmtime(ref2) < os.path.getmtime(rsrc2)
     ):
         subprocess.check_call(["make", "-s", "-C", _HERE, "_ref/libref_scalar.so"])
+    # the DuckDB-linked reference (CREATE INDEX / rtree_index_dump / ST_Within / SPATIAL_JOIN through SQL): DuckDB core
+    # (~6 min the first time) + the unmodified reference translation units, see the `ref_duckdb` rules of the Makefile
+    if os.path.isdir("/root/reference/duckdb/src") and not os.environ.get("ORACLE_SKIP_DUCKDB"):
+        subprocess.check_call(["make", "-s", "-j8", "-C", _HERE, "ref_duckdb"])
 
 
 def _p(a, t):
@@ -100,6 +104,10 @@ def lib():
         L.orc_point_within_box.argtypes = [C.c_double] * 6
         L.orc_pip_native.restype = C.c_int
         L.orc_pip_native.argtypes = [C.c_double, C.c_double, f64p, f64p, u64p, C.c_uint64, C.c_uint64]
+        L.orc_orient2d_sign.restype = C.c_int
+        L.orc_orient2d_sign.argtypes = [C.c_double] * 6
+        L.orc_point_polygon_locate.restype = C.c_int
+        L.orc_point_polygon_locate.argtypes = [C.c_double, C.c_double, f64p, f64p, u64p, C.c_uint64, C.c_uint64]
         L.orc_distance_pp.restype = C.c_double
         L.orc_distance_pp.argtypes = [C.c_double] * 4
         L.orc_join_points_boxes.restype = C.c_uint64
@@ -502,6 +510,30 @@ def join_points_boxes(px, py, bminx, bminy, bmaxx, bmaxy, pred=0, threads=0, wan
 
 def pip_native(x, y, vx, vy, ring_off, r0, r1):
     return lib().orc_pip_native(x, y, _p(vx, f64p), _p(vy, f64p), _p(ring_off, u64p), C.c_uint64(r0), C.c_uint64(r1))
+
+
+def orient2d_sign(ax, ay, bx, by, cx, cy):
+    """exact sign of (b-a) x (c-a): +1 left / counter-clockwise, -1 right, 0 collinear"""
+    return lib().orc_orient2d_sign(ax, ay, bx, by, cx, cy)
+
+
+def point_polygon_locate(x, y, vx, vy, ring_off, r0, r1):
+    """GEOS point-in-area location (exact orientation): 0 exterior, 1 boundary, 2 interior"""
+    return lib().orc_point_polygon_locate(x, y, _p(vx, f64p), _p(vy, f64p), _p(ring_off, u64p), C.c_uint64(r0), C.c_uint64(r1))
+
+
+def point_polygon_exact(px, py, pi, qi, vx, vy, ring_off, poly_off, pred=0):
+    """pairs (pi[k], qi[k]) -> uint8 mask; pred 0 = ST_Intersects, 1 = ST_Within(point, polygon) (GEOS semantics)"""
+    px, py, vx, vy = [np.ascontiguousarray(v, np.float64) for v in (px, py, vx, vy)]
+    ring_off = np.ascontiguousarray(ring_off, np.uint64)
+    poly_off = np.ascontiguousarray(poly_off, np.uint64)
+    pi = None if pi is None else np.ascontiguousarray(pi, np.uint32)
+    qi = None if qi is None else np.ascontiguousarray(qi, np.uint32)
+    n = len(pi) if pi is not None else (len(qi) if qi is not None else len(px))
+    out = np.empty(n, np.uint8)
+    lib().orc_point_polygon_exact(_p(px, f64p), _p(py, f64p), _p(pi, u32p), _p(qi, u32p), C.c_uint64(n), _p(vx, f64p),
+                                  _p(vy, f64p), _p(ring_off, u64p), _p(poly_off, u64p), C.c_int(pred), _p(out, u8p))
+    return out
 
 
 def dwithin_brute(ax, ay, bx, by, r):

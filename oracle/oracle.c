@@ -1493,7 +1493,10 @@ ORC_API int orc_pip_native(double x, double y, const double *vx, const double *v
 		}
 		if (on_edge) {
 			/* `contains = false; break;` leaves the coordinate loop only (:2011-2016); the ring is then
-			 * judged by the winding number accumulated so far (:2025-2044). */
+			 * judged by the winding number accumulated so far (:2025-2044). For the shell the assignment is
+			 * overwritten below; for a hole that is not "in_ring" it STAYS false (pinned on the reference's
+			 * own ST_Within through oracle/_ref/libref_duckdb.so: a point on a hole's boundary is outside). */
+			contains = 0;
 		}
 		const int in_ring = wn != 0;
 		if (first) {
@@ -1509,6 +1512,147 @@ ORC_API int orc_pip_native(double x, double y, const double *vx, const double *v
 		first = 0;
 	}
 	return contains;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * GEOMETRY-argument predicates (the GEOS route): ST_Intersects geos_module.cpp:1128-1153, ST_Contains :386-415,
+ * ST_Within :1885-1908. GEOS itself is a third-party dependency absent from /root/reference (vcpkg.json:6,
+ * baseline 5e5d0e1c..., GEOS >= 3.12); what is restated here is its published point-in-area algorithm:
+ * algorithm::RayCrossingCounter::countSegment with the robust orientation test CGAlgorithmsDD::orientationIndex,
+ * combined per polygon as locate::SimplePointInAreaLocator::locatePointInPolygon (shell, then holes).
+ * The orientation sign is computed EXACTLY (expansion arithmetic), so the answer is the mathematically true
+ * location; parity is anchored on the reference's own vectors for the path: test/sql/geos/predicates.test:15-46
+ * (boundary => intersects, not contains; GEOS ticket 580), index/rtree_filter_prune.test:14-20 (ids 5,6,8,9).
+ * ---------------------------------------------------------------------------------------------- */
+
+/* error-free transforms (round-to-nearest fp64, no overflow assumed) */
+static void two_sum(double a, double b, double *s, double *e) {
+	const double x = a + b, bv = x - a, av = x - bv;
+	*s = x;
+	*e = (a - av) + (b - bv);
+}
+static void two_prod(double a, double b, double *p, double *e) {
+	*p = a * b;
+	*e = fma(a, b, -*p);
+}
+/* h = e + b for a non-overlapping expansion e of length n (increasing magnitude); returns the new length (zeros kept) */
+static int grow_expansion(int n, const double *e, double b, double *h) {
+	double q = b;
+	for (int i = 0; i < n; i++) {
+		double s, r;
+		two_sum(q, e[i], &s, &r);
+		h[i] = r;
+		q = s;
+	}
+	h[n] = q;
+	return n + 1;
+}
+
+/* sign of (bx-ax)*(cy-ay) - (by-ay)*(cx-ax): +1 = c left of a->b (counter-clockwise), -1 = right, 0 = collinear.
+ * Expanded into six exact products: ax*by - ax*cy - ay*bx + ay*cx + bx*cy - by*cx. */
+ORC_API int orc_orient2d_sign(double ax, double ay, double bx, double by, double cx, double cy) {
+	/* fast filter (Shewchuk's stage A bound) */
+	const double dl = (bx - ax) * (cy - ay), dr = (by - ay) * (cx - ax);
+	const double det = dl - dr;
+	const double eps = 1.1102230246251565e-16;
+	const double bound = (3.0 + 16.0 * eps) * eps * (fabs(dl) + fabs(dr));
+	if (det > bound) {
+		return 1;
+	}
+	if (-det > bound) {
+		return -1;
+	}
+	const double pa[6] = {ax, -ax, -ay, ay, bx, -by};
+	const double pb[6] = {by, cy, bx, cx, cy, cx};
+	double e[16], h[16];
+	int n = 0;
+	for (int k = 0; k < 6; k++) {
+		double p, r;
+		two_prod(pa[k], pb[k], &p, &r);
+		n = grow_expansion(n, e, r, h);
+		memcpy(e, h, sizeof(double) * (size_t)n);
+		n = grow_expansion(n, e, p, h);
+		memcpy(e, h, sizeof(double) * (size_t)n);
+	}
+	for (int i = n - 1; i >= 0; i--) {
+		if (e[i] > 0) {
+			return 1;
+		}
+		if (e[i] < 0) {
+			return -1;
+		}
+	}
+	return 0;
+}
+
+/* RayCrossingCounter over one ring [o, o+len): returns 0 exterior, 1 boundary, 2 interior */
+static int ring_locate_exact(double x, double y, const double *vx, const double *vy, uint64_t o, uint64_t len) {
+	int crossings = 0;
+	for (uint64_t i = 1; i < len; i++) {
+		const double x1 = vx[o + i - 1], y1 = vy[o + i - 1], x2 = vx[o + i], y2 = vy[o + i];
+		if (x1 < x && x2 < x) {
+			continue; /* strictly to the left of the point: the ray to +x cannot cross it */
+		}
+		if (x == x2 && y == y2) {
+			return 1; /* the point is a ring vertex */
+		}
+		if (y1 == y && y2 == y) {
+			const double mn = x1 < x2 ? x1 : x2, mx = x1 < x2 ? x2 : x1;
+			if (x >= mn && x <= mx) {
+				return 1; /* on a horizontal segment */
+			}
+			continue;
+		}
+		if ((y1 > y && y2 <= y) || (y2 > y && y1 <= y)) {
+			int sign = orc_orient2d_sign(x1, y1, x2, y2, x, y);
+			if (sign == 0) {
+				return 1;
+			}
+			if (y2 < y1) {
+				sign = -sign;
+			}
+			if (sign > 0) {
+				crossings++;
+			}
+		}
+	}
+	return (crossings & 1) ? 2 : 0;
+}
+
+/* location of a point relative to a polygon (rings [r0, r1) of ring_off[], ring 0 = shell): 0 exterior, 1 boundary,
+ * 2 interior. A polygon without rings (empty) has no interior: exterior. */
+ORC_API int orc_point_polygon_locate(double x, double y, const double *vx, const double *vy, const uint64_t *ring_off,
+                                     uint64_t r0, uint64_t r1) {
+	if (r0 >= r1 || x != x || y != y) {
+		return 0;
+	}
+	const int shell = ring_locate_exact(x, y, vx, vy, ring_off[r0], ring_off[r0 + 1] - ring_off[r0]);
+	if (shell != 2) {
+		return shell;
+	}
+	for (uint64_t r = r0 + 1; r < r1; r++) {
+		const int hole = ring_locate_exact(x, y, vx, vy, ring_off[r], ring_off[r + 1] - ring_off[r]);
+		if (hole == 2) {
+			return 0;
+		}
+		if (hole == 1) {
+			return 1;
+		}
+	}
+	return 2;
+}
+
+/* batch: pairs (point pi[k], polygon qi[k]); pred 0 = ST_Intersects (location != exterior), 1 = ST_Within(point,
+ * polygon) / ST_Contains(polygon, point) (location == interior). poly_off: rings of polygon q = [poly_off[q], poly_off[q+1]) */
+ORC_API void orc_point_polygon_exact(const double *px, const double *py, const uint32_t *pi, const uint32_t *qi,
+                                     uint64_t n, const double *vx, const double *vy, const uint64_t *ring_off,
+                                     const uint64_t *poly_off, int pred, uint8_t *out) {
+#pragma omp parallel for schedule(dynamic, 256)
+	for (int64_t k = 0; k < (int64_t)n; k++) {
+		const uint32_t p = pi ? pi[k] : (uint32_t)k, q = qi ? qi[k] : (uint32_t)k;
+		const int loc = orc_point_polygon_locate(px[p], py[p], vx, vy, ring_off, poly_off[q], poly_off[q + 1]);
+		out[k] = (uint8_t)(pred == 0 ? loc != 0 : loc == 2);
+	}
 }
 
 /* ST_Distance(POINT_2D, POINT_2D), spatial_functions_scalar.cpp:2189-2214 */

@@ -44,3 +44,13 @@ def RS(O):
     if r is None:
         pytest.skip("oracle/_ref/libref_scalar.so not built (no /root/reference)")
     return r
+
+
+@pytest.fixture(scope="session")
+def RDB():
+    """the reference's DuckDB-linked code (oracle/_ref/libref_duckdb.so, `make -C oracle ref_duckdb`)"""
+    from oracle import refdb
+
+    if not refdb.available():
+        pytest.skip("oracle/_ref/libref_duckdb.so not built")
+    return refdb
