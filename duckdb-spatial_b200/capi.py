@@ -74,6 +74,8 @@ SIGNATURES = {
     "sb_join_points_boxes": (i32, [vp, i32, i32, vp, vp, u64, vp, vp, vp, vp, u32, vp, vp, u64, C.POINTER(u64)]),
     "sb_join_mark_matched": (i32, [vp, i32, vp, vp, u64, u32, vp, u64, vp, u64]),
     "sb_join_unmatched_rows": (i32, [vp, i32, vp, u64, u32, vp, u64, C.POINTER(u64)]),
+    "sb_context_trim": (i32, [vp]),
+    "sb_pairs_checksum": (i32, [vp, i32, vp, vp, u64, u32, u32, C.POINTER(u64), C.POINTER(u64)]),
     "sb_join_points_polygons": (i32, [vp, i32, vp, vp, u64, vp, vp, vp, vp, u64, u64, u64, vp, vp, u64, C.POINTER(u64)]),
     "sb_generate_points": (i32, [vp, i32, u64, u64, u64, vp, vp, vp]),
     "sb_join_dwithin": (i32, [vp, i32, vp, vp, u64, vp, vp, u32, f64, vp, vp, vp, u64, C.POINTER(u64)]),

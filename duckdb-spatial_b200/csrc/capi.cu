@@ -391,8 +391,9 @@ extern "C" void sb_rtree_destroy(sb_rtree *tree) {
 	if (!tree) {
 		return;
 	}
-	cudaSetDevice(tree->device);
-	cudaFreeAsync(tree->entries, nullptr); // callers destroy a tree only after its work has completed
+	// stream-ordered on the building context's stream: ordered after the build and after every scan / export that
+	// context enqueued. Work on OTHER contexts' streams must have completed before the tree is destroyed.
+	sb_owner_free(tree->owner, tree->device, tree->entries);
 	delete tree;
 }
 extern "C" int sb_rtree_num_levels(const sb_rtree *tree) {
@@ -477,8 +478,7 @@ extern "C" void sb_flat_destroy(sb_flat *tree) {
 		return;
 	}
 	if (tree->owns && tree->buffer) {
-		cudaSetDevice(tree->device);
-		cudaFreeAsync(tree->buffer, nullptr); // callers destroy a tree only after its work has completed
+		sb_owner_free(tree->owner, tree->device, tree->buffer); // see sb_rtree_destroy
 	}
 	delete tree;
 }
@@ -508,10 +508,20 @@ extern "C" int sb_flat_attach(sb_context *ctx, void *dev_ptr, uint64_t bytes, sb
 	sb_flat *t = new sb_flat();
 	SB_CUDA(cudaMemcpyAsync(&t->h, dev_ptr, sizeof(t->h), cudaMemcpyDeviceToHost, ctx->stream));
 	SB_CUDA(cudaStreamSynchronize(ctx->stream));
-	if (t->h.magic != SB_FLAT_MAGIC ||
-	    sizeof(sb_flat_header) + (uint64_t)t->h.nodes * (sizeof(float4) + sizeof(uint32_t)) > bytes) {
+	// the invariants sbi_flat_build establishes (the probe kernels index layer_bounds[16], a 320-entry shared stack
+	// and 32-lane node loads with them): a stale or foreign buffer must fail here, not fault in a kernel
+	bool ok = t->h.magic == SB_FLAT_MAGIC && t->h.node_size >= 2 && t->h.node_size <= 32 && t->h.nlayers >= 1 &&
+	          t->h.nlayers <= 16 && t->h.nodes < (1u << 27) &&
+	          sizeof(sb_flat_header) + (uint64_t)t->h.nodes * (sizeof(float4) + sizeof(uint32_t)) <= bytes;
+	if (ok) {
+		ok = t->h.layer_bounds[0] == t->h.item_count && t->h.layer_bounds[t->h.nlayers - 1] == t->h.nodes;
+		for (uint32_t l = 1; ok && l < t->h.nlayers; l++) {
+			ok = t->h.layer_bounds[l] > t->h.layer_bounds[l - 1];
+		}
+	}
+	if (!ok) {
 		delete t;
-		sb_set_error("sb_flat_attach: not a FlatRTree buffer");
+		sb_set_error("sb_flat_attach: not a FlatRTree buffer (magic / node size / layer bounds)");
 		return SB_ERR_ARG;
 	}
 	t->device = ctx->device;
@@ -798,6 +808,10 @@ static int join_points_boxes_pipelined(sb_context *ctx, sb_predicate pred, const
 		return SB_OK;
 	};
 	uint64_t next_h2d = 0;
+	// The chunk loop runs inside a lambda: SB_CUDA / SB_TRY leave the LAMBDA on an error, and every exit then passes
+	// through the three-stream drain and the event destruction below (no copy may still read the caller's columns or
+	// write its pair arrays when the call returns, and the next call resets the arena slots those copies use).
+	auto run_chunks = [&]() -> int {
 	for (uint64_t c = 0; c < nchunks && status == SB_OK; c++) {
 		const int slot = (int)(c & 1);
 		const uint64_t islot = c % in_slots;
@@ -870,6 +884,14 @@ static int join_points_boxes_pipelined(sb_context *ctx, sb_predicate pred, const
 		SB_CUDA(cudaEventRecord(d2h_done[slot], ctx->d2h_stream));
 		SB_CUDA(cudaEventRecord(probe_done[slot], ctx->stream));
 		SB_CUDA(cudaEventRecord(in_free[islot], ctx->stream));
+	}
+	return SB_OK;
+	};
+	{
+		const int rs = run_chunks();
+		if (status == SB_OK) {
+			status = rs;
+		}
 	}
 	cudaStreamSynchronize(ctx->h2d_stream);
 	cudaStreamSynchronize(ctx->d2h_stream);
@@ -1037,6 +1059,25 @@ extern "C" int sb_join_mark_matched(sb_context *ctx, sb_mem mem, const uint32_t 
 	SB_TRY(sb_to_host(ctx, mem, probe_matched, pm, n_probe));
 	SB_TRY(sb_to_host(ctx, mem, build_matched, bm, n_build));
 	return finish(ctx, mem);
+}
+
+extern "C" int sb_pairs_checksum(sb_context *ctx, sb_mem mem, const uint32_t *pair_probe, const uint32_t *pair_build,
+                                 uint64_t count, uint32_t probe_lo, uint32_t probe_hi, uint64_t *out_count,
+                                 uint64_t *out_hash) {
+	SB_BEGIN(ctx);
+	SB_ARG(out_count != nullptr && out_hash != nullptr, "out");
+	SB_ARG(count == 0 || (pair_probe != nullptr && pair_build != nullptr), "pairs");
+	const uint32_t *dp, *db;
+	SB_TRY(sb_to_device(ctx, mem, pair_probe, count, &dp));
+	SB_TRY(sb_to_device(ctx, mem, pair_build, count, &db));
+	unsigned long long *d2 = nullptr;
+	SB_TRY(ctx->scratch_t(2, &d2));
+	SB_TRY(sbi_pairs_checksum(ctx, dp, db, count, probe_lo, probe_hi, d2));
+	uint64_t w[2];
+	SB_TRY(sbi_read_words(ctx, d2, 2, w));
+	*out_count = w[0];
+	*out_hash = w[1];
+	return SB_OK;
 }
 
 extern "C" int sb_join_unmatched_rows(sb_context *ctx, sb_mem mem, const uint8_t *matched, uint64_t n, uint32_t row_base,

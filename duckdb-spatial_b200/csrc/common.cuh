@@ -54,7 +54,8 @@ struct sb_arena {
 	};
 	std::vector<block> blocks;
 	size_t cur_block = 0, cur_off = 0, high_water = 0, used = 0;
-	cudaStream_t *stream = nullptr; // blocks come from the device's stream-ordered pool, ordered on *stream
+	cudaStream_t *stream = nullptr; // blocks come from the context's private stream-ordered pool, ordered on *stream
+	cudaMemPool_t pool = nullptr;
 	int alloc(size_t bytes, void **out);
 	// mark / rewind: give back everything allocated after the mark (same stream => safe to reuse in stream order)
 	struct mark_t {
@@ -80,6 +81,9 @@ struct sb_context {
 	int device = 0;
 	cudaStream_t stream = nullptr;
 	cudaStream_t own_stream = nullptr;
+	// private stream-ordered pool (release threshold = max): nothing this library caches shows up in, or changes the
+	// behaviour of, the host process's default pool; destroyed (memory returned) with the context
+	cudaMemPool_t pool = nullptr;
 	sb_arena arena;
 	uint64_t launches = 0;
 	bool profiling = false;
@@ -116,6 +120,14 @@ struct sb_prof_scope {
 	sb_prof_scope(sb_context *c, const char *t);
 	~sb_prof_scope();
 };
+
+// long-lived device buffers (trees): from the context's pool, on its stream
+static inline cudaError_t sb_pool_alloc(sb_context *ctx, void **out, size_t bytes) {
+	return cudaMallocFromPoolAsync(out, bytes, ctx->pool, ctx->stream);
+}
+// frees a tree buffer in stream order on its building context's stream when that context is still alive (registry in
+// context.cu); otherwise after a device synchronise
+void sb_owner_free(sb_context *owner, int device, void *ptr);
 
 void sb_trace_point(sb_context *ctx, const char *what);
 #define SB_TRACE(ctx, what)                                                                                          \

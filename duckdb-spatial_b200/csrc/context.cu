@@ -3,7 +3,13 @@
 
 #include <stdarg.h>
 
+#include <mutex>
+#include <set>
+
 static thread_local char g_err[512] = "";
+
+static std::mutex g_live_mu;
+static std::set<sb_context *> g_live; // contexts that exist: trees free on their owner's stream only while it lives
 
 void sb_set_error(const char *fmt, ...) {
 	va_list ap;
@@ -90,7 +96,7 @@ int sb_arena::alloc(size_t bytes, void **out) {
 	}
 	size_t sz = bytes > ((size_t)64 << 20) ? bytes : ((size_t)64 << 20);
 	block nb;
-	cudaError_t e = cudaMallocAsync((void **)&nb.ptr, sz, *stream);
+	cudaError_t e = cudaMallocFromPoolAsync((void **)&nb.ptr, sz, pool, *stream);
 	if (e != cudaSuccess) {
 		sb_set_error("cudaMalloc(%zu) failed: %s", sz, cudaGetErrorString(e));
 		return SB_ERR_CUDA;
@@ -113,7 +119,7 @@ void sb_arena::reset() {
 		size_t want = high_water + (high_water >> 3);
 		release(); // stream-ordered free: work already enqueued on the stream still sees the old blocks
 		block nb;
-		if (cudaMallocAsync((void **)&nb.ptr, want, *stream) == cudaSuccess) {
+		if (cudaMallocFromPoolAsync((void **)&nb.ptr, want, pool, *stream) == cudaSuccess) {
 			nb.size = want;
 			blocks.push_back(nb);
 		} else {
@@ -160,25 +166,64 @@ extern "C" int sb_context_create(int device, sb_context **out) {
 	SB_CUDA(cudaStreamCreateWithFlags(&ctx->h2d_stream, cudaStreamNonBlocking));
 	SB_CUDA(cudaStreamCreateWithFlags(&ctx->d2h_stream, cudaStreamNonBlocking));
 	ctx->arena.stream = &ctx->stream;
-	// Device buffers (scratch arena, trees) come from the stream-ordered pool and the pool keeps what is freed:
+	// Device buffers (scratch arena, trees) come from a stream-ordered pool that keeps what is freed:
 	// cudaMalloc/cudaFree of a few hundred MB per call cost milliseconds (measured: 3.5 -> 17 ms per index build
-	// depending on the allocator state), pool allocations microseconds.
+	// depending on the allocator state), pool allocations microseconds. The pool is PRIVATE to the context, so the
+	// release threshold does not leak into the host process's default pool (DuckDB, torch, ...).
 	{
-		cudaMemPool_t pool;
-		SB_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+		cudaMemPoolProps props = {};
+		props.allocType = cudaMemAllocationTypePinned;
+		props.handleTypes = cudaMemHandleTypeNone;
+		props.location.type = cudaMemLocationTypeDevice;
+		props.location.id = device;
+		SB_CUDA(cudaMemPoolCreate(&ctx->pool, &props));
 		uint64_t keep = UINT64_MAX;
-		SB_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+		SB_CUDA(cudaMemPoolSetAttribute(ctx->pool, cudaMemPoolAttrReleaseThreshold, &keep));
+		ctx->arena.pool = ctx->pool;
 	}
 	// mapped: the counters are written by a kernel (sbi_read_words), not by a copy engine
 	SB_CUDA(cudaHostAlloc((void **)&ctx->pinned_u64, 64 * sizeof(uint64_t), cudaHostAllocMapped));
 	SB_CUDA(cudaHostGetDevicePointer((void **)&ctx->pinned_u64_dev, ctx->pinned_u64, 0));
+	{
+		std::lock_guard<std::mutex> g(g_live_mu);
+		g_live.insert(ctx);
+	}
 	*out = ctx;
+	return SB_OK;
+}
+
+void sb_owner_free(sb_context *owner, int device, void *ptr) {
+	if (!ptr) {
+		return;
+	}
+	cudaSetDevice(device);
+	std::lock_guard<std::mutex> g(g_live_mu);
+	if (owner && g_live.count(owner)) {
+		// ordered after everything the owning context has enqueued so far (build, probes of that context)
+		cudaFreeAsync(ptr, owner->stream);
+	} else {
+		cudaDeviceSynchronize();
+		cudaFree(ptr);
+	}
+}
+
+extern "C" int sb_context_trim(sb_context *ctx) {
+	SB_ARG(ctx != nullptr, "ctx");
+	SB_CUDA(cudaSetDevice(ctx->device));
+	SB_CUDA(cudaStreamSynchronize(ctx->stream));
+	ctx->arena.release();
+	SB_CUDA(cudaStreamSynchronize(ctx->stream));
+	SB_CUDA(cudaMemPoolTrimTo(ctx->pool, 0));
 	return SB_OK;
 }
 
 extern "C" void sb_context_destroy(sb_context *ctx) {
 	if (!ctx) {
 		return;
+	}
+	{
+		std::lock_guard<std::mutex> g(g_live_mu);
+		g_live.erase(ctx);
 	}
 	cudaSetDevice(ctx->device);
 	cudaStreamSynchronize(ctx->stream);
@@ -192,6 +237,10 @@ extern "C" void sb_context_destroy(sb_context *ctx) {
 		cudaEventDestroy(ev);
 	}
 	ctx->arena.release();
+	cudaStreamSynchronize(ctx->stream);
+	if (ctx->pool) {
+		cudaMemPoolDestroy(ctx->pool); // memory goes back to the driver (outstanding tree buffers keep theirs until freed)
+	}
 	cudaFreeHost(ctx->pinned_u64);
 	cudaStreamDestroy(ctx->h2d_stream);
 	cudaStreamDestroy(ctx->d2h_stream);

@@ -106,6 +106,7 @@ int sbi_flat_build(sb_context *ctx, const float *box4, uint32_t n, uint32_t node
 	sb_flat *t = new sb_flat();
 	*out = t;
 	t->device = ctx->device;
+	t->owner = ctx;
 	memset(&t->h, 0, sizeof(t->h));
 	t->h.magic = SB_FLAT_MAGIC;
 	t->h.item_count = n;
@@ -125,7 +126,7 @@ int sbi_flat_build(sb_context *ctx, const float *box4, uint32_t n, uint32_t node
 	t->h.nodes = n > 0 ? (uint32_t)nodes : 0;
 	t->bytes = sizeof(sb_flat_header) + (size_t)t->h.nodes * (sizeof(float4) + sizeof(uint32_t));
 	t->bytes = (t->bytes + 255) & ~(uint64_t)255;
-	SB_CUDA(cudaMallocAsync(&t->buffer, t->bytes, ctx->stream));
+	SB_CUDA(sb_pool_alloc(ctx, &t->buffer, t->bytes));
 	t->owns = true;
 	SB_CUDA(cudaMemcpyAsync(t->buffer, &t->h, sizeof(t->h), cudaMemcpyHostToDevice, ctx->stream));
 	if (n == 0) {

@@ -36,6 +36,7 @@ static_assert(sizeof(sb_entry) == 24, "RTreeEntry must be 24 bytes");
 
 struct sb_rtree {
 	int device = 0;
+	sb_context *owner = nullptr; // building context: the entries are freed in stream order on its stream
 	uint32_t cap = 0;
 	uint64_t slice = 0;
 	int nlevels = 0;
@@ -58,6 +59,7 @@ static_assert(sizeof(sb_flat_header) == 256, "flat header is 256 bytes");
 
 struct sb_flat {
 	int device = 0;
+	sb_context *owner = nullptr; // building context: the buffer is freed in stream order on its stream
 	sb_flat_header h;
 	void *buffer = nullptr; // device
 	uint64_t bytes = 0;
@@ -135,7 +137,10 @@ int sbi_cell_partition(sb_context *ctx, const sb_flat *tree, const double *px, c
 // pip_join.cu : ST_Within(point, polygon) join, polygon-centric over the cell-sorted points
 int sbi_join_points_polygons(sb_context *ctx, const double *px, const double *py, uint64_t n_points, const double *vx,
                              const double *vy, const uint64_t *ring_off, const uint64_t *poly_off, uint64_t n_polys,
-                             uint32_t *out_point, uint32_t *out_poly, uint64_t capacity, uint64_t *count);
+                             uint32_t *out_point, uint32_t *out_poly, uint64_t capacity, uint64_t *count, int exact = 0,
+                             int pred = 1);
+int sbi_pip_boxes(sb_context *ctx, const double *vx, const double *vy, const uint64_t *ring_off, const uint64_t *poly_off,
+                  uint64_t n_polys, float *out_box4);
 
 // refine.cu
 int sbi_pack_box2d(sb_context *ctx, const double *x0, const double *y0, const double *x1, const double *y1, uint64_t n,
@@ -146,6 +151,9 @@ int sbi_refine_point_box(sb_context *ctx, int pred, const double *px, const doub
 int sbi_refine_point_polygon(sb_context *ctx, const double *px, const double *py, const double *vx, const double *vy,
                              const uint64_t *ring_off, const uint64_t *poly_off, uint32_t *pp, uint32_t *pb, uint64_t n,
                              uint64_t *d_count);
+int sbi_refine_point_polygon_exact(sb_context *ctx, int pred, const double *px, const double *py, const double *vx,
+                                   const double *vy, const uint64_t *ring_off, const uint64_t *poly_off, uint32_t *pp,
+                                   uint32_t *pb, uint64_t n, uint64_t *d_count);
 int sbi_refine_dwithin(sb_context *ctx, const double *ax, const double *ay, const double *bx, const double *by,
                        double r, uint32_t *pa, uint32_t *pb, double *out_d, uint64_t n, uint64_t *d_count);
 int sbi_distance_points(sb_context *ctx, const double *ax, const double *ay, const double *bx, const double *by,
@@ -157,6 +165,9 @@ int sbi_mark_matched(sb_context *ctx, const uint32_t *pp, const uint32_t *pb, ui
                      uint8_t *pm, uint64_t n_probe, uint8_t *bm, uint64_t n_build);
 int sbi_unmatched_rows(sb_context *ctx, const uint8_t *flags, uint64_t n, uint32_t row_base, uint32_t *out,
                        uint64_t capacity, uint64_t *count);
+
+int sbi_pairs_checksum(sb_context *ctx, const uint32_t *pp, const uint32_t *pb, uint64_t n, uint32_t lo, uint32_t hi,
+                       unsigned long long *d_out2);
 
 // read a device u64 counter back (synchronises the stream)
 // transcode.cu: GEOMETRY blobs -> POINT_2D / POLYGON_2D columns

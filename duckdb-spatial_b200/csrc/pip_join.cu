@@ -36,6 +36,7 @@
 // of the routine is false), they are dropped by the partition.
 #include "cells.cuh"
 #include "pip.cuh"
+#include "exact.cuh"
 
 #define PIP_G 32 // (the row scans below assume one warp = one row set: PIP_G == 32)
 #define PIP_NCELL (PIP_G * PIP_G)
@@ -183,8 +184,14 @@ __device__ __forceinline__ void pip_flush(uint32_t *stage, uint32_t cnt, uint32_
 	__syncwarp();
 }
 
+// EXACT = 0: the native winding routine (ST_Within(POINT_2D, POLYGON_2D)). EXACT = 1: the GEOS-route predicates on
+// GEOMETRY arguments (exact.cuh): the same index serves the ray-crossing count -- an edge wholly to the right of the
+// point's cell is crossed iff the half-open y rule holds (its orientation sign is known), the parity of W0 equals the
+// parity of the number of spanning edges, and a point can only lie ON an edge that overlaps its cell, i.e. a listed
+// edge, which gets the exact evaluation. pred: SB_PRED_INTERSECTS (location != exterior) or SB_PRED_WITHIN (interior).
+template <int EXACT>
 __global__ void __launch_bounds__(PIP_THREADS, 3)
-    k_pip_join(const pip_poly *__restrict__ polys, uint32_t n_polys, const double *__restrict__ gvx,
+    k_pip_join(int pred, const pip_poly *__restrict__ polys, uint32_t n_polys, const double *__restrict__ gvx,
                const double *__restrict__ gvy, const uint64_t *__restrict__ ring_off, const uint64_t *__restrict__ poly_off,
                const bp_grid *__restrict__ gp, const uint2 *__restrict__ rec, const double2 *__restrict__ xy,
                const uint32_t *__restrict__ cell_off, uint32_t *__restrict__ ticket, uint32_t *__restrict__ out_point,
@@ -236,7 +243,7 @@ __global__ void __launch_bounds__(PIP_THREADS, 3)
 			for (uint32_t e = tid; e < ne; e += PIP_THREADS) {
 				const double x1 = S.vx[e], y1 = S.vy[e], x2 = S.vx[e + 1], y2 = S.vy[e + 1];
 				uchar4 rg = make_uchar4(1, 0, 0, 0); // first row > last row: the edge is in no list (zero length)
-				if (!(x1 == x2 && y1 == y2)) {
+				if (EXACT || !(x1 == x2 && y1 == y2)) { // (exact mode: a zero-length edge can still carry the point)
 					const double exmin = x1 < x2 ? x1 : x2, exmax = x1 < x2 ? x2 : x1;
 					const double eymin = y1 < y2 ? y1 : y2, eymax = y1 < y2 ? y2 : y1;
 					const double m = fmax(__dmul_ru(exmax - exmin, 0x1p-40), 0x1p-500);
@@ -363,7 +370,29 @@ __global__ void __launch_bounds__(PIP_THREADS, 3)
 					const double x = q.x, y = q.y;
 					const float4 pb = make_float4(sb_f64_to_f32_down(x), sb_f64_to_f32_down(y), sb_f64_to_f32_up(x), sb_f64_to_f32_up(y));
 					if (sb_box_intersects(pb, P.fbox)) {
-						if (indexed) {
+						if (indexed && EXACT) {
+							const int row = pip_cell(y, P.miny, fsy);
+							const int c = row * PIP_G + pip_cell(x, P.minx, fsx);
+							int cr = S.w0[c]; // parity of the signed sum == parity of the number of spanning edges
+							const uint16_t *rl = S.rowlist + S.rowoff[row];
+							const uint32_t np = S.npre[c];
+							for (uint32_t k = 0; k < np; k++) {
+								const uint32_t e = rl[k];
+								const double y1 = S.vy[e], y2 = S.vy[e + 1];
+								cr += ((y1 > y && y2 <= y) || (y2 > y && y1 <= y)) ? 1 : 0;
+							}
+							bool on_edge = false;
+							const uint32_t le = S.off[c + 1];
+							for (uint32_t k = S.off[c]; k < le && !on_edge; k++) {
+								const uint32_t e = S.list[k];
+								on_edge = sb_geos_edge(x, y, S.vx[e], S.vy[e], S.vx[e + 1], S.vy[e + 1], cr);
+							}
+							const int loc = on_edge ? 1 : ((cr & 1) ? 2 : 0);
+							hit = pred == SB_PRED_INTERSECTS ? loc != 0 : loc == 2;
+						} else if (EXACT) {
+							const int loc = sb_point_polygon_locate(x, y, gvx, gvy, ring_off, r0, poly_off[p + 1]);
+							hit = pred == SB_PRED_INTERSECTS ? loc != 0 : loc == 2;
+						} else if (indexed) {
 							const int row = pip_cell(y, P.miny, fsy);
 							const int c = row * PIP_G + pip_cell(x, P.minx, fsx);
 							int wn = S.w0[c];
@@ -423,7 +452,8 @@ __global__ void __launch_bounds__(PIP_THREADS, 3)
 
 int sbi_join_points_polygons(sb_context *ctx, const double *px, const double *py, uint64_t n_points, const double *vx,
                              const double *vy, const uint64_t *ring_off, const uint64_t *poly_off, uint64_t n_polys,
-                             uint32_t *out_point, uint32_t *out_poly, uint64_t capacity, uint64_t *count) {
+                             uint32_t *out_point, uint32_t *out_poly, uint64_t capacity, uint64_t *count, int exact,
+                             int pred) {
 	*count = 0;
 	if (n_points == 0 || n_polys == 0) {
 		return SB_OK;
@@ -471,7 +501,8 @@ int sbi_join_points_polygons(sb_context *ctx, const double *px, const double *py
 	if (part.n_units == 0) {
 		return SB_OK;
 	}
-	SB_SMEM_OPTIN(ctx, k_pip_join, sizeof(pip_smem));
+	SB_SMEM_OPTIN(ctx, k_pip_join<0>, sizeof(pip_smem));
+	SB_SMEM_OPTIN(ctx, k_pip_join<1>, sizeof(pip_smem));
 	{
 		sb_prof_scope ps(ctx, "pip_gather");
 		k_pip_gather<<<sb_grid(BP_UNIT_TILES * part.n_units, 1, 4), 512, 0, ctx->stream>>>(
@@ -482,9 +513,15 @@ int sbi_join_points_polygons(sb_context *ctx, const double *px, const double *py
 	{
 		sb_prof_scope ps(ctx, "pip_join");
 		const unsigned grid = (unsigned)(n_polys < 3 * SB_NUM_SMS ? n_polys : 3 * SB_NUM_SMS);
-		k_pip_join<<<grid, PIP_THREADS, sizeof(pip_smem), ctx->stream>>>(
-		    d_polys, (uint32_t)n_polys, vx, vy, ring_off, poly_off, static_cast<const bp_grid *>(part.grid),
-		    static_cast<const uint2 *>(part.rec), d_xy, part.cell_off, d_ticket, out_point, out_poly, capacity, d_counter);
+		if (exact) {
+			k_pip_join<1><<<grid, PIP_THREADS, sizeof(pip_smem), ctx->stream>>>(
+			    pred, d_polys, (uint32_t)n_polys, vx, vy, ring_off, poly_off, static_cast<const bp_grid *>(part.grid),
+			    static_cast<const uint2 *>(part.rec), d_xy, part.cell_off, d_ticket, out_point, out_poly, capacity, d_counter);
+		} else {
+			k_pip_join<0><<<grid, PIP_THREADS, sizeof(pip_smem), ctx->stream>>>(
+			    pred, d_polys, (uint32_t)n_polys, vx, vy, ring_off, poly_off, static_cast<const bp_grid *>(part.grid),
+			    static_cast<const uint2 *>(part.rec), d_xy, part.cell_off, d_ticket, out_point, out_poly, capacity, d_counter);
+		}
 		SB_LAUNCH_CHECK(ctx);
 	}
 	SB_TRY(sbi_read_u64(ctx, reinterpret_cast<const uint64_t *>(d_counter), count));

@@ -232,6 +232,49 @@ int sbi_mark_matched(sb_context *ctx, const uint32_t *pp, const uint32_t *pb, ui
 	return SB_OK;
 }
 
+// Order-independent checksum of a pair list restricted to probe ids in [lo, hi): count and the wrapping 64-bit sum of
+// mix(probe, build). Used to compare a join result of any size with a reference pair set without moving or sorting
+// it (bench.py's in-run parity check, tests). mix() is restated in oracle/ref_harness.cpp and tests.
+__device__ __forceinline__ unsigned long long sb_pair_mix(uint32_t p, uint32_t b) {
+	unsigned long long k = (unsigned long long)p * 2654435761ull + (unsigned long long)b * 2246822519ull;
+	k ^= k >> 29;
+	k *= 0xBF58476D1CE4E5B9ull;
+	k ^= k >> 32;
+	return k;
+}
+__global__ void __launch_bounds__(256) k_pairs_checksum(const uint32_t *__restrict__ pp, const uint32_t *__restrict__ pb,
+                                                        uint64_t n, uint32_t lo, uint32_t hi,
+                                                        unsigned long long *__restrict__ out2) {
+	unsigned long long cnt = 0, sum = 0;
+	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+		const uint32_t p = pp[i];
+		if (p >= lo && p < hi) {
+			cnt++;
+			sum += sb_pair_mix(p, pb[i]);
+		}
+	}
+#pragma unroll
+	for (int s = 16; s > 0; s >>= 1) {
+		cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, s);
+		sum += __shfl_xor_sync(0xFFFFFFFFu, sum, s);
+	}
+	if (sb_lane() == 0 && cnt) {
+		atomicAdd(out2, cnt);
+		atomicAdd(out2 + 1, sum);
+	}
+}
+
+int sbi_pairs_checksum(sb_context *ctx, const uint32_t *pp, const uint32_t *pb, uint64_t n, uint32_t lo, uint32_t hi,
+                       unsigned long long *d_out2) {
+	SB_TRY(sbi_zero(ctx, d_out2, 2 * sizeof(unsigned long long)));
+	if (n) {
+		k_pairs_checksum<<<sb_grid(n, 256 * 8, 8), 256, 0, ctx->stream>>>(pp, pb, n, lo, hi, d_out2);
+		SB_LAUNCH_CHECK(ctx);
+	}
+	return SB_OK;
+}
+
 #define UM_TILE 4096
 __global__ void __launch_bounds__(256) k_unmatched_count(const uint8_t *__restrict__ flags, uint64_t n,
                                                          uint32_t *__restrict__ tile_cnt) {

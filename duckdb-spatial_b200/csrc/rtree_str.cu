@@ -234,7 +234,8 @@ int sbi_rtree_build_str(sb_context *ctx, const float *box4, const int64_t *row_i
 	}
 	t->nlevels = nl;
 	t->total = total;
-	SB_CUDA(cudaMallocAsync((void **)&t->entries, total * sizeof(sb_entry), ctx->stream));
+	SB_CUDA(sb_pool_alloc(ctx, (void **)&t->entries, total * sizeof(sb_entry)));
+	t->owner = ctx;
 
 	const float4 *box = reinterpret_cast<const float4 *>(box4);
 	const unsigned block = ((cap + 31) / 32) * 32;

@@ -337,6 +337,15 @@ class Context:
                                                _ptr(probe_matched), n_probe, _ptr(build_matched), n_build))
         return probe_matched, build_matched
 
+    def pairs_checksum(self, pair_probe, pair_build, probe_lo=0, probe_hi=0xFFFFFFFF, count=None):
+        """(count, hash) of the pairs whose probe id lies in [probe_lo, probe_hi): order-independent 64-bit checksum
+        (see include/spatial_b200.h); compares a join result with a reference pair set without sorting it."""
+        n = len(pair_probe) if count is None else int(count)
+        c, h = C.c_uint64(0), C.c_uint64(0)
+        capi.check(self.L.sb_pairs_checksum(self.h, self._mem(pair_probe, pair_build), _ptr(pair_probe), _ptr(pair_build),
+                                            n, probe_lo, probe_hi, C.byref(c), C.byref(h)))
+        return c.value, h.value
+
     def join_unmatched_rows(self, matched, row_base=0):
         """ascending row ids (row_base + position) whose flag is 0."""
         n = len(matched)

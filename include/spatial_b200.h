@@ -63,6 +63,9 @@ SB_API void sb_context_destroy(sb_context *ctx);
  * legacy default stream has to be named as cudaStreamLegacy ((cudaStream_t)0x1) */
 SB_API int sb_context_set_stream(sb_context *ctx, void *cuda_stream);
 SB_API int sb_context_sync(sb_context *ctx);
+/* give the context's cached device memory (scratch arena, freed trees) back to the driver. The context keeps a PRIVATE
+ * stream-ordered memory pool, so nothing it caches changes the host process's default pool; sb_context_destroy trims too. */
+SB_API int sb_context_trim(sb_context *ctx);
 /* tuning / test knobs. "probe_path": 0 = auto, 1 = per-probe tree walk only, 2 = bucketed bulk probe only
  * (both produce the same pair set; the parity tests run every join through both). "pipe_chunk": probe rows per
  * chunk of the host-pointer join pipeline (default 8 Mi; calls with >= 2 chunks overlap H2D / probe / D2H).
@@ -303,6 +306,14 @@ SB_API int sb_join_mark_matched(sb_context *ctx, sb_mem mem, const uint32_t *pai
  * (PhysicalSpatialJoin::GetData :1022-1068, NULL-padded on the probe side). SB_ERR_CAPACITY when *count > capacity. */
 SB_API int sb_join_unmatched_rows(sb_context *ctx, sb_mem mem, const uint8_t *matched, uint64_t n, uint32_t row_base,
                                   uint32_t *out_rows, uint64_t capacity, uint64_t *count);
+/* Order-independent checksum of a pair list: *out_count = pairs whose probe id lies in [probe_lo, probe_hi),
+ * *out_hash = wrapping 64-bit sum over those pairs of mix(probe, build), mix(p, b): k = p * 2654435761 + b * 2246822519;
+ * k ^= k >> 29; k *= 0xBF58476D1CE4E5B9; k ^= k >> 32. Compares a join result of any size with the pair set of the
+ * reference operator (spatial_join_physical.cpp:781-912 emits the same (probe row, build row) pairs) without
+ * sorting or moving it; harness utility, no reference counterpart. */
+SB_API int sb_pairs_checksum(sb_context *ctx, sb_mem mem, const uint32_t *pair_probe, const uint32_t *pair_build,
+                             uint64_t count, uint32_t probe_lo, uint32_t probe_hi, uint64_t *out_count,
+                             uint64_t *out_hash);
 
 /* ---- probe-side operator glue: PhysicalSpatialJoin's life cycle for a STREAMING probe side ------------------
  * DuckDB hands the operator one <= 2048-row probe chunk per ExecuteInternal call (spatial_join_physical.cpp:695-945);

@@ -152,6 +152,7 @@ def ref():
         R.ref_flat_lookup.restype = C.c_uint64
         R.ref_flat_lookup.argtypes = [C.c_void_p, f32p, u32p, C.c_uint64]
         R.ref_flat_join_count.restype = C.c_uint64
+        R.ref_flat_join_hash.restype = C.c_uint64
         R.ref_cached_bounds.restype = C.c_int
         _REF = R
     return _REF
@@ -506,6 +507,18 @@ def join_points_boxes(px, py, bminx, bminy, bmaxx, bmaxy, pred=0, threads=0, wan
     ob = np.empty(n, np.uint32)
     lib().orc_join_points_boxes(*args, _p(op, u32p), _p(ob, u32p), C.c_uint64(n), C.byref(cand))
     return np.stack([op, ob], 1), cand.value
+
+
+def pair_checksum(pairs_probe, pairs_build):
+    """(count, hash): the order-independent checksum of include/spatial_b200.h's sb_pairs_checksum, in numpy"""
+    p = np.asarray(pairs_probe).astype(np.uint64)
+    b = np.asarray(pairs_build).astype(np.uint64)
+    with np.errstate(over="ignore"):
+        k = p * np.uint64(2654435761) + b * np.uint64(2246822519)
+        k ^= k >> np.uint64(29)
+        k *= np.uint64(0xBF58476D1CE4E5B9)
+        k ^= k >> np.uint64(32)
+        return len(p), int(k.sum(dtype=np.uint64))
 
 
 def pip_native(x, y, vx, vy, ring_off, r0, r1):

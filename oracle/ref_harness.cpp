@@ -197,16 +197,23 @@ __attribute__((visibility("default"))) uint64_t ref_flat_lookup(void *h, const f
 // chunk-parallel, spatial_join_physical.hpp:39-41), with the exact stand-in predicate for a POINT against an
 // ST_MakeEnvelope polygon (GEOS is an un-vendored dependency): pred 0 = intersects (closed), 1 = within (strict).
 // Counts only (the timed CPU baseline); returns refined pairs, *cand = float-box candidates.
-__attribute__((visibility("default"))) uint64_t ref_flat_join_count(void *h, const double *px, const double *py,
-                                                                     uint64_t np, const double *bminx,
-                                                                     const double *bminy, const double *bmaxx,
-                                                                     const double *bmaxy, int pred, int threads,
-                                                                     uint64_t *cand_out) {
+// ref_flat_join_hash additionally returns the order-independent checksum of the pair set that the product's
+// sb_pairs_checksum computes (wrapping sum of mix(probe_base + i, build)); see include/spatial_b200.h.
+static inline uint64_t pair_mix(uint32_t p, uint32_t b) {
+	uint64_t k = (uint64_t)p * 2654435761ull + (uint64_t)b * 2246822519ull;
+	k ^= k >> 29;
+	k *= 0xBF58476D1CE4E5B9ull;
+	k ^= k >> 32;
+	return k;
+}
+static uint64_t flat_join_impl(void *h, const double *px, const double *py, uint64_t np, const double *bminx,
+                               const double *bminy, const double *bmaxx, const double *bmaxy, int pred, int threads,
+                               uint64_t *cand_out, uint32_t probe_base, uint64_t *hash_out) {
 	auto t = static_cast<FlatRTree *>(h);
-	uint64_t total = 0, cand = 0;
+	uint64_t total = 0, cand = 0, hsum = 0;
 	const uint64_t chunk = STANDARD_VECTOR_SIZE;
 	const int64_t nchunks = (int64_t)((np + chunk - 1) / chunk);
-#pragma omp parallel num_threads(threads) reduction(+ : total, cand)
+#pragma omp parallel num_threads(threads) reduction(+ : total, cand, hsum)
 	{
 		RawScan raw;
 		auto &st = *reinterpret_cast<FlatRTreeScanState *>(raw.mem);
@@ -225,6 +232,9 @@ __attribute__((visibility("default"))) uint64_t ref_flat_join_count(void *h, con
 					const bool ok = pred == 0 ? (bminx[b] <= px[i] && px[i] <= bmaxx[b] && bminy[b] <= py[i] && py[i] <= bmaxy[b])
 					                          : (bminx[b] < px[i] && px[i] < bmaxx[b] && bminy[b] < py[i] && py[i] < bmaxy[b]);
 					total += ok;
+					if (ok && hash_out) {
+						hsum += pair_mix(probe_base + (uint32_t)i, b);
+					}
 				}
 			}
 		}
@@ -233,7 +243,24 @@ __attribute__((visibility("default"))) uint64_t ref_flat_join_count(void *h, con
 	if (cand_out) {
 		*cand_out = cand;
 	}
+	if (hash_out) {
+		*hash_out = hsum;
+	}
 	return total;
+}
+__attribute__((visibility("default"))) uint64_t ref_flat_join_count(void *h, const double *px, const double *py,
+                                                                     uint64_t np, const double *bminx,
+                                                                     const double *bminy, const double *bmaxx,
+                                                                     const double *bmaxy, int pred, int threads,
+                                                                     uint64_t *cand_out) {
+	return flat_join_impl(h, px, py, np, bminx, bminy, bmaxx, bmaxy, pred, threads, cand_out, 0, nullptr);
+}
+__attribute__((visibility("default"))) uint64_t ref_flat_join_hash(void *h, const double *px, const double *py,
+                                                                    uint64_t np, const double *bminx,
+                                                                    const double *bminy, const double *bmaxx,
+                                                                    const double *bmaxy, int pred, int threads,
+                                                                    uint32_t probe_base, uint64_t *hash_out) {
+	return flat_join_impl(h, px, py, np, bminx, bminy, bmaxx, bmaxy, pred, threads, nullptr, probe_base, hash_out);
 }
 
 // ST_Extent(WKB_BLOB): ST_Extent::ExecuteWKB, spatial_functions_scalar.cpp:2576-2629 (reader flags as set there).

@@ -113,7 +113,7 @@ def test_gpu_flat_tree_vs_reference_arrays(ctx, sb):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("path", [1, 2])
+@pytest.mark.parametrize("path", [1, 2, 3])
 def test_gpu_join_counts_vs_reference(ctx, sb, path):
     b2d = G["flat_box2d"]
     cols = [np.ascontiguousarray(b2d[:, k]) for k in range(4)]
