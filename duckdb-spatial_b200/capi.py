@@ -67,6 +67,7 @@ SIGNATURES = {
     "sb_flat_probe_points": (i32, [vp, vp, i32, i32, vp, vp, u64, u32, vp, vp, vp, u64, C.POINTER(u64)]),
     "sb_refine_point_box": (i32, [vp, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, C.POINTER(u64)]),
     "sb_refine_point_polygon": (i32, [vp, i32, vp, vp, vp, vp, vp, vp, u64, u64, u64, u64, vp, vp, C.POINTER(u64)]),
+    "sb_refine_point_polygon_exact": (i32, [vp, i32, i32, vp, vp, vp, vp, vp, vp, u64, u64, u64, u64, vp, vp, C.POINTER(u64)]),
     "sb_refine_dwithin": (i32, [vp, i32, vp, vp, vp, vp, f64, vp, vp, vp, C.POINTER(u64)]),
     "sb_distance_points": (i32, [vp, i32, vp, vp, vp, vp, u64, vp]),
     "sb_intersects_box2d": (i32, [vp, i32] + [vp] * 8 + [u32, vp, vp, u64, vp]),
@@ -74,9 +75,12 @@ SIGNATURES = {
     "sb_join_points_boxes": (i32, [vp, i32, i32, vp, vp, u64, vp, vp, vp, vp, u32, vp, vp, u64, C.POINTER(u64)]),
     "sb_join_mark_matched": (i32, [vp, i32, vp, vp, u64, u32, vp, u64, vp, u64]),
     "sb_join_unmatched_rows": (i32, [vp, i32, vp, u64, u32, vp, u64, C.POINTER(u64)]),
+    "sb_rtree_build_from_blobs": (i32, [vp, i32, vp, vp, u64, vp, u32, C.POINTER(vp), C.POINTER(u64), vp]),
+    "sb_rtree_dump": (i32, [vp, vp, i32, vp, vp, vp, u64, C.POINTER(u64)]),
     "sb_context_trim": (i32, [vp]),
     "sb_pairs_checksum": (i32, [vp, i32, vp, vp, u64, u32, u32, C.POINTER(u64), C.POINTER(u64)]),
     "sb_join_points_polygons": (i32, [vp, i32, vp, vp, u64, vp, vp, vp, vp, u64, u64, u64, vp, vp, u64, C.POINTER(u64)]),
+    "sb_join_points_polygons_exact": (i32, [vp, i32, i32, vp, vp, u64, vp, vp, vp, vp, u64, u64, u64, vp, vp, u64, C.POINTER(u64)]),
     "sb_generate_points": (i32, [vp, i32, u64, u64, u64, vp, vp, vp]),
     "sb_join_dwithin": (i32, [vp, i32, vp, vp, u64, vp, vp, u32, f64, vp, vp, vp, u64, C.POINTER(u64)]),
 }

@@ -387,6 +387,67 @@ extern "C" int sb_rtree_build_str(sb_context *ctx, sb_mem mem, const float *box4
 	return finish(ctx, mem);
 }
 
+extern "C" int sb_rtree_build_from_blobs(sb_context *ctx, sb_mem mem, const uint8_t *data, const uint64_t *offsets,
+                                         uint64_t n, const int64_t *row_ids, uint32_t max_node_capacity, sb_rtree **out,
+                                         uint64_t *indexed_rows, int32_t *row_status) {
+	SB_BEGIN(ctx);
+	SB_ARG(out != nullptr, "out");
+	*out = nullptr;
+	if (indexed_rows) {
+		*indexed_rows = 0;
+	}
+	SB_ARG(n == 0 || (data != nullptr && offsets != nullptr), "data/offsets");
+	uint64_t total = 0;
+	if (n) {
+		if (mem == SB_HOST) {
+			total = offsets[n];
+		} else {
+			SB_CUDA(cudaMemcpyAsync(&total, offsets + n, sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+			SB_CUDA(cudaStreamSynchronize(ctx->stream));
+		}
+	}
+	const uint8_t *d_data;
+	const uint64_t *d_off;
+	const int64_t *d_rows;
+	SB_TRY(sb_to_device(ctx, mem, data, total, &d_data));
+	SB_TRY(sb_to_device(ctx, mem, offsets, n + 1, &d_off));
+	SB_TRY(sb_to_device(ctx, mem, row_ids, n, &d_rows));
+	float *d_box = nullptr, *d_sbox = nullptr;
+	int64_t *d_srows = nullptr;
+	uint8_t *d_valid = nullptr;
+	int32_t *d_status = nullptr;
+	int *d_bad = nullptr;
+	const uint64_t m = n ? n : 1;
+	SB_TRY(ctx->scratch_t(4 * m, &d_box));
+	SB_TRY(ctx->scratch_t(4 * m, &d_sbox));
+	SB_TRY(ctx->scratch_t(m, &d_srows));
+	SB_TRY(ctx->scratch_t(m, &d_valid));
+	SB_TRY(ctx->scratch_t(1, &d_bad));
+	SB_TRY(sbi_zero(ctx, d_bad, sizeof(int)));
+	SB_TRY(sb_out_buffer(ctx, mem, row_status, n, &d_status));
+	uint64_t kept = 0;
+	if (n) {
+		// cached bbox per row (geometry_type.hpp:102-148); rows without one are filtered out like the planner's
+		// bounds filter does (rtree_index_create_logical.cpp:42-72), malformed rows are reported in row_status
+		SB_TRY(sbi_blob_bounds(ctx, 0, d_data, d_off, n, d_box, nullptr, d_valid, d_status, d_bad));
+		SB_TRY(sbi_select_valid(ctx, d_valid, n, d_box, d_rows, d_sbox, d_srows, &kept));
+	}
+	SB_TRY(sb_to_host(ctx, mem, row_status, d_status, n));
+	sb_rtree *t = nullptr;
+	int s = sbi_rtree_build_str(ctx, d_sbox, d_srows, kept, max_node_capacity, &t);
+	if (s != SB_OK) {
+		if (t) {
+			sb_rtree_destroy(t);
+		}
+		return s;
+	}
+	*out = t;
+	if (indexed_rows) {
+		*indexed_rows = kept;
+	}
+	return finish(ctx, mem);
+}
+
 extern "C" void sb_rtree_destroy(sb_rtree *tree) {
 	if (!tree) {
 		return;
@@ -412,6 +473,35 @@ extern "C" int sb_rtree_export_level(sb_context *ctx, const sb_rtree *tree, int 
 	SB_CUDA(cudaSetDevice(ctx->device));
 	SB_CUDA(cudaMemcpyAsync(out_entries, tree->entries + tree->offsets[level], tree->counts[level] * sizeof(sb_entry),
 	                        mem == SB_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, ctx->stream));
+	return finish(ctx, mem);
+}
+
+extern "C" int sb_rtree_dump(sb_context *ctx, const sb_rtree *tree, sb_mem mem, int32_t *out_level, float *out_box4,
+                             int64_t *out_row_id, uint64_t capacity, uint64_t *count) {
+	SB_BEGIN(ctx);
+	SB_ARG(tree != nullptr && count != nullptr, "tree/count");
+	uint64_t total = 0;
+	for (int l = 0; l + 1 < tree->nlevels; l++) {
+		total += tree->counts[l];
+	}
+	*count = total;
+	if (total > capacity || out_level == nullptr) {
+		if (out_level == nullptr) {
+			return SB_OK; // size query
+		}
+		sb_set_error("rtree dump: %llu rows, capacity %llu", (unsigned long long)total, (unsigned long long)capacity);
+		return SB_ERR_CAPACITY;
+	}
+	int32_t *dl;
+	float *db;
+	int64_t *dr;
+	SB_TRY(sb_out_buffer(ctx, mem, out_level, total, &dl));
+	SB_TRY(sb_out_buffer(ctx, mem, out_box4, 4 * total, &db));
+	SB_TRY(sb_out_buffer(ctx, mem, out_row_id, total, &dr));
+	SB_TRY(sbi_rtree_dump(ctx, tree, dl, db, dr, total, count));
+	SB_TRY(sb_to_host(ctx, mem, out_level, dl, total));
+	SB_TRY(sb_to_host(ctx, mem, out_box4, db, 4 * total));
+	SB_TRY(sb_to_host(ctx, mem, out_row_id, dr, total));
 	return finish(ctx, mem);
 }
 
@@ -600,11 +690,11 @@ extern "C" int sb_refine_point_box(sb_context *ctx, sb_mem mem, sb_predicate pre
 	                            count);
 }
 
-extern "C" int sb_refine_point_polygon(sb_context *ctx, sb_mem mem, const double *px, const double *py,
-                                       const double *vx, const double *vy, const uint64_t *ring_vert_off,
-                                       const uint64_t *poly_ring_off, uint64_t n_polys, uint64_t n_rings,
-                                       uint64_t n_verts, uint64_t n_points, uint32_t *pair_probe, uint32_t *pair_build,
-                                       uint64_t *count) {
+// exact < 0: the native winding routine; otherwise the GEOS-route predicate `exact` (sb_predicate)
+static int refine_point_polygon(sb_context *ctx, sb_mem mem, int exact, const double *px, const double *py,
+                                const double *vx, const double *vy, const uint64_t *ring_vert_off,
+                                const uint64_t *poly_ring_off, uint64_t n_polys, uint64_t n_rings, uint64_t n_verts,
+                                uint64_t n_points, uint32_t *pair_probe, uint32_t *pair_build, uint64_t *count) {
 	SB_BEGIN(ctx);
 	SB_ARG(count != nullptr, "count");
 	const uint64_t n = *count;
@@ -623,10 +713,33 @@ extern "C" int sb_refine_point_polygon(sb_context *ctx, sb_mem mem, const double
 		SB_CUDA(cudaMemcpyAsync(dpp, pair_probe, n * 4, cudaMemcpyHostToDevice, ctx->stream));
 		SB_CUDA(cudaMemcpyAsync(dpb, pair_build, n * 4, cudaMemcpyHostToDevice, ctx->stream));
 	}
-	SB_TRY(sbi_refine_point_polygon(ctx, dpx, dpy, dvx, dvy, dro, dpo, dpp, dpb, n, count));
+	if (exact < 0) {
+		SB_TRY(sbi_refine_point_polygon(ctx, dpx, dpy, dvx, dvy, dro, dpo, dpp, dpb, n, count));
+	} else {
+		SB_TRY(sbi_refine_point_polygon_exact(ctx, exact, dpx, dpy, dvx, dvy, dro, dpo, dpp, dpb, n, count));
+	}
 	SB_TRY(sb_to_host(ctx, mem, pair_probe, dpp, *count));
 	SB_TRY(sb_to_host(ctx, mem, pair_build, dpb, *count));
 	return finish(ctx, mem);
+}
+
+extern "C" int sb_refine_point_polygon(sb_context *ctx, sb_mem mem, const double *px, const double *py,
+                                       const double *vx, const double *vy, const uint64_t *ring_vert_off,
+                                       const uint64_t *poly_ring_off, uint64_t n_polys, uint64_t n_rings,
+                                       uint64_t n_verts, uint64_t n_points, uint32_t *pair_probe, uint32_t *pair_build,
+                                       uint64_t *count) {
+	return refine_point_polygon(ctx, mem, -1, px, py, vx, vy, ring_vert_off, poly_ring_off, n_polys, n_rings, n_verts,
+	                            n_points, pair_probe, pair_build, count);
+}
+
+extern "C" int sb_refine_point_polygon_exact(sb_context *ctx, sb_mem mem, sb_predicate pred, const double *px,
+                                             const double *py, const double *vx, const double *vy,
+                                             const uint64_t *ring_vert_off, const uint64_t *poly_ring_off,
+                                             uint64_t n_polys, uint64_t n_rings, uint64_t n_verts, uint64_t n_points,
+                                             uint32_t *pair_probe, uint32_t *pair_build, uint64_t *count) {
+	SB_ARG(pred == SB_PRED_INTERSECTS || pred == SB_PRED_WITHIN, "pred");
+	return refine_point_polygon(ctx, mem, (int)pred, px, py, vx, vy, ring_vert_off, poly_ring_off, n_polys, n_rings,
+	                            n_verts, n_points, pair_probe, pair_build, count);
 }
 
 extern "C" int sb_refine_dwithin(sb_context *ctx, sb_mem mem, const double *ax, const double *ay, const double *bx,
@@ -1102,10 +1215,10 @@ extern "C" int sb_join_unmatched_rows(sb_context *ctx, sb_mem mem, const uint8_t
 int sbi_pip_boxes(sb_context *ctx, const double *vx, const double *vy, const uint64_t *ring_off, const uint64_t *poly_off,
                   uint64_t n_polys, float *out_box4);
 
-extern "C" int sb_join_points_polygons(sb_context *ctx, sb_mem mem, const double *px, const double *py, uint64_t n_points,
-                                       const double *vx, const double *vy, const uint64_t *ring_vert_off,
-                                       const uint64_t *poly_ring_off, uint64_t n_polys, uint64_t n_rings, uint64_t n_verts,
-                                       uint32_t *out_point, uint32_t *out_poly, uint64_t capacity, uint64_t *count) {
+static int join_points_polygons(sb_context *ctx, sb_mem mem, int exact, const double *px, const double *py,
+                                uint64_t n_points, const double *vx, const double *vy, const uint64_t *ring_vert_off,
+                                const uint64_t *poly_ring_off, uint64_t n_polys, uint64_t n_rings, uint64_t n_verts,
+                                uint32_t *out_point, uint32_t *out_poly, uint64_t capacity, uint64_t *count) {
 	SB_BEGIN(ctx);
 	SB_ARG(count != nullptr, "count");
 	*count = 0;
@@ -1127,7 +1240,8 @@ extern "C" int sb_join_points_polygons(sb_context *ctx, sb_mem mem, const double
 	// polygon-centric kernel when every polygon sees many probes (option "pip_path": 1 = candidate list, 2 = polygon-centric)
 	const bool centric = ctx->pip_path == 2 || (ctx->pip_path == 0 && n_points >= (1u << 17) && n_points / n_polys >= 32);
 	if (centric) {
-		s = sbi_join_points_polygons(ctx, dpx, dpy, n_points, dvx, dvy, dro, dpo, n_polys, dop, dob, capacity, count);
+		s = sbi_join_points_polygons(ctx, dpx, dpy, n_points, dvx, dvy, dro, dpo, n_polys, dop, dob, capacity, count,
+		                             exact >= 0, exact >= 0 ? exact : (int)SB_PRED_WITHIN);
 	} else {
 		float *fbox = nullptr;
 		SB_TRY(ctx->scratch_t(4 * n_polys, &fbox));
@@ -1143,8 +1257,10 @@ extern "C" int sb_join_points_polygons(sb_context *ctx, sb_mem mem, const double
 			s = sbi_flat_probe(ctx, tree, a, dop, dob, capacity, &cand);
 			*count = cand;
 		}
-		if (s == SB_OK) {
+		if (s == SB_OK && exact < 0) {
 			s = sbi_refine_point_polygon(ctx, dpx, dpy, dvx, dvy, dro, dpo, dop, dob, cand, count);
+		} else if (s == SB_OK) {
+			s = sbi_refine_point_polygon_exact(ctx, exact, dpx, dpy, dvx, dvy, dro, dpo, dop, dob, cand, count);
 		}
 		if (tree) {
 			sb_flat_destroy(tree);
@@ -1156,4 +1272,22 @@ extern "C" int sb_join_points_polygons(sb_context *ctx, sb_mem mem, const double
 	SB_TRY(sb_to_host(ctx, mem, out_point, dop, *count));
 	SB_TRY(sb_to_host(ctx, mem, out_poly, dob, *count));
 	return finish(ctx, mem);
+}
+
+extern "C" int sb_join_points_polygons(sb_context *ctx, sb_mem mem, const double *px, const double *py, uint64_t n_points,
+                                       const double *vx, const double *vy, const uint64_t *ring_vert_off,
+                                       const uint64_t *poly_ring_off, uint64_t n_polys, uint64_t n_rings, uint64_t n_verts,
+                                       uint32_t *out_point, uint32_t *out_poly, uint64_t capacity, uint64_t *count) {
+	return join_points_polygons(ctx, mem, -1, px, py, n_points, vx, vy, ring_vert_off, poly_ring_off, n_polys, n_rings,
+	                            n_verts, out_point, out_poly, capacity, count);
+}
+
+extern "C" int sb_join_points_polygons_exact(sb_context *ctx, sb_mem mem, sb_predicate pred, const double *px,
+                                             const double *py, uint64_t n_points, const double *vx, const double *vy,
+                                             const uint64_t *ring_vert_off, const uint64_t *poly_ring_off,
+                                             uint64_t n_polys, uint64_t n_rings, uint64_t n_verts, uint32_t *out_point,
+                                             uint32_t *out_poly, uint64_t capacity, uint64_t *count) {
+	SB_ARG(pred == SB_PRED_INTERSECTS || pred == SB_PRED_WITHIN, "pred");
+	return join_points_polygons(ctx, mem, (int)pred, px, py, n_points, vx, vy, ring_vert_off, poly_ring_off, n_polys,
+	                            n_rings, n_verts, out_point, out_poly, capacity, count);
 }

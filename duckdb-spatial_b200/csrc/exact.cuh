@@ -11,7 +11,7 @@
 
 // exact sign of (bx-ax)*(cy-ay) - (by-ay)*(cx-ax) = ax*by - ax*cy - ay*bx + ay*cx + bx*cy - by*cx, each product exact
 // as (p, fma(a, b, -p)), the twelve terms summed as a non-overlapping expansion (grow-expansion). Rare path.
-__device__ __noinline__ int sb_orient2d_exact(double ax, double ay, double bx, double by, double cx, double cy) {
+static __device__ __noinline__ int sb_orient2d_exact(double ax, double ay, double bx, double by, double cx, double cy) {
 	const double pa[6] = {ax, -ax, -ay, ay, bx, -by};
 	const double pb[6] = {by, cy, bx, cx, cy, cx};
 	double e[12];

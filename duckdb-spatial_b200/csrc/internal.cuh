@@ -79,6 +79,10 @@ int sbi_rtree_build_str(sb_context *ctx, const float *box4, const int64_t *row_i
 int sbi_rtree_scan(sb_context *ctx, const sb_rtree *tree, const float *qbox4, uint32_t nq, uint32_t *out_query,
                    int64_t *out_row, uint64_t capacity, uint64_t *count);
 
+int sbi_select_valid(sb_context *ctx, const uint8_t *valid, uint64_t n, const float *box4, const int64_t *rows,
+                     float *obox4, int64_t *orows, uint64_t *count);
+int sbi_rtree_dump(sb_context *ctx, const sb_rtree *tree, int32_t *out_level, float *out_box4, int64_t *out_row,
+                   uint64_t capacity, uint64_t *count);
 int sbi_fsa_layout(uint64_t segment_size, uint64_t block_size, uint64_t *segments_per_buffer, uint64_t *bitmask_count);
 int sbi_rtree_pages_info(const sb_rtree *tree, uint64_t block_size, sb_rtree_pages_info *info);
 int sbi_rtree_export_pages(sb_context *ctx, const sb_rtree *tree, uint64_t block_size, void *leaf_img,

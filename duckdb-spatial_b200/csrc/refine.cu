@@ -2,6 +2,7 @@
 // Compiled with -fmad=false: every product/difference is individually rounded like the reference's x86-64 build.
 #include "internal.cuh"
 #include "pip.cuh"
+#include "exact.cuh"
 
 int sbi_read_u64(sb_context *ctx, const uint64_t *dev, uint64_t *host) {
 	return sbi_read_words(ctx, dev, 1, host);
@@ -85,6 +86,18 @@ struct pred_point_polygon {
 	}
 };
 
+// GEOMETRY-argument predicates (the GEOS route, exact.cuh): location of the point relative to the polygon with exact
+// orientation signs; intersects <=> not exterior, within / contains <=> interior.
+struct pred_point_polygon_exact {
+	const double *px, *py, *vx, *vy;
+	const uint64_t *ring_off, *poly_off;
+	int pred;
+	__device__ bool operator()(uint32_t a, uint32_t p, double &) const {
+		const int loc = sb_point_polygon_locate(px[a], py[a], vx, vy, ring_off, poly_off[p], poly_off[p + 1]);
+		return pred == SB_PRED_INTERSECTS ? loc != 0 : loc == 2;
+	}
+};
+
 // ST_Distance(POINT_2D, POINT_2D) :2189-2214: sqrt(pow(dx,2) + pow(dy,2)); pow(v,2) == v*v exactly (glibc),
 // sqrt is IEEE correctly rounded on both sides.
 __device__ __forceinline__ double dist_pp(double ax, double ay, double bx, double by) {
@@ -146,6 +159,13 @@ int sbi_refine_point_polygon(sb_context *ctx, const double *px, const double *py
                              uint64_t *count) {
 	pred_point_polygon p = {px, py, vx, vy, ring_off, poly_off};
 	return run_refine(ctx, "refine_pip", p, pp, pb, nullptr, n, count);
+}
+
+int sbi_refine_point_polygon_exact(sb_context *ctx, int pred, const double *px, const double *py, const double *vx,
+                                   const double *vy, const uint64_t *ring_off, const uint64_t *poly_off, uint32_t *pp,
+                                   uint32_t *pb, uint64_t n, uint64_t *count) {
+	pred_point_polygon_exact p = {px, py, vx, vy, ring_off, poly_off, pred};
+	return run_refine(ctx, "refine_pip_exact", p, pp, pb, nullptr, n, count);
 }
 
 int sbi_refine_dwithin(sb_context *ctx, const double *ax, const double *ay, const double *bx, const double *by,

@@ -658,3 +658,195 @@ int sbi_rtree_export_pages(sb_context *ctx, const sb_rtree *tree, uint64_t block
 	memcpy(root_entry, root, 24);
 	return SB_OK;
 }
+
+// ---- rtree_index_dump ------------------------------------------------------------------------------------------
+// (level, bounds, row_id) of every entry below the root entry in the DFS order of the reference's pragma
+// (rtree_index_pragmas.cpp:137-227 over RTreeScanner, rtree_scanner.hpp:38-83: the root node's entries are level 0, the
+// root entry itself is not emitted, an entry is followed by its whole subtree). The packed tree is complete -- node j
+// of a level is the entries [j * cap, (j + 1) * cap) of the level below -- so the DFS position of entry i of stored
+// level l is a closed form and every entry is written by its own thread:
+//   pos = sum over the levels m above l (below the root entry) of (i / cap^(m-l) + 1)      ancestors and their elder siblings' heads
+//       + i                                                                                 earlier entries of level l
+//       + sum over the levels m below l of min(i * cap^(l-m), count[m])                      descendants of earlier entries
+struct dump_levels {
+	const sb_entry *lvl[16];
+	uint64_t count[16];
+	int top; // stored level of the root entry (not emitted)
+	uint32_t cap;
+};
+
+__global__ void __launch_bounds__(256) k_rtree_dump(dump_levels L, int l, int32_t *__restrict__ out_level,
+                                                    float4 *__restrict__ out_box, int64_t *__restrict__ out_row,
+                                                    uint64_t capacity) {
+	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < L.count[l]; i += stride) {
+		uint64_t pos = i;
+		uint64_t a = i;
+		for (int m = l + 1; m < L.top; m++) {
+			a /= L.cap;
+			pos += a + 1;
+		}
+		uint64_t d = i;
+		for (int m = l - 1; m >= 0; m--) {
+			d = d > L.count[m] / L.cap + 1 ? L.count[m] : d * L.cap; // (saturating product)
+			pos += d < L.count[m] ? d : L.count[m];
+		}
+		if (pos < capacity) {
+			uint64_t ptr;
+			float4 b;
+			load_entry(L.lvl[l] + i, ptr, b);
+			out_level[pos] = L.top - 1 - l;
+			out_box[pos] = b;
+			out_row[pos] = l == 0 ? (int64_t)(ptr << 8) >> 8 : -1;
+		}
+	}
+}
+
+int sbi_rtree_dump(sb_context *ctx, const sb_rtree *tree, int32_t *out_level, float *out_box4, int64_t *out_row,
+                   uint64_t capacity, uint64_t *count) {
+	dump_levels L;
+	memset(&L, 0, sizeof(L));
+	L.top = tree->nlevels - 1;
+	L.cap = tree->cap;
+	uint64_t total = 0;
+	for (int l = 0; l < tree->nlevels; l++) {
+		L.lvl[l] = tree->entries + tree->offsets[l];
+		L.count[l] = tree->counts[l];
+		if (l < L.top) {
+			total += tree->counts[l];
+		}
+	}
+	*count = total;
+	if (total > capacity) {
+		sb_set_error("rtree dump: %llu rows, capacity %llu", (unsigned long long)total, (unsigned long long)capacity);
+		return SB_ERR_CAPACITY;
+	}
+	for (int l = 0; l < L.top; l++) {
+		k_rtree_dump<<<sb_grid(L.count[l], 256, 16), 256, 0, ctx->stream>>>(L, l, out_level,
+		                                                                      reinterpret_cast<float4 *>(out_box4), out_row,
+		                                                                      capacity);
+		SB_LAUNCH_CHECK(ctx);
+	}
+	return SB_OK;
+}
+
+// ---- CREATE INDEX straight from the GEOMETRY column --------------------------------------------------------------
+// rows without bounds (empty geometries, malformed blobs) never reach the index: the reference plans a filter on
+// the key's cached bbox below the sort (rtree_index_create_logical.cpp:42-72). Selection = tile counts + scan + gather,
+// order preserving.
+#define SEL_TILE 2048
+__global__ void __launch_bounds__(256) k_sel_count(const uint8_t *__restrict__ valid, uint64_t n, uint32_t *__restrict__ tile_cnt) {
+	__shared__ uint32_t s_cnt;
+	for (uint64_t tile = blockIdx.x; tile * SEL_TILE < n; tile += gridDim.x) {
+		if (threadIdx.x == 0) {
+			s_cnt = 0;
+		}
+		__syncthreads();
+		uint32_t c = 0;
+		for (uint32_t k = threadIdx.x; k < SEL_TILE; k += 256) {
+			const uint64_t i = tile * SEL_TILE + k;
+			c += (i < n && valid[i]) ? 1u : 0u;
+		}
+		c = __reduce_add_sync(0xFFFFFFFFu, c);
+		if (sb_lane() == 0 && c) {
+			atomicAdd(&s_cnt, c);
+		}
+		__syncthreads();
+		if (threadIdx.x == 0) {
+			tile_cnt[tile] = s_cnt;
+		}
+		__syncthreads();
+	}
+}
+// single CTA: exclusive scan of the tile counts (in place), total to *total
+__global__ void __launch_bounds__(1024) k_sel_scan(uint32_t *__restrict__ tile_cnt, uint64_t tiles, unsigned long long *__restrict__ total) {
+	__shared__ unsigned long long s_carry;
+	__shared__ uint32_t s_w[32];
+	if (threadIdx.x == 0) {
+		s_carry = 0;
+	}
+	__syncthreads();
+	for (uint64_t base = 0; base < tiles; base += 1024) {
+		const uint64_t i = base + threadIdx.x;
+		const uint32_t v = i < tiles ? tile_cnt[i] : 0u;
+		uint32_t inc = v;
+#pragma unroll
+		for (int sft = 1; sft < 32; sft <<= 1) {
+			const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, sft);
+			if (sb_lane() >= (unsigned)sft) {
+				inc += o;
+			}
+		}
+		if (sb_lane() == 31) {
+			s_w[threadIdx.x >> 5] = inc;
+		}
+		__syncthreads();
+		uint32_t wb = 0;
+		for (unsigned w = 0; w < (threadIdx.x >> 5); w++) {
+			wb += s_w[w];
+		}
+		const unsigned long long carry = s_carry;
+		if (i < tiles) {
+			tile_cnt[i] = (uint32_t)(carry + wb + inc - v);
+		}
+		__syncthreads();
+		if (threadIdx.x == 1023) {
+			s_carry = carry + wb + inc;
+		}
+		__syncthreads();
+	}
+	if (threadIdx.x == 0) {
+		*total = s_carry;
+	}
+}
+__global__ void __launch_bounds__(256) k_sel_gather(const uint8_t *__restrict__ valid, uint64_t n, const uint32_t *__restrict__ tile_off,
+                                                    const float4 *__restrict__ box, const int64_t *__restrict__ rows,
+                                                    float4 *__restrict__ obox, int64_t *__restrict__ orows) {
+	__shared__ uint32_t s_w[8];
+	const unsigned lane = sb_lane(), warp = threadIdx.x >> 5;
+	for (uint64_t tile = blockIdx.x; tile * SEL_TILE < n; tile += gridDim.x) {
+		uint32_t run = tile_off[tile];
+		for (uint32_t k0 = 0; k0 < SEL_TILE; k0 += 256) {
+			const uint64_t i = tile * SEL_TILE + k0 + threadIdx.x;
+			const bool v = i < n && valid[i];
+			const uint32_t m = __ballot_sync(0xFFFFFFFFu, v);
+			if (lane == 0) {
+				s_w[warp] = __popc(m);
+			}
+			__syncthreads();
+			uint32_t wb = 0, tot = 0;
+			for (unsigned w = 0; w < 8; w++) {
+				wb += w < warp ? s_w[w] : 0u;
+				tot += s_w[w];
+			}
+			if (v) {
+				const uint32_t o = run + wb + __popc(m & sb_lanemask_lt());
+				obox[o] = box[i];
+				orows[o] = rows ? rows[i] : (int64_t)i;
+			}
+			run += tot;
+			__syncthreads();
+		}
+	}
+}
+
+int sbi_select_valid(sb_context *ctx, const uint8_t *valid, uint64_t n, const float *box4, const int64_t *rows,
+                     float *obox4, int64_t *orows, uint64_t *count) {
+	*count = 0;
+	if (n == 0) {
+		return SB_OK;
+	}
+	const uint64_t tiles = (n + SEL_TILE - 1) / SEL_TILE;
+	uint32_t *d_tiles = nullptr;
+	unsigned long long *d_total = nullptr;
+	SB_TRY(ctx->scratch_t(tiles, &d_tiles));
+	SB_TRY(ctx->scratch_t(1, &d_total));
+	k_sel_count<<<sb_grid(tiles, 1, 16), 256, 0, ctx->stream>>>(valid, n, d_tiles);
+	SB_LAUNCH_CHECK(ctx);
+	k_sel_scan<<<1, 1024, 0, ctx->stream>>>(d_tiles, tiles, d_total);
+	SB_LAUNCH_CHECK(ctx);
+	k_sel_gather<<<sb_grid(tiles, 1, 16), 256, 0, ctx->stream>>>(valid, n, d_tiles, reinterpret_cast<const float4 *>(box4), rows,
+	                                                            reinterpret_cast<float4 *>(obox4), orows);
+	SB_LAUNCH_CHECK(ctx);
+	return sbi_read_u64(ctx, reinterpret_cast<const uint64_t *>(d_total), count);
+}

@@ -27,6 +27,10 @@ def _ptr(a):
     return a.ctypes.data
 
 
+def _pred_code(name):
+    return {"intersects": capi.PRED_INTERSECTS, "within": capi.PRED_WITHIN, "contains": capi.PRED_WITHIN}[name]
+
+
 class Context:
     """One per GPU / calling thread (sb_context): owns a stream and a scratch arena."""
 
@@ -291,16 +295,20 @@ class Context:
         eb, vb = self.st_extent(data_b, off_b)
         return self.st_intersects_box2d(ea, eb, va, vb)
 
-    def st_within_point_polygon(self, px, py, vx, vy, ring_off, poly_off, pair_point, pair_poly):
-        """ST_Within(POINT_2D, POLYGON_2D) over candidate pairs -> surviving (point, polygon) pairs."""
+    def st_within_point_polygon(self, px, py, vx, vy, ring_off, poly_off, pair_point, pair_poly, geos=None):
+        """ST_Within(POINT_2D, POLYGON_2D) over candidate pairs -> surviving (point, polygon) pairs.
+        geos="intersects" | "within": the GEOMETRY-argument (GEOS route) predicate with exact orientation instead."""
         px, py, vx, vy = [self._f64(v) for v in (px, py, vx, vy)]
         cnt = C.c_uint64(len(pair_point))
         pp = pair_point.clone() if _is_torch(pair_point) else np.ascontiguousarray(pair_point, np.uint32).copy()
         pb = pair_poly.clone() if _is_torch(pair_poly) else np.ascontiguousarray(pair_poly, np.uint32).copy()
-        capi.check(self.L.sb_refine_point_polygon(
-            self.h, self._mem(px, py, vx, vy, ring_off, poly_off, pp, pb), _ptr(px), _ptr(py), _ptr(vx), _ptr(vy),
-            _ptr(ring_off), _ptr(poly_off), len(poly_off) - 1, len(ring_off) - 1, len(vx), len(px), _ptr(pp), _ptr(pb),
-            C.byref(cnt)))
+        mem = self._mem(px, py, vx, vy, ring_off, poly_off, pp, pb)
+        tail = (_ptr(px), _ptr(py), _ptr(vx), _ptr(vy), _ptr(ring_off), _ptr(poly_off), len(poly_off) - 1, len(ring_off) - 1,
+                len(vx), len(px), _ptr(pp), _ptr(pb), C.byref(cnt))
+        if geos is None:
+            capi.check(self.L.sb_refine_point_polygon(self.h, mem, *tail))
+        else:
+            capi.check(self.L.sb_refine_point_polygon_exact(self.h, mem, _pred_code(geos), *tail))
         return pp[: cnt.value], pb[: cnt.value]
 
     # -- whole joins ---------------------------------------------------------------------------------------
@@ -378,8 +386,10 @@ class Context:
         ub = self.join_unmatched_rows(bm) if jt in ("right", "full", "outer") else empty
         return p, b, up, ub
 
-    def join_points_polygons(self, px, py, vx, vy, ring_off, poly_off, capacity=None, out=None):
-        """ST_Within(point, polygon) join over POLYGON_2D list columns -> (point rows, polygon rows), unordered."""
+    def join_points_polygons(self, px, py, vx, vy, ring_off, poly_off, capacity=None, out=None, geos=None):
+        """ST_Within(point, polygon) join over POLYGON_2D list columns -> (point rows, polygon rows), unordered.
+        geos="intersects" | "within": GEOMETRY-argument (GEOS route) predicate with exact orientation instead of the
+        native winding routine."""
         px, py, vx, vy = [self._f64(v) for v in (px, py, vx, vy)]
         cap = int(capacity if capacity is not None else max(1024, 2 * len(px)))
         while True:
@@ -390,10 +400,13 @@ class Context:
                 op = self._empty(px, (cap,), np.uint32)
                 ob = self._empty(px, (cap,), np.uint32)
             cnt = C.c_uint64(0)
-            rc = self.L.sb_join_points_polygons(self.h, self._mem(px, py, vx, vy, ring_off, poly_off), _ptr(px), _ptr(py),
-                                                len(px), _ptr(vx), _ptr(vy), _ptr(ring_off), _ptr(poly_off),
-                                                len(poly_off) - 1, len(ring_off) - 1, len(vx), _ptr(op), _ptr(ob), cap,
-                                                C.byref(cnt))
+            tail = (_ptr(px), _ptr(py), len(px), _ptr(vx), _ptr(vy), _ptr(ring_off), _ptr(poly_off), len(poly_off) - 1,
+                    len(ring_off) - 1, len(vx), _ptr(op), _ptr(ob), cap, C.byref(cnt))
+            mem = self._mem(px, py, vx, vy, ring_off, poly_off)
+            if geos is None:
+                rc = self.L.sb_join_points_polygons(self.h, mem, *tail)
+            else:
+                rc = self.L.sb_join_points_polygons_exact(self.h, mem, _pred_code(geos), *tail)
             if rc == capi.ERR_CAPACITY and out is None:
                 cap = int(cnt.value)
                 continue
@@ -496,6 +509,24 @@ class RTreeIndex:
         self.h = h
         self.cap = max_node_capacity
 
+    @classmethod
+    def from_blobs(cls, ctx, data, offsets, row_ids=None, max_node_capacity=128):
+        """CREATE INDEX ... USING RTREE over a serialized GEOMETRY column; rows without bounds are not indexed."""
+        self = cls.__new__(cls)
+        self.ctx = ctx
+        self.cap = max_node_capacity
+        if not _is_torch(data):
+            data = np.ascontiguousarray(data, np.uint8)
+            offsets = np.ascontiguousarray(offsets, np.uint64)
+            row_ids = None if row_ids is None else np.ascontiguousarray(row_ids, np.int64)
+        h, kept = C.c_void_p(), C.c_uint64(0)
+        capi.check(ctx.L.sb_rtree_build_from_blobs(ctx.h, ctx._mem(data, offsets), _ptr(data), _ptr(offsets), len(offsets) - 1,
+                                                   _ptr(row_ids) if row_ids is not None else None, max_node_capacity,
+                                                   C.byref(h), C.byref(kept), None))
+        self.h = h
+        self.indexed_rows = kept.value
+        return self
+
     def close(self):
         if getattr(self, "h", None):
             self.ctx.L.sb_rtree_destroy(self.h)
@@ -524,6 +555,26 @@ class RTreeIndex:
         out = np.empty(n, ENTRY_DTYPE)
         capi.check(self.ctx.L.sb_rtree_export_level(self.ctx.h, self.h, l, capi.HOST, _ptr(out)))
         return out
+
+    def dump(self, device=False):
+        """rtree_index_dump: (level int32[n], bounds float32[n,4], row_id int64[n], -1 for branch entries) in the
+        reference pragma's DFS order (rtree_index_pragmas.cpp:137-227)."""
+        cnt = C.c_uint64(0)
+        capi.check(self.ctx.L.sb_rtree_dump(self.ctx.h, self.h, capi.HOST, None, None, None, 0, C.byref(cnt)))
+        n = cnt.value
+        if device:
+            import torch
+
+            dev = torch.device("cuda", self.ctx.device)
+            lv = torch.empty(n, dtype=torch.int32, device=dev)
+            box = torch.empty((n, 4), dtype=torch.float32, device=dev)
+            rid = torch.empty(n, dtype=torch.int64, device=dev)
+            mem = capi.DEVICE
+        else:
+            lv, box, rid = np.empty(n, np.int32), np.empty((n, 4), np.float32), np.empty(n, np.int64)
+            mem = capi.HOST
+        capi.check(self.ctx.L.sb_rtree_dump(self.ctx.h, self.h, mem, _ptr(lv), _ptr(box), _ptr(rid), n, C.byref(cnt)))
+        return lv, box, rid
 
     def pages_layout(self, block_size=262136):
         """FixedSizeAllocator geometry + page / buffer counts of the exported tree (sb_rtree_pages_layout)."""

@@ -157,6 +157,13 @@ SB_API int sb_sort_pairs_u64(sb_context *ctx, sb_mem mem, uint64_t *keys, uint32
  * does (rtree_index_create_logical.cpp:42-72). max_node_capacity in [4, 255] (rtree_index.cpp:30-63). */
 SB_API int sb_rtree_build_str(sb_context *ctx, sb_mem mem, const float *box4, const int64_t *row_ids, uint64_t n,
                               uint32_t max_node_capacity, sb_rtree **out);
+/* CREATE INDEX straight from the GEOMETRY key column: TryGetCachedBounds per row (geometry_type.hpp:102-148), rows
+ * without bounds dropped as the planner's filter does (rtree_index_create_logical.cpp:42-72), then the same STR bulk
+ * load -- the 64.2 B/key variant of the build (32 B blob + 8 B row id in, 24 B entry out). row_ids NULL = ordinals.
+ * *indexed_rows = rows that reached the index; row_status (optional) as in sb_bbox_from_blobs. */
+SB_API int sb_rtree_build_from_blobs(sb_context *ctx, sb_mem mem, const uint8_t *data, const uint64_t *offsets, uint64_t n,
+                                     const int64_t *row_ids, uint32_t max_node_capacity, sb_rtree **out,
+                                     uint64_t *indexed_rows, int32_t *row_status);
 SB_API void sb_rtree_destroy(sb_rtree *tree);
 /* level 0 = leaf entries (row ids); the last level has one entry = the root entry. */
 SB_API int sb_rtree_num_levels(const sb_rtree *tree);
@@ -168,6 +175,12 @@ SB_API uint64_t sb_rtree_slice_size(const sb_rtree *tree);
  * ((type<<56) | child node index, type LEAF_PAGE=1 / BRANCH_PAGE=2) into IndexPointers. Leaf-level pointers are
  * row ids with type ROW_ID=0 (rtree.cpp:37-42). */
 SB_API int sb_rtree_export_level(sb_context *ctx, const sb_rtree *tree, int level, sb_mem mem, void *out_entries);
+/* rtree_index_dump('idx'): replaces the traversal of RTreeIndexDumpExecute (rtree_index_pragmas.cpp:137-227 over
+ * RTreeScanner::Scan, rtree_scanner.hpp:38-83): one row (level, bounds, row_id) per entry below the root entry, in the
+ * pragma's DFS order -- the root node's entries are level 0 and each entry is followed by its subtree; row_id is -1
+ * where the pragma yields NULL (branch entries). out_level == NULL: only *count (= rows) is returned. */
+SB_API int sb_rtree_dump(sb_context *ctx, const sb_rtree *tree, sb_mem mem, int32_t *out_level, float *out_box4,
+                         int64_t *out_row_id, uint64_t capacity, uint64_t *count);
 /* Persistent-index export (GetStorageInfo / checkpoint path, rtree_index.cpp:234-259): the whole tree as the block
  * images of the reference's two FixedSizeAllocators (rtree.hpp:31-36; leaf pages and branch pages), with real
  * IndexPointers (index_pointer.hpp:19-24: metadata << 56 | offset << 32 | buffer id), exactly as
@@ -240,6 +253,18 @@ SB_API int sb_refine_point_polygon(sb_context *ctx, sb_mem mem, const double *px
                                    const double *vy, const uint64_t *ring_vert_off, const uint64_t *poly_ring_off,
                                    uint64_t n_polys, uint64_t n_rings, uint64_t n_verts, uint64_t n_points,
                                    uint32_t *pair_probe, uint32_t *pair_build, uint64_t *count);
+/* The GEOS route of the same refinement, for GEOMETRY arguments: replaces GEOSPreparedIntersects_r / GEOSIntersects_r
+ * (ST_Intersects, geos_module.cpp:1128-1153), GEOSContains_r (ST_Contains, :386-415) and GEOSWithin_r (ST_Within,
+ * :1885-1908) for point x polygon pairs. GEOS is not part of the reference tree; implemented is its point-in-area
+ * algorithm (RayCrossingCounter + locatePointInPolygon: shell, then holes) with an exact orientation sign (fp64 filter
+ * + expansion arithmetic), i.e. the true OGC answer: a point on the boundary (shell or hole) intersects but is not
+ * within (test/sql/geos/predicates.test:15-46, index/rtree_filter_prune.test:14-20). pred = SB_PRED_INTERSECTS or
+ * SB_PRED_WITHIN (= ST_Contains(polygon, point)). Same arguments and in-place compaction as sb_refine_point_polygon. */
+SB_API int sb_refine_point_polygon_exact(sb_context *ctx, sb_mem mem, sb_predicate pred, const double *px,
+                                         const double *py, const double *vx, const double *vy,
+                                         const uint64_t *ring_vert_off, const uint64_t *poly_ring_off, uint64_t n_polys,
+                                         uint64_t n_rings, uint64_t n_verts, uint64_t n_points, uint32_t *pair_probe,
+                                         uint32_t *pair_build, uint64_t *count);
 /* ST_Distance(POINT_2D, POINT_2D) (:2189-2214) for each pair, and ST_DWithin filtering (dist <= r). out_dist may
  * be NULL. Survivors compacted in place. */
 SB_API int sb_refine_dwithin(sb_context *ctx, sb_mem mem, const double *ax, const double *ay, const double *bx,
@@ -287,6 +312,14 @@ SB_API int sb_join_points_polygons(sb_context *ctx, sb_mem mem, const double *px
                                    const double *vx, const double *vy, const uint64_t *ring_vert_off,
                                    const uint64_t *poly_ring_off, uint64_t n_polys, uint64_t n_rings, uint64_t n_verts,
                                    uint32_t *out_point, uint32_t *out_poly, uint64_t capacity, uint64_t *count);
+/* the same join under the GEOS-route predicates (ST_Intersects / ST_Within / ST_Contains on GEOMETRY arguments, see
+ * sb_refine_point_polygon_exact): float-box candidates, then the exact point-in-area location. Large probe sides run
+ * polygon-centric with the same shared-memory edge index (pip_join.cu, exact mode). */
+SB_API int sb_join_points_polygons_exact(sb_context *ctx, sb_mem mem, sb_predicate pred, const double *px,
+                                         const double *py, uint64_t n_points, const double *vx, const double *vy,
+                                         const uint64_t *ring_vert_off, const uint64_t *poly_ring_off, uint64_t n_polys,
+                                         uint64_t n_rings, uint64_t n_verts, uint32_t *out_point, uint32_t *out_poly,
+                                         uint64_t capacity, uint64_t *count);
 /* radius join (new capability behind the same operator): all (a, b) with distance <= radius.
  * Builds a FlatRTree over b's points expanded by radius, probes with a, refines with ST_Distance. */
 SB_API int sb_join_dwithin(sb_context *ctx, sb_mem mem, const double *ax, const double *ay, uint64_t na,

@@ -122,3 +122,42 @@ def test_winding_on_hole_boundary(ctx, O):
     exp = exp & in_box.astype(np.uint8)
     bad = np.nonzero(got2 != exp)[0]
     assert len(bad) == 0, [(px[i], py[i], int(got2[i]), int(exp[i])) for i in bad[:12]]
+
+
+@pytest.mark.parametrize("n,cap", [(1, 128), (2, 4), (129, 128), (5000, 16), (100_000, 128), (300_001, 7)])
+def test_rtree_dump_matches_oracle_dfs(ctx, sb, O, n, cap):
+    # sb_rtree_dump == the oracle's DFS dump, which is pinned row for row on the reference's rtree_index_dump
+    # (tests/test_oracle_vs_refdb.py)
+    x, y = O.generate_points(77, n, (0, 0, 1000, 1000))
+    box = O.bbox_from_points(x, y)
+    rows = np.arange(n, dtype=np.int64) * 3 - 5
+    idx = sb.RTreeIndex(ctx, box, rows, cap)
+    lv, b, rid = idx.dump()
+    olv, obox, orid = O.StrTree(box, rows, cap).dump()
+    assert np.array_equal(lv, olv)
+    assert np.array_equal(b.view(np.uint32), obox.reshape(-1, 4).view(np.uint32))
+    assert np.array_equal(rid, orid)
+    idx.close()
+
+
+def test_rtree_build_from_blobs_skips_rows_without_bounds(ctx, sb, O):
+    import geomblob
+
+    n = 20_000
+    x, y = O.generate_points(5, n, (0, 0, 1000, 1000))
+    raw, _ = O.point_blobs(x, y)
+    blobs = [raw[i * 32:(i + 1) * 32].tobytes() for i in range(n)]
+    empty = geomblob.blob(("POINT", []), O)
+    keep = np.ones(n, bool)
+    for i in range(0, n, 97):
+        blobs[i] = empty
+        keep[i] = False
+    data, off = O.concat_blobs(blobs)
+    idx = sb.RTreeIndex.from_blobs(ctx, data, off, None, 64)
+    assert idx.indexed_rows == int(keep.sum())
+    rows = np.nonzero(keep)[0].astype(np.int64)
+    ref = sb.RTreeIndex(ctx, O.bbox_from_points(x[keep], y[keep]), rows, 64)
+    for l in range(idx.nlevels):
+        assert np.array_equal(idx.level(l), ref.level(l))
+    idx.close()
+    ref.close()
