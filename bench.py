@@ -738,55 +738,77 @@ def run_ours(a):
 
 
 def run_e2e(a, result, ctx, capi, L, rank, world, dev, px, py, boxes, cap, barrier, all_sum, out_p, out_b, ref_prefix):
-    """e2e: N = 1: sb_join_points_boxes(SB_HOST). N > 1: every rank runs the host-pointer join on its own replica.
-    Returns False when the host-pointer result fails the parity check."""
+    """e2e through the C-ABI with HOST (pinned) buffers, copies inside the timed region.
+    N = 1: sb_join_points_boxes(SB_HOST). N > 1: rank 0 alone drives all N devices through sb_join_points_boxes_multi --
+    ONE P x B join (its own probe column) split over N PCIe links, one pair list back (strong scaling); the other
+    ranks wait on the host. Returns False when the host-pointer result fails the parity check."""
     import ctypes as C
 
     import torch
     import torch.distributed as dist
 
+    import sb200
+
+    sb = sb200.load()
     P, B = a.points, a.boxes
     cnt = C.c_uint64(0)
-    hp = [t.cpu().pin_memory() for t in (px, py) + tuple(boxes)]
-    ho_p = torch.empty(cap, dtype=torch.int32).pin_memory()
-    ho_b = torch.empty(cap, dtype=torch.int32).pin_memory()
-
-    def step_e2e():
-        capi.check(L.sb_join_points_boxes(ctx.h, capi.HOST, capi.PRED_INTERSECTS, hp[0].data_ptr(), hp[1].data_ptr(),
-                                          P, hp[2].data_ptr(), hp[3].data_ptr(), hp[4].data_ptr(), hp[5].data_ptr(),
-                                          B, ho_p.data_ptr(), ho_b.data_ptr(), cap, C.byref(cnt)))
-        return cnt.value
-
-    for _ in range(3):  # warm-up: the first calls grow (and then coalesce) the context's staging arena
-        step_e2e()
-    barrier()
-    t0 = time.perf_counter()
-    ep = 0
-    for _ in range(a.e2e_steps):
-        ep += step_e2e()
-    torch.cuda.synchronize()
-    et = time.perf_counter() - t0
-    if world > 1:
-        t = torch.tensor([et], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        et = float(t.item())
-    ep = all_sum(ep)
-    e2e = {"value": ep / et, "unit": UNIT, "h2d_bytes_per_step": 16 * P + 32 * B,
-           "d2h_bytes_per_step": 8 * (ep // a.e2e_steps // world), "ms_per_step": 1e3 * et / a.e2e_steps,
-           "note": "sb_join_points_boxes(SB_HOST): pinned host columns in, pair arrays out, copies inside the timed region; per-rank replicas for N>1"}
     ok = True
-    if ref_prefix is not None:
-        # the host-pointer result of the last step (probe ids are slice-local there) against the reference prefix:
-        # rank 0's slice starts at row 0, so its checksum must equal the reference's; the other ranks compare counts
-        n = cnt.value
-        out_p[:n].copy_(ho_p[:n])
-        out_b[:n].copy_(ho_b[:n])
-        np_rows, rc, rh = ref_prefix
-        c, hsh = ctx.pairs_checksum(out_p, out_b, 0, np_rows, count=n)
-        ok = (c == rc) and (rank != 0 or hsh == rh)
-        e2e["parity"] = {"ok": bool(all_sum(0 if ok else 1) == 0), "checked_probes": np_rows, "pairs": c, "ref_pairs": rc}
-    result["e2e"] = e2e
-    del hp, ho_p, ho_b
+    store = dist.distributed_c10d._get_default_store() if world > 1 else None
+    if rank == 0:
+        hp = [t.cpu().pin_memory() for t in (px, py) + tuple(boxes)]
+        ho_p = torch.empty(cap, dtype=torch.int32).pin_memory()
+        ho_b = torch.empty(cap, dtype=torch.int32).pin_memory()
+        extra = [sb.Context(d) for d in range(world) if d != ctx.device] if world > 1 else []
+        ctxs = [ctx] + extra
+        hs = (C.c_void_p * len(ctxs))(*[c.h for c in ctxs])
+
+        def step_e2e():
+            if world == 1:
+                capi.check(L.sb_join_points_boxes(ctx.h, capi.HOST, capi.PRED_INTERSECTS, hp[0].data_ptr(), hp[1].data_ptr(),
+                                                  P, hp[2].data_ptr(), hp[3].data_ptr(), hp[4].data_ptr(), hp[5].data_ptr(),
+                                                  B, ho_p.data_ptr(), ho_b.data_ptr(), cap, C.byref(cnt)))
+            else:
+                capi.check(L.sb_join_points_boxes_multi(hs, len(ctxs), capi.PRED_INTERSECTS, hp[0].data_ptr(), hp[1].data_ptr(),
+                                                        P, hp[2].data_ptr(), hp[3].data_ptr(), hp[4].data_ptr(),
+                                                        hp[5].data_ptr(), B, ho_p.data_ptr(), ho_b.data_ptr(), cap,
+                                                        C.byref(cnt)))
+            return cnt.value
+
+        for _ in range(3):  # warm-up: the first calls grow (and then coalesce) the contexts' staging arenas
+            step_e2e()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        ep = 0
+        for _ in range(a.e2e_steps):
+            ep += step_e2e()
+        for d in range(world):
+            torch.cuda.synchronize(d)
+        et = time.perf_counter() - t0
+        e2e = {"value": ep / et, "unit": UNIT, "h2d_bytes_per_step": 16 * P + 32 * B,
+               "d2h_bytes_per_step": 8 * (ep // a.e2e_steps), "ms_per_step": 1e3 * et / a.e2e_steps,
+               "note": ("sb_join_points_boxes(SB_HOST): pinned host columns in, pair arrays out, copies inside the timed region" if world == 1 else
+                        "sb_join_points_boxes_multi over %d devices from ONE process (rank 0): one %d x %d join, pinned host columns in, one host "
+                        "pair list out, tree replicated by peer copies, every device streams its probe slice over its own PCIe link; "
+                        "strong scaling of the fixed job" % (world, P, B))}
+        if ref_prefix is not None:
+            # the host-pointer result of the last step against the reference prefix (rank 0's slice starts at row 0)
+            n = cnt.value
+            out_p[:n].copy_(ho_p[:n])
+            out_b[:n].copy_(ho_b[:n])
+            np_rows, rc, rh = ref_prefix
+            c, hsh = ctx.pairs_checksum(out_p, out_b, 0, np_rows, count=n)
+            ok = (c == rc) and (hsh == rh)
+            e2e["parity"] = {"ok": bool(ok), "checked_probes": np_rows, "pairs": c, "ref_pairs": rc}
+        result["e2e"] = e2e
+        for c in extra:
+            c.close()
+        del hp, ho_p, ho_b
+        if store is not None:
+            store.set("sb_e2e_done", "1")
+    elif store is not None:
+        store.wait(["sb_e2e_done"])  # host-side wait: no spinning NCCL kernel on this rank's GPU while rank 0 measures
+    if world > 1:
+        dist.barrier()
     return ok
 
 

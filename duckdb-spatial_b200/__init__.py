@@ -5,11 +5,11 @@ function / index / operator surface for that path. There is no CPU fallback."""
 from . import build as _build
 from . import capi
 from .capi import SpatialB200Error
-from .functions import ENTRY_DTYPE, Context, FlatRTree, RTreeIndex, SpatialJoinOp
+from .functions import ENTRY_DTYPE, Context, FlatRTree, RTreeIndex, SpatialJoinOp, spatial_join_points_boxes_multi
 
 
 def build_native(force=False, verbose=False):
     return _build.build(force=force, verbose=verbose)
 
 
-__all__ = ["capi", "Context", "RTreeIndex", "FlatRTree", "SpatialJoinOp", "ENTRY_DTYPE", "SpatialB200Error", "build_native"]
+__all__ = ["capi", "Context", "RTreeIndex", "FlatRTree", "SpatialJoinOp", "spatial_join_points_boxes_multi", "ENTRY_DTYPE", "SpatialB200Error", "build_native"]

@@ -73,6 +73,7 @@ SIGNATURES = {
     "sb_intersects_box2d": (i32, [vp, i32] + [vp] * 8 + [u32, vp, vp, u64, vp]),
     "sb_distance_point_linestring": (i32, [vp, i32, vp, vp, vp, u64, vp, vp, u64, vp]),
     "sb_join_points_boxes": (i32, [vp, i32, i32, vp, vp, u64, vp, vp, vp, vp, u32, vp, vp, u64, C.POINTER(u64)]),
+    "sb_join_points_boxes_multi": (i32, [vp, i32, i32, vp, vp, u64, vp, vp, vp, vp, u32, vp, vp, u64, C.POINTER(u64)]),
     "sb_join_mark_matched": (i32, [vp, i32, vp, vp, u64, u32, vp, u64, vp, u64]),
     "sb_join_unmatched_rows": (i32, [vp, i32, vp, u64, u32, vp, u64, C.POINTER(u64)]),
     "sb_rtree_build_from_blobs": (i32, [vp, i32, vp, vp, u64, vp, u32, C.POINTER(vp), C.POINTER(u64), vp]),

@@ -3,6 +3,11 @@
 // calls only enqueue work (except where a count has to be returned).
 #include "internal.cuh"
 
+#include <atomic>
+#include <string>
+#include <thread>
+#include <vector>
+
 #define SB_BEGIN(ctx)                                                                                                \
 	SB_ARG((ctx) != nullptr, "ctx");                                                                                 \
 	SB_CUDA(cudaSetDevice((ctx)->device));                                                                           \
@@ -835,10 +840,14 @@ extern "C" int sb_distance_point_linestring(sb_context *ctx, sb_mem mem, const d
 // Host-pointer join of a large probe column: the probe column is streamed through the device in chunks so that the
 // H2D copy of chunk k+1, the probe of chunk k and the D2H copy of chunk k-1's pairs overlap (three streams, PCIe is
 // full duplex). The call is bound by the larger of the two copy directions instead of their sum plus the kernels.
+// shared_total != nullptr (sb_join_points_boxes_multi): several devices write one pair list; a chunk's place in the
+// caller's arrays is reserved from the shared counter once its pair count is known, row ids start at index_base.
 static int join_points_boxes_pipelined(sb_context *ctx, sb_predicate pred, const double *px, const double *py,
                                        uint64_t n_points, const sb_flat *tree, const double4 *box2d, uint32_t n_boxes,
-                                       uint32_t *out_probe, uint32_t *out_build, uint64_t capacity, uint64_t *count) {
-	const uint64_t chunk = ctx->pipe_chunk;
+                                       uint32_t *out_probe, uint32_t *out_build, uint64_t capacity, uint64_t *count,
+                                       uint64_t index_base = 0, std::atomic<uint64_t> *shared_total = nullptr,
+                                       uint64_t chunk_rows = 0) {
+	const uint64_t chunk = chunk_rows ? chunk_rows : ctx->pipe_chunk;
 	// a chunk's pairs must fit one output slot; a probe row pairs with at most n_boxes build rows. When a chunk
 	// overflows its slot it is split (below), so any positive slot size >= n_boxes terminates.
 	uint64_t slot_cap = 12 * chunk;
@@ -948,14 +957,16 @@ static int join_points_boxes_pipelined(sb_context *ctx, sb_predicate pred, const
 			a.px = dx[islot] + done;
 			a.py = dy[islot] + done;
 			a.m = piece;
-			a.index_base = (uint32_t)(beg + done);
+			a.index_base = (uint32_t)(index_base + beg + done);
 			a.build_box2d = box2d;
 			a.pred = (int)pred;
 			uint64_t got = 0;
 			ctx->arena.rewind(mark);
 			tl_mark(ctx->stream, 'p', c);
-			const uint64_t lead_p = (reinterpret_cast<uintptr_t>(out_probe + total) >> 2) % PAGE_WORDS;
-			const uint64_t lead_b = (reinterpret_cast<uintptr_t>(out_build + total) >> 2) % PAGE_WORDS;
+			// (shared list: the destination is only known after the probe; the slot is then written at its aligned start
+			// and only the HOST side of the copy is split at a page boundary)
+			uint64_t lead_p = shared_total ? 0 : (reinterpret_cast<uintptr_t>(out_probe + total) >> 2) % PAGE_WORDS;
+			uint64_t lead_b = shared_total ? 0 : (reinterpret_cast<uintptr_t>(out_build + total) >> 2) % PAGE_WORDS;
 			uint32_t *sp = dp[slot] + lead_p, *sb = db[slot] + lead_b;
 			int s = sbi_flat_probe(ctx, tree, a, sp, sb, slot_cap, &got);
 			tl_mark(ctx->stream, 'P', c);
@@ -968,7 +979,13 @@ static int join_points_boxes_pipelined(sb_context *ctx, sb_predicate pred, const
 				break;
 			}
 			// sbi_flat_probe returned => the pairs are complete in the slot (it synchronises to read the count)
-			if (total + got <= capacity) {
+			uint64_t dst = total;
+			if (shared_total) {
+				dst = shared_total->fetch_add(got);
+				lead_p = (reinterpret_cast<uintptr_t>(out_probe + dst) >> 2) % PAGE_WORDS;
+				lead_b = (reinterpret_cast<uintptr_t>(out_build + dst) >> 2) % PAGE_WORDS;
+			}
+			if (dst + got <= capacity) {
 				tl_mark(ctx->d2h_stream, 'd', c);
 				auto copy_out = [&](uint32_t *host, const uint32_t *dev, uint64_t lead) -> int {
 					uint64_t head = (PAGE_WORDS - lead) % PAGE_WORDS;
@@ -982,8 +999,8 @@ static int join_points_boxes_pipelined(sb_context *ctx, sb_predicate pred, const
 					}
 					return SB_OK;
 				};
-				SB_TRY(copy_out(out_probe + total, sp, lead_p));
-				SB_TRY(copy_out(out_build + total, sb, lead_b));
+				SB_TRY(copy_out(out_probe + dst, sp, lead_p));
+				SB_TRY(copy_out(out_build + dst, sb, lead_b));
 				tl_mark(ctx->d2h_stream, 'D', c);
 			}
 			total += got;
@@ -1026,7 +1043,7 @@ static int join_points_boxes_pipelined(sb_context *ctx, sb_predicate pred, const
 		cudaEventDestroy(probe_done[k]);
 	}
 	*count = total;
-	if (status == SB_OK && total > capacity) {
+	if (status == SB_OK && !shared_total && total > capacity) {
 		sb_set_error("join: %llu pairs, capacity %llu", (unsigned long long)total, (unsigned long long)capacity);
 		return SB_ERR_CAPACITY;
 	}
@@ -1291,3 +1308,155 @@ extern "C" int sb_join_points_polygons_exact(sb_context *ctx, sb_mem mem, sb_pre
 	return join_points_polygons(ctx, mem, (int)pred, px, py, n_points, vx, vy, ring_vert_off, poly_ring_off, n_polys,
 	                            n_rings, n_verts, out_point, out_poly, capacity, count);
 }
+
+// One join over several devices of ONE process (the reference operator is one process,
+// spatial_join_physical.cpp:695-945): device 0 builds the FlatRTree, the packed tree and the build side's exact boxes
+// go to the other devices as peer copies (NVLink), every device streams a contiguous slice of the host probe column
+// through its own three-stream pipeline (one host thread per device) and the pair lists land in ONE host pair list --
+// each chunk reserves its range from a shared counter when its pair count is known. Row ids are global.
+extern "C" int sb_join_points_boxes_multi(sb_context *const *ctxs, int n_ctx, sb_predicate pred, const double *px,
+                                          const double *py, uint64_t n_points, const double *bmin_x, const double *bmin_y,
+                                          const double *bmax_x, const double *bmax_y, uint32_t n_boxes,
+                                          uint32_t *out_probe, uint32_t *out_build, uint64_t capacity, uint64_t *count) {
+	SB_ARG(ctxs != nullptr && n_ctx >= 1 && n_ctx <= 64 && count != nullptr, "ctxs/count");
+	for (int d = 0; d < n_ctx; d++) {
+		SB_ARG(ctxs[d] != nullptr, "ctxs[d]");
+		for (int e = 0; e < d; e++) {
+			SB_ARG(ctxs[e] != ctxs[d], "contexts must be distinct");
+		}
+	}
+	*count = 0;
+	if (n_boxes == 0 || n_points == 0) {
+		return SB_OK;
+	}
+	SB_ARG(n_points <= 0xFFFFFFFFull, "probe indices must fit 32 bits");
+	sb_context *c0 = ctxs[0];
+	{
+		SB_BEGIN(c0);
+	}
+	const double *b0, *b1, *b2, *b3;
+	SB_TRY(sb_to_device(c0, SB_HOST, bmin_x, (uint64_t)n_boxes, &b0));
+	SB_TRY(sb_to_device(c0, SB_HOST, bmin_y, (uint64_t)n_boxes, &b1));
+	SB_TRY(sb_to_device(c0, SB_HOST, bmax_x, (uint64_t)n_boxes, &b2));
+	SB_TRY(sb_to_device(c0, SB_HOST, bmax_y, (uint64_t)n_boxes, &b3));
+	float *fbox = nullptr;
+	double *box2d = nullptr;
+	SB_TRY(c0->scratch_t(4 * (uint64_t)n_boxes, &fbox));
+	SB_TRY(c0->scratch_t(4 * (uint64_t)n_boxes, &box2d));
+	SB_TRY(sbi_bbox_box2d(c0, b0, b1, b2, b3, n_boxes, fbox));
+	SB_TRY(sbi_pack_box2d(c0, b0, b1, b2, b3, n_boxes, box2d));
+	sb_flat *tree = nullptr;
+	int s = sbi_flat_build(c0, fbox, n_boxes, 32, &tree);
+	if (s != SB_OK) {
+		if (tree) {
+			sb_flat_destroy(tree);
+		}
+		return s;
+	}
+	// replicate: tree buffer + exact boxes to every other device, ordered after the build on device 0's stream
+	cudaEvent_t built = nullptr;
+	std::vector<sb_flat> views((size_t)n_ctx);
+	std::vector<const double4 *> boxes((size_t)n_ctx, nullptr);
+	views[0] = *tree;
+	views[0].owns = false;
+	boxes[0] = reinterpret_cast<const double4 *>(box2d);
+	auto fail = [&](int code) {
+		if (built) {
+			cudaEventDestroy(built);
+		}
+		cudaSetDevice(c0->device);
+		cudaStreamSynchronize(c0->stream);
+		sb_flat_destroy(tree);
+		return code;
+	};
+	if (cudaSetDevice(c0->device) != cudaSuccess || cudaEventCreateWithFlags(&built, cudaEventDisableTiming) != cudaSuccess ||
+	    cudaEventRecord(built, c0->stream) != cudaSuccess) {
+		sb_set_error("multi join: event setup failed");
+		return fail(SB_ERR_CUDA);
+	}
+	for (int d = 1; d < n_ctx; d++) {
+		sb_context *cd = ctxs[d];
+		if (cudaSetDevice(cd->device) != cudaSuccess) {
+			sb_set_error("multi join: cudaSetDevice(%d) failed", cd->device);
+			return fail(SB_ERR_CUDA);
+		}
+		cd->arena.reset();
+		void *tb = nullptr, *bb = nullptr;
+		if (cd->scratch(tree->bytes, &tb) != SB_OK || cd->scratch(sizeof(double4) * (size_t)n_boxes, &bb) != SB_OK) {
+			return fail(SB_ERR_CUDA);
+		}
+		cudaError_t e = cudaStreamWaitEvent(cd->stream, built, 0);
+		if (e == cudaSuccess) {
+			e = cudaMemcpyPeerAsync(tb, cd->device, tree->buffer, c0->device, tree->bytes, cd->stream);
+		}
+		if (e == cudaSuccess) {
+			e = cudaMemcpyPeerAsync(bb, cd->device, box2d, c0->device, sizeof(double4) * (size_t)n_boxes, cd->stream);
+		}
+		if (e != cudaSuccess) {
+			sb_set_error("multi join: peer copy to device %d failed: %s", cd->device, cudaGetErrorString(e));
+			return fail(SB_ERR_CUDA);
+		}
+		views[d] = *tree;
+		views[d].device = cd->device;
+		views[d].owner = nullptr;
+		views[d].buffer = tb;
+		views[d].owns = false;
+		boxes[d] = static_cast<const double4 *>(bb);
+	}
+	// contiguous probe slices, one host thread per device
+	std::atomic<uint64_t> total{0};
+	std::vector<int> status((size_t)n_ctx, SB_OK);
+	std::vector<std::string> errors((size_t)n_ctx);
+	std::vector<std::thread> workers;
+	const uint64_t base = n_points / (uint64_t)n_ctx, rem = n_points % (uint64_t)n_ctx;
+	auto work = [&](int d) {
+		sb_context *cd = ctxs[d];
+		const uint64_t beg = (uint64_t)d * base + ((uint64_t)d < rem ? (uint64_t)d : rem);
+		const uint64_t len = base + ((uint64_t)d < rem ? 1 : 0);
+		if (cudaSetDevice(cd->device) != cudaSuccess) {
+			status[d] = SB_ERR_CUDA;
+			errors[d] = "cudaSetDevice failed";
+			return;
+		}
+		if (len == 0) {
+			return;
+		}
+		// at least ~6 chunks per device so that copy-in, probe and copy-out overlap inside the slice
+		uint64_t chunk = cd->pipe_chunk;
+		while (chunk > (1u << 20) && len < 6 * chunk) {
+			chunk >>= 1;
+		}
+		uint64_t mine = 0;
+		status[d] = join_points_boxes_pipelined(cd, pred, px + beg, py + beg, len, &views[d], boxes[d], n_boxes, out_probe,
+		                                        out_build, capacity, &mine, beg, &total, chunk);
+		if (status[d] != SB_OK) {
+			errors[d] = sb_last_error();
+		}
+		cudaStreamSynchronize(cd->stream);
+	};
+	for (int d = 1; d < n_ctx; d++) {
+		workers.emplace_back(work, d);
+	}
+	work(0);
+	for (auto &w : workers) {
+		w.join();
+	}
+	cudaSetDevice(c0->device);
+	cudaEventDestroy(built);
+	built = nullptr;
+	cudaStreamSynchronize(c0->stream);
+	sb_flat_destroy(tree);
+	*count = total.load();
+	for (int d = 0; d < n_ctx; d++) {
+		if (status[d] != SB_OK) {
+			sb_set_error("multi join, device %d: %s", ctxs[d]->device, errors[d].c_str());
+			return status[d];
+		}
+	}
+	if (*count > capacity) {
+		sb_set_error("join: %llu pairs, capacity %llu", (unsigned long long)*count, (unsigned long long)capacity);
+		return SB_ERR_CAPACITY;
+	}
+	return SB_OK;
+}
+

@@ -662,43 +662,62 @@ int sbi_rtree_export_pages(sb_context *ctx, const sb_rtree *tree, uint64_t block
 // ---- rtree_index_dump ------------------------------------------------------------------------------------------
 // (level, bounds, row_id) of every entry below the root entry in the DFS order of the reference's pragma
 // (rtree_index_pragmas.cpp:137-227 over RTreeScanner, rtree_scanner.hpp:38-83: the root node's entries are level 0, the
-// root entry itself is not emitted, an entry is followed by its whole subtree). The packed tree is complete -- node j
-// of a level is the entries [j * cap, (j + 1) * cap) of the level below -- so the DFS position of entry i of stored
-// level l is a closed form and every entry is written by its own thread:
-//   pos = sum over the levels m above l (below the root entry) of (i / cap^(m-l) + 1)      ancestors and their elder siblings' heads
-//       + i                                                                                 earlier entries of level l
-//       + sum over the levels m below l of min(i * cap^(l-m), count[m])                      descendants of earlier entries
+// root entry itself is not emitted, an entry is followed by its whole subtree). Node c of stored level l is the
+// entries [c * cap, (c + 1) * cap) of that level; the entry of level l + 1 that owns it carries c in its pointer (upper
+// levels are re-sorted by STR, so it is NOT entry c). Three data-parallel sweeps instead of a recursion:
+//   sizes   bottom-up: size(l, i) = 1 + sum of the sizes of the entries of its child node
+//   places  top-down : the entries of a node follow their parent entry, each after its elder siblings' subtrees
+//   write   every entry to its place
 struct dump_levels {
 	const sb_entry *lvl[16];
 	uint64_t count[16];
-	int top; // stored level of the root entry (not emitted)
+	uint64_t off[16]; // entry offset of the level inside the size / place arrays
+	int top;          // stored level of the root entry (not emitted)
 	uint32_t cap;
 };
 
-__global__ void __launch_bounds__(256) k_rtree_dump(dump_levels L, int l, int32_t *__restrict__ out_level,
-                                                    float4 *__restrict__ out_box, int64_t *__restrict__ out_row,
-                                                    uint64_t capacity) {
+__global__ void __launch_bounds__(256) k_dump_sizes(dump_levels L, int l, uint64_t *__restrict__ size) {
 	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
 	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < L.count[l]; i += stride) {
-		uint64_t pos = i;
-		uint64_t a = i;
-		for (int m = l + 1; m < L.top; m++) {
-			a /= L.cap;
-			pos += a + 1;
+		uint64_t sz = 1;
+		if (l > 0) {
+			const uint64_t c = L.lvl[l][i].ptr & 0x00FFFFFFFFFFFFFFull;
+			const uint64_t b = c * L.cap, e = min(b + L.cap, L.count[l - 1]);
+			for (uint64_t k = b; k < e; k++) {
+				sz += size[L.off[l - 1] + k];
+			}
 		}
-		uint64_t d = i;
-		for (int m = l - 1; m >= 0; m--) {
-			d = d > L.count[m] / L.cap + 1 ? L.count[m] : d * L.cap; // (saturating product)
-			pos += d < L.count[m] ? d : L.count[m];
+		size[L.off[l] + i] = sz;
+	}
+}
+
+// parents = entries of level l + 1 (the single root entry when l + 1 == top, whose children start at place 0)
+__global__ void __launch_bounds__(256) k_dump_places(dump_levels L, int l, const uint64_t *__restrict__ size,
+                                                     uint64_t *__restrict__ place) {
+	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+	for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < L.count[l + 1]; j += stride) {
+		uint64_t at = l + 1 == L.top ? 0 : place[L.off[l + 1] + j] + 1;
+		const uint64_t c = L.lvl[l + 1][j].ptr & 0x00FFFFFFFFFFFFFFull;
+		const uint64_t b = c * L.cap, e = min(b + L.cap, L.count[l]);
+		for (uint64_t k = b; k < e; k++) {
+			place[L.off[l] + k] = at;
+			at += size[L.off[l] + k];
 		}
-		if (pos < capacity) {
-			uint64_t ptr;
-			float4 b;
-			load_entry(L.lvl[l] + i, ptr, b);
-			out_level[pos] = L.top - 1 - l;
-			out_box[pos] = b;
-			out_row[pos] = l == 0 ? (int64_t)(ptr << 8) >> 8 : -1;
-		}
+	}
+}
+
+__global__ void __launch_bounds__(256) k_dump_write(dump_levels L, int l, const uint64_t *__restrict__ place,
+                                                    int32_t *__restrict__ out_level, float4 *__restrict__ out_box,
+                                                    int64_t *__restrict__ out_row) {
+	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < L.count[l]; i += stride) {
+		const uint64_t pos = place[L.off[l] + i];
+		uint64_t ptr;
+		float4 b;
+		load_entry(L.lvl[l] + i, ptr, b);
+		out_level[pos] = L.top - 1 - l;
+		out_box[pos] = b;
+		out_row[pos] = l == 0 ? (int64_t)(ptr & 0x00FFFFFFFFFFFFFFull) : -1; // RTreePointer::GetRowId of a ROW_ID pointer
 	}
 }
 
@@ -712,6 +731,7 @@ int sbi_rtree_dump(sb_context *ctx, const sb_rtree *tree, int32_t *out_level, fl
 	for (int l = 0; l < tree->nlevels; l++) {
 		L.lvl[l] = tree->entries + tree->offsets[l];
 		L.count[l] = tree->counts[l];
+		L.off[l] = tree->offsets[l];
 		if (l < L.top) {
 			total += tree->counts[l];
 		}
@@ -721,10 +741,23 @@ int sbi_rtree_dump(sb_context *ctx, const sb_rtree *tree, int32_t *out_level, fl
 		sb_set_error("rtree dump: %llu rows, capacity %llu", (unsigned long long)total, (unsigned long long)capacity);
 		return SB_ERR_CAPACITY;
 	}
+	if (total == 0) {
+		return SB_OK;
+	}
+	uint64_t *d_size = nullptr, *d_place = nullptr;
+	SB_TRY(ctx->scratch_t(tree->total, &d_size));
+	SB_TRY(ctx->scratch_t(tree->total, &d_place));
 	for (int l = 0; l < L.top; l++) {
-		k_rtree_dump<<<sb_grid(L.count[l], 256, 16), 256, 0, ctx->stream>>>(L, l, out_level,
-		                                                                      reinterpret_cast<float4 *>(out_box4), out_row,
-		                                                                      capacity);
+		k_dump_sizes<<<sb_grid(L.count[l], 256, 16), 256, 0, ctx->stream>>>(L, l, d_size);
+		SB_LAUNCH_CHECK(ctx);
+	}
+	for (int l = L.top - 1; l >= 0; l--) {
+		k_dump_places<<<sb_grid(L.count[l + 1], 256, 16), 256, 0, ctx->stream>>>(L, l, d_size, d_place);
+		SB_LAUNCH_CHECK(ctx);
+	}
+	for (int l = 0; l < L.top; l++) {
+		k_dump_write<<<sb_grid(L.count[l], 256, 16), 256, 0, ctx->stream>>>(L, l, d_place, out_level,
+		                                                                      reinterpret_cast<float4 *>(out_box4), out_row);
 		SB_LAUNCH_CHECK(ctx);
 	}
 	return SB_OK;

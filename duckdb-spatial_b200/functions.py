@@ -431,6 +431,29 @@ class Context:
             return oa[: cnt.value], ob[: cnt.value], od[: cnt.value]
 
 
+def spatial_join_points_boxes_multi(ctxs, px, py, bminx, bminy, bmaxx, bmaxy, predicate="intersects", capacity=None, out=None):
+    """ONE point x box join split over the devices of `ctxs` (contexts on distinct GPUs of this process): host (numpy or
+    pinned torch CPU) columns in, one unordered pair list out -> (probe rows, build rows)."""
+    arrs = [np.ascontiguousarray(v, np.float64) if not _is_torch(v) else v for v in (px, py, bminx, bminy, bmaxx, bmaxy)]
+    n, m = len(arrs[0]), len(arrs[2])
+    cap = int(capacity if capacity is not None else max(1024, 4 * n))
+    hs = (C.c_void_p * len(ctxs))(*[c.h for c in ctxs])
+    while True:
+        if out is not None:
+            op, ob = out
+            cap = len(op)
+        else:
+            op, ob = np.empty(cap, np.uint32), np.empty(cap, np.uint32)
+        cnt = C.c_uint64(0)
+        rc = ctxs[0].L.sb_join_points_boxes_multi(hs, len(ctxs), _pred_code(predicate), *[_ptr(v) for v in arrs[:2]], n,
+                                                  *[_ptr(v) for v in arrs[2:]], m, _ptr(op), _ptr(ob), cap, C.byref(cnt))
+        if rc == capi.ERR_CAPACITY and out is None:
+            cap = int(cnt.value)
+            continue
+        capi.check(rc)
+        return op[: cnt.value], ob[: cnt.value]
+
+
 class SpatialJoinOp:
     """PhysicalSpatialJoin for a streaming probe side (sb_join_op): the build side is finalized at construction,
     probe chunks (DuckDB: <= 2048 rows) are pushed and probed in device batches. Host (numpy) columns."""

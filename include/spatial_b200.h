@@ -298,6 +298,16 @@ SB_API int sb_join_points_boxes(sb_context *ctx, sb_mem mem, sb_predicate pred, 
                                 uint64_t n_points, const double *bmin_x, const double *bmin_y, const double *bmax_x,
                                 const double *bmax_y, uint32_t n_boxes, uint32_t *out_probe, uint32_t *out_build,
                                 uint64_t capacity, uint64_t *count);
+/* The same join driven over SEVERAL devices from one process -- what the single-process DuckDB operator
+ * (PhysicalSpatialJoin, spatial_join_physical.cpp:695-945) would call on a multi-GPU host. ctxs[0..n_ctx) are contexts
+ * on distinct devices. Host pointers only. Device ctxs[0] builds the FlatRTree; the packed tree and the build side's
+ * exact boxes are replicated to the other devices with peer copies (NVLink); every device streams a contiguous slice
+ * of the probe column through its own copy-in / probe / copy-out pipeline (one host thread per device, one PCIe link
+ * each) and all pair lists land in the caller's ONE pair list (unordered; probe row ids are global). */
+SB_API int sb_join_points_boxes_multi(sb_context *const *ctxs, int n_ctx, sb_predicate pred, const double *px,
+                                      const double *py, uint64_t n_points, const double *bmin_x, const double *bmin_y,
+                                      const double *bmax_x, const double *bmax_y, uint32_t n_boxes, uint32_t *out_probe,
+                                      uint32_t *out_build, uint64_t capacity, uint64_t *count);
 /* probe an existing tree with points and refine in the same kernel (multi-GPU path: tree was broadcast).
  * point indices emitted = probe_index_base + local index. */
 SB_API int sb_flat_probe_points(sb_context *ctx, const sb_flat *tree, sb_mem mem, sb_predicate pred, const double *px,

@@ -130,7 +130,7 @@ def test_rtree_dump_matches_oracle_dfs(ctx, sb, O, n, cap):
     # (tests/test_oracle_vs_refdb.py)
     x, y = O.generate_points(77, n, (0, 0, 1000, 1000))
     box = O.bbox_from_points(x, y)
-    rows = np.arange(n, dtype=np.int64) * 3 - 5
+    rows = np.arange(n, dtype=np.int64) * 3 + 5
     idx = sb.RTreeIndex(ctx, box, rows, cap)
     lv, b, rid = idx.dump()
     olv, obox, orid = O.StrTree(box, rows, cap).dump()
