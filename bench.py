@@ -634,9 +634,6 @@ def run_ours(a):
             if not run_e2e(a, result, ctx, capi, L, rank, world, dev, px, py, (bx0, by0, bx1, by1), cap, barrier, all_sum,
                            out_p, out_b, ref_prefix):
                 failures.append("e2e (host-pointer) pair set differs from the reference on the checked prefix")
-        clk = clocks.stop(tw0, clocks.mark()) if rank == 0 else None
-        result["clocks"] = clk
-
         # ---- CREATE INDEX side: STR bulk load of config C1 (10 M points), reported beside the headline --------
         if not a.no_index and rank == 0:
             n1 = 10_000_000
@@ -676,7 +673,49 @@ def run_ours(a):
                 if not okb:
                     failures.append("C1 index build differs from the reference's known answers")
             result["rtree_build"] = rb
+            if not a.no_extras:
+                import bench_extras as X
+
+                idx = build_index()
+                result["c1_scans"] = X.run_c1_scans(ctx, sb, torch, dev, stream, idx, ctx.bbox_from_points(ix, iy))
+                idx.close()
+                if not result["c1_scans"]["parity"]["ok"]:
+                    failures.append("C1 batched scans differ from brute force")
             del ix, iy, rows
+
+        # ---- the other BASELINE configs under the same clock record: C2 (rank 0), C4 (weak, all ranks), C5 (strong) ----
+        if not a.no_extras:
+            import bench_extras as X
+
+            import oracle as O
+
+            def all_max(v):
+                if world == 1:
+                    return float(v)
+                t = torch.tensor([float(v)], dtype=torch.float64, device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                return float(t.item())
+
+            del px, py, out_p, out_b
+            if world > 1:
+                del tree_buf, box2d
+            ctx.sync()
+            torch.cuda.empty_cache()
+            if rank == 0:
+                result["c2"] = X.run_c2(ctx, sb, torch, dev, stream, hbm_peak)
+                if not result["c2"]["parity"]["ok"]:
+                    failures.append("C2 extents / scans differ")
+                torch.cuda.empty_cache()
+            barrier()
+            result["c4"], ok4 = X.run_c4(ctx, sb, torch, dev, stream, O, rank, world, all_sum, all_max)
+            if not ok4:
+                failures.append("C4 pair sets differ (route agreement / oracle prefix)")
+            torch.cuda.empty_cache()
+            barrier()
+            result["c5"], ok5 = X.run_c5(ctx, sb, torch, dev, stream, rank, world, all_sum, all_max)
+            if not ok5:
+                failures.append("C5 radius join differs from brute force / tolerance")
+        result["clocks"] = clocks.stop(tw0, clocks.mark()) if rank == 0 else None
 
     # ---- CPU baselines (rank 0, N=1): the reference's own code on this box's host cores ---------------------------
     if rank == 0 and world == 1 and not a.no_cpu:

@@ -93,9 +93,9 @@ static int blob_call(sb_context *ctx, sb_mem mem, int which, const uint8_t *data
 	} else if (which == 1) {
 		SB_TRY(sbi_blob_bounds(ctx, 1, d_data, d_off, n, nullptr, d_key, d_valid, d_status, d_bad));
 	} else if (which == 2) {
-		SB_TRY(sbi_blob_extent(ctx, 0, d_data, d_off, n, d_d, d_valid, d_status, nullptr, nullptr, d_bad));
+		SB_TRY(sbi_blob_extent(ctx, 0, d_data, d_off, n, d_d, d_valid, d_status, nullptr, nullptr, d_bad, total / n));
 	} else {
-		SB_TRY(sbi_blob_extent(ctx, 1, d_data, d_off, n, nullptr, nullptr, d_status, bounds, d_key, d_bad));
+		SB_TRY(sbi_blob_extent(ctx, 1, d_data, d_off, n, nullptr, nullptr, d_status, bounds, d_key, d_bad, total / n));
 	}
 	SB_TRY(sb_to_host(ctx, mem, out_f, d_f, 4 * n));
 	SB_TRY(sb_to_host(ctx, mem, out_d, d_d, 4 * n));

@@ -10,7 +10,8 @@ int sbi_bbox_box2d(sb_context *ctx, const double *x0, const double *y0, const do
 int sbi_blob_bounds(sb_context *ctx, int mode, const uint8_t *data, const uint64_t *off, uint64_t n, float *out_box,
                     uint32_t *out_key, uint8_t *valid, int32_t *status, int *any_bad);
 int sbi_blob_extent(sb_context *ctx, int mode, const uint8_t *data, const uint64_t *off, uint64_t n, double *out_box,
-                    uint8_t *valid, int32_t *status, const double *bounds, uint32_t *out_key, int *any_bad);
+                    uint8_t *valid, int32_t *status, const double *bounds, uint32_t *out_key, int *any_bad,
+                    uint64_t avg_bytes = 0);
 int sbi_hilbert_xy(sb_context *ctx, const double *x, const double *y, uint64_t n, const double *b, uint32_t *out);
 int sbi_hilbert_box2d(sb_context *ctx, const double *box4, uint64_t n, const double *b, uint32_t *out);
 int sbi_hilbert_box2df(sb_context *ctx, const float *box4, uint64_t n, const float *b, uint32_t *out);
