@@ -294,3 +294,169 @@ RD_API int rd_create_table(void *hp, const char *name, int ncols, const char **c
 		return 1;
 	}
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// N2: a bulk-loaded tree handed over as FixedSizeAllocator block images (sb_rtree_export_pages / the oracle's
+// orc_rtree_export_pages) is loaded into the REFERENCE's RTree through the reference's own allocators, then the
+// reference's own scan / insert / delete code (rtree.cpp:73-592, rtree_scanner.hpp:38-83) runs on it.
+//   rd_rtree_load : allocates leaf_pages / branch_pages segments with FixedSizeAllocator::New() (the MakePage order of
+//   a fresh index), checks that every returned IndexPointer is the one the image assigned to that page, copies the page
+//   bodies in, compares the allocator's whole buffers (validity bitmask + segments) with the images byte for byte,
+//   and sets the root entry. *mismatch: 0 = identical, 1 = pointer sequence differs, 2 = buffer bytes differ.
+// ---------------------------------------------------------------------------------------------------------------
+#include "duckdb/storage/in_memory_block_manager.hpp"
+#include "duckdb/storage/buffer_manager.hpp"
+#include "spatial/index/rtree/rtree.hpp"
+#include "spatial/index/rtree/rtree_scanner.hpp"
+
+namespace {
+struct RdTree {
+	unique_ptr<InMemoryBlockManager> bm;
+	unique_ptr<RTree> tree;
+};
+} // namespace
+
+RD_API void *rd_rtree_load(void *hp, uint32_t cap, uint32_t min_cap, const uint8_t *leaf_img, uint64_t leaf_pages,
+                           const uint8_t *branch_img, uint64_t branch_pages, const void *root24, uint64_t block_size,
+                           int *mismatch) {
+	auto h = static_cast<RdDb *>(hp);
+	try {
+		*mismatch = 0;
+		auto t = new RdTree();
+		auto &buffer_manager = BufferManager::GetBufferManager(*h->db->instance);
+		t->bm = make_uniq<InMemoryBlockManager>(buffer_manager, optional_idx(block_size + 8), optional_idx(8));
+		RTreeConfig cfg;
+		cfg.max_node_capacity = cap;
+		cfg.min_node_capacity = min_cap;
+		t->tree = make_uniq<RTree>(*t->bm, cfg);
+		if (t->bm->GetBlockSize() != block_size) {
+			g_err = "block size " + std::to_string(t->bm->GetBlockSize()) + " != " + std::to_string(block_size);
+			delete t;
+			return nullptr;
+		}
+		const idx_t seg = cfg.GetNodeByteSize();
+		struct Side {
+			FixedSizeAllocator *alloc;
+			const uint8_t *img;
+			uint64_t pages;
+		} sides[2] = {{&t->tree->GetLeafAllocator(), leaf_img, leaf_pages}, {&t->tree->GetNodeAllocator(), branch_img, branch_pages}};
+		for (auto &s : sides) {
+			if (s.pages == 0) {
+				continue;
+			}
+			// the allocator's geometry (private fields; this TU is compiled with -fno-access-control)
+			const idx_t per_buffer = s.alloc->available_segments_per_buffer, bitmask_offset = s.alloc->bitmask_offset;
+			std::vector<IndexPointer> ptrs;
+			for (uint64_t k = 0; k < s.pages; k++) {
+				ptrs.push_back(s.alloc->New());
+			}
+			for (uint64_t k = 0; k < s.pages; k++) {
+				const idx_t want_buf = k / per_buffer, want_off = k % per_buffer;
+				if (ptrs[k].GetBufferId() != want_buf || ptrs[k].GetOffset() != want_off) {
+					*mismatch = 1; // the image numbered its pages differently from FixedSizeAllocator::New()
+				}
+				memcpy(s.alloc->Get(ptrs[k], true), s.img + want_buf * block_size + bitmask_offset + want_off * seg, seg);
+			}
+			// whole buffers: validity bitmask + segments, byte for byte
+			const uint64_t nbuf = (s.pages + per_buffer - 1) / per_buffer;
+			for (uint64_t b = 0; b < nbuf && *mismatch == 0; b++) {
+				const data_ptr_t base = s.alloc->Get(ptrs[b * per_buffer], false) - bitmask_offset;
+				const uint64_t in_buf = std::min<uint64_t>(per_buffer, s.pages - b * per_buffer);
+				if (memcmp(base, s.img + b * block_size, bitmask_offset + in_buf * seg) != 0) {
+					*mismatch = 2;
+				}
+			}
+		}
+		RTreeEntry root;
+		memcpy(&root, root24, sizeof(RTreeEntry));
+		t->tree->SetRoot(root);
+		return t;
+	} catch (std::exception &e) {
+		g_err = e.what();
+		return nullptr;
+	}
+}
+
+RD_API void rd_rtree_free(void *tp) {
+	delete static_cast<RdTree *>(tp);
+}
+
+// DFS dump through the reference's RTreeScanner (what rtree_index_dump does); returns rows (arrays may be NULL)
+RD_API uint64_t rd_rtree_dump(void *tp, int32_t *lvl, float *box4, int64_t *rid, uint64_t cap) {
+	auto t = static_cast<RdTree *>(tp);
+	uint64_t n = 0;
+	if (!t->tree->GetRoot().pointer.IsSet()) {
+		return 0;
+	}
+	RTreeScanner sc;
+	sc.Init(t->tree->GetRoot());
+	sc.Scan(*t->tree, [&](const RTreeEntry &e, const idx_t &level) {
+		if (lvl && n < cap) {
+			lvl[n] = (int32_t)level;
+			memcpy(box4 + 4 * n, &e.bounds, 16);
+			rid[n] = e.pointer.IsRowId() ? e.pointer.GetRowId() : -1;
+		}
+		n++;
+		return RTreeScanResult::CONTINUE;
+	});
+	return n;
+}
+
+// box scan like RTreeIndex::Scan (rtree_index.cpp:106-139): row ids of leaf entries intersecting q
+RD_API uint64_t rd_rtree_scan(void *tp, const float *q, int64_t *out, uint64_t cap) {
+	auto t = static_cast<RdTree *>(tp);
+	RTreeBounds qb;
+	memcpy(&qb, q, 16);
+	uint64_t n = 0;
+	auto &root = t->tree->GetRoot();
+	if (!root.pointer.IsSet() || !qb.Intersects(root.bounds)) {
+		return 0;
+	}
+	RTreeScanner sc;
+	sc.Init(root);
+	sc.Scan(*t->tree, [&](const RTreeEntry &e, const idx_t &) {
+		if (!e.bounds.Intersects(qb)) {
+			return RTreeScanResult::SKIP;
+		}
+		if (e.pointer.IsRowId()) {
+			if (n < cap) {
+				out[n] = e.pointer.GetRowId();
+			}
+			n++;
+		}
+		return RTreeScanResult::CONTINUE;
+	});
+	return n;
+}
+
+RD_API int rd_rtree_insert(void *tp, const float *box4, const int64_t *rid, uint64_t n) {
+	auto t = static_cast<RdTree *>(tp);
+	try {
+		for (uint64_t i = 0; i < n; i++) {
+			RTreeEntry e;
+			e.pointer = RTree::MakeRowId(rid[i]);
+			memcpy(&e.bounds, box4 + 4 * i, 16);
+			t->tree->Insert(e);
+		}
+		return 0;
+	} catch (std::exception &ex) {
+		g_err = ex.what();
+		return 1;
+	}
+}
+
+RD_API int rd_rtree_delete(void *tp, const float *box4, const int64_t *rid, uint64_t n) {
+	auto t = static_cast<RdTree *>(tp);
+	try {
+		for (uint64_t i = 0; i < n; i++) {
+			RTreeEntry e;
+			e.pointer = RTree::MakeRowId(rid[i]);
+			memcpy(&e.bounds, box4 + 4 * i, 16);
+			t->tree->Delete(e);
+		}
+		return 0;
+	} catch (std::exception &ex) {
+		g_err = ex.what();
+		return 1;
+	}
+}

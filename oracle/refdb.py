@@ -121,3 +121,63 @@ class RefDB:
             "SELECT level, ST_XMin(bounds), ST_YMin(bounds), ST_XMax(bounds), ST_YMax(bounds), row_id FROM rtree_index_dump('%s')" % index,
             "iffffi")
         return lv, np.stack([x0, y0, x1, y1], 1).astype(np.float32), rid
+
+
+class RefRTree:
+    """A bulk-loaded tree given as FixedSizeAllocator block images, loaded into the REFERENCE's RTree through the
+    reference's own allocators (rd_rtree_load); scan / insert / delete run the reference's rtree.cpp on it."""
+
+    def __init__(self, db, cap, leaf_img, leaf_pages, branch_img, branch_pages, root24, block_size=262136, min_cap=None):
+        self.L = db.L
+        self.db = db
+        leaf_img = np.ascontiguousarray(leaf_img, np.uint8)
+        branch_img = np.ascontiguousarray(branch_img, np.uint8)
+        root24 = np.ascontiguousarray(root24, np.uint8)
+        mm = C.c_int(0)
+        self.L.rd_rtree_load.restype = C.c_void_p
+        self.L.rd_rtree_dump.restype = C.c_uint64
+        self.L.rd_rtree_scan.restype = C.c_uint64
+        u8p = C.POINTER(C.c_uint8)
+        self.h = self.L.rd_rtree_load(C.c_void_p(db.h), C.c_uint32(cap), C.c_uint32(min_cap or max(cap // 2, 1)),
+                                      leaf_img.ctypes.data_as(u8p), C.c_uint64(leaf_pages), branch_img.ctypes.data_as(u8p),
+                                      C.c_uint64(branch_pages), root24.ctypes.data_as(u8p), C.c_uint64(block_size), C.byref(mm))
+        if not self.h:
+            raise RuntimeError("rd_rtree_load: " + self.L.rd_last_error().decode())
+        self.mismatch = mm.value
+
+    def close(self):
+        if self.h:
+            self.L.rd_rtree_free(C.c_void_p(self.h))
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def dump(self):
+        n = self.L.rd_rtree_dump(C.c_void_p(self.h), None, None, None, C.c_uint64(0))
+        lv, box, rid = np.empty(n, np.int32), np.empty((n, 4), np.float32), np.empty(n, np.int64)
+        self.L.rd_rtree_dump(C.c_void_p(self.h), lv.ctypes.data_as(C.POINTER(C.c_int32)), box.ctypes.data_as(C.POINTER(C.c_float)),
+                             rid.ctypes.data_as(C.POINTER(C.c_int64)), C.c_uint64(n))
+        return lv, box, rid
+
+    def scan(self, qbox):
+        q = np.ascontiguousarray(qbox, np.float32)
+        n = self.L.rd_rtree_scan(C.c_void_p(self.h), q.ctypes.data_as(C.POINTER(C.c_float)), None, C.c_uint64(0))
+        out = np.empty(n, np.int64)
+        self.L.rd_rtree_scan(C.c_void_p(self.h), q.ctypes.data_as(C.POINTER(C.c_float)), out.ctypes.data_as(C.POINTER(C.c_int64)), C.c_uint64(n))
+        return out
+
+    def _mut(self, fn, box4, rid):
+        b = np.ascontiguousarray(box4, np.float32).reshape(-1, 4)
+        r = np.ascontiguousarray(rid, np.int64)
+        if fn(C.c_void_p(self.h), b.ctypes.data_as(C.POINTER(C.c_float)), r.ctypes.data_as(C.POINTER(C.c_int64)), C.c_uint64(len(r))):
+            raise RuntimeError(self.L.rd_last_error().decode())
+
+    def insert(self, box4, rid):
+        self._mut(self.L.rd_rtree_insert, box4, rid)
+
+    def delete(self, box4, rid):
+        self._mut(self.L.rd_rtree_delete, box4, rid)
