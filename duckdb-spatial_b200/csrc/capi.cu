@@ -3,6 +3,8 @@
 // calls only enqueue work (except where a count has to be returned).
 #include "internal.cuh"
 
+#include <math.h>
+
 #include <atomic>
 #include <string>
 #include <thread>
@@ -382,6 +384,54 @@ extern "C" int sb_rtree_build_str(sb_context *ctx, sb_mem mem, const float *box4
 	SB_TRY(sb_to_device(ctx, mem, row_ids, n, &dr));
 	sb_rtree *t = nullptr;
 	int s = sbi_rtree_build_str(ctx, db, dr, n, max_node_capacity, &t);
+	if (s != SB_OK) {
+		if (t) {
+			sb_rtree_destroy(t);
+		}
+		return s;
+	}
+	*out = t;
+	return finish(ctx, mem);
+}
+
+extern "C" uint64_t sb_rtree_slice_for(uint64_t n, uint32_t max_node_capacity) {
+	if (n == 0 || max_node_capacity == 0) {
+		return 0;
+	}
+	const uint64_t cap = max_node_capacity;
+	return (uint64_t)ceil(sqrt((double)((n + cap - 1) / cap))) * cap;
+}
+
+extern "C" int sb_rtree_build_leaf_shard(sb_context *ctx, sb_mem mem, const float *box4, const int64_t *row_ids,
+                                         uint64_t n_shard, uint32_t max_node_capacity, uint64_t slice_size,
+                                         uint64_t node_base, void *out_leaf_entries, void *out_node_entries) {
+	SB_BEGIN(ctx);
+	SB_ARG(n_shard == 0 || (box4 && row_ids && out_leaf_entries && out_node_entries), "arrays");
+	const uint64_t nodes = (n_shard + max_node_capacity - 1) / (max_node_capacity ? max_node_capacity : 1);
+	const float *db;
+	const int64_t *dr;
+	sb_entry *d0, *d1;
+	SB_TRY(sb_to_device(ctx, mem, box4, 4 * n_shard, &db));
+	SB_TRY(sb_to_device(ctx, mem, row_ids, n_shard, &dr));
+	SB_TRY(sb_out_buffer(ctx, mem, static_cast<sb_entry *>(out_leaf_entries), n_shard, &d0));
+	SB_TRY(sb_out_buffer(ctx, mem, static_cast<sb_entry *>(out_node_entries), nodes, &d1));
+	SB_TRY(sbi_rtree_leaf_shard(ctx, db, dr, n_shard, max_node_capacity, slice_size, node_base, d0, d1));
+	SB_TRY(sb_to_host(ctx, mem, static_cast<sb_entry *>(out_leaf_entries), d0, n_shard));
+	SB_TRY(sb_to_host(ctx, mem, static_cast<sb_entry *>(out_node_entries), d1, nodes));
+	return finish(ctx, mem);
+}
+
+extern "C" int sb_rtree_from_leaf_level(sb_context *ctx, sb_mem mem, const void *leaf_entries, uint64_t n,
+                                        const void *node_entries, uint32_t max_node_capacity, sb_rtree **out) {
+	SB_BEGIN(ctx);
+	SB_ARG(out != nullptr && leaf_entries != nullptr && node_entries != nullptr, "out/entries");
+	*out = nullptr;
+	const uint64_t nodes = (n + max_node_capacity - 1) / (max_node_capacity ? max_node_capacity : 1);
+	const sb_entry *d0, *d1;
+	SB_TRY(sb_to_device(ctx, mem, static_cast<const sb_entry *>(leaf_entries), n, &d0));
+	SB_TRY(sb_to_device(ctx, mem, static_cast<const sb_entry *>(node_entries), nodes, &d1));
+	sb_rtree *t = nullptr;
+	int s = sbi_rtree_from_leaf_level(ctx, d0, n, d1, max_node_capacity, &t);
 	if (s != SB_OK) {
 		if (t) {
 			sb_rtree_destroy(t);

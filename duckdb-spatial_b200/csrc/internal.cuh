@@ -77,6 +77,10 @@ struct sb_flat {
 // rtree_str.cu
 int sbi_rtree_build_str(sb_context *ctx, const float *box4, const int64_t *row_ids, uint64_t n, uint32_t cap,
                         sb_rtree **out);
+int sbi_rtree_leaf_shard(sb_context *ctx, const float *box4, const int64_t *row_ids, uint64_t n, uint32_t cap,
+                         uint64_t slice, uint64_t node_base, sb_entry *level0, sb_entry *parents);
+int sbi_rtree_from_leaf_level(sb_context *ctx, const sb_entry *level0, uint64_t n, const sb_entry *nodes_in, uint32_t cap,
+                              sb_rtree **out);
 int sbi_rtree_scan(sb_context *ctx, const sb_rtree *tree, const float *qbox4, uint32_t nq, uint32_t *out_query,
                    int64_t *out_row, uint64_t capacity, uint64_t *count);
 

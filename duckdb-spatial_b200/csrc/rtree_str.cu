@@ -57,7 +57,7 @@ template <bool LEAF>
 __global__ void __launch_bounds__(256)
     k_str_pack(const float4 *__restrict__ box, const int64_t *__restrict__ row_ids, const sb_entry *__restrict__ cur,
                const uint32_t *__restrict__ perm, uint64_t count, uint32_t cap, sb_entry *__restrict__ level_out,
-               sb_entry *__restrict__ parent_out, uint64_t parent_type) {
+               sb_entry *__restrict__ parent_out, uint64_t parent_type, uint64_t node_base) {
 	__shared__ int64_t s_row[256];
 	__shared__ uint64_t s_words[256 * 3];
 	__shared__ float s_red[8][4];
@@ -148,7 +148,7 @@ __global__ void __launch_bounds__(256)
 			u3 = fmaxf(u3, s_red[w][3]);
 		}
 		sb_entry p;
-		p.ptr = (parent_type << 56) | node;
+		p.ptr = (parent_type << 56) | (node_base + node);
 		p.box[0] = u0, p.box[1] = u1, p.box[2] = u2, p.box[3] = u3;
 		parent_out[node] = p;
 	}
@@ -205,20 +205,10 @@ __global__ void __launch_bounds__(1024)
 	}
 }
 
-int sbi_rtree_build_str(sb_context *ctx, const float *box4, const int64_t *row_ids, uint64_t n, uint32_t cap,
-                        sb_rtree **out) {
-	SB_ARG(cap >= 4 && cap <= 255, "max_node_capacity must be in [4, 255]");
-	SB_ARG(n < ((uint64_t)1 << 30), "n must be < 2^30");
-	sb_rtree *t = new sb_rtree();
-	t->device = ctx->device;
-	t->cap = cap;
-	*out = t;
-	if (n == 0) {
-		return SB_OK;
-	}
+// level sizes, offsets and the slice size are pure functions of (n, cap)
+static void str_shape(sb_rtree *t, uint64_t n, uint32_t cap) {
 	// Finalize: slice = ceil(sqrt(ceil(n / cap))) * cap, rtree_index_create_physical.cpp:349-351
 	t->slice = (uint64_t)ceil(sqrt((double)((n + cap - 1) / cap))) * cap;
-	// level sizes are a pure function of (n, cap)
 	uint64_t cnt = n;
 	int nl = 0;
 	uint64_t total = 0;
@@ -234,12 +224,17 @@ int sbi_rtree_build_str(sb_context *ctx, const float *box4, const int64_t *row_i
 	}
 	t->nlevels = nl;
 	t->total = total;
-	SB_CUDA(sb_pool_alloc(ctx, (void **)&t->entries, total * sizeof(sb_entry)));
-	t->owner = ctx;
+}
 
-	const float4 *box = reinterpret_cast<const float4 *>(box4);
+// Leaf level of (a shard of) the layer: ORDER BY x centre (stable), y-sort inside runs of `slice` positions, pack `cap`
+// per node with the entries ordered by row id. level0 receives the n leaf entries, parents one entry per node whose
+// pointer is (LEAF_PAGE << 56) | (node_base + node). With node_base = 0 and the whole layer this is the first stage
+// of the build; a shard that is a contiguous, slice-aligned range of the global x order produces exactly its part of
+// the global leaf level (multi-GPU build).
+static int str_leaf_level(sb_context *ctx, const float4 *box, const int64_t *row_ids, uint64_t n, uint32_t cap,
+                          uint64_t slice, uint64_t node_base, sb_entry *level0, sb_entry *parents, uint32_t **yk_out,
+                          uint32_t **ykb_out, uint32_t **yv_out, uint32_t **yvb_out) {
 	const unsigned block = ((cap + 31) / 32) * 32;
-
 	// --- ORDER BY x centre ---------------------------------------------------------------------------------
 	uint32_t *k32 = nullptr, *k32b = nullptr, *v32 = nullptr, *v32b = nullptr;
 	SB_TRY(ctx->scratch_t(n, &k32));
@@ -258,7 +253,7 @@ int sbi_rtree_build_str(sb_context *ctx, const float *box4, const int64_t *row_i
 	const uint32_t *xperm = alt ? v32b : v32;
 	uint32_t *free_v = alt ? v32 : v32b; // the other value buffer is reusable
 
-	// --- level 0: y-sort inside slices, pack leaves ---------------------------------------------------------
+	// --- y-sort inside slices, pack leaves --------------------------------------------------------------------
 	// segmented sort: every slice of the x order is sorted by y on its own (4 passes over 32-bit keys; a 64-bit
 	// (slice, y) key sort needed 6)
 	uint32_t *yk = k32, *ykb = k32b; // dead after the x sort
@@ -269,21 +264,28 @@ int sbi_rtree_build_str(sb_context *ctx, const float *box4, const int64_t *row_i
 		k_str_ykeys_leaf<<<sb_grid(n, 256, 16), 256, 0, ctx->stream>>>(yk_in, xperm, n, yk, yv);
 		SB_LAUNCH_CHECK(ctx);
 	}
-	SB_TRY(sbi_radix_sort_u32_segmented(ctx, yk, ykb, yv, yvb, n, t->slice, 0, 32, false, &alt));
+	SB_TRY(sbi_radix_sort_u32_segmented(ctx, yk, ykb, yv, yvb, n, slice, 0, 32, false, &alt));
 	const uint32_t *perm = alt ? yvb : yv;
-
-	uint64_t nodes = (n + cap - 1) / cap;
-	sb_entry *parents = nullptr, *parents_b = nullptr;
-	SB_TRY(ctx->scratch_t(nodes, &parents));
-	SB_TRY(ctx->scratch_t((nodes + cap - 1) / cap + 1, &parents_b));
+	const uint64_t nodes = (n + cap - 1) / cap;
 	{
 		sb_prof_scope ps(ctx, "str_pack");
-		k_str_pack<true><<<(unsigned)nodes, block, 0, ctx->stream>>>(box, row_ids, nullptr, perm, n, cap,
-		                                                            t->entries + t->offsets[0], parents, 1ull);
+		k_str_pack<true><<<(unsigned)nodes, block, 0, ctx->stream>>>(box, row_ids, nullptr, perm, n, cap, level0, parents,
+		                                                            1ull, node_base);
 		SB_LAUNCH_CHECK(ctx);
 	}
-	// --- upper levels ------------------------------------------------------------------------------------------
-	for (int level = 1; level < nl; level++) {
+	*yk_out = yk, *ykb_out = ykb, *yv_out = yv, *yvb_out = yvb;
+	return SB_OK;
+}
+
+// Levels >= 1 from the node entries of the leaf level (in node order): per level y-sort inside runs of `slice`, pack.
+// parents / parents_b: ping-pong buffers (parents holds counts[1] entries on entry); yk .. yvb: sort scratch of at
+// least counts[1] words each.
+static int str_upper_levels(sb_context *ctx, sb_rtree *t, sb_entry *parents, sb_entry *parents_b, uint32_t *yk,
+                            uint32_t *ykb, uint32_t *yv, uint32_t *yvb) {
+	const uint32_t cap = t->cap;
+	const unsigned block = ((cap + 31) / 32) * 32;
+	int alt = 0;
+	for (int level = 1; level < t->nlevels; level++) {
 		const uint64_t c = t->counts[level];
 		if (c == 1) {
 			SB_CUDA(cudaMemcpyAsync(t->entries + t->offsets[level], parents, sizeof(sb_entry), cudaMemcpyDeviceToDevice,
@@ -311,7 +313,7 @@ int sbi_rtree_build_str(sb_context *ctx, const float *box4, const int64_t *row_i
 		{
 			sb_prof_scope ps(ctx, "str_pack");
 			k_str_pack<false><<<(unsigned)nn, block, 0, ctx->stream>>>(nullptr, nullptr, parents, p, c, cap,
-			                                                          t->entries + t->offsets[level], parents_b, 2ull);
+			                                                          t->entries + t->offsets[level], parents_b, 2ull, 0ull);
 			SB_LAUNCH_CHECK(ctx);
 		}
 		sb_entry *tmp = parents;
@@ -319,6 +321,72 @@ int sbi_rtree_build_str(sb_context *ctx, const float *box4, const int64_t *row_i
 		parents_b = tmp;
 	}
 	return SB_OK;
+}
+
+int sbi_rtree_build_str(sb_context *ctx, const float *box4, const int64_t *row_ids, uint64_t n, uint32_t cap,
+                        sb_rtree **out) {
+	SB_ARG(cap >= 4 && cap <= 255, "max_node_capacity must be in [4, 255]");
+	SB_ARG(n < ((uint64_t)1 << 30), "n must be < 2^30");
+	sb_rtree *t = new sb_rtree();
+	t->device = ctx->device;
+	t->cap = cap;
+	*out = t;
+	if (n == 0) {
+		return SB_OK;
+	}
+	str_shape(t, n, cap);
+	SB_CUDA(sb_pool_alloc(ctx, (void **)&t->entries, t->total * sizeof(sb_entry)));
+	t->owner = ctx;
+	const uint64_t nodes = (n + cap - 1) / cap;
+	sb_entry *parents = nullptr, *parents_b = nullptr;
+	SB_TRY(ctx->scratch_t(nodes, &parents));
+	SB_TRY(ctx->scratch_t((nodes + cap - 1) / cap + 1, &parents_b));
+	uint32_t *yk, *ykb, *yv, *yvb;
+	SB_TRY(str_leaf_level(ctx, reinterpret_cast<const float4 *>(box4), row_ids, n, cap, t->slice, 0, t->entries + t->offsets[0],
+	                      parents, &yk, &ykb, &yv, &yvb));
+	return str_upper_levels(ctx, t, parents, parents_b, yk, ykb, yv, yvb);
+}
+
+// ---- multi-GPU build: the leaf level is built shard by shard, the upper levels from the gathered nodes ----
+// shard = a contiguous range of the GLOBAL x order (ties by global input position) that starts at a multiple of
+// `slice` positions; slice = the global slice size (sb_rtree_slice_for); node_base = global index of the shard's first node.
+int sbi_rtree_leaf_shard(sb_context *ctx, const float *box4, const int64_t *row_ids, uint64_t n, uint32_t cap,
+                         uint64_t slice, uint64_t node_base, sb_entry *level0, sb_entry *parents) {
+	SB_ARG(cap >= 4 && cap <= 255, "max_node_capacity must be in [4, 255]");
+	SB_ARG(n < ((uint64_t)1 << 30), "n must be < 2^30");
+	SB_ARG(slice >= cap && slice % cap == 0, "slice must be a multiple of the node capacity");
+	if (n == 0) {
+		return SB_OK;
+	}
+	uint32_t *yk, *ykb, *yv, *yvb;
+	return str_leaf_level(ctx, reinterpret_cast<const float4 *>(box4), row_ids, n, cap, slice, node_base, level0, parents,
+	                      &yk, &ykb, &yv, &yvb);
+}
+
+// the whole tree from its leaf entries (global order) and the leaf nodes' entries (node order)
+int sbi_rtree_from_leaf_level(sb_context *ctx, const sb_entry *level0, uint64_t n, const sb_entry *nodes_in, uint32_t cap,
+                              sb_rtree **out) {
+	SB_ARG(cap >= 4 && cap <= 255, "max_node_capacity must be in [4, 255]");
+	SB_ARG(n > 0 && n < ((uint64_t)1 << 30), "n must be in (0, 2^30)");
+	sb_rtree *t = new sb_rtree();
+	t->device = ctx->device;
+	t->cap = cap;
+	*out = t;
+	str_shape(t, n, cap);
+	SB_CUDA(sb_pool_alloc(ctx, (void **)&t->entries, t->total * sizeof(sb_entry)));
+	t->owner = ctx;
+	const uint64_t nodes = (n + cap - 1) / cap;
+	SB_CUDA(cudaMemcpyAsync(t->entries, level0, n * sizeof(sb_entry), cudaMemcpyDeviceToDevice, ctx->stream));
+	sb_entry *parents = nullptr, *parents_b = nullptr;
+	uint32_t *yk = nullptr, *ykb = nullptr, *yv = nullptr, *yvb = nullptr;
+	SB_TRY(ctx->scratch_t(nodes, &parents));
+	SB_TRY(ctx->scratch_t((nodes + cap - 1) / cap + 1, &parents_b));
+	SB_TRY(ctx->scratch_t(nodes, &yk));
+	SB_TRY(ctx->scratch_t(nodes, &ykb));
+	SB_TRY(ctx->scratch_t(nodes, &yv));
+	SB_TRY(ctx->scratch_t(nodes, &yvb));
+	SB_CUDA(cudaMemcpyAsync(parents, nodes_in, nodes * sizeof(sb_entry), cudaMemcpyDeviceToDevice, ctx->stream));
+	return str_upper_levels(ctx, t, parents, parents_b, yk, ykb, yv, yvb);
 }
 
 // ---------------------------------------------------------------------------------------------------------------

@@ -90,3 +90,113 @@ def sharded_join(n_probe, build_tree, probe_slice, src=0):
     b, e = shard_range(n_probe, rank, world)
     pp, pb = probe_slice(tree, boxes, b, e)
     return gather_pairs(pp, pb, src)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Multi-GPU CREATE INDEX: distributed sample sort of the ORDER BY + per-rank leaf level
+# ---------------------------------------------------------------------------------------------------------------
+def str_slice_size(n, cap):
+    """Finalize, rtree_index_create_physical.cpp:349-351: ceil(sqrt(ceil(n / cap))) * cap (= sb_rtree_slice_for)"""
+    import math
+
+    return int(math.ceil(math.sqrt(float((n + cap - 1) // cap)))) * cap if n else 0
+
+
+def str_x_sort_key(box4):
+    """order-preserving 32-bit key of the STR x order, as int64: bits of float32(min_x + max_x) (fp32 add,
+    ST_Centroid::ExecuteBox<float>, spatial_functions_scalar.cpp:1490-1494; the fp64 x 0.5 is monotone), -0 folded on +0"""
+    f = (box4[:, 0] + box4[:, 2]) + 0.0
+    r = f.contiguous().view(torch.int32).to(torch.int64) & 0xFFFFFFFF
+    neg = r >= 0x80000000
+    return torch.where(neg, 0xFFFFFFFF - r, r | 0x80000000)
+
+
+def exact_splitters(sorted_keys, targets):
+    """smallest key values K_j with exactly targets[j] keys (over ALL ranks) below them. sorted_keys: this rank's keys,
+    ascending, distinct across ranks, in [0, 2^63). 63 rounds of bisection, one all-reduce of len(targets) counts each."""
+    dev = sorted_keys.device
+    t = torch.tensor(list(targets), dtype=torch.int64, device=dev)
+    lo = torch.zeros_like(t)
+    hi = torch.full_like(t, (1 << 63) - 1)
+    for _ in range(63):
+        mid = lo + (hi - lo) // 2
+        cnt = torch.searchsorted(sorted_keys, mid, right=False).to(torch.int64)  # keys < mid on this rank
+        dist.all_reduce(cnt)
+        ge = cnt >= t
+        hi = torch.where(ge, mid, hi)
+        lo = torch.where(ge, lo, mid + 1)
+    return lo
+
+
+def gather_rows(t, dst=0):
+    """gather variable-length first-dimension slices of a tensor to `dst` (rank order) -> tensor on dst, None elsewhere"""
+    rank, world = dist.get_rank(), dist.get_world_size()
+    mine = torch.tensor([t.shape[0]], dtype=torch.int64, device=t.device)
+    counts = torch.zeros(world, dtype=torch.int64, device=t.device)
+    dist.all_gather_into_tensor(counts, mine)
+    cl = [int(c) for c in counts.tolist()]
+    if rank == dst:
+        out = torch.empty((sum(cl),) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+        ops, o = [], 0
+        for r in range(world):
+            if r == dst:
+                out[o : o + cl[r]].copy_(t)
+            elif cl[r]:
+                ops.append(dist.P2POp(dist.irecv, out[o : o + cl[r]], r))
+            o += cl[r]
+    else:
+        out, ops = None, ([dist.P2POp(dist.isend, t.contiguous(), dst)] if cl[rank] else [])
+    if ops:
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+    return out
+
+
+def sharded_rtree_build(box4, row_ids, cap, sort_keys, leaf_shard, assemble, dst=0):
+    """CREATE INDEX over a (box, row id) column that is sharded over the ranks, identical -- node for node -- to the
+    single-device STR bulk load of the concatenated column (rank order = input order).
+
+    box4 [n_r, 4] float32, row_ids [n_r] int64: this rank's rows.
+    sort_keys(keys int64) -> (sorted keys, permutation int64)        device sort of 63-bit keys
+    leaf_shard(box4, row_ids, cap, slice, node_base) -> (leaf entries uint8 [n, 24], node entries uint8 [nodes, 24])
+    assemble(leaf entries, n, node entries, cap) -> the tree (called on `dst` only)
+    Steps: x keys -> globally unique 63-bit keys (x key, global input position) -> exact, slice-aligned splitters by
+    bisection -> all-to-all of the rows -> local order -> leaf level of the rank's slices -> gather -> upper levels."""
+    rank, world = dist.get_rank(), dist.get_world_size()
+    dev = box4.device
+    n_r = box4.shape[0]
+    counts = torch.zeros(world, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(counts, torch.tensor([n_r], dtype=torch.int64, device=dev))
+    cl = [int(c) for c in counts.tolist()]
+    n, g0 = sum(cl), sum(cl[:rank])
+    assert 0 < n < (1 << 30), "row count"
+    slice_size = str_slice_size(n, cap)
+    n_slices = (n + slice_size - 1) // slice_size
+    chunk = ((n_slices + world - 1) // world) * slice_size  # rows per rank in the global x order: whole slices
+    keys = (str_x_sort_key(box4) << 31) | (g0 + torch.arange(n_r, dtype=torch.int64, device=dev))
+    skeys, perm = sort_keys(keys)
+    targets = [min(r * chunk, n) for r in range(1, world)]
+    cuts = torch.searchsorted(skeys, exact_splitters(skeys, targets), right=False).tolist() if world > 1 else []
+    send = [b - a for a, b in zip([0] + cuts, cuts + [n_r])]
+    recv_t = torch.zeros(world, dtype=torch.int64, device=dev)
+    dist.all_to_all_single(recv_t, torch.tensor(send, dtype=torch.int64, device=dev))
+    recv = [int(c) for c in recv_t.tolist()]
+    m = sum(recv)
+
+    def exchange(t):
+        out = torch.empty((m,) + tuple(t.shape[1:]), dtype=t.dtype, device=dev)
+        dist.all_to_all_single(out, t.contiguous(), output_split_sizes=recv, input_split_sizes=send)
+        return out
+
+    rkeys = exchange(skeys)
+    rbox = exchange(box4[perm])
+    rrow = exchange(row_ids[perm])
+    _, order = sort_keys(rkeys)  # the received runs are sorted; one more sort merges them (ties by global position)
+    lo = min(rank * chunk, n)
+    assert m == min((rank + 1) * chunk, n) - lo, "exact splitters must give every rank its slice-aligned range"
+    leaf, nodes = leaf_shard(rbox[order].contiguous(), rrow[order].contiguous(), cap, slice_size, lo // cap)
+    leaf_all = gather_rows(leaf, dst)
+    nodes_all = gather_rows(nodes, dst)
+    if rank == dst:
+        return assemble(leaf_all, n, nodes_all, cap)
+    return None

@@ -532,6 +532,30 @@ class RTreeIndex:
         self.h = h
         self.cap = max_node_capacity
 
+    @staticmethod
+    def leaf_shard(ctx, box4, row_ids, max_node_capacity, slice_size, node_base):
+        """multi-GPU build, per rank: leaf entries + node entries (uint8 [., 24]) of a slice-aligned shard of the global x
+        order (sb_rtree_build_leaf_shard)."""
+        n = len(row_ids)
+        nodes = (n + max_node_capacity - 1) // max_node_capacity
+        leaf = ctx._empty(box4, (n, 24), np.uint8)
+        node = ctx._empty(box4, (nodes, 24), np.uint8)
+        capi.check(ctx.L.sb_rtree_build_leaf_shard(ctx.h, ctx._mem(box4, row_ids), _ptr(box4), _ptr(row_ids), n,
+                                                   max_node_capacity, slice_size, node_base, _ptr(leaf), _ptr(node)))
+        return leaf, node
+
+    @classmethod
+    def from_leaf_level(cls, ctx, leaf_entries, n, node_entries, max_node_capacity):
+        """multi-GPU build, on the gathering rank: the whole tree from all leaf entries and all leaf-page entries"""
+        self = cls.__new__(cls)
+        self.ctx = ctx
+        self.cap = max_node_capacity
+        h = C.c_void_p()
+        capi.check(ctx.L.sb_rtree_from_leaf_level(ctx.h, ctx._mem(leaf_entries, node_entries), _ptr(leaf_entries), n,
+                                                  _ptr(node_entries), max_node_capacity, C.byref(h)))
+        self.h = h
+        return self
+
     @classmethod
     def from_blobs(cls, ctx, data, offsets, row_ids=None, max_node_capacity=128):
         """CREATE INDEX ... USING RTREE over a serialized GEOMETRY column; rows without bounds are not indexed."""

@@ -157,6 +157,22 @@ SB_API int sb_sort_pairs_u64(sb_context *ctx, sb_mem mem, uint64_t *keys, uint32
  * does (rtree_index_create_logical.cpp:42-72). max_node_capacity in [4, 255] (rtree_index.cpp:30-63). */
 SB_API int sb_rtree_build_str(sb_context *ctx, sb_mem mem, const float *box4, const int64_t *row_ids, uint64_t n,
                               uint32_t max_node_capacity, sb_rtree **out);
+/* ---- multi-GPU CREATE INDEX (one process per GPU; the host side is duckdb-spatial_b200/distributed.py) ----------------
+ * The reference builds the index in one process (PhysicalCreateRTreeIndex, rtree_index_create_physical.cpp:95-256); past
+ * one GPU's memory the ORDER BY becomes a distributed sample sort: every rank ends up with a contiguous, slice-aligned
+ * range of the global x order (ties by global input position) and builds ITS part of the leaf level; the nodes' entries
+ * (one per leaf page) are gathered and the upper levels built from them. The result is the tree sb_rtree_build_str
+ * builds over the whole input, node for node.
+ *   sb_rtree_slice_for        the global slice size, Finalize :349-351: ceil(sqrt(ceil(n / cap))) * cap
+ *   sb_rtree_build_leaf_shard leaf entries (24 B x n_shard, shard order) + one node entry per leaf page, pointer =
+ *                             (LEAF_PAGE << 56) | (node_base + page); the shard must start at a multiple of slice_size
+ *   sb_rtree_from_leaf_level  the whole tree from all leaf entries (global order) and all node entries (page order) */
+SB_API uint64_t sb_rtree_slice_for(uint64_t n, uint32_t max_node_capacity);
+SB_API int sb_rtree_build_leaf_shard(sb_context *ctx, sb_mem mem, const float *box4, const int64_t *row_ids, uint64_t n_shard,
+                                     uint32_t max_node_capacity, uint64_t slice_size, uint64_t node_base,
+                                     void *out_leaf_entries, void *out_node_entries);
+SB_API int sb_rtree_from_leaf_level(sb_context *ctx, sb_mem mem, const void *leaf_entries, uint64_t n,
+                                    const void *node_entries, uint32_t max_node_capacity, sb_rtree **out);
 /* CREATE INDEX straight from the GEOMETRY key column: TryGetCachedBounds per row (geometry_type.hpp:102-148), rows
  * without bounds dropped as the planner's filter does (rtree_index_create_logical.cpp:42-72), then the same STR bulk
  * load -- the 64.2 B/key variant of the build (32 B blob + 8 B row id in, 24 B entry out). row_ids NULL = ordinals.

@@ -133,3 +133,69 @@ def test_nccl_sharded_join_gathered_pairs_vs_oracle(O):
     exp, _ = O.join_points_boxes(px, py, *b, pred=0)
     assert sum(counts) == len(exp)
     assert (sort_pairs(gp, gb) == sort_pairs(exp[:, 0], exp[:, 1])).all()
+
+
+def _build_worker(rank, world, port, n, cap, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
+    sys.path.insert(0, ROOT)
+    import importlib
+
+    import torch
+    import torch.distributed as dist
+
+    import oracle as O
+    import sb200
+
+    sb = sb200.load()
+    D = importlib.import_module("duckdb_spatial_b200.distributed")
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", device_id=dev)
+    ctx = sb.Context(rank)
+    ctx.use_torch_stream()
+    x, y = O.generate_points(31, n, (0, 0, 1000, 1000))
+    x = np.round(x, 2)  # equal x keys: ties follow the global input position
+    box = O.bbox_from_points(x, y)
+    rows = np.arange(n, dtype=np.int64) * 3 + 7
+    b, e = D.shard_range(n, rank, world)
+
+    def sort_keys(k):
+        kk = k.clone()
+        vv = torch.arange(len(k), dtype=torch.int32, device=dev)
+        ctx.sort_pairs(kk, vv)
+        return kk, vv.long()
+
+    tree = D.sharded_rtree_build(torch.from_numpy(box[b:e].copy()).to(dev), torch.from_numpy(rows[b:e].copy()).to(dev), cap, sort_keys,
+                                 lambda bx, rw, c, s, nb: sb.RTreeIndex.leaf_shard(ctx, bx, rw, c, s, nb),
+                                 lambda leaf, nn, nodes, c: sb.RTreeIndex.from_leaf_level(ctx, leaf, nn, nodes, c))
+    if rank == 0:
+        ref = sb.RTreeIndex(ctx, box, rows, cap)
+        same = tree.nlevels == ref.nlevels and all(np.array_equal(np.asarray(tree.level(l)), np.asarray(ref.level(l))) for l in range(ref.nlevels))
+        q.put(bool(same))
+        ref.close()
+        tree.close()
+    dist.barrier()
+    dist.destroy_process_group()
+    ctx.close()
+
+
+@pytest.mark.skipif(_ndev() < 2, reason="needs >= 2 GPUs")
+@pytest.mark.parametrize("n,cap", [(200_003, 16), (1_500_000, 128)])
+def test_nccl_sharded_rtree_build_equals_single_gpu_build(n, cap):
+    import torch.multiprocessing as mp
+
+    world = 2
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctxm = mp.get_context("spawn")
+    q = ctxm.Queue()
+    procs = [ctxm.Process(target=_build_worker, args=(r, world, port, n, cap, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    same = q.get(timeout=600)
+    for p in procs:
+        p.join(timeout=600)
+        assert p.exitcode == 0
+    assert same, "the sharded build differs from the single-GPU build of the concatenated input"
