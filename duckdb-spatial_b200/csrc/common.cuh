@@ -94,6 +94,10 @@ struct sb_context {
 	int probe_path = 0;
 	// sb_context_set_option("pip_path"): 0 = auto, 1 = FlatRTree candidates + per-pair refinement, 2 = polygon-centric
 	int pip_path = 0;
+	// sb_context_set_option("hist_sample"): 1 = size the bucket regions of the cell partition from a 1/16 sample of the
+	// probe rows for large inputs (exact counts are recovered afterwards, overflow repeats with the exact histogram),
+	// 0 = always the exact histogram pass
+	int hist_sample = 1;
 	// sb_context_set_option("trace", 1): synchronise at SB_TRACE points and print the wall time of each phase
 	int trace = 0;
 	double trace_t0 = 0;

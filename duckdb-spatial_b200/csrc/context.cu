@@ -267,6 +267,11 @@ extern "C" int sb_context_set_option(sb_context *ctx, const char *key, int64_t v
 		ctx->pip_path = (int)value;
 		return SB_OK;
 	}
+	if (strcmp(key, "hist_sample") == 0) {
+		SB_ARG(value >= 0 && value <= 1, "hist_sample must be 0 (exact bucket histogram) or 1 (sampled for large inputs)");
+		ctx->hist_sample = (int)value;
+		return SB_OK;
+	}
 	if (strcmp(key, "pipe_chunk") == 0) {
 		SB_ARG(value >= 1024, "pipe_chunk must be >= 1024 rows");
 		ctx->pipe_chunk = (uint64_t)value;

@@ -161,3 +161,38 @@ def test_rtree_build_from_blobs_skips_rows_without_bounds(ctx, sb, O):
         assert np.array_equal(idx.level(l), ref.level(l))
     idx.close()
     ref.close()
+
+
+def test_sampled_histogram_overflow_falls_back_to_exact(ctx, O, R, sb):
+    # inputs >= 32 Mi rows size the bucket regions of the cell partition from every 16th 4096-row tile. Here every sampled
+    # tile lies in one corner and all other tiles in the opposite corner, so the sampled regions are far too small: the
+    # partition must notice (k_cp_actual) and repeat with the exact histogram. Checked against the reference FlatRTree.
+    import torch
+
+    n, m = 40 << 20, 100_000
+    rng = np.random.default_rng(8)
+    tile = np.arange(n) // 4096
+    sampled = (tile % 16) == 0
+    px = np.where(sampled, rng.uniform(0, 500, n), rng.uniform(9000, 10000, n))
+    py = np.where(sampled, rng.uniform(0, 500, n), rng.uniform(9000, 10000, n))
+    cx = np.concatenate([rng.uniform(0, 500, m // 2), rng.uniform(9000, 10000, m // 2)])
+    cy = np.concatenate([rng.uniform(0, 500, m // 2), rng.uniform(9000, 10000, m // 2)])
+    b = [np.ascontiguousarray(v) for v in (cx - 2, cy - 2, cx + 2, cy + 2)]
+    dev = torch.device("cuda", 0)
+    tx, ty = torch.from_numpy(px).to(dev), torch.from_numpy(py).to(dev)
+    tb = [torch.from_numpy(v).to(dev) for v in b]
+    f32p, f64p = C.POINTER(C.c_float), C.POINTER(C.c_double)
+    fbox = O.bbox_from_box2d(*b)
+    tree = R.ref_flat_build(fbox.ctypes.data_as(f32p), C.c_uint32(m), C.c_uint32(32))
+    h = C.c_uint64(0)
+    rc = R.ref_flat_join_hash(C.c_void_p(tree), px.ctypes.data_as(f64p), py.ctypes.data_as(f64p), C.c_uint64(n),
+                              *[v.ctypes.data_as(f64p) for v in b], C.c_int(0), C.c_int(16), C.c_uint32(0), C.byref(h))
+    R.ref_flat_free(C.c_void_p(tree))
+    for opt in (1, 0):
+        ctx.set_option("hist_sample", opt)
+        try:
+            gp, gb = ctx.spatial_join_points_boxes(tx, ty, *tb, predicate="intersects", capacity=int(rc) + 1024)
+        finally:
+            ctx.set_option("hist_sample", 1)
+        assert ctx.pairs_checksum(gp, gb) == (int(rc), int(h.value)), opt
+        del gp, gb
