@@ -83,6 +83,7 @@ SIGNATURES = {
     "sb_rtree_dump": (i32, [vp, vp, i32, vp, vp, vp, u64, C.POINTER(u64)]),
     "sb_context_trim": (i32, [vp]),
     "sb_pairs_checksum": (i32, [vp, i32, vp, vp, u64, u32, u32, C.POINTER(u64), C.POINTER(u64)]),
+    "sb_pairs_checksum_noalloc": (i32, [i32, vp, vp, vp, u64, u32, u32, vp]),
     "sb_join_points_polygons": (i32, [vp, i32, vp, vp, u64, vp, vp, vp, vp, u64, u64, u64, vp, vp, u64, C.POINTER(u64)]),
     "sb_join_points_polygons_exact": (i32, [vp, i32, i32, vp, vp, u64, vp, vp, vp, vp, u64, u64, u64, vp, vp, u64, C.POINTER(u64)]),
     "sb_generate_points": (i32, [vp, i32, u64, u64, u64, vp, vp, vp]),

@@ -373,6 +373,19 @@ SB_API int sb_join_unmatched_rows(sb_context *ctx, sb_mem mem, const uint8_t *ma
 SB_API int sb_pairs_checksum(sb_context *ctx, sb_mem mem, const uint32_t *pair_probe, const uint32_t *pair_build,
                              uint64_t count, uint32_t probe_lo, uint32_t probe_hi, uint64_t *out_count,
                              uint64_t *out_hash);
+/* sb_pairs_checksum for callers that may not allocate (CUDA graph capture, serving loops, harnesses that forbid
+ * cudaMalloc). No counterpart in the reference. It takes no context and
+ * calls no cudaMalloc / cudaFree / pool routine: its scratch (one partial per 4096-pair tile) is a static 256 KiB
+ * __device__ array every GPU that loads the library holds until exit. DEVICE pointers only: pair_probe / pair_build
+ * [count], out_count_hash[2] = {count, hash} as sb_pairs_checksum defines them, written on `cuda_stream` (a
+ * cudaStream_t, NULL = default stream) of `device` (< 0 = the current device); the call does not synchronise.
+ * count > SB_NOALLOC_MAX_PAIRS fails with SB_ERR_ARG. All calls on a device share the scratch: calls that overlap on
+ * the GPU (two streams, two threads) race; calls on one stream are safe. The first call per device looks the scratch
+ * address up (cudaGetSymbolAddress) -- make it outside a capture. */
+#define SB_NOALLOC_MAX_PAIRS 67108864ull /* 2^26 pairs */
+SB_API int sb_pairs_checksum_noalloc(int device, void *cuda_stream, const uint32_t *pair_probe,
+                                     const uint32_t *pair_build, uint64_t count, uint32_t probe_lo, uint32_t probe_hi,
+                                     uint64_t *out_count_hash);
 
 /* ---- probe-side operator glue: PhysicalSpatialJoin's life cycle for a STREAMING probe side ------------------
  * DuckDB hands the operator one <= 2048-row probe chunk per ExecuteInternal call (spatial_join_physical.cpp:695-945);
