@@ -12,6 +12,7 @@ OK, ERR_CUDA, ERR_ARG, ERR_CAPACITY, ERR_GEOMETRY, ERR_EMPTY = 0, -1, -2, -3, -4
 vp = C.c_void_p
 u32, u64, i32 = C.c_uint32, C.c_uint64, C.c_int
 f64 = C.c_double
+i64 = C.c_int64
 
 # name -> (restype, argtypes). Data pointers are void* so numpy / torch / raw addresses all pass as ints.
 SIGNATURES = {
@@ -78,7 +79,7 @@ SIGNATURES = {
     "sb_join_unmatched_rows": (i32, [vp, i32, vp, u64, u32, vp, u64, C.POINTER(u64)]),
     "sb_rtree_build_from_blobs": (i32, [vp, i32, vp, vp, u64, vp, u32, C.POINTER(vp), C.POINTER(u64), vp]),
     "sb_rtree_slice_for": (u64, [u64, u32]),
-    "sb_rtree_build_leaf_shard": (i32, [vp, i32, vp, vp, u64, u32, u64, u64, vp, vp]),
+    "sb_rtree_build_leaf_shard": (i32, [vp, i32, vp, vp, u64, u32, u64, u64, i64, i64, vp, vp]),
     "sb_rtree_from_leaf_level": (i32, [vp, i32, vp, u64, vp, u32, C.POINTER(vp)]),
     "sb_rtree_dump": (i32, [vp, vp, i32, vp, vp, vp, u64, C.POINTER(u64)]),
     "sb_context_trim": (i32, [vp]),
@@ -100,7 +101,8 @@ class SpatialB200Error(RuntimeError):
 
 
 def library_path():
-    return _build.LIB
+    # SPATIAL_B200_LIB: another build of the same library (A/B measurements of kernel variants, scripts/build_variant.py)
+    return os.environ.get("SPATIAL_B200_LIB") or _build.LIB
 
 
 def lib(build_if_missing=True):

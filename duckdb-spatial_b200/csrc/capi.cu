@@ -404,7 +404,8 @@ extern "C" uint64_t sb_rtree_slice_for(uint64_t n, uint32_t max_node_capacity) {
 
 extern "C" int sb_rtree_build_leaf_shard(sb_context *ctx, sb_mem mem, const float *box4, const int64_t *row_ids,
                                          uint64_t n_shard, uint32_t max_node_capacity, uint64_t slice_size,
-                                         uint64_t node_base, void *out_leaf_entries, void *out_node_entries) {
+                                         uint64_t node_base, int64_t x_key_before, int64_t x_key_after,
+                                         void *out_leaf_entries, void *out_node_entries) {
 	SB_BEGIN(ctx);
 	SB_ARG(n_shard == 0 || (box4 && row_ids && out_leaf_entries && out_node_entries), "arrays");
 	const uint64_t nodes = (n_shard + max_node_capacity - 1) / (max_node_capacity ? max_node_capacity : 1);
@@ -415,7 +416,8 @@ extern "C" int sb_rtree_build_leaf_shard(sb_context *ctx, sb_mem mem, const floa
 	SB_TRY(sb_to_device(ctx, mem, row_ids, n_shard, &dr));
 	SB_TRY(sb_out_buffer(ctx, mem, static_cast<sb_entry *>(out_leaf_entries), n_shard, &d0));
 	SB_TRY(sb_out_buffer(ctx, mem, static_cast<sb_entry *>(out_node_entries), nodes, &d1));
-	SB_TRY(sbi_rtree_leaf_shard(ctx, db, dr, n_shard, max_node_capacity, slice_size, node_base, d0, d1));
+	SB_TRY(sbi_rtree_leaf_shard(ctx, db, dr, n_shard, max_node_capacity, slice_size, node_base, x_key_before, x_key_after,
+	                            d0, d1));
 	SB_TRY(sb_to_host(ctx, mem, static_cast<sb_entry *>(out_leaf_entries), d0, n_shard));
 	SB_TRY(sb_to_host(ctx, mem, static_cast<sb_entry *>(out_node_entries), d1, nodes));
 	return finish(ctx, mem);

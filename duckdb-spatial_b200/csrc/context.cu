@@ -267,6 +267,11 @@ extern "C" int sb_context_set_option(sb_context *ctx, const char *key, int64_t v
 		ctx->pip_path = (int)value;
 		return SB_OK;
 	}
+	if (strcmp(key, "str_path") == 0) {
+		SB_ARG(value >= 0 && value <= 1, "str_path must be 0 (auto) or 1 (bin-id sort + gather)");
+		ctx->str_path = (int)value;
+		return SB_OK;
+	}
 	if (strcmp(key, "hist_sample") == 0) {
 		SB_ARG(value >= 0 && value <= 1, "hist_sample must be 0 (exact bucket histogram) or 1 (sampled for large inputs)");
 		ctx->hist_sample = (int)value;

@@ -74,11 +74,38 @@ struct sb_flat {
 	}
 };
 
+// str_partition.cu: the x order of the STR bulk load as a select + stable partition (no sort)
+struct __align__(32) sb_rec32 { // one entry on its way through the leaf level: a whole 32-byte sector
+	float4 box;
+	int64_t row;
+	uint32_t ykey;
+	uint32_t pad;
+};
+static_assert(sizeof(sb_rec32) == 32, "partition record must be one 32-byte sector");
+#define SP_MAXBINS 1025 // bins of the one-pass record partition: 2 * 512 cut keys + 1
+// key_lo / key_hi: cut keys of the enclosing global order just outside a shard (-1 = none)
+struct sb_str_select {
+	uint32_t nsp, ncut;
+	uint64_t slice;
+	int64_t key_lo, key_hi;
+	uint32_t *cuts;  // [ncut] sorted cut keys (device), valid after finish
+	uint32_t *hist1; // [2048] histogram of the x keys' top 11 bits, to be filled between begin and finish (NULL: not needed)
+	uint32_t *temp;
+};
+int sbi_str_select_begin(sb_context *ctx, uint64_t n, uint64_t slice, int64_t key_lo, int64_t key_hi, sb_str_select *sel);
+int sbi_str_select_finish(sb_context *ctx, const uint32_t *xkeys, uint64_t n, sb_str_select *sel);
+int sbi_str_bin_ids(sb_context *ctx, const uint32_t *xkeys, uint64_t n, const uint32_t *cuts, uint32_t ncut,
+                    uint32_t *bins);
+int sbi_str_partition_rec(sb_context *ctx, const float4 *box, const int64_t *rows, const uint32_t *xkeys,
+                          const uint32_t *ykeys, uint64_t n, const uint32_t *cuts, uint32_t ncut, sb_rec32 *rec_out,
+                          uint32_t *ykey_out);
+
 // rtree_str.cu
 int sbi_rtree_build_str(sb_context *ctx, const float *box4, const int64_t *row_ids, uint64_t n, uint32_t cap,
                         sb_rtree **out);
 int sbi_rtree_leaf_shard(sb_context *ctx, const float *box4, const int64_t *row_ids, uint64_t n, uint32_t cap,
-                         uint64_t slice, uint64_t node_base, sb_entry *level0, sb_entry *parents);
+                         uint64_t slice, uint64_t node_base, int64_t x_key_before, int64_t x_key_after, sb_entry *level0,
+                         sb_entry *parents);
 int sbi_rtree_from_leaf_level(sb_context *ctx, const sb_entry *level0, uint64_t n, const sb_entry *nodes_in, uint32_t cap,
                               sb_rtree **out);
 int sbi_rtree_scan(sb_context *ctx, const sb_rtree *tree, const float *qbox4, uint32_t nq, uint32_t *out_query,

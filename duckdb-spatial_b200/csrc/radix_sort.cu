@@ -14,6 +14,26 @@
 #define RS_FLAG_INC 0x80000000u
 #define RS_VALUE_MASK 0x3FFFFFFFu
 #define RS_LOOK 8 // predecessor status words fetched per look-back round
+// onesweep pass kernel shape (tile = OS_THREADS * items keys)
+#ifndef OS_THREADS
+#define OS_THREADS 256
+#endif
+#ifndef OS_ITEMS32
+#define OS_ITEMS32 16
+#endif
+#ifndef OS_ITEMS64
+#define OS_ITEMS64 12
+#endif
+#ifndef OS_MIN_CTAS
+#define OS_MIN_CTAS 3
+#endif
+#ifndef OS_LATE_VALS
+#define OS_LATE_VALS 0 // 1: values are loaded after the ranking (not live across it), 2: at the scatter
+#endif
+#ifndef OS_PACK_POS
+#define OS_PACK_POS 0 // 1: two 16-bit tile ranks per register
+#endif
+#define OS_WARPS (OS_THREADS / 32)
 
 __device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t *p) {
 	uint32_t v;
@@ -166,25 +186,25 @@ __global__ void __launch_bounds__(RS_BINS) k_radix_scan_seg(uint32_t *__restrict
 // never leave their segment: tiles do not straddle segments (`tiles_per_seg` tiles each), the first tile of a segment
 // starts a new look-back chain, and bin_base holds one row of 256 bases per segment (segment start + digit prefix).
 template <typename KeyT, int ITEMS, bool SEG>
-__global__ void __launch_bounds__(RS_THREADS, 3)
+__global__ void __launch_bounds__(OS_THREADS, OS_MIN_CTAS)
     k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const uint32_t *__restrict__ vals_in,
                uint32_t *__restrict__ vals_out, uint64_t n, int shift, uint32_t digit_mask,
                const uint32_t *__restrict__ bin_base, uint32_t *__restrict__ tile_state, uint32_t *__restrict__ ticket,
                uint64_t seg_size, uint32_t tiles_per_seg) {
-	constexpr int TILE = RS_THREADS * ITEMS;
+	constexpr int TILE = OS_THREADS * ITEMS;
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	KeyT *s_keys = reinterpret_cast<KeyT *>(smem_raw);
 	uint32_t *s_vals = reinterpret_cast<uint32_t *>(smem_raw + sizeof(KeyT) * TILE);
-	uint32_t *s_warp_hist = s_vals + TILE;          // [RS_WARPS][RS_BINS]
-	uint32_t *s_digit_off = s_warp_hist + RS_WARPS * RS_BINS; // [RS_BINS] tile-local exclusive scan over digits
+	uint32_t *s_warp_hist = s_vals + TILE;          // [OS_WARPS][RS_BINS]
+	uint32_t *s_digit_off = s_warp_hist + OS_WARPS * RS_BINS; // [RS_BINS] tile-local exclusive scan over digits
 	uint32_t *s_global = s_digit_off + RS_BINS;     // [RS_BINS] global base - digit_off
-	uint32_t *s_scan = s_global + RS_BINS;          // [RS_WARPS]
+	uint32_t *s_scan = s_global + RS_BINS;          // [RS_BINS / 32]
 	__shared__ uint32_t s_tile;
 
 	if (threadIdx.x == 0) {
 		s_tile = atomicAdd(ticket, 1u); // tiles are claimed in order => a tile's predecessors are always running
 	}
-	for (int i = threadIdx.x; i < RS_WARPS * RS_BINS; i += RS_THREADS) {
+	for (int i = threadIdx.x; i < OS_WARPS * RS_BINS; i += OS_THREADS) {
 		s_warp_hist[i] = 0;
 	}
 	__syncthreads();
@@ -202,14 +222,20 @@ __global__ void __launch_bounds__(RS_THREADS, 3)
 
 	KeyT key[ITEMS];
 	uint32_t val[ITEMS];
+#if OS_PACK_POS
+	uint32_t pos2[(ITEMS + 1) / 2]; // tile ranks < TILE <= 65536: two per register
+#else
 	uint32_t pos[ITEMS];
+#endif
 	const uint64_t first = tile_base + (uint64_t)warp * (32 * ITEMS) + lane;
 #pragma unroll
 	for (int i = 0; i < ITEMS; i++) {
 		const uint64_t gi = first + (uint64_t)i * 32;
 		const bool valid = gi < n;
 		key[i] = valid ? keys_in[gi] : KeyT(0);
+#if !OS_LATE_VALS
 		val[i] = valid ? (vals_in ? vals_in[gi] : (uint32_t)gi) : 0u;
+#endif
 	}
 	// warp multi-split: stable rank of every key among the warp's keys with the same digit
 	uint32_t *my_hist = s_warp_hist + warp * RS_BINS;
@@ -225,22 +251,40 @@ __global__ void __launch_bounds__(RS_THREADS, 3)
 			my_hist[d] = prev + __popc(peers);
 		}
 		prev = __shfl_sync(0xFFFFFFFFu, prev, leader);
+#if OS_PACK_POS
+		if (i & 1) {
+			pos2[i >> 1] |= (prev + __popc(peers & lt_mask)) << 16;
+		} else {
+			pos2[i >> 1] = prev + __popc(peers & lt_mask);
+		}
+#else
 		pos[i] = prev + __popc(peers & lt_mask);
+#endif
 		__syncwarp();
 	}
+#if OS_LATE_VALS == 1
+#pragma unroll
+	for (int i = 0; i < ITEMS; i++) {
+		const uint64_t gi = first + (uint64_t)i * 32;
+		val[i] = gi < n ? (vals_in ? vals_in[gi] : (uint32_t)gi) : 0u;
+	}
+#endif
 	__syncthreads();
 
-	// thread d owns digit d: exclusive offsets of the warps, tile total, look-back
-	const unsigned d = threadIdx.x;
+	// thread d < 256 owns digit d: exclusive offsets of the warps, tile total, look-back
+	const unsigned d = threadIdx.x & (RS_BINS - 1);
+	const bool owner = OS_THREADS == RS_BINS || threadIdx.x < RS_BINS;
 	uint32_t total = 0;
-#pragma unroll
-	for (int w = 0; w < RS_WARPS; w++) {
-		const uint32_t c = s_warp_hist[w * RS_BINS + d];
-		s_warp_hist[w * RS_BINS + d] = total;
-		total += c;
-	}
 	uint32_t *my_state = tile_state + (uint64_t)tile * RS_BINS + d;
-	st_volatile_u32(my_state, (tile == chain_first ? RS_FLAG_INC : RS_FLAG_AGG) | total);
+	if (owner) {
+#pragma unroll
+		for (int w = 0; w < OS_WARPS; w++) {
+			const uint32_t c = s_warp_hist[w * RS_BINS + d];
+			s_warp_hist[w * RS_BINS + d] = total;
+			total += c;
+		}
+		st_volatile_u32(my_state, (tile == chain_first ? RS_FLAG_INC : RS_FLAG_AGG) | total);
+	}
 
 	// block exclusive scan of `total` over the 256 digits
 	uint32_t inc = total;
@@ -251,19 +295,21 @@ __global__ void __launch_bounds__(RS_THREADS, 3)
 			inc += o;
 		}
 	}
-	if (lane == 31) {
+	if (lane == 31 && owner) {
 		s_scan[warp] = inc;
 	}
 	__syncthreads();
 	uint32_t dbase = 0;
-	for (unsigned w = 0; w < warp; w++) {
+	for (unsigned w = 0; w < (warp & (RS_BINS / 32 - 1)); w++) {
 		dbase += s_scan[w];
 	}
 	const uint32_t digit_off = dbase + inc - total;
-	s_digit_off[d] = digit_off;
+	if (owner) {
+		s_digit_off[d] = digit_off;
+	}
 
 	uint32_t excl = 0;
-	if (tile > chain_first) {
+	if (owner && tile > chain_first) {
 		// look back over the predecessors' status words, RS_LOOK loads in flight at a time (a one-at-a-time walk made the
 		// first wave of tiles pay one L2 round trip per predecessor: the whole pass was latency bound at 10 M keys)
 		int64_t look = (int64_t)tile - 1;
@@ -289,7 +335,9 @@ __global__ void __launch_bounds__(RS_THREADS, 3)
 		}
 		st_volatile_u32(my_state, RS_FLAG_INC | (excl + total));
 	}
-	s_global[d] = bin_base[d] + excl - digit_off;
+	if (owner) {
+		s_global[d] = bin_base[d] + excl - digit_off;
+	}
 	__syncthreads();
 
 	// scatter into shared memory in tile-sorted order
@@ -297,16 +345,26 @@ __global__ void __launch_bounds__(RS_THREADS, 3)
 	for (int i = 0; i < ITEMS; i++) {
 		if (first + (uint64_t)i * 32 < n) {
 			const uint32_t dg = (uint32_t)(key[i] >> shift) & digit_mask;
-			const uint32_t p = s_digit_off[dg] + s_warp_hist[warp * RS_BINS + dg] + pos[i];
+#if OS_PACK_POS
+			const uint32_t rank = (i & 1) ? pos2[i >> 1] >> 16 : pos2[i >> 1] & 0xFFFFu;
+#else
+			const uint32_t rank = pos[i];
+#endif
+			const uint32_t p = s_digit_off[dg] + s_warp_hist[warp * RS_BINS + dg] + rank;
 			s_keys[p] = key[i];
+#if OS_LATE_VALS == 2
+			const uint64_t gi = first + (uint64_t)i * 32;
+			s_vals[p] = vals_in ? vals_in[gi] : (uint32_t)gi;
+#else
 			s_vals[p] = val[i];
+#endif
 		}
 	}
 	__syncthreads();
 	// coalesced runs out to global memory
 #pragma unroll
 	for (int i = 0; i < ITEMS; i++) {
-		const uint32_t p = threadIdx.x + i * RS_THREADS;
+		const uint32_t p = threadIdx.x + i * OS_THREADS;
 		if (p < tile_count) {
 			const KeyT k = s_keys[p];
 			const uint32_t dg = (uint32_t)(k >> shift) & digit_mask;
@@ -319,10 +377,10 @@ __global__ void __launch_bounds__(RS_THREADS, 3)
 
 template <typename KeyT>
 struct rs_cfg {
-	static constexpr int ITEMS = sizeof(KeyT) == 4 ? 16 : 12;
-	static constexpr int TILE = RS_THREADS * ITEMS;
+	static constexpr int ITEMS = sizeof(KeyT) == 4 ? OS_ITEMS32 : OS_ITEMS64;
+	static constexpr int TILE = OS_THREADS * ITEMS;
 	static constexpr size_t SMEM =
-	    (sizeof(KeyT) + 4) * TILE + sizeof(uint32_t) * (RS_WARPS * RS_BINS + 2 * RS_BINS + RS_WARPS);
+	    (sizeof(KeyT) + 4) * TILE + sizeof(uint32_t) * (OS_WARPS * RS_BINS + 2 * RS_BINS + RS_BINS / 32);
 	static constexpr int MAX_PASSES = sizeof(KeyT);
 };
 
@@ -368,7 +426,7 @@ int sbi_radix_sort_impl(sb_context *ctx, KeyT *keys, KeyT *keys_alt, uint32_t *v
 		const int shift = begin_bit + 8 * p;
 		const int bits = end_bit - shift < 8 ? end_bit - shift : 8;
 		sb_prof_scope ps(ctx, "radix_onesweep");
-		k_onesweep<KeyT, cfg::ITEMS, false><<<(unsigned)tiles, RS_THREADS, cfg::SMEM, ctx->stream>>>(
+		k_onesweep<KeyT, cfg::ITEMS, false><<<(unsigned)tiles, OS_THREADS, cfg::SMEM, ctx->stream>>>(
 		    kin, kout, (p == 0 && vals_iota) ? nullptr : vin, vout, n, shift, (1u << bits) - 1, hist + p * RS_BINS,
 		    state + (size_t)p * tiles * RS_BINS, tickets + p, 0, 0);
 		SB_LAUNCH_CHECK(ctx);
@@ -431,7 +489,7 @@ int sbi_radix_sort_u32_segmented(sb_context *ctx, uint32_t *keys, uint32_t *keys
 		const int shift = begin_bit + 8 * p;
 		const int bits = end_bit - shift < 8 ? end_bit - shift : 8;
 		sb_prof_scope ps(ctx, "radix_onesweep");
-		k_onesweep<uint32_t, cfg::ITEMS, true><<<(unsigned)tiles, RS_THREADS, cfg::SMEM, ctx->stream>>>(
+		k_onesweep<uint32_t, cfg::ITEMS, true><<<(unsigned)tiles, OS_THREADS, cfg::SMEM, ctx->stream>>>(
 		    kin, kout, (p == 0 && vals_iota) ? nullptr : vin, vout, n, shift, (1u << bits) - 1,
 		    hist + (size_t)p * nseg * RS_BINS, state + (size_t)p * tiles * RS_BINS, tickets + p, seg_size, (uint32_t)tps);
 		SB_LAUNCH_CHECK(ctx);

@@ -2,10 +2,13 @@
 //
 // Reference algorithm (see include/spatial_b200.h for file:line): ORDER BY x-centre, then per layer: runs of
 // `slice` entries re-sorted by fp32 y-centre, packed `cap` per node, leaf nodes sorted by row id, node box = union.
-// B200 formulation: every sort is one stable radix sort over the whole layer --
-//   x-order : 32-bit key  = order-preserving bits of float(min_x + max_x)   (x0.5 in fp64 is monotone and exact)
+// B200 formulation --
+//   x-order : 32-bit key  = order-preserving bits of float(min_x + max_x)   (x0.5 in fp64 is monotone and exact). The
+//             layer is never sorted by it: the slices of the x order come from a radix select of the slice-boundary keys
+//             and one stable partition of the 32-byte records (str_partition.cu)
 //   y-order : 32-bit key  = order-preserving bits of float((min_y+max_y)/2), sorted per slice of the x order by the
-//             segmented radix sort (segment = `slice` consecutive positions of the layer)
+//             segmented radix sort (segment = `slice` consecutive positions of the layer); equal y keys of a slice
+//             stay in (x bin, input position) order
 // followed by a pack kernel (one CTA per node: gather, rank-sort by row id in shared memory, union, coalesced
 // 24-byte entry stores). Level sizes are known on the host from n and cap, so the whole build is enqueued
 // without a single device->host synchronisation.
@@ -16,15 +19,38 @@
 // x keys for the ORDER BY and, from the same read of the boxes, the y keys of the leaf level in input order: the
 // leaf level later picks its y key with a 4-byte gather from this 4n-byte array (L2-resident at 10 M keys) instead
 // of a 16-byte gather from the boxes.
+// hist1 (may be NULL): the 2048-bin histogram of the x keys' top 11 bits, level 1 of the cut-key select (str_partition.cu).
 __global__ void __launch_bounds__(256) k_str_xkeys(const float4 *__restrict__ box, uint64_t n,
-                                                   uint32_t *__restrict__ keys, uint32_t *__restrict__ ykeys) {
+                                                   uint32_t *__restrict__ keys, uint32_t *__restrict__ ykeys,
+                                                   uint32_t *__restrict__ hist1) {
+	__shared__ uint32_t s_h[4 * 2048]; // 4 replicas (lane & 3): float keys share their top bits
+	if (hist1) {
+		for (uint32_t i = threadIdx.x; i < 4 * 2048; i += 256) {
+			s_h[i] = 0;
+		}
+		__syncthreads();
+	}
+	uint32_t *mine = s_h + (threadIdx.x & 3u) * 2048;
 	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
 	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
 		const float4 b = box[i];
 		// ST_Centroid::ExecuteBox<float>: (float)min_x + (float)max_x in fp32, spatial_functions_scalar.cpp:1490-1494
-		keys[i] = sb_f32_sort_key(__fadd_rn(b.x, b.z));
+		const uint32_t xk = sb_f32_sort_key(__fadd_rn(b.x, b.z));
+		keys[i] = xk;
 		// bounds.Center().y = (min.y + max.y) / 2 in fp32, bbox.hpp:78-80, rtree_index_create_physical.cpp:172-174
 		ykeys[i] = sb_f32_sort_key(__fdiv_rn(__fadd_rn(b.y, b.w), 2.0f));
+		if (hist1) {
+			atomicAdd(&mine[xk >> 21], 1u);
+		}
+	}
+	if (hist1) {
+		__syncthreads();
+		for (uint32_t d = threadIdx.x; d < 2048; d += 256) {
+			const uint32_t c = s_h[d] + s_h[2048 + d] + s_h[4096 + d] + s_h[6144 + d];
+			if (c) {
+				atomicAdd(&hist1[d], c);
+			}
+		}
 	}
 }
 
@@ -57,7 +83,8 @@ template <bool LEAF>
 __global__ void __launch_bounds__(256)
     k_str_pack(const float4 *__restrict__ box, const int64_t *__restrict__ row_ids, const sb_entry *__restrict__ cur,
                const uint32_t *__restrict__ perm, uint64_t count, uint32_t cap, sb_entry *__restrict__ level_out,
-               sb_entry *__restrict__ parent_out, uint64_t parent_type, uint64_t node_base) {
+               sb_entry *__restrict__ parent_out, uint64_t parent_type, uint64_t node_base,
+               const sb_rec32 *__restrict__ rec) {
 	__shared__ int64_t s_row[256];
 	__shared__ uint64_t s_words[256 * 3];
 	__shared__ float s_red[8][4];
@@ -72,8 +99,18 @@ __global__ void __launch_bounds__(256)
 	if (t < cnt) {
 		const uint32_t src = perm[beg + t];
 		if (LEAF) {
-			const float4 b = box[src];
-			e.ptr = (uint64_t)row_ids[src] & 0x00FFFFFFFFFFFFFFull; // RTree::MakeRowId: type ROW_ID = 0
+			float4 b;
+			int64_t row;
+			if (rec) { // partitioned records: `src` is a position inside this node's slice (local gather)
+				const float4 *r = reinterpret_cast<const float4 *>(rec + src);
+				b = r[0];
+				const float4 hi = r[1];
+				row = (int64_t)(((uint64_t)__float_as_uint(hi.y) << 32) | __float_as_uint(hi.x));
+			} else {
+				b = box[src];
+				row = row_ids[src];
+			}
+			e.ptr = (uint64_t)row & 0x00FFFFFFFFFFFFFFull; // RTree::MakeRowId: type ROW_ID = 0
 			e.box[0] = b.x, e.box[1] = b.y, e.box[2] = b.z, e.box[3] = b.w;
 		} else {
 			e = cur[src];
@@ -165,7 +202,11 @@ __global__ void __launch_bounds__(1024)
                       sb_entry *__restrict__ level_out, sb_entry *__restrict__ parent_out, uint64_t parent_type) {
 	__shared__ uint64_t s_key[STR_SMALL];
 	const unsigned t = threadIdx.x;
-	for (uint32_t i = t; i < STR_SMALL; i += blockDim.x) {
+	uint32_t sz = 2; // the network only spans the next power of two (a 5-entry level is not a 2048-entry sort)
+	while (sz < count) {
+		sz <<= 1;
+	}
+	for (uint32_t i = t; i < sz; i += blockDim.x) {
 		uint64_t k = ~0ull; // padding sorts last
 		if (i < count) {
 			const float yc = __fdiv_rn(__fadd_rn(cur[i].box[1], cur[i].box[3]), 2.0f);
@@ -174,9 +215,9 @@ __global__ void __launch_bounds__(1024)
 		s_key[i] = k;
 	}
 	__syncthreads();
-	for (uint32_t size = 2; size <= STR_SMALL; size <<= 1) {
+	for (uint32_t size = 2; size <= sz; size <<= 1) {
 		for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
-			for (uint32_t i = t; i < STR_SMALL / 2; i += blockDim.x) {
+			for (uint32_t i = t; i < sz / 2; i += blockDim.x) {
 				const uint32_t lo = 2 * i - (i & (stride - 1));
 				const uint32_t hi = lo + stride;
 				const bool up = (lo & size) == 0;
@@ -226,51 +267,74 @@ static void str_shape(sb_rtree *t, uint64_t n, uint32_t cap) {
 	t->total = total;
 }
 
-// Leaf level of (a shard of) the layer: ORDER BY x centre (stable), y-sort inside runs of `slice` positions, pack `cap`
-// per node with the entries ordered by row id. level0 receives the n leaf entries, parents one entry per node whose
-// pointer is (LEAF_PAGE << 56) | (node_base + node). With node_base = 0 and the whole layer this is the first stage
-// of the build; a shard that is a contiguous, slice-aligned range of the global x order produces exactly its part of
-// the global leaf level (multi-GPU build).
+// Leaf level of (a shard of) the layer: slices of the x order (select + stable partition, str_partition.cu), y-sort
+// inside runs of `slice` positions, pack `cap` per node with the entries ordered by row id. level0 receives the n leaf
+// entries, parents one entry per node whose pointer is (LEAF_PAGE << 56) | (node_base + node). With node_base = 0 and the
+// whole layer this is the first stage of the build; a shard that holds a contiguous, slice-aligned range of the global x
+// order (rows in ascending global input position, x_key_before / x_key_after = the global cut keys at its two ends,
+// -1 at the ends of the layer) produces exactly its part of the global leaf level (multi-GPU build).
 static int str_leaf_level(sb_context *ctx, const float4 *box, const int64_t *row_ids, uint64_t n, uint32_t cap,
-                          uint64_t slice, uint64_t node_base, sb_entry *level0, sb_entry *parents, uint32_t **yk_out,
-                          uint32_t **ykb_out, uint32_t **yv_out, uint32_t **yvb_out) {
+                          uint64_t slice, uint64_t node_base, int64_t x_key_before, int64_t x_key_after, sb_entry *level0,
+                          sb_entry *parents, uint32_t **yk_out, uint32_t **ykb_out, uint32_t **yv_out, uint32_t **yvb_out) {
 	const unsigned block = ((cap + 31) / 32) * 32;
-	// --- ORDER BY x centre ---------------------------------------------------------------------------------
-	uint32_t *k32 = nullptr, *k32b = nullptr, *v32 = nullptr, *v32b = nullptr;
-	SB_TRY(ctx->scratch_t(n, &k32));
-	SB_TRY(ctx->scratch_t(n, &k32b));
-	SB_TRY(ctx->scratch_t(n, &v32));
-	SB_TRY(ctx->scratch_t(n, &v32b));
-	uint32_t *yk_in = nullptr;
+	uint32_t *xk = nullptr, *yk_in = nullptr;
+	uint32_t *yk = nullptr, *ykb = nullptr, *yv = nullptr, *yvb = nullptr;
+	SB_TRY(ctx->scratch_t(n, &xk));
 	SB_TRY(ctx->scratch_t(n, &yk_in));
+	SB_TRY(ctx->scratch_t(n, &yk));
+	SB_TRY(ctx->scratch_t(n, &ykb));
+	SB_TRY(ctx->scratch_t(n, &yv));
+	SB_TRY(ctx->scratch_t(n, &yvb));
+	// --- slices of the x order: x / y keys (and the first histogram of the select), then the cut keys ------------
+	sb_str_select sel;
+	SB_TRY(sbi_str_select_begin(ctx, n, slice, x_key_before, x_key_after, &sel));
 	{
 		sb_prof_scope ps(ctx, "str_keys");
-		k_str_xkeys<<<sb_grid(n, 256, 16), 256, 0, ctx->stream>>>(box, n, k32, yk_in);
+		k_str_xkeys<<<sb_grid(n, 256 * 8, 8), 256, 0, ctx->stream>>>(box, n, xk, yk_in, sel.hist1);
 		SB_LAUNCH_CHECK(ctx);
 	}
+	SB_TRY(sbi_str_select_finish(ctx, xk, n, &sel));
+	uint32_t *cuts = sel.cuts;
+	const uint32_t ncut = sel.ncut;
+	const sb_rec32 *rec = nullptr;
 	int alt = 0;
-	SB_TRY(sbi_radix_sort_u32(ctx, k32, k32b, v32, v32b, n, 0, 32, true, &alt));
-	const uint32_t *xperm = alt ? v32b : v32;
-	uint32_t *free_v = alt ? v32 : v32b; // the other value buffer is reusable
-
+	bool iota = true;
+	if (2 * ncut + 1 <= SP_MAXBINS && ctx->str_path != 1) {
+		// one pass: the records themselves go to their place in the slice order, y keys beside them
+		sb_rec32 *r = nullptr;
+		SB_TRY(ctx->scratch_t(n, &r));
+		SB_TRY(sbi_str_partition_rec(ctx, box, row_ids, xk, yk_in, n, cuts, ncut, r, yk));
+		rec = r;
+	} else {
+		// many slices: the bin ids are sorted as small integers (stable, 8 bits per pass) and the entries are addressed
+		// through the permutation, as a sorted layer would be
+		int bits = 0;
+		while ((1ull << bits) < 2ull * ncut + 1) {
+			bits++;
+		}
+		SB_TRY(sbi_str_bin_ids(ctx, xk, n, cuts, ncut, yk));
+		SB_TRY(sbi_radix_sort_u32(ctx, yk, ykb, yv, yvb, n, 0, bits, true, &alt));
+		const uint32_t *xperm = alt ? yvb : yv;
+		uint32_t *other = alt ? yv : yvb;
+		{
+			sb_prof_scope ps(ctx, "str_keys");
+			k_str_ykeys_leaf<<<sb_grid(n, 256, 16), 256, 0, ctx->stream>>>(yk_in, xperm, n, yk, other);
+			SB_LAUNCH_CHECK(ctx);
+		}
+		yv = other;
+		yvb = const_cast<uint32_t *>(xperm);
+		iota = false;
+	}
 	// --- y-sort inside slices, pack leaves --------------------------------------------------------------------
 	// segmented sort: every slice of the x order is sorted by y on its own (4 passes over 32-bit keys; a 64-bit
 	// (slice, y) key sort needed 6)
-	uint32_t *yk = k32, *ykb = k32b; // dead after the x sort
-	uint32_t *yv = free_v, *yvb = nullptr;
-	SB_TRY(ctx->scratch_t(n, &yvb));
-	{
-		sb_prof_scope ps(ctx, "str_keys");
-		k_str_ykeys_leaf<<<sb_grid(n, 256, 16), 256, 0, ctx->stream>>>(yk_in, xperm, n, yk, yv);
-		SB_LAUNCH_CHECK(ctx);
-	}
-	SB_TRY(sbi_radix_sort_u32_segmented(ctx, yk, ykb, yv, yvb, n, slice, 0, 32, false, &alt));
+	SB_TRY(sbi_radix_sort_u32_segmented(ctx, yk, ykb, yv, yvb, n, slice, 0, 32, iota, &alt));
 	const uint32_t *perm = alt ? yvb : yv;
 	const uint64_t nodes = (n + cap - 1) / cap;
 	{
 		sb_prof_scope ps(ctx, "str_pack");
 		k_str_pack<true><<<(unsigned)nodes, block, 0, ctx->stream>>>(box, row_ids, nullptr, perm, n, cap, level0, parents,
-		                                                            1ull, node_base);
+		                                                            1ull, node_base, rec);
 		SB_LAUNCH_CHECK(ctx);
 	}
 	*yk_out = yk, *ykb_out = ykb, *yv_out = yv, *yvb_out = yvb;
@@ -313,7 +377,8 @@ static int str_upper_levels(sb_context *ctx, sb_rtree *t, sb_entry *parents, sb_
 		{
 			sb_prof_scope ps(ctx, "str_pack");
 			k_str_pack<false><<<(unsigned)nn, block, 0, ctx->stream>>>(nullptr, nullptr, parents, p, c, cap,
-			                                                          t->entries + t->offsets[level], parents_b, 2ull, 0ull);
+			                                                          t->entries + t->offsets[level], parents_b, 2ull, 0ull,
+			                                                          nullptr);
 			SB_LAUNCH_CHECK(ctx);
 		}
 		sb_entry *tmp = parents;
@@ -342,16 +407,19 @@ int sbi_rtree_build_str(sb_context *ctx, const float *box4, const int64_t *row_i
 	SB_TRY(ctx->scratch_t(nodes, &parents));
 	SB_TRY(ctx->scratch_t((nodes + cap - 1) / cap + 1, &parents_b));
 	uint32_t *yk, *ykb, *yv, *yvb;
-	SB_TRY(str_leaf_level(ctx, reinterpret_cast<const float4 *>(box4), row_ids, n, cap, t->slice, 0, t->entries + t->offsets[0],
-	                      parents, &yk, &ykb, &yv, &yvb));
+	SB_TRY(str_leaf_level(ctx, reinterpret_cast<const float4 *>(box4), row_ids, n, cap, t->slice, 0, -1, -1,
+	                      t->entries + t->offsets[0], parents, &yk, &ykb, &yv, &yvb));
 	return str_upper_levels(ctx, t, parents, parents_b, yk, ykb, yv, yvb);
 }
 
 // ---- multi-GPU build: the leaf level is built shard by shard, the upper levels from the gathered nodes ----
-// shard = a contiguous range of the GLOBAL x order (ties by global input position) that starts at a multiple of
-// `slice` positions; slice = the global slice size (sb_rtree_slice_for); node_base = global index of the shard's first node.
+// shard = the rows of a contiguous range of the GLOBAL x order (ties by global input position) that starts at a multiple
+// of `slice` positions, presented in ascending global input position; slice = the global slice size
+// (sb_rtree_slice_for); node_base = global index of the shard's first node; x_key_before / x_key_after = x keys of the
+// global order at the shard's first rank and at the first rank after it (-1 at the two ends of the layer).
 int sbi_rtree_leaf_shard(sb_context *ctx, const float *box4, const int64_t *row_ids, uint64_t n, uint32_t cap,
-                         uint64_t slice, uint64_t node_base, sb_entry *level0, sb_entry *parents) {
+                         uint64_t slice, uint64_t node_base, int64_t x_key_before, int64_t x_key_after, sb_entry *level0,
+                         sb_entry *parents) {
 	SB_ARG(cap >= 4 && cap <= 255, "max_node_capacity must be in [4, 255]");
 	SB_ARG(n < ((uint64_t)1 << 30), "n must be < 2^30");
 	SB_ARG(slice >= cap && slice % cap == 0, "slice must be a multiple of the node capacity");
@@ -359,8 +427,9 @@ int sbi_rtree_leaf_shard(sb_context *ctx, const float *box4, const int64_t *row_
 		return SB_OK;
 	}
 	uint32_t *yk, *ykb, *yv, *yvb;
-	return str_leaf_level(ctx, reinterpret_cast<const float4 *>(box4), row_ids, n, cap, slice, node_base, level0, parents,
-	                      &yk, &ykb, &yv, &yvb);
+	SB_ARG(x_key_before <= 0xFFFFFFFFll && x_key_after <= 0xFFFFFFFFll, "x keys are 32-bit (-1 = none)");
+	return str_leaf_level(ctx, reinterpret_cast<const float4 *>(box4), row_ids, n, cap, slice, node_base, x_key_before,
+	                      x_key_after, level0, parents, &yk, &ykb, &yv, &yvb);
 }
 
 // the whole tree from its leaf entries (global order) and the leaf nodes' entries (node order)

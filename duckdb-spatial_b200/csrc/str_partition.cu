@@ -1,0 +1,656 @@
+// str_partition.cu -- K4b: the ORDER BY of CREATE INDEX ... USING RTREE without a sort.
+//
+// BuildRTreeBottomUp (rtree_index_create_physical.cpp:149-236) consumes the x-sorted layer in runs of `slice` entries
+// and re-sorts every run by y: of the x order it only uses WHICH slice an entry falls in. So the x sort (4 radix passes)
+// is replaced by
+//   1. the exact x keys at ranks slice, 2*slice, ... ("cut keys"): a radix SELECT of all ranks at once -- three
+//      histogram levels (11 + 9 + 12 key bits), each level only counting keys that fall in a bucket holding a rank.
+//      Float keys share their top bits, so level 2 still sees nearly every key: it is counted in shared memory (one
+//      global atomic per key made it 138 us for 10 M keys); level 3 only sees the few keys next to a rank;
+//   2. a stable PARTITION of the entries (in input order) into bins: bin(key) = #{cut < key} + #{cut <= key}, i.e. the
+//      open intervals between consecutive cut keys (even bins) and the runs of keys EQUAL to a cut key (odd bins). Bins
+//      are laid out in key order and keep the input order inside, so the positions [j*slice, (j+1)*slice) of the result
+//      hold exactly the entries of slice j of the (x key, input position) order -- equal-key runs that straddle a slice
+//      boundary are cut by input position, as a stable sort would cut them.
+// The partition moves the whole 32-byte record (box, row id, y key), so the one random permute the leaf level needs
+// happens here as writes in runs per bin, and everything after it (y sort inside slices, pack) is local to a slice.
+// Order inside a slice after the y sort: (y key, bin, input position).
+#include "internal.cuh"
+
+#define SEL_L1 2048u // key bits 31..21
+#define SEL_L2 512u  // key bits 20..12
+#define SEL_L3 4096u // key bits 11..0
+#define SEL_SH2 12
+#define SEL_SMEM_C1 32u // level 2 is counted in shared memory when at most this many level-1 buckets hold a rank
+
+// exclusive block scan of one value per thread; *total = sum over the block. s_w: 33 words.
+template <int THREADS>
+__device__ __forceinline__ uint32_t sp_block_scan(uint32_t v, uint32_t *s_w, uint32_t *total) {
+	const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	uint32_t inc = v;
+#pragma unroll
+	for (int s = 1; s < 32; s <<= 1) {
+		const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, s);
+		if (lane >= (unsigned)s) {
+			inc += o;
+		}
+	}
+	if (lane == 31) {
+		s_w[warp] = inc;
+	}
+	__syncthreads();
+	if (warp == 0) {
+		const uint32_t w = lane < THREADS / 32 ? s_w[lane] : 0u;
+		uint32_t wi = w;
+#pragma unroll
+		for (int s = 1; s < 32; s <<= 1) {
+			const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, wi, s);
+			if (lane >= (unsigned)s) {
+				wi += o;
+			}
+		}
+		s_w[lane] = wi - w;
+		if (lane == 31) {
+			s_w[32] = wi;
+		}
+	}
+	__syncthreads();
+	const uint32_t r = s_w[warp] + inc - v;
+	*total = s_w[32];
+	__syncthreads();
+	return r;
+}
+
+// first index in [0, cnt] whose prefix exceeds r, minus one: the bucket that holds rank r (pre[cnt] > r is guaranteed)
+__device__ __forceinline__ uint32_t sp_bucket_of(const uint32_t *pre, uint32_t cnt, uint32_t r) {
+	uint32_t lo = 0, hi = cnt;
+	while (lo < hi) {
+		const uint32_t mid = (lo + hi) >> 1;
+		if (pre[mid] > r) {
+			hi = mid;
+		} else {
+			lo = mid + 1;
+		}
+	}
+	return lo - 1;
+}
+
+// ---- level 1: the histogram of the top 11 bits is counted by the kernel that makes the keys (rtree_str.cu k_str_xkeys)
+
+// per splitter k (rank (k + 1) * slice): sp[0] = level-1 bucket, sp[1] = rank inside it, sp[2] = index of the bucket among
+// the distinct buckets that hold a rank, sp[3..5] = the same for level 2. map1[bucket] = that index + 1 (0 = no rank).
+__global__ void __launch_bounds__(1024) k_sel_cut1(const uint32_t *__restrict__ hist1, uint32_t nsp, uint64_t slice,
+                                                   uint32_t *__restrict__ sp, uint32_t *__restrict__ map1,
+                                                   uint32_t *__restrict__ ncut1) {
+	__shared__ uint32_t s_pre[SEL_L1 + 1];
+	__shared__ uint32_t s_w[33];
+	const uint32_t t = threadIdx.x;
+	const uint32_t a = hist1[2 * t], b = hist1[2 * t + 1];
+	uint32_t total;
+	const uint32_t ex = sp_block_scan<1024>(a + b, s_w, &total);
+	s_pre[2 * t] = ex;
+	s_pre[2 * t + 1] = ex + a;
+	if (t == 0) {
+		s_pre[SEL_L1] = total;
+	}
+	__syncthreads();
+	uint32_t *b1 = sp, *rem1 = sp + nsp, *c1 = sp + 2 * (size_t)nsp;
+	for (uint32_t k = t; k < nsp; k += 1024) {
+		const uint32_t r = (uint32_t)((uint64_t)(k + 1) * slice);
+		const uint32_t bk = sp_bucket_of(s_pre, SEL_L1, r);
+		b1[k] = bk;
+		rem1[k] = r - s_pre[bk];
+	}
+	__syncthreads();
+	uint32_t base = 0;
+	for (uint32_t k0 = 0; k0 < nsp; k0 += 1024) {
+		const uint32_t k = k0 + t;
+		const uint32_t flag = (k < nsp && (k == 0 || b1[k] != b1[k - 1])) ? 1u : 0u;
+		uint32_t tot;
+		const uint32_t e = sp_block_scan<1024>(flag, s_w, &tot);
+		if (k < nsp) {
+			const uint32_t c = base + e + flag - 1;
+			c1[k] = c;
+			if (flag) {
+				map1[b1[k]] = c + 1;
+			}
+		}
+		base += tot;
+	}
+	if (t == 0) {
+		*ncut1 = base;
+	}
+}
+
+// ---- levels 2 and 3: histograms of the next bits of the keys whose prefix holds a rank ----------------------------
+// count one key into hist[a]; a warp whose keys all count into one word (constant columns, grids) issues one atomic
+__device__ __forceinline__ void sel_count(uint32_t *hist, uint32_t a, unsigned lane) {
+	const unsigned act = __ballot_sync(0xFFFFFFFFu, a != 0xFFFFFFFFu);
+	if (!act) {
+		return;
+	}
+	const int leader = __ffs(act) - 1;
+	const uint32_t a0 = __shfl_sync(0xFFFFFFFFu, a, leader);
+	const unsigned same = __ballot_sync(0xFFFFFFFFu, a == a0);
+	if (same == act) {
+		if ((int)lane == leader) {
+			atomicAdd(&hist[a0], (uint32_t)__popc(act));
+		}
+	} else if (a != 0xFFFFFFFFu) {
+		atomicAdd(&hist[a], 1u);
+	}
+}
+
+// level 2. Dynamic shared memory: SEL_SMEM_C1 * SEL_L2 counters, used when *ncut1 <= SEL_SMEM_C1 (then flushed).
+__global__ void __launch_bounds__(1024) k_sel_hist2(const uint32_t *__restrict__ keys, uint64_t n,
+                                                    const uint32_t *__restrict__ map1, const uint32_t *__restrict__ ncut1,
+                                                    uint32_t *__restrict__ hist2) {
+	extern __shared__ uint32_t s_tab[];
+	__shared__ uint16_t s_map1[SEL_L1];
+	const uint32_t nc = *ncut1;
+	const bool in_smem = nc <= SEL_SMEM_C1;
+	for (uint32_t i = threadIdx.x; i < SEL_L1; i += 1024) {
+		s_map1[i] = (uint16_t)map1[i];
+	}
+	if (in_smem) {
+		for (uint32_t i = threadIdx.x; i < nc * SEL_L2; i += 1024) {
+			s_tab[i] = 0;
+		}
+	}
+	__syncthreads();
+	uint32_t *tab = in_smem ? s_tab : hist2;
+	const unsigned lane = threadIdx.x & 31u;
+	const uint64_t stride = (uint64_t)gridDim.x * 1024;
+	for (uint64_t wbase = (uint64_t)blockIdx.x * 1024 + (threadIdx.x & ~31u); wbase < n; wbase += stride) {
+		const uint64_t i = wbase + lane;
+		uint32_t a = 0xFFFFFFFFu;
+		if (i < n) {
+			const uint32_t key = keys[i];
+			const uint32_t m1 = s_map1[key >> 21];
+			if (m1) {
+				a = (m1 - 1) * SEL_L2 + ((key >> SEL_SH2) & (SEL_L2 - 1));
+			}
+		}
+		sel_count(tab, a, lane);
+	}
+	if (in_smem) {
+		__syncthreads();
+		for (uint32_t i = threadIdx.x; i < nc * SEL_L2; i += 1024) {
+			const uint32_t c = s_tab[i];
+			if (c) {
+				atomicAdd(&hist2[i], c);
+			}
+		}
+	}
+}
+
+__global__ void __launch_bounds__(256) k_sel_hist3(const uint32_t *__restrict__ keys, uint64_t n,
+                                                   const uint32_t *__restrict__ map1, const uint32_t *__restrict__ map2,
+                                                   uint32_t *__restrict__ hist3) {
+	__shared__ uint16_t s_map1[SEL_L1];
+	for (uint32_t i = threadIdx.x; i < SEL_L1; i += 256) {
+		s_map1[i] = (uint16_t)map1[i];
+	}
+	__syncthreads();
+	const unsigned lane = threadIdx.x & 31u;
+	const uint64_t stride = (uint64_t)gridDim.x * 256;
+	for (uint64_t wbase = (uint64_t)blockIdx.x * 256 + (threadIdx.x & ~31u); wbase < n; wbase += stride) {
+		const uint64_t i = wbase + lane;
+		uint32_t a = 0xFFFFFFFFu;
+		if (i < n) {
+			const uint32_t key = keys[i];
+			const uint32_t m1 = s_map1[key >> 21];
+			if (m1) {
+				const uint32_t m2 = map2[(size_t)(m1 - 1) * SEL_L2 + ((key >> SEL_SH2) & (SEL_L2 - 1))];
+				if (m2) {
+					a = (m2 - 1) * SEL_L3 + (key & (SEL_L3 - 1));
+				}
+			}
+		}
+		sel_count(hist3, a, lane);
+	}
+}
+
+// one CTA per level-1 bucket that holds a rank: the level-2 bucket of each of its ranks
+__global__ void __launch_bounds__(SEL_L2 / 2) k_sel_cut2(const uint32_t *__restrict__ hist2, uint32_t nsp,
+                                                          uint32_t *__restrict__ sp, const uint32_t *__restrict__ ncut1) {
+	__shared__ uint32_t s_pre[SEL_L2 + 1];
+	__shared__ uint32_t s_w[33];
+	const uint32_t c = blockIdx.x;
+	if (c >= *ncut1) {
+		return;
+	}
+	const uint32_t t = threadIdx.x;
+	const uint32_t *h = hist2 + (size_t)c * SEL_L2;
+	const uint32_t a = h[2 * t], b = h[2 * t + 1];
+	uint32_t total;
+	const uint32_t ex = sp_block_scan<SEL_L2 / 2>(a + b, s_w, &total);
+	s_pre[2 * t] = ex;
+	s_pre[2 * t + 1] = ex + a;
+	if (t == 0) {
+		s_pre[SEL_L2] = total;
+	}
+	__syncthreads();
+	const uint32_t *rem1 = sp + nsp, *c1 = sp + 2 * (size_t)nsp;
+	uint32_t *b2 = sp + 3 * (size_t)nsp, *rem2 = sp + 4 * (size_t)nsp;
+	for (uint32_t k = t; k < nsp; k += SEL_L2 / 2) {
+		if (c1[k] == c) {
+			const uint32_t r = rem1[k];
+			const uint32_t bk = sp_bucket_of(s_pre, SEL_L2, r);
+			b2[k] = bk;
+			rem2[k] = r - s_pre[bk];
+		}
+	}
+}
+
+// distinct (level-1, level-2) prefixes that hold a rank: sp[5] and map2[c1 * SEL_L2 + b2] = index + 1
+__global__ void __launch_bounds__(1024) k_sel_cut2b(uint32_t nsp, uint32_t *__restrict__ sp, uint32_t *__restrict__ map2) {
+	__shared__ uint32_t s_w[33];
+	const uint32_t t = threadIdx.x;
+	const uint32_t *c1 = sp + 2 * (size_t)nsp, *b2 = sp + 3 * (size_t)nsp;
+	uint32_t *c2 = sp + 5 * (size_t)nsp;
+	uint32_t base = 0;
+	for (uint32_t k0 = 0; k0 < nsp; k0 += 1024) {
+		const uint32_t k = k0 + t;
+		const uint32_t flag = (k < nsp && (k == 0 || c1[k] != c1[k - 1] || b2[k] != b2[k - 1])) ? 1u : 0u;
+		uint32_t tot;
+		const uint32_t e = sp_block_scan<1024>(flag, s_w, &tot);
+		if (k < nsp) {
+			const uint32_t c = base + e + flag - 1;
+			c2[k] = c;
+			if (flag) {
+				map2[(size_t)c1[k] * SEL_L2 + b2[k]] = c + 1;
+			}
+		}
+		base += tot;
+	}
+}
+
+// one CTA per splitter: the low bits from its level-3 histogram -> the cut key. Block 0 also stores the boundary keys
+// a shard of a larger layer brings along (the cut keys of the global order just outside the shard).
+__global__ void __launch_bounds__(256) k_sel_cut3(const uint32_t *__restrict__ hist3, uint32_t nsp, const uint32_t *__restrict__ sp,
+                                                  uint32_t *__restrict__ cuts, uint32_t ncut, int64_t key_lo, int64_t key_hi) {
+	__shared__ uint32_t s_pre[SEL_L3 + 1];
+	__shared__ uint32_t s_w[33];
+	const uint32_t k = blockIdx.x, t = threadIdx.x;
+	if (k == 0 && t == 0) {
+		if (key_lo >= 0) {
+			cuts[0] = (uint32_t)key_lo;
+		}
+		if (key_hi >= 0) {
+			cuts[ncut - 1] = (uint32_t)key_hi;
+		}
+	}
+	if (k >= nsp) {
+		return;
+	}
+	const uint32_t *h = hist3 + (size_t)sp[5 * (size_t)nsp + k] * SEL_L3;
+	constexpr int PER = SEL_L3 / 256;
+	uint32_t v[PER], sum = 0;
+#pragma unroll
+	for (int j = 0; j < PER; j++) {
+		v[j] = h[PER * t + j];
+		sum += v[j];
+	}
+	uint32_t total;
+	uint32_t run = sp_block_scan<256>(sum, s_w, &total);
+#pragma unroll
+	for (int j = 0; j < PER; j++) {
+		s_pre[PER * t + j] = run;
+		run += v[j];
+	}
+	if (t == 0) {
+		s_pre[SEL_L3] = total;
+	}
+	__syncthreads();
+	if (t == 0) {
+		const uint32_t low = sp_bucket_of(s_pre, SEL_L3, sp[4 * (size_t)nsp + k]);
+		cuts[(key_lo >= 0 ? 1 : 0) + k] = (sp[k] << 21) | (sp[3 * (size_t)nsp + k] << SEL_SH2) | low;
+	}
+}
+
+// begin: scratch + zeroing (sel->hist1 is then filled by the key kernel); finish: levels 2, 3 and the cut keys
+int sbi_str_select_begin(sb_context *ctx, uint64_t n, uint64_t slice, int64_t key_lo, int64_t key_hi, sb_str_select *sel) {
+	const uint32_t nsp = (uint32_t)((n + slice - 1) / slice - 1);
+	sel->nsp = nsp;
+	sel->slice = slice;
+	sel->key_lo = key_lo;
+	sel->key_hi = key_hi;
+	sel->ncut = nsp + (key_lo >= 0 ? 1u : 0u) + (key_hi >= 0 ? 1u : 0u);
+	sel->cuts = nullptr;
+	sel->hist1 = nullptr;
+	sel->temp = nullptr;
+	if (sel->ncut == 0) {
+		return SB_OK;
+	}
+	SB_TRY(ctx->scratch_t(sel->ncut, &sel->cuts));
+	if (nsp == 0) {
+		return SB_OK;
+	}
+	const uint32_t c1max = nsp < SEL_L1 ? nsp : SEL_L1;
+	// [hist1 2048][map1 2048][ncut1 (padded to 64)][sp 6 * nsp][hist2 c1max * 512][map2 c1max * 512][hist3 nsp * 4096]
+	const size_t words = 2 * (size_t)SEL_L1 + 64 + 6 * (size_t)nsp + 2 * (size_t)c1max * SEL_L2 + (size_t)nsp * SEL_L3;
+	SB_TRY(ctx->scratch_t(words, &sel->temp));
+	SB_CUDA(cudaMemsetAsync(sel->temp, 0, words * sizeof(uint32_t), ctx->stream));
+	sel->hist1 = sel->temp;
+	return SB_OK;
+}
+
+int sbi_str_select_finish(sb_context *ctx, const uint32_t *xkeys, uint64_t n, sb_str_select *sel) {
+	if (sel->ncut == 0) {
+		return SB_OK;
+	}
+	sb_prof_scope ps(ctx, "str_select");
+	const uint32_t nsp = sel->nsp;
+	const uint32_t c1max = nsp < SEL_L1 ? nsp : SEL_L1;
+	uint32_t *hist1 = sel->temp, *map1 = hist1 + SEL_L1, *ncut1 = map1 + SEL_L1, *sp = ncut1 + 64;
+	uint32_t *hist2 = sp + 6 * (size_t)nsp, *map2 = hist2 + (size_t)c1max * SEL_L2, *hist3 = map2 + (size_t)c1max * SEL_L2;
+	if (nsp) {
+		const unsigned grid = sb_grid(n, 256 * 8, 8);
+		k_sel_cut1<<<1, 1024, 0, ctx->stream>>>(hist1, nsp, sel->slice, sp, map1, ncut1);
+		SB_LAUNCH_CHECK(ctx);
+		SB_SMEM_OPTIN(ctx, k_sel_hist2, SEL_SMEM_C1 * SEL_L2 * sizeof(uint32_t));
+		k_sel_hist2<<<sb_grid(n, 1024 * 16, 1), 1024, SEL_SMEM_C1 * SEL_L2 * sizeof(uint32_t), ctx->stream>>>(xkeys, n, map1, ncut1,
+		                                                                                                    hist2);
+		SB_LAUNCH_CHECK(ctx);
+		k_sel_cut2<<<c1max, SEL_L2 / 2, 0, ctx->stream>>>(hist2, nsp, sp, ncut1);
+		SB_LAUNCH_CHECK(ctx);
+		k_sel_cut2b<<<1, 1024, 0, ctx->stream>>>(nsp, sp, map2);
+		SB_LAUNCH_CHECK(ctx);
+		k_sel_hist3<<<grid, 256, 0, ctx->stream>>>(xkeys, n, map1, map2, hist3);
+		SB_LAUNCH_CHECK(ctx);
+	}
+	k_sel_cut3<<<nsp ? nsp : 1, 256, 0, ctx->stream>>>(hist3, nsp, sp, sel->cuts, sel->ncut, sel->key_lo, sel->key_hi);
+	SB_LAUNCH_CHECK(ctx);
+	return SB_OK;
+}
+
+// ---- the partition ----------------------------------------------------------------------------------------------
+// bin of a key among the sorted cut keys (duplicates allowed): #{cut < key} + #{cut <= key}
+__device__ __forceinline__ uint32_t sp_bin(uint32_t key, const uint32_t *s_cuts, uint32_t ncut) {
+	uint32_t lo = 0, hi = ncut;
+	while (lo < hi) {
+		const uint32_t mid = (lo + hi) >> 1;
+		if (s_cuts[mid] < key) {
+			lo = mid + 1;
+		} else {
+			hi = mid;
+		}
+	}
+	uint32_t ub = lo;
+	if (lo < ncut && s_cuts[lo] == key) {
+		ub = lo + 1;
+		hi = ncut;
+		while (ub < hi) {
+			const uint32_t mid = (ub + hi) >> 1;
+			if (s_cuts[mid] <= key) {
+				ub = mid + 1;
+			} else {
+				hi = mid;
+			}
+		}
+	}
+	return lo + ub;
+}
+
+// generic form: bin ids as 32-bit sort keys (any number of cut keys that fits shared memory)
+__global__ void __launch_bounds__(256) k_part_bins(const uint32_t *__restrict__ xkeys, uint64_t n,
+                                                   const uint32_t *__restrict__ cuts, uint32_t ncut,
+                                                   uint32_t *__restrict__ bins) {
+	extern __shared__ uint32_t s_cuts_dyn[];
+	for (uint32_t i = threadIdx.x; i < ncut; i += 256) {
+		s_cuts_dyn[i] = cuts[i];
+	}
+	__syncthreads();
+	const uint64_t stride = (uint64_t)gridDim.x * 256;
+	for (uint64_t i = (uint64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += stride) {
+		bins[i] = sp_bin(xkeys[i], s_cuts_dyn, ncut);
+	}
+}
+
+int sbi_str_bin_ids(sb_context *ctx, const uint32_t *xkeys, uint64_t n, const uint32_t *cuts, uint32_t ncut,
+                    uint32_t *bins) {
+	SB_ARG(ncut <= 12000, "STR partition: too many slices for one device build");
+	sb_prof_scope ps(ctx, "str_partition");
+	k_part_bins<<<sb_grid(n, 256 * 8, 8), 256, ncut * sizeof(uint32_t), ctx->stream>>>(xkeys, n, cuts, ncut, bins);
+	SB_LAUNCH_CHECK(ctx);
+	return SB_OK;
+}
+
+// fast form (<= SP_MAXBINS bins): count per (tile, bin) -> exclusive positions -> stable scatter of the records
+#define PT_THREADS 256
+#define PT_ITEMS 8
+#define PT_TILE (PT_THREADS * PT_ITEMS) // 2048 records: the scatter stages a tile in shared memory (2 CTAs per SM)
+
+__global__ void __launch_bounds__(PT_THREADS) k_part_count(const uint32_t *__restrict__ xkeys, uint64_t n,
+                                                           const uint32_t *__restrict__ cuts, uint32_t ncut, uint32_t nb,
+                                                           uint16_t *__restrict__ bins, uint32_t *__restrict__ tile_hist) {
+	__shared__ uint32_t s_cuts[SP_MAXBINS / 2];
+	__shared__ uint32_t s_hist[SP_MAXBINS];
+	for (uint32_t i = threadIdx.x; i < ncut; i += PT_THREADS) {
+		s_cuts[i] = cuts[i];
+	}
+	for (uint32_t i = threadIdx.x; i < nb; i += PT_THREADS) {
+		s_hist[i] = 0;
+	}
+	__syncthreads();
+	const uint64_t base = (uint64_t)blockIdx.x * PT_TILE;
+#pragma unroll
+	for (int j = 0; j < PT_ITEMS; j++) {
+		const uint64_t i = base + (uint64_t)j * PT_THREADS + threadIdx.x;
+		if (i < n) {
+			const uint32_t b = sp_bin(xkeys[i], s_cuts, ncut);
+			bins[i] = (uint16_t)b;
+			atomicAdd(&s_hist[b], 1u);
+		}
+	}
+	__syncthreads();
+	// bin-major table [bin][tile]: its exclusive scan, read in memory order, IS the first position of every (tile, bin)
+	for (uint32_t i = threadIdx.x; i < nb; i += PT_THREADS) {
+		tile_hist[(size_t)i * gridDim.x + blockIdx.x] = s_hist[i];
+	}
+}
+
+// exclusive scan of a u32 array in three launches: sums of 2048-element blocks, scan of the sums (one CTA), apply
+#define SC_BLOCK 2048
+__global__ void __launch_bounds__(256) k_scan_sums(const uint32_t *__restrict__ v, uint64_t n, uint32_t *__restrict__ sums) {
+	__shared__ uint32_t s_w[33];
+	const uint64_t base = (uint64_t)blockIdx.x * SC_BLOCK + threadIdx.x * 8;
+	uint32_t a = 0;
+#pragma unroll
+	for (int j = 0; j < 8; j++) {
+		a += base + j < n ? v[base + j] : 0u;
+	}
+	uint32_t tot;
+	sp_block_scan<256>(a, s_w, &tot);
+	if (threadIdx.x == 0) {
+		sums[blockIdx.x] = tot;
+	}
+}
+__global__ void __launch_bounds__(1024) k_scan_top(uint32_t *__restrict__ sums, uint32_t nblk) {
+	__shared__ uint32_t s_w[33];
+	uint32_t carry = 0;
+	for (uint32_t b0 = 0; b0 < nblk; b0 += 1024) {
+		const uint32_t b = b0 + threadIdx.x;
+		const uint32_t a = b < nblk ? sums[b] : 0u;
+		uint32_t tot;
+		const uint32_t e = sp_block_scan<1024>(a, s_w, &tot);
+		if (b < nblk) {
+			sums[b] = carry + e;
+		}
+		carry += tot;
+	}
+}
+__global__ void __launch_bounds__(256) k_scan_apply(uint32_t *__restrict__ v, uint64_t n, const uint32_t *__restrict__ sums) {
+	__shared__ uint32_t s_w[33];
+	const uint64_t base = (uint64_t)blockIdx.x * SC_BLOCK + threadIdx.x * 8;
+	uint32_t x[8], a = 0;
+#pragma unroll
+	for (int j = 0; j < 8; j++) {
+		x[j] = base + j < n ? v[base + j] : 0u;
+		a += x[j];
+	}
+	uint32_t tot;
+	uint32_t run = sums[blockIdx.x] + sp_block_scan<256>(a, s_w, &tot);
+#pragma unroll
+	for (int j = 0; j < 8; j++) {
+		if (base + j < n) {
+			v[base + j] = run;
+		}
+		run += x[j];
+	}
+}
+
+// stable scatter of a tile: rank of every record among the tile's records of its bin (warp multi-split over the bin
+// bits + per-warp counters, warps in order), the records are laid out in tile-sorted order in shared memory and leave
+// as runs per bin, so that a store instruction covers whole 32-byte sectors of consecutive records (direct 16-byte
+// stores from the ranking threads cost 3 sector transactions per record: 332 us for 10 M records).
+#define PS_KBINS ((SP_MAXBINS + PT_THREADS - 1) / PT_THREADS) // bins per thread in the per-bin steps
+struct ps_smem {
+	float4 rec[2 * PT_TILE];                    // tile-sorted records, two 16-byte halves each
+	uint32_t yk[PT_TILE];                       // their y keys
+	uint32_t gl[SP_MAXBINS + 3];                // first global position of the bin's run - first tile position of the run
+	uint16_t wh[PT_THREADS / 32][SP_MAXBINS + 1]; // per-warp bin counts -> exclusive offsets of the warps inside a bin
+	uint16_t doff[SP_MAXBINS + 3];              // first tile position of the bin's run
+	uint16_t bin[PT_TILE];                      // bin of the record in tile position p
+	uint32_t scan[33];
+};
+__global__ void __launch_bounds__(PT_THREADS) k_part_scatter(const uint16_t *__restrict__ bins, uint64_t n, uint32_t nb,
+                                                             int nbits, const uint32_t *__restrict__ tile_pos,
+                                                             const float4 *__restrict__ box, const int64_t *__restrict__ rows,
+                                                             const uint32_t *__restrict__ ykeys, sb_rec32 *__restrict__ rec_out,
+                                                             uint32_t *__restrict__ ykey_out) {
+	extern __shared__ __align__(16) unsigned char ps_raw[];
+	ps_smem &S = *reinterpret_cast<ps_smem *>(ps_raw);
+	{
+		uint32_t *z = reinterpret_cast<uint32_t *>(&S.wh[0][0]);
+		for (uint32_t i = threadIdx.x; i < sizeof(S.wh) / 4; i += PT_THREADS) {
+			z[i] = 0;
+		}
+	}
+	__syncthreads();
+	const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+	const unsigned lt_mask = sb_lanemask_lt();
+	const uint64_t tile_base = (uint64_t)blockIdx.x * PT_TILE;
+	const uint32_t tile_count = (uint32_t)min((uint64_t)PT_TILE, n - tile_base);
+	const uint64_t first = tile_base + (uint64_t)warp * (32 * PT_ITEMS) + lane;
+	uint32_t br[PT_ITEMS]; // bin | rank in the warp << 16
+	uint16_t *my = S.wh[warp];
+#pragma unroll
+	for (int i = 0; i < PT_ITEMS; i++) {
+		const uint64_t gi = first + (uint64_t)i * 32;
+		const bool valid = gi < n;
+		const uint32_t b = valid ? bins[gi] : 0u;
+		unsigned peers = __ballot_sync(0xFFFFFFFFu, valid);
+#pragma unroll
+		for (int k = 0; k < 11; k++) {
+			if (k < nbits) {
+				const bool bit = (b >> k) & 1u;
+				const unsigned m = __ballot_sync(0xFFFFFFFFu, bit);
+				peers &= bit ? m : ~m;
+			}
+		}
+		const int leader = __ffs(peers) - 1;
+		uint32_t prev = 0;
+		if ((int)lane == leader && valid) {
+			prev = my[b];
+			my[b] = (uint16_t)(prev + __popc(peers));
+		}
+		prev = __shfl_sync(0xFFFFFFFFu, prev, leader < 0 ? 0 : leader);
+		br[i] = b | ((prev + __popc(peers & lt_mask)) << 16);
+		__syncwarp();
+	}
+	__syncthreads();
+	// thread t owns bins [t * K, (t + 1) * K): offsets of the warps inside each bin, run starts by a block scan
+	{
+		uint32_t tot[PS_KBINS], sum = 0;
+#pragma unroll
+		for (int k = 0; k < PS_KBINS; k++) {
+			const uint32_t b = threadIdx.x * PS_KBINS + k;
+			uint32_t run = 0;
+			if (b < nb) {
+#pragma unroll
+				for (int w = 0; w < PT_THREADS / 32; w++) {
+					const uint32_t c = S.wh[w][b];
+					S.wh[w][b] = (uint16_t)run;
+					run += c;
+				}
+			}
+			tot[k] = run;
+			sum += run;
+		}
+		uint32_t all;
+		uint32_t run = sp_block_scan<PT_THREADS>(sum, S.scan, &all);
+#pragma unroll
+		for (int k = 0; k < PS_KBINS; k++) {
+			const uint32_t b = threadIdx.x * PS_KBINS + k;
+			if (b < nb) {
+				S.doff[b] = (uint16_t)run;
+				S.gl[b] = tile_pos[(size_t)b * gridDim.x + blockIdx.x] - run;
+			}
+			run += tot[k];
+		}
+	}
+	__syncthreads();
+	// records into tile-sorted order
+#pragma unroll 4
+	for (int i = 0; i < PT_ITEMS; i++) {
+		const uint64_t gi = first + (uint64_t)i * 32;
+		if (gi < n) {
+			const uint32_t b = br[i] & 0xFFFFu;
+			const uint32_t p = (uint32_t)S.doff[b] + my[b] + (br[i] >> 16);
+			const float4 bx = box[gi];
+			const int64_t r = rows[gi];
+			const uint32_t yk = ykeys[gi];
+			S.rec[2 * p] = bx;
+			S.rec[2 * p + 1] = make_float4(__int_as_float((int)(uint32_t)(uint64_t)r),
+			                               __int_as_float((int)(uint32_t)((uint64_t)r >> 32)), __uint_as_float(yk), 0.0f);
+			S.yk[p] = yk;
+			S.bin[p] = (uint16_t)b;
+		}
+	}
+	__syncthreads();
+	// out: consecutive threads store consecutive 16-byte halves / y keys of the tile order (runs per bin in global memory)
+	float4 *out4 = reinterpret_cast<float4 *>(rec_out);
+	for (uint32_t c = threadIdx.x; c < 2 * tile_count; c += PT_THREADS) {
+		const uint32_t p = c >> 1;
+		const uint32_t g = S.gl[S.bin[p]] + p;
+		out4[2 * (size_t)g + (c & 1u)] = S.rec[c];
+	}
+	for (uint32_t p = threadIdx.x; p < tile_count; p += PT_THREADS) {
+		ykey_out[S.gl[S.bin[p]] + p] = S.yk[p];
+	}
+}
+
+int sbi_str_partition_rec(sb_context *ctx, const float4 *box, const int64_t *rows, const uint32_t *xkeys,
+                          const uint32_t *ykeys, uint64_t n, const uint32_t *cuts, uint32_t ncut, sb_rec32 *rec_out,
+                          uint32_t *ykey_out) {
+	const uint32_t nb = 2 * ncut + 1;
+	SB_ARG(nb <= SP_MAXBINS, "STR partition: bin count");
+	int nbits = 0;
+	while ((1u << nbits) < nb) {
+		nbits++;
+	}
+	const uint32_t tiles = (uint32_t)((n + PT_TILE - 1) / PT_TILE);
+	const uint64_t cells = (uint64_t)tiles * nb;
+	const uint32_t nblk = (uint32_t)((cells + SC_BLOCK - 1) / SC_BLOCK);
+	uint16_t *bins = nullptr;
+	uint32_t *tile_hist = nullptr, *sums = nullptr;
+	SB_TRY(ctx->scratch_t(n, &bins));
+	SB_TRY(ctx->scratch_t(cells, &tile_hist));
+	SB_TRY(ctx->scratch_t(nblk, &sums));
+	sb_prof_scope ps(ctx, "str_partition");
+	k_part_count<<<tiles, PT_THREADS, 0, ctx->stream>>>(xkeys, n, cuts, ncut, nb, bins, tile_hist);
+	SB_LAUNCH_CHECK(ctx);
+	k_scan_sums<<<nblk, 256, 0, ctx->stream>>>(tile_hist, cells, sums);
+	SB_LAUNCH_CHECK(ctx);
+	k_scan_top<<<1, 1024, 0, ctx->stream>>>(sums, nblk);
+	SB_LAUNCH_CHECK(ctx);
+	k_scan_apply<<<nblk, 256, 0, ctx->stream>>>(tile_hist, cells, sums);
+	SB_LAUNCH_CHECK(ctx);
+	SB_SMEM_OPTIN(ctx, k_part_scatter, sizeof(ps_smem));
+	k_part_scatter<<<tiles, PT_THREADS, sizeof(ps_smem), ctx->stream>>>(bins, n, nb, nbits, tile_hist, box, rows, ykeys, rec_out,
+	                                                                   ykey_out);
+	SB_LAUNCH_CHECK(ctx);
+	return SB_OK;
+}

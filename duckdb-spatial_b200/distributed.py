@@ -158,10 +158,12 @@ def sharded_rtree_build(box4, row_ids, cap, sort_keys, leaf_shard, assemble, dst
 
     box4 [n_r, 4] float32, row_ids [n_r] int64: this rank's rows.
     sort_keys(keys int64) -> (sorted keys, permutation int64)        device sort of 63-bit keys
-    leaf_shard(box4, row_ids, cap, slice, node_base) -> (leaf entries uint8 [n, 24], node entries uint8 [nodes, 24])
+    leaf_shard(box4, row_ids, cap, slice, node_base, x_key_before, x_key_after)
+                                              -> (leaf entries uint8 [n, 24], node entries uint8 [nodes, 24])
     assemble(leaf entries, n, node entries, cap) -> the tree (called on `dst` only)
     Steps: x keys -> globally unique 63-bit keys (x key, global input position) -> exact, slice-aligned splitters by
-    bisection -> all-to-all of the rows -> local order -> leaf level of the rank's slices -> gather -> upper levels."""
+    bisection -> all-to-all of the rows -> rows back in global input order + the x keys at the range's two ends -> leaf
+    level of the rank's slices -> gather -> upper levels."""
     rank, world = dist.get_rank(), dist.get_world_size()
     dev = box4.device
     n_r = box4.shape[0]
@@ -191,10 +193,17 @@ def sharded_rtree_build(box4, row_ids, cap, sort_keys, leaf_shard, assemble, dst
     rkeys = exchange(skeys)
     rbox = exchange(box4[perm])
     rrow = exchange(row_ids[perm])
-    _, order = sort_keys(rkeys)  # the received runs are sorted; one more sort merges them (ties by global position)
+    # the leaf level wants its rows in ascending global input position (equal y keys of a slice keep that order) and the
+    # x keys of the global order at the two ends of the range: the range's own smallest key and the next range's
+    _, order = sort_keys(rkeys & ((1 << 31) - 1))
     lo = min(rank * chunk, n)
     assert m == min((rank + 1) * chunk, n) - lo, "exact splitters must give every rank its slice-aligned range"
-    leaf, nodes = leaf_shard(rbox[order].contiguous(), rrow[order].contiguous(), cap, slice_size, lo // cap)
+    first = torch.full((world,), -1, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(first, (rkeys.min() >> 31).reshape(1) if m else torch.full((1,), -1, dtype=torch.int64, device=dev))
+    fl = [int(v) for v in first.tolist()]
+    before = fl[rank] if lo > 0 else -1
+    after = next((v for v in fl[rank + 1:] if v >= 0), -1)
+    leaf, nodes = leaf_shard(rbox[order].contiguous(), rrow[order].contiguous(), cap, slice_size, lo // cap, before, after)
     leaf_all = gather_rows(leaf, dst)
     nodes_all = gather_rows(nodes, dst)
     if rank == dst:

@@ -533,15 +533,17 @@ class RTreeIndex:
         self.cap = max_node_capacity
 
     @staticmethod
-    def leaf_shard(ctx, box4, row_ids, max_node_capacity, slice_size, node_base):
+    def leaf_shard(ctx, box4, row_ids, max_node_capacity, slice_size, node_base, x_key_before=-1, x_key_after=-1):
         """multi-GPU build, per rank: leaf entries + node entries (uint8 [., 24]) of a slice-aligned shard of the global x
-        order (sb_rtree_build_leaf_shard)."""
+        order, rows in ascending global input position; x_key_before / x_key_after: the global order's x keys at the
+        shard's first rank and just after its last (-1 at the layer's ends) (sb_rtree_build_leaf_shard)."""
         n = len(row_ids)
         nodes = (n + max_node_capacity - 1) // max_node_capacity
         leaf = ctx._empty(box4, (n, 24), np.uint8)
         node = ctx._empty(box4, (nodes, 24), np.uint8)
         capi.check(ctx.L.sb_rtree_build_leaf_shard(ctx.h, ctx._mem(box4, row_ids), _ptr(box4), _ptr(row_ids), n,
-                                                   max_node_capacity, slice_size, node_base, _ptr(leaf), _ptr(node)))
+                                                   max_node_capacity, slice_size, node_base, int(x_key_before),
+                                                   int(x_key_after), _ptr(leaf), _ptr(node)))
         return leaf, node
 
     @classmethod

@@ -159,18 +159,23 @@ SB_API int sb_rtree_build_str(sb_context *ctx, sb_mem mem, const float *box4, co
                               uint32_t max_node_capacity, sb_rtree **out);
 /* ---- multi-GPU CREATE INDEX (one process per GPU; the host side is duckdb-spatial_b200/distributed.py) ----------------
  * The reference builds the index in one process (PhysicalCreateRTreeIndex, rtree_index_create_physical.cpp:95-256); past
- * one GPU's memory the ORDER BY becomes a distributed sample sort: every rank ends up with a contiguous, slice-aligned
- * range of the global x order (ties by global input position) and builds ITS part of the leaf level; the nodes' entries
- * (one per leaf page) are gathered and the upper levels built from them. The result is the tree sb_rtree_build_str
- * builds over the whole input, node for node.
+ * one GPU's memory the ORDER BY becomes a distributed sample sort: every rank ends up with the rows of a contiguous,
+ * slice-aligned range of the global x order (ties by global input position) and builds ITS part of the leaf level; the
+ * nodes' entries (one per leaf page) are gathered and the upper levels built from them. The result is the tree
+ * sb_rtree_build_str builds over the whole input, node for node.
  *   sb_rtree_slice_for        the global slice size, Finalize :349-351: ceil(sqrt(ceil(n / cap))) * cap
  *   sb_rtree_build_leaf_shard leaf entries (24 B x n_shard, shard order) + one node entry per leaf page, pointer =
  *                             (LEAF_PAGE << 56) | (node_base + page); the shard must start at a multiple of slice_size
+ *                             and list its rows in ascending GLOBAL input position. x_key_before / x_key_after: the
+ *                             32-bit x sort key (order-preserving bits of float(min_x + max_x)) of the global order at
+ *                             the shard's first rank and at the first rank after the shard, -1 at the layer's two ends
+ *                             (they keep equal-y ties of the boundary slices in the single-device order)
  *   sb_rtree_from_leaf_level  the whole tree from all leaf entries (global order) and all node entries (page order) */
 SB_API uint64_t sb_rtree_slice_for(uint64_t n, uint32_t max_node_capacity);
 SB_API int sb_rtree_build_leaf_shard(sb_context *ctx, sb_mem mem, const float *box4, const int64_t *row_ids, uint64_t n_shard,
                                      uint32_t max_node_capacity, uint64_t slice_size, uint64_t node_base,
-                                     void *out_leaf_entries, void *out_node_entries);
+                                     int64_t x_key_before, int64_t x_key_after, void *out_leaf_entries,
+                                     void *out_node_entries);
 SB_API int sb_rtree_from_leaf_level(sb_context *ctx, sb_mem mem, const void *leaf_entries, uint64_t n,
                                     const void *node_entries, uint32_t max_node_capacity, sb_rtree **out);
 /* CREATE INDEX straight from the GEOMETRY key column: TryGetCachedBounds per row (geometry_type.hpp:102-148), rows

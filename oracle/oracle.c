@@ -919,13 +919,38 @@ ORC_API double orc_str_sort_key(const float *box) {
 	return (double)(box[0] + box[2]) * 0.5;
 }
 
-ORC_API orc_rtree *orc_rtree_build_str(const float *box4, const int64_t *rowid, uint64_t n, uint32_t cap) {
+/* The y order inside a slice of the leaf level. The reference re-sorts each slice with std::sort by y centre
+ * (rtree_index_create_physical.cpp:172-176), which leaves the order of EQUAL y keys unspecified; the CUDA build (and
+ * this restatement) fixes it as (y key, x bin, input position), x bin = #{cut < x key} + #{cut <= x key} over the x keys at
+ * the slice boundaries of the (x key, input position) order -- the order its stable partition into slices produces. */
+typedef struct {
+	double key;
+	uint64_t bin;
+	uint64_t idx; /* input position */
+	uint64_t pos; /* position in the layer */
+} ykeypos;
+
+static int cmp_ykeypos(const void *a, const void *b) {
+	const ykeypos *x = (const ykeypos *)a, *y = (const ykeypos *)b;
+	if (x->key != y->key) {
+		return x->key < y->key ? -1 : 1;
+	}
+	if (x->bin != y->bin) {
+		return x->bin < y->bin ? -1 : 1;
+	}
+	return x->idx < y->idx ? -1 : (x->idx > y->idx ? 1 : 0);
+}
+
+/* x_key_before / x_key_after: NULL, or the x sort keys of an enclosing order just outside this range (shards of a
+ * multi-GPU build bring the global cut keys at their two ends along) */
+static orc_rtree *rtree_build_str_impl(const float *box4, const int64_t *rowid, uint64_t n, uint32_t cap, uint64_t slice,
+                                       const double *x_key_before, const double *x_key_after) {
 	orc_rtree *t = (orc_rtree *)calloc(1, sizeof(orc_rtree));
 	t->cap = cap;
 	if (n == 0) {
 		return t;
 	}
-	t->slice = orc_str_slice_size(n, cap);
+	t->slice = slice ? slice : orc_str_slice_size(n, cap);
 	/* ORDER BY x-centre */
 	keypos *kp = (keypos *)malloc(sizeof(keypos) * n);
 	for (uint64_t i = 0; i < n; i++) {
@@ -933,28 +958,57 @@ ORC_API orc_rtree *orc_rtree_build_str(const float *box4, const int64_t *rowid, 
 		kp[i].pos = i;
 	}
 	qsort(kp, n, sizeof(keypos), cmp_keypos);
+	/* cut keys: the x keys at ranks slice, 2 * slice, ... (+ the boundary keys of a shard) */
+	const uint64_t nsp = (n + t->slice - 1) / t->slice - 1;
+	double *cuts = (double *)malloc(sizeof(double) * (nsp + 2));
+	uint64_t ncut = 0;
+	if (x_key_before) {
+		cuts[ncut++] = *x_key_before;
+	}
+	for (uint64_t k = 1; k <= nsp; k++) {
+		cuts[ncut++] = kp[k * t->slice].key;
+	}
+	if (x_key_after) {
+		cuts[ncut++] = *x_key_after;
+	}
 	orc_entry *cur = (orc_entry *)malloc(sizeof(orc_entry) * n);
+	uint64_t *cur_bin = (uint64_t *)malloc(sizeof(uint64_t) * n), *cur_idx = (uint64_t *)malloc(sizeof(uint64_t) * n);
 	for (uint64_t i = 0; i < n; i++) {
 		cur[i].ptr = (uint64_t)rowid[kp[i].pos] & 0x00FFFFFFFFFFFFFFULL;
 		memcpy(cur[i].box, box4 + 4 * kp[i].pos, 16);
+		uint64_t lb = 0, ub = 0;
+		for (uint64_t c = 0; c < ncut; c++) { /* fine for a test oracle: ncut ~ sqrt(n / cap) */
+			lb += cuts[c] < kp[i].key;
+			ub += cuts[c] <= kp[i].key;
+		}
+		cur_bin[i] = lb + ub;
+		cur_idx[i] = kp[i].pos;
 	}
+	free(cuts);
 	free(kp);
 	uint64_t cnt = n;
 	int level = 0;
 	while (cnt != 1) {
 		/* sort each slice by fp32 y centre: bounds.Center().y = (min.y + max.y) / 2 in float (bbox.hpp:78-80) */
-		keypos *sk = (keypos *)malloc(sizeof(keypos) * cnt);
+		ykeypos *sk = (ykeypos *)malloc(sizeof(ykeypos) * cnt);
 		orc_entry *sorted = (orc_entry *)malloc(sizeof(orc_entry) * cnt);
 		for (uint64_t s = 0; s < cnt; s += t->slice) {
 			const uint64_t e = s + t->slice < cnt ? s + t->slice : cnt;
 			for (uint64_t i = s; i < e; i++) {
 				sk[i].key = (double)((cur[i].box[1] + cur[i].box[3]) / 2.0f);
+				sk[i].bin = level == 0 ? cur_bin[i] : 0;
+				sk[i].idx = level == 0 ? cur_idx[i] : i; /* upper levels: ties keep the node order */
 				sk[i].pos = i;
 			}
-			qsort(sk + s, e - s, sizeof(keypos), cmp_keypos);
+			qsort(sk + s, e - s, sizeof(ykeypos), cmp_ykeypos);
 			for (uint64_t i = s; i < e; i++) {
 				sorted[i] = cur[sk[i].pos];
 			}
+		}
+		if (level == 0) {
+			free(cur_bin);
+			free(cur_idx);
+			cur_bin = cur_idx = NULL;
 		}
 		free(sk);
 		free(cur);
@@ -983,6 +1037,8 @@ ORC_API orc_rtree *orc_rtree_build_str(const float *box4, const int64_t *rowid, 
 		cur = next;
 		cnt = nn;
 	}
+	free(cur_bin);
+	free(cur_idx);
 	if (level == 0) {
 		/* single row id: wrapped into a leaf page (:241-246) */
 		t->levels[0] = cur;
@@ -999,6 +1055,20 @@ ORC_API orc_rtree *orc_rtree_build_str(const float *box4, const int64_t *rowid, 
 	t->counts[level] = 1;
 	t->nlevels = level + 1;
 	return t;
+}
+
+ORC_API orc_rtree *orc_rtree_build_str(const float *box4, const int64_t *rowid, uint64_t n, uint32_t cap) {
+	return rtree_build_str_impl(box4, rowid, n, cap, 0, NULL, NULL);
+}
+
+/* leaf level of a slice-aligned shard of a larger layer (multi-GPU build): `slice` is the global slice size, the
+ * boundary keys are orc_str_sort_key values (has_before / has_after = 0: the shard touches that end of the layer).
+ * The returned tree's level 0 / level 1 are the shard's leaf entries and leaf-page entries (page numbers from 0). */
+ORC_API orc_rtree *orc_rtree_build_str_shard(const float *box4, const int64_t *rowid, uint64_t n, uint32_t cap,
+                                             uint64_t slice, int has_before, double x_key_before, int has_after,
+                                             double x_key_after) {
+	return rtree_build_str_impl(box4, rowid, n, cap, slice, has_before ? &x_key_before : NULL,
+	                            has_after ? &x_key_after : NULL);
 }
 
 ORC_API void orc_rtree_free(orc_rtree *t) {

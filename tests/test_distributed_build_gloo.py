@@ -27,13 +27,24 @@ def _f32_key(f):
     return np.where(r & 0x80000000, 0xFFFFFFFF - r, r | 0x80000000)
 
 
-def np_leaf_shard(box, rows, cap, slice_size, node_base):
-    """STR leaf level of a slice-aligned shard (rtree_index_create_physical.cpp:136-256): stable x order, stable y
-    order inside runs of `slice_size`, `cap` entries per node ordered by row id, node box = fp32 union"""
+def np_leaf_shard(box, rows, cap, slice_size, node_base, key_before=-1, key_after=-1):
+    """STR leaf level of a slice-aligned shard (rtree_index_create_physical.cpp:136-256), rows in ascending global input
+    position: slices of the (x key, position) order, inside a slice by (y key, x bin, position) with x bin = #{cut < key}
+    + #{cut <= key} over the x keys at the slice boundaries (and at the shard's two ends), `cap` entries per node ordered
+    by row id, node box = fp32 union"""
     n = len(rows)
-    xo = np.argsort(_f32_key(box[:, 0] + box[:, 2]), kind="stable")
+    xk = _f32_key(box[:, 0] + box[:, 2])
+    xo = np.argsort(xk, kind="stable")
+    cuts = [int(xk[xo[r]]) for r in range(slice_size, n, slice_size)]
+    cuts = ([key_before] if key_before >= 0 else []) + cuts + ([key_after] if key_after >= 0 else [])
+    cuts = np.array(cuts, np.uint64)
+    bins = np.searchsorted(cuts, xk, "left") + np.searchsorted(cuts, xk, "right")
     yk = _f32_key((box[:, 1] + box[:, 3]) / np.float32(2))
-    perm = np.concatenate([xo[s:s + slice_size][np.argsort(yk[xo[s:s + slice_size]], kind="stable")] for s in range(0, n, slice_size)]) if n else xo
+    parts = []
+    for s in range(0, n, slice_size):
+        idx = xo[s:s + slice_size]
+        parts.append(idx[np.lexsort((idx, bins[idx], yk[idx]))])
+    perm = np.concatenate(parts) if n else xo
     leaf = np.zeros(n, ENTRY)
     nodes = np.zeros((n + cap - 1) // cap, ENTRY)
     for j in range(len(nodes)):
@@ -63,6 +74,8 @@ def _worker(rank, world, port, n, cap, out_dir):
     try:
         x, y = O.generate_points(31, n, (0, 0, 100, 100))
         x = np.round(x, 1)  # many equal x keys: ties must follow the global input position
+        if n == 20_000:
+            y = np.round(y, 0)  # and many equal y keys inside every slice: (y key, x bin, input position)
         box = O.bbox_from_points(x, y)
         rows = np.arange(n, dtype=np.int64) * 3 + 7
         b, e = D.shard_range(n, rank, world)
@@ -71,8 +84,8 @@ def _worker(rank, world, port, n, cap, out_dir):
             s, p = torch.sort(k, stable=True)
             return s, p
 
-        def leaf_shard(bx, rw, cap_, slice_size, node_base):
-            leaf, nodes = np_leaf_shard(bx.numpy(), rw.numpy(), cap_, slice_size, node_base)
+        def leaf_shard(bx, rw, cap_, slice_size, node_base, key_before, key_after):
+            leaf, nodes = np_leaf_shard(bx.numpy(), rw.numpy(), cap_, slice_size, node_base, key_before, key_after)
             return (torch.from_numpy(leaf.view(np.uint8).reshape(-1, 24).copy()), torch.from_numpy(nodes.view(np.uint8).reshape(-1, 24).copy()))
 
         def assemble(leaf_all, n_all, nodes_all, cap_):
@@ -96,6 +109,8 @@ def test_sharded_rtree_build_gloo(O, tmp_path, world, n, cap):
     leaf, nodes = np.load(tmp_path / "leaf.npy"), np.load(tmp_path / "nodes.npy")
     x, y = O.generate_points(31, n, (0, 0, 100, 100))
     x = np.round(x, 1)
+    if n == 20_000:
+        y = np.round(y, 0)
     box = O.bbox_from_points(x, y)
     rows = np.arange(n, dtype=np.int64) * 3 + 7
     t = O.StrTree(box, rows, cap)

@@ -155,6 +155,8 @@ def _build_worker(rank, world, port, n, cap, q):
     ctx.use_torch_stream()
     x, y = O.generate_points(31, n, (0, 0, 1000, 1000))
     x = np.round(x, 2)  # equal x keys: ties follow the global input position
+    if cap == 16:
+        y = np.round(y, 0)  # equal y keys inside the slices: (y key, x bin, input position)
     box = O.bbox_from_points(x, y)
     rows = np.arange(n, dtype=np.int64) * 3 + 7
     b, e = D.shard_range(n, rank, world)
@@ -166,7 +168,7 @@ def _build_worker(rank, world, port, n, cap, q):
         return kk, vv.long()
 
     tree = D.sharded_rtree_build(torch.from_numpy(box[b:e].copy()).to(dev), torch.from_numpy(rows[b:e].copy()).to(dev), cap, sort_keys,
-                                 lambda bx, rw, c, s, nb: sb.RTreeIndex.leaf_shard(ctx, bx, rw, c, s, nb),
+                                 lambda bx, rw, c, s, nb, kb, ka: sb.RTreeIndex.leaf_shard(ctx, bx, rw, c, s, nb, kb, ka),
                                  lambda leaf, nn, nodes, c: sb.RTreeIndex.from_leaf_level(ctx, leaf, nn, nodes, c))
     if rank == 0:
         ref = sb.RTreeIndex(ctx, box, rows, cap)
