@@ -14,18 +14,21 @@
 #define RS_FLAG_INC 0x80000000u
 #define RS_VALUE_MASK 0x3FFFFFFFu
 #define RS_LOOK 8 // predecessor status words fetched per look-back round
-// onesweep pass kernel shape (tile = OS_THREADS * items keys)
+// onesweep pass kernel shape (tile = OS_THREADS * items keys). Measured on the C1 build (16 launches, 10 M keys, sum of the
+// onesweep scopes): 256 threads x 16 keys, 3 CTAs / SM (80 registers, spills) 0.873 ms; 4 CTAs / SM with late value loads
+// and packed ranks 1.00 - 1.06 ms; 5 CTAs 4.3 ms (spills); 512 threads x 8 keys, 2 CTAs / SM 0.801 ms (kept);
+// 512 x 8 with 3 CTAs 0.81 - 0.88 ms. Occupancy is not what bounds the pass.
 #ifndef OS_THREADS
-#define OS_THREADS 256
+#define OS_THREADS 512
 #endif
 #ifndef OS_ITEMS32
-#define OS_ITEMS32 16
+#define OS_ITEMS32 8
 #endif
 #ifndef OS_ITEMS64
-#define OS_ITEMS64 12
+#define OS_ITEMS64 6
 #endif
 #ifndef OS_MIN_CTAS
-#define OS_MIN_CTAS 3
+#define OS_MIN_CTAS 2
 #endif
 #ifndef OS_LATE_VALS
 #define OS_LATE_VALS 0 // 1: values are loaded after the ranking (not live across it), 2: at the scatter

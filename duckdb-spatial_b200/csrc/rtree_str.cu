@@ -118,35 +118,92 @@ __global__ void __launch_bounds__(256)
 	}
 	uint32_t rank = t;
 	if (LEAF) {
-		// rank of the entry among the node's row ids. Fast path: when every row id of the node is within 2^31 of
-		// the first one, ranks are counted over 32-bit offsets read four at a time; equal row ids (not expected:
-		// row ids are unique) or a wider spread fall back to the 64-bit count with the position tie-break.
-		__shared__ __align__(16) uint32_t s_k32[256];
-		__shared__ uint32_t s_slot[256];
+		// rank of the entry among the node's row ids. All-pairs counting (cap compares per entry) made the pack
+		// instruction bound (205 M warp instructions at C1); the row ids are bucketed instead: 256 buckets by a monotone
+		// map of (row id - node minimum), bucket starts from a scan, and an entry only compares itself with the entries of
+		// its own bucket (about one). Nodes whose row ids spread over 2^32 or crowd into one bucket (> 8) take the 64-bit
+		// all-pairs count with the position tie-break (equal row ids are not expected: row ids are unique).
+		__shared__ uint32_t s_cnt[257];
+		__shared__ uint32_t s_key[256];
+		__shared__ uint8_t s_src[256];
+		__shared__ unsigned long long s_mm[2][8];
 		const int64_t mine = (int64_t)(e.ptr << 8) >> 8; // sign-extended 56-bit row id
+		const unsigned long long u = (unsigned long long)mine ^ 0x8000000000000000ull; // unsigned order = signed order
+		unsigned long long mn = t < cnt ? u : ~0ull, mx = t < cnt ? u : 0ull;
+#pragma unroll
+		for (int s = 16; s > 0; s >>= 1) {
+			const unsigned long long a = __shfl_xor_sync(0xFFFFFFFFu, mn, s), b = __shfl_xor_sync(0xFFFFFFFFu, mx, s);
+			mn = a < mn ? a : mn;
+			mx = b > mx ? b : mx;
+		}
+		if (sb_lane() == 0) {
+			s_mm[0][t >> 5] = mn;
+			s_mm[1][t >> 5] = mx;
+		}
+		for (uint32_t i = t; i < 257; i += blockDim.x) {
+			s_cnt[i] = 0;
+		}
 		if (t < cnt) {
 			s_row[t] = mine;
 		}
 		__syncthreads();
-		const int64_t d = mine - s_row[0];
-		const bool narrow = t >= cnt || d == (int64_t)(int32_t)d;
-		const uint32_t k32 = t < cnt ? (uint32_t)(int32_t)d ^ 0x80000000u : 0xFFFFFFFFu;
-		s_k32[t] = k32;
-		bool slow = !__syncthreads_and(narrow);
-		if (!slow) {
-			rank = 0;
-			const uint4 *k4 = reinterpret_cast<const uint4 *>(s_k32);
-			for (uint32_t k = 0; k < (cnt + 3) / 4; k++) {
-				const uint4 v = k4[k];
-				rank += (v.x < k32) + (v.y < k32) + (v.z < k32) + (v.w < k32);
-			}
-			if (t < cnt) {
-				s_slot[rank] = t;
+		for (unsigned w = 0; w < (blockDim.x >> 5); w++) {
+			const unsigned long long a = s_mm[0][w], b = s_mm[1][w];
+			mn = a < mn ? a : mn;
+			mx = b > mx ? b : mx;
+		}
+		const unsigned long long range = mx - mn;
+		const bool fast = range < 0xFFFFFFFFull;
+		uint32_t k32 = 0, bkt = 0, slot = 0;
+		if (fast && t < cnt) {
+			k32 = (uint32_t)(u - mn);
+			// conversion, product with a positive constant and truncation are monotone: so is the bucket
+			bkt = min(255u, __float2uint_rz(__uint2float_rz(k32) * (256.0f / (__ull2float_rz(range) + 1.0f))));
+			slot = atomicAdd(&s_cnt[bkt], 1u);
+		}
+		const bool crowded = __syncthreads_or(slot >= 8);
+		if (fast && !crowded) {
+			if (t < 32) { // exclusive scan of the 256 counts: 8 per lane
+				uint32_t c[8], sum = 0;
+#pragma unroll
+				for (int j = 0; j < 8; j++) {
+					c[j] = s_cnt[t * 8 + j];
+					sum += c[j];
+				}
+				uint32_t inc = sum;
+#pragma unroll
+				for (int s = 1; s < 32; s <<= 1) {
+					const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, s);
+					if (t >= (unsigned)s) {
+						inc += o;
+					}
+				}
+				uint32_t run = inc - sum;
+#pragma unroll
+				for (int j = 0; j < 8; j++) {
+					s_cnt[t * 8 + j] = run;
+					run += c[j];
+				}
+				if (t == 31) {
+					s_cnt[256] = run;
+				}
 			}
 			__syncthreads();
-			slow = __syncthreads_or(t < cnt && s_slot[rank] != t);
-		}
-		if (slow && t < cnt) {
+			if (t < cnt) {
+				const uint32_t pos = s_cnt[bkt] + slot;
+				s_key[pos] = k32;
+				s_src[pos] = (uint8_t)t;
+			}
+			__syncthreads();
+			if (t < cnt) {
+				const uint32_t beg = s_cnt[bkt], end = s_cnt[bkt + 1];
+				rank = beg;
+				for (uint32_t j = beg; j < end; j++) {
+					const uint32_t kk = s_key[j];
+					rank += (kk < k32) || (kk == k32 && s_src[j] < t);
+				}
+			}
+		} else if (t < cnt) {
 			rank = 0;
 			for (uint32_t k = 0; k < cnt; k++) {
 				const int64_t o = s_row[k];

@@ -420,7 +420,7 @@ int sbi_str_bin_ids(sb_context *ctx, const uint32_t *xkeys, uint64_t n, const ui
 // fast form (<= SP_MAXBINS bins): count per (tile, bin) -> exclusive positions -> stable scatter of the records
 #define PT_THREADS 256
 #define PT_ITEMS 8
-#define PT_TILE (PT_THREADS * PT_ITEMS) // 2048 records: the scatter stages a tile in shared memory (2 CTAs per SM)
+#define PT_TILE (PT_THREADS * PT_ITEMS) // 2048 records
 
 __global__ void __launch_bounds__(PT_THREADS) k_part_count(const uint32_t *__restrict__ xkeys, uint64_t n,
                                                            const uint32_t *__restrict__ cuts, uint32_t ncut, uint32_t nb,
@@ -502,30 +502,38 @@ __global__ void __launch_bounds__(256) k_scan_apply(uint32_t *__restrict__ v, ui
 }
 
 // stable scatter of a tile: rank of every record among the tile's records of its bin (warp multi-split over the bin
-// bits + per-warp counters, warps in order), the records are laid out in tile-sorted order in shared memory and leave
-// as runs per bin, so that a store instruction covers whole 32-byte sectors of consecutive records (direct 16-byte
-// stores from the ranking threads cost 3 sector transactions per record: 332 us for 10 M records).
+// bits + per-warp counters, warps in order), then the records go straight from the ranking threads to their place.
+// A record is one 32-byte sector but a thread stores 16 bytes at a time: lanes work in pairs so that ONE store
+// instruction carries both halves of a record and L2 receives whole sectors. Only the y keys (4-byte items, runs of
+// ~7 per bin and tile) are staged in shared memory in tile order and leave as runs.
+// Measured at C1 (10 M records, 559 bins, ncu): plain 16-byte stores + 4-byte y-key stores 332 us (29.5 M store sectors
+// for 12.7 M of payload); whole tile staged in shared memory and written out in runs 264 us (minimal sectors, but 100 KB
+// of shared memory = 2 CTAs / SM and 26 M shared-memory wavefronts); this form 179 us.
 #define PS_KBINS ((SP_MAXBINS + PT_THREADS - 1) / PT_THREADS) // bins per thread in the per-bin steps
-struct ps_smem {
-	float4 rec[2 * PT_TILE];                    // tile-sorted records, two 16-byte halves each
-	uint32_t yk[PT_TILE];                       // their y keys
-	uint32_t gl[SP_MAXBINS + 3];                // first global position of the bin's run - first tile position of the run
-	uint16_t wh[PT_THREADS / 32][SP_MAXBINS + 1]; // per-warp bin counts -> exclusive offsets of the warps inside a bin
-	uint16_t doff[SP_MAXBINS + 3];              // first tile position of the bin's run
-	uint16_t bin[PT_TILE];                      // bin of the record in tile position p
+struct pd_smem {
+	uint32_t yk[PT_TILE];
+	uint32_t gl[SP_MAXBINS + 3];
+	uint16_t wh[PT_THREADS / 32][SP_MAXBINS + 1];
+	uint16_t doff[SP_MAXBINS + 3];
+	uint16_t tot[PS_KBINS * PT_THREADS];
+	uint16_t bin[PT_TILE];
 	uint32_t scan[33];
 };
-__global__ void __launch_bounds__(PT_THREADS) k_part_scatter(const uint16_t *__restrict__ bins, uint64_t n, uint32_t nb,
-                                                             int nbits, const uint32_t *__restrict__ tile_pos,
-                                                             const float4 *__restrict__ box, const int64_t *__restrict__ rows,
-                                                             const uint32_t *__restrict__ ykeys, sb_rec32 *__restrict__ rec_out,
-                                                             uint32_t *__restrict__ ykey_out) {
-	extern __shared__ __align__(16) unsigned char ps_raw[];
-	ps_smem &S = *reinterpret_cast<ps_smem *>(ps_raw);
+__device__ __forceinline__ void pd_store16(void *p, float x, float y, float z, float w) {
+	asm volatile("st.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
+}
+__global__ void __launch_bounds__(PT_THREADS, 4) k_part_scatter(const uint16_t *__restrict__ bins, uint64_t n, uint32_t nb,
+                                                                       int nbits, const uint32_t *__restrict__ tile_pos,
+                                                                       const float4 *__restrict__ box,
+                                                                       const int64_t *__restrict__ rows,
+                                                                       const uint32_t *__restrict__ ykeys,
+                                                                       sb_rec32 *__restrict__ rec_out,
+                                                                       uint32_t *__restrict__ ykey_out) {
+	__shared__ pd_smem S;
 	{
-		uint32_t *z = reinterpret_cast<uint32_t *>(&S.wh[0][0]);
-		for (uint32_t i = threadIdx.x; i < sizeof(S.wh) / 4; i += PT_THREADS) {
-			z[i] = 0;
+		const uint32_t words = (nb + 2) / 2;
+		for (uint32_t i = threadIdx.x; i < (PT_THREADS / 32) * words; i += PT_THREADS) {
+			reinterpret_cast<uint32_t *>(S.wh[i / words])[i % words] = 0;
 		}
 	}
 	__syncthreads();
@@ -534,13 +542,23 @@ __global__ void __launch_bounds__(PT_THREADS) k_part_scatter(const uint16_t *__r
 	const uint64_t tile_base = (uint64_t)blockIdx.x * PT_TILE;
 	const uint32_t tile_count = (uint32_t)min((uint64_t)PT_TILE, n - tile_base);
 	const uint64_t first = tile_base + (uint64_t)warp * (32 * PT_ITEMS) + lane;
-	uint32_t br[PT_ITEMS]; // bin | rank in the warp << 16
+	uint32_t br[PT_ITEMS];
 	uint16_t *my = S.wh[warp];
+	uint32_t r_pos[PS_KBINS];
 #pragma unroll
 	for (int i = 0; i < PT_ITEMS; i++) {
 		const uint64_t gi = first + (uint64_t)i * 32;
-		const bool valid = gi < n;
-		const uint32_t b = valid ? bins[gi] : 0u;
+		br[i] = gi < n ? bins[gi] : 0u;
+	}
+#pragma unroll
+	for (int k = 0; k < PS_KBINS; k++) {
+		const uint32_t b = threadIdx.x * PS_KBINS + k;
+		r_pos[k] = b < nb ? tile_pos[(size_t)b * gridDim.x + blockIdx.x] : 0u;
+	}
+#pragma unroll
+	for (int i = 0; i < PT_ITEMS; i++) {
+		const bool valid = first + (uint64_t)i * 32 < n;
+		const uint32_t b = br[i];
 		unsigned peers = __ballot_sync(0xFFFFFFFFu, valid);
 #pragma unroll
 		for (int k = 0; k < 11; k++) {
@@ -561,23 +579,25 @@ __global__ void __launch_bounds__(PT_THREADS) k_part_scatter(const uint16_t *__r
 		__syncwarp();
 	}
 	__syncthreads();
-	// thread t owns bins [t * K, (t + 1) * K): offsets of the warps inside each bin, run starts by a block scan
+	for (uint32_t b = threadIdx.x; b < PS_KBINS * PT_THREADS; b += PT_THREADS) {
+		uint32_t run = 0;
+		if (b < nb) {
+#pragma unroll
+			for (int w = 0; w < PT_THREADS / 32; w++) {
+				const uint32_t c = S.wh[w][b];
+				S.wh[w][b] = (uint16_t)run;
+				run += c;
+			}
+		}
+		S.tot[b] = (uint16_t)run;
+	}
+	__syncthreads();
 	{
 		uint32_t tot[PS_KBINS], sum = 0;
 #pragma unroll
 		for (int k = 0; k < PS_KBINS; k++) {
-			const uint32_t b = threadIdx.x * PS_KBINS + k;
-			uint32_t run = 0;
-			if (b < nb) {
-#pragma unroll
-				for (int w = 0; w < PT_THREADS / 32; w++) {
-					const uint32_t c = S.wh[w][b];
-					S.wh[w][b] = (uint16_t)run;
-					run += c;
-				}
-			}
-			tot[k] = run;
-			sum += run;
+			tot[k] = S.tot[threadIdx.x * PS_KBINS + k];
+			sum += tot[k];
 		}
 		uint32_t all;
 		uint32_t run = sp_block_scan<PT_THREADS>(sum, S.scan, &all);
@@ -586,37 +606,49 @@ __global__ void __launch_bounds__(PT_THREADS) k_part_scatter(const uint16_t *__r
 			const uint32_t b = threadIdx.x * PS_KBINS + k;
 			if (b < nb) {
 				S.doff[b] = (uint16_t)run;
-				S.gl[b] = tile_pos[(size_t)b * gridDim.x + blockIdx.x] - run;
+				S.gl[b] = r_pos[k] - run;
 			}
 			run += tot[k];
 		}
 	}
 	__syncthreads();
-	// records into tile-sorted order
+	const bool odd = lane & 1u;
+	char *out = reinterpret_cast<char *>(rec_out);
 #pragma unroll 4
 	for (int i = 0; i < PT_ITEMS; i++) {
 		const uint64_t gi = first + (uint64_t)i * 32;
+		uint32_t g = 0xFFFFFFFFu;
+		float4 lo = make_float4(0.f, 0.f, 0.f, 0.f), hi = lo;
 		if (gi < n) {
 			const uint32_t b = br[i] & 0xFFFFu;
 			const uint32_t p = (uint32_t)S.doff[b] + my[b] + (br[i] >> 16);
-			const float4 bx = box[gi];
+			g = S.gl[b] + p;
+			lo = box[gi];
 			const int64_t r = rows[gi];
 			const uint32_t yk = ykeys[gi];
-			S.rec[2 * p] = bx;
-			S.rec[2 * p + 1] = make_float4(__int_as_float((int)(uint32_t)(uint64_t)r),
-			                               __int_as_float((int)(uint32_t)((uint64_t)r >> 32)), __uint_as_float(yk), 0.0f);
+			hi = make_float4(__int_as_float((int)(uint32_t)(uint64_t)r), __int_as_float((int)(uint32_t)((uint64_t)r >> 32)),
+			                 __uint_as_float(yk), 0.0f);
 			S.yk[p] = yk;
 			S.bin[p] = (uint16_t)b;
 		}
+		// the partner gets the half of MY record it stores (even lane: my upper half, odd lane: my lower half) + its position
+		const float gx = __shfl_xor_sync(0xFFFFFFFFu, odd ? lo.x : hi.x, 1);
+		const float gy = __shfl_xor_sync(0xFFFFFFFFu, odd ? lo.y : hi.y, 1);
+		const float gz = __shfl_xor_sync(0xFFFFFFFFu, odd ? lo.z : hi.z, 1);
+		const float gw = __shfl_xor_sync(0xFFFFFFFFu, odd ? lo.w : hi.w, 1);
+		const uint32_t pg = __shfl_xor_sync(0xFFFFFFFFu, g, 1);
+		// round 1: the even lane's record (even lane: own lower half, odd lane: the even lane's upper half)
+		const uint32_t t1 = odd ? pg : g;
+		if (t1 != 0xFFFFFFFFu) {
+			pd_store16(out + (size_t)t1 * 32 + (odd ? 16 : 0), odd ? gx : lo.x, odd ? gy : lo.y, odd ? gz : lo.z, odd ? gw : lo.w);
+		}
+		// round 2: the odd lane's record (even lane: the odd lane's lower half, odd lane: own upper half)
+		const uint32_t t2 = odd ? g : pg;
+		if (t2 != 0xFFFFFFFFu) {
+			pd_store16(out + (size_t)t2 * 32 + (odd ? 16 : 0), odd ? hi.x : gx, odd ? hi.y : gy, odd ? hi.z : gz, odd ? hi.w : gw);
+		}
 	}
 	__syncthreads();
-	// out: consecutive threads store consecutive 16-byte halves / y keys of the tile order (runs per bin in global memory)
-	float4 *out4 = reinterpret_cast<float4 *>(rec_out);
-	for (uint32_t c = threadIdx.x; c < 2 * tile_count; c += PT_THREADS) {
-		const uint32_t p = c >> 1;
-		const uint32_t g = S.gl[S.bin[p]] + p;
-		out4[2 * (size_t)g + (c & 1u)] = S.rec[c];
-	}
 	for (uint32_t p = threadIdx.x; p < tile_count; p += PT_THREADS) {
 		ykey_out[S.gl[S.bin[p]] + p] = S.yk[p];
 	}
@@ -648,9 +680,7 @@ int sbi_str_partition_rec(sb_context *ctx, const float4 *box, const int64_t *row
 	SB_LAUNCH_CHECK(ctx);
 	k_scan_apply<<<nblk, 256, 0, ctx->stream>>>(tile_hist, cells, sums);
 	SB_LAUNCH_CHECK(ctx);
-	SB_SMEM_OPTIN(ctx, k_part_scatter, sizeof(ps_smem));
-	k_part_scatter<<<tiles, PT_THREADS, sizeof(ps_smem), ctx->stream>>>(bins, n, nb, nbits, tile_hist, box, rows, ykeys, rec_out,
-	                                                                   ykey_out);
+	k_part_scatter<<<tiles, PT_THREADS, 0, ctx->stream>>>(bins, n, nb, nbits, tile_hist, box, rows, ykeys, rec_out, ykey_out);
 	SB_LAUNCH_CHECK(ctx);
 	return SB_OK;
 }
