@@ -75,17 +75,11 @@ __global__ void __launch_bounds__(256) k_str_ykeys_upper(const sb_entry *__restr
 	}
 }
 
-// One CTA per node. LEAF: gather (row id, box) through the permutation and order the node's entries by row id
-// (RTreeNode::SortEntriesByRowId, rtree_node.hpp:151-155). UPPER: gather already-built entries in sorted order.
-// Writes the node's entries (24 B each, staged in shared memory, stored as coalesced 8-byte words) and one
-// parent entry {(type<<56)|node index, union box}.
-template <bool LEAF>
+// Upper levels, one CTA per node: gather already-built entries in sorted order, write the node's entries (24 B each,
+// staged in shared memory, stored as coalesced 8-byte words) and one parent entry {(type<<56)|node index, union box}.
 __global__ void __launch_bounds__(256)
-    k_str_pack(const float4 *__restrict__ box, const int64_t *__restrict__ row_ids, const sb_entry *__restrict__ cur,
-               const uint32_t *__restrict__ perm, uint64_t count, uint32_t cap, sb_entry *__restrict__ level_out,
-               sb_entry *__restrict__ parent_out, uint64_t parent_type, uint64_t node_base,
-               const sb_rec32 *__restrict__ rec) {
-	__shared__ int64_t s_row[256];
+    k_str_pack_upper(const sb_entry *__restrict__ cur, const uint32_t *__restrict__ perm, uint64_t count, uint32_t cap,
+                     sb_entry *__restrict__ level_out, sb_entry *__restrict__ parent_out, uint64_t parent_type) {
 	__shared__ uint64_t s_words[256 * 3];
 	__shared__ float s_red[8][4];
 	const uint64_t node = blockIdx.x;
@@ -97,124 +91,10 @@ __global__ void __launch_bounds__(256)
 	e.box[0] = e.box[1] = FLT_MAX;
 	e.box[2] = e.box[3] = -FLT_MAX;
 	if (t < cnt) {
-		const uint32_t src = perm[beg + t];
-		if (LEAF) {
-			float4 b;
-			int64_t row;
-			if (rec) { // partitioned records: `src` is a position inside this node's slice (local gather)
-				const float4 *r = reinterpret_cast<const float4 *>(rec + src);
-				b = r[0];
-				const float4 hi = r[1];
-				row = (int64_t)(((uint64_t)__float_as_uint(hi.y) << 32) | __float_as_uint(hi.x));
-			} else {
-				b = box[src];
-				row = row_ids[src];
-			}
-			e.ptr = (uint64_t)row & 0x00FFFFFFFFFFFFFFull; // RTree::MakeRowId: type ROW_ID = 0
-			e.box[0] = b.x, e.box[1] = b.y, e.box[2] = b.z, e.box[3] = b.w;
-		} else {
-			e = cur[src];
-		}
-	}
-	uint32_t rank = t;
-	if (LEAF) {
-		// rank of the entry among the node's row ids. All-pairs counting (cap compares per entry) made the pack
-		// instruction bound (205 M warp instructions at C1); the row ids are bucketed instead: 256 buckets by a monotone
-		// map of (row id - node minimum), bucket starts from a scan, and an entry only compares itself with the entries of
-		// its own bucket (about one). Nodes whose row ids spread over 2^32 or crowd into one bucket (> 8) take the 64-bit
-		// all-pairs count with the position tie-break (equal row ids are not expected: row ids are unique).
-		__shared__ uint32_t s_cnt[257];
-		__shared__ uint32_t s_key[256];
-		__shared__ uint8_t s_src[256];
-		__shared__ unsigned long long s_mm[2][8];
-		const int64_t mine = (int64_t)(e.ptr << 8) >> 8; // sign-extended 56-bit row id
-		const unsigned long long u = (unsigned long long)mine ^ 0x8000000000000000ull; // unsigned order = signed order
-		unsigned long long mn = t < cnt ? u : ~0ull, mx = t < cnt ? u : 0ull;
-#pragma unroll
-		for (int s = 16; s > 0; s >>= 1) {
-			const unsigned long long a = __shfl_xor_sync(0xFFFFFFFFu, mn, s), b = __shfl_xor_sync(0xFFFFFFFFu, mx, s);
-			mn = a < mn ? a : mn;
-			mx = b > mx ? b : mx;
-		}
-		if (sb_lane() == 0) {
-			s_mm[0][t >> 5] = mn;
-			s_mm[1][t >> 5] = mx;
-		}
-		for (uint32_t i = t; i < 257; i += blockDim.x) {
-			s_cnt[i] = 0;
-		}
-		if (t < cnt) {
-			s_row[t] = mine;
-		}
-		__syncthreads();
-		for (unsigned w = 0; w < (blockDim.x >> 5); w++) {
-			const unsigned long long a = s_mm[0][w], b = s_mm[1][w];
-			mn = a < mn ? a : mn;
-			mx = b > mx ? b : mx;
-		}
-		const unsigned long long range = mx - mn;
-		const bool fast = range < 0xFFFFFFFFull;
-		uint32_t k32 = 0, bkt = 0, slot = 0;
-		if (fast && t < cnt) {
-			k32 = (uint32_t)(u - mn);
-			// conversion, product with a positive constant and truncation are monotone: so is the bucket
-			bkt = min(255u, __float2uint_rz(__uint2float_rz(k32) * (256.0f / (__ull2float_rz(range) + 1.0f))));
-			slot = atomicAdd(&s_cnt[bkt], 1u);
-		}
-		const bool crowded = __syncthreads_or(slot >= 8);
-		if (fast && !crowded) {
-			if (t < 32) { // exclusive scan of the 256 counts: 8 per lane
-				uint32_t c[8], sum = 0;
-#pragma unroll
-				for (int j = 0; j < 8; j++) {
-					c[j] = s_cnt[t * 8 + j];
-					sum += c[j];
-				}
-				uint32_t inc = sum;
-#pragma unroll
-				for (int s = 1; s < 32; s <<= 1) {
-					const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, s);
-					if (t >= (unsigned)s) {
-						inc += o;
-					}
-				}
-				uint32_t run = inc - sum;
-#pragma unroll
-				for (int j = 0; j < 8; j++) {
-					s_cnt[t * 8 + j] = run;
-					run += c[j];
-				}
-				if (t == 31) {
-					s_cnt[256] = run;
-				}
-			}
-			__syncthreads();
-			if (t < cnt) {
-				const uint32_t pos = s_cnt[bkt] + slot;
-				s_key[pos] = k32;
-				s_src[pos] = (uint8_t)t;
-			}
-			__syncthreads();
-			if (t < cnt) {
-				const uint32_t beg = s_cnt[bkt], end = s_cnt[bkt + 1];
-				rank = beg;
-				for (uint32_t j = beg; j < end; j++) {
-					const uint32_t kk = s_key[j];
-					rank += (kk < k32) || (kk == k32 && s_src[j] < t);
-				}
-			}
-		} else if (t < cnt) {
-			rank = 0;
-			for (uint32_t k = 0; k < cnt; k++) {
-				const int64_t o = s_row[k];
-				rank += (o < mine) || (o == mine && k < t);
-			}
-		}
-	}
-	if (t < cnt) {
-		s_words[3 * rank + 0] = e.ptr;
-		s_words[3 * rank + 1] = ((uint64_t)__float_as_uint(e.box[1]) << 32) | __float_as_uint(e.box[0]);
-		s_words[3 * rank + 2] = ((uint64_t)__float_as_uint(e.box[3]) << 32) | __float_as_uint(e.box[2]);
+		e = cur[perm[beg + t]];
+		s_words[3 * t + 0] = e.ptr;
+		s_words[3 * t + 1] = ((uint64_t)__float_as_uint(e.box[1]) << 32) | __float_as_uint(e.box[0]);
+		s_words[3 * t + 2] = ((uint64_t)__float_as_uint(e.box[3]) << 32) | __float_as_uint(e.box[2]);
 	}
 	// union of the node's boxes (RTreeNode::GetBounds, rtree_node.hpp:92-99): fp32 min/max
 	float u0 = e.box[0], u1 = e.box[1], u2 = e.box[2], u3 = e.box[3];
@@ -242,7 +122,203 @@ __global__ void __launch_bounds__(256)
 			u3 = fmaxf(u3, s_red[w][3]);
 		}
 		sb_entry p;
-		p.ptr = (parent_type << 56) | (node_base + node);
+		p.ptr = (parent_type << 56) | node;
+		p.box[0] = u0, p.box[1] = u1, p.box[2] = u2, p.box[3] = u3;
+		parent_out[node] = p;
+	}
+}
+
+// Leaf pack, one WARP per node (lane l holds entries l, l + 32, ... of the node): the CTA-per-node form above spends
+// ~570 warp instructions per 32 entries on block-wide reductions, barriers and address arithmetic that do not grow
+// with the entries a lane holds (178 M warp instructions at C1 = instruction bound at 234 us for 572 MB of traffic).
+// Same result: entries gathered through `perm` (from the partitioned records `rec` when given, else from the input
+// columns), ordered by row id (RTreeNode::SortEntriesByRowId, rtree_node.hpp:151-155) with the bucketed rank described
+// above, stored as coalesced 8-byte words; one parent entry {(LEAF_PAGE << 56) | node, union box} per node.
+#define PKW_WARPS 4
+#define PKW_CNT(b) ((b) + ((b) >> 3))
+template <int PER>
+__global__ void __launch_bounds__(PKW_WARPS * 32)
+    k_str_pack_leaf(const float4 *__restrict__ box, const int64_t *__restrict__ row_ids, const sb_rec32 *__restrict__ rec,
+                    const uint32_t *__restrict__ perm, uint64_t count, uint32_t cap, uint64_t nodes,
+                    sb_entry *__restrict__ level_out, sb_entry *__restrict__ parent_out, uint64_t node_base) {
+	__shared__ uint64_t s_words_all[PKW_WARPS][PER * 32 * 3];
+	__shared__ uint32_t s_cnt_all[PKW_WARPS][PKW_CNT(256) + 1]; // padded: lane * 8 + q falls in 32 different banks
+	__shared__ uint32_t s_key_all[PKW_WARPS][PER * 32];
+	__shared__ uint8_t s_src_all[PKW_WARPS][PER * 32];
+	const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+	const uint64_t node = (uint64_t)blockIdx.x * PKW_WARPS + warp;
+	if (node >= nodes) {
+		return; // warps are independent: no block barrier below
+	}
+	uint64_t *s_words = s_words_all[warp];
+	int64_t *s_row = reinterpret_cast<int64_t *>(s_words); // only read before the words are written (slow rank path)
+	uint32_t *s_cnt = s_cnt_all[warp], *s_key = s_key_all[warp];
+	uint8_t *s_src = s_src_all[warp];
+	const uint64_t beg = node * cap;
+	const uint32_t cnt = (uint32_t)min((uint64_t)cap, count - beg);
+	float4 bx[PER];
+	int64_t row[PER];
+#pragma unroll
+	for (int j = 0; j < PER; j++) {
+		const uint32_t i = j * 32 + lane;
+		bx[j] = make_float4(FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX);
+		row[j] = 0;
+		if (i < cnt) {
+			const uint32_t src = perm[beg + i];
+			if (rec) { // partitioned records: `src` is a position inside this node's slice (local gather)
+				const float4 *r = reinterpret_cast<const float4 *>(rec + src);
+				bx[j] = r[0];
+				const float4 hi = r[1];
+				row[j] = (int64_t)(((uint64_t)__float_as_uint(hi.y) << 32) | __float_as_uint(hi.x));
+			} else {
+				bx[j] = box[src];
+				row[j] = row_ids[src];
+			}
+			row[j] = (int64_t)((uint64_t)row[j] << 8) >> 8; // RTree::MakeRowId keeps 56 bits (type ROW_ID = 0)
+		}
+	}
+	// node minimum / maximum of the row ids
+	unsigned long long mn = ~0ull, mx = 0ull;
+#pragma unroll
+	for (int j = 0; j < PER; j++) {
+		if (j * 32 + lane < cnt) {
+			const unsigned long long u = (unsigned long long)row[j] ^ 0x8000000000000000ull;
+			mn = u < mn ? u : mn;
+			mx = u > mx ? u : mx;
+		}
+	}
+#pragma unroll
+	for (int s = 16; s > 0; s >>= 1) {
+		const unsigned long long a = __shfl_xor_sync(0xFFFFFFFFu, mn, s), b = __shfl_xor_sync(0xFFFFFFFFu, mx, s);
+		mn = a < mn ? a : mn;
+		mx = b > mx ? b : mx;
+	}
+	for (uint32_t i = lane; i < PKW_CNT(256) + 1; i += 32) {
+		s_cnt[i] = 0;
+	}
+	__syncwarp();
+	const unsigned long long range = mx - mn;
+	const bool fast = range < 0xFFFFFFFFull;
+	uint32_t k32[PER], bs[PER]; // bs = bucket | slot << 8
+	bool crowded = false;
+	if (fast) {
+		const float scale = __fdividef(256.0f, __ull2float_rz(range) + 1.0f); // any positive factor keeps the map monotone
+#pragma unroll
+		for (int j = 0; j < PER; j++) {
+			k32[j] = 0;
+			bs[j] = 0;
+			if (j * 32 + lane < cnt) {
+				k32[j] = (uint32_t)(((unsigned long long)row[j] ^ 0x8000000000000000ull) - mn);
+				const uint32_t b = min(255u, __float2uint_rz(__uint2float_rz(k32[j]) * scale));
+				const uint32_t slot = atomicAdd(&s_cnt[PKW_CNT(b)], 1u);
+				bs[j] = b | (slot << 8);
+				crowded |= slot >= 8;
+			}
+		}
+	}
+	crowded = __any_sync(0xFFFFFFFFu, crowded);
+	uint32_t rank[PER];
+	if (fast && !crowded) {
+		{ // exclusive scan of the 256 counts: 8 per lane
+			uint32_t c[8], sum = 0;
+#pragma unroll
+			for (int q = 0; q < 8; q++) {
+				c[q] = s_cnt[lane * 9 + q];
+				sum += c[q];
+			}
+			uint32_t inc = sum;
+#pragma unroll
+			for (int s = 1; s < 32; s <<= 1) {
+				const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, s);
+				if (lane >= (unsigned)s) {
+					inc += o;
+				}
+			}
+			uint32_t run = inc - sum;
+			__syncwarp();
+#pragma unroll
+			for (int q = 0; q < 8; q++) {
+				s_cnt[lane * 9 + q] = run;
+				run += c[q];
+			}
+			if (lane == 31) {
+				s_cnt[PKW_CNT(256)] = run;
+			}
+		}
+		__syncwarp();
+#pragma unroll
+		for (int j = 0; j < PER; j++) {
+			if (j * 32 + lane < cnt) {
+				const uint32_t pos = s_cnt[PKW_CNT(bs[j] & 255u)] + (bs[j] >> 8);
+				s_key[pos] = k32[j];
+				s_src[pos] = (uint8_t)(j * 32 + lane);
+			}
+		}
+		__syncwarp();
+#pragma unroll
+		for (int j = 0; j < PER; j++) {
+			rank[j] = 0;
+			if (j * 32 + lane < cnt) {
+				const uint32_t b = bs[j] & 255u, me = j * 32 + lane;
+				const uint32_t b0 = s_cnt[PKW_CNT(b)], b1 = s_cnt[PKW_CNT(b + 1)];
+				uint32_t r = b0;
+				for (uint32_t q = b0; q < b1; q++) {
+					const uint32_t kk = s_key[q];
+					r += (kk < k32[j]) || (kk == k32[j] && s_src[q] < me);
+				}
+				rank[j] = r;
+			}
+		}
+	} else {
+		// row ids spread over 2^32 or crowded into a bucket: 64-bit all-pairs count, equal row ids by position
+#pragma unroll
+		for (int j = 0; j < PER; j++) {
+			if (j * 32 + lane < cnt) {
+				s_row[j * 32 + lane] = row[j];
+			}
+		}
+		__syncwarp();
+#pragma unroll
+		for (int j = 0; j < PER; j++) {
+			rank[j] = 0;
+			if (j * 32 + lane < cnt) {
+				const uint32_t me = j * 32 + lane;
+				uint32_t r = 0;
+				for (uint32_t q = 0; q < cnt; q++) {
+					const int64_t o = s_row[q];
+					r += (o < row[j]) || (o == row[j] && q < me);
+				}
+				rank[j] = r;
+			}
+		}
+	}
+	__syncwarp();
+	float u0 = FLT_MAX, u1 = FLT_MAX, u2 = -FLT_MAX, u3 = -FLT_MAX;
+#pragma unroll
+	for (int j = 0; j < PER; j++) {
+		if (j * 32 + lane < cnt) {
+			s_words[3 * rank[j] + 0] = (uint64_t)row[j] & 0x00FFFFFFFFFFFFFFull;
+			s_words[3 * rank[j] + 1] = ((uint64_t)__float_as_uint(bx[j].y) << 32) | __float_as_uint(bx[j].x);
+			s_words[3 * rank[j] + 2] = ((uint64_t)__float_as_uint(bx[j].w) << 32) | __float_as_uint(bx[j].z);
+		}
+		// union of the node's boxes (RTreeNode::GetBounds, rtree_node.hpp:92-99): fp32 min/max; absent entries are neutral
+		u0 = fminf(u0, bx[j].x), u1 = fminf(u1, bx[j].y), u2 = fmaxf(u2, bx[j].z), u3 = fmaxf(u3, bx[j].w);
+	}
+#pragma unroll
+	for (int s = 16; s > 0; s >>= 1) {
+		u0 = fminf(u0, __shfl_xor_sync(0xFFFFFFFFu, u0, s));
+		u1 = fminf(u1, __shfl_xor_sync(0xFFFFFFFFu, u1, s));
+		u2 = fmaxf(u2, __shfl_xor_sync(0xFFFFFFFFu, u2, s));
+		u3 = fmaxf(u3, __shfl_xor_sync(0xFFFFFFFFu, u3, s));
+	}
+	__syncwarp();
+	uint64_t *out_words = reinterpret_cast<uint64_t *>(level_out + beg);
+	for (uint32_t w = lane; w < cnt * 3; w += 32) {
+		out_words[w] = s_words[w];
+	}
+	if (lane == 0) {
+		sb_entry p;
+		p.ptr = (1ull << 56) | (node_base + node);
 		p.box[0] = u0, p.box[1] = u1, p.box[2] = u2, p.box[3] = u3;
 		parent_out[node] = p;
 	}
@@ -333,7 +409,6 @@ static void str_shape(sb_rtree *t, uint64_t n, uint32_t cap) {
 static int str_leaf_level(sb_context *ctx, const float4 *box, const int64_t *row_ids, uint64_t n, uint32_t cap,
                           uint64_t slice, uint64_t node_base, int64_t x_key_before, int64_t x_key_after, sb_entry *level0,
                           sb_entry *parents, uint32_t **yk_out, uint32_t **ykb_out, uint32_t **yv_out, uint32_t **yvb_out) {
-	const unsigned block = ((cap + 31) / 32) * 32;
 	uint32_t *xk = nullptr, *yk_in = nullptr;
 	uint32_t *yk = nullptr, *ykb = nullptr, *yv = nullptr, *yvb = nullptr;
 	SB_TRY(ctx->scratch_t(n, &xk));
@@ -390,8 +465,14 @@ static int str_leaf_level(sb_context *ctx, const float4 *box, const int64_t *row
 	const uint64_t nodes = (n + cap - 1) / cap;
 	{
 		sb_prof_scope ps(ctx, "str_pack");
-		k_str_pack<true><<<(unsigned)nodes, block, 0, ctx->stream>>>(box, row_ids, nullptr, perm, n, cap, level0, parents,
-		                                                            1ull, node_base, rec);
+		const unsigned grid = (unsigned)((nodes + PKW_WARPS - 1) / PKW_WARPS);
+		if (cap <= 128) {
+			k_str_pack_leaf<4><<<grid, PKW_WARPS * 32, 0, ctx->stream>>>(box, row_ids, rec, perm, n, cap, nodes, level0, parents,
+			                                                            node_base);
+		} else {
+			k_str_pack_leaf<8><<<grid, PKW_WARPS * 32, 0, ctx->stream>>>(box, row_ids, rec, perm, n, cap, nodes, level0, parents,
+			                                                            node_base);
+		}
 		SB_LAUNCH_CHECK(ctx);
 	}
 	*yk_out = yk, *ykb_out = ykb, *yv_out = yv, *yvb_out = yvb;
@@ -433,9 +514,8 @@ static int str_upper_levels(sb_context *ctx, sb_rtree *t, sb_entry *parents, sb_
 		const uint64_t nn = (c + cap - 1) / cap;
 		{
 			sb_prof_scope ps(ctx, "str_pack");
-			k_str_pack<false><<<(unsigned)nn, block, 0, ctx->stream>>>(nullptr, nullptr, parents, p, c, cap,
-			                                                          t->entries + t->offsets[level], parents_b, 2ull, 0ull,
-			                                                          nullptr);
+			k_str_pack_upper<<<(unsigned)nn, block, 0, ctx->stream>>>(parents, p, c, cap, t->entries + t->offsets[level],
+			                                                         parents_b, 2ull);
 			SB_LAUNCH_CHECK(ctx);
 		}
 		sb_entry *tmp = parents;

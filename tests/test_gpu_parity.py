@@ -221,6 +221,43 @@ def test_str_build_wide_row_ids(ctx, sb, O, n, cap, spread):
     _tree_equal(sb.RTreeIndex(ctx, box, rows, cap), O.StrTree(box, rows, cap))
 
 
+@pytest.mark.parametrize("case", ["same_x", "same_xy", "two_x", "grid", "sorted", "reverse", "clustered_rows", "wide_keys"])
+@pytest.mark.parametrize("path", [0, 1])
+def test_str_build_degenerate_inputs(ctx, sb, O, case, path):
+    # the x order is a radix select of the slice-boundary keys + a stable partition (str_partition.cu): inputs whose x keys
+    # repeat across slice boundaries, whose keys sit in one histogram bucket / in all of them, presorted inputs; both
+    # forms of the leaf level (str_path 0: one-pass record partition, 1: bin-id sort + gather)
+    rng = np.random.default_rng(11)
+    n, cap = 70_001, 16
+    x, y = O.generate_points(5, n, (0, 0, 1000, 1000))
+    rows = rng.permutation(n).astype(np.int64) + 1
+    if case == "same_x":
+        x[:] = 123.25
+    elif case == "same_xy":
+        x[:] = 7.0
+        y[:] = -3.0
+    elif case == "two_x":
+        x = np.where(rng.random(n) < 0.37, 10.0, 20.0)
+    elif case == "grid":
+        x, y = np.floor(x / 50) * 50, np.floor(y / 25) * 25
+    elif case == "sorted":
+        x = np.sort(x)
+    elif case == "reverse":
+        x = np.sort(x)[::-1].copy()
+    elif case == "clustered_rows":
+        rows = np.arange(n, dtype=np.int64)
+        rows[::97] += 1 << 30  # one far row id in many nodes: the bucketed rank crowds and falls back
+    elif case == "wide_keys":
+        x = np.ldexp(rng.uniform(1, 2, n), rng.integers(-120, 120, n)) * np.where(rng.random(n) < 0.5, -1.0, 1.0)
+    box = O.bbox_from_box2d(x, y, x, y)
+    ctx.set_option("str_path", path)
+    try:
+        idx = sb.RTreeIndex(ctx, box, rows, cap)
+    finally:
+        ctx.set_option("str_path", 0)
+    _tree_equal(idx, O.StrTree(box, rows, cap))
+
+
 def test_str_empty(ctx, sb):
     idx = sb.RTreeIndex(ctx, np.zeros((0, 4), np.float32), np.zeros(0, np.int64))
     assert idx.nlevels == 0
