@@ -977,6 +977,20 @@ __global__ void __launch_bounds__(1024, 1)
 			S.lim[BP_NB] = region_end[BP_NB];
 		}
 	}
+	// One 1024-thread CTA per SM (shared memory): nothing else hides the latency of a tile's coordinate loads, so the
+	// next tile's loads are issued as soon as the registers are free (after the ranking atomics) and complete behind
+	// the scan / reorder / write-out of the current tile. XY keeps the coordinates until the reorder: no prefetch.
+	double x[ITEMS], y[ITEMS];
+	if (!XY && blockIdx.x < tiles) {
+#pragma unroll
+		for (int k = 0; k < ITEMS; k++) {
+			const uint64_t i = (uint64_t)blockIdx.x * CP_TILE1 + tid + (uint64_t)k * 1024;
+			if (i < n) {
+				x[k] = px[i];
+				y[k] = py[i];
+			}
+		}
+	}
 	for (uint64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
 		S.cnt[tid] = 0;
 		if (tid == 0) {
@@ -984,13 +998,14 @@ __global__ void __launch_bounds__(1024, 1)
 		}
 		__syncthreads();
 		const uint64_t base = tile * CP_TILE1 + tid;
-		double x[ITEMS], y[ITEMS];
+		if (XY) {
 #pragma unroll
-		for (int k = 0; k < ITEMS; k++) {
-			const uint64_t i = base + (uint64_t)k * 1024;
-			if (i < n) {
-				x[k] = px[i];
-				y[k] = py[i];
+			for (int k = 0; k < ITEMS; k++) {
+				const uint64_t i = base + (uint64_t)k * 1024;
+				if (i < n) {
+					x[k] = px[i];
+					y[k] = py[i];
+				}
 			}
 		}
 		uint32_t pq[ITEMS], br[ITEMS];
@@ -1005,6 +1020,17 @@ __global__ void __launch_bounds__(1024, 1)
 					const int qx = bp_q(x[k], g.minx, g.sx), qy = bp_q(y[k], g.miny, g.sy);
 					pq[k] = ((uint32_t)(qy & 32767) << 16) | (uint32_t)(qx & 32767);
 					br[k] = ((uint32_t)b << 16) | atomicAdd(&S.cnt[b], 1u);
+				}
+			}
+		}
+		if (!XY && tile + gridDim.x < tiles) {
+			const uint64_t nbase = (tile + gridDim.x) * CP_TILE1 + tid;
+#pragma unroll
+			for (int k = 0; k < ITEMS; k++) {
+				const uint64_t i = nbase + (uint64_t)k * 1024;
+				if (i < n) {
+					x[k] = px[i];
+					y[k] = py[i];
 				}
 			}
 		}
