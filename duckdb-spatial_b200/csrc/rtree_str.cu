@@ -363,19 +363,32 @@ __global__ void __launch_bounds__(1024)
 			__syncthreads();
 		}
 	}
+	// entries out in sorted order (all threads), then one warp per node takes the union box (fp32 min / max are order-free)
+	for (uint32_t j = t; j < count; j += blockDim.x) {
+		level_out[j] = cur[s_key[j] & 2047u];
+	}
+	__syncthreads();
 	const uint32_t nodes = (count + cap - 1) / cap;
-	for (uint32_t node = t; node < nodes; node += blockDim.x) {
+	for (uint32_t node = t >> 5; node < nodes; node += blockDim.x >> 5) {
 		const uint32_t beg = node * cap, end = min(beg + cap, count);
 		float u0 = FLT_MAX, u1 = FLT_MAX, u2 = -FLT_MAX, u3 = -FLT_MAX;
-		for (uint32_t j = beg; j < end; j++) {
-			const sb_entry e = cur[s_key[j] & 2047u];
-			level_out[j] = e;
+		for (uint32_t j = beg + sb_lane(); j < end; j += 32) {
+			const sb_entry e = level_out[j];
 			u0 = fminf(u0, e.box[0]), u1 = fminf(u1, e.box[1]), u2 = fmaxf(u2, e.box[2]), u3 = fmaxf(u3, e.box[3]);
 		}
-		sb_entry p;
-		p.ptr = (parent_type << 56) | node;
-		p.box[0] = u0, p.box[1] = u1, p.box[2] = u2, p.box[3] = u3;
-		parent_out[node] = p;
+#pragma unroll
+		for (int s = 16; s > 0; s >>= 1) {
+			u0 = fminf(u0, __shfl_xor_sync(0xFFFFFFFFu, u0, s));
+			u1 = fminf(u1, __shfl_xor_sync(0xFFFFFFFFu, u1, s));
+			u2 = fmaxf(u2, __shfl_xor_sync(0xFFFFFFFFu, u2, s));
+			u3 = fmaxf(u3, __shfl_xor_sync(0xFFFFFFFFu, u3, s));
+		}
+		if (sb_lane() == 0) {
+			sb_entry p;
+			p.ptr = (parent_type << 56) | node;
+			p.box[0] = u0, p.box[1] = u1, p.box[2] = u2, p.box[3] = u3;
+			parent_out[node] = p;
+		}
 	}
 }
 

@@ -50,5 +50,8 @@ idx = build()
 levels = sorted((int(c) for c in idx.level_counts()), reverse=True)
 q = ctx.bbox_from_box2d(*[torch.tensor([v], dtype=torch.float64, device=dev) for v in (450.0, 450.0, 650.0, 650.0)])
 _, got = idx.scan(q)
+brute = int(((ix >= 450) & (ix <= 650) & (iy >= 450) & (iy <= 650)).sum().item())
+inside = int(((ix[got.long()] >= 450) & (ix[got.long()] <= 650) & (iy[got.long()] >= 450) & (iy[got.long()] <= 650)).sum().item())
+assert inside == brute, (inside, brute)  # the scan returns float-box candidates: every true hit must be among them
 print({"lib": os.environ.get("SPATIAL_B200_LIB", "default"), "n": n, "ms": round(ms, 4), "scopes": scopes, "levels": levels,
-       "scan": int(len(got))}, flush=True)
+       "scan": int(len(got)), "brute_force_hits": brute}, flush=True)
