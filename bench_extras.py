@@ -67,7 +67,7 @@ def _scan_parity(torch, qb, fbox, oq, orow, nsample=64):
 
 def run_c1_scans(ctx, sb, torch, dev, stream, idx, fbox, reps=3):
     qb = _range_queries(ctx)
-    cap = 1 << 26
+    cap = 1 << 24  # result slots of the caller (9.7 M rows come back): sized like a caller that knows its selectivity
     ms, (oq, orow) = timed(stream, lambda: idx.scan(qb, capacity=cap), reps)
     rows = int(len(orow))
     ok = _scan_parity(torch, qb, fbox, oq, orow)
@@ -157,7 +157,7 @@ def run_c2(ctx, sb, torch, dev, stream, hbm, n_poly=5_000_000, n_box=5_000_000, 
     bms, _ = timed(stream, build, reps)
     idx = sb.RTreeIndex.from_blobs(ctx, data, off, None, 128)
     qb = _range_queries(ctx)
-    sms, (oq, orow) = timed(stream, lambda: idx.scan(qb, capacity=1 << 27), reps)
+    sms, (oq, orow) = timed(stream, lambda: idx.scan(qb, capacity=1 << 25), reps)
     ok_s = _scan_parity(torch, qb, fb, oq, orow, 32) and idx.indexed_rows == n
     levels = [int(c) for c in idx.level_counts()]
     idx.close()

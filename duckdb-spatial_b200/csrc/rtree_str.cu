@@ -633,8 +633,11 @@ __device__ __forceinline__ void load_entry(const sb_entry *e, uint64_t &ptr, flo
 __global__ void __launch_bounds__(SCAN_WARPS * 32)
     k_rtree_scan(scan_levels L, const float4 *__restrict__ queries, uint32_t nq, uint64_t *__restrict__ counts,
                  const uint64_t *__restrict__ offsets, uint32_t *__restrict__ out_query,
-                 int64_t *__restrict__ out_row) {
+                 int64_t *__restrict__ out_row, uint64_t capacity) {
 	__shared__ uint32_t s_stack[SCAN_WARPS][SCAN_STACK];
+	if (offsets && offsets[nq] > capacity) {
+		return; // fill pass: the results do not fit the caller's arrays (the host reports SB_ERR_CAPACITY from the same word)
+	}
 	const unsigned warp = threadIdx.x >> 5, lane = sb_lane();
 	const unsigned lt = sb_lanemask_lt();
 	uint32_t *stack = s_stack[warp];
@@ -716,6 +719,54 @@ __global__ void __launch_bounds__(SCAN_WARPS * 32)
 	}
 }
 
+// exclusive scan of the per-query result counts, in place is not needed: off[q] = first result slot of query q,
+// off[nq] = total. One CTA (nq is a batch of queries, not a column).
+__global__ void __launch_bounds__(1024) k_scan_offsets(const uint64_t *__restrict__ cnt, uint32_t nq, uint64_t *__restrict__ off) {
+	__shared__ unsigned long long s_w[33];
+	const unsigned lane = sb_lane(), warp = threadIdx.x >> 5;
+	unsigned long long carry = 0;
+	for (uint32_t q0 = 0; q0 < nq; q0 += 1024) {
+		const uint32_t q = q0 + threadIdx.x;
+		const unsigned long long v = q < nq ? cnt[q] : 0ull;
+		unsigned long long inc = v;
+#pragma unroll
+		for (int s = 1; s < 32; s <<= 1) {
+			const unsigned long long o = __shfl_up_sync(0xFFFFFFFFu, inc, s);
+			if (lane >= (unsigned)s) {
+				inc += o;
+			}
+		}
+		if (lane == 31) {
+			s_w[warp] = inc;
+		}
+		__syncthreads();
+		if (warp == 0) {
+			const unsigned long long w = s_w[lane];
+			unsigned long long wi = w;
+#pragma unroll
+			for (int s = 1; s < 32; s <<= 1) {
+				const unsigned long long o = __shfl_up_sync(0xFFFFFFFFu, wi, s);
+				if (lane >= (unsigned)s) {
+					wi += o;
+				}
+			}
+			s_w[lane] = wi - w;
+			if (lane == 31) {
+				s_w[32] = wi;
+			}
+		}
+		__syncthreads();
+		if (q < nq) {
+			off[q] = carry + s_w[warp] + inc - v;
+		}
+		carry += s_w[32];
+		__syncthreads();
+	}
+	if (threadIdx.x == 0) {
+		off[nq] = carry;
+	}
+}
+
 int sbi_rtree_scan(sb_context *ctx, const sb_rtree *tree, const float *qbox4, uint32_t nq, uint32_t *out_query,
                    int64_t *out_row, uint64_t capacity, uint64_t *count) {
 	*count = 0;
@@ -732,39 +783,29 @@ int sbi_rtree_scan(sb_context *ctx, const sb_rtree *tree, const float *qbox4, ui
 	}
 	uint64_t *d_counts = nullptr, *d_offsets = nullptr;
 	SB_TRY(ctx->scratch_t(nq, &d_counts));
-	SB_TRY(ctx->scratch_t(nq, &d_offsets));
+	SB_TRY(ctx->scratch_t((size_t)nq + 1, &d_offsets));
 	const unsigned grid = sb_grid(nq, SCAN_WARPS, 8);
 	const float4 *q = reinterpret_cast<const float4 *>(qbox4);
+	// count, offsets and fill are enqueued back to back: the fill pass checks the capacity on the device, the host only
+	// reads the total when everything is in flight (one synchronisation per call instead of two + two pageable copies)
 	{
 		sb_prof_scope ps(ctx, "rtree_scan");
-		k_rtree_scan<<<grid, SCAN_WARPS * 32, 0, ctx->stream>>>(L, q, nq, d_counts, nullptr, nullptr, nullptr);
+		k_rtree_scan<<<grid, SCAN_WARPS * 32, 0, ctx->stream>>>(L, q, nq, d_counts, nullptr, nullptr, nullptr, 0);
 		SB_LAUNCH_CHECK(ctx);
+		k_scan_offsets<<<1, 1024, 0, ctx->stream>>>(d_counts, nq, d_offsets);
+		SB_LAUNCH_CHECK(ctx);
+		if (capacity) {
+			k_rtree_scan<<<grid, SCAN_WARPS * 32, 0, ctx->stream>>>(L, q, nq, nullptr, d_offsets, out_query, out_row, capacity);
+			SB_LAUNCH_CHECK(ctx);
+		}
 	}
-	std::vector<uint64_t> h(nq);
-	SB_CUDA(cudaMemcpyAsync(h.data(), d_counts, nq * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
-	SB_CUDA(cudaStreamSynchronize(ctx->stream));
-	uint64_t run = 0;
-	for (uint32_t i = 0; i < nq; i++) {
-		const uint64_t c = h[i];
-		h[i] = run;
-		run += c;
-	}
-	*count = run;
-	if (run > capacity) {
-		sb_set_error("rtree scan: %llu results, capacity %llu", (unsigned long long)run, (unsigned long long)capacity);
+	uint64_t total = 0;
+	SB_TRY(sbi_read_words(ctx, d_offsets + nq, 1, &total));
+	*count = total;
+	if (total > capacity) {
+		sb_set_error("rtree scan: %llu results, capacity %llu", (unsigned long long)total, (unsigned long long)capacity);
 		return SB_ERR_CAPACITY;
 	}
-	if (run == 0) {
-		return SB_OK;
-	}
-	SB_CUDA(cudaMemcpyAsync(d_offsets, h.data(), nq * sizeof(uint64_t), cudaMemcpyHostToDevice, ctx->stream));
-	{
-		sb_prof_scope ps(ctx, "rtree_scan");
-		k_rtree_scan<<<grid, SCAN_WARPS * 32, 0, ctx->stream>>>(L, q, nq, nullptr, d_offsets, out_query, out_row);
-		SB_LAUNCH_CHECK(ctx);
-	}
-	// h (pageable) is read by the async H2D copy: finish it before h goes out of scope
-	SB_CUDA(cudaStreamSynchronize(ctx->stream));
 	return SB_OK;
 }
 
