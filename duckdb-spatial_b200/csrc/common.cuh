@@ -99,7 +99,8 @@ struct sb_context {
 	// 0 = always the exact histogram pass
 	int hist_sample = 1;
 	// sb_context_set_option("str_path"): 0 = auto (STR leaf level: one-pass record partition when the layer has <= 512
-	// slices), 1 = always the bin-id sort + gather form used for larger layers (tests).
+	// slices, leaf nodes by a second select + partition per slice), 1 = always the bin-id sort + gather form used for
+	// larger layers, 2 = record partition + segmented y sort (tests, A/B).
 	int str_path = 0;
 	// sb_context_set_option("trace", 1): synchronise at SB_TRACE points and print the wall time of each phase
 	int trace = 0;

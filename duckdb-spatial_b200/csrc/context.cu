@@ -268,7 +268,7 @@ extern "C" int sb_context_set_option(sb_context *ctx, const char *key, int64_t v
 		return SB_OK;
 	}
 	if (strcmp(key, "str_path") == 0) {
-		SB_ARG(value >= 0 && value <= 1, "str_path must be 0 (auto) or 1 (bin-id sort + gather)");
+		SB_ARG(value >= 0 && value <= 2, "str_path must be 0 (auto), 1 (bin-id sort + gather) or 2 (record partition + y sort)");
 		ctx->str_path = (int)value;
 		return SB_OK;
 	}

@@ -96,6 +96,7 @@ int sbi_str_select_begin(sb_context *ctx, uint64_t n, uint64_t slice, int64_t ke
 int sbi_str_select_finish(sb_context *ctx, const uint32_t *xkeys, uint64_t n, sb_str_select *sel);
 int sbi_str_bin_ids(sb_context *ctx, const uint32_t *xkeys, uint64_t n, const uint32_t *cuts, uint32_t ncut,
                     uint32_t *bins);
+int sbi_str_node_partition(sb_context *ctx, const uint32_t *ykeys, uint64_t n, uint64_t slice, uint32_t cap, uint32_t *perm);
 int sbi_str_partition_rec(sb_context *ctx, const float4 *box, const int64_t *rows, const uint32_t *xkeys,
                           const uint32_t *ykeys, uint64_t n, const uint32_t *cuts, uint32_t ncut, sb_rec32 *rec_out,
                           uint32_t *ykey_out);

@@ -470,11 +470,19 @@ static int str_leaf_level(sb_context *ctx, const float4 *box, const int64_t *row
 		yvb = const_cast<uint32_t *>(xperm);
 		iota = false;
 	}
-	// --- y-sort inside slices, pack leaves --------------------------------------------------------------------
-	// segmented sort: every slice of the x order is sorted by y on its own (4 passes over 32-bit keys; a 64-bit
-	// (slice, y) key sort needed 6)
-	SB_TRY(sbi_radix_sort_u32_segmented(ctx, yk, ykb, yv, yvb, n, slice, 0, 32, iota, &alt));
-	const uint32_t *perm = alt ? yvb : yv;
+	// --- y order inside slices, pack leaves ---------------------------------------------------------------------
+	const uint32_t *perm;
+	if (rec && slice % cap == 0 && slice / cap <= 512 && ctx->str_path != 2) {
+		// leaf nodes are re-ordered by row id when packed: only the node an entry falls in matters, not the y order inside
+		// it -- the y keys at the node boundaries of every slice + one stable partition of the slice's positions
+		SB_TRY(sbi_str_node_partition(ctx, yk, n, slice, cap, yv));
+		perm = yv;
+	} else {
+		// segmented sort: every slice of the x order is sorted by y on its own (4 passes over 32-bit keys; a 64-bit
+		// (slice, y) key sort needed 6)
+		SB_TRY(sbi_radix_sort_u32_segmented(ctx, yk, ykb, yv, yvb, n, slice, 0, 32, iota, &alt));
+		perm = alt ? yvb : yv;
+	}
 	const uint64_t nodes = (n + cap - 1) / cap;
 	{
 		sb_prof_scope ps(ctx, "str_pack");

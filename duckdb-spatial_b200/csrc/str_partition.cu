@@ -784,3 +784,496 @@ int sbi_str_partition_rec(sb_context *ctx, const float4 *box, const int64_t *row
 	SB_LAUNCH_CHECK(ctx);
 	return SB_OK;
 }
+
+// =====================================================================================================================
+// The y order of the leaf level without a sort. A leaf node's entries are re-ordered by row id when the node is packed
+// (RTreeNode::SortEntriesByRowId), so of the y order inside a slice the leaf level only uses WHICH node an entry falls
+// in: the same select + stable partition as for the x order, once per slice -- the y keys at ranks cap, 2 * cap, ...
+// of every slice (k_ysel_slice: one CTA per slice, all histogram levels in shared memory) and a partition of the
+// slice's positions into the bins of those keys (k_ypart_count / scan / k_ypart_scatter). Equal y keys that straddle a
+// node boundary are cut by their order in the slice -- (x bin, input position) -- exactly as the stable segmented sort
+// cut them, so the nodes are the same entry for entry. Replaces four segmented radix passes + their histogram pass.
+// =====================================================================================================================
+#define YS_THREADS 1024
+#define YS_NSP 512u     // ranks per slice (slice / cap - 1 <= 511)
+#define YS_L2 512u      // key bits 20..12
+#define YS_L34 64u      // key bits 11..6 and 5..0
+#define YS_CHUNK 24u    // level-1 buckets whose level-2 rows fit the table at once
+#define YS_REPL 4u      // level-1 histogram replicas (float keys share their top bits)
+
+// Shared memory is carved by the number of ranks of a full slice (nspc) so that two CTAs fit an SM at C1 (105 KB):
+// one wave of slices instead of two, and twice the loads in flight (the kernel is latency bound: four sweeps over the
+// slice's keys). tab holds, in turn: YS_REPL x 2048 level-1 counters, YS_CHUNK x 512 level-2 counters, nspc x 64 level-3 /
+// level-4 counters.
+struct ys_smem {
+	uint32_t *tab;
+	uint32_t *pre1;   // [2049]
+	uint32_t *bitmap; // [nspc * 16] per level-1 cut bucket: which level-2 buckets hold a rank
+	uint32_t *rem;    // [nspc] rank inside the current prefix
+	uint32_t *p2, *p3; // [nspc] 20-bit / 26-bit key prefix of every rank
+	uint32_t *scan;   // [33]
+	uint16_t *map1;   // [2048]
+	uint16_t *b1, *c1, *c2, *c3; // [nspc]
+	uint16_t *wpre;   // [nspc * 16] set bits of the bitmap before each word
+	uint16_t *firstk; // [nspc + 1] first rank of each distinct 20-bit prefix
+};
+__host__ __device__ inline uint32_t ys_tab_words(uint32_t nspc) {
+	uint32_t w = YS_REPL * SEL_L1;
+	w = w > YS_CHUNK * YS_L2 ? w : YS_CHUNK * YS_L2;
+	return w > nspc * YS_L34 ? w : nspc * YS_L34;
+}
+__host__ __device__ inline size_t ys_smem_bytes(uint32_t nspc) {
+	return sizeof(uint32_t) * ((size_t)ys_tab_words(nspc) + SEL_L1 + 1 + (size_t)nspc * (YS_L2 / 32) + 3 * (size_t)nspc + 33 + 3) +
+	       sizeof(uint16_t) * (SEL_L1 + 4 * (size_t)nspc + (size_t)nspc * (YS_L2 / 32) + nspc + 1 + 8);
+}
+__device__ __forceinline__ ys_smem ys_carve(unsigned char *raw, uint32_t nspc) {
+	ys_smem S;
+	uint32_t *w = reinterpret_cast<uint32_t *>(raw);
+	S.tab = w, w += ys_tab_words(nspc);
+	S.pre1 = w, w += SEL_L1 + 1;
+	S.bitmap = w, w += (size_t)nspc * (YS_L2 / 32);
+	S.rem = w, w += nspc;
+	S.p2 = w, w += nspc;
+	S.p3 = w, w += nspc;
+	S.scan = w, w += 33;
+	uint16_t *h = reinterpret_cast<uint16_t *>(w);
+	S.map1 = h, h += SEL_L1;
+	S.b1 = h, h += nspc;
+	S.c1 = h, h += nspc;
+	S.c2 = h, h += nspc;
+	S.c3 = h, h += nspc;
+	S.wpre = h, h += (size_t)nspc * (YS_L2 / 32);
+	S.firstk = h;
+	return S;
+}
+
+// the bucket of `row` (32 * PER counters) that holds rank `rem`, by the whole warp; returns bucket, *left = rank inside it
+template <int PER>
+__device__ __forceinline__ uint32_t ys_warp_find(const uint32_t *row, uint32_t rem, unsigned lane, uint32_t *left) {
+	uint32_t v[PER], sum = 0;
+#pragma unroll
+	for (int j = 0; j < PER; j++) {
+		v[j] = row[lane * PER + j];
+		sum += v[j];
+	}
+	uint32_t inc = sum;
+#pragma unroll
+	for (int s = 1; s < 32; s <<= 1) {
+		const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, s);
+		if (lane >= (unsigned)s) {
+			inc += o;
+		}
+	}
+	const uint32_t excl = inc - sum;
+	const unsigned holders = __ballot_sync(0xFFFFFFFFu, excl <= rem);
+	const int L = 31 - __clz(holders);
+	uint32_t bucket = 0, r = rem - excl;
+	if ((int)lane == L) {
+#pragma unroll
+		for (int j = 0; j < PER; j++) {
+			if (r < v[j]) {
+				bucket = lane * PER + j;
+				break;
+			}
+			r -= v[j];
+		}
+	}
+	*left = __shfl_sync(0xFFFFFFFFu, r, L);
+	return __shfl_sync(0xFFFFFFFFu, bucket, L);
+}
+
+// first index of the sorted array whose value is >= v
+__device__ __forceinline__ uint32_t ys_lower_bound(const uint32_t *a, uint32_t n, uint32_t v) {
+	uint32_t lo = 0, hi = n;
+	while (lo < hi) {
+		const uint32_t mid = (lo + hi) >> 1;
+		if (a[mid] < v) {
+			lo = mid + 1;
+		} else {
+			hi = mid;
+		}
+	}
+	return lo;
+}
+
+// index of each rank's prefix among the distinct prefixes (p sorted, one per rank): c[k]; returns the distinct count
+__device__ __forceinline__ uint32_t ys_distinct(const uint32_t *p, uint32_t nsp, uint16_t *c, uint32_t *s_scan) {
+	const uint32_t k = threadIdx.x;
+	const uint32_t flag = (k < nsp && (k == 0 || p[k] != p[k - 1])) ? 1u : 0u;
+	uint32_t tot;
+	const uint32_t e = sp_block_scan<YS_THREADS>(flag, s_scan, &tot);
+	if (k < nsp) {
+		c[k] = (uint16_t)(e + flag - 1);
+	}
+	__syncthreads();
+	return tot;
+}
+
+__global__ void __launch_bounds__(YS_THREADS, 2) k_ysel_slice(const uint32_t *__restrict__ ykeys, uint64_t n, uint64_t slice,
+                                                              uint32_t cap, uint32_t stride, uint32_t *__restrict__ ycuts) {
+	extern __shared__ __align__(16) unsigned char ys_raw[];
+	const ys_smem S = ys_carve(ys_raw, stride);
+	const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+	const uint64_t beg = (uint64_t)blockIdx.x * slice;
+	const uint32_t m = (uint32_t)min(slice, n - beg);
+	const uint32_t nsp = (m + cap - 1) / cap - 1;
+	if (nsp == 0) {
+		return;
+	}
+	const uint32_t *keys = ykeys + beg;
+	uint32_t *cuts = ycuts + (size_t)blockIdx.x * stride;
+
+	// ---- level 1: top 11 bits, 8 replicas (float keys share their top bits) ----
+	for (uint32_t i = tid; i < YS_REPL * SEL_L1; i += YS_THREADS) {
+		S.tab[i] = 0;
+	}
+	__syncthreads();
+	{
+		uint32_t *mine = S.tab + (lane & (YS_REPL - 1)) * SEL_L1;
+#pragma unroll 4
+		for (uint32_t i = tid; i < m; i += YS_THREADS) {
+			atomicAdd(&mine[keys[i] >> 21], 1u);
+		}
+	}
+	__syncthreads();
+	{
+		uint32_t a = 0, b = 0;
+#pragma unroll
+		for (int r = 0; r < (int)YS_REPL; r++) {
+			a += S.tab[r * SEL_L1 + 2 * tid];
+			b += S.tab[r * SEL_L1 + 2 * tid + 1];
+		}
+		uint32_t total;
+		const uint32_t ex = sp_block_scan<YS_THREADS>(a + b, S.scan, &total);
+		S.pre1[2 * tid] = ex;
+		S.pre1[2 * tid + 1] = ex + a;
+		S.map1[2 * tid] = 0;
+		S.map1[2 * tid + 1] = 0;
+		if (tid == 0) {
+			S.pre1[SEL_L1] = total;
+		}
+	}
+	__syncthreads();
+	if (tid < nsp) {
+		const uint32_t r = (tid + 1) * cap;
+		const uint32_t bk = sp_bucket_of(S.pre1, SEL_L1, r);
+		S.b1[tid] = (uint16_t)bk;
+		S.rem[tid] = r - S.pre1[bk];
+		S.p2[tid] = bk; // level-1 prefix for now
+	}
+	__syncthreads();
+	const uint32_t ncut1 = ys_distinct(S.p2, nsp, S.c1, S.scan);
+	if (tid < nsp && (tid == 0 || S.b1[tid] != S.b1[tid - 1])) {
+		S.map1[S.b1[tid]] = (uint16_t)(S.c1[tid] + 1);
+	}
+	for (uint32_t i = tid; i < ncut1 * (YS_L2 / 32); i += YS_THREADS) {
+		S.bitmap[i] = 0;
+	}
+	__syncthreads();
+
+	// ---- level 2: 9 bits, YS_CHUNK level-1 buckets at a time ----
+	for (uint32_t c0 = 0; c0 < ncut1; c0 += YS_CHUNK) {
+		const uint32_t nc = min(YS_CHUNK, ncut1 - c0);
+		for (uint32_t i = tid; i < nc * YS_L2; i += YS_THREADS) {
+			S.tab[i] = 0;
+		}
+		__syncthreads();
+#pragma unroll 4
+		for (uint32_t i = tid; i < m; i += YS_THREADS) {
+			const uint32_t key = keys[i];
+			const uint32_t c = (uint32_t)S.map1[key >> 21] - 1u - c0; // map1 == 0 wraps to a large value
+			if (c < nc) {
+				atomicAdd(&S.tab[c * YS_L2 + ((key >> SEL_SH2) & (YS_L2 - 1))], 1u);
+			}
+		}
+		__syncthreads();
+		for (uint32_t k = warp; k < nsp; k += YS_THREADS / 32) {
+			const uint32_t c = (uint32_t)S.c1[k] - c0;
+			if (c < nc) { // warp-uniform
+				uint32_t left;
+				const uint32_t b2 = ys_warp_find<YS_L2 / 32>(S.tab + c * YS_L2, S.rem[k], lane, &left);
+				if (lane == 0) {
+					S.rem[k] = left;
+					S.p2[k] = ((uint32_t)S.b1[k] << 9) | b2;
+					atomicOr(&S.bitmap[(uint32_t)S.c1[k] * (YS_L2 / 32) + (b2 >> 5)], 1u << (b2 & 31u));
+				}
+			}
+		}
+		__syncthreads();
+	}
+	const uint32_t ncut2 = ys_distinct(S.p2, nsp, S.c2, S.scan);
+
+	// The 20-bit prefixes that hold a rank are the set bits of the bitmap, in row-major = ascending order: the index of a
+	// prefix among them (= c2 of its ranks) is a popcount rank, so a key finds its counter row without a search
+	// (a binary search per passing key in divergent code was 53 % of this kernel's instructions).
+	{
+		const uint32_t nw = ncut1 * (YS_L2 / 32);
+		uint32_t carry = 0;
+		for (uint32_t w0 = 0; w0 < nw; w0 += YS_THREADS) {
+			const uint32_t w = w0 + tid;
+			const uint32_t pc = w < nw ? __popc(S.bitmap[w]) : 0u;
+			uint32_t tot;
+			const uint32_t e = sp_block_scan<YS_THREADS>(pc, S.scan, &tot);
+			if (w < nw) {
+				S.wpre[w] = (uint16_t)(carry + e);
+			}
+			carry += tot;
+		}
+		if (tid < nsp && (tid == 0 || S.p2[tid] != S.p2[tid - 1])) {
+			S.firstk[S.c2[tid]] = (uint16_t)tid;
+		}
+		if (tid == 0) {
+			S.firstk[ncut2] = (uint16_t)nsp;
+		}
+	}
+	__syncthreads();
+
+	// ---- levels 3 and 4: 6 bits each, only keys whose 20-bit prefix holds a rank ----
+	for (int level = 3; level <= 4; level++) {
+		const uint16_t *cidx = level == 3 ? S.c2 : S.c3;
+		for (uint32_t i = tid; i < nsp * YS_L34; i += YS_THREADS) {
+			S.tab[i] = 0;
+		}
+		__syncthreads();
+#pragma unroll 4
+		for (uint32_t i = tid; i < m; i += YS_THREADS) {
+			const uint32_t key = keys[i];
+			const uint32_t m1 = S.map1[key >> 21];
+			if (m1) {
+				const uint32_t mid = (key >> SEL_SH2) & (YS_L2 - 1);
+				const uint32_t w = (m1 - 1) * (YS_L2 / 32) + (mid >> 5);
+				const uint32_t bits = S.bitmap[w];
+				if ((bits >> (mid & 31u)) & 1u) {
+					const uint32_t c2 = (uint32_t)S.wpre[w] + __popc(bits & ((1u << (mid & 31u)) - 1u));
+					if (level == 3) {
+						atomicAdd(&S.tab[c2 * YS_L34 + ((key >> 6) & (YS_L34 - 1))], 1u);
+					} else {
+						const uint32_t want = key >> 6;
+						for (uint32_t k = S.firstk[c2]; k < S.firstk[c2 + 1]; k++) {
+							if (S.p3[k] == want) { // ranks with one 26-bit prefix are adjacent and share c3
+								atomicAdd(&S.tab[(uint32_t)S.c3[k] * YS_L34 + (key & (YS_L34 - 1))], 1u);
+								break;
+							}
+						}
+					}
+				}
+			}
+		}
+		__syncthreads();
+		for (uint32_t k = warp; k < nsp; k += YS_THREADS / 32) {
+			uint32_t left;
+			const uint32_t b = ys_warp_find<YS_L34 / 32>(S.tab + (uint32_t)cidx[k] * YS_L34, S.rem[k], lane, &left);
+			if (lane == 0) {
+				S.rem[k] = left;
+				if (level == 3) {
+					S.p3[k] = (S.p2[k] << 6) | b;
+				} else {
+					cuts[k] = (S.p3[k] << 6) | b;
+				}
+			}
+		}
+		__syncthreads();
+		if (level == 3) {
+			ys_distinct(S.p3, nsp, S.c3, S.scan);
+		}
+	}
+}
+
+// bins of a slice's positions among the slice's y cuts + the [slice][bin][tile] count table (tiles do not straddle slices)
+__global__ void __launch_bounds__(PT_THREADS) k_ypart_count(const uint32_t *__restrict__ ykeys, uint64_t n, uint64_t slice,
+                                                            uint32_t cap, const uint32_t *__restrict__ ycuts, uint32_t stride,
+                                                            uint32_t nb, uint16_t *__restrict__ bins,
+                                                            uint32_t *__restrict__ tile_hist) {
+	__shared__ uint32_t s_cuts[SP_MAXBINS / 2];
+	__shared__ uint32_t s_hist[SP_MAXBINS];
+	const uint32_t sl = blockIdx.y, tile = blockIdx.x, tps = gridDim.x;
+	const uint64_t sbeg = (uint64_t)sl * slice;
+	const uint32_t m = (uint32_t)min(slice, n - sbeg);
+	const uint32_t ncut = (m + cap - 1) / cap - 1;
+	for (uint32_t i = threadIdx.x; i < ncut; i += PT_THREADS) {
+		s_cuts[i] = ycuts[(size_t)sl * stride + i];
+	}
+	for (uint32_t i = threadIdx.x; i < nb; i += PT_THREADS) {
+		s_hist[i] = 0;
+	}
+	__syncthreads();
+	const uint32_t t0 = tile * PT_TILE;
+#pragma unroll
+	for (int j = 0; j < PT_ITEMS; j++) {
+		const uint32_t i = t0 + (uint32_t)j * PT_THREADS + threadIdx.x;
+		if (i < m) {
+			const uint32_t b = sp_bin(ykeys[sbeg + i], s_cuts, ncut);
+			bins[sbeg + i] = (uint16_t)b;
+			atomicAdd(&s_hist[b], 1u);
+		}
+	}
+	__syncthreads();
+	uint32_t *tab = tile_hist + (size_t)sl * nb * tps;
+	for (uint32_t i = threadIdx.x; i < nb; i += PT_THREADS) {
+		tab[(size_t)i * tps + tile] = s_hist[i];
+	}
+}
+
+// stable scatter of a slice tile's POSITIONS into node order: perm[first position of (slice, bin, tile) + rank] = position
+struct yp_smem {
+	uint32_t val[PT_TILE];
+	uint32_t gl[SP_MAXBINS + 3];
+	uint16_t wh[PT_THREADS / 32][SP_MAXBINS + 1];
+	uint16_t doff[SP_MAXBINS + 3];
+	uint16_t tot[PS_KBINS * PT_THREADS];
+	uint16_t bin[PT_TILE];
+	uint32_t scan[33];
+};
+__global__ void __launch_bounds__(PT_THREADS, 5) k_ypart_scatter(const uint16_t *__restrict__ bins, uint64_t n, uint64_t slice,
+                                                                 uint32_t nb, int nbits, const uint32_t *__restrict__ tile_pos,
+                                                                 uint32_t *__restrict__ perm) {
+	__shared__ yp_smem S;
+	const uint32_t sl = blockIdx.y, tile = blockIdx.x, tps = gridDim.x;
+	const uint64_t sbeg = (uint64_t)sl * slice;
+	const uint32_t m = (uint32_t)min(slice, n - sbeg);
+	const uint32_t t0 = tile * PT_TILE;
+	if (t0 >= m) {
+		return;
+	}
+	{
+		const uint32_t words = (nb + 2) / 2;
+		for (uint32_t i = threadIdx.x; i < (PT_THREADS / 32) * words; i += PT_THREADS) {
+			reinterpret_cast<uint32_t *>(S.wh[i / words])[i % words] = 0;
+		}
+	}
+	__syncthreads();
+	const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+	const unsigned lt_mask = sb_lanemask_lt();
+	const uint32_t tile_count = min((uint32_t)PT_TILE, m - t0);
+	const uint32_t first = t0 + warp * (32 * PT_ITEMS) + lane; // position inside the slice
+	uint32_t br[PT_ITEMS];
+	uint16_t *my = S.wh[warp];
+	uint32_t r_pos[PS_KBINS];
+#pragma unroll
+	for (int i = 0; i < PT_ITEMS; i++) {
+		const uint32_t gi = first + (uint32_t)i * 32;
+		br[i] = gi < m ? bins[sbeg + gi] : 0u;
+	}
+	const uint32_t *tab = tile_pos + (size_t)sl * nb * tps;
+#pragma unroll
+	for (int k = 0; k < PS_KBINS; k++) {
+		const uint32_t b = threadIdx.x * PS_KBINS + k;
+		r_pos[k] = b < nb ? tab[(size_t)b * tps + tile] : 0u;
+	}
+#pragma unroll
+	for (int i = 0; i < PT_ITEMS; i++) {
+		const bool valid = first + (uint32_t)i * 32 < m;
+		const uint32_t b = br[i];
+		unsigned peers = __ballot_sync(0xFFFFFFFFu, valid);
+#pragma unroll
+		for (int k = 0; k < 11; k++) {
+			if (k < nbits) {
+				const bool bit = (b >> k) & 1u;
+				const unsigned mm = __ballot_sync(0xFFFFFFFFu, bit);
+				peers &= bit ? mm : ~mm;
+			}
+		}
+		const int leader = __ffs(peers) - 1;
+		uint32_t prev = 0;
+		if ((int)lane == leader && valid) {
+			prev = my[b];
+			my[b] = (uint16_t)(prev + __popc(peers));
+		}
+		prev = __shfl_sync(0xFFFFFFFFu, prev, leader < 0 ? 0 : leader);
+		br[i] = b | ((prev + __popc(peers & lt_mask)) << 16);
+		__syncwarp();
+	}
+	__syncthreads();
+	for (uint32_t b = threadIdx.x; b < PS_KBINS * PT_THREADS; b += PT_THREADS) {
+		uint32_t run = 0;
+		if (b < nb) {
+#pragma unroll
+			for (int w = 0; w < PT_THREADS / 32; w++) {
+				const uint32_t c = S.wh[w][b];
+				S.wh[w][b] = (uint16_t)run;
+				run += c;
+			}
+		}
+		S.tot[b] = (uint16_t)run;
+	}
+	__syncthreads();
+	{
+		uint32_t tot[PS_KBINS], sum = 0;
+#pragma unroll
+		for (int k = 0; k < PS_KBINS; k++) {
+			tot[k] = S.tot[threadIdx.x * PS_KBINS + k];
+			sum += tot[k];
+		}
+		uint32_t all;
+		uint32_t run = sp_block_scan<PT_THREADS>(sum, S.scan, &all);
+#pragma unroll
+		for (int k = 0; k < PS_KBINS; k++) {
+			const uint32_t b = threadIdx.x * PS_KBINS + k;
+			if (b < nb) {
+				S.doff[b] = (uint16_t)run;
+				S.gl[b] = r_pos[k] - run;
+			}
+			run += tot[k];
+		}
+	}
+	__syncthreads();
+#pragma unroll
+	for (int i = 0; i < PT_ITEMS; i++) {
+		const uint32_t gi = first + (uint32_t)i * 32;
+		if (gi < m) {
+			const uint32_t b = br[i] & 0xFFFFu;
+			const uint32_t p = (uint32_t)S.doff[b] + my[b] + (br[i] >> 16);
+			S.val[p] = (uint32_t)(sbeg + gi);
+			S.bin[p] = (uint16_t)b;
+		}
+	}
+	__syncthreads();
+	for (uint32_t p = threadIdx.x; p < tile_count; p += PT_THREADS) {
+		perm[S.gl[S.bin[p]] + p] = S.val[p];
+	}
+}
+
+// perm[j] = position (in the x-partitioned order) of the j-th entry of the leaf level's node order, up to the order of the
+// entries inside a node. ykeys: y keys in x-partitioned order. Requires slice / cap - 1 <= 511.
+int sbi_str_node_partition(sb_context *ctx, const uint32_t *ykeys, uint64_t n, uint64_t slice, uint32_t cap, uint32_t *perm) {
+	const uint32_t nsp_max = (uint32_t)(slice / cap) - 1; // ranks of a full slice
+	SB_ARG(slice % cap == 0 && nsp_max < YS_NSP, "STR node partition: slice / cap");
+	const uint32_t nslices = (uint32_t)((n + slice - 1) / slice);
+	const uint32_t stride = nsp_max ? nsp_max : 1;
+	const uint32_t nb = 2 * nsp_max + 1;
+	int nbits = 0;
+	while ((1u << nbits) < nb) {
+		nbits++;
+	}
+	const uint32_t tps = (uint32_t)((slice + PT_TILE - 1) / PT_TILE);
+	const uint64_t cells = (uint64_t)nslices * nb * tps;
+	const uint32_t nblk = (uint32_t)((cells + SC_BLOCK - 1) / SC_BLOCK);
+	uint32_t *ycuts = nullptr, *tile_hist = nullptr, *sums = nullptr;
+	uint16_t *bins = nullptr;
+	SB_TRY(ctx->scratch_t((size_t)nslices * stride, &ycuts));
+	SB_TRY(ctx->scratch_t(n, &bins));
+	SB_TRY(ctx->scratch_t(cells, &tile_hist));
+	SB_TRY(ctx->scratch_t(nblk, &sums));
+	{
+		sb_prof_scope ps(ctx, "str_select");
+		if (nsp_max) {
+			SB_SMEM_OPTIN(ctx, k_ysel_slice, ys_smem_bytes(YS_NSP));
+			k_ysel_slice<<<nslices, YS_THREADS, ys_smem_bytes(stride), ctx->stream>>>(ykeys, n, slice, cap, stride, ycuts);
+			SB_LAUNCH_CHECK(ctx);
+		}
+	}
+	sb_prof_scope ps(ctx, "str_partition");
+	// every (slice, tile) CTA writes its whole column of the table (zeros past the end of a short last slice)
+	const dim3 grid(tps, nslices);
+	k_ypart_count<<<grid, PT_THREADS, 0, ctx->stream>>>(ykeys, n, slice, cap, ycuts, stride, nb, bins, tile_hist);
+	SB_LAUNCH_CHECK(ctx);
+	k_scan_sums<<<nblk, 256, 0, ctx->stream>>>(tile_hist, cells, sums);
+	SB_LAUNCH_CHECK(ctx);
+	k_scan_top<<<1, 1024, 0, ctx->stream>>>(sums, nblk);
+	SB_LAUNCH_CHECK(ctx);
+	k_scan_apply<<<nblk, 256, 0, ctx->stream>>>(tile_hist, cells, sums);
+	SB_LAUNCH_CHECK(ctx);
+	k_ypart_scatter<<<grid, PT_THREADS, 0, ctx->stream>>>(bins, n, slice, nb, nbits, tile_hist, perm);
+	SB_LAUNCH_CHECK(ctx);
+	return SB_OK;
+}
