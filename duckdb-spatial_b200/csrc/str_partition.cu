@@ -823,14 +823,16 @@ __host__ __device__ inline uint32_t ys_tab_words(uint32_t nspc) {
 	return w > nspc * YS_L34 ? w : nspc * YS_L34;
 }
 __host__ __device__ inline size_t ys_smem_bytes(uint32_t nspc) {
-	return sizeof(uint32_t) * ((size_t)ys_tab_words(nspc) + SEL_L1 + 1 + (size_t)nspc * (YS_L2 / 32) + 3 * (size_t)nspc + 33 + 3) +
-	       sizeof(uint16_t) * (SEL_L1 + 4 * (size_t)nspc + (size_t)nspc * (YS_L2 / 32) + nspc + 1 + 8);
+	// pre1 (level 1 only) and wpre / firstk (levels 3, 4) share their storage
+	const size_t late = sizeof(uint16_t) * ((size_t)nspc * (YS_L2 / 32) + nspc + 2);
+	const size_t early = sizeof(uint32_t) * (SEL_L1 + 1);
+	return sizeof(uint32_t) * ((size_t)ys_tab_words(nspc) + (size_t)nspc * (YS_L2 / 32) + 3 * (size_t)nspc + 33 + 3) +
+	       sizeof(uint16_t) * (SEL_L1 + 4 * (size_t)nspc + 8) + (late > early ? late : early) + 16;
 }
 __device__ __forceinline__ ys_smem ys_carve(unsigned char *raw, uint32_t nspc) {
 	ys_smem S;
 	uint32_t *w = reinterpret_cast<uint32_t *>(raw);
 	S.tab = w, w += ys_tab_words(nspc);
-	S.pre1 = w, w += SEL_L1 + 1;
 	S.bitmap = w, w += (size_t)nspc * (YS_L2 / 32);
 	S.rem = w, w += nspc;
 	S.p2 = w, w += nspc;
@@ -842,6 +844,8 @@ __device__ __forceinline__ ys_smem ys_carve(unsigned char *raw, uint32_t nspc) {
 	S.c1 = h, h += nspc;
 	S.c2 = h, h += nspc;
 	S.c3 = h, h += nspc;
+	h += (reinterpret_cast<uintptr_t>(h) & 2u) ? 1 : 0; // 4-byte alignment for pre1
+	S.pre1 = reinterpret_cast<uint32_t *>(h);
 	S.wpre = h, h += (size_t)nspc * (YS_L2 / 32);
 	S.firstk = h;
 	return S;
@@ -910,7 +914,8 @@ __device__ __forceinline__ uint32_t ys_distinct(const uint32_t *p, uint32_t nsp,
 }
 
 __global__ void __launch_bounds__(YS_THREADS, 2) k_ysel_slice(const uint32_t *__restrict__ ykeys, uint64_t n, uint64_t slice,
-                                                              uint32_t cap, uint32_t stride, uint32_t *__restrict__ ycuts) {
+                                                              uint32_t cap, uint32_t stride, uint32_t *__restrict__ ycuts,
+                                                              uint32_t *__restrict__ yluts) {
 	extern __shared__ __align__(16) unsigned char ys_raw[];
 	const ys_smem S = ys_carve(ys_raw, stride);
 	const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
@@ -1068,7 +1073,7 @@ __global__ void __launch_bounds__(YS_THREADS, 2) k_ysel_slice(const uint32_t *__
 				if (level == 3) {
 					S.p3[k] = (S.p2[k] << 6) | b;
 				} else {
-					cuts[k] = (S.p3[k] << 6) | b;
+					cuts[k] = S.p2[k] = (S.p3[k] << 6) | b; // p2 is free by now: the slice's cut keys stay in shared memory
 				}
 			}
 		}
@@ -1077,15 +1082,39 @@ __global__ void __launch_bounds__(YS_THREADS, 2) k_ysel_slice(const uint32_t *__
 			ys_distinct(S.p3, nsp, S.c3, S.scan);
 		}
 	}
+	// the slice's table for the bin search of the partition (see k_part_lut): [0] = first cut, [1] = shift, [2 ..] = table
+	{
+		uint32_t *lut = yluts + (size_t)blockIdx.x * (SP_LUT + 3);
+		const uint32_t lo = S.p2[0], hi = S.p2[nsp - 1];
+		const int bits = 32 - __clz((hi - lo) | 1u);
+		const int shift = bits > 10 ? bits - 10 : 0;
+		const unsigned long long start = (unsigned long long)lo + ((unsigned long long)tid << shift);
+		uint32_t a = 0, b = nsp;
+		while (a < b) {
+			const uint32_t mid = (a + b) >> 1;
+			if ((unsigned long long)S.p2[mid] < start) {
+				a = mid + 1;
+			} else {
+				b = mid;
+			}
+		}
+		lut[2 + tid] = a;
+		if (tid == 0) {
+			lut[0] = lo;
+			lut[1] = (uint32_t)shift;
+			lut[2 + SP_LUT] = nsp;
+		}
+	}
 }
 
 // bins of a slice's positions among the slice's y cuts + the [slice][bin][tile] count table (tiles do not straddle slices)
 __global__ void __launch_bounds__(PT_THREADS) k_ypart_count(const uint32_t *__restrict__ ykeys, uint64_t n, uint64_t slice,
                                                             uint32_t cap, const uint32_t *__restrict__ ycuts, uint32_t stride,
-                                                            uint32_t nb, uint16_t *__restrict__ bins,
-                                                            uint32_t *__restrict__ tile_hist) {
+                                                            const uint32_t *__restrict__ yluts, uint32_t nb,
+                                                            uint16_t *__restrict__ bins, uint32_t *__restrict__ tile_hist) {
 	__shared__ uint32_t s_cuts[SP_MAXBINS / 2];
 	__shared__ uint32_t s_hist[SP_MAXBINS];
+	__shared__ uint16_t s_lut[SP_LUT + 1];
 	const uint32_t sl = blockIdx.y, tile = blockIdx.x, tps = gridDim.x;
 	const uint64_t sbeg = (uint64_t)sl * slice;
 	const uint32_t m = (uint32_t)min(slice, n - sbeg);
@@ -1096,13 +1125,19 @@ __global__ void __launch_bounds__(PT_THREADS) k_ypart_count(const uint32_t *__re
 	for (uint32_t i = threadIdx.x; i < nb; i += PT_THREADS) {
 		s_hist[i] = 0;
 	}
+	// a slice without cuts (a short last slice of one node) has no table: lo = 0, shift = 0, all entries 0 -> bin 0
+	const uint32_t *lut = yluts + (size_t)sl * (SP_LUT + 3);
+	for (uint32_t i = threadIdx.x; i < SP_LUT + 1; i += PT_THREADS) {
+		s_lut[i] = ncut ? (uint16_t)lut[2 + i] : (uint16_t)0;
+	}
+	const uint32_t lut_lo = ncut ? lut[0] : 0u, lut_shift = ncut ? lut[1] : 0u;
 	__syncthreads();
 	const uint32_t t0 = tile * PT_TILE;
 #pragma unroll
 	for (int j = 0; j < PT_ITEMS; j++) {
 		const uint32_t i = t0 + (uint32_t)j * PT_THREADS + threadIdx.x;
 		if (i < m) {
-			const uint32_t b = sp_bin(ykeys[sbeg + i], s_cuts, ncut);
+			const uint32_t b = sp_bin_lut(ykeys[sbeg + i], s_cuts, ncut, s_lut, lut_lo, lut_shift);
 			bins[sbeg + i] = (uint16_t)b;
 			atomicAdd(&s_hist[b], 1u);
 		}
@@ -1248,9 +1283,10 @@ int sbi_str_node_partition(sb_context *ctx, const uint32_t *ykeys, uint64_t n, u
 	const uint32_t tps = (uint32_t)((slice + PT_TILE - 1) / PT_TILE);
 	const uint64_t cells = (uint64_t)nslices * nb * tps;
 	const uint32_t nblk = (uint32_t)((cells + SC_BLOCK - 1) / SC_BLOCK);
-	uint32_t *ycuts = nullptr, *tile_hist = nullptr, *sums = nullptr;
+	uint32_t *ycuts = nullptr, *yluts = nullptr, *tile_hist = nullptr, *sums = nullptr;
 	uint16_t *bins = nullptr;
 	SB_TRY(ctx->scratch_t((size_t)nslices * stride, &ycuts));
+	SB_TRY(ctx->scratch_t((size_t)nslices * (SP_LUT + 3), &yluts));
 	SB_TRY(ctx->scratch_t(n, &bins));
 	SB_TRY(ctx->scratch_t(cells, &tile_hist));
 	SB_TRY(ctx->scratch_t(nblk, &sums));
@@ -1258,14 +1294,14 @@ int sbi_str_node_partition(sb_context *ctx, const uint32_t *ykeys, uint64_t n, u
 		sb_prof_scope ps(ctx, "str_select");
 		if (nsp_max) {
 			SB_SMEM_OPTIN(ctx, k_ysel_slice, ys_smem_bytes(YS_NSP));
-			k_ysel_slice<<<nslices, YS_THREADS, ys_smem_bytes(stride), ctx->stream>>>(ykeys, n, slice, cap, stride, ycuts);
+			k_ysel_slice<<<nslices, YS_THREADS, ys_smem_bytes(stride), ctx->stream>>>(ykeys, n, slice, cap, stride, ycuts, yluts);
 			SB_LAUNCH_CHECK(ctx);
 		}
 	}
 	sb_prof_scope ps(ctx, "str_partition");
 	// every (slice, tile) CTA writes its whole column of the table (zeros past the end of a short last slice)
 	const dim3 grid(tps, nslices);
-	k_ypart_count<<<grid, PT_THREADS, 0, ctx->stream>>>(ykeys, n, slice, cap, ycuts, stride, nb, bins, tile_hist);
+	k_ypart_count<<<grid, PT_THREADS, 0, ctx->stream>>>(ykeys, n, slice, cap, ycuts, stride, yluts, nb, bins, tile_hist);
 	SB_LAUNCH_CHECK(ctx);
 	k_scan_sums<<<nblk, 256, 0, ctx->stream>>>(tile_hist, cells, sums);
 	SB_LAUNCH_CHECK(ctx);
