@@ -656,7 +656,7 @@ def run_ours(a):
             s1.record(stream)
             torch.cuda.synchronize()
             bms = s0.elapsed_time(s1) / reps
-            rb = {"workload": "C1: CREATE INDEX USING RTREE, 10M ST_GeneratePoints points (bbox + x-slice select / partition + slice y-sort + pack, cap 128)",
+            rb = {"workload": "C1: CREATE INDEX USING RTREE, 10M ST_GeneratePoints points (bbox + x-slice select / partition + per-slice node select / partition + pack, cap 128)",
                   "mkeys_per_s": n1 / bms / 1e3, "ms": bms, "algorithmic_gbs": 48.2 * n1 / (bms / 1e3) / 1e9,
                   "hbm_frac": 48.2 * n1 / (bms / 1e3) / 1e9 / hbm_peak}
             if not a.no_parity:
