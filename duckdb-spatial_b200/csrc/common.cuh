@@ -100,7 +100,8 @@ struct sb_context {
 	int hist_sample = 1;
 	// sb_context_set_option("str_path"): 0 = auto (STR leaf level: one-pass record partition when the layer has <= 512
 	// slices, leaf nodes by a second select + partition per slice), 1 = always the bin-id sort + gather form used for
-	// larger layers, 2 = record partition + segmented y sort (tests, A/B).
+	// larger layers, 2 = record partition + segmented y sort, 3 = node partition of a slice by separate count / scan /
+	// scatter kernels instead of inside the select kernel (what slices above 65535 entries take) (tests, A/B).
 	int str_path = 0;
 	// sb_context_set_option("trace", 1): synchronise at SB_TRACE points and print the wall time of each phase
 	int trace = 0;

@@ -268,7 +268,8 @@ extern "C" int sb_context_set_option(sb_context *ctx, const char *key, int64_t v
 		return SB_OK;
 	}
 	if (strcmp(key, "str_path") == 0) {
-		SB_ARG(value >= 0 && value <= 2, "str_path must be 0 (auto), 1 (bin-id sort + gather) or 2 (record partition + y sort)");
+		SB_ARG(value >= 0 && value <= 3, "str_path must be 0 (auto), 1 (bin-id sort + gather), 2 (record partition + y sort) or 3 "
+		                                 "(node partition by separate kernels, the form of slices above 65535 entries)");
 		ctx->str_path = (int)value;
 		return SB_OK;
 	}

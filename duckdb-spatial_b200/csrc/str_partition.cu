@@ -915,7 +915,7 @@ __device__ __forceinline__ uint32_t ys_distinct(const uint32_t *p, uint32_t nsp,
 
 __global__ void __launch_bounds__(YS_THREADS, 2) k_ysel_slice(const uint32_t *__restrict__ ykeys, uint64_t n, uint64_t slice,
                                                               uint32_t cap, uint32_t stride, uint32_t *__restrict__ ycuts,
-                                                              uint32_t *__restrict__ yluts) {
+                                                              uint32_t *__restrict__ yluts, uint32_t *__restrict__ perm) {
 	extern __shared__ __align__(16) unsigned char ys_raw[];
 	const ys_smem S = ys_carve(ys_raw, stride);
 	const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
@@ -923,6 +923,11 @@ __global__ void __launch_bounds__(YS_THREADS, 2) k_ysel_slice(const uint32_t *__
 	const uint32_t m = (uint32_t)min(slice, n - beg);
 	const uint32_t nsp = (m + cap - 1) / cap - 1;
 	if (nsp == 0) {
+		if (perm) { // one node: any order
+			for (uint32_t i = tid; i < m; i += YS_THREADS) {
+				perm[beg + i] = (uint32_t)(beg + i);
+			}
+		}
 		return;
 	}
 	const uint32_t *keys = ykeys + beg;
@@ -1103,6 +1108,99 @@ __global__ void __launch_bounds__(YS_THREADS, 2) k_ysel_slice(const uint32_t *__
 			lut[0] = lo;
 			lut[1] = (uint32_t)shift;
 			lut[2 + SP_LUT] = nsp;
+		}
+		if (!perm) {
+			return;
+		}
+		// ---- the slice's positions in node order, by the same CTA (slices of <= 65535 entries) -----------------------
+		// Warp w owns the w-th 32nd of the slice. Pass A counts its keys per bin, a scan turns the counts into the first
+		// place of (bin, warp), pass B ranks each row of 32 keys with ballots against the warp's running cursors: the
+		// result is stable in (bin, position), no count table, bin array or second launch goes through global memory.
+		uint16_t *s_lut = reinterpret_cast<uint16_t *>(S.pre1); // wpre / firstk / pre1 are dead: their storage holds the table
+		__syncthreads();
+		s_lut[tid] = (uint16_t)a;
+		if (tid == 0) {
+			s_lut[SP_LUT] = (uint16_t)nsp;
+		}
+		const uint32_t nb = 2 * nsp + 1, nbp = (nb + 2) & ~1u; // row length of the per-warp counters (even)
+		uint16_t *wh = reinterpret_cast<uint16_t *>(S.tab);     // [32][nbp]
+		uint32_t *base = S.tab + 16 * nbp;                       // [nb] first place of the bin
+		for (uint32_t i = tid; i < 16 * nbp; i += YS_THREADS) {
+			S.tab[i] = 0;
+		}
+		__syncthreads();
+		const uint32_t chunk = ((m + 1023u) / 1024u) * 32u; // positions per warp, whole rows
+		const uint32_t w0 = warp * chunk;
+		uint32_t *wrow32 = S.tab + (warp * nbp) / 2;
+#pragma unroll 4
+		for (uint32_t r = 0; r < chunk; r += 32) {
+			const uint32_t i = w0 + r + lane;
+			if (i < m) {
+				const uint32_t bin = sp_bin_lut(keys[i], S.p2, nsp, s_lut, lo, (uint32_t)shift);
+				atomicAdd(&wrow32[bin >> 1], 1u << (16u * (bin & 1u)));
+			}
+		}
+		__syncthreads();
+		{
+			uint32_t run = 0;
+			if (tid < nb) {
+#pragma unroll 8
+				for (uint32_t w = 0; w < 32; w++) {
+					const uint32_t c = wh[w * nbp + tid];
+					wh[w * nbp + tid] = (uint16_t)run;
+					run += c;
+				}
+			}
+			uint32_t tot;
+			const uint32_t e = sp_block_scan<YS_THREADS>(run, S.scan, &tot);
+			if (tid < nb) {
+				base[tid] = e;
+			}
+		}
+		__syncthreads();
+		int nbits = 0;
+		while ((1u << nbits) < nb) {
+			nbits++;
+		}
+		const unsigned lt_mask = sb_lanemask_lt();
+		uint16_t *my = wh + warp * nbp;
+		// four rows at a time: the key loads and bin searches of a batch overlap, only the cursor updates are sequential
+		for (uint32_t r0 = 0; r0 < chunk; r0 += 128) {
+			uint32_t bins4[4];
+#pragma unroll
+			for (int q = 0; q < 4; q++) {
+				const uint32_t i = w0 + r0 + q * 32 + lane;
+				bins4[q] = (r0 + q * 32 < chunk && i < m) ? sp_bin_lut(keys[i], S.p2, nsp, s_lut, lo, (uint32_t)shift) : 0xFFFFFFFFu;
+			}
+#pragma unroll
+			for (int q = 0; q < 4; q++) {
+				const uint32_t i = w0 + r0 + q * 32 + lane;
+				const bool valid = bins4[q] != 0xFFFFFFFFu;
+				const uint32_t bin = valid ? bins4[q] : 0u;
+				unsigned peers = __ballot_sync(0xFFFFFFFFu, valid);
+				if (peers == 0) {
+					continue; // warp-uniform: an empty row
+				}
+#pragma unroll
+				for (int k = 0; k < 10; k++) {
+					if (k < nbits) {
+						const bool bit = (bin >> k) & 1u;
+						const unsigned mm = __ballot_sync(0xFFFFFFFFu, bit);
+						peers &= bit ? mm : ~mm;
+					}
+				}
+				const int leader = __ffs(peers) - 1;
+				uint32_t prev = 0;
+				if ((int)lane == leader && valid) {
+					prev = my[bin];
+					my[bin] = (uint16_t)(prev + __popc(peers));
+				}
+				prev = __shfl_sync(0xFFFFFFFFu, prev, leader < 0 ? 0 : leader);
+				if (valid) {
+					perm[beg + base[bin] + prev + __popc(peers & lt_mask)] = (uint32_t)(beg + i);
+				}
+				__syncwarp();
+			}
 		}
 	}
 }
@@ -1290,13 +1388,18 @@ int sbi_str_node_partition(sb_context *ctx, const uint32_t *ykeys, uint64_t n, u
 	SB_TRY(ctx->scratch_t(n, &bins));
 	SB_TRY(ctx->scratch_t(cells, &tile_hist));
 	SB_TRY(ctx->scratch_t(nblk, &sums));
+	const bool fused = slice <= 65535 && nsp_max > 0 && ctx->str_path != 3; // 16-bit cursors inside a slice
 	{
 		sb_prof_scope ps(ctx, "str_select");
 		if (nsp_max) {
 			SB_SMEM_OPTIN(ctx, k_ysel_slice, ys_smem_bytes(YS_NSP));
-			k_ysel_slice<<<nslices, YS_THREADS, ys_smem_bytes(stride), ctx->stream>>>(ykeys, n, slice, cap, stride, ycuts, yluts);
+			k_ysel_slice<<<nslices, YS_THREADS, ys_smem_bytes(stride), ctx->stream>>>(ykeys, n, slice, cap, stride, ycuts, yluts,
+			                                                                         fused ? perm : nullptr);
 			SB_LAUNCH_CHECK(ctx);
 		}
+	}
+	if (fused) {
+		return SB_OK;
 	}
 	sb_prof_scope ps(ctx, "str_partition");
 	// every (slice, tile) CTA writes its whole column of the table (zeros past the end of a short last slice)

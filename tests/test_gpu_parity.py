@@ -222,12 +222,12 @@ def test_str_build_wide_row_ids(ctx, sb, O, n, cap, spread):
 
 
 @pytest.mark.parametrize("case", ["same_x", "same_xy", "two_x", "grid", "sorted", "reverse", "clustered_rows", "wide_keys"])
-@pytest.mark.parametrize("path", [0, 1, 2])
+@pytest.mark.parametrize("path", [0, 1, 2, 3])
 def test_str_build_degenerate_inputs(ctx, sb, O, case, path):
     # the x order is a radix select of the slice-boundary keys + a stable partition (str_partition.cu): inputs whose x keys
     # repeat across slice boundaries, whose keys sit in one histogram bucket / in all of them, presorted inputs; both
     # forms of the leaf level (str_path 0: record partition + node partition per slice, 1: bin-id sort + gather,
-    # 2: record partition + segmented y sort)
+    # 2: record partition + segmented y sort, 3: node partition by separate kernels)
     rng = np.random.default_rng(11)
     n, cap = 70_001, 16
     x, y = O.generate_points(5, n, (0, 0, 1000, 1000))
