@@ -136,15 +136,18 @@ __global__ void __launch_bounds__(256)
 // above, stored as coalesced 8-byte words; one parent entry {(LEAF_PAGE << 56) | node, union box} per node.
 #define PKW_WARPS 4
 #define PKW_CNT(b) ((b) + ((b) >> 3))
+#ifndef PKW_MIN_CTAS
+#define PKW_MIN_CTAS 8
+#endif
 template <int PER>
-__global__ void __launch_bounds__(PKW_WARPS * 32)
+__global__ void __launch_bounds__(PKW_WARPS * 32, PKW_MIN_CTAS)
     k_str_pack_leaf(const float4 *__restrict__ box, const int64_t *__restrict__ row_ids, const sb_rec32 *__restrict__ rec,
                     const uint32_t *__restrict__ perm, uint64_t count, uint32_t cap, uint64_t nodes,
                     sb_entry *__restrict__ level_out, sb_entry *__restrict__ parent_out, uint64_t node_base) {
+	// per warp: the node's output words; the ranking scratch (bucket counters padded so that lane * 8 + q falls in 32
+	// different banks, keys and sources by bucket) lives in the same storage -- it is dead when the words are written
 	__shared__ uint64_t s_words_all[PKW_WARPS][PER * 32 * 3];
-	__shared__ uint32_t s_cnt_all[PKW_WARPS][PKW_CNT(256) + 1]; // padded: lane * 8 + q falls in 32 different banks
-	__shared__ uint32_t s_key_all[PKW_WARPS][PER * 32];
-	__shared__ uint8_t s_src_all[PKW_WARPS][PER * 32];
+	static_assert((PKW_CNT(256) + 1 + PER * 32 + PER * 8) * 4 <= PER * 32 * 3 * 8, "ranking scratch fits the output words");
 	const unsigned warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
 	const uint64_t node = (uint64_t)blockIdx.x * PKW_WARPS + warp;
 	if (node >= nodes) {
@@ -152,8 +155,8 @@ __global__ void __launch_bounds__(PKW_WARPS * 32)
 	}
 	uint64_t *s_words = s_words_all[warp];
 	int64_t *s_row = reinterpret_cast<int64_t *>(s_words); // only read before the words are written (slow rank path)
-	uint32_t *s_cnt = s_cnt_all[warp], *s_key = s_key_all[warp];
-	uint8_t *s_src = s_src_all[warp];
+	uint32_t *s_cnt = reinterpret_cast<uint32_t *>(s_words), *s_key = s_cnt + PKW_CNT(256) + 1;
+	uint8_t *s_src = reinterpret_cast<uint8_t *>(s_key + PER * 32);
 	const uint64_t beg = node * cap;
 	const uint32_t cnt = (uint32_t)min((uint64_t)cap, count - beg);
 	float4 bx[PER];
