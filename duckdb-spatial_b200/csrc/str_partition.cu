@@ -422,8 +422,13 @@ __global__ void __launch_bounds__(1024) k_part_lut(const uint32_t *__restrict__ 
 	}
 }
 
+// is_run (optional): the key EQUALS a cut key (its bin is a run of equal keys; with d equal cut keys the bin id is
+// 2 * lb + d, so the parity of the id does not tell)
 __device__ __forceinline__ uint32_t sp_bin_lut(uint32_t key, const uint32_t *s_cuts, uint32_t ncut, const uint16_t *s_lut,
-                                               uint32_t lo, uint32_t shift) {
+                                               uint32_t lo, uint32_t shift, bool *is_run = nullptr) {
+	if (is_run) {
+		*is_run = false;
+	}
 	if (key < lo) {
 		return 0;
 	}
@@ -439,6 +444,9 @@ __device__ __forceinline__ uint32_t sp_bin_lut(uint32_t key, const uint32_t *s_c
 	}
 	uint32_t ub = a;
 	if (a < ncut && s_cuts[a] == key) {
+		if (is_run) {
+			*is_run = true;
+		}
 		ub = a + 1;
 		uint32_t hi = ncut;
 		while (ub < hi) {
@@ -1170,24 +1178,36 @@ __global__ void __launch_bounds__(YS_THREADS, 2) k_ysel_slice(const uint32_t *__
 #pragma unroll
 			for (int q = 0; q < 4; q++) {
 				const uint32_t i = w0 + r0 + q * 32 + lane;
-				bins4[q] = (r0 + q * 32 < chunk && i < m) ? sp_bin_lut(keys[i], S.p2, nsp, s_lut, lo, (uint32_t)shift) : 0xFFFFFFFFu;
+				bool run = false;
+				bins4[q] = (r0 + q * 32 < chunk && i < m) ? sp_bin_lut(keys[i], S.p2, nsp, s_lut, lo, (uint32_t)shift, &run) : 0x7FFFFFFFu;
+				bins4[q] |= run ? 0x80000000u : 0u;
 			}
 #pragma unroll
 			for (int q = 0; q < 4; q++) {
 				const uint32_t i = w0 + r0 + q * 32 + lane;
-				const bool valid = bins4[q] != 0xFFFFFFFFu;
-				const uint32_t bin = valid ? bins4[q] : 0u;
+				const bool valid = (bins4[q] & 0x7FFFFFFFu) != 0x7FFFFFFFu;
+				const bool run = bins4[q] >> 31;
+				const uint32_t bin = valid ? bins4[q] & 0x7FFFFFFFu : 0u;
 				unsigned peers = __ballot_sync(0xFFFFFFFFu, valid);
 				if (peers == 0) {
 					continue; // warp-uniform: an empty row
 				}
-#pragma unroll
-				for (int k = 0; k < 10; k++) {
-					if (k < nbits) {
-						const bool bit = (bin >> k) & 1u;
-						const unsigned mm = __ballot_sync(0xFFFFFFFFu, bit);
-						peers &= bit ? mm : ~mm;
+				// Keys strictly between two cut keys lie inside ONE node, whose entries are re-ordered by row id anyway:
+				// their order is free, a shared-memory atomic on the warp's cursor places them. Only rows that hold a key
+				// EQUAL to a cut key (the run of equal keys may straddle a node boundary and is cut by position) take the
+				// stable ballot ranking. (The ballots were 2/3 of this phase's instructions.)
+				if (!__any_sync(0xFFFFFFFFu, valid && run)) {
+					if (valid) {
+						const uint32_t sh16 = 16u * (bin & 1u);
+						const uint32_t old = atomicAdd(reinterpret_cast<uint32_t *>(my) + (bin >> 1), 1u << sh16);
+						perm[beg + base[bin] + ((old >> sh16) & 0xFFFFu)] = (uint32_t)(beg + i);
 					}
+					continue;
+				}
+				for (int k = 0; k < nbits; k++) {
+					const bool bit = (bin >> k) & 1u;
+					const unsigned mm = __ballot_sync(0xFFFFFFFFu, bit);
+					peers &= bit ? mm : ~mm;
 				}
 				const int leader = __ffs(peers) - 1;
 				uint32_t prev = 0;

@@ -221,7 +221,7 @@ def test_str_build_wide_row_ids(ctx, sb, O, n, cap, spread):
     _tree_equal(sb.RTreeIndex(ctx, box, rows, cap), O.StrTree(box, rows, cap))
 
 
-@pytest.mark.parametrize("case", ["same_x", "same_xy", "two_x", "grid", "sorted", "reverse", "clustered_rows", "wide_keys"])
+@pytest.mark.parametrize("case", ["same_x", "same_xy", "two_x", "grid", "y_runs", "sorted", "reverse", "clustered_rows", "wide_keys"])
 @pytest.mark.parametrize("path", [0, 1, 2, 3])
 def test_str_build_degenerate_inputs(ctx, sb, O, case, path):
     # the x order is a radix select of the slice-boundary keys + a stable partition (str_partition.cu): inputs whose x keys
@@ -241,6 +241,8 @@ def test_str_build_degenerate_inputs(ctx, sb, O, case, path):
         x = np.where(rng.random(n) < 0.37, 10.0, 20.0)
     elif case == "grid":
         x, y = np.floor(x / 50) * 50, np.floor(y / 25) * 25
+    elif case == "y_runs":
+        y = np.floor(y / 100) * 100  # runs of ~100 equal y keys per slice: every run spans several nodes of 16
     elif case == "sorted":
         x = np.sort(x)
     elif case == "reverse":
