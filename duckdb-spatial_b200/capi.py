@@ -79,6 +79,7 @@ SIGNATURES = {
     "sb_join_unmatched_rows": (i32, [vp, i32, vp, u64, u32, vp, u64, C.POINTER(u64)]),
     "sb_rtree_build_from_blobs": (i32, [vp, i32, vp, vp, u64, vp, u32, C.POINTER(vp), C.POINTER(u64), vp]),
     "sb_rtree_slice_for": (u64, [u64, u32]),
+    "sb_rtree_build_from_points": (i32, [vp, i32, vp, vp, vp, u64, u32, C.POINTER(vp)]),
     "sb_rtree_build_leaf_shard": (i32, [vp, i32, vp, vp, u64, u32, u64, u64, i64, i64, vp, vp]),
     "sb_rtree_from_leaf_level": (i32, [vp, i32, vp, u64, vp, u32, C.POINTER(vp)]),
     "sb_rtree_dump": (i32, [vp, vp, i32, vp, vp, vp, u64, C.POINTER(u64)]),

@@ -394,6 +394,29 @@ extern "C" int sb_rtree_build_str(sb_context *ctx, sb_mem mem, const float *box4
 	return finish(ctx, mem);
 }
 
+extern "C" int sb_rtree_build_from_points(sb_context *ctx, sb_mem mem, const double *x, const double *y,
+                                          const int64_t *row_ids, uint64_t n, uint32_t max_node_capacity, sb_rtree **out) {
+	SB_BEGIN(ctx);
+	SB_ARG(out != nullptr, "out");
+	*out = nullptr;
+	SB_ARG(n == 0 || (x && y && row_ids), "arrays");
+	const double *dx, *dy;
+	const int64_t *dr;
+	SB_TRY(sb_to_device(ctx, mem, x, n, &dx));
+	SB_TRY(sb_to_device(ctx, mem, y, n, &dy));
+	SB_TRY(sb_to_device(ctx, mem, row_ids, n, &dr));
+	sb_rtree *t = nullptr;
+	int s = sbi_rtree_build_str(ctx, nullptr, dr, n, max_node_capacity, &t, dx, dy);
+	if (s != SB_OK) {
+		if (t) {
+			sb_rtree_destroy(t);
+		}
+		return s;
+	}
+	*out = t;
+	return finish(ctx, mem);
+}
+
 extern "C" uint64_t sb_rtree_slice_for(uint64_t n, uint32_t max_node_capacity) {
 	if (n == 0 || max_node_capacity == 0) {
 		return 0;

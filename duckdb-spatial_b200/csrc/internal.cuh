@@ -74,6 +74,21 @@ struct sb_flat {
 	}
 };
 
+// where the STR build reads an entry's BOX_2DF from: the box column, or a POINT_2D column rounded outward on the fly
+// (geometry_t::TryGetCachedBounds point branch + MathUtil::DoubleToFloatDown / Up, as k_bbox_points does)
+struct sb_boxsrc {
+	const float4 *box;
+	const double *x, *y;
+	template <bool POINTS>
+	__device__ __forceinline__ float4 load(uint64_t i) const {
+		if (!POINTS) {
+			return box[i];
+		}
+		const double xv = x[i], yv = y[i];
+		return make_float4(sb_f64_to_f32_down(xv), sb_f64_to_f32_down(yv), sb_f64_to_f32_up(xv), sb_f64_to_f32_up(yv));
+	}
+};
+
 // str_partition.cu: the x order of the STR bulk load as a select + stable partition (no sort)
 struct __align__(32) sb_rec32 { // one entry on its way through the leaf level: a whole 32-byte sector
 	float4 box;
@@ -97,13 +112,14 @@ int sbi_str_select_finish(sb_context *ctx, const uint32_t *xkeys, uint64_t n, sb
 int sbi_str_bin_ids(sb_context *ctx, const uint32_t *xkeys, uint64_t n, const uint32_t *cuts, uint32_t ncut,
                     uint32_t *bins);
 int sbi_str_node_partition(sb_context *ctx, const uint32_t *ykeys, uint64_t n, uint64_t slice, uint32_t cap, uint32_t *perm);
-int sbi_str_partition_rec(sb_context *ctx, const float4 *box, const int64_t *rows, const uint32_t *xkeys,
+int sbi_str_partition_rec(sb_context *ctx, sb_boxsrc box, const int64_t *rows, const uint32_t *xkeys,
                           const uint32_t *ykeys, uint64_t n, const uint32_t *cuts, uint32_t ncut, sb_rec32 *rec_out,
                           uint32_t *ykey_out);
 
 // rtree_str.cu
+// px / py (optional, with box4 == NULL): build straight from a POINT_2D column
 int sbi_rtree_build_str(sb_context *ctx, const float *box4, const int64_t *row_ids, uint64_t n, uint32_t cap,
-                        sb_rtree **out);
+                        sb_rtree **out, const double *px = nullptr, const double *py = nullptr);
 int sbi_rtree_leaf_shard(sb_context *ctx, const float *box4, const int64_t *row_ids, uint64_t n, uint32_t cap,
                          uint64_t slice, uint64_t node_base, int64_t x_key_before, int64_t x_key_after, sb_entry *level0,
                          sb_entry *parents);

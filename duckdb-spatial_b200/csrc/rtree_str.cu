@@ -20,7 +20,8 @@
 // leaf level later picks its y key with a 4-byte gather from this 4n-byte array (L2-resident at 10 M keys) instead
 // of a 16-byte gather from the boxes.
 // hist1 (may be NULL): the 2048-bin histogram of the x keys' top 11 bits, level 1 of the cut-key select (str_partition.cu).
-__global__ void __launch_bounds__(256) k_str_xkeys(const float4 *__restrict__ box, uint64_t n,
+template <bool POINTS>
+__global__ void __launch_bounds__(256) k_str_xkeys(const sb_boxsrc box, uint64_t n,
                                                    uint32_t *__restrict__ keys, uint32_t *__restrict__ ykeys,
                                                    uint32_t *__restrict__ hist1) {
 	__shared__ uint32_t s_h[4 * 2048]; // 4 replicas (lane & 3): float keys share their top bits
@@ -33,7 +34,7 @@ __global__ void __launch_bounds__(256) k_str_xkeys(const float4 *__restrict__ bo
 	uint32_t *mine = s_h + (threadIdx.x & 3u) * 2048;
 	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
 	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-		const float4 b = box[i];
+		const float4 b = box.template load<POINTS>(i);
 		// ST_Centroid::ExecuteBox<float>: (float)min_x + (float)max_x in fp32, spatial_functions_scalar.cpp:1490-1494
 		const uint32_t xk = sb_f32_sort_key(__fadd_rn(b.x, b.z));
 		keys[i] = xk;
@@ -422,9 +423,20 @@ static void str_shape(sb_rtree *t, uint64_t n, uint32_t cap) {
 // whole layer this is the first stage of the build; a shard that holds a contiguous, slice-aligned range of the global x
 // order (rows in ascending global input position, x_key_before / x_key_after = the global cut keys at its two ends,
 // -1 at the ends of the layer) produces exactly its part of the global leaf level (multi-GPU build).
-static int str_leaf_level(sb_context *ctx, const float4 *box, const int64_t *row_ids, uint64_t n, uint32_t cap,
+static int str_leaf_level(sb_context *ctx, sb_boxsrc src, const int64_t *row_ids, uint64_t n, uint32_t cap,
                           uint64_t slice, uint64_t node_base, int64_t x_key_before, int64_t x_key_after, sb_entry *level0,
                           sb_entry *parents, uint32_t **yk_out, uint32_t **ykb_out, uint32_t **yv_out, uint32_t **yvb_out) {
+	// the one-pass record partition reads every box once, in input order: a POINT_2D source is rounded on the fly there.
+	// The bin-id sort + gather form gathers boxes at random: it gets a materialised box column.
+	const uint32_t ncut_host = (uint32_t)((n + slice - 1) / slice - 1) + (x_key_before >= 0 ? 1u : 0u) + (x_key_after >= 0 ? 1u : 0u);
+	const bool one_pass = 2 * (uint64_t)ncut_host + 1 <= SP_MAXBINS && ctx->str_path != 1;
+	sb_boxsrc box = src;
+	if (!box.box && !one_pass) {
+		float4 *mat = nullptr;
+		SB_TRY(ctx->scratch_t(n, &mat));
+		SB_TRY(sbi_bbox_points(ctx, src.x, src.y, n, reinterpret_cast<float *>(mat)));
+		box.box = mat;
+	}
 	uint32_t *xk = nullptr, *yk_in = nullptr;
 	uint32_t *yk = nullptr, *ykb = nullptr, *yv = nullptr, *yvb = nullptr;
 	SB_TRY(ctx->scratch_t(n, &xk));
@@ -438,7 +450,11 @@ static int str_leaf_level(sb_context *ctx, const float4 *box, const int64_t *row
 	SB_TRY(sbi_str_select_begin(ctx, n, slice, x_key_before, x_key_after, &sel));
 	{
 		sb_prof_scope ps(ctx, "str_keys");
-		k_str_xkeys<<<sb_grid(n, 256 * 8, 8), 256, 0, ctx->stream>>>(box, n, xk, yk_in, sel.hist1);
+		if (box.box) {
+			k_str_xkeys<false><<<sb_grid(n, 256 * 8, 8), 256, 0, ctx->stream>>>(box, n, xk, yk_in, sel.hist1);
+		} else {
+			k_str_xkeys<true><<<sb_grid(n, 256 * 8, 8), 256, 0, ctx->stream>>>(box, n, xk, yk_in, sel.hist1);
+		}
 		SB_LAUNCH_CHECK(ctx);
 	}
 	SB_TRY(sbi_str_select_finish(ctx, xk, n, &sel));
@@ -447,7 +463,7 @@ static int str_leaf_level(sb_context *ctx, const float4 *box, const int64_t *row
 	const sb_rec32 *rec = nullptr;
 	int alt = 0;
 	bool iota = true;
-	if (2 * ncut + 1 <= SP_MAXBINS && ctx->str_path != 1) {
+	if (one_pass) {
 		// one pass: the records themselves go to their place in the slice order, y keys beside them
 		sb_rec32 *r = nullptr;
 		SB_TRY(ctx->scratch_t(n, &r));
@@ -491,10 +507,10 @@ static int str_leaf_level(sb_context *ctx, const float4 *box, const int64_t *row
 		sb_prof_scope ps(ctx, "str_pack");
 		const unsigned grid = (unsigned)((nodes + PKW_WARPS - 1) / PKW_WARPS);
 		if (cap <= 128) {
-			k_str_pack_leaf<4><<<grid, PKW_WARPS * 32, 0, ctx->stream>>>(box, row_ids, rec, perm, n, cap, nodes, level0, parents,
+			k_str_pack_leaf<4><<<grid, PKW_WARPS * 32, 0, ctx->stream>>>(box.box, row_ids, rec, perm, n, cap, nodes, level0, parents,
 			                                                            node_base);
 		} else {
-			k_str_pack_leaf<8><<<grid, PKW_WARPS * 32, 0, ctx->stream>>>(box, row_ids, rec, perm, n, cap, nodes, level0, parents,
+			k_str_pack_leaf<8><<<grid, PKW_WARPS * 32, 0, ctx->stream>>>(box.box, row_ids, rec, perm, n, cap, nodes, level0, parents,
 			                                                            node_base);
 		}
 		SB_LAUNCH_CHECK(ctx);
@@ -550,7 +566,7 @@ static int str_upper_levels(sb_context *ctx, sb_rtree *t, sb_entry *parents, sb_
 }
 
 int sbi_rtree_build_str(sb_context *ctx, const float *box4, const int64_t *row_ids, uint64_t n, uint32_t cap,
-                        sb_rtree **out) {
+                        sb_rtree **out, const double *px, const double *py) {
 	SB_ARG(cap >= 4 && cap <= 255, "max_node_capacity must be in [4, 255]");
 	SB_ARG(n < ((uint64_t)1 << 30), "n must be < 2^30");
 	sb_rtree *t = new sb_rtree();
@@ -568,8 +584,9 @@ int sbi_rtree_build_str(sb_context *ctx, const float *box4, const int64_t *row_i
 	SB_TRY(ctx->scratch_t(nodes, &parents));
 	SB_TRY(ctx->scratch_t((nodes + cap - 1) / cap + 1, &parents_b));
 	uint32_t *yk, *ykb, *yv, *yvb;
-	SB_TRY(str_leaf_level(ctx, reinterpret_cast<const float4 *>(box4), row_ids, n, cap, t->slice, 0, -1, -1,
-	                      t->entries + t->offsets[0], parents, &yk, &ykb, &yv, &yvb));
+	const sb_boxsrc src = {reinterpret_cast<const float4 *>(box4), px, py};
+	SB_TRY(str_leaf_level(ctx, src, row_ids, n, cap, t->slice, 0, -1, -1, t->entries + t->offsets[0], parents, &yk, &ykb,
+	                      &yv, &yvb));
 	return str_upper_levels(ctx, t, parents, parents_b, yk, ykb, yv, yvb);
 }
 
@@ -589,8 +606,9 @@ int sbi_rtree_leaf_shard(sb_context *ctx, const float *box4, const int64_t *row_
 	}
 	uint32_t *yk, *ykb, *yv, *yvb;
 	SB_ARG(x_key_before <= 0xFFFFFFFFll && x_key_after <= 0xFFFFFFFFll, "x keys are 32-bit (-1 = none)");
-	return str_leaf_level(ctx, reinterpret_cast<const float4 *>(box4), row_ids, n, cap, slice, node_base, x_key_before,
-	                      x_key_after, level0, parents, &yk, &ykb, &yv, &yvb);
+	const sb_boxsrc src = {reinterpret_cast<const float4 *>(box4), nullptr, nullptr};
+	return str_leaf_level(ctx, src, row_ids, n, cap, slice, node_base, x_key_before, x_key_after, level0, parents, &yk, &ykb,
+	                      &yv, &yvb);
 }
 
 // the whole tree from its leaf entries (global order) and the leaf nodes' entries (node order)

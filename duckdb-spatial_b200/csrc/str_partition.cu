@@ -621,9 +621,10 @@ __device__ __forceinline__ void pd_store16(void *p, float x, float y, float z, f
 #ifndef PS_UNROLL
 #define PS_UNROLL 4
 #endif
-__global__ void __launch_bounds__(PT_THREADS, PS_MIN_CTAS) k_part_scatter(const uint16_t *__restrict__ bins, uint64_t n, uint32_t nb,
+template <bool POINTS>
+__global__ void __launch_bounds__(PT_THREADS, POINTS ? 4 : PS_MIN_CTAS) k_part_scatter(const uint16_t *__restrict__ bins, uint64_t n, uint32_t nb,
                                                                        int nbits, const uint32_t *__restrict__ tile_pos,
-                                                                       const float4 *__restrict__ box,
+                                                                       const sb_boxsrc box,
                                                                        const int64_t *__restrict__ rows,
                                                                        const uint32_t *__restrict__ ykeys,
                                                                        sb_rec32 *__restrict__ rec_out,
@@ -723,7 +724,7 @@ __global__ void __launch_bounds__(PT_THREADS, PS_MIN_CTAS) k_part_scatter(const 
 			const uint32_t b = br[i] & 0xFFFFu;
 			const uint32_t p = (uint32_t)S.doff[b] + my[b] + (br[i] >> 16);
 			g = S.gl[b] + p;
-			lo = box[gi];
+			lo = box.template load<POINTS>(gi);
 			const int64_t r = rows[gi];
 			const uint32_t yk = ykeys[gi];
 			hi = make_float4(__int_as_float((int)(uint32_t)(uint64_t)r), __int_as_float((int)(uint32_t)((uint64_t)r >> 32)),
@@ -754,7 +755,7 @@ __global__ void __launch_bounds__(PT_THREADS, PS_MIN_CTAS) k_part_scatter(const 
 	}
 }
 
-int sbi_str_partition_rec(sb_context *ctx, const float4 *box, const int64_t *rows, const uint32_t *xkeys,
+int sbi_str_partition_rec(sb_context *ctx, sb_boxsrc box, const int64_t *rows, const uint32_t *xkeys,
                           const uint32_t *ykeys, uint64_t n, const uint32_t *cuts, uint32_t ncut, sb_rec32 *rec_out,
                           uint32_t *ykey_out) {
 	const uint32_t nb = 2 * ncut + 1;
@@ -788,7 +789,11 @@ int sbi_str_partition_rec(sb_context *ctx, const float4 *box, const int64_t *row
 	SB_LAUNCH_CHECK(ctx);
 	k_scan_apply<<<nblk, 256, 0, ctx->stream>>>(tile_hist, cells, sums);
 	SB_LAUNCH_CHECK(ctx);
-	k_part_scatter<<<tiles, PT_THREADS, 0, ctx->stream>>>(bins, n, nb, nbits, tile_hist, box, rows, ykeys, rec_out, ykey_out);
+	if (box.box) {
+		k_part_scatter<false><<<tiles, PT_THREADS, 0, ctx->stream>>>(bins, n, nb, nbits, tile_hist, box, rows, ykeys, rec_out, ykey_out);
+	} else {
+		k_part_scatter<true><<<tiles, PT_THREADS, 0, ctx->stream>>>(bins, n, nb, nbits, tile_hist, box, rows, ykeys, rec_out, ykey_out);
+	}
 	SB_LAUNCH_CHECK(ctx);
 	return SB_OK;
 }

@@ -532,6 +532,19 @@ class RTreeIndex:
         self.h = h
         self.cap = max_node_capacity
 
+    @classmethod
+    def from_points(cls, ctx, x, y, row_ids, max_node_capacity=128):
+        """CREATE INDEX over a POINT_2D column: the float boxes are computed inside the build (sb_rtree_build_from_points);
+        same tree as RTreeIndex(ctx, ctx.bbox_from_points(x, y), row_ids)."""
+        self = cls.__new__(cls)
+        self.ctx = ctx
+        self.cap = max_node_capacity
+        h = C.c_void_p()
+        capi.check(ctx.L.sb_rtree_build_from_points(ctx.h, ctx._mem(x, y, row_ids), _ptr(x), _ptr(y), _ptr(row_ids), len(row_ids),
+                                                    max_node_capacity, C.byref(h)))
+        self.h = h
+        return self
+
     @staticmethod
     def leaf_shard(ctx, box4, row_ids, max_node_capacity, slice_size, node_base, x_key_before=-1, x_key_after=-1):
         """multi-GPU build, per rank: leaf entries + node entries (uint8 [., 24]) of a slice-aligned shard of the global x

@@ -157,6 +157,11 @@ SB_API int sb_sort_pairs_u64(sb_context *ctx, sb_mem mem, uint64_t *keys, uint32
  * does (rtree_index_create_logical.cpp:42-72). max_node_capacity in [4, 255] (rtree_index.cpp:30-63). */
 SB_API int sb_rtree_build_str(sb_context *ctx, sb_mem mem, const float *box4, const int64_t *row_ids, uint64_t n,
                               uint32_t max_node_capacity, sb_rtree **out);
+/* CREATE INDEX over a POINT_2D key column: sb_bbox_from_points fused into the build (the outward-rounded BOX_2DF of a
+ * point, geometry_type.hpp:126-145 + math.hpp:19-47, is computed where the build reads it and never stored: 32 bytes of
+ * traffic per key less). Same tree as sb_rtree_build_str over sb_bbox_from_points(x, y), entry for entry. */
+SB_API int sb_rtree_build_from_points(sb_context *ctx, sb_mem mem, const double *x, const double *y, const int64_t *row_ids,
+                                      uint64_t n, uint32_t max_node_capacity, sb_rtree **out);
 /* ---- multi-GPU CREATE INDEX (one process per GPU; the host side is duckdb-spatial_b200/distributed.py) ----------------
  * The reference builds the index in one process (PhysicalCreateRTreeIndex, rtree_index_create_physical.cpp:95-256); past
  * one GPU's memory the ORDER BY becomes a distributed sample sort: every rank ends up with the rows of a contiguous,

@@ -22,7 +22,12 @@ ix, iy = ctx.st_generate_points(1337, n, (0.0, 0.0, 10000.0, 10000.0), device=Tr
 rows = torch.arange(n, dtype=torch.int64, device=dev)
 
 
+FUSED = os.environ.get("C1_FROM_POINTS", "1") == "1"
+
+
 def build():
+    if FUSED:
+        return sb.RTreeIndex.from_points(ctx, ix, iy, rows, cap)
     return sb.RTreeIndex(ctx, ctx.bbox_from_points(ix, iy), rows, cap)
 
 

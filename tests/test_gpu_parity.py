@@ -261,6 +261,25 @@ def test_str_build_degenerate_inputs(ctx, sb, O, case, path):
     _tree_equal(idx, O.StrTree(box, rows, cap))
 
 
+@pytest.mark.parametrize("n,cap,path", [(1, 128, 0), (129, 128, 0), (50_001, 16, 0), (200_000, 128, 0), (50_001, 16, 1)])
+def test_str_build_from_points_equals_build_from_boxes(ctx, sb, O, n, cap, path):
+    # sb_rtree_build_from_points: the float boxes are computed inside the build; host and device memory
+    rng = np.random.default_rng(n)
+    x, y = O.generate_points(17, n, (-500, -500, 500, 500))
+    rows = rng.permutation(n).astype(np.int64)
+    ot = O.StrTree(O.bbox_from_points(x, y), rows, cap)
+    ctx.set_option("str_path", path)
+    try:
+        _tree_equal(sb.RTreeIndex.from_points(ctx, x, y, rows, cap), ot)
+        import torch
+
+        dev = torch.device("cuda", 0)
+        tx, ty, tr = (torch.from_numpy(v).to(dev) for v in (x, y, rows))
+        _tree_equal(sb.RTreeIndex.from_points(ctx, tx, ty, tr, cap), ot)
+    finally:
+        ctx.set_option("str_path", 0)
+
+
 def test_str_empty(ctx, sb):
     idx = sb.RTreeIndex(ctx, np.zeros((0, 4), np.float32), np.zeros(0, np.int64))
     assert idx.nlevels == 0
