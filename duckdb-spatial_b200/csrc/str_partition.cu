@@ -434,12 +434,16 @@ __device__ __forceinline__ uint32_t sp_bin_lut(uint32_t key, const uint32_t *s_c
 	}
 	const uint32_t c = min(SP_LUT - 1, (key - lo) >> shift);
 	uint32_t a = s_lut[c], b = s_lut[c + 1];
-	while (a < b) {
-		const uint32_t mid = (a + b) >> 1;
-		if (s_cuts[mid] < key) {
-			a = mid + 1;
-		} else {
-			b = mid;
+	if (b - a <= 1) { // the usual case: at most one cut key starts in the interval
+		a += (a < b && s_cuts[a] < key) ? 1u : 0u;
+	} else {
+		while (a < b) {
+			const uint32_t mid = (a + b) >> 1;
+			if (s_cuts[mid] < key) {
+				a = mid + 1;
+			} else {
+				b = mid;
+			}
 		}
 	}
 	uint32_t ub = a;
@@ -928,7 +932,8 @@ __device__ __forceinline__ uint32_t ys_distinct(const uint32_t *p, uint32_t nsp,
 
 __global__ void __launch_bounds__(YS_THREADS, 2) k_ysel_slice(const uint32_t *__restrict__ ykeys, uint64_t n, uint64_t slice,
                                                               uint32_t cap, uint32_t stride, uint32_t *__restrict__ ycuts,
-                                                              uint32_t *__restrict__ yluts, uint32_t *__restrict__ perm) {
+                                                              uint32_t *__restrict__ yluts, uint32_t *__restrict__ perm,
+                                                              uint16_t *__restrict__ bins) {
 	extern __shared__ __align__(16) unsigned char ys_raw[];
 	const ys_smem S = ys_carve(ys_raw, stride);
 	const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
@@ -1145,11 +1150,14 @@ __global__ void __launch_bounds__(YS_THREADS, 2) k_ysel_slice(const uint32_t *__
 		const uint32_t chunk = ((m + 1023u) / 1024u) * 32u; // positions per warp, whole rows
 		const uint32_t w0 = warp * chunk;
 		uint32_t *wrow32 = S.tab + (warp * nbp) / 2;
+		// pass A also leaves every key's bin (bit 15: the key equals a cut key) for pass B
 #pragma unroll 4
 		for (uint32_t r = 0; r < chunk; r += 32) {
 			const uint32_t i = w0 + r + lane;
 			if (i < m) {
-				const uint32_t bin = sp_bin_lut(keys[i], S.p2, nsp, s_lut, lo, (uint32_t)shift);
+				bool run;
+				const uint32_t bin = sp_bin_lut(keys[i], S.p2, nsp, s_lut, lo, (uint32_t)shift, &run);
+				bins[beg + i] = (uint16_t)(bin | (run ? 0x8000u : 0u));
 				atomicAdd(&wrow32[bin >> 1], 1u << (16u * (bin & 1u)));
 			}
 		}
@@ -1171,10 +1179,6 @@ __global__ void __launch_bounds__(YS_THREADS, 2) k_ysel_slice(const uint32_t *__
 			}
 		}
 		__syncthreads();
-		int nbits = 0;
-		while ((1u << nbits) < nb) {
-			nbits++;
-		}
 		const unsigned lt_mask = sb_lanemask_lt();
 		uint16_t *my = wh + warp * nbp;
 		// four rows at a time: the key loads and bin searches of a batch overlap, only the cursor updates are sequential
@@ -1183,46 +1187,45 @@ __global__ void __launch_bounds__(YS_THREADS, 2) k_ysel_slice(const uint32_t *__
 #pragma unroll
 			for (int q = 0; q < 4; q++) {
 				const uint32_t i = w0 + r0 + q * 32 + lane;
-				bool run = false;
-				bins4[q] = (r0 + q * 32 < chunk && i < m) ? sp_bin_lut(keys[i], S.p2, nsp, s_lut, lo, (uint32_t)shift, &run) : 0x7FFFFFFFu;
-				bins4[q] |= run ? 0x80000000u : 0u;
+				bins4[q] = (r0 + q * 32 < chunk && i < m) ? bins[beg + i] : 0xFFFFFFFFu;
 			}
 #pragma unroll
 			for (int q = 0; q < 4; q++) {
 				const uint32_t i = w0 + r0 + q * 32 + lane;
-				const bool valid = (bins4[q] & 0x7FFFFFFFu) != 0x7FFFFFFFu;
-				const bool run = bins4[q] >> 31;
-				const uint32_t bin = valid ? bins4[q] & 0x7FFFFFFFu : 0u;
+				const bool valid = bins4[q] != 0xFFFFFFFFu;
+				const bool run = valid && (bins4[q] & 0x8000u);
+				const uint32_t bin = valid ? bins4[q] & 0x7FFFu : 0u;
 				unsigned peers = __ballot_sync(0xFFFFFFFFu, valid);
 				if (peers == 0) {
 					continue; // warp-uniform: an empty row
 				}
 				// Keys strictly between two cut keys lie inside ONE node, whose entries are re-ordered by row id anyway:
-				// their order is free, a shared-memory atomic on the warp's cursor places them. Only rows that hold a key
-				// EQUAL to a cut key (the run of equal keys may straddle a node boundary and is cut by position) take the
-				// stable ballot ranking. (The ballots were 2/3 of this phase's instructions.)
-				if (!__any_sync(0xFFFFFFFFu, valid && run)) {
-					if (valid) {
-						const uint32_t sh16 = 16u * (bin & 1u);
-						const uint32_t old = atomicAdd(reinterpret_cast<uint32_t *>(my) + (bin >> 1), 1u << sh16);
-						perm[beg + base[bin] + ((old >> sh16) & 0xFFFFu)] = (uint32_t)(beg + i);
+				// their order is free, a shared-memory atomic on the warp's cursor places them. Keys EQUAL to a cut key
+				// (one key in 128 is one, so a quarter of the rows hold some) form runs that may straddle a node
+				// boundary and are cut by position: the lanes of each such bin are ranked by one ballot, in lane order,
+				// against the same cursor. (A 10-ballot multi-split of every row was 2/3 of this phase's instructions.)
+				if (valid && !run) {
+					const uint32_t sh16 = 16u * (bin & 1u);
+					const uint32_t old = atomicAdd(reinterpret_cast<uint32_t *>(my) + (bin >> 1), 1u << sh16);
+					perm[beg + base[bin] + ((old >> sh16) & 0xFFFFu)] = (uint32_t)(beg + i);
+				}
+				__syncwarp();
+				unsigned todo = __ballot_sync(0xFFFFFFFFu, valid && run);
+				while (todo) {
+					const int ld = __ffs(todo) - 1;
+					const uint32_t b = __shfl_sync(0xFFFFFFFFu, bin, ld);
+					const bool mine = valid && run && bin == b;
+					const unsigned same = __ballot_sync(0xFFFFFFFFu, mine);
+					uint32_t prev = 0;
+					if ((int)lane == ld) {
+						prev = my[b];
+						my[b] = (uint16_t)(prev + __popc(same));
 					}
-					continue;
-				}
-				for (int k = 0; k < nbits; k++) {
-					const bool bit = (bin >> k) & 1u;
-					const unsigned mm = __ballot_sync(0xFFFFFFFFu, bit);
-					peers &= bit ? mm : ~mm;
-				}
-				const int leader = __ffs(peers) - 1;
-				uint32_t prev = 0;
-				if ((int)lane == leader && valid) {
-					prev = my[bin];
-					my[bin] = (uint16_t)(prev + __popc(peers));
-				}
-				prev = __shfl_sync(0xFFFFFFFFu, prev, leader < 0 ? 0 : leader);
-				if (valid) {
-					perm[beg + base[bin] + prev + __popc(peers & lt_mask)] = (uint32_t)(beg + i);
+					prev = __shfl_sync(0xFFFFFFFFu, prev, ld);
+					if (mine) {
+						perm[beg + base[b] + prev + __popc(same & lt_mask)] = (uint32_t)(beg + i);
+					}
+					todo &= ~same;
 				}
 				__syncwarp();
 			}
@@ -1419,7 +1422,7 @@ int sbi_str_node_partition(sb_context *ctx, const uint32_t *ykeys, uint64_t n, u
 		if (nsp_max) {
 			SB_SMEM_OPTIN(ctx, k_ysel_slice, ys_smem_bytes(YS_NSP));
 			k_ysel_slice<<<nslices, YS_THREADS, ys_smem_bytes(stride), ctx->stream>>>(ykeys, n, slice, cap, stride, ycuts, yluts,
-			                                                                         fused ? perm : nullptr);
+			                                                                         fused ? perm : nullptr, bins);
 			SB_LAUNCH_CHECK(ctx);
 		}
 	}
