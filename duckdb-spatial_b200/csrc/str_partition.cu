@@ -625,9 +625,10 @@ __device__ __forceinline__ void pd_store16(void *p, float x, float y, float z, f
 #ifndef PS_UNROLL
 #define PS_UNROLL 4
 #endif
-template <bool POINTS>
+// NBITS: bits of a bin id (compile-time: the ballot loop has no per-bit predicate)
+template <bool POINTS, int NBITS>
 __global__ void __launch_bounds__(PT_THREADS, POINTS ? 4 : PS_MIN_CTAS) k_part_scatter(const uint16_t *__restrict__ bins, uint64_t n, uint32_t nb,
-                                                                       int nbits, const uint32_t *__restrict__ tile_pos,
+                                                                       const uint32_t *__restrict__ tile_pos,
                                                                        const sb_boxsrc box,
                                                                        const int64_t *__restrict__ rows,
                                                                        const uint32_t *__restrict__ ykeys,
@@ -665,12 +666,10 @@ __global__ void __launch_bounds__(PT_THREADS, POINTS ? 4 : PS_MIN_CTAS) k_part_s
 		const uint32_t b = br[i];
 		unsigned peers = __ballot_sync(0xFFFFFFFFu, valid);
 #pragma unroll
-		for (int k = 0; k < 11; k++) {
-			if (k < nbits) {
-				const bool bit = (b >> k) & 1u;
-				const unsigned m = __ballot_sync(0xFFFFFFFFu, bit);
-				peers &= bit ? m : ~m;
-			}
+		for (int k = 0; k < NBITS; k++) {
+			const bool bit = (b >> k) & 1u;
+			const unsigned m = __ballot_sync(0xFFFFFFFFu, bit);
+			peers &= bit ? m : ~m;
 		}
 		const int leader = __ffs(peers) - 1;
 		uint32_t prev = 0;
@@ -793,11 +792,33 @@ int sbi_str_partition_rec(sb_context *ctx, sb_boxsrc box, const int64_t *rows, c
 	SB_LAUNCH_CHECK(ctx);
 	k_scan_apply<<<nblk, 256, 0, ctx->stream>>>(tile_hist, cells, sums);
 	SB_LAUNCH_CHECK(ctx);
-	if (box.box) {
-		k_part_scatter<false><<<tiles, PT_THREADS, 0, ctx->stream>>>(bins, n, nb, nbits, tile_hist, box, rows, ykeys, rec_out, ykey_out);
-	} else {
-		k_part_scatter<true><<<tiles, PT_THREADS, 0, ctx->stream>>>(bins, n, nb, nbits, tile_hist, box, rows, ykeys, rec_out, ykey_out);
+#define PS_LAUNCH(P, B)                                                                                                \
+	k_part_scatter<P, B><<<tiles, PT_THREADS, 0, ctx->stream>>>(bins, n, nb, tile_hist, box, rows, ykeys, rec_out, ykey_out)
+#define PS_CASE(B)                                                                                                     \
+	case B:                                                                                                            \
+		if (box.box) {                                                                                                 \
+			PS_LAUNCH(false, B);                                                                                       \
+		} else {                                                                                                       \
+			PS_LAUNCH(true, B);                                                                                        \
+		}                                                                                                              \
+		break
+	switch (nbits) {
+		PS_CASE(0);
+		PS_CASE(1);
+		PS_CASE(2);
+		PS_CASE(3);
+		PS_CASE(4);
+		PS_CASE(5);
+		PS_CASE(6);
+		PS_CASE(7);
+		PS_CASE(8);
+		PS_CASE(9);
+		PS_CASE(10);
+	default:
+		PS_CASE(11);
 	}
+#undef PS_CASE
+#undef PS_LAUNCH
 	SB_LAUNCH_CHECK(ctx);
 	return SB_OK;
 }
@@ -811,7 +832,9 @@ int sbi_str_partition_rec(sb_context *ctx, sb_boxsrc box, const int64_t *rows, c
 // node boundary are cut by their order in the slice -- (x bin, input position) -- exactly as the stable segmented sort
 // cut them, so the nodes are the same entry for entry. Replaces four segmented radix passes + their histogram pass.
 // =====================================================================================================================
-#define YS_THREADS 1024
+#ifndef YS_THREADS
+#define YS_THREADS 1024 // 512 measured slower (0.336 vs 0.318 ms for both y phases at C1); must be >= YS_NSP
+#endif
 #define YS_NSP 512u     // ranks per slice (slice / cap - 1 <= 511)
 #define YS_L2 512u      // key bits 20..12
 #define YS_L34 64u      // key bits 11..6 and 5..0
@@ -965,18 +988,25 @@ __global__ void __launch_bounds__(YS_THREADS, 2) k_ysel_slice(const uint32_t *__
 	}
 	__syncthreads();
 	{
-		uint32_t a = 0, b = 0;
+		constexpr int PERB = SEL_L1 / YS_THREADS; // consecutive level-1 bins per thread
+		uint32_t v[PERB], sum = 0;
 #pragma unroll
-		for (int r = 0; r < (int)YS_REPL; r++) {
-			a += S.tab[r * SEL_L1 + 2 * tid];
-			b += S.tab[r * SEL_L1 + 2 * tid + 1];
+		for (int j = 0; j < PERB; j++) {
+			v[j] = 0;
+#pragma unroll
+			for (int r = 0; r < (int)YS_REPL; r++) {
+				v[j] += S.tab[r * SEL_L1 + PERB * tid + j];
+			}
+			sum += v[j];
 		}
 		uint32_t total;
-		const uint32_t ex = sp_block_scan<YS_THREADS>(a + b, S.scan, &total);
-		S.pre1[2 * tid] = ex;
-		S.pre1[2 * tid + 1] = ex + a;
-		S.map1[2 * tid] = 0;
-		S.map1[2 * tid + 1] = 0;
+		uint32_t run = sp_block_scan<YS_THREADS>(sum, S.scan, &total);
+#pragma unroll
+		for (int j = 0; j < PERB; j++) {
+			S.pre1[PERB * tid + j] = run;
+			S.map1[PERB * tid + j] = 0;
+			run += v[j];
+		}
 		if (tid == 0) {
 			S.pre1[SEL_L1] = total;
 		}
@@ -1111,17 +1141,24 @@ __global__ void __launch_bounds__(YS_THREADS, 2) k_ysel_slice(const uint32_t *__
 		const uint32_t lo = S.p2[0], hi = S.p2[nsp - 1];
 		const int bits = 32 - __clz((hi - lo) | 1u);
 		const int shift = bits > 10 ? bits - 10 : 0;
-		const unsigned long long start = (unsigned long long)lo + ((unsigned long long)tid << shift);
-		uint32_t a = 0, b = nsp;
-		while (a < b) {
-			const uint32_t mid = (a + b) >> 1;
-			if ((unsigned long long)S.p2[mid] < start) {
-				a = mid + 1;
-			} else {
-				b = mid;
+		constexpr int PERL = SP_LUT / YS_THREADS; // table entries per thread
+		uint32_t la[PERL];
+#pragma unroll
+		for (int j = 0; j < PERL; j++) {
+			const uint32_t c = tid + j * YS_THREADS;
+			const unsigned long long start = (unsigned long long)lo + ((unsigned long long)c << shift);
+			uint32_t a = 0, b = nsp;
+			while (a < b) {
+				const uint32_t mid = (a + b) >> 1;
+				if ((unsigned long long)S.p2[mid] < start) {
+					a = mid + 1;
+				} else {
+					b = mid;
+				}
 			}
+			la[j] = a;
+			lut[2 + c] = a;
 		}
-		lut[2 + tid] = a;
 		if (tid == 0) {
 			lut[0] = lo;
 			lut[1] = (uint32_t)shift;
@@ -1136,18 +1173,22 @@ __global__ void __launch_bounds__(YS_THREADS, 2) k_ysel_slice(const uint32_t *__
 		// result is stable in (bin, position), no count table, bin array or second launch goes through global memory.
 		uint16_t *s_lut = reinterpret_cast<uint16_t *>(S.pre1); // wpre / firstk / pre1 are dead: their storage holds the table
 		__syncthreads();
-		s_lut[tid] = (uint16_t)a;
+#pragma unroll
+		for (int j = 0; j < PERL; j++) {
+			s_lut[tid + j * YS_THREADS] = (uint16_t)la[j];
+		}
 		if (tid == 0) {
 			s_lut[SP_LUT] = (uint16_t)nsp;
 		}
+		constexpr uint32_t NW = YS_THREADS / 32;
 		const uint32_t nb = 2 * nsp + 1, nbp = (nb + 2) & ~1u; // row length of the per-warp counters (even)
-		uint16_t *wh = reinterpret_cast<uint16_t *>(S.tab);     // [32][nbp]
-		uint32_t *base = S.tab + 16 * nbp;                       // [nb] first place of the bin
-		for (uint32_t i = tid; i < 16 * nbp; i += YS_THREADS) {
+		uint16_t *wh = reinterpret_cast<uint16_t *>(S.tab);     // [NW][nbp]
+		uint32_t *base = S.tab + (NW / 2) * nbp;                 // [nb] first place of the bin
+		for (uint32_t i = tid; i < (NW / 2) * nbp; i += YS_THREADS) {
 			S.tab[i] = 0;
 		}
 		__syncthreads();
-		const uint32_t chunk = ((m + 1023u) / 1024u) * 32u; // positions per warp, whole rows
+		const uint32_t chunk = ((m + YS_THREADS - 1) / YS_THREADS) * 32u; // positions per warp, whole rows
 		const uint32_t w0 = warp * chunk;
 		uint32_t *wrow32 = S.tab + (warp * nbp) / 2;
 		// pass A also leaves every key's bin (bit 15: the key equals a cut key) for pass B
@@ -1163,19 +1204,24 @@ __global__ void __launch_bounds__(YS_THREADS, 2) k_ysel_slice(const uint32_t *__
 		}
 		__syncthreads();
 		{
-			uint32_t run = 0;
-			if (tid < nb) {
+			uint32_t carry = 0;
+			for (uint32_t b0 = 0; b0 < nb; b0 += YS_THREADS) {
+				const uint32_t b = b0 + tid;
+				uint32_t run = 0;
+				if (b < nb) {
 #pragma unroll 8
-				for (uint32_t w = 0; w < 32; w++) {
-					const uint32_t c = wh[w * nbp + tid];
-					wh[w * nbp + tid] = (uint16_t)run;
-					run += c;
+					for (uint32_t w = 0; w < NW; w++) {
+						const uint32_t c = wh[w * nbp + b];
+						wh[w * nbp + b] = (uint16_t)run;
+						run += c;
+					}
 				}
-			}
-			uint32_t tot;
-			const uint32_t e = sp_block_scan<YS_THREADS>(run, S.scan, &tot);
-			if (tid < nb) {
-				base[tid] = e;
+				uint32_t tot;
+				const uint32_t e = sp_block_scan<YS_THREADS>(run, S.scan, &tot);
+				if (b < nb) {
+					base[b] = carry + e;
+				}
+				carry += tot;
 			}
 		}
 		__syncthreads();
