@@ -72,7 +72,12 @@ SB_API int sb_context_trim(sb_context *ctx);
  * "trace": bit 0 = print per-phase wall times to stderr (synchronises at every phase), bit 1 = print the per-chunk
  * timeline of that pipeline's three streams when the call ends (no extra synchronisation). "probe_path" 3 = the cell-sorted
  * bulk probe (v3, what auto picks), 2 = the bucketed v2 kernel. "pip_path": route of sb_join_points_polygons, 0 = auto,
- * 1 = FlatRTree candidates + sb_refine_point_polygon, 2 = polygon-centric kernel. */
+ * 1 = FlatRTree candidates + sb_refine_point_polygon, 2 = polygon-centric kernel. "hist_sample": 1 (default) = the bucket
+ * regions of the cell partition are sized from a 1/16 sample for inputs >= 32 Mi points (exact histogram on overflow),
+ * 0 = always the exact histogram. "str_path": form of the STR leaf level, 0 = auto (select + record partition for the x
+ * order, select + position partition per slice for the leaf nodes; layers above 512 slices sort bin ids and gather),
+ * 1 = always the bin-id sort + gather form, 2 = record partition + segmented y sort, 3 = node partition by separate
+ * kernels; all forms build the same tree (tests run every form). */
 SB_API int sb_context_set_option(sb_context *ctx, const char *key, int64_t value);
 /* number of kernels this context has launched so far (bench.py's gpu_launches) */
 SB_API uint64_t sb_context_launches(const sb_context *ctx);
