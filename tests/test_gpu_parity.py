@@ -280,6 +280,22 @@ def test_str_build_from_points_equals_build_from_boxes(ctx, sb, O, n, cap, path)
         ctx.set_option("str_path", 0)
 
 
+@pytest.mark.parametrize("dist", ["uniform", "wide_keys"])
+def test_str_build_many_slices(ctx, sb, O, dist):
+    # ~350 slices of ~350 nodes each: hundreds of cut keys per select (several chunks of level-1 buckets in the per-slice
+    # select, the global-atomic form of the x select when the keys spread over more than 96 level-1 buckets)
+    rng = np.random.default_rng(5)
+    n, cap = 2_000_003, 16
+    if dist == "uniform":
+        x, y = O.generate_points(23, n, (0, 0, 1000, 1000))
+    else:
+        x = np.ldexp(rng.uniform(1, 2, n), rng.integers(-100, 100, n)) * np.where(rng.random(n) < 0.5, -1.0, 1.0)
+        y = np.ldexp(rng.uniform(1, 2, n), rng.integers(-100, 100, n)) * np.where(rng.random(n) < 0.5, -1.0, 1.0)
+    rows = rng.permutation(n).astype(np.int64)
+    box = O.bbox_from_box2d(x, y, x, y)
+    _tree_equal(sb.RTreeIndex(ctx, box, rows, cap), O.StrTree(box, rows, cap))
+
+
 def test_str_empty(ctx, sb):
     idx = sb.RTreeIndex(ctx, np.zeros((0, 4), np.float32), np.zeros(0, np.int64))
     assert idx.nlevels == 0
