@@ -191,11 +191,24 @@ __global__ void __launch_bounds__(PKW_WARPS * 32, PKW_MIN_CTAS)
 			mx = u > mx ? u : mx;
 		}
 	}
+	{
+		// warp minimum / maximum: when every lane's values share their upper 32 bits (row ids of a node are almost always
+		// within 2^32 of each other) the hardware 32-bit warp reductions do it in two instructions, else 64-bit shuffles
+		const uint32_t hi0 = __shfl_sync(0xFFFFFFFFu, (uint32_t)(mn >> 32), 0); // lane 0 always holds entry 0
+		const bool same_hi = (cnt <= lane || ((uint32_t)(mn >> 32) == hi0 && (uint32_t)(mx >> 32) == hi0));
+		if (__all_sync(0xFFFFFFFFu, same_hi)) {
+			const uint32_t lo_mn = __reduce_min_sync(0xFFFFFFFFu, cnt <= lane ? 0xFFFFFFFFu : (uint32_t)mn);
+			const uint32_t lo_mx = __reduce_max_sync(0xFFFFFFFFu, cnt <= lane ? 0u : (uint32_t)mx);
+			mn = ((unsigned long long)hi0 << 32) | lo_mn;
+			mx = ((unsigned long long)hi0 << 32) | lo_mx;
+		} else {
 #pragma unroll
-	for (int s = 16; s > 0; s >>= 1) {
-		const unsigned long long a = __shfl_xor_sync(0xFFFFFFFFu, mn, s), b = __shfl_xor_sync(0xFFFFFFFFu, mx, s);
-		mn = a < mn ? a : mn;
-		mx = b > mx ? b : mx;
+			for (int s = 16; s > 0; s >>= 1) {
+				const unsigned long long a = __shfl_xor_sync(0xFFFFFFFFu, mn, s), b = __shfl_xor_sync(0xFFFFFFFFu, mx, s);
+				mn = a < mn ? a : mn;
+				mx = b > mx ? b : mx;
+			}
+		}
 	}
 	for (uint32_t i = lane; i < PKW_CNT(256) + 1; i += 32) {
 		s_cnt[i] = 0;
